@@ -1,0 +1,95 @@
+"""ctypes binding of libechr_b200.so (the sm_100a CUDA library behind include/echr_b200.h).
+
+There is deliberately no fallback: if the shared library is missing or a call fails, an exception
+is raised.  torch is only used by callers for device memory and streams; this module passes raw
+pointers.
+"""
+import ctypes
+import os
+import re
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libechr_b200.so")
+HEADER_PATH = os.path.join(os.path.dirname(_HERE), "include", "echr_b200.h")
+
+
+class EchrError(RuntimeError):
+    pass
+
+
+_lib = None
+
+_CTYPES = {
+    "int": ctypes.c_int,
+    "int64_t": ctypes.c_int64,
+    "float": ctypes.c_float,
+    "double": ctypes.c_double,
+    "void*": ctypes.c_void_p,
+    "const void*": ctypes.c_void_p,
+    "float*": ctypes.c_void_p,
+    "const float*": ctypes.c_void_p,
+    "int*": ctypes.c_void_p,
+    "const int*": ctypes.c_void_p,
+    "int64_t*": ctypes.c_void_p,
+    "const int64_t*": ctypes.c_void_p,
+    "const char*": ctypes.c_char_p,
+    "echr_model_t*": ctypes.c_void_p,
+    "echr_model_t**": ctypes.c_void_p,
+    "const echr_model_t*": ctypes.c_void_p,
+    "echr_batch_t*": ctypes.c_void_p,
+    "echr_batch_t**": ctypes.c_void_p,
+    "const echr_batch_t*": ctypes.c_void_p,
+    "const echr_config_t*": ctypes.c_void_p,
+    "echr_config_t*": ctypes.c_void_p,
+    "const echr_host_weights_t*": ctypes.c_void_p,
+    "const echr_batch_desc_t*": ctypes.c_void_p,
+    "echr_timing_t*": ctypes.c_void_p,
+}
+
+
+def declared_symbols(header_path=HEADER_PATH):
+    """Parse include/echr_b200.h: {name: (restype, [argtypes])}. The tests use this to check that
+    the library exports exactly what the header declares."""
+    text = open(header_path).read()
+    text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
+    out = {}
+    for m in re.finditer(r"ECHR_API\s+([\w\s\*]+?)\s*\b(echr_\w+)\s*\(([^;]*?)\)\s*;", text, flags=re.S):
+        ret, name, args = m.group(1).strip(), m.group(2), m.group(3).strip()
+        ret = re.sub(r"\s+", " ", ret).replace(" *", "*")
+        argtypes = []
+        if args and args != "void":
+            for a in args.split(","):
+                a = re.sub(r"\s+", " ", a.strip())
+                # drop the parameter name
+                mm = re.match(r"(.*?)(\w+)$", a)
+                ty = mm.group(1).strip().replace(" *", "*") if mm else a
+                argtypes.append(ty)
+        out[name] = (ret, argtypes)
+    return out
+
+
+def load():
+    """Load the shared library (once). Raises EchrError if it has not been built."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise EchrError(
+            "libechr_b200.so not found at %s — build it with `python -c 'import __graft_entry__ as g; "
+            "g.build()'` or `make -C echr_b200/csrc`. There is no CPU fallback." % LIB_PATH)
+    lib = ctypes.CDLL(LIB_PATH)
+    for name, (ret, args) in declared_symbols().items():
+        fn = getattr(lib, name)  # AttributeError if the library lacks a declared symbol
+        fn.restype = _CTYPES[ret]
+        fn.argtypes = [_CTYPES[a] for a in args]
+    _lib = lib
+    return lib
+
+
+def last_error():
+    return load().echr_last_error().decode("utf-8", "replace")
+
+
+def check(rc, what=""):
+    if rc != 0:
+        raise EchrError("%s failed (%d): %s" % (what or "echr call", rc, last_error()))

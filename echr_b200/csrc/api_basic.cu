@@ -1,0 +1,101 @@
+// C-ABI: library info, error string, fp32 -> bf16 plane conversion, and the stand-alone GEMM entry
+// (used for the one-off projections and by the parity tests of the tensor-core kernel).
+#include "../../include/echr_b200.h"
+#include "gemm_tc.cuh"
+#include "util.cuh"
+
+namespace echr {
+char* last_error_buf() {
+  static thread_local char buf[512] = {0};
+  return buf;
+}
+
+__global__ void split_planes_kernel(const float* __restrict__ src, long long rows, long long cols,
+                                    long long ld_src, __nv_bfloat16* __restrict__ hi,
+                                    __nv_bfloat16* __restrict__ lo, long long ld_dst,
+                                    long long cols_dst) {
+  const long long total = rows * cols_dst;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x) {
+    const long long r = i / cols_dst, c = i - r * cols_dst;
+    const float x = (c < cols) ? src[r * ld_src + c] : 0.f;
+    __nv_bfloat16 h, l;
+    split_bf16(x, h, l);
+    hi[r * ld_dst + c] = h;
+    if (lo != nullptr) lo[r * ld_dst + c] = l;
+  }
+}
+}  // namespace echr
+
+using namespace echr;
+
+extern "C" {
+
+const char* echr_last_error(void) { return last_error_buf(); }
+
+int echr_abi_version(void) { return ECHR_B200_ABI_VERSION; }
+
+int echr_device_check(int device) {
+  cudaDeviceProp prop;
+  ECHR_CUDA(cudaGetDeviceProperties(&prop, device));
+  if (prop.major != 10)
+    return set_error(ECHR_ERR_NO_DEVICE, "device %d is sm_%d%d; this library is built for sm_100a only",
+                     device, prop.major, prop.minor);
+  return ECHR_OK;
+}
+
+int echr_split_bf16(const float* src, int64_t rows, int64_t cols, int64_t ld_src, void* hi, void* lo,
+                    int64_t ld_dst, int64_t cols_dst, void* stream) {
+  ECHR_REQUIRE(src && hi, "echr_split_bf16: null pointer");
+  ECHR_REQUIRE(rows >= 0 && cols >= 0 && cols_dst >= cols && ld_dst >= cols_dst && ld_src >= cols,
+               "echr_split_bf16: bad shape");
+  if (rows == 0 || cols_dst == 0) return ECHR_OK;
+  const long long total = rows * cols_dst;
+  int blocks = (int)((total + 255) / 256);
+  if (blocks > 148 * 16) blocks = 148 * 16;
+  split_planes_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(
+      src, rows, cols, ld_src, (__nv_bfloat16*)hi, (__nv_bfloat16*)lo, ld_dst, cols_dst);
+  ECHR_CUDA(cudaGetLastError());
+  return ECHR_OK;
+}
+
+int echr_gemm_planes(const void* a, int64_t m, int64_t k, int64_t a_ld, int a_planes,
+                     int64_t a_plane_stride, const void* w, int64_t n, int64_t w_ld, int w_planes,
+                     int64_t w_plane_stride, const float* bias, int act, float* out_f32,
+                     int64_t ld_f32, void* out_hi, void* out_lo, int64_t ld_bf, int block_n,
+                     void* stream) {
+  ECHR_REQUIRE(a && w, "echr_gemm_planes: null operand");
+  ECHR_REQUIRE(m > 0 && n > 0 && k > 0 && k % GEMM_BLOCK_K == 0 && k / GEMM_BLOCK_K <= GEMM_MAX_KB,
+               "echr_gemm_planes: K=%lld must be a multiple of 64 and <= %d", (long long)k,
+               GEMM_BLOCK_K * GEMM_MAX_KB);
+  ECHR_REQUIRE((a_planes == 1 || a_planes == 2) && (w_planes == 1 || w_planes == 2) &&
+                   !(a_planes == 1 && w_planes == 2),
+               "echr_gemm_planes: unsupported plane combination a=%d w=%d", a_planes, w_planes);
+  ECHR_REQUIRE(block_n == 128 || block_n == 16, "echr_gemm_planes: block_n must be 16 or 128");
+  ECHR_REQUIRE(m < (1ll << 31) && n < (1ll << 31), "echr_gemm_planes: dimension too large");
+  GemmParams P;
+  memset(&P, 0, sizeof(P));
+  GemmProblem& pb = P.prob[0];
+  const char* err = make_tmap_bf16(&pb.tmA, a, (uint64_t)k, (uint64_t)m, (uint64_t)a_planes,
+                                   (uint64_t)a_ld, (uint64_t)a_plane_stride, GEMM_BLOCK_M);
+  if (err) return set_error(ECHR_ERR_CUDA, "echr_gemm_planes: A: %s", err);
+  err = make_tmap_bf16(&pb.tmW, w, (uint64_t)k, (uint64_t)n, (uint64_t)w_planes, (uint64_t)w_ld,
+                       (uint64_t)w_plane_stride, (uint32_t)block_n);
+  if (err) return set_error(ECHR_ERR_CUDA, "echr_gemm_planes: W: %s", err);
+  pb.M = (int)m;
+  pb.N = (int)n;
+  pb.num_kb = (int)(k / GEMM_BLOCK_K);
+  pb.act = act;
+  for (int i = 0; i < pb.num_kb; ++i) pb.a_kb[i] = (uint16_t)i;
+  pb.bias = bias;
+  pb.out_f32 = out_f32;
+  pb.ld_f32 = ld_f32;
+  pb.out_hi = (__nv_bfloat16*)out_hi;
+  pb.out_lo = (__nv_bfloat16*)out_lo;
+  pb.ld_bf = ld_bf;
+  ECHR_CUDA(gemm_launch(P, 1, (int)m, (int)n, a_planes, w_planes, block_n, EPI_STORE, 1,
+                        (cudaStream_t)stream));
+  return ECHR_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,87 @@
+// Host side of the tcgen05 GEMM: tensor-map encoding (driver entry point fetched at run time so
+// the library has no link-time libcuda dependency) and the template dispatch table.
+#include "gemm_tc.cuh"
+
+#include <mutex>
+
+namespace echr {
+
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*,
+                                  const cuuint64_t*, const cuuint64_t*, const cuuint32_t*,
+                                  const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static EncodeTiledFn get_encode_fn() {
+  static EncodeTiledFn fn = nullptr;
+  static std::once_flag once;
+  std::call_once(once, [] {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &qres) ==
+            cudaSuccess &&
+        qres == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<EncodeTiledFn>(p);
+  });
+  return fn;
+}
+
+const char* make_tmap_bf16(CUtensorMap* out, const void* ptr, uint64_t cols, uint64_t rows,
+                           uint64_t planes, uint64_t ld_elems, uint64_t plane_stride_elems,
+                           uint32_t box_rows) {
+  EncodeTiledFn fn = get_encode_fn();
+  if (!fn) return "cuTensorMapEncodeTiled entry point not available";
+  if ((reinterpret_cast<uintptr_t>(ptr) & 15) != 0) return "tensor map base not 16-byte aligned";
+  if ((ld_elems * 2) % 16 != 0 || (plane_stride_elems * 2) % 16 != 0)
+    return "tensor map strides must be multiples of 16 bytes";
+  if (box_rows == 0 || box_rows > 256) return "tensor map box rows out of range";
+  cuuint64_t gdim[3] = {cols, rows, planes};
+  cuuint64_t gstr[2] = {ld_elems * 2, plane_stride_elems * 2};
+  cuuint32_t box[3] = {static_cast<cuuint32_t>(GEMM_BLOCK_K), box_rows, 1};
+  cuuint32_t estr[3] = {1, 1, 1};
+  CUresult r = fn(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, const_cast<void*>(ptr), gdim, gstr, box,
+                  estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                  CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) return "cuTensorMapEncodeTiled failed";
+  return nullptr;
+}
+
+template <int A, int W, int BN, int EPI, int TOPK>
+static cudaError_t launch_one(const GemmParams& P, dim3 grid, cudaStream_t stream) {
+  using Cfg = GemmCfg<A, W, BN>;
+  auto kern = gemm_tc_kernel<A, W, BN, EPI, TOPK>;
+  static bool attr_set = false;  // per instantiation
+  if (!attr_set) {
+    cudaError_t e =
+        cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES);
+    if (e != cudaSuccess) return e;
+    attr_set = true;
+  }
+  kern<<<grid, GEMM_THREADS, Cfg::SMEM_BYTES, stream>>>(P);
+  return cudaGetLastError();
+}
+
+template <int A, int W>
+static cudaError_t launch_aw(const GemmParams& P, dim3 grid, int block_n, int epi, int topk,
+                             cudaStream_t stream) {
+  if (epi == EPI_STORE && block_n == 128) return launch_one<A, W, 128, EPI_STORE, 1>(P, grid, stream);
+  if (epi == EPI_STORE && block_n == 16) return launch_one<A, W, 16, EPI_STORE, 1>(P, grid, stream);
+  if (epi == EPI_LSTM && block_n == 128) return launch_one<A, W, 128, EPI_LSTM, 1>(P, grid, stream);
+  if (epi == EPI_LOGITS && block_n == 128 && topk == 1)
+    return launch_one<A, W, 128, EPI_LOGITS, 1>(P, grid, stream);
+  if (epi == EPI_LOGITS && block_n == 128 && topk == 4)
+    return launch_one<A, W, 128, EPI_LOGITS, 4>(P, grid, stream);
+  return cudaErrorInvalidValue;
+}
+
+cudaError_t gemm_launch(const GemmParams& P, int groups, int max_m, int max_n, int a_terms,
+                        int w_terms, int block_n, int epi, int topk, cudaStream_t stream) {
+  if (groups < 1 || groups > GEMM_MAX_GROUPS || max_m <= 0 || max_n <= 0)
+    return cudaErrorInvalidValue;
+  dim3 grid((max_n + block_n - 1) / block_n, (max_m + GEMM_BLOCK_M - 1) / GEMM_BLOCK_M, groups);
+  if (a_terms == 1 && w_terms == 1) return launch_aw<1, 1>(P, grid, block_n, epi, topk, stream);
+  if (a_terms == 2 && w_terms == 1) return launch_aw<2, 1>(P, grid, block_n, epi, topk, stream);
+  if (a_terms == 2 && w_terms == 2) return launch_aw<2, 2>(P, grid, block_n, epi, topk, stream);
+  return cudaErrorInvalidValue;
+}
+
+}  // namespace echr

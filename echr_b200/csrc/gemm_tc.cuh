@@ -1,0 +1,367 @@
+// Warp-specialised tcgen05 GEMM for sm_100a:   D[M x N] = A[M x K] * W[N x K]^T   (bf16 in, fp32 acc)
+//
+//   * A (activations: decode rows) and W (weights, nn.Linear layout [out, in]) are both K-major.
+//   * Operands may be given as one or two bf16 "planes" (hi, lo) so that hi+lo carries an fp32
+//     value to 16 mantissa bits; the kernel then issues hi*hi (+ lo*hi) (+ hi*lo) into the same
+//     TMEM accumulator.  A_TERMS/W_TERMS = 1 is the plain bf16 product.
+//   * TMA (SWIZZLE_128B boxes of 64 K-elements) -> smem ring -> tcgen05.mma (M=128, N=BLOCK_N,
+//     K=16) issued by one thread -> fp32 accumulator in TMEM -> 4 epilogue warps (tcgen05.ld).
+//   * The K loop of one problem may walk over non-contiguous 64-column blocks of a wide
+//     activation matrix (table a_kb[]): this is how the LSTM layers read [x_t | context | h].
+//   * Up to GEMM_MAX_GROUPS independent problems per launch (blockIdx.z).
+//
+// Epilogues (one thread owns one output row = TMEM lane, so row reductions need no shuffles):
+//   EPI_STORE : + bias, optional tanh, store fp32 and/or bf16 hi/lo planes.
+//   EPI_LSTM  : columns are gate-interleaved (i,f,g,o of one hidden unit adjacent); applies the
+//               LSTMCell update (reference: nn.LSTMCell in models/OldModel_NEW.py:780-782,
+//               809-817) and writes c (fp32) and h (bf16 hi/lo planes).
+//   EPI_LOGITS: + bias, mask padded vocabulary, per-row/per-tile {sum-exp, top-K} partials for the
+//               fused log-softmax / argmax / beam top-k (reference: OldModel_NEW.py:136,158).
+#pragma once
+#include <cuda.h>
+#include "ptx.cuh"
+
+namespace echr {
+
+constexpr int GEMM_BLOCK_M = 128;
+constexpr int GEMM_BLOCK_K = 64;
+constexpr int GEMM_MAX_KB = 32;
+constexpr int GEMM_MAX_GROUPS = 3;
+constexpr int GEMM_THREADS = 256;
+
+enum : int { EPI_STORE = 0, EPI_LSTM = 1, EPI_LOGITS = 2 };
+enum : int { ACT_NONE = 0, ACT_TANH = 1, ACT_TANH_FAST = 2 };
+
+struct GemmProblem {
+  CUtensorMap tmA;  // 3-D {K cols, M rows, planes}, box {64, 128, 1}, SWIZZLE_128B
+  CUtensorMap tmW;  // 3-D {K cols, N rows, planes}, box {64, BLOCK_N, 1}, SWIZZLE_128B
+  int M;            // valid rows of A / D
+  int N;            // valid columns of D (rows of W)
+  int num_kb;       // K / 64
+  int act;          // EPI_STORE activation
+  uint16_t a_kb[GEMM_MAX_KB];  // A column-block index for each k-block
+  const float* bias;           // [N] (EPI_LSTM: gate-interleaved order)
+  // EPI_STORE
+  float* out_f32;
+  long long ld_f32;
+  __nv_bfloat16* out_hi;
+  __nv_bfloat16* out_lo;
+  long long ld_bf;
+  // EPI_LSTM
+  const float* c_in;   // [M, H]
+  float* c_out;        // [M, H]
+  const int* parent;   // optional row indirection for c_in
+  int hidden;          // H (N == 4H)
+  // EPI_LOGITS
+  float* partial;      // [M, n_tiles, REC]
+  float* logits_out;   // optional [M, ld_logits]
+  long long ld_logits;
+};
+
+struct GemmParams {
+  GemmProblem prob[GEMM_MAX_GROUPS];
+};
+
+template <int TOPK>
+struct LogitRec {
+  // words: [0]=sum-exp relative to val[0]; [1..TOPK]=values (descending); [1+TOPK..2*TOPK]=indices
+  static constexpr int WORDS = (TOPK == 1) ? 4 : 12;
+};
+
+template <int A_TERMS, int W_TERMS, int BLOCK_N>
+struct GemmCfg {
+  static constexpr int A_PLANE_BYTES = GEMM_BLOCK_M * GEMM_BLOCK_K * 2;  // 16 KB
+  static constexpr int W_PLANE_BYTES = BLOCK_N * GEMM_BLOCK_K * 2;
+  static constexpr int STAGE_BYTES = A_TERMS * A_PLANE_BYTES + W_TERMS * W_PLANE_BYTES;
+  static constexpr int STAGES_RAW = (196 * 1024) / STAGE_BYTES;
+  static constexpr int STAGES = STAGES_RAW > 8 ? 8 : STAGES_RAW;
+  static constexpr int TMEM_COLS = BLOCK_N <= 32 ? 32 : (BLOCK_N <= 64 ? 64 : (BLOCK_N <= 128 ? 128 : 256));
+  static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 /*align slack*/ + 256 /*barriers*/;
+};
+
+__device__ __forceinline__ float apply_act(float x, int act) {
+  if (act == ACT_TANH) return tanhf(x);
+  if (act == ACT_TANH_FAST) {
+    float y;
+    asm("tanh.approx.f32 %0, %1;" : "=f"(y) : "f"(x));
+    return y;
+  }
+  return x;
+}
+
+template <int A_TERMS, int W_TERMS, int BLOCK_N, int EPI, int TOPK>
+__global__ void __launch_bounds__(GEMM_THREADS, 1)
+gemm_tc_kernel(const __grid_constant__ GemmParams P) {
+  using Cfg = GemmCfg<A_TERMS, W_TERMS, BLOCK_N>;
+  const GemmProblem& pb = P.prob[blockIdx.z];
+  const int n_tile = blockIdx.x;
+  const int m_tile = blockIdx.y;
+  if (n_tile * BLOCK_N >= pb.N || m_tile * GEMM_BLOCK_M >= pb.M) return;  // whole CTA leaves
+
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  const uint32_t bar_base = smem_base + Cfg::STAGES * Cfg::STAGE_BYTES;
+  // barriers: full[s] at +8*s, empty[s] at +64+8*s, tmem_full at +128, tmem ptr at +136
+  auto full_bar = [&](int s) { return bar_base + 8u * s; };
+  auto empty_bar = [&](int s) { return bar_base + 64u + 8u * s; };
+  const uint32_t tmem_full_bar = bar_base + 128u;
+  const uint32_t tmem_ptr_smem = bar_base + 136u;
+  volatile uint32_t* tmem_ptr_generic =
+      reinterpret_cast<volatile uint32_t*>(smem_raw + (tmem_ptr_smem - smem_u32(smem_raw)));
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const int num_kb = pb.num_kb;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&pb.tmA);
+    tma_prefetch_desc(&pb.tmW);
+  }
+  if (warp == 1 && lane == 0) {
+    for (int s = 0; s < Cfg::STAGES; ++s) {
+      mbar_init(full_bar(s), 1);
+      mbar_init(empty_bar(s), 1);
+    }
+    mbar_init(tmem_full_bar, 1);
+    fence_mbar_init();
+  }
+  if (warp == 2) tmem_alloc<Cfg::TMEM_COLS>(tmem_ptr_smem);
+  tc_fence_before_sync();
+  __syncthreads();
+  tc_fence_after_sync();
+  const uint32_t tmem_base = *tmem_ptr_generic;
+
+  if (warp == 0) {
+    // ===================== TMA producer =====================
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int kb = 0; kb < num_kb; ++kb) {
+        mbar_wait(empty_bar(stage), phase ^ 1u);
+        const uint32_t sa = smem_base + stage * Cfg::STAGE_BYTES;
+        const uint32_t sw = sa + A_TERMS * Cfg::A_PLANE_BYTES;
+        mbar_arrive_expect_tx(full_bar(stage), Cfg::STAGE_BYTES);
+        const int a_col = static_cast<int>(pb.a_kb[kb]) * GEMM_BLOCK_K;
+#pragma unroll
+        for (int t = 0; t < A_TERMS; ++t)
+          tma_load_3d(sa + t * Cfg::A_PLANE_BYTES, &pb.tmA, full_bar(stage), a_col,
+                      m_tile * GEMM_BLOCK_M, t);
+#pragma unroll
+        for (int t = 0; t < W_TERMS; ++t)
+          tma_load_3d(sw + t * Cfg::W_PLANE_BYTES, &pb.tmW, full_bar(stage), kb * GEMM_BLOCK_K,
+                      n_tile * BLOCK_N, t);
+        if (++stage == Cfg::STAGES) { stage = 0; phase ^= 1u; }
+      }
+    }
+  } else if (warp == 1) {
+    // ===================== MMA issuer (single thread) =====================
+    if (lane == 0) {
+      constexpr uint32_t idesc = umma_idesc_bf16_m128(BLOCK_N);
+      int stage = 0;
+      uint32_t phase = 0;
+      uint32_t accum = 0;
+      for (int kb = 0; kb < num_kb; ++kb) {
+        mbar_wait(full_bar(stage), phase);
+        tc_fence_after_sync();
+        const uint32_t sa = smem_base + stage * Cfg::STAGE_BYTES;
+        const uint32_t sw = sa + A_TERMS * Cfg::A_PLANE_BYTES;
+        const uint64_t a_hi = umma_desc_k_sw128(sa);
+        const uint64_t w_hi = umma_desc_k_sw128(sw);
+#pragma unroll
+        for (int k = 0; k < GEMM_BLOCK_K / 16; ++k) {
+          const uint64_t koff = static_cast<uint64_t>(k * 2);  // 32 B per K=16 step, >>4
+          umma_bf16(tmem_base, a_hi + koff, w_hi + koff, idesc, accum);
+          accum = 1;
+          if (A_TERMS == 2) {
+            const uint64_t a_lo = umma_desc_k_sw128(sa + Cfg::A_PLANE_BYTES);
+            umma_bf16(tmem_base, a_lo + koff, w_hi + koff, idesc, 1);
+          }
+          if (W_TERMS == 2) {
+            const uint64_t w_lo = umma_desc_k_sw128(sw + Cfg::W_PLANE_BYTES);
+            umma_bf16(tmem_base, a_hi + koff, w_lo + koff, idesc, 1);
+          }
+        }
+        umma_commit(empty_bar(stage));  // frees the smem slot when these MMAs retire
+        if (++stage == Cfg::STAGES) { stage = 0; phase ^= 1u; }
+      }
+      umma_commit(tmem_full_bar);  // accumulator complete
+    }
+  } else if (warp >= 4) {
+    // ===================== epilogue: 4 warps, thread = one output row =====================
+    const int q = warp & 3;  // TMEM lane quarter this warp may access
+    const int row = m_tile * GEMM_BLOCK_M + q * 32 + lane;
+    const bool row_ok = row < pb.M;
+    mbar_wait(tmem_full_bar, 0);
+    tc_fence_after_sync();
+    const uint32_t t_row = tmem_base + (static_cast<uint32_t>(q * 32) << 16);
+    const int col0 = n_tile * BLOCK_N;
+
+    if constexpr (EPI == EPI_STORE) {
+      constexpr int CH = BLOCK_N >= 32 ? 32 : 16;
+#pragma unroll 1
+      for (int c = 0; c < BLOCK_N / CH; ++c) {
+        float v[32];
+        if constexpr (CH == 32) tmem_ld_32x32(t_row + c * CH, v);
+        else tmem_ld_32x16(t_row + c * CH, v);
+        tmem_ld_wait();
+        const int cb = col0 + c * CH;
+        if (row_ok) {
+#pragma unroll
+          for (int i = 0; i < CH; ++i) {
+            float x = v[i];
+            if (pb.bias != nullptr && cb + i < pb.N) x += __ldg(pb.bias + cb + i);
+            v[i] = apply_act(x, pb.act);
+          }
+          const bool full = (cb + CH <= pb.N);
+          if (pb.out_f32 != nullptr) {
+            float* o = pb.out_f32 + static_cast<long long>(row) * pb.ld_f32 + cb;
+            if (full && ((reinterpret_cast<uintptr_t>(o) & 15) == 0)) {
+#pragma unroll
+              for (int i = 0; i < CH; i += 4)
+                *reinterpret_cast<float4*>(o + i) = make_float4(v[i], v[i + 1], v[i + 2], v[i + 3]);
+            } else {
+              for (int i = 0; i < CH; ++i)
+                if (cb + i < pb.N) o[i] = v[i];
+            }
+          }
+          if (pb.out_hi != nullptr) {
+            __nv_bfloat16* oh = pb.out_hi + static_cast<long long>(row) * pb.ld_bf + cb;
+            __nv_bfloat16* ol =
+                pb.out_lo ? pb.out_lo + static_cast<long long>(row) * pb.ld_bf + cb : nullptr;
+            for (int i = 0; i < CH; ++i) {
+              if (cb + i < pb.N) {
+                __nv_bfloat16 h, l;
+                split_bf16(v[i], h, l);
+                oh[i] = h;
+                if (ol) ol[i] = l;
+              }
+            }
+          }
+        }
+      }
+    } else if constexpr (EPI == EPI_LSTM) {
+      const int H = pb.hidden;
+      const int src_row = (row_ok && pb.parent != nullptr) ? pb.parent[row] : row;
+#pragma unroll 1
+      for (int c = 0; c < BLOCK_N / 32; ++c) {
+        float v[32];
+        tmem_ld_32x32(t_row + c * 32, v);
+        tmem_ld_wait();
+        if (row_ok) {
+          const int cb = col0 + c * 32;  // gate-interleaved column, multiple of 32
+          const int j0 = cb >> 2;        // first hidden unit of this chunk (8 units)
+          const float4* bp = reinterpret_cast<const float4*>(pb.bias + cb);
+          const float4* cp =
+              reinterpret_cast<const float4*>(pb.c_in + static_cast<long long>(src_row) * H + j0);
+          float cprev[8];
+          {
+            const float4 c0 = __ldg(cp), c1 = __ldg(cp + 1);
+            cprev[0] = c0.x; cprev[1] = c0.y; cprev[2] = c0.z; cprev[3] = c0.w;
+            cprev[4] = c1.x; cprev[5] = c1.y; cprev[6] = c1.z; cprev[7] = c1.w;
+          }
+          float cn[8];
+          __align__(16) __nv_bfloat16 hh[8];
+          __align__(16) __nv_bfloat16 hl[8];
+#pragma unroll
+          for (int u = 0; u < 8; ++u) {
+            const float4 b = __ldg(bp + u);
+            const float gi = sigmoid_acc(v[4 * u + 0] + b.x);
+            const float gf = sigmoid_acc(v[4 * u + 1] + b.y);
+            const float gg = tanhf(v[4 * u + 2] + b.z);
+            const float go = sigmoid_acc(v[4 * u + 3] + b.w);
+            const float cc = gf * cprev[u] + gi * gg;
+            cn[u] = cc;
+            split_bf16(go * tanhf(cc), hh[u], hl[u]);
+          }
+          float4* co = reinterpret_cast<float4*>(pb.c_out + static_cast<long long>(row) * H + j0);
+          co[0] = make_float4(cn[0], cn[1], cn[2], cn[3]);
+          co[1] = make_float4(cn[4], cn[5], cn[6], cn[7]);
+          *reinterpret_cast<uint4*>(pb.out_hi + static_cast<long long>(row) * pb.ld_bf + j0) =
+              *reinterpret_cast<const uint4*>(hh);
+          if (pb.out_lo != nullptr)
+            *reinterpret_cast<uint4*>(pb.out_lo + static_cast<long long>(row) * pb.ld_bf + j0) =
+                *reinterpret_cast<const uint4*>(hl);
+        }
+      }
+    } else {  // EPI_LOGITS
+      float tv[TOPK];
+      int ti[TOPK];
+#pragma unroll
+      for (int k = 0; k < TOPK; ++k) { tv[k] = -INFINITY; ti[k] = 0x7fffffff; }
+      // pass 1: bias, mask, optional store, running top-K (ascending column scan: ties keep the
+      // lower index, like torch.max on the reference path)
+#pragma unroll 1
+      for (int c = 0; c < BLOCK_N / 32; ++c) {
+        float v[32];
+        tmem_ld_32x32(t_row + c * 32, v);
+        tmem_ld_wait();
+        const int cb = col0 + c * 32;
+#pragma unroll
+        for (int i = 0; i < 32; ++i) {
+          const int col = cb + i;
+          const float x = (col < pb.N) ? v[i] + __ldg(pb.bias + col) : -INFINITY;
+          v[i] = x;
+          if (x > tv[TOPK - 1]) {
+#pragma unroll
+            for (int k = TOPK - 1; k >= 1; --k) {
+              const bool shift = x > tv[k - 1];
+              const bool here = !shift && (x > tv[k]);
+              tv[k] = shift ? tv[k - 1] : (here ? x : tv[k]);
+              ti[k] = shift ? ti[k - 1] : (here ? col : ti[k]);
+            }
+            if (x > tv[0]) { tv[0] = x; ti[0] = col; }
+          }
+        }
+        if (row_ok && pb.logits_out != nullptr) {
+          float* o = pb.logits_out + static_cast<long long>(row) * pb.ld_logits + cb;
+          for (int i = 0; i < 32; ++i)
+            if (cb + i < pb.N) o[i] = v[i];
+        }
+      }
+      // pass 2: sum of exp relative to the tile maximum
+      float se = 0.f;
+#pragma unroll 1
+      for (int c = 0; c < BLOCK_N / 32; ++c) {
+        float v[32];
+        tmem_ld_32x32(t_row + c * 32, v);
+        tmem_ld_wait();
+        const int cb = col0 + c * 32;
+#pragma unroll
+        for (int i = 0; i < 32; ++i) {
+          const int col = cb + i;
+          if (col < pb.N) se += expf(v[i] + __ldg(pb.bias + col) - tv[0]);
+        }
+      }
+      if (row_ok) {
+        const int n_tiles = (pb.N + BLOCK_N - 1) / BLOCK_N;
+        float* rec = pb.partial +
+                     (static_cast<long long>(row) * n_tiles + n_tile) * LogitRec<TOPK>::WORDS;
+        rec[0] = se;
+#pragma unroll
+        for (int k = 0; k < TOPK; ++k) {
+          rec[1 + k] = tv[k];
+          rec[1 + TOPK + k] = __int_as_float(ti[k]);
+        }
+      }
+    }
+    tc_fence_before_sync();
+  }
+
+  __syncthreads();
+  if (warp == 2) {
+    tc_fence_after_sync();
+    tmem_dealloc<Cfg::TMEM_COLS>(tmem_base);
+  }
+}
+
+// ---------------------------------------------------------------- host side
+// Returns nullptr on success or a static error string.
+const char* make_tmap_bf16(CUtensorMap* out, const void* ptr, uint64_t cols, uint64_t rows,
+                           uint64_t planes, uint64_t ld_elems, uint64_t plane_stride_elems,
+                           uint32_t box_rows);
+
+// Dispatch to the instantiated kernel. grid = (max n_tiles, max m_tiles, groups).
+cudaError_t gemm_launch(const GemmParams& P, int groups, int max_m, int max_n, int a_terms,
+                        int w_terms, int block_n, int epi, int topk, cudaStream_t stream);
+
+}  // namespace echr

@@ -1,0 +1,88 @@
+"""Parity of the tcgen05 GEMM (echr_gemm_planes) against an fp64 torch matmul of the same planes."""
+import pytest
+import torch
+
+from echr_b200 import _lib
+
+pytestmark = pytest.mark.gpu
+
+
+def _split(x, cols_dst):
+    lib = _lib.load()
+    rows, cols = x.shape
+    hi = torch.empty(rows, cols_dst, dtype=torch.bfloat16, device=x.device)
+    lo = torch.empty_like(hi)
+    _lib.check(lib.echr_split_bf16(x.data_ptr(), rows, cols, x.stride(0), hi.data_ptr(), lo.data_ptr(),
+                                   cols_dst, cols_dst, torch.cuda.current_stream().cuda_stream), "split")
+    return hi, lo
+
+
+def _gemm(a_planes, w_planes, m, n, k, bias, act, block_n, want_bf=False):
+    lib = _lib.load()
+    dev = a_planes.device
+    out = torch.full((m, n), float("nan"), dtype=torch.float32, device=dev)
+    oh = ol = None
+    if want_bf:
+        oh = torch.zeros(m, n, dtype=torch.bfloat16, device=dev)
+        ol = torch.zeros(m, n, dtype=torch.bfloat16, device=dev)
+    rc = lib.echr_gemm_planes(
+        a_planes.data_ptr(), m, k, a_planes.stride(1), a_planes.shape[0], a_planes.stride(0),
+        w_planes.data_ptr(), n, w_planes.stride(1), w_planes.shape[0], w_planes.stride(0),
+        bias.data_ptr() if bias is not None else None, act, out.data_ptr(), out.stride(0),
+        oh.data_ptr() if want_bf else None, ol.data_ptr() if want_bf else None, n, block_n,
+        torch.cuda.current_stream().cuda_stream)
+    _lib.check(rc, "gemm")
+    torch.cuda.synchronize()
+    return out, oh, ol
+
+
+@pytest.mark.parametrize("m,n,k,block_n", [
+    (128, 128, 64, 128), (128, 128, 512, 128), (256, 512, 1024, 128), (3, 2048, 1536, 128),
+    (300, 5748, 1536, 128), (77, 16, 512, 16), (1000, 16, 512, 16), (130, 500, 128, 128),
+])
+@pytest.mark.parametrize("terms", [(1, 1), (2, 1), (2, 2)])
+def test_gemm_planes(m, n, k, block_n, terms):
+    torch.manual_seed(m * 7 + n * 3 + k)
+    dev = torch.device("cuda:0")
+    a = torch.randn(m, k, device=dev)
+    w = torch.randn(n, k, device=dev) * 0.05
+    bias = torch.randn(n, device=dev)
+    ah, al = _split(a, k)
+    wh, wl = _split(w, k)
+    at, wt = terms
+    a_pl = torch.stack([ah, al])[:at].contiguous()
+    w_pl = torch.stack([wh, wl])[:wt].contiguous()
+    out, _, _ = _gemm(a_pl, w_pl, m, n, k, bias, 0, block_n)
+    # exact model of what the kernel computes (products of bf16 values are exact in fp32; only the
+    # accumulation order differs), evaluated in fp64
+    A = [ah.double(), al.double()]
+    W = [wh.double(), wl.double()]
+    ref = A[0] @ W[0].T
+    if at == 2:
+        ref = ref + A[1] @ W[0].T
+    if wt == 2:
+        ref = ref + A[0] @ W[1].T
+    ref = ref + bias.double()
+    err = (out.double() - ref).abs().max().item()
+    assert torch.isfinite(out).all()
+    assert err < 2e-4 * max(1.0, ref.abs().max().item()), err
+    if terms == (2, 2):  # fp32-grade: compare with the unsplit fp32 operands
+        full = a.double() @ w.double().T + bias.double()
+        err2 = (out.double() - full).abs().max().item()
+        assert err2 < 1e-4, err2
+
+
+def test_gemm_tanh_and_bf16_out():
+    dev = torch.device("cuda:0")
+    torch.manual_seed(5)
+    m, n, k = 200, 512, 512
+    a = torch.randn(m, k, device=dev)
+    w = torch.randn(n, k, device=dev) * 0.04
+    bias = torch.randn(n, device=dev) * 0.1
+    ah, al = _split(a, k)
+    wh, wl = _split(w, k)
+    out, oh, ol = _gemm(torch.stack([ah, al]), torch.stack([wh, wl]), m, n, k, bias, 1, 128, want_bf=True)
+    ref = torch.tanh(a.double() @ w.double().T + bias.double())
+    assert (out.double() - ref).abs().max().item() < 1e-4
+    rec = oh.double() + ol.double()
+    assert (rec - out.double()).abs().max().item() < 1e-5
