@@ -23,15 +23,12 @@ _CTYPES = {
     "int": ctypes.c_int,
     "int64_t": ctypes.c_int64,
     "float": ctypes.c_float,
-    "double": ctypes.c_double,
     "void*": ctypes.c_void_p,
     "const void*": ctypes.c_void_p,
     "float*": ctypes.c_void_p,
     "const float*": ctypes.c_void_p,
-    "int*": ctypes.c_void_p,
-    "const int*": ctypes.c_void_p,
-    "int64_t*": ctypes.c_void_p,
-    "const int64_t*": ctypes.c_void_p,
+    "int32_t*": ctypes.c_void_p,
+    "const int32_t*": ctypes.c_void_p,
     "const char*": ctypes.c_char_p,
     "echr_model_t*": ctypes.c_void_p,
     "echr_model_t**": ctypes.c_void_p,
@@ -40,11 +37,55 @@ _CTYPES = {
     "echr_batch_t**": ctypes.c_void_p,
     "const echr_batch_t*": ctypes.c_void_p,
     "const echr_config_t*": ctypes.c_void_p,
-    "echr_config_t*": ctypes.c_void_p,
-    "const echr_host_weights_t*": ctypes.c_void_p,
+    "const echr_weights_t*": ctypes.c_void_p,
+    "const echr_capacity_t*": ctypes.c_void_p,
     "const echr_batch_desc_t*": ctypes.c_void_p,
-    "echr_timing_t*": ctypes.c_void_p,
 }
+
+
+class Config(ctypes.Structure):
+    _fields_ = [("vocab_size", ctypes.c_int32), ("seq_length", ctypes.c_int32), ("a_terms", ctypes.c_int32),
+                ("w_terms", ctypes.c_int32), ("clip_bf16", ctypes.c_int32)]
+
+
+# field order of echr_weights_t (include/echr_b200.h) -> state_dict key
+WEIGHT_FIELDS = [
+    ("event_emb_w", "fusion_model.event_emb.weight"), ("event_emb_b", "fusion_model.event_emb.bias"),
+    ("pos_fc1_w", "fusion_model.enc_attn.pair_pos_fc1.weight"), ("pos_fc1_b", "fusion_model.enc_attn.pair_pos_fc1.bias"),
+    ("pos_fc2_w", "fusion_model.enc_attn.pair_pos_fc2.weight"), ("pos_fc2_b", "fusion_model.enc_attn.pair_pos_fc2.bias"),
+    ("query_w", "fusion_model.enc_attn.query_1.weight"), ("query_b", "fusion_model.enc_attn.query_1.bias"),
+    ("key_w", "fusion_model.enc_attn.key_1.weight"), ("key_b", "fusion_model.enc_attn.key_1.bias"),
+    ("out_w", "fusion_model.enc_attn.linear_out_1.weight"), ("out_b", "fusion_model.enc_attn.linear_out_1.bias"),
+    ("embed_w", "lm_model.embed.weight"),
+    ("logit_w", "lm_model.logit.weight"), ("logit_b", "lm_model.logit.bias"),
+    ("lstm_w_ih0", "lm_model.core.layer0.weight_ih"), ("lstm_w_ih1", "lm_model.core.layer1.weight_ih"),
+    ("lstm_w_ih2", "lm_model.core.layer2.weight_ih"),
+    ("lstm_w_hh0", "lm_model.core.layer0.weight_hh"), ("lstm_w_hh1", "lm_model.core.layer1.weight_hh"),
+    ("lstm_w_hh2", "lm_model.core.layer2.weight_hh"),
+    ("lstm_b_ih0", "lm_model.core.layer0.bias_ih"), ("lstm_b_ih1", "lm_model.core.layer1.bias_ih"),
+    ("lstm_b_ih2", "lm_model.core.layer2.bias_ih"),
+    ("lstm_b_hh0", "lm_model.core.layer0.bias_hh"), ("lstm_b_hh1", "lm_model.core.layer1.bias_hh"),
+    ("lstm_b_hh2", "lm_model.core.layer2.bias_hh"),
+    ("ctx2att_w", "lm_model.core.attention.ctx2att.weight"), ("ctx2att_b", "lm_model.core.attention.ctx2att.bias"),
+    ("h2att_w", "lm_model.core.attention.h2att.weight"), ("h2att_b", "lm_model.core.attention.h2att.bias"),
+    ("alpha_w", "lm_model.core.attention.alpha_net.weight"),
+]
+
+
+class Weights(ctypes.Structure):
+    _fields_ = [(name, ctypes.c_void_p) for name, _ in WEIGHT_FIELDS]
+
+
+class Capacity(ctypes.Structure):
+    _fields_ = [("max_videos", ctypes.c_int64), ("max_clips", ctypes.c_int64), ("max_events", ctypes.c_int64),
+                ("max_pairs", ctypes.c_int64), ("max_rows", ctypes.c_int64)]
+
+
+class BatchDesc(ctypes.Structure):
+    _fields_ = [("n_videos", ctypes.c_int32), ("n_events", ctypes.c_int32),
+                ("host_clip_offsets", ctypes.c_void_p), ("host_event_video", ctypes.c_void_p),
+                ("host_event_start", ctypes.c_void_p), ("host_event_end", ctypes.c_void_p),
+                ("host_event_ind", ctypes.c_void_p)]
 
 
 def declared_symbols(header_path=HEADER_PATH):

@@ -1,0 +1,195 @@
+"""Drop-in mirror of the reference's caption-generation call surface, running on the B200 engine.
+
+Mirrors (same names, arguments, return contract, parameter names/shapes):
+  CaptionGenerator            CaptionGenerator.py:7-53          forward(..., mode='eval'|'train')
+  MA_Attention8 (fusion)      models/MA_attention_8_NEW.py:9-49
+  ThreestreamModel (lm)       models/OldModel_NEW.py:18-187,1040-1043   forward / sample
+  setup_lm / setup_fusion     models/__init__.py:6-29
+
+The nn.Parameters here are only the checkpoint container (`load_state_dict(strict=True)` of a
+reference `cg_model` works); all arithmetic runs in libechr_b200.so.  Additive API:
+`caption_batch(videos, beam_size)` for many videos per call and `beam_size` in `forward(mode='eval')`.
+"""
+import torch
+from torch import nn
+
+from . import config as _config
+from .engine import BatchLayout, Engine
+
+
+class _EncAttn(nn.Module):  # attention_module_multi_head parameters (MA:82-100)
+    def __init__(self, opt):
+        super().__init__()
+        d, g = opt.d_feats, opt.n_head
+        self.pair_pos_fc1 = nn.Linear(opt.d_pos_vec, opt.d_pos_vec)
+        self.pair_pos_fc2 = nn.Linear(opt.d_pos_vec, g)
+        self.query_1 = nn.Linear(d, d)
+        self.key_1 = nn.Linear(d, d)
+        self.linear_out_1 = nn.Conv2d(g * d, opt.d_o, kernel_size=(1, 1), stride=1, groups=g)
+
+
+class MA_Attention8(nn.Module):
+    def __init__(self, opt):
+        super().__init__()
+        _config.validate(opt)
+        self.h2a_layer = nn.Linear(10, 10)  # dead parameter of the reference (MA:23)
+        self.event_emb = nn.Linear(opt.TSRM_input_dim, opt.d_feats)
+        self.enc_attn = _EncAttn(opt)
+        self.output_dim, self.use_posit, self.d_pos_vec, self.fST_type = opt.d_o, opt.use_posit, opt.d_pos_vec, "fST0"
+
+
+class _Attention(nn.Module):  # OldModel_NEW.py:366-374
+    def __init__(self, opt):
+        super().__init__()
+        self.ctx2att = nn.Linear(opt.clip_context_dim, opt.CG_att_hid_size)
+        self.h2att = nn.Linear(opt.CG_rnn_size, opt.CG_att_hid_size)
+        self.alpha_net = nn.Linear(opt.CG_att_hid_size, 1)
+
+
+class _ThreeStreamCore(nn.Module):  # OldModel_NEW.py:762-788
+    def __init__(self, opt):
+        super().__init__()
+        e, h = opt.CG_input_encoding_size, opt.CG_rnn_size
+        self.layer0 = nn.LSTMCell(opt.event_context_dim + e, h)
+        self.layer1 = nn.LSTMCell(opt.clip_context_dim + e, h)
+        self.layer2 = nn.LSTMCell(opt.video_context_dim + e, h)
+        self.fusion_layer = nn.Linear(3 * h, h)  # dead parameter of the reference (OldModel_NEW.py:783)
+        self.attention = _Attention(opt)
+
+
+class ThreestreamModel(nn.Module):
+    def __init__(self, opt):
+        super().__init__()
+        _config.validate(opt)
+        self.opt = opt
+        self.vocab_size, self.seq_length = opt.CG_vocab_size, opt.CG_seq_length
+        self.embed = nn.Embedding(self.vocab_size + 1, opt.CG_input_encoding_size)
+        self.logit = nn.Linear(3 * opt.CG_rnn_size, self.vocab_size + 1)
+        self.core = _ThreeStreamCore(opt)
+
+
+def setup_lm(opt):
+    if opt.caption_model != "three_stream":
+        raise ValueError("echr_b200 implements caption_model='three_stream' only")
+    return ThreestreamModel(opt)
+
+
+def setup_fusion(opt):
+    if opt.fusion_model != "TSRM8":
+        raise ValueError("fusion model not supported: {}".format(opt.fusion_model))
+    return MA_Attention8(opt)
+
+
+def trim_greedy(tokens, logp):
+    """The reference stops (and so trims the columns) at the first step where every row of the call
+    has already produced token 0 (OldModel_NEW.py:175-183); an empty result is ([], [])."""
+    alive = (tokens != 0).any(dim=0)
+    dead = (~alive).nonzero()
+    ncols = int(dead[0]) if dead.numel() else tokens.shape[1]
+    if ncols == 0:
+        return [], []
+    return tokens[:, :ncols].long(), logp[:, :ncols]
+
+
+class CaptionGenerator(nn.Module):
+    def __init__(self, opt, precision="fp32"):
+        super().__init__()
+        self.opt = _config.validate(opt)
+        self.precision = precision
+        self.fusion_model = setup_fusion(opt)
+        self.lm_model = setup_lm(opt)
+        self._engine = None
+        self.eval()
+
+    # -- engine lifetime: rebuilt whenever the parameters may have changed
+    def _invalidate(self):
+        if self._engine is not None:
+            self._engine.close()
+        self._engine = None
+
+    def load_state_dict(self, state_dict, strict=True, **kw):
+        out = super().load_state_dict(state_dict, strict=strict, **kw)
+        self._invalidate()
+        return out
+
+    def _apply(self, fn, *a, **kw):
+        out = super()._apply(fn, *a, **kw)
+        self._invalidate()
+        return out
+
+    def set_precision(self, precision):
+        self.precision = precision
+        self._invalidate()
+
+    @property
+    def engine(self):
+        if self._engine is None:
+            dev = next(self.parameters()).device
+            if dev.type != "cuda":
+                raise RuntimeError("echr_b200.CaptionGenerator has no CPU path: call .cuda() first")
+            self._engine = Engine(self.state_dict(), self.opt.CG_vocab_size, self.opt.CG_seq_length,
+                                  precision=self.precision, device=dev)
+        return self._engine
+
+    # -- batched API (additive)
+    def _stage(self, videos, beam):
+        eng = self.engine
+        layout = BatchLayout([v[1].shape[0] for v in videos], [v[3] for v in videos], [v[4] for v in videos])
+        f32 = lambda t: t.to(device=eng.device, dtype=torch.float32)
+        c3d = torch.cat([f32(v[1]) for v in videos], 0).contiguous()
+        tap = torch.cat([f32(v[0]) for v in videos], 0).contiguous()
+        lda = torch.stack([f32(v[2]).reshape(-1) for v in videos], 0).contiguous()
+        eng.set_inputs(layout, c3d, tap, lda, beam=beam)
+        eng.encode()
+        return eng, layout
+
+    def caption_batch(self, videos, beam_size=1):
+        """videos: list of (tap_feats[T,512], c3d_feats[T,500], lda_feats[100], ind_select_list,
+        soi_select_list).  Returns one (seq, logp) per video with the reference's per-call trimming
+        (greedy) or (seq[N,S], logp[N,S], score[N]) per video (beam_size > 1)."""
+        with torch.no_grad():
+            eng, layout = self._stage(videos, max(1, beam_size))
+            if beam_size > 1:
+                tokens, logp, score = eng.decode_beam(beam_size)
+            else:
+                tokens, logp = eng.decode_greedy()
+            out, r0 = [], 0
+            for n in layout.events_per_video:
+                if beam_size > 1:
+                    out.append((tokens[r0:r0 + n].long(), logp[r0:r0 + n], score[r0:r0 + n]))
+                elif n == 0:
+                    out.append(([], []))
+                else:
+                    out.append(trim_greedy(tokens[r0:r0 + n], logp[r0:r0 + n]))
+                r0 += n
+            return out
+
+    def teacher_forced(self, videos, seqs):
+        """Per-video teacher-forced log-probs (the `mode='train'` forward), no trimming."""
+        with torch.no_grad():
+            eng, layout = self._stage(videos, 1)
+            seq = torch.cat([s.to(eng.device) for s in seqs], 0)
+            lp = eng.teacher_forced(seq)
+            out, r0 = [], 0
+            for n in layout.events_per_video:
+                out.append(lp[r0:r0 + n])
+                r0 += n
+            return out
+
+    # -- the reference's call (eval_utils.py:129, train.py:298)
+    def forward(self, tap_feats, c3d_feats, lda_feats, lm_labels, ind_select_list, soi_select_list, mode="train",
+                beam_size=1):
+        video = (tap_feats, c3d_feats, lda_feats, list(ind_select_list), [list(s) for s in soi_select_list])
+        if mode == "eval":
+            res = self.caption_batch([video], beam_size)[0]
+            return res if beam_size > 1 else (res[0], res[1])
+        if mode == "train":
+            # OldModel.forward (OldModel_NEW.py:98-130): stop at the first all-zero label column i >= 1
+            seq = lm_labels
+            cols = seq.shape[1]
+            for i in range(1, cols - 1):
+                if int(seq[:, i].sum()) == 0:
+                    cols = i + 1
+                    break
+            return self.teacher_forced([video], [seq[:, :cols]])[0]
+        raise ValueError("echr_b200.CaptionGenerator supports mode='eval' and mode='train' (forward only); got %r" % mode)

@@ -1,7 +1,7 @@
 // C-ABI: library info, error string, fp32 -> bf16 plane conversion, and the stand-alone GEMM entry
 // (used for the one-off projections and by the parity tests of the tensor-core kernel).
 #include "../../include/echr_b200.h"
-#include "gemm_tc.cuh"
+#include "engine.cuh"
 #include "util.cuh"
 
 namespace echr {
@@ -10,21 +10,6 @@ char* last_error_buf() {
   return buf;
 }
 
-__global__ void split_planes_kernel(const float* __restrict__ src, long long rows, long long cols,
-                                    long long ld_src, __nv_bfloat16* __restrict__ hi,
-                                    __nv_bfloat16* __restrict__ lo, long long ld_dst,
-                                    long long cols_dst) {
-  const long long total = rows * cols_dst;
-  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
-       i += (long long)gridDim.x * blockDim.x) {
-    const long long r = i / cols_dst, c = i - r * cols_dst;
-    const float x = (c < cols) ? src[r * ld_src + c] : 0.f;
-    __nv_bfloat16 h, l;
-    split_bf16(x, h, l);
-    hi[r * ld_dst + c] = h;
-    if (lo != nullptr) lo[r * ld_dst + c] = l;
-  }
-}
 }  // namespace echr
 
 using namespace echr;
@@ -49,13 +34,20 @@ int echr_split_bf16(const float* src, int64_t rows, int64_t cols, int64_t ld_src
   ECHR_REQUIRE(src && hi, "echr_split_bf16: null pointer");
   ECHR_REQUIRE(rows >= 0 && cols >= 0 && cols_dst >= cols && ld_dst >= cols_dst && ld_src >= cols,
                "echr_split_bf16: bad shape");
-  if (rows == 0 || cols_dst == 0) return ECHR_OK;
-  const long long total = rows * cols_dst;
-  int blocks = (int)((total + 255) / 256);
-  if (blocks > 148 * 16) blocks = 148 * 16;
-  split_planes_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(
-      src, rows, cols, ld_src, (__nv_bfloat16*)hi, (__nv_bfloat16*)lo, ld_dst, cols_dst);
-  ECHR_CUDA(cudaGetLastError());
+  ECHR_CUDA(launch_split(src, rows, cols, ld_src, (bf16*)hi, (bf16*)lo, ld_dst, cols_dst, (cudaStream_t)stream));
+  return ECHR_OK;
+}
+
+int echr_attention_step(const float* q, const void* proj, const void* clip, int64_t ld_clip,
+                        int clip_bf16, const float* alpha, const int32_t* row_start,
+                        const int32_t* row_len, int64_t rows, float* out_f32, void* out_hi,
+                        void* out_lo, int64_t ld_bf, void* stream) {
+  ECHR_REQUIRE(q && proj && clip && alpha && row_start && row_len, "echr_attention_step: null pointer");
+  ECHR_REQUIRE(rows >= 0 && rows < (1ll << 31), "echr_attention_step: bad row count");
+  ECHR_REQUIRE(ld_clip >= ECHR_VIDEO_DIM && (ld_clip * (clip_bf16 ? 2 : 4)) % 16 == 0,
+               "echr_attention_step: clip row stride must be >= 500 and 16-byte aligned");
+  ECHR_CUDA(launch_attention(q, proj, clip, ld_clip, clip_bf16, alpha, row_start, row_len, rows, out_f32,
+                             (bf16*)out_hi, (bf16*)out_lo, ld_bf, (cudaStream_t)stream));
   return ECHR_OK;
 }
 
@@ -95,6 +87,7 @@ int echr_gemm_planes(const void* a, int64_t m, int64_t k, int64_t a_ld, int a_pl
   pb.ld_bf = ld_bf;
   ECHR_CUDA(gemm_launch(P, 1, (int)m, (int)n, a_planes, w_planes, block_n, EPI_STORE, 1,
                         (cudaStream_t)stream));
+  count_launch();
   return ECHR_OK;
 }
 

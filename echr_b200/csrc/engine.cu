@@ -1,0 +1,703 @@
+// Engine: weight packing (echr_model_*), batch workspace (echr_batch_*), the encode pipeline and
+// the device-resident decode loops, exported through the C-ABI of include/echr_b200.h.
+#include "engine.cuh"
+#include "util.cuh"
+
+#include <atomic>
+#include <new>
+#include <vector>
+
+using namespace echr;
+
+namespace echr {
+
+static std::atomic<long long> g_launches{0};
+void count_launch(int n) { g_launches.fetch_add(n, std::memory_order_relaxed); }
+
+// ---------------------------------------------------------------- arena helper
+struct Arena {
+  size_t off = 0;
+  char* base = nullptr;
+  template <typename T>
+  T* take(size_t n) {
+    off = (off + 255) & ~(size_t)255;
+    T* p = base ? reinterpret_cast<T*>(base + off) : nullptr;
+    off += n * sizeof(T);
+    return p;
+  }
+  PlaneMat planes(int64_t planes_, int64_t rows, int64_t ld) {
+    PlaneMat m;
+    m.rows = rows; m.ld = ld; m.planes = planes_;
+    m.p = take<bf16>((size_t)planes_ * rows * ld);
+    return m;
+  }
+};
+
+// ---------------------------------------------------------------- packing kernels
+// LSTM weights: dst[4j+g, :] = [ w_ih[g*512+j, 0:512] | w_ih[g*512+j, 512:512+ctx] (zero padded to
+// ctx_pad) | w_hh[g*512+j, :] ]  (gate-interleaved rows so that one epilogue thread sees i,f,g,o of
+// a hidden unit in adjacent accumulator columns).
+__global__ void pack_lstm_kernel(const float* __restrict__ w_ih, const float* __restrict__ w_hh, int ctx,
+                                 int ctx_pad, bf16* __restrict__ hi, bf16* __restrict__ lo) {
+  const int K = HID + ctx_pad + HID;
+  const int in_ih = HID + ctx;
+  const long long total = (long long)GATES * K;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x) {
+    const int n = (int)(i / K), c = (int)(i - (long long)n * K);
+    const int j = n >> 2, g = n & 3;
+    const int src = g * HID + j;
+    float x = 0.f;
+    if (c < HID) x = w_ih[(long long)src * in_ih + c];
+    else if (c < HID + ctx_pad) { if (c - HID < ctx) x = w_ih[(long long)src * in_ih + c]; }
+    else x = w_hh[(long long)src * HID + (c - HID - ctx_pad)];
+    bf16 h, l;
+    split_bf16(x, h, l);
+    hi[i] = h;
+    if (lo != nullptr) lo[i] = l;
+  }
+}
+__global__ void pack_lstm_bias_kernel(const float* __restrict__ b_ih, const float* __restrict__ b_hh,
+                                      float* __restrict__ out) {
+  const int n = blockIdx.x * blockDim.x + threadIdx.x;
+  if (n < GATES) {
+    const int j = n >> 2, g = n & 3;
+    out[n] = b_ih[g * HID + j] + b_hh[g * HID + j];
+  }
+}
+__global__ void copy_f32_kernel(const float* __restrict__ src, float* __restrict__ dst, int n) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) dst[i] = src ? src[i] : 0.f;
+}
+
+static cudaError_t copy_vec(const float* src, float* dst, int n, cudaStream_t st) {
+  copy_f32_kernel<<<(n + 255) / 256, 256, 0, st>>>(src, dst, n);
+  return cudaGetLastError();
+}
+
+// ---------------------------------------------------------------- GEMM problem helper
+struct GemmSpec {
+  const PlaneMat* A = nullptr;
+  int a_col0 = 0;        // first activation column (multiple of 64) when the k-blocks are contiguous
+  const int* a_kb = nullptr;  // or an explicit k-block table
+  int M = 0;
+  const PlaneMat* W = nullptr;
+  int N = 0, K = 0;
+  const float* bias = nullptr;
+  int act = ACT_NONE;
+  float* out_f32 = nullptr;
+  long long ld_f32 = 0;
+  bf16* out_hi = nullptr;
+  bf16* out_lo = nullptr;
+  long long ld_bf = 0;
+  // LSTM
+  const float* c_in = nullptr;
+  float* c_out = nullptr;
+  // logits
+  float* partial = nullptr;
+  float* logits_out = nullptr;
+  long long ld_logits = 0;
+};
+
+static const char* fill_problem(GemmProblem& pb, const GemmSpec& s, int a_terms, int w_terms, int block_n) {
+  if (s.K % GEMM_BLOCK_K != 0 || s.K / GEMM_BLOCK_K > GEMM_MAX_KB) return "bad K";
+  if (a_terms > s.A->planes || w_terms > s.W->planes) return "operand has too few planes";
+  const char* err = make_tmap_bf16(&pb.tmA, s.A->p, (uint64_t)s.A->ld, (uint64_t)s.M, (uint64_t)s.A->planes,
+                                   (uint64_t)s.A->ld, (uint64_t)s.A->plane_stride(), GEMM_BLOCK_M);
+  if (err) return err;
+  err = make_tmap_bf16(&pb.tmW, s.W->p, (uint64_t)s.W->ld, (uint64_t)s.N, (uint64_t)s.W->planes,
+                       (uint64_t)s.W->ld, (uint64_t)s.W->plane_stride(), (uint32_t)block_n);
+  if (err) return err;
+  pb.M = s.M;
+  pb.N = s.N;
+  pb.num_kb = s.K / GEMM_BLOCK_K;
+  pb.act = s.act;
+  for (int i = 0; i < pb.num_kb; ++i)
+    pb.a_kb[i] = (uint16_t)(s.a_kb ? s.a_kb[i] : s.a_col0 / GEMM_BLOCK_K + i);
+  pb.bias = s.bias;
+  pb.out_f32 = s.out_f32;
+  pb.ld_f32 = s.ld_f32;
+  pb.out_hi = s.out_hi;
+  pb.out_lo = s.out_lo;
+  pb.ld_bf = s.ld_bf;
+  pb.c_in = s.c_in;
+  pb.c_out = s.c_out;
+  pb.parent = nullptr;
+  pb.hidden = HID;
+  pb.partial = s.partial;
+  pb.logits_out = s.logits_out;
+  pb.ld_logits = s.ld_logits;
+  return nullptr;
+}
+
+static int run_gemm(const GemmSpec* specs, int groups, int a_terms, int w_terms, int block_n, int epi,
+                    int topk, cudaStream_t st, const char* what) {
+  GemmParams P;
+  memset(&P, 0, sizeof(P));
+  int max_m = 0, max_n = 0;
+  for (int g = 0; g < groups; ++g) {
+    const char* err = fill_problem(P.prob[g], specs[g], a_terms, w_terms, block_n);
+    if (err) return set_error(ECHR_ERR_CUDA, "%s: %s", what, err);
+    if (specs[g].M > max_m) max_m = specs[g].M;
+    if (specs[g].N > max_n) max_n = specs[g].N;
+  }
+  if (max_m == 0) return ECHR_OK;
+  cudaError_t e = gemm_launch(P, groups, max_m, max_n, a_terms, w_terms, block_n, epi, topk, st);
+  if (e != cudaSuccess) return set_error(ECHR_ERR_CUDA, "%s: launch failed: %s", what, cudaGetErrorString(e));
+  count_launch();
+  return ECHR_OK;
+}
+
+static int check_device() {
+  int dev = 0;
+  ECHR_CUDA(cudaGetDevice(&dev));
+  return echr_device_check(dev);
+}
+
+}  // namespace echr
+
+#define ECHR_TRY(expr)          \
+  do {                          \
+    int _rc = (expr);           \
+    if (_rc != 0) return _rc;   \
+  } while (0)
+
+// =============================================================================================
+// Model
+// =============================================================================================
+static void model_layout(echr_model* m, Arena& a) {
+  const int wt = m->cfg.w_terms;
+  m->w_event_emb = a.planes(wt, HID, FEAT_PAD);
+  m->w_qky = a.planes(wt, 3 * HID, HID);
+  m->w_fc1 = a.planes(wt, HID, HID);
+  m->w_fc2 = a.planes(wt, ECHR_HEADS, HID);
+  m->w_ctx2att = a.planes(wt, HID, CLIP_PAD);
+  m->w_h2att = a.planes(wt, HID, HID);
+  m->w_lstm[0] = a.planes(wt, GATES, HID + HID + HID);
+  m->w_lstm[1] = a.planes(wt, GATES, HID + CLIP_PAD + HID);
+  m->w_lstm[2] = a.planes(wt, GATES, HID + VID_PAD + HID);
+  m->w_logit = a.planes(wt, m->V1, 3 * HID);
+  m->embed = a.planes(2, m->V1, HID);
+  m->b_event_emb = a.take<float>(HID);
+  m->b_qky = a.take<float>(3 * HID);
+  m->b_fc1 = a.take<float>(HID);
+  m->b_fc2 = a.take<float>(ECHR_HEADS);
+  m->b_ctx2att = a.take<float>(HID);
+  m->b_h2att = a.take<float>(HID);
+  for (int l = 0; l < 3; ++l) m->b_lstm[l] = a.take<float>(GATES);
+  m->b_logit = a.take<float>(m->V1);
+  m->b_out = a.take<float>(HID);
+  m->alpha = a.take<float>(HID);
+}
+
+static cudaError_t pack_linear(const float* w, int out_f, int in_f, const PlaneMat& dst, int row0,
+                               cudaStream_t st) {
+  bf16* hi = dst.plane(0) + (long long)row0 * dst.ld;
+  bf16* lo = dst.planes > 1 ? dst.plane(1) + (long long)row0 * dst.ld : nullptr;
+  return launch_split(w, out_f, in_f, in_f, hi, lo, dst.ld, dst.ld, st);
+}
+
+extern "C" int echr_model_create(const echr_config_t* config, const echr_weights_t* w, void* stream,
+                                 echr_model_t** out) {
+  ECHR_REQUIRE(config && w && out, "echr_model_create: null argument");
+  ECHR_REQUIRE(config->vocab_size >= 1 && config->vocab_size <= 65535, "echr_model_create: vocab_size out of range");
+  ECHR_REQUIRE(config->seq_length >= 1 && config->seq_length <= 64, "echr_model_create: seq_length out of range");
+  ECHR_REQUIRE((config->a_terms == 1 || config->a_terms == 2) && (config->w_terms == 1 || config->w_terms == 2) &&
+                   !(config->a_terms == 1 && config->w_terms == 2),
+               "echr_model_create: (a_terms, w_terms) must be (1,1), (2,1) or (2,2)");
+  const float* const* wp = reinterpret_cast<const float* const*>(w);
+  for (size_t i = 0; i < sizeof(echr_weights_t) / sizeof(float*); ++i)
+    ECHR_REQUIRE(wp[i] != nullptr, "echr_model_create: weight pointer %d is null", (int)i);
+  ECHR_TRY(check_device());
+  cudaStream_t st = (cudaStream_t)stream;
+  echr_model* m = new (std::nothrow) echr_model();
+  ECHR_REQUIRE(m, "echr_model_create: out of host memory");
+  memset(m, 0, sizeof(*m));
+  m->cfg = *config;
+  m->V1 = config->vocab_size + 1;
+  Arena sizing;
+  model_layout(m, sizing);
+  cudaError_t e = cudaMalloc(&m->arena, sizing.off + 256);
+  if (e != cudaSuccess) {
+    delete m;
+    return set_error(ECHR_ERR_CUDA, "echr_model_create: cudaMalloc(%zu) failed: %s", sizing.off, cudaGetErrorString(e));
+  }
+  Arena a;
+  a.base = reinterpret_cast<char*>(m->arena);
+  model_layout(m, a);
+#define PK(expr)                                                                        \
+  do {                                                                                  \
+    cudaError_t _e = (expr);                                                            \
+    if (_e != cudaSuccess) {                                                            \
+      cudaFree(m->arena);                                                               \
+      delete m;                                                                         \
+      return set_error(ECHR_ERR_CUDA, "echr_model_create: %s: %s", #expr, cudaGetErrorString(_e)); \
+    }                                                                                   \
+  } while (0)
+  PK(cudaMemsetAsync(m->arena, 0, sizing.off, st));
+  PK(pack_linear(w->event_emb_w, HID, ECHR_VIDEO_DIM + HID, m->w_event_emb, 0, st));
+  PK(pack_linear(w->query_w, HID, HID, m->w_qky, 0, st));
+  PK(pack_linear(w->key_w, HID, HID, m->w_qky, HID, st));
+  PK(pack_linear(w->out_w, HID, HID, m->w_qky, 2 * HID, st));
+  PK(pack_linear(w->pos_fc1_w, HID, HID, m->w_fc1, 0, st));
+  PK(pack_linear(w->pos_fc2_w, ECHR_HEADS, HID, m->w_fc2, 0, st));
+  PK(pack_linear(w->ctx2att_w, HID, ECHR_VIDEO_DIM, m->w_ctx2att, 0, st));
+  PK(pack_linear(w->h2att_w, HID, HID, m->w_h2att, 0, st));
+  PK(pack_linear(w->logit_w, m->V1, 3 * HID, m->w_logit, 0, st));
+  PK(pack_linear(w->embed_w, m->V1, HID, m->embed, 0, st));
+  const int ctx[3] = {HID, ECHR_VIDEO_DIM, ECHR_LDA_DIM};
+  const int ctx_pad[3] = {HID, CLIP_PAD, VID_PAD};
+  for (int l = 0; l < 3; ++l) {
+    pack_lstm_kernel<<<148 * 8, 256, 0, st>>>(w->lstm_w_ih[l], w->lstm_w_hh[l], ctx[l], ctx_pad[l],
+                                              m->w_lstm[l].plane(0),
+                                              m->w_lstm[l].planes > 1 ? m->w_lstm[l].plane(1) : nullptr);
+    PK(cudaGetLastError());
+    pack_lstm_bias_kernel<<<GATES / 256, 256, 0, st>>>(w->lstm_b_ih[l], w->lstm_b_hh[l], m->b_lstm[l]);
+    PK(cudaGetLastError());
+  }
+  PK(copy_vec(w->event_emb_b, m->b_event_emb, HID, st));
+  PK(copy_vec(w->query_b, m->b_qky, HID, st));
+  PK(copy_vec(w->key_b, m->b_qky + HID, HID, st));
+  PK(copy_vec(nullptr, m->b_qky + 2 * HID, HID, st));
+  PK(copy_vec(w->pos_fc1_b, m->b_fc1, HID, st));
+  PK(copy_vec(w->pos_fc2_b, m->b_fc2, ECHR_HEADS, st));
+  PK(copy_vec(w->ctx2att_b, m->b_ctx2att, HID, st));
+  PK(copy_vec(w->h2att_b, m->b_h2att, HID, st));
+  PK(copy_vec(w->logit_b, m->b_logit, m->V1, st));
+  PK(copy_vec(w->out_b, m->b_out, HID, st));
+  PK(copy_vec(w->alpha_w, m->alpha, HID, st));
+  PK(cudaStreamSynchronize(st));
+#undef PK
+  *out = m;
+  return ECHR_OK;
+}
+
+extern "C" int echr_model_destroy(echr_model_t* m) {
+  if (!m) return ECHR_OK;
+  cudaFree(m->arena);
+  delete m;
+  return ECHR_OK;
+}
+
+// =============================================================================================
+// Batch
+// =============================================================================================
+static void batch_layout(echr_batch* b, Arena& a) {
+  const echr_capacity_t& c = b->cap;
+  const echr_model* m = b->model;
+  const int ap = m->cfg.a_terms;
+  const int S = m->cfg.seq_length;
+  const int n_tiles = (m->V1 + 127) / 128;
+  b->c3d = a.take<float>((size_t)c.max_clips * ECHR_VIDEO_DIM);
+  b->tap = a.take<float>((size_t)c.max_clips * HID);
+  b->lda = a.take<float>((size_t)c.max_videos * ECHR_LDA_DIM);
+  int32_t* ints = a.take<int32_t>((size_t)7 * c.max_events + 2 * c.max_videos);
+  b->ev_video = ints;
+  b->ev_start = ints + 1 * c.max_events;
+  b->ev_len = ints + 2 * c.max_events;
+  b->ev_ind = ints + 3 * c.max_events;
+  b->ev_pair_off = ints + 4 * c.max_events;
+  b->ev_first = ints + 5 * c.max_events;
+  b->ev_n = ints + 6 * c.max_events;
+  b->vid_first = ints + 7 * c.max_events;
+  b->vid_n = b->vid_first + c.max_videos;
+  b->clip_pl = a.planes(ap, c.max_clips, CLIP_PAD);
+  if (m->cfg.clip_bf16) {
+    b->proj_bf = a.take<bf16>((size_t)c.max_clips * HID);
+    b->proj_f32 = nullptr;
+  } else {
+    b->proj_f32 = a.take<float>((size_t)c.max_clips * HID);
+    b->proj_bf = nullptr;
+  }
+  b->feat_pl = a.planes(ap, c.max_events, FEAT_PAD);
+  b->x_pl = a.planes(ap, c.max_events, HID);
+  b->qky = a.take<float>((size_t)c.max_events * 3 * HID);
+  b->pe_pl = a.planes(ap, c.max_pairs, HID);
+  b->hid_pl = a.planes(ap, c.max_pairs, HID);
+  b->pair_w = a.take<float>((size_t)c.max_pairs * ECHR_HEADS);
+  b->event_ctx = a.take<float>((size_t)c.max_events * HID);
+  for (int i = 0; i < 2; ++i) {
+    b->act[i] = a.planes(ap, c.max_rows, ACT_LD);
+    b->cstate[i] = a.take<float>((size_t)3 * c.max_rows * HID);
+  }
+  b->q_att = a.take<float>((size_t)c.max_rows * HID);
+  b->partial = a.take<float>((size_t)c.max_rows * n_tiles * LogitRec<4>::WORDS);
+  b->row_start = a.take<int32_t>(c.max_rows);
+  b->row_len = a.take<int32_t>(c.max_rows);
+  b->unfinished = a.take<int32_t>(c.max_rows);
+  b->tokens_dev = a.take<int32_t>((size_t)c.max_events * S);
+  b->logp_dev = a.take<float>((size_t)c.max_events * S);
+  b->score_dev = a.take<float>(c.max_events);
+  b->beam_score = a.take<float>(c.max_rows);
+  b->beam_live = a.take<int32_t>(c.max_rows);
+  b->beam_hist_tok = a.take<int32_t>((size_t)2 * c.max_rows * S);
+  b->beam_hist_lp = a.take<float>((size_t)2 * c.max_rows * S);
+  b->best_score = a.take<float>(c.max_events);
+}
+
+extern "C" int echr_batch_create(const echr_model_t* model, const echr_capacity_t* cap, echr_batch_t** out) {
+  ECHR_REQUIRE(model && cap && out, "echr_batch_create: null argument");
+  ECHR_REQUIRE(cap->max_videos >= 1 && cap->max_clips >= 1 && cap->max_events >= 1 && cap->max_pairs >= 1 &&
+                   cap->max_rows >= cap->max_events,
+               "echr_batch_create: capacities must be >= 1 and max_rows >= max_events");
+  ECHR_REQUIRE(cap->max_rows < (1ll << 24) && cap->max_pairs < (1ll << 30) && cap->max_clips < (1ll << 30),
+               "echr_batch_create: capacity too large");
+  ECHR_TRY(check_device());
+  echr_batch* b = new (std::nothrow) echr_batch();
+  ECHR_REQUIRE(b, "echr_batch_create: out of host memory");
+  memset(b, 0, sizeof(*b));
+  b->model = model;
+  b->cap = *cap;
+  Arena sizing;
+  batch_layout(b, sizing);
+  b->arena_bytes = sizing.off + 256;
+  cudaError_t e = cudaMalloc(&b->arena, b->arena_bytes);
+  if (e != cudaSuccess) {
+    delete b;
+    return set_error(ECHR_ERR_CUDA, "echr_batch_create: cudaMalloc(%zu) failed: %s", sizing.off, cudaGetErrorString(e));
+  }
+  e = cudaMallocHost(reinterpret_cast<void**>(&b->host_stage),
+                     sizeof(int32_t) * ((size_t)7 * cap->max_events + 2 * cap->max_videos));
+  if (e != cudaSuccess) {
+    cudaFree(b->arena);
+    delete b;
+    return set_error(ECHR_ERR_CUDA, "echr_batch_create: cudaMallocHost failed: %s", cudaGetErrorString(e));
+  }
+  Arena a;
+  a.base = reinterpret_cast<char*>(b->arena);
+  batch_layout(b, a);
+  e = cudaMemset(b->arena, 0, b->arena_bytes);
+  if (e != cudaSuccess) {
+    cudaFreeHost(b->host_stage);
+    cudaFree(b->arena);
+    delete b;
+    return set_error(ECHR_ERR_CUDA, "echr_batch_create: cudaMemset failed: %s", cudaGetErrorString(e));
+  }
+  *out = b;
+  return ECHR_OK;
+}
+
+extern "C" int echr_batch_destroy(echr_batch_t* b) {
+  if (!b) return ECHR_OK;
+  if (b->graph_exec) cudaGraphExecDestroy(b->graph_exec);
+  if (b->cap_stream) cudaStreamDestroy(b->cap_stream);
+  cudaFreeHost(b->host_stage);
+  cudaFree(b->arena);
+  delete b;
+  return ECHR_OK;
+}
+
+extern "C" int echr_batch_set_inputs(echr_batch_t* b, const echr_batch_desc_t* d, const float* c3d,
+                                     const float* tap, const float* lda, int on_host, void* stream) {
+  ECHR_REQUIRE(b && d && c3d && tap && lda, "echr_batch_set_inputs: null argument");
+  ECHR_REQUIRE(d->n_videos >= 1 && d->n_videos <= b->cap.max_videos, "echr_batch_set_inputs: n_videos=%d out of range (capacity %lld)", d->n_videos, (long long)b->cap.max_videos);
+  ECHR_REQUIRE(d->n_events >= 0 && d->n_events <= b->cap.max_events, "echr_batch_set_inputs: n_events=%d exceeds capacity %lld", d->n_events, (long long)b->cap.max_events);
+  ECHR_REQUIRE(d->host_clip_offsets && (d->n_events == 0 || (d->host_event_video && d->host_event_start && d->host_event_end && d->host_event_ind)),
+               "echr_batch_set_inputs: null index array");
+  const int32_t* off = d->host_clip_offsets;
+  ECHR_REQUIRE(off[0] == 0, "echr_batch_set_inputs: clip_offsets[0] must be 0");
+  for (int v = 0; v < d->n_videos; ++v)
+    ECHR_REQUIRE(off[v + 1] > off[v], "echr_batch_set_inputs: video %d has no clips", v);
+  const int n_clips = off[d->n_videos];
+  ECHR_REQUIRE(n_clips <= b->cap.max_clips, "echr_batch_set_inputs: %d clips exceed capacity %lld", n_clips, (long long)b->cap.max_clips);
+  cudaStream_t st = (cudaStream_t)stream;
+  // the pinned staging buffer may still be in flight from the previous call on this stream
+  ECHR_CUDA(cudaStreamSynchronize(st));
+  const int64_t E = b->cap.max_events;
+  int32_t* hs = b->host_stage;
+  int32_t* vid_first = hs + 7 * E;
+  int32_t* vid_n = vid_first + b->cap.max_videos;
+  for (int v = 0; v < d->n_videos; ++v) { vid_first[v] = 0; vid_n[v] = 0; }
+  int prev_v = 0;
+  for (int i = 0; i < d->n_events; ++i) {
+    const int v = d->host_event_video[i];
+    ECHR_REQUIRE(v >= prev_v && v < d->n_videos, "echr_batch_set_inputs: event %d: video index %d not non-decreasing / out of range", i, v);
+    prev_v = v;
+    const int T = off[v + 1] - off[v];
+    const int s = d->host_event_start[i], e = d->host_event_end[i], ind = d->host_event_ind[i];
+    ECHR_REQUIRE(s >= 0 && e > s && e <= T, "echr_batch_set_inputs: event %d: span [%d,%d) invalid for a video of %d clips", i, s, e, T);
+    ECHR_REQUIRE(e - s <= 1024, "echr_batch_set_inputs: event %d: span of %d clips exceeds 1024", i, e - s);
+    ECHR_REQUIRE(ind >= 0 && ind < T, "echr_batch_set_inputs: event %d: ind %d out of range", i, ind);
+    if (vid_n[v] == 0) vid_first[v] = i;
+    vid_n[v] += 1;
+    hs[0 * E + i] = v;
+    hs[1 * E + i] = off[v] + s;
+    hs[2 * E + i] = e - s;
+    hs[3 * E + i] = off[v] + ind;
+  }
+  long long pairs = 0;
+  int max_n = 0;
+  for (int v = 0; v < d->n_videos; ++v) {
+    const int n = vid_n[v];
+    ECHR_REQUIRE(n <= 512, "echr_batch_set_inputs: video %d has %d events (limit 512)", v, n);
+    if (n > max_n) max_n = n;
+    for (int j = 0; j < n; ++j) {
+      const int i = vid_first[v] + j;
+      hs[4 * E + i] = (int32_t)(pairs + (long long)j * n);
+      hs[5 * E + i] = vid_first[v];
+      hs[6 * E + i] = n;
+    }
+    pairs += (long long)n * n;
+  }
+  ECHR_REQUIRE(pairs <= b->cap.max_pairs, "echr_batch_set_inputs: %lld event pairs exceed capacity %lld", pairs, (long long)b->cap.max_pairs);
+  b->n_videos = d->n_videos;
+  b->n_events = d->n_events;
+  b->n_clips = n_clips;
+  b->n_pairs = (int)pairs;
+  b->max_n = max_n;
+  b->encoded = false;
+  ECHR_CUDA(cudaMemcpyAsync(b->ev_video, hs, sizeof(int32_t) * ((size_t)7 * E + 2 * b->cap.max_videos),
+                            cudaMemcpyHostToDevice, st));
+  const cudaMemcpyKind kind = on_host ? cudaMemcpyHostToDevice : cudaMemcpyDeviceToDevice;
+  ECHR_CUDA(cudaMemcpyAsync(b->c3d, c3d, sizeof(float) * (size_t)n_clips * ECHR_VIDEO_DIM, kind, st));
+  ECHR_CUDA(cudaMemcpyAsync(b->tap, tap, sizeof(float) * (size_t)n_clips * HID, kind, st));
+  ECHR_CUDA(cudaMemcpyAsync(b->lda, lda, sizeof(float) * (size_t)d->n_videos * ECHR_LDA_DIM, kind, st));
+  return ECHR_OK;
+}
+
+// =============================================================================================
+// Encode: context prologue + relation encoder
+// =============================================================================================
+extern "C" int echr_encode(echr_batch_t* b, void* stream) {
+  ECHR_REQUIRE(b, "echr_encode: null batch");
+  ECHR_REQUIRE(b->n_videos > 0, "echr_encode: no inputs set");
+  cudaStream_t st = (cudaStream_t)stream;
+  const echr_model* m = b->model;
+  const int at = m->cfg.a_terms, wt = m->cfg.w_terms;
+  // clip planes + hoisted ctx2att projection over every clip of the batch (OldModel_NEW.py:381,
+  // computed once instead of once per decode step)
+  ECHR_CUDA(launch_split(b->c3d, b->n_clips, ECHR_VIDEO_DIM, ECHR_VIDEO_DIM, b->clip_pl.plane(0),
+                         at > 1 ? b->clip_pl.plane(1) : nullptr, CLIP_PAD, CLIP_PAD, st));
+  {
+    GemmSpec s;
+    s.A = &b->clip_pl; s.M = b->n_clips; s.W = &m->w_ctx2att; s.N = HID; s.K = CLIP_PAD;
+    s.bias = m->b_ctx2att;
+    if (m->cfg.clip_bf16) { s.out_hi = b->proj_bf; s.ld_bf = HID; }
+    else { s.out_f32 = b->proj_f32; s.ld_f32 = HID; }
+    ECHR_TRY(run_gemm(&s, 1, at, wt, 128, EPI_STORE, 1, st, "ctx2att"));
+  }
+  if (b->n_events == 0) { b->encoded = true; return ECHR_OK; }
+  // event features -> embedding -> query | key | value*W_out
+  ECHR_CUDA(launch_event_feats(b, st));
+  {
+    GemmSpec s;
+    s.A = &b->feat_pl; s.M = b->n_events; s.W = &m->w_event_emb; s.N = HID; s.K = FEAT_PAD;
+    s.bias = m->b_event_emb;
+    s.out_hi = b->x_pl.plane(0); s.out_lo = at > 1 ? b->x_pl.plane(1) : nullptr; s.ld_bf = HID;
+    ECHR_TRY(run_gemm(&s, 1, at, wt, 128, EPI_STORE, 1, st, "event_emb"));
+  }
+  {
+    GemmSpec s;
+    s.A = &b->x_pl; s.M = b->n_events; s.W = &m->w_qky; s.N = 3 * HID; s.K = HID;
+    s.bias = m->b_qky; s.out_f32 = b->qky; s.ld_f32 = 3 * HID;
+    ECHR_TRY(run_gemm(&s, 1, at, wt, 128, EPI_STORE, 1, st, "query_key_value"));
+  }
+  // pair position embedding -> fc1 + tanh -> fc2
+  ECHR_CUDA(launch_posemb(b, st));
+  {
+    GemmSpec s;
+    s.A = &b->pe_pl; s.M = b->n_pairs; s.W = &m->w_fc1; s.N = HID; s.K = HID;
+    s.bias = m->b_fc1; s.act = ACT_TANH;
+    s.out_hi = b->hid_pl.plane(0); s.out_lo = at > 1 ? b->hid_pl.plane(1) : nullptr; s.ld_bf = HID;
+    ECHR_TRY(run_gemm(&s, 1, at, wt, 128, EPI_STORE, 1, st, "pair_pos_fc1"));
+  }
+  {
+    GemmSpec s;
+    s.A = &b->hid_pl; s.M = b->n_pairs; s.W = &m->w_fc2; s.N = ECHR_HEADS; s.K = HID;
+    s.bias = m->b_fc2; s.out_f32 = b->pair_w; s.ld_f32 = ECHR_HEADS;
+    ECHR_TRY(run_gemm(&s, 1, at, wt, 16, EPI_STORE, 1, st, "pair_pos_fc2"));
+  }
+  ECHR_CUDA(launch_relation_attn(b, st));
+  b->encoded = true;
+  return ECHR_OK;
+}
+
+extern "C" int echr_get_event_context(const echr_batch_t* b, float* out, void* stream) {
+  ECHR_REQUIRE(b && out, "echr_get_event_context: null argument");
+  ECHR_REQUIRE(b->encoded, "echr_get_event_context: call echr_encode first");
+  ECHR_CUDA(cudaMemcpyAsync(out, b->event_ctx, sizeof(float) * (size_t)b->n_events * HID,
+                            cudaMemcpyDeviceToDevice, (cudaStream_t)stream));
+  return ECHR_OK;
+}
+
+// =============================================================================================
+// Decode
+// =============================================================================================
+static const int KB_L0[24] = {0, 1, 2, 3, 4, 5, 6, 7, 8, 9, 10, 11, 12, 13, 14, 15, 26, 27, 28, 29, 30, 31, 32, 33};
+static const int KB_L1[24] = {0, 1, 2, 3, 4, 5, 6, 7, 16, 17, 18, 19, 20, 21, 22, 23, 34, 35, 36, 37, 38, 39, 40, 41};
+static const int KB_L2[18] = {0, 1, 2, 3, 4, 5, 6, 7, 24, 25, 42, 43, 44, 45, 46, 47, 48, 49};
+
+enum { MODE_GREEDY = 0, MODE_BEAM = 1, MODE_TF = 2 };
+
+static int enqueue_init(echr_batch* b, int beam, cudaStream_t st) {
+  const long long rows = (long long)b->n_events * beam;
+  for (int i = 0; i < 2; ++i)
+    for (int p = 0; p < b->act[i].planes; ++p)
+      ECHR_CUDA(cudaMemsetAsync(b->act[i].plane(p), 0, sizeof(bf16) * (size_t)rows * ACT_LD, st));
+  ECHR_CUDA(cudaMemsetAsync(b->cstate[0], 0, sizeof(float) * (size_t)3 * rows * HID, st));
+  ECHR_CUDA(launch_decode_init(b, beam, st));
+  return ECHR_OK;
+}
+
+// One decode step t: attention query + attention (stream 1 uses the PREVIOUS h1), the three gate
+// GEMMs with the fused LSTM cell update, the vocabulary projection with fused partial
+// log-softmax / top-k.  The caller appends the mode's finalize kernel.
+static int enqueue_step(echr_batch* b, int rows, int t, int topk, float* logits_out, long long ld_logits,
+                        cudaStream_t st) {
+  const echr_model* m = b->model;
+  const int at = m->cfg.a_terms, wt = m->cfg.w_terms;
+  const int p = t & 1, n = p ^ 1;
+  PlaneMat& cur = b->act[p];
+  PlaneMat& nxt = b->act[n];
+  {
+    GemmSpec s;
+    s.A = &cur; s.a_col0 = ACT_H + HID; s.M = rows; s.W = &m->w_h2att; s.N = HID; s.K = HID;
+    s.bias = m->b_h2att; s.out_f32 = b->q_att; s.ld_f32 = HID;
+    ECHR_TRY(run_gemm(&s, 1, at, wt, 128, EPI_STORE, 1, st, "h2att"));
+  }
+  ECHR_CUDA(launch_attention(b->q_att, m->cfg.clip_bf16 ? (const void*)b->proj_bf : (const void*)b->proj_f32,
+                             m->cfg.clip_bf16 ? (const void*)b->clip_pl.plane(0) : (const void*)b->c3d,
+                             m->cfg.clip_bf16 ? CLIP_PAD : ECHR_VIDEO_DIM, m->cfg.clip_bf16, m->alpha,
+                             b->row_start, b->row_len, rows, nullptr, cur.plane(0) + ACT_ATT,
+                             at > 1 ? cur.plane(1) + ACT_ATT : nullptr, ACT_LD, st));
+  {
+    GemmSpec s[3];
+    const int* kbs[3] = {KB_L0, KB_L1, KB_L2};
+    const int K[3] = {24 * 64, 24 * 64, 18 * 64};
+    for (int l = 0; l < 3; ++l) {
+      s[l].A = &cur; s[l].a_kb = kbs[l]; s[l].M = rows; s[l].W = &m->w_lstm[l]; s[l].N = GATES; s[l].K = K[l];
+      s[l].bias = m->b_lstm[l];
+      s[l].c_in = b->cstate[p] + (long long)l * rows * HID;
+      s[l].c_out = b->cstate[n] + (long long)l * rows * HID;
+      s[l].out_hi = nxt.plane(0) + ACT_H + l * HID;
+      s[l].out_lo = at > 1 ? nxt.plane(1) + ACT_H + l * HID : nullptr;
+      s[l].ld_bf = ACT_LD;
+    }
+    ECHR_TRY(run_gemm(s, 3, at, wt, 128, EPI_LSTM, 1, st, "lstm_gates"));
+  }
+  {
+    GemmSpec s;
+    s.A = &nxt; s.a_col0 = ACT_H; s.M = rows; s.W = &m->w_logit; s.N = m->V1; s.K = 3 * HID;
+    s.bias = m->b_logit; s.partial = b->partial; s.logits_out = logits_out; s.ld_logits = ld_logits;
+    ECHR_TRY(run_gemm(&s, 1, at, wt, 128, EPI_LOGITS, topk, st, "logit"));
+  }
+  return ECHR_OK;
+}
+
+static int enqueue_decode(echr_batch* b, int beam, int mode, cudaStream_t st) {
+  const int rows = b->n_events * beam;
+  const int S = b->model->cfg.seq_length;
+  ECHR_TRY(enqueue_init(b, beam, st));
+  if (mode == MODE_BEAM) {
+    ECHR_CUDA(cudaMemsetAsync(b->tokens_dev, 0, sizeof(int32_t) * (size_t)b->n_events * S, st));
+    ECHR_CUDA(cudaMemsetAsync(b->logp_dev, 0, sizeof(float) * (size_t)b->n_events * S, st));
+  }
+  for (int t = 0; t < S; ++t) {
+    ECHR_TRY(enqueue_step(b, rows, t, mode == MODE_BEAM ? 4 : 1, nullptr, 0, st));
+    if (mode == MODE_BEAM)
+      ECHR_CUDA(launch_finalize_beam(b, beam, t, b->tokens_dev, b->logp_dev, b->score_dev, st));
+    else
+      ECHR_CUDA(launch_finalize_greedy(b, t, b->tokens_dev, b->logp_dev, st));
+  }
+  return ECHR_OK;
+}
+
+// Capture the whole decode (init + seq_length steps) into one CUDA graph per (rows, beam, mode)
+// and replay it: one launch from the host per batch instead of ~150.
+static int run_decode(echr_batch* b, int beam, int mode, cudaStream_t st) {
+  ECHR_REQUIRE(b->encoded, "decode: call echr_encode first");
+  ECHR_REQUIRE((long long)b->n_events * beam <= b->cap.max_rows, "decode: %d events x beam %d exceed max_rows %lld", b->n_events, beam, (long long)b->cap.max_rows);
+  if (b->n_events == 0) return ECHR_OK;
+  const int rows = b->n_events * beam;
+  const int key_beam = mode == MODE_BEAM ? beam : 0;
+  if (b->graph_exec == nullptr || b->graph_rows != rows || b->graph_beam != key_beam) {
+    if (b->graph_exec) { cudaGraphExecDestroy(b->graph_exec); b->graph_exec = nullptr; }
+    const long long before = g_launches.load();
+    cudaGraph_t graph = nullptr;
+    // capture on a private stream: the caller's stream may be the legacy default stream, which
+    // cannot be captured
+    if (b->cap_stream == nullptr) ECHR_CUDA(cudaStreamCreateWithFlags(&b->cap_stream, cudaStreamNonBlocking));
+    ECHR_CUDA(cudaStreamBeginCapture(b->cap_stream, cudaStreamCaptureModeRelaxed));
+    int rc = enqueue_decode(b, beam, mode, b->cap_stream);
+    cudaError_t e = cudaStreamEndCapture(b->cap_stream, &graph);
+    if (rc != 0) { if (graph) cudaGraphDestroy(graph); return rc; }
+    if (e != cudaSuccess) return set_error(ECHR_ERR_CUDA, "decode: graph capture failed: %s", cudaGetErrorString(e));
+    e = cudaGraphInstantiate(&b->graph_exec, graph, 0);
+    cudaGraphDestroy(graph);
+    if (e != cudaSuccess) { b->graph_exec = nullptr; return set_error(ECHR_ERR_CUDA, "decode: graph instantiate failed: %s", cudaGetErrorString(e)); }
+    b->graph_kernels = g_launches.load() - before;
+    g_launches.store(before);
+    b->graph_rows = rows;
+    b->graph_beam = key_beam;
+  }
+  ECHR_CUDA(cudaGraphLaunch(b->graph_exec, st));
+  count_launch((int)b->graph_kernels);
+  return ECHR_OK;
+}
+
+static int copy_results(echr_batch* b, int32_t* tokens, float* logp, float* score, cudaMemcpyKind kind,
+                        cudaStream_t st) {
+  const size_t n = (size_t)b->n_events * b->model->cfg.seq_length;
+  if (n == 0) return ECHR_OK;
+  if (tokens) ECHR_CUDA(cudaMemcpyAsync(tokens, b->tokens_dev, sizeof(int32_t) * n, kind, st));
+  if (logp) ECHR_CUDA(cudaMemcpyAsync(logp, b->logp_dev, sizeof(float) * n, kind, st));
+  if (score) ECHR_CUDA(cudaMemcpyAsync(score, b->score_dev, sizeof(float) * (size_t)b->n_events, kind, st));
+  return ECHR_OK;
+}
+
+extern "C" int echr_decode_greedy(echr_batch_t* b, int32_t* tokens, float* logp, void* stream) {
+  ECHR_REQUIRE(b, "echr_decode_greedy: null batch");
+  cudaStream_t st = (cudaStream_t)stream;
+  ECHR_TRY(run_decode(b, 1, MODE_GREEDY, st));
+  return copy_results(b, tokens, logp, nullptr, cudaMemcpyDeviceToDevice, st);
+}
+
+extern "C" int echr_decode_beam(echr_batch_t* b, int beam, int32_t* tokens, float* logp, float* score,
+                                void* stream) {
+  ECHR_REQUIRE(b, "echr_decode_beam: null batch");
+  ECHR_REQUIRE(beam >= 1 && beam <= 4, "echr_decode_beam: beam must be in 1..4");
+  cudaStream_t st = (cudaStream_t)stream;
+  ECHR_TRY(run_decode(b, beam, MODE_BEAM, st));
+  return copy_results(b, tokens, logp, score, cudaMemcpyDeviceToDevice, st);
+}
+
+extern "C" int echr_teacher_forced(echr_batch_t* b, const int32_t* seq, int seq_cols, float* logprobs,
+                                   void* stream) {
+  ECHR_REQUIRE(b && seq && logprobs, "echr_teacher_forced: null argument");
+  ECHR_REQUIRE(b->encoded, "echr_teacher_forced: call echr_encode first");
+  ECHR_REQUIRE(seq_cols >= 2 && seq_cols <= 65, "echr_teacher_forced: seq_cols must be in 2..65");
+  cudaStream_t st = (cudaStream_t)stream;
+  if (b->n_events == 0) return ECHR_OK;
+  const int rows = b->n_events;
+  const int V1 = b->model->V1;
+  ECHR_TRY(enqueue_init(b, 1, st));
+  ECHR_CUDA(launch_finalize_tf(b, -1, seq, seq_cols, logprobs, st));
+  for (int t = 0; t < seq_cols - 1; ++t) {
+    ECHR_TRY(enqueue_step(b, rows, t, 1, logprobs + (long long)t * V1, (long long)(seq_cols - 1) * V1, st));
+    ECHR_CUDA(launch_finalize_tf(b, t, seq, seq_cols, logprobs, st));
+  }
+  return ECHR_OK;
+}
+
+extern "C" int echr_caption_host(echr_batch_t* b, const echr_batch_desc_t* desc, const float* host_c3d,
+                                 const float* host_tap, const float* host_lda, int beam,
+                                 int32_t* host_tokens, float* host_logp, float* host_score, void* stream) {
+  ECHR_REQUIRE(b && host_tokens && host_logp, "echr_caption_host: null argument");
+  cudaStream_t st = (cudaStream_t)stream;
+  ECHR_TRY(echr_batch_set_inputs(b, desc, host_c3d, host_tap, host_lda, 1, st));
+  ECHR_TRY(echr_encode(b, st));
+  if (beam > 1) {
+    ECHR_REQUIRE(beam <= 4, "echr_caption_host: beam must be in 1..4");
+    ECHR_TRY(run_decode(b, beam, MODE_BEAM, st));
+  } else {
+    ECHR_TRY(run_decode(b, 1, MODE_GREEDY, st));
+  }
+  ECHR_TRY(copy_results(b, host_tokens, host_logp, beam > 1 ? host_score : nullptr, cudaMemcpyDeviceToHost, st));
+  ECHR_CUDA(cudaStreamSynchronize(st));
+  return ECHR_OK;
+}
+
+extern "C" int64_t echr_launch_count(int reset) {
+  const long long v = reset ? g_launches.exchange(0) : g_launches.load();
+  return (int64_t)v;
+}

@@ -1,0 +1,130 @@
+// Internal data model of the engine: packed weights (Model) and the per-batch workspace (Batch).
+// Layout notes are in DESIGN.md §"Data layout in HBM".
+#pragma once
+#include <cuda_runtime.h>
+#include <cuda_bf16.h>
+#include <stdint.h>
+
+#include "../../include/echr_b200.h"
+#include "gemm_tc.cuh"
+
+namespace echr {
+
+typedef __nv_bfloat16 bf16;
+
+// ---- activation matrix: one row per decode row, bf16, `planes` planes, two ping-pong buffers.
+// Column blocks of 64 (= one TMA box / one GEMM k-block).
+constexpr int ACT_X = 0;       // embedded input token      512  (kb 0..7)
+constexpr int ACT_EV = 512;    // event context (relation)  512  (kb 8..15)
+constexpr int ACT_ATT = 1024;  // attended clip feature     500 -> 512 (kb 16..23)
+constexpr int ACT_VID = 1536;  // video (LDA) context       100 -> 128 (kb 24..25)
+constexpr int ACT_H = 1664;    // h of stream 0,1,2         3 x 512    (kb 26..49)
+constexpr int ACT_LD = 3200;
+constexpr int HID = 512;
+constexpr int VID_PAD = 128;
+constexpr int CLIP_PAD = 512;   // 500 -> 512
+constexpr int FEAT_PAD = 1024;  // 1012 -> 1024
+constexpr int GATES = 2048;
+
+struct PlaneMat {  // [planes][rows][ld] bf16
+  bf16* p = nullptr;
+  int64_t rows = 0, ld = 0, planes = 0;
+  int64_t plane_stride() const { return rows * ld; }
+  bf16* plane(int i) const { return p + i * plane_stride(); }
+};
+
+}  // namespace echr
+
+struct echr_model {
+  echr_config_t cfg;
+  int V1;  // vocab_size + 1
+  // tensor-core weights as bf16 planes (w_terms planes), row-major [out, in_padded]
+  echr::PlaneMat w_event_emb;  // [512, 1024]
+  echr::PlaneMat w_qky;        // [1536, 512]  rows: query | key | linear_out (grouped conv as dense)
+  echr::PlaneMat w_fc1;        // [512, 512]
+  echr::PlaneMat w_fc2;        // [16, 512]
+  echr::PlaneMat w_ctx2att;    // [512, 512(500)]
+  echr::PlaneMat w_h2att;      // [512, 512]
+  echr::PlaneMat w_lstm[3];    // [2048 gate-interleaved, K_l]  K = 1536, 1536, 1152 (x | ctx | h)
+  echr::PlaneMat w_logit;      // [V1, 1536]
+  echr::PlaneMat embed;        // [V1, 512] always 2 planes (a_terms are read from it)
+  // fp32 vectors
+  float *b_event_emb, *b_qky, *b_fc1, *b_fc2, *b_ctx2att, *b_h2att, *b_lstm[3], *b_logit, *b_out,
+      *alpha;
+  void* arena;  // one allocation behind everything above
+};
+
+struct echr_batch {
+  const echr_model* model;
+  echr_capacity_t cap;
+  // current batch
+  int n_videos, n_events, n_clips, n_pairs, max_n;  // max_n = largest events-per-video
+  bool encoded;
+  // inputs (copies)
+  float *c3d, *tap, *lda;  // [clips,500] [clips,512] [videos,100]
+  // per-event int arrays on device: video, first clip (global), length, ind (global), pair row
+  // offset, first event of the video, events in the video
+  int32_t *ev_video, *ev_start, *ev_len, *ev_ind, *ev_pair_off, *ev_first, *ev_n;
+  int32_t *vid_first, *vid_n;  // per video: first event, number of events
+  int32_t* host_stage;  // pinned staging for the arrays above
+  // encode workspace
+  echr::PlaneMat clip_pl;   // [clips, 512]   c3d planes (A of ctx2att; plane 0 doubles as bf16 clip)
+  float* proj_f32;          // [clips, 512]   ctx2att(c3d)+b    (clip_bf16 == 0)
+  echr::bf16* proj_bf;      // [clips, 512]                     (clip_bf16 == 1)
+  echr::PlaneMat feat_pl;   // [events, 1024] (mean c3d | tap[ind])
+  echr::PlaneMat x_pl;      // [events, 512]  event_emb output
+  float* qky;               // [events, 1536]
+  echr::PlaneMat pe_pl;     // [pairs, 512]   position embedding
+  echr::PlaneMat hid_pl;    // [pairs, 512]   tanh(fc1)
+  float* pair_w;            // [pairs, 16]
+  float* event_ctx;         // [events, 512]
+  // decode workspace (rows = events * beam)
+  echr::PlaneMat act[2];    // [rows, ACT_LD]
+  float* cstate[2];         // [3][rows][512]
+  float* q_att;             // [rows, 512]
+  float* partial;           // [rows, n_vtiles, 12]
+  int32_t *row_start, *row_len;  // attention window per decode row
+  int32_t* unfinished;      // [rows]
+  int32_t* tokens_dev;      // [events, S] scratch outputs for echr_caption_host
+  float* logp_dev;
+  float* score_dev;
+  // beam state
+  float* beam_score;        // [rows]
+  int32_t* beam_live;       // [rows]
+  int32_t* beam_hist_tok;   // [2][rows][S]
+  float* beam_hist_lp;      // [2][rows][S]
+  float* best_score;        // [events]
+  // decode graph cache
+  cudaGraphExec_t graph_exec;
+  cudaStream_t cap_stream;  // private stream the decode graph is captured on
+  int graph_rows, graph_beam;
+  int32_t *graph_tokens_out;
+  float *graph_logp_out, *graph_score_out;
+  int64_t graph_kernels;
+  void* arena;
+  size_t arena_bytes;
+};
+
+namespace echr {
+
+// ---- kernels_ctx.cu
+cudaError_t launch_split(const float* src, int64_t rows, int64_t cols, int64_t ld_src, bf16* hi,
+                         bf16* lo, int64_t ld_dst, int64_t cols_dst, cudaStream_t st);
+cudaError_t launch_event_feats(const echr_batch* b, cudaStream_t st);
+cudaError_t launch_posemb(const echr_batch* b, cudaStream_t st);
+cudaError_t launch_relation_attn(const echr_batch* b, cudaStream_t st);
+// ---- kernels_step.cu
+cudaError_t launch_attention(const float* q, const void* proj, const void* clip, int64_t ld_clip,
+                             int clip_bf16, const float* alpha, const int32_t* row_start,
+                             const int32_t* row_len, int64_t rows, float* out_f32, bf16* out_hi,
+                             bf16* out_lo, int64_t ld_bf, cudaStream_t st);
+cudaError_t launch_decode_init(const echr_batch* b, int beam, cudaStream_t st);
+cudaError_t launch_finalize_greedy(const echr_batch* b, int step, int32_t* tokens, float* logp,
+                                   cudaStream_t st);
+cudaError_t launch_finalize_beam(const echr_batch* b, int beam, int step, int32_t* tokens,
+                                 float* logp, float* score, cudaStream_t st);
+cudaError_t launch_finalize_tf(const echr_batch* b, int step, const int32_t* seq, int seq_cols,
+                               float* logprobs, cudaStream_t st);
+void count_launch(int n = 1);
+
+}  // namespace echr

@@ -1,0 +1,233 @@
+// Context prologue and event relation encoder kernels (everything that runs once per batch):
+//   split_planes        fp32 -> bf16 hi/lo planes (tensor-core operand staging)
+//   event_feats         mean-pooled clip feature | proposal state per event (CaptionGenerator.py:106-127)
+//   posemb              pairwise temporal position embedding (MA_attention_8_NEW.py:51-79), fp64 math
+//   relation_attn       multi-head relation attention with the pair weights (MA:122-175)
+//   fill_video          LDA video context into the activation matrix (CaptionGenerator.py:87-104)
+#include "engine.cuh"
+#include "util.cuh"
+
+namespace echr {
+
+__global__ void split_planes_kernel(const float* __restrict__ src, long long rows, long long cols,
+                                    long long ld_src, bf16* __restrict__ hi, bf16* __restrict__ lo,
+                                    long long ld_dst, long long cols_dst) {
+  const long long total = rows * cols_dst;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x) {
+    const long long r = i / cols_dst, c = i - r * cols_dst;
+    const float x = (c < cols) ? src[r * ld_src + c] : 0.f;
+    bf16 h, l;
+    split_bf16(x, h, l);
+    hi[r * ld_dst + c] = h;
+    if (lo != nullptr) lo[r * ld_dst + c] = l;
+  }
+}
+
+cudaError_t launch_split(const float* src, int64_t rows, int64_t cols, int64_t ld_src, bf16* hi,
+                         bf16* lo, int64_t ld_dst, int64_t cols_dst, cudaStream_t st) {
+  if (rows == 0 || cols_dst == 0) return cudaSuccess;
+  const long long total = rows * cols_dst;
+  long long blocks = (total + 255) / 256;
+  if (blocks > 148 * 16) blocks = 148 * 16;
+  split_planes_kernel<<<(int)blocks, 256, 0, st>>>(src, rows, cols, ld_src, hi, lo, ld_dst, cols_dst);
+  count_launch();
+  return cudaGetLastError();
+}
+
+// ---------------------------------------------------------------------------------------------
+// one block per event, 256 threads, 4 columns each of the 1024-wide feature row
+__global__ void __launch_bounds__(256)
+event_feats_kernel(const float* __restrict__ c3d, const float* __restrict__ tap,
+                   const int32_t* __restrict__ ev_start, const int32_t* __restrict__ ev_len,
+                   const int32_t* __restrict__ ev_ind, bf16* __restrict__ hi, bf16* __restrict__ lo) {
+  const int e = blockIdx.x;
+  const int s = ev_start[e], len = ev_len[e], ind = ev_ind[e];
+  const float inv = 1.0f / (float)len;
+  for (int c = threadIdx.x; c < FEAT_PAD; c += blockDim.x) {
+    float v = 0.f;
+    if (c < ECHR_VIDEO_DIM) {
+      float acc = 0.f;
+      for (int l = 0; l < len; ++l) acc += __ldg(c3d + (long long)(s + l) * ECHR_VIDEO_DIM + c);
+      v = acc / (float)len;
+      (void)inv;
+    } else if (c < ECHR_VIDEO_DIM + HID) {
+      v = __ldg(tap + (long long)ind * HID + (c - ECHR_VIDEO_DIM));
+    }
+    bf16 h, l2;
+    split_bf16(v, h, l2);
+    hi[(long long)e * FEAT_PAD + c] = h;
+    if (lo != nullptr) lo[(long long)e * FEAT_PAD + c] = l2;
+  }
+}
+
+cudaError_t launch_event_feats(const echr_batch* b, cudaStream_t st) {
+  if (b->n_events == 0) return cudaSuccess;
+  event_feats_kernel<<<b->n_events, 256, 0, st>>>(b->c3d, b->tap, b->ev_start, b->ev_len, b->ev_ind,
+                                                  b->feat_pl.plane(0),
+                                                  b->feat_pl.planes > 1 ? b->feat_pl.plane(1) : nullptr);
+  count_launch();
+  return cudaGetLastError();
+}
+
+// ---------------------------------------------------------------------------------------------
+// Position embedding.  The reference builds it in numpy float64 on the host (MA:39-41,51-79):
+//   dc = max(|c_i - c_j| / len_i, 1e-3)               (float64; len cast to float32 first)
+//   dl = log(len_j / len_i)                            (float32 division and float32 log)
+//   z  = 100 * p / 10000^(k/128),  k = 0..127          (float64)
+//   row(i,j) = [sin z(dc) | cos z(dc) | sin z(dl) | cos z(dl)]  -> float32
+// Arguments reach ~4e4, so the sine/cosine are evaluated in float64 here too.
+__constant__ double c_pos_div[128];
+
+__global__ void __launch_bounds__(256)
+posemb_kernel(const int32_t* __restrict__ ev_start, const int32_t* __restrict__ ev_len,
+              const int32_t* __restrict__ ev_pair_off, const int32_t* __restrict__ ev_first,
+              const int32_t* __restrict__ ev_n, bf16* __restrict__ hi, bf16* __restrict__ lo,
+              int j_chunk) {
+  const int i = blockIdx.x;
+  const int n = ev_n[i], first = ev_first[i];
+  const int j0 = blockIdx.y * j_chunk;
+  if (j0 >= n) return;
+  const int j1 = min(n, j0 + j_chunk);
+  const int k = threadIdx.x & 127;
+  const int which = threadIdx.x >> 7;  // 0: centre distance, 1: length ratio
+  const double ci = 0.5 * ((double)ev_start[i] + (double)(ev_start[i] + ev_len[i]));
+  const float li = (float)ev_len[i];
+  const double div = c_pos_div[k];
+  const long long row0 = ev_pair_off[i];
+  for (int j = j0; j < j1; ++j) {
+    const int ej = first + j;
+    double p;
+    if (which == 0) {
+      const double cj = 0.5 * ((double)ev_start[ej] + (double)(ev_start[ej] + ev_len[ej]));
+      p = fmax(fabs((ci - cj) / (double)li), 1e-3);
+    } else {
+      const float r = (float)ev_len[ej] / li;
+      p = (double)(float)log((double)r);
+    }
+    const double z = (100.0 * p) / div;
+    double sn, cs;
+    sincos(z, &sn, &cs);
+    bf16 sh, sl, ch, cl;
+    split_bf16((float)sn, sh, sl);
+    split_bf16((float)cs, ch, cl);
+    const long long base = (row0 + j) * HID + which * 256 + k;
+    hi[base] = sh;
+    hi[base + 128] = ch;
+    if (lo != nullptr) {
+      lo[base] = sl;
+      lo[base + 128] = cl;
+    }
+  }
+}
+
+static cudaError_t upload_pos_div() {
+  static bool done = false;  // per process; the table is device-constant per context
+  static int done_dev = -1;
+  int dev = 0;
+  cudaGetDevice(&dev);
+  if (done && done_dev == dev) return cudaSuccess;
+  double h[128];
+  for (int k = 0; k < 128; ++k) h[k] = pow(10000.0, (4.0 / 512.0) * (double)k);
+  cudaError_t e = cudaMemcpyToSymbol(c_pos_div, h, sizeof(h));
+  if (e == cudaSuccess) { done = true; done_dev = dev; }
+  return e;
+}
+
+cudaError_t launch_posemb(const echr_batch* b, cudaStream_t st) {
+  if (b->n_events == 0) return cudaSuccess;
+  cudaError_t e = upload_pos_div();
+  if (e != cudaSuccess) return e;
+  const int j_chunk = 32;
+  dim3 grid(b->n_events, (b->max_n + j_chunk - 1) / j_chunk);
+  posemb_kernel<<<grid, 256, 0, st>>>(b->ev_start, b->ev_len, b->ev_pair_off, b->ev_first, b->ev_n,
+                                      b->pe_pl.plane(0),
+                                      b->pe_pl.planes > 1 ? b->pe_pl.plane(1) : nullptr, j_chunk);
+  count_launch();
+  return cudaGetLastError();
+}
+
+// ---------------------------------------------------------------------------------------------
+// Relation attention (MA:122-175), one CTA per (video, head):
+//   s[i,j] = w[i,j,g] * (Q_i,g . K_j,g) / sqrt(32)         fST0: multiplicative fusion (MA:148-149)
+//   p[i,:] = softmax_j(s[i,:])                               (MA:160)
+//   out[i, 32g+d] = sum_j p[i,j] * Y[j, 32g+d] + b[32g+d]    with Y = x * W_out^T  (grouped 1x1 conv,
+//                                                            MA:98,167-175, re-associated)
+// K_g and Y_g of the whole video sit in shared memory (rows padded to 33 words: conflict-free for
+// both the per-lane row walk of the scores and the per-lane column walk of the mix); one warp per
+// query event, warp-shuffle softmax.
+constexpr int REL_WARPS = 8;
+constexpr int REL_MAX_N = 512;
+
+__global__ void __launch_bounds__(REL_WARPS * 32)
+relation_attn_kernel(const float* __restrict__ qky, const float* __restrict__ pair_w,
+                     const int32_t* __restrict__ ev_pair_off, const int32_t* __restrict__ vid_first,
+                     const int32_t* __restrict__ vid_n, const float* __restrict__ b_out,
+                     float* __restrict__ event_ctx) {
+  extern __shared__ float rel_smem[];
+  const int v = blockIdx.x, g = blockIdx.y;
+  const int first = vid_first[v], n = vid_n[v];
+  float* Ks = rel_smem;                 // [n][33]
+  float* Ys = Ks + (size_t)n * 33;      // [n][33]
+  float* Ss = Ys + (size_t)n * 33;      // [REL_WARPS][n]
+  float* Qs = Ss + (size_t)REL_WARPS * n;  // [REL_WARPS][32]
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  for (int idx = threadIdx.x; idx < n * 32; idx += blockDim.x) {
+    const int j = idx >> 5, d = idx & 31;
+    const float* row = qky + (long long)(first + j) * 1536 + 32 * g + d;
+    Ks[j * 33 + d] = __ldg(row + 512);
+    Ys[j * 33 + d] = __ldg(row + 1024);
+  }
+  __syncthreads();
+  const float scale = 1.0f / sqrtf(32.0f);
+  float* S = Ss + (size_t)warp * n;
+  float* Q = Qs + warp * 32;
+  for (int i = warp; i < n; i += REL_WARPS) {
+    Q[lane] = __ldg(qky + (long long)(first + i) * 1536 + 32 * g + lane);
+    __syncwarp();
+    const float* wrow = pair_w + (long long)ev_pair_off[first + i] * ECHR_HEADS + g;
+    float m = -INFINITY;
+    for (int j = lane; j < n; j += 32) {
+      float dot = 0.f;
+#pragma unroll
+      for (int d = 0; d < 32; ++d) dot = fmaf(Q[d], Ks[j * 33 + d], dot);
+      const float s = __ldg(wrow + (long long)j * ECHR_HEADS) * (scale * dot);
+      S[j] = s;
+      m = fmaxf(m, s);
+    }
+    m = warp_max(m);
+    float sum = 0.f;
+    for (int j = lane; j < n; j += 32) {
+      const float e = expf(S[j] - m);
+      S[j] = e;
+      sum += e;
+    }
+    sum = warp_sum(sum);
+    __syncwarp();
+    float acc = 0.f;
+    for (int j = 0; j < n; ++j) acc = fmaf(S[j], Ys[j * 33 + lane], acc);
+    event_ctx[(long long)(first + i) * HID + 32 * g + lane] = acc / sum + __ldg(b_out + 32 * g + lane);
+    __syncwarp();
+  }
+}
+
+cudaError_t launch_relation_attn(const echr_batch* b, cudaStream_t st) {
+  if (b->n_events == 0) return cudaSuccess;
+  if (b->max_n > REL_MAX_N) return cudaErrorInvalidValue;
+  const size_t smem = ((size_t)b->max_n * 66 + (size_t)REL_WARPS * b->max_n + REL_WARPS * 32) * sizeof(float);
+  static size_t attr = 0;
+  if (smem > 48 * 1024 && smem > attr) {
+    cudaError_t e = cudaFuncSetAttribute(relation_attn_kernel,
+                                         cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+    attr = smem;
+  }
+  dim3 grid(b->n_videos, ECHR_HEADS);
+  relation_attn_kernel<<<grid, REL_WARPS * 32, smem, st>>>(b->qky, b->pair_w, b->ev_pair_off,
+                                                          b->vid_first, b->vid_n, b->model->b_out,
+                                                          b->event_ctx);
+  count_launch();
+  return cudaGetLastError();
+}
+
+}  // namespace echr

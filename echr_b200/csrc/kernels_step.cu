@@ -1,0 +1,527 @@
+// Per-decode-step kernels that are not GEMMs:
+//   attention_kernel   late-fusion attention over an event's clip window (OldModel_NEW.py:376-401)
+//   decode_init        zero state, BOS embedding, constant context columns (OldModel_NEW.py:72-78,150-156)
+//   finalize_greedy    merge the logit tiles' partials -> argmax / log-prob / next input (OldModel_NEW.py:158,175-183)
+//   finalize_tf        same merge for the teacher-forced path (OldModel_NEW.py:98-130)
+//   finalize_beam      beam selection + state reorder (spec: oracle/echr_oracle.py beam_search)
+#include "engine.cuh"
+#include "util.cuh"
+
+namespace echr {
+
+// tanh with ~4e-7 absolute error from one ex2 and one fast division (inputs here are O(1)).
+__device__ __forceinline__ float tanh_fast(float x) {
+  const float e = __expf(2.0f * x);
+  return 1.0f - __fdividef(2.0f, e + 1.0f);
+}
+
+constexpr int ATT_THREADS = 256;
+constexpr int ATT_MAX_L = 1024;
+
+// One CTA per decode row.  Pass 1: one warp per clip, lanes across the 512 hidden units (coalesced
+// 16-byte loads), score_l = alpha . tanh(P_l + q).  Softmax over the window (the reference's
+// softmax-then-mask-then-renormalise over the padded length, OldModel_NEW.py:394-397, is the same
+// function).  Pass 2: threads across the 500 feature columns, att = sum_l w_l * clip_l.
+template <bool BF16>
+__global__ void __launch_bounds__(ATT_THREADS)
+attention_kernel(const float* __restrict__ q, const void* __restrict__ proj_v,
+                 const void* __restrict__ clip_v, long long ld_clip, const float* __restrict__ alpha,
+                 const int32_t* __restrict__ row_start, const int32_t* __restrict__ row_len,
+                 float* __restrict__ out_f32, bf16* __restrict__ out_hi, bf16* __restrict__ out_lo,
+                 long long ld_bf) {
+  __shared__ float sc[ATT_MAX_L];
+  __shared__ __align__(16) float red[4][512];
+  const int r = blockIdx.x;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int s0 = row_start[r];
+  const int L = row_len[r];
+  // q and alpha: lane owns hidden units [128*m + 4*lane, +4), m = 0..3
+  float qv[16], av[16];
+#pragma unroll
+  for (int m = 0; m < 4; ++m) {
+    const float4 t = __ldg(reinterpret_cast<const float4*>(q + (long long)r * HID + 128 * m + 4 * lane));
+    const float4 a = __ldg(reinterpret_cast<const float4*>(alpha + 128 * m + 4 * lane));
+    qv[4 * m] = t.x; qv[4 * m + 1] = t.y; qv[4 * m + 2] = t.z; qv[4 * m + 3] = t.w;
+    av[4 * m] = a.x; av[4 * m + 1] = a.y; av[4 * m + 2] = a.z; av[4 * m + 3] = a.w;
+  }
+  for (int l = warp; l < L; l += ATT_THREADS / 32) {
+    float pv[16];
+    if (BF16) {
+      const bf16* prow = reinterpret_cast<const bf16*>(proj_v) + (long long)(s0 + l) * HID;
+#pragma unroll
+      for (int m = 0; m < 4; ++m) {
+        const uint2 u = __ldg(reinterpret_cast<const uint2*>(prow + 128 * m + 4 * lane));
+        const __nv_bfloat162 b0 = *reinterpret_cast<const __nv_bfloat162*>(&u.x);
+        const __nv_bfloat162 b1 = *reinterpret_cast<const __nv_bfloat162*>(&u.y);
+        pv[4 * m] = __low2float(b0); pv[4 * m + 1] = __high2float(b0);
+        pv[4 * m + 2] = __low2float(b1); pv[4 * m + 3] = __high2float(b1);
+      }
+    } else {
+      const float* prow = reinterpret_cast<const float*>(proj_v) + (long long)(s0 + l) * HID;
+#pragma unroll
+      for (int m = 0; m < 4; ++m) {
+        const float4 t = __ldg(reinterpret_cast<const float4*>(prow + 128 * m + 4 * lane));
+        pv[4 * m] = t.x; pv[4 * m + 1] = t.y; pv[4 * m + 2] = t.z; pv[4 * m + 3] = t.w;
+      }
+    }
+    float s = 0.f;
+#pragma unroll
+    for (int i = 0; i < 16; ++i) s = fmaf(av[i], tanh_fast(pv[i] + qv[i]), s);
+    s = warp_sum(s);
+    if (lane == 0) sc[l] = s;
+  }
+  __syncthreads();
+  // softmax statistics (every warp computes them redundantly: L is a few hundred at most)
+  float mx = -INFINITY;
+  for (int l = lane; l < L; l += 32) mx = fmaxf(mx, sc[l]);
+  mx = warp_max(mx);
+  float sum = 0.f;
+  for (int l = lane; l < L; l += 32) sum += expf(sc[l] - mx);
+  sum = warp_sum(sum);
+  __syncthreads();
+  const float inv = 1.0f / sum;
+  for (int l = threadIdx.x; l < L; l += ATT_THREADS) sc[l] = expf(sc[l] - mx) * inv;
+  __syncthreads();
+  // pass 2
+  if (BF16) {
+    // 64 threads per clip row (8 bf16 each), 4 clip groups
+    const int grp = threadIdx.x >> 6, t = threadIdx.x & 63;
+    float acc[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) acc[i] = 0.f;
+    const bf16* cbase = reinterpret_cast<const bf16*>(clip_v) + (long long)s0 * ld_clip + 8 * t;
+    for (int l = grp; l < L; l += 4) {
+      const uint4 u = __ldg(reinterpret_cast<const uint4*>(cbase + (long long)l * ld_clip));
+      const float w = sc[l];
+      const __nv_bfloat162* b = reinterpret_cast<const __nv_bfloat162*>(&u);
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        acc[2 * i] = fmaf(w, __low2float(b[i]), acc[2 * i]);
+        acc[2 * i + 1] = fmaf(w, __high2float(b[i]), acc[2 * i + 1]);
+      }
+    }
+#pragma unroll
+    for (int i = 0; i < 8; ++i) red[grp][8 * t + i] = acc[i];
+  } else {
+    // 128 threads per clip row (4 floats each, 125 active), 2 clip groups
+    const int grp = threadIdx.x >> 7, t = threadIdx.x & 127;
+    float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (t < ECHR_VIDEO_DIM / 4) {
+      const float* cbase = reinterpret_cast<const float*>(clip_v) + (long long)s0 * ld_clip + 4 * t;
+      for (int l = grp; l < L; l += 2) {
+        const float4 c = __ldg(reinterpret_cast<const float4*>(cbase + (long long)l * ld_clip));
+        const float w = sc[l];
+        acc.x = fmaf(w, c.x, acc.x); acc.y = fmaf(w, c.y, acc.y);
+        acc.z = fmaf(w, c.z, acc.z); acc.w = fmaf(w, c.w, acc.w);
+      }
+    }
+    *reinterpret_cast<float4*>(&red[grp][4 * t]) = acc;
+  }
+  __syncthreads();
+  for (int c = threadIdx.x; c < ECHR_VIDEO_DIM; c += ATT_THREADS) {
+    float v = red[0][c] + red[1][c];
+    if (BF16) v += red[2][c] + red[3][c];
+    if (out_f32 != nullptr) out_f32[(long long)r * ECHR_VIDEO_DIM + c] = v;
+    if (out_hi != nullptr) {
+      bf16 h, l2;
+      split_bf16(v, h, l2);
+      out_hi[(long long)r * ld_bf + c] = h;
+      if (out_lo != nullptr) out_lo[(long long)r * ld_bf + c] = l2;
+    }
+  }
+}
+
+cudaError_t launch_attention(const float* q, const void* proj, const void* clip, int64_t ld_clip,
+                             int clip_bf16, const float* alpha, const int32_t* row_start,
+                             const int32_t* row_len, int64_t rows, float* out_f32, bf16* out_hi,
+                             bf16* out_lo, int64_t ld_bf, cudaStream_t st) {
+  if (rows == 0) return cudaSuccess;
+  if (clip_bf16)
+    attention_kernel<true><<<(int)rows, ATT_THREADS, 0, st>>>(q, proj, clip, ld_clip, alpha, row_start,
+                                                              row_len, out_f32, out_hi, out_lo, ld_bf);
+  else
+    attention_kernel<false><<<(int)rows, ATT_THREADS, 0, st>>>(q, proj, clip, ld_clip, alpha, row_start,
+                                                               row_len, out_f32, out_hi, out_lo, ld_bf);
+  count_launch();
+  return cudaGetLastError();
+}
+
+// ---------------------------------------------------------------------------------------------
+// decode_init: one CTA per decode row (row = event * beam + slot).  The activation buffers and
+// c-state were zeroed by memset nodes before this kernel.
+__global__ void __launch_bounds__(128)
+decode_init_kernel(int beam, int a_planes, const float* __restrict__ event_ctx,
+                   const float* __restrict__ lda, const int32_t* __restrict__ ev_video,
+                   const int32_t* __restrict__ ev_start, const int32_t* __restrict__ ev_len,
+                   const bf16* __restrict__ embed, long long embed_plane, bf16* __restrict__ act0,
+                   bf16* __restrict__ act1, long long act_plane, int32_t* __restrict__ row_start,
+                   int32_t* __restrict__ row_len, int32_t* __restrict__ unfinished,
+                   float* __restrict__ beam_score, int32_t* __restrict__ beam_live,
+                   float* __restrict__ best_score) {
+  const int r = blockIdx.x;
+  const int e = r / beam, slot = r - e * beam;
+  const int v = ev_video[e];
+  bf16* rows[2] = {act0 + (long long)r * ACT_LD, act1 + (long long)r * ACT_LD};
+  for (int c = threadIdx.x; c < HID + VID_PAD; c += blockDim.x) {
+    float x;
+    int col;
+    if (c < HID) {
+      x = __ldg(event_ctx + (long long)e * HID + c);
+      col = ACT_EV + c;
+    } else {
+      const int d = c - HID;
+      x = d < ECHR_LDA_DIM ? __ldg(lda + (long long)v * ECHR_LDA_DIM + d) : 0.f;
+      col = ACT_VID + d;
+    }
+    bf16 h, l;
+    split_bf16(x, h, l);
+#pragma unroll
+    for (int b = 0; b < 2; ++b) {
+      rows[b][col] = h;
+      if (a_planes > 1) rows[b][act_plane + col] = l;
+    }
+  }
+  // BOS embedding (token 0) into buffer 0
+  for (int c = threadIdx.x; c < HID; c += blockDim.x) {
+    rows[0][ACT_X + c] = embed[c];
+    if (a_planes > 1) rows[0][act_plane + ACT_X + c] = embed[embed_plane + c];
+  }
+  if (threadIdx.x == 0) {
+    row_start[r] = ev_start[e];
+    row_len[r] = ev_len[e];
+    unfinished[r] = 1;
+    beam_score[r] = 0.f;
+    beam_live[r] = (slot == 0) ? 1 : 0;
+    if (slot == 0) best_score[e] = -INFINITY;
+  }
+}
+
+cudaError_t launch_decode_init(const echr_batch* b, int beam, cudaStream_t st) {
+  const int rows = b->n_events * beam;
+  if (rows == 0) return cudaSuccess;
+  const echr_model* m = b->model;
+  decode_init_kernel<<<rows, 128, 0, st>>>(
+      beam, (int)b->act[0].planes, b->event_ctx, b->lda, b->ev_video, b->ev_start, b->ev_len,
+      m->embed.p, m->embed.plane_stride(), b->act[0].p, b->act[1].p, b->act[0].plane_stride(),
+      b->row_start, b->row_len, b->unfinished, b->beam_score, b->beam_live, b->best_score);
+  count_launch();
+  return cudaGetLastError();
+}
+
+// ---------------------------------------------------------------------------------------------
+// Merge of the logit GEMM's per-tile partial records of one row, by one warp.
+// Record layout (LogitRec<TOPK>): [0] sum exp(x - v0), [1..TOPK] values desc, [1+TOPK..] indices.
+struct RowStat {
+  float max_val;   // largest logit of the row
+  int max_idx;     // its column (lowest column among equals, like torch.max)
+  float log_sum;   // log sum_j exp(x_j - max_val)   => log-prob of column j = x_j - max_val - log_sum
+};
+
+template <int TOPK>
+__device__ __forceinline__ RowStat merge_row_stats(const float* __restrict__ rec_row, int n_tiles,
+                                                   int lane) {
+  constexpr int W = LogitRec<TOPK>::WORDS;
+  float bv = -INFINITY;
+  int bi = 0x7fffffff;
+  for (int t = lane; t < n_tiles; t += 32) {
+    const float v = rec_row[t * W + 1];
+    const int i = __float_as_int(rec_row[t * W + 1 + TOPK]);
+    if (v > bv || (v == bv && i < bi)) { bv = v; bi = i; }
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    const float ov = __shfl_xor_sync(0xffffffffu, bv, o);
+    const int oi = __shfl_xor_sync(0xffffffffu, bi, o);
+    if (ov > bv || (ov == bv && oi < bi)) { bv = ov; bi = oi; }
+  }
+  float sum = 0.f;
+  for (int t = lane; t < n_tiles; t += 32)
+    sum += rec_row[t * W] * expf(rec_row[t * W + 1] - bv);
+  sum = warp_sum(sum);
+  RowStat s;
+  s.max_val = bv;
+  s.max_idx = bi;
+  s.log_sum = logf(sum);
+  return s;
+}
+
+// copy one embedding row (512 bf16 per plane) into the X columns of an activation row
+__device__ __forceinline__ void copy_embed_row(const bf16* __restrict__ embed, long long embed_plane,
+                                               int tok, bf16* __restrict__ act_row, long long act_plane,
+                                               int planes, int lane) {
+  for (int p = 0; p < planes; ++p) {
+    const uint4* src = reinterpret_cast<const uint4*>(embed + p * embed_plane + (long long)tok * HID);
+    uint4* dst = reinterpret_cast<uint4*>(act_row + p * act_plane + ACT_X);
+    dst[lane] = __ldg(src + lane);
+    dst[lane + 32] = __ldg(src + lane + 32);
+  }
+}
+
+constexpr int FIN_WARPS = 4;
+
+// Greedy bookkeeping of OldModel.sample (OldModel_NEW.py:154-183): step `t` here is the
+// reference's iteration t+1 — token = argmax of this step's log-probs, `unfinished` is and-ed with
+// token > 0, the stored token is masked, the stored log-prob is NOT, and the raw argmax is what
+// gets embedded for the next step.
+__global__ void __launch_bounds__(FIN_WARPS * 32)
+finalize_greedy_kernel(int rows, int n_tiles, int step, int seq_len, const float* __restrict__ partial,
+                       const bf16* __restrict__ embed, long long embed_plane, bf16* __restrict__ act_next,
+                       long long act_plane, int planes, int32_t* __restrict__ unfinished,
+                       int32_t* __restrict__ tokens, float* __restrict__ logp) {
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int r = blockIdx.x * FIN_WARPS + warp;
+  if (r >= rows) return;
+  const RowStat s = merge_row_stats<1>(partial + (long long)r * n_tiles * LogitRec<1>::WORDS, n_tiles, lane);
+  const int tok = s.max_idx;
+  if (lane == 0) {
+    const int unf = (step == 0 ? 1 : unfinished[r]) & (tok > 0 ? 1 : 0);
+    unfinished[r] = unf;
+    tokens[(long long)r * seq_len + step] = unf ? tok : 0;
+    logp[(long long)r * seq_len + step] = -s.log_sum;
+  }
+  if (step + 1 < seq_len)
+    copy_embed_row(embed, embed_plane, tok, act_next + (long long)r * ACT_LD, act_plane, planes, lane);
+}
+
+cudaError_t launch_finalize_greedy(const echr_batch* b, int step, int32_t* tokens, float* logp,
+                                   cudaStream_t st) {
+  const int rows = b->n_events;
+  if (rows == 0) return cudaSuccess;
+  const echr_model* m = b->model;
+  const int n_tiles = (m->V1 + 127) / 128;
+  const PlaneMat& nxt = b->act[(step + 1) & 1];
+  finalize_greedy_kernel<<<(rows + FIN_WARPS - 1) / FIN_WARPS, FIN_WARPS * 32, 0, st>>>(
+      rows, n_tiles, step, m->cfg.seq_length, b->partial, m->embed.p, m->embed.plane_stride(), nxt.p,
+      nxt.plane_stride(), (int)nxt.planes, b->unfinished, tokens, logp);
+  count_launch();
+  return cudaGetLastError();
+}
+
+// Teacher-forced step (OldModel_NEW.py:98-130): the logit GEMM stored raw logits into
+// logprobs[r, step, :]; subtract the row's log-sum-exp in place and embed seq[r, step+1].
+__global__ void __launch_bounds__(FIN_WARPS * 32)
+finalize_tf_kernel(int rows, int n_tiles, int step, int seq_cols, int V1, const float* __restrict__ partial,
+                   const int32_t* __restrict__ seq, const bf16* __restrict__ embed, long long embed_plane,
+                   bf16* __restrict__ act_next, long long act_plane, int planes,
+                   float* __restrict__ logprobs) {
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int r = blockIdx.x * FIN_WARPS + warp;
+  if (r >= rows) return;
+  if (step >= 0) {  // step == -1: only embed seq[:, 0]
+    const RowStat s = merge_row_stats<1>(partial + (long long)r * n_tiles * LogitRec<1>::WORDS, n_tiles, lane);
+    const float lse = s.max_val + s.log_sum;
+    float* row = logprobs + ((long long)r * (seq_cols - 1) + step) * V1;
+    for (int c = lane; c < V1; c += 32) row[c] -= lse;
+  }
+  if (step + 1 < seq_cols - 1) {
+    int tok = seq[(long long)r * seq_cols + step + 1];
+    tok = min(max(tok, 0), V1 - 1);
+    copy_embed_row(embed, embed_plane, tok, act_next + (long long)r * ACT_LD, act_plane, planes, lane);
+  }
+}
+
+cudaError_t launch_finalize_tf(const echr_batch* b, int step, const int32_t* seq, int seq_cols,
+                               float* logprobs, cudaStream_t st) {
+  const int rows = b->n_events;
+  if (rows == 0) return cudaSuccess;
+  const echr_model* m = b->model;
+  const int n_tiles = (m->V1 + 127) / 128;
+  const PlaneMat& nxt = b->act[(step + 1) & 1];
+  finalize_tf_kernel<<<(rows + FIN_WARPS - 1) / FIN_WARPS, FIN_WARPS * 32, 0, st>>>(
+      rows, n_tiles, step, seq_cols, m->V1, b->partial, seq, m->embed.p, m->embed.plane_stride(), nxt.p,
+      nxt.plane_stride(), (int)nxt.planes, logprobs);
+  count_launch();
+  return cudaGetLastError();
+}
+
+// ---------------------------------------------------------------------------------------------
+// Beam step (spec: oracle/echr_oracle.py beam_search).  One CTA per event, warp b = slot b.
+constexpr int BEAM_MAX = 4;
+constexpr int BEAM_SEG = 3 * HID;  // 1536 elements: h of the three streams / c of the three streams
+
+__global__ void __launch_bounds__(BEAM_MAX * 32)
+finalize_beam_kernel(int beam, int n_tiles, int step, int seq_len, const float* __restrict__ partial,
+                     const bf16* __restrict__ embed, long long embed_plane, bf16* __restrict__ act_next,
+                     long long act_plane, int planes, float* __restrict__ c_next, long long c_layer_stride,
+                     float* __restrict__ beam_score, int32_t* __restrict__ beam_live,
+                     const int32_t* __restrict__ hist_tok_in, int32_t* __restrict__ hist_tok_out,
+                     const float* __restrict__ hist_lp_in, float* __restrict__ hist_lp_out,
+                     float* __restrict__ best_score, int32_t* __restrict__ tokens,
+                     float* __restrict__ logp, float* __restrict__ score_out) {
+  constexpr int W = LogitRec<4>::WORDS;
+  __shared__ float cand_total[BEAM_MAX][BEAM_MAX];
+  __shared__ float cand_lp[BEAM_MAX][BEAM_MAX];
+  __shared__ int cand_tok[BEAM_MAX][BEAM_MAX];
+  __shared__ int sel_parent[BEAM_MAX], sel_tok[BEAM_MAX], sel_fin[BEAM_MAX];
+  __shared__ float sel_lp[BEAM_MAX], sel_total[BEAM_MAX];
+  __shared__ __align__(16) float stage[BEAM_MAX * BEAM_SEG];  // 24 KB
+  const int e = blockIdx.x;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int row0 = e * beam;
+
+  // ---- 1. per-slot top-`beam` log-probs
+  if (warp < beam) {
+    const int r = row0 + warp;
+    const float* rec = partial + (long long)r * n_tiles * W;
+    const RowStat s = merge_row_stats<4>(rec, n_tiles, lane);
+    // each lane holds the candidates of its tiles (<= 2 tiles x 4)
+    float cv[8];
+    int ci[8];
+#pragma unroll
+    for (int u = 0; u < 2; ++u) {
+      const int t = lane + 32 * u;
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        cv[4 * u + k] = (t < n_tiles) ? rec[t * W + 1 + k] : -INFINITY;
+        ci[4 * u + k] = (t < n_tiles) ? __float_as_int(rec[t * W + 5 + k]) : 0x7fffffff;
+      }
+    }
+    const bool live = beam_live[r] != 0;
+    const float base = beam_score[r];
+    for (int k = 0; k < beam; ++k) {
+      float bv = -INFINITY;
+      int bi = 0x7fffffff, bslot = -1;
+#pragma unroll
+      for (int u = 0; u < 8; ++u)
+        if (cv[u] > bv || (cv[u] == bv && ci[u] < bi)) { bv = cv[u]; bi = ci[u]; bslot = u; }
+      float wv = bv;
+      int wi = bi;
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) {
+        const float ov = __shfl_xor_sync(0xffffffffu, wv, o);
+        const int oi = __shfl_xor_sync(0xffffffffu, wi, o);
+        if (ov > wv || (ov == wv && oi < wi)) { wv = ov; wi = oi; }
+      }
+      if (bslot >= 0 && bv == wv && bi == wi) {  // the owning lane retires the winner
+#pragma unroll
+        for (int u = 0; u < 8; ++u)
+          if (u == bslot) { cv[u] = -INFINITY; ci[u] = 0x7fffffff; }
+      }
+      if (lane == 0) {
+        const float lp = (wv - s.max_val) - s.log_sum;
+        cand_lp[warp][k] = lp;
+        cand_tok[warp][k] = wi;
+        cand_total[warp][k] = live ? base + lp : -INFINITY;
+      }
+    }
+  }
+  __syncthreads();
+
+  // ---- 2. select the `beam` best proposals (score desc, then parent slot, then rank)
+  if (threadIdx.x == 0) {
+    bool used[BEAM_MAX][BEAM_MAX];
+    for (int b = 0; b < BEAM_MAX; ++b)
+      for (int k = 0; k < BEAM_MAX; ++k) used[b][k] = false;
+    for (int n = 0; n < beam; ++n) {
+      int pb = -1, pk = -1;
+      float best = -INFINITY;
+      for (int b = 0; b < beam; ++b) {
+        if (beam_live[row0 + b] == 0) continue;
+        for (int k = 0; k < beam; ++k) {
+          if (used[b][k]) continue;
+          if (pb < 0 || cand_total[b][k] > best) { best = cand_total[b][k]; pb = b; pk = k; }
+        }
+      }
+      used[pb][pk] = true;
+      sel_parent[n] = pb;
+      sel_tok[n] = cand_tok[pb][pk];
+      sel_lp[n] = cand_lp[pb][pk];
+      sel_total[n] = best;
+      sel_fin[n] = (cand_tok[pb][pk] == 0 || step == seq_len - 1) ? 1 : 0;
+    }
+  }
+  __syncthreads();
+
+  // ---- 3. histories (ping-pong), scores, live flags, result update
+  if (warp < beam) {
+    const int r = row0 + warp, pr = row0 + sel_parent[warp];
+    for (int t = lane; t < seq_len; t += 32) {
+      int tk = 0;
+      float lp = 0.f;
+      if (t < step) { tk = hist_tok_in[(long long)pr * seq_len + t]; lp = hist_lp_in[(long long)pr * seq_len + t]; }
+      else if (t == step) { tk = sel_tok[warp]; lp = sel_lp[warp]; }
+      hist_tok_out[(long long)r * seq_len + t] = tk;
+      hist_lp_out[(long long)r * seq_len + t] = lp;
+    }
+  }
+  __syncthreads();
+  if (warp == 0) {
+    float best = best_score[e];
+    for (int n = 0; n < beam; ++n) {  // ascending slot: lower slots win ties
+      if (sel_fin[n] && sel_total[n] > best) {
+        best = sel_total[n];
+        for (int t = lane; t < seq_len; t += 32) {
+          tokens[(long long)e * seq_len + t] = hist_tok_out[(long long)(row0 + n) * seq_len + t];
+          logp[(long long)e * seq_len + t] = hist_lp_out[(long long)(row0 + n) * seq_len + t];
+        }
+      }
+    }
+    if (lane == 0) {
+      best_score[e] = best;
+      score_out[e] = best;
+    }
+    if (lane < beam) {
+      beam_score[row0 + lane] = sel_total[lane];
+      beam_live[row0 + lane] = sel_fin[lane] ? 0 : 1;
+    }
+  }
+  if (step + 1 >= seq_len) return;
+
+  // ---- 4. next inputs and state reorder
+  if (warp < beam)
+    copy_embed_row(embed, embed_plane, sel_tok[warp], act_next + (long long)(row0 + warp) * ACT_LD,
+                   act_plane, planes, lane);
+  bool identity = true;
+  for (int n = 0; n < beam; ++n) identity = identity && (sel_parent[n] == n);
+  if (identity) return;  // uniform across the CTA
+  // h planes: 1536 bf16 = 768 words per row
+  for (int p = 0; p < planes; ++p) {
+    uint32_t* st32 = reinterpret_cast<uint32_t*>(stage);
+    for (int i = threadIdx.x; i < beam * (BEAM_SEG / 2); i += blockDim.x) {
+      const int b = i / (BEAM_SEG / 2), c = i - b * (BEAM_SEG / 2);
+      st32[i] = *reinterpret_cast<const uint32_t*>(act_next + p * act_plane + (long long)(row0 + b) * ACT_LD + ACT_H + 2 * c);
+    }
+    __syncthreads();
+    for (int i = threadIdx.x; i < beam * (BEAM_SEG / 2); i += blockDim.x) {
+      const int b = i / (BEAM_SEG / 2), c = i - b * (BEAM_SEG / 2);
+      *reinterpret_cast<uint32_t*>(act_next + p * act_plane + (long long)(row0 + b) * ACT_LD + ACT_H + 2 * c) =
+          st32[sel_parent[b] * (BEAM_SEG / 2) + c];
+    }
+    __syncthreads();
+  }
+  // c state: [3][rows][512] fp32
+  for (int i = threadIdx.x; i < beam * BEAM_SEG; i += blockDim.x) {
+    const int b = i / BEAM_SEG, c = i - b * BEAM_SEG;
+    const int layer = c / HID, u = c - layer * HID;
+    stage[i] = c_next[layer * c_layer_stride + (long long)(row0 + b) * HID + u];
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < beam * BEAM_SEG; i += blockDim.x) {
+    const int b = i / BEAM_SEG, c = i - b * BEAM_SEG;
+    const int layer = c / HID, u = c - layer * HID;
+    c_next[layer * c_layer_stride + (long long)(row0 + b) * HID + u] = stage[sel_parent[b] * BEAM_SEG + c];
+  }
+}
+
+cudaError_t launch_finalize_beam(const echr_batch* b, int beam, int step, int32_t* tokens,
+                                 float* logp, float* score, cudaStream_t st) {
+  if (b->n_events == 0) return cudaSuccess;
+  if (beam < 1 || beam > BEAM_MAX) return cudaErrorInvalidValue;
+  const echr_model* m = b->model;
+  const int n_tiles = (m->V1 + 127) / 128;
+  if (n_tiles > 64) return cudaErrorInvalidValue;
+  const int S = m->cfg.seq_length;
+  const long long rows = (long long)b->n_events * beam;
+  const PlaneMat& nxt = b->act[(step + 1) & 1];
+  const long long hist = (long long)b->cap.max_rows * S;
+  const int in = step & 1, out = in ^ 1;
+  finalize_beam_kernel<<<b->n_events, BEAM_MAX * 32, 0, st>>>(
+      beam, n_tiles, step, S, b->partial, m->embed.p, m->embed.plane_stride(), nxt.p,
+      nxt.plane_stride(), (int)nxt.planes, b->cstate[(step + 1) & 1], rows * HID, b->beam_score,
+      b->beam_live, b->beam_hist_tok + in * hist, b->beam_hist_tok + out * hist,
+      b->beam_hist_lp + in * hist, b->beam_hist_lp + out * hist, b->best_score, tokens, logp, score);
+  count_launch();
+  return cudaGetLastError();
+}
+
+}  // namespace echr

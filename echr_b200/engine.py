@@ -1,0 +1,209 @@
+"""Python handle on the C-ABI engine (include/echr_b200.h): packed model + batch workspace.
+
+torch is used for device memory and streams only; every computation happens inside
+libechr_b200.so.  There is no fallback path: a missing library or a non-sm_100 device raises.
+"""
+import ctypes
+
+import numpy as np
+import torch
+
+from . import _lib
+from ._lib import BatchDesc, Capacity, Config, EchrError, Weights, WEIGHT_FIELDS, check
+
+# name -> (a_terms, w_terms, clip_bf16)
+PRECISIONS = {
+    # activations and weights as bf16 hi+lo planes (3 tensor-core products): fp32-grade for any checkpoint
+    "fp32": (2, 2, 0),
+    # weights rounded to bf16 (exact when the checkpoint is bf16-representable), activations hi+lo
+    "bf16w": (2, 1, 0),
+    # everything single-plane bf16, attention reads bf16 clip features / projections
+    "bf16": (1, 1, 1),
+}
+
+
+def _stream():
+    return torch.cuda.current_stream().cuda_stream
+
+
+def _i32(a):
+    return np.ascontiguousarray(np.asarray(a, dtype=np.int32))
+
+
+class BatchLayout(object):
+    """Host-side index arrays of a batch of independent videos (echr_batch_desc_t)."""
+
+    def __init__(self, clip_counts, ind_lists, soi_lists):
+        self.n_videos = len(clip_counts)
+        self.clip_offsets = _i32(np.concatenate([[0], np.cumsum(clip_counts)]))
+        ev_video, ev_s, ev_e, ev_ind = [], [], [], []
+        self.events_per_video = []
+        for v, (inds, sois) in enumerate(zip(ind_lists, soi_lists)):
+            if len(inds) != len(sois):
+                raise ValueError("video %d: ind_select_list and soi_select_list differ in length" % v)
+            self.events_per_video.append(len(sois))
+            for ind, soi in zip(inds, sois):
+                ev_video.append(v)
+                ev_s.append(int(soi[0]))
+                ev_e.append(int(soi[1]))
+                ev_ind.append(int(ind))
+        self.event_video, self.event_start = _i32(ev_video), _i32(ev_s)
+        self.event_end, self.event_ind = _i32(ev_e), _i32(ev_ind)
+        self.n_events = len(ev_video)
+        self.n_clips = int(self.clip_offsets[-1])
+        self.n_pairs = int(sum(n * n for n in self.events_per_video))
+
+    def desc(self):
+        d = BatchDesc()
+        d.n_videos, d.n_events = self.n_videos, self.n_events
+        d.host_clip_offsets = self.clip_offsets.ctypes.data
+        d.host_event_video = self.event_video.ctypes.data
+        d.host_event_start = self.event_start.ctypes.data
+        d.host_event_end = self.event_end.ctypes.data
+        d.host_event_ind = self.event_ind.ctypes.data
+        return d
+
+
+class Engine(object):
+    """Packed weights (echr_model_t) plus one growable batch workspace (echr_batch_t)."""
+
+    def __init__(self, state_dict, vocab_size, seq_length=30, precision="fp32", device="cuda:0"):
+        if precision not in PRECISIONS:
+            raise ValueError("precision must be one of %s" % sorted(PRECISIONS))
+        self.lib = _lib.load()
+        self.device = torch.device(device)
+        if self.device.type != "cuda":
+            raise EchrError("echr_b200 runs on a B200 (sm_100a) only; there is no CPU path")
+        self.precision = precision
+        self.vocab_size, self.seq_length = int(vocab_size), int(seq_length)
+        self.V1 = self.vocab_size + 1
+        self._model = ctypes.c_void_p()
+        self._batch = ctypes.c_void_p()
+        self._cap = None
+        self.beam_cap = 1
+        with torch.cuda.device(self.device):
+            check(self.lib.echr_device_check(self.device.index or 0), "echr_device_check")
+            a, w, cb = PRECISIONS[precision]
+            cfg = Config(self.vocab_size, self.seq_length, a, w, cb)
+            ws = Weights()
+            keep = []
+            for field, key in WEIGHT_FIELDS:
+                t = state_dict[key].detach().to(device=self.device, dtype=torch.float32).contiguous()
+                keep.append(t)
+                setattr(ws, field, t.data_ptr())
+            check(self.lib.echr_model_create(ctypes.byref(cfg), ctypes.byref(ws), _stream(),
+                                             ctypes.byref(self._model)), "echr_model_create")
+            del keep  # echr_model_create synchronises; the packed copy is what the kernels read
+
+    # ------------------------------------------------------------------ lifetime
+    def close(self):
+        if getattr(self, "_batch", None) is not None and self._batch.value:
+            self.lib.echr_batch_destroy(self._batch)
+            self._batch = ctypes.c_void_p()
+        if getattr(self, "_model", None) is not None and self._model.value:
+            self.lib.echr_model_destroy(self._model)
+            self._model = ctypes.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def reserve(self, n_videos, n_clips, n_events, n_pairs, beam=1):
+        """Make sure the workspace holds a batch of this size (re-allocates only when it grows)."""
+        need = (n_videos, n_clips, max(n_events, 1), max(n_pairs, 1), max(n_events, 1) * beam)
+        if self._cap is not None and all(c >= n for c, n in zip(self._cap, need)):
+            return
+        if self._cap is not None:
+            need = tuple(max(c, n) for c, n in zip(self._cap, need))
+        with torch.cuda.device(self.device):
+            torch.cuda.synchronize()
+            if self._batch.value:
+                check(self.lib.echr_batch_destroy(self._batch), "echr_batch_destroy")
+                self._batch = ctypes.c_void_p()
+            cap = Capacity(*need)
+            check(self.lib.echr_batch_create(self._model, ctypes.byref(cap), ctypes.byref(self._batch)),
+                  "echr_batch_create")
+        self._cap = need
+
+    # ------------------------------------------------------------------ device-input path
+    def set_inputs(self, layout, c3d, tap, lda, beam=1):
+        """c3d [clips,500], tap [clips,512], lda [videos,100]: fp32 tensors on this device (or on
+        the host: they are then copied with cudaMemcpyAsync)."""
+        self.reserve(layout.n_videos, layout.n_clips, layout.n_events, layout.n_pairs, beam)
+        on_host = 0 if c3d.is_cuda else 1
+        for t, shape in ((c3d, (layout.n_clips, 500)), (tap, (layout.n_clips, 512)), (lda, (layout.n_videos, 100))):
+            if tuple(t.shape) != shape or t.dtype != torch.float32 or not t.is_contiguous():
+                raise ValueError("expected contiguous fp32 tensor of shape %s, got %s %s" % (shape, tuple(t.shape), t.dtype))
+            if t.is_cuda != c3d.is_cuda:
+                raise ValueError("c3d, tap and lda must live on the same side (all host or all device)")
+        self.layout = layout
+        d = layout.desc()
+        with torch.cuda.device(self.device):
+            check(self.lib.echr_batch_set_inputs(self._batch, ctypes.byref(d), c3d.data_ptr(), tap.data_ptr(),
+                                                 lda.data_ptr(), on_host, _stream()), "echr_batch_set_inputs")
+
+    def encode(self):
+        with torch.cuda.device(self.device):
+            check(self.lib.echr_encode(self._batch, _stream()), "echr_encode")
+
+    def event_context(self):
+        out = torch.empty(self.layout.n_events, 512, dtype=torch.float32, device=self.device)
+        with torch.cuda.device(self.device):
+            check(self.lib.echr_get_event_context(self._batch, out.data_ptr(), _stream()), "echr_get_event_context")
+        return out
+
+    def decode_greedy(self):
+        n, S = self.layout.n_events, self.seq_length
+        tokens = torch.zeros(n, S, dtype=torch.int32, device=self.device)
+        logp = torch.zeros(n, S, dtype=torch.float32, device=self.device)
+        with torch.cuda.device(self.device):
+            check(self.lib.echr_decode_greedy(self._batch, tokens.data_ptr(), logp.data_ptr(), _stream()),
+                  "echr_decode_greedy")
+        return tokens, logp
+
+    def decode_beam(self, beam):
+        n, S = self.layout.n_events, self.seq_length
+        if self._cap[4] < n * beam:
+            raise EchrError("workspace was reserved for a smaller beam; pass beam= to set_inputs")
+        tokens = torch.zeros(n, S, dtype=torch.int32, device=self.device)
+        logp = torch.zeros(n, S, dtype=torch.float32, device=self.device)
+        score = torch.zeros(n, dtype=torch.float32, device=self.device)
+        with torch.cuda.device(self.device):
+            check(self.lib.echr_decode_beam(self._batch, int(beam), tokens.data_ptr(), logp.data_ptr(),
+                                            score.data_ptr(), _stream()), "echr_decode_beam")
+        return tokens, logp, score
+
+    def teacher_forced(self, seq):
+        """seq int [n_events, S] (column 0 = BOS) -> log-probs fp32 [n_events, S-1, V+1]."""
+        seq = seq.to(device=self.device, dtype=torch.int32).contiguous()
+        n, cols = seq.shape
+        if n != self.layout.n_events:
+            raise ValueError("seq has %d rows, batch has %d events" % (n, self.layout.n_events))
+        out = torch.empty(n, cols - 1, self.V1, dtype=torch.float32, device=self.device)
+        with torch.cuda.device(self.device):
+            check(self.lib.echr_teacher_forced(self._batch, seq.data_ptr(), cols, out.data_ptr(), _stream()),
+                  "echr_teacher_forced")
+        return out
+
+    # ------------------------------------------------------------------ host-buffer path (e2e)
+    def caption_host(self, layout, c3d, tap, lda, beam=1, out=None):
+        """Everything through one C-ABI call with HOST buffers: H2D, encode, decode, D2H, sync.
+        c3d/tap/lda are host fp32 tensors (pinned for full-speed copies).  Returns host tensors."""
+        self.reserve(layout.n_videos, layout.n_clips, layout.n_events, layout.n_pairs, beam)
+        self.layout = layout
+        n, S = layout.n_events, self.seq_length
+        if out is None:
+            out = (torch.zeros(n, S, dtype=torch.int32).pin_memory(), torch.zeros(n, S, dtype=torch.float32).pin_memory(),
+                   torch.zeros(n, dtype=torch.float32).pin_memory())
+        tokens, logp, score = out
+        d = layout.desc()
+        with torch.cuda.device(self.device):
+            check(self.lib.echr_caption_host(self._batch, ctypes.byref(d), c3d.data_ptr(), tap.data_ptr(), lda.data_ptr(),
+                                             int(beam), tokens.data_ptr(), logp.data_ptr(), score.data_ptr(), _stream()),
+                  "echr_caption_host")
+        return tokens, logp, score
+
+    def launch_count(self, reset=False):
+        return int(self.lib.echr_launch_count(1 if reset else 0))

@@ -1,16 +1,17 @@
 /* echr_b200 — C-ABI of the B200-native (sm_100a) ECHR caption-generation hot path.
  *
  * The reference (ttengwang/ECHR) is pure Python/PyTorch and has no FFI of its own; the entry
- * points below are the ones a binding for its hot path would need.  Each one names the reference
- * code it replaces (paths relative to the reference repository root).
+ * points below are the ones a binding for its hot path would need.  Each one names
+ * the reference code it replaces (paths relative to the reference repository root).
  *
  * Conventions
  *   - every function returns 0 on success or a negative code; echr_last_error() gives the text
- *     (thread-local).  No function allocates behind the caller's back except the *_create calls.
- *   - all pointers are DEVICE pointers unless the name says host; sizes/strides are in elements.
+ *     (thread-local).  Only the *_create calls allocate.
+ *   - pointers are DEVICE pointers unless the parameter name starts with `host_` or the comment
+ *     says host; sizes/strides are in elements.
  *   - `stream` is a cudaStream_t passed as void*; work is stream-ordered, nothing synchronises
  *     unless stated.
- *   - there is no CPU fallback: on a non-sm_100 device every entry fails with ECHR_ERR_NO_DEVICE.
+ *   - there is no CPU fallback: on a non-sm_100 device every entry fails with code -3.
  */
 #ifndef ECHR_B200_H_
 #define ECHR_B200_H_
@@ -21,7 +22,7 @@
 extern "C" {
 #endif
 
-#define ECHR_B200_ABI_VERSION 1
+#define ECHR_B200_ABI_VERSION 2
 
 #if defined(__GNUC__)
 #define ECHR_API __attribute__((visibility("default")))
@@ -29,15 +30,80 @@ extern "C" {
 #define ECHR_API
 #endif
 
+/* fixed sizes of the ECHR recipe (experiments/train_ECHR.sh:5, opts.py:81-154) */
+#define ECHR_VIDEO_DIM 500  /* C3D clip feature */
+#define ECHR_HIDDEN 512     /* every hidden / embedding size on the path */
+#define ECHR_LDA_DIM 100
+#define ECHR_HEADS 16
+
+typedef struct echr_model echr_model_t;
+typedef struct echr_batch echr_batch_t;
+
+typedef struct echr_config {
+  int32_t vocab_size; /* CG_vocab_size; the logit/embedding tables have vocab_size+1 rows        */
+  int32_t seq_length; /* CG_seq_length (30)                                                       */
+  int32_t a_terms;    /* 1: activations as one bf16 plane, 2: bf16 hi+lo planes (fp32-grade)      */
+  int32_t w_terms;    /* 1: weights rounded to bf16,        2: bf16 hi+lo planes (fp32-grade)     */
+  int32_t clip_bf16;  /* 1: the step attention reads bf16 clip features/projections, 0: fp32      */
+} echr_config_t;
+
+/* fp32 device pointers into the reference checkpoint's `cg_model` state_dict (train.py:456-461;
+ * key names in comments).  Dead parameters (h2a_layer, fusion_layer) are not needed. */
+typedef struct echr_weights {
+  const float* event_emb_w;  /* fusion_model.event_emb.weight            [512,1012] */
+  const float* event_emb_b;  /*                       .bias              [512]      */
+  const float* pos_fc1_w;    /* fusion_model.enc_attn.pair_pos_fc1.weight [512,512] */
+  const float* pos_fc1_b;
+  const float* pos_fc2_w;    /* fusion_model.enc_attn.pair_pos_fc2.weight [16,512]  */
+  const float* pos_fc2_b;
+  const float* query_w;      /* fusion_model.enc_attn.query_1.weight      [512,512] */
+  const float* query_b;
+  const float* key_w;        /* fusion_model.enc_attn.key_1.weight        [512,512] */
+  const float* key_b;
+  const float* out_w;        /* fusion_model.enc_attn.linear_out_1.weight [512,512,1,1] */
+  const float* out_b;
+  const float* embed_w;      /* lm_model.embed.weight                     [V+1,512] */
+  const float* logit_w;      /* lm_model.logit.weight                     [V+1,1536] */
+  const float* logit_b;
+  const float* lstm_w_ih[3]; /* lm_model.core.layer{0,1,2}.weight_ih      [2048,1024|1012|612] */
+  const float* lstm_w_hh[3]; /*                           .weight_hh      [2048,512] */
+  const float* lstm_b_ih[3];
+  const float* lstm_b_hh[3];
+  const float* ctx2att_w;    /* lm_model.core.attention.ctx2att.weight    [512,500] */
+  const float* ctx2att_b;
+  const float* h2att_w;      /* lm_model.core.attention.h2att.weight      [512,512] */
+  const float* h2att_b;
+  const float* alpha_w;      /* lm_model.core.attention.alpha_net.weight  [1,512] (bias cancels in the softmax) */
+} echr_weights_t;
+
+typedef struct echr_capacity {
+  int64_t max_videos;
+  int64_t max_clips;  /* sum of clips over the videos of one batch   */
+  int64_t max_events; /* sum of events (proposals) over the videos   */
+  int64_t max_pairs;  /* sum over videos of events^2                 */
+  int64_t max_rows;   /* decode rows = events * beam                 */
+} echr_capacity_t;
+
+/* One batch of independent videos.  All index arrays are HOST arrays. */
+typedef struct echr_batch_desc {
+  int32_t n_videos;
+  int32_t n_events;
+  const int32_t* host_clip_offsets; /* [n_videos+1] first clip row of each video in c3d/tap      */
+  const int32_t* host_event_video;  /* [n_events]   video of each event (non-decreasing)          */
+  const int32_t* host_event_start;  /* [n_events]   soi_select_list[i][0], video-local, inclusive */
+  const int32_t* host_event_end;    /* [n_events]   soi_select_list[i][1], video-local, exclusive */
+  const int32_t* host_event_ind;    /* [n_events]   ind_select_list[i],   video-local             */
+} echr_batch_desc_t;
+
 /* ---- library ---------------------------------------------------------------------------- */
 ECHR_API const char* echr_last_error(void);
 ECHR_API int echr_abi_version(void);
 /* 0 if `device` is an sm_100 GPU this build can run on. */
 ECHR_API int echr_device_check(int device);
 
-/* ---- building blocks ---------------------------------------------------------------------- */
+/* ---- building blocks (also used by the unit parity tests) -------------------------------- */
 /* fp32 [rows, cols] (row stride ld_src) -> bf16 planes hi (and lo = bf16(x - hi), may be NULL),
- * zero-padded to cols_dst columns, row stride ld_dst.  Used to stage tensor-core operands. */
+ * zero-padded to cols_dst columns, row stride ld_dst. */
 ECHR_API int echr_split_bf16(const float* src, int64_t rows, int64_t cols, int64_t ld_src, void* hi, void* lo,
                     int64_t ld_dst, int64_t cols_dst, void* stream);
 
@@ -45,13 +111,73 @@ ECHR_API int echr_split_bf16(const float* src, int64_t rows, int64_t cols, int64
  * Replaces every nn.Linear on the path (models/MA_attention_8_NEW.py:29,93-96;
  * models/OldModel_NEW.py:51,372-374).  A and W are bf16 plane stacks ([planes][rows][ld]):
  * planes=1 is the plain bf16 operand, planes=2 adds the low-order plane (fp32-grade product).
- * k must be a multiple of 64 (pad with zeros), k <= 2048.  act: 0 none, 1 tanh, 2 tanh.approx.
+ * k must be a multiple of 64 (pad with zeros), k <= 2048.  act: 0 none, 1 tanh.
  * Outputs: out_f32 (may be NULL) and/or bf16 planes out_hi/out_lo (may be NULL). */
 ECHR_API int echr_gemm_planes(const void* a, int64_t m, int64_t k, int64_t a_ld, int a_planes,
                      int64_t a_plane_stride, const void* w, int64_t n, int64_t w_ld, int w_planes,
                      int64_t w_plane_stride, const float* bias, int act, float* out_f32,
                      int64_t ld_f32, void* out_hi, void* out_lo, int64_t ld_bf, int block_n,
                      void* stream);
+
+/* One late-fusion attention step (models/OldModel_NEW.py:376-401 with ctx2att hoisted):
+ * for each row r: window = clips [row_start[r], row_start[r]+row_len[r]) of proj/clip;
+ * score_l = alpha . tanh(proj[l] + q[r]); att[r] = sum_l softmax(score)_l * clip[l].
+ * proj [n_clips,512], clip [n_clips, ld_clip] are fp32 (clip_bf16=0) or bf16 (clip_bf16=1);
+ * q fp32 [rows,512]; out_f32 [rows,500] (may be NULL); out_hi/out_lo bf16 [rows, ld_bf] (may be NULL). */
+ECHR_API int echr_attention_step(const float* q, const void* proj, const void* clip, int64_t ld_clip,
+                        int clip_bf16, const float* alpha, const int32_t* row_start,
+                        const int32_t* row_len, int64_t rows, float* out_f32, void* out_hi,
+                        void* out_lo, int64_t ld_bf, void* stream);
+
+/* ---- model: packed weights --------------------------------------------------------------- */
+/* Packs the checkpoint into kernel layouts (bf16 planes, gate-interleaved LSTM rows, fused biases).
+ * Replaces CaptionGenerator.__init__ + load_state_dict (CaptionGenerator.py:8-14, eval.py:65-67).
+ * Synchronises `stream` before returning. */
+ECHR_API int echr_model_create(const echr_config_t* config, const echr_weights_t* weights, void* stream,
+                      echr_model_t** out);
+ECHR_API int echr_model_destroy(echr_model_t* model);
+
+/* ---- batch: workspace + inputs ----------------------------------------------------------- */
+ECHR_API int echr_batch_create(const echr_model_t* model, const echr_capacity_t* capacity, echr_batch_t** out);
+ECHR_API int echr_batch_destroy(echr_batch_t* batch);
+/* c3d [n_clips,500], tap [n_clips,512], lda [n_videos,100] fp32; on_host=1: host buffers (pinned or
+ * pageable), copied with cudaMemcpyAsync; on_host=0: device buffers.  Inputs are copied into the
+ * batch workspace, so the caller's buffers may be reused once the stream has passed this call. */
+ECHR_API int echr_batch_set_inputs(echr_batch_t* batch, const echr_batch_desc_t* desc, const float* c3d,
+                          const float* tap, const float* lda, int on_host, void* stream);
+
+/* Context assembly + event relation encoder for the whole batch: mean-pooled clips and proposal
+ * states per event, pairwise position embedding, pair MLP, multi-head relation attention, and the
+ * hoisted ctx2att projection (CaptionGenerator.py:87-167; models/MA_attention_8_NEW.py:35-177;
+ * models/OldModel_NEW.py:381). */
+ECHR_API int echr_encode(echr_batch_t* batch, void* stream);
+/* event context [n_events,512] fp32 produced by echr_encode (CaptionGenerator.py:129). */
+ECHR_API int echr_get_event_context(const echr_batch_t* batch, float* out, void* stream);
+
+/* Greedy decode resident on the device (models/OldModel_NEW.py:139-187, sample_max=1):
+ * tokens int32 [n_events, seq_length] with the reference's masking (finished rows -> 0),
+ * logp fp32 [n_events, seq_length] UNmasked max log-probabilities (as the reference returns). */
+ECHR_API int echr_decode_greedy(echr_batch_t* batch, int32_t* tokens, float* logp, void* stream);
+/* Beam search resident on the device (spec: oracle/echr_oracle.py beam_search; the reference has
+ * none, models/OldModel_NEW.py:144-146).  beam in 1..4.  tokens/logp [n_events, seq_length] zero
+ * padded, score [n_events] = cumulative log-probability of the returned hypothesis. */
+ECHR_API int echr_decode_beam(echr_batch_t* batch, int beam, int32_t* tokens, float* logp, float* score,
+                     void* stream);
+/* Teacher-forced log-probabilities (models/OldModel_NEW.py:98-130): seq int32 [n_events, seq_cols]
+ * (column 0 = BOS = 0); logprobs fp32 [n_events, seq_cols-1, vocab_size+1]. */
+ECHR_API int echr_teacher_forced(echr_batch_t* batch, const int32_t* seq, int seq_cols, float* logprobs,
+                        void* stream);
+
+/* End-to-end call with HOST buffers (eval_utils.py:52,129-136 for a whole batch of videos):
+ * H2D of the features, encode, decode (beam<=1: greedy), D2H of the results, stream synchronised
+ * before returning.  host_score may be NULL. */
+ECHR_API int echr_caption_host(echr_batch_t* batch, const echr_batch_desc_t* desc, const float* host_c3d,
+                      const float* host_tap, const float* host_lda, int beam, int32_t* host_tokens,
+                      float* host_logp, float* host_score, void* stream);
+
+/* Number of kernel launches this library issued since the last call (graph replays count their
+ * kernel nodes); used by bench.py's `gpu_launches`. */
+ECHR_API int64_t echr_launch_count(int reset);
 
 #ifdef __cplusplus
 }

@@ -1,0 +1,61 @@
+"""GPU unit parity of the stand-alone kernels: fused attention step vs the oracle's `attend`."""
+import numpy as np
+import pytest
+import torch
+
+import helpers
+from echr_b200 import _lib
+from oracle import echr_oracle as O
+
+pytestmark = pytest.mark.gpu
+torch.set_grad_enabled(False)
+DEV = "cuda:0"
+
+
+@pytest.mark.parametrize("clip_bf16", [0, 1])
+def test_attention_step_matches_oracle(clip_bf16):
+    lib = _lib.load()
+    sd = helpers.state_dict("bf16w" if clip_bf16 else "fp32")
+    a = "lm_model.core.attention."
+    g = torch.Generator().manual_seed(3)
+    T = 300
+    c3d = torch.randn(T, 500, generator=g)
+    if clip_bf16:
+        c3d = c3d.bfloat16().float()
+    lens = [1, 2, 7, 33, 64, 100, 257, 300, 5]
+    starts = [0, 299 - 1, 10, 200, 100, 150, 20, 0, 295]
+    n = len(lens)
+    h = torch.randn(n, 512, generator=g) * 0.3
+    lmax = max(lens)
+    clip = torch.zeros(n, lmax, 500)
+    mask = torch.zeros(n, lmax)
+    for i, (s, l) in enumerate(zip(starts, lens)):
+        clip[i, :l] = c3d[s:s + l]
+        mask[i, :l] = 1
+    want = O.attend(sd, h, clip, mask)
+    proj = torch.nn.functional.linear(c3d, sd[a + "ctx2att.weight"], sd[a + "ctx2att.bias"])
+    q = torch.nn.functional.linear(h, sd[a + "h2att.weight"], sd[a + "h2att.bias"]).to(DEV)
+    alpha = sd[a + "alpha_net.weight"].reshape(-1).contiguous().to(DEV)
+    if clip_bf16:
+        clip_d = torch.zeros(T, 512, dtype=torch.bfloat16, device=DEV)
+        clip_d[:, :500] = c3d.to(DEV).bfloat16()
+        proj_d = proj.to(DEV).bfloat16().contiguous()
+        ld = 512
+    else:
+        clip_d, proj_d, ld = c3d.to(DEV).contiguous(), proj.to(DEV).contiguous(), 500
+    rs = torch.tensor(starts, dtype=torch.int32, device=DEV)
+    rl = torch.tensor(lens, dtype=torch.int32, device=DEV)
+    out = torch.full((n, 500), float("nan"), device=DEV)
+    hi = torch.zeros(n, 512, dtype=torch.bfloat16, device=DEV)
+    lo = torch.zeros(n, 512, dtype=torch.bfloat16, device=DEV)
+    _lib.check(lib.echr_attention_step(q.data_ptr(), proj_d.data_ptr(), clip_d.data_ptr(), ld, clip_bf16,
+                                       alpha.data_ptr(), rs.data_ptr(), rl.data_ptr(), n, out.data_ptr(),
+                                       hi.data_ptr(), lo.data_ptr(), 512,
+                                       torch.cuda.current_stream().cuda_stream), "attention")
+    torch.cuda.synchronize()
+    err = (out.cpu() - want).abs().max().item()
+    print("attention max err", err)
+    assert err < (2e-2 if clip_bf16 else 2e-5), err
+    rec = hi.float() + lo.float()
+    assert (rec[:, :500] - out).abs().max().item() < 1e-5
+    assert (rec[:, 500:] == 0).all()
