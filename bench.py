@@ -1,0 +1,312 @@
+#!/usr/bin/env python
+"""Benchmark of the ECHR caption-generation hot path (BASELINE.json metric: events captioned / s).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--workload cfg2] [--beam 1] [--precision bf16w]
+    python bench.py --impl reference ...      # the reference algorithm's CPU path (oracle port) on the host cores
+
+One "step" = one pass of the hot path (context assembly + relation encoder + 30-token decode) over
+one batch of synthetic videos.  Videos are independent, so with N GPUs every rank captions its own
+`workload` batch (weak scaling) and the only collective is one all_gather of the token ids per step.
+Prints ONE JSON line on rank 0.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+import torch  # noqa: E402
+
+from echr_b200 import synth  # noqa: E402
+from echr_b200.config import echr_opt  # noqa: E402
+
+METRIC = "events_captioned_per_sec"
+UNIT = "events/s"
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--workload", default="cfg2", choices=sorted(synth.WORKLOADS))
+    ap.add_argument("--videos", type=int, default=None, help="override the workload's video count (per GPU)")
+    ap.add_argument("--beam", type=int, default=None)
+    ap.add_argument("--precision", default="bf16w", choices=["fp32", "bf16w", "bf16"])
+    ap.add_argument("--cpu-sample", type=int, default=None, help="videos in the CPU-baseline sample")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    return ap.parse_args()
+
+
+def peaks():
+    try:
+        return json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json"))), "measured"
+    except Exception:
+        return {"hbm_gbs": 6650.0, "bf16_tflops": 1590.0, "bf16_tflops_sustained": 1400.0}, "fallback"
+
+
+class ClockSampler(object):
+    """nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md recipe)."""
+
+    def __init__(self, index=0):
+        self.index, self.rows, self.proc = index, [], None
+
+    def start(self):
+        q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+             "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+             "clocks_event_reasons.sw_power_cap")
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + q,
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            threading.Thread(target=self._read, daemon=True).start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([x.strip() for x in line.split(",")])
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        sm = sorted(int(r[0]) for r in self.rows if r and r[0].isdigit())
+        mx = [int(r[1]) for r in self.rows if len(r) > 1 and r[1].isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = [n for i, n in enumerate(names) if any(len(r) > 3 + i and r[3 + i] == "Active" for r in self.rows)]
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": reasons, "samples": len(sm)}
+
+
+def cpu_reference_run(vids, sd, beam, reps, warm):
+    """The reference algorithm's own work shape on the host cores (oracle port, torch CPU fp32):
+    one video per call, looped.  Returns (events/s, seconds per pass)."""
+    from oracle import echr_oracle as O
+    torch.set_num_threads(os.cpu_count() or 1)
+    torch.set_grad_enabled(False)
+    n_events = sum(v.n_events for v in vids)
+
+    def one_pass():
+        for v in vids:
+            if beam > 1:
+                O.caption_video_beam(sd, v.tap_feats, v.c3d_feats, v.lda_feats, v.ind_select_list,
+                                     v.soi_select_list, beam=beam)
+            else:
+                O.caption_video(sd, v.tap_feats, v.c3d_feats, v.lda_feats, v.ind_select_list, v.soi_select_list)
+
+    for _ in range(warm):
+        one_pass()
+    times = []
+    for _ in range(reps):
+        t0 = time.perf_counter()
+        one_pass()
+        times.append(time.perf_counter() - t0)
+    times.sort()
+    med = times[len(times) // 2]
+    return n_events / med, med
+
+
+def workload_config(args, w, n_events, n_gpus):
+    return {"workload": "%s: %d videos x T=%d clips, %d events (%s proposals), beam=%d, vocab 5747, max_len 30"
+                        % (args.workload, w["n_videos"], w["T"], n_events, w["style"], w["beam"]),
+            "videos_per_gpu": w["n_videos"], "events_per_gpu": n_events, "beam": w["beam"],
+            "parallelism": "video-sharded dp%d, one all_gather of token ids per step" % n_gpus}
+
+
+def main_reference(args, rank, world):
+    if rank != 0:
+        return 0
+    opt = echr_opt()
+    sd = synth.init_state_dict(opt, seed=0)
+    vids, w = synth.make_workload(args.workload, n_videos=args.videos)
+    if args.beam is not None:
+        w["beam"] = args.beam
+    sample = args.cpu_sample or {"cfg1": 1, "cfg2": 16, "cfg3": 1, "cfg4": 1, "cfg5": 16}[args.workload]
+    sub = vids[:sample]
+    n_ev = sum(v.n_events for v in sub)
+    value, sec = cpu_reference_run(sub, sd, w["beam"], reps=max(1, args.steps), warm=max(0, args.warmup))
+    cores = os.cpu_count() or 1
+    line = {"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": sec * 1e3, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": workload_config(args, w, sum(v.n_events for v in vids), world),
+            "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port",
+                             "sample": "first %d videos (%d events) of the workload, one video per call, median of %d passes"
+                                       % (sample, n_ev, max(1, args.steps))},
+            "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(line))
+    return 0
+
+
+def main():
+    args = parse()
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.impl == "reference":
+        return main_reference(args, rank, world)
+
+    import torch.distributed as dist
+    from echr_b200.caption_generator import CaptionGenerator
+    from echr_b200.engine import BatchLayout
+    from echr_b200.parallel import gather_tokens
+
+    torch.set_grad_enabled(False)
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=dev)
+
+    opt = echr_opt()
+    sd_full = synth.init_state_dict(opt, seed=0)
+    sd = synth.round_state_dict_bf16(sd_full) if args.precision != "fp32" else sd_full
+    model = CaptionGenerator(opt, precision=args.precision)
+    model.load_state_dict(sd, strict=True)
+    model = model.to(dev)
+    eng = model.engine
+
+    # this rank's shard: its own block of videos (seeds disjoint across ranks)
+    w0 = synth.WORKLOADS[args.workload]
+    nv = args.videos or w0["n_videos"]
+    vids, w = synth.make_workload(args.workload, n_videos=nv, first_seed=rank * nv,
+                                  bf16_features=(args.precision != "fp32"))
+    if args.beam is not None:
+        w["beam"] = args.beam
+    beam = w["beam"]
+    lay = BatchLayout([v.c3d_feats.shape[0] for v in vids], [v.ind_select_list for v in vids],
+                      [v.soi_select_list for v in vids])
+    n_events = lay.n_events
+    h_c3d = torch.cat([v.c3d_feats for v in vids]).contiguous().pin_memory()
+    h_tap = torch.cat([v.tap_feats for v in vids]).contiguous().pin_memory()
+    h_lda = torch.stack([v.lda_feats for v in vids]).contiguous().pin_memory()
+    d_c3d, d_tap, d_lda = h_c3d.to(dev), h_tap.to(dev), h_lda.to(dev)
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)  # > 126 MB L2
+
+    def step_device():
+        eng.set_inputs(lay, d_c3d, d_tap, d_lda, beam=beam)
+        eng.encode()
+        if beam > 1:
+            tok, lp, sc = eng.decode_beam(beam)
+        else:
+            tok, lp = eng.decode_greedy()
+        if world > 1:
+            tok = gather_tokens(tok)
+        return tok
+
+    host_out = (torch.zeros(n_events, opt.CG_seq_length, dtype=torch.int32).pin_memory(),
+                torch.zeros(n_events, opt.CG_seq_length, dtype=torch.float32).pin_memory(),
+                torch.zeros(n_events, dtype=torch.float32).pin_memory())
+
+    def step_host():
+        tok, lp, sc = eng.caption_host(lay, h_c3d, h_tap, h_lda, beam=beam, out=host_out)
+        if world > 1:
+            tok = gather_tokens(tok.to(dev, non_blocking=True))
+        return tok
+
+    def timed(fn, steps, warm):
+        for _ in range(warm):
+            fn()
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+        ms = 0.0
+        for _ in range(steps):
+            flush.zero_()  # L2 flush between timed iterations (not timed)
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            fn()
+            e1.record()
+            e1.synchronize()
+            ms += e0.elapsed_time(e1)
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+            t = torch.tensor([ms], dtype=torch.float64, device=dev)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            ms = float(t.item())
+        return ms
+
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    eng.launch_count(reset=True)
+    ms_dev = timed(step_device, args.steps, args.warmup)
+    launches = eng.launch_count(reset=True) // max(1, args.steps + args.warmup) * args.steps
+    ms_host = timed(step_host, args.steps, args.warmup)
+    clocks = sampler.stop() if rank == 0 else None
+
+    # per-kernel timing of one decode step (CUDA events on the launching stream, inside the library)
+    kt = eng.time_step_kernels(beam=beam, iters=20)
+
+    total_events = n_events * world
+    if world > 1:
+        t = torch.tensor([n_events], dtype=torch.int64, device=dev)
+        dist.all_reduce(t)
+        total_events = int(t.item())
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return 0
+
+    pk, pk_kind = peaks()
+    rows = n_events * beam
+    V1, S = opt.CG_vocab_size + 1, opt.CG_seq_length
+    # dominant kernel: the larger of the two GEMM launches of a step
+    flops = {"lstm_gates": 2.0 * rows * 2048 * (1536 + 1536 + 1152), "logit": 2.0 * rows * V1 * 1536}
+    dom = max(("lstm_gates", "logit"), key=lambda k: kt[k])
+    ach = flops[dom] / (kt[dom] * 1e-3) / 1e12
+    peak_tf = pk.get("bf16_tflops_sustained", pk["bf16_tflops"])
+    roofline = {"bound": "tensor", "kernel": "gemm_tc_kernel<%s>" % dom, "achieved": ach, "peak": peak_tf,
+                "unit": "TFLOP/s", "frac": ach / peak_tf, "traffic": None, "peak_source": pk_kind + " (sustained)",
+                "ms_per_launch": kt[dom], "step_kernel_ms": kt,
+                "note": "algorithmic FLOPs 2*M*N*K of one product; the %s mode issues %d tcgen05 products per k-step"
+                        % (args.precision, {"fp32": 3, "bf16w": 2, "bf16": 1}[args.precision])}
+    # attention kernel against HBM (2024*L + 4048 bytes per event-step at bf16, fp32 clip doubles the window)
+    el = 2 if args.precision == "bf16" else 4
+    win = sum((s[1] - s[0]) for v in vids for s in v.soi_select_list) * beam
+    att_bytes = win * (500 + 512) * el + rows * (512 * 4 + 500 * 4)
+    roofline["attention"] = {"bound": "hbm", "achieved": att_bytes / (kt["attention"] * 1e-3) / 1e9,
+                             "peak": pk["hbm_gbs"], "unit": "GB/s",
+                             "frac": att_bytes / (kt["attention"] * 1e-3) / 1e9 / pk["hbm_gbs"]}
+
+    line = {"metric": METRIC, "value": total_events * args.steps / (ms_dev * 1e-3), "unit": UNIT, "n_gpus": world,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_dev / args.steps,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": {"fp32": "bf16x3 (fp32-grade)", "bf16w": "bf16", "bf16": "bf16"}[args.precision],
+            "data": "synthetic",
+            "config": dict(workload_config(args, w, n_events, world), precision=args.precision,
+                           l2_flush_between_steps=True, ms_per_decode_step=ms_dev / args.steps / S),
+            "clocks": clocks,
+            "e2e": {"value": total_events * args.steps / (ms_host * 1e-3), "unit": UNIT,
+                    "h2d_bytes_per_step": int(h_c3d.numel() + h_tap.numel() + h_lda.numel()) * 4,
+                    "d2h_bytes_per_step": int(n_events * S * 8 + (n_events * 4 if beam > 1 else 0)),
+                    "ms_per_step": ms_host / args.steps},
+            "gpu_launches": int(launches),
+            "roofline": roofline}
+    if not args.no_cpu_baseline and world >= 1:
+        sample = args.cpu_sample or {"cfg1": 1, "cfg2": 8, "cfg3": 1, "cfg4": 1, "cfg5": 8}[args.workload]
+        sub = [synth.make_video(i, T=w["T"], n_events=w0["n_events"], style=w["style"]) for i in range(sample)]
+        v, sec = cpu_reference_run(sub, sd_full, beam, reps=3, warm=1)
+        line["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": os.cpu_count() or 1, "kind": "port",
+                                "sample": "first %d videos (%d events) of the workload, one video per call, "
+                                          "median of 3 passes after 1 warm-up (%.2f s per pass)"
+                                          % (sample, sum(x.n_events for x in sub), sec)}
+    print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())

@@ -542,25 +542,28 @@ static int enqueue_init(echr_batch* b, int beam, cudaStream_t st) {
 // One decode step t: attention query + attention (stream 1 uses the PREVIOUS h1), the three gate
 // GEMMs with the fused LSTM cell update, the vocabulary projection with fused partial
 // log-softmax / top-k.  The caller appends the mode's finalize kernel.
+enum { PART_H2ATT = 1, PART_ATT = 2, PART_GATES = 4, PART_LOGIT = 8, PART_ALL = 15 };
+
 static int enqueue_step(echr_batch* b, int rows, int t, int topk, float* logits_out, long long ld_logits,
-                        cudaStream_t st) {
+                        cudaStream_t st, int parts = PART_ALL) {
   const echr_model* m = b->model;
   const int at = m->cfg.a_terms, wt = m->cfg.w_terms;
   const int p = t & 1, n = p ^ 1;
   PlaneMat& cur = b->act[p];
   PlaneMat& nxt = b->act[n];
-  {
+  if (parts & PART_H2ATT) {
     GemmSpec s;
     s.A = &cur; s.a_col0 = ACT_H + HID; s.M = rows; s.W = &m->w_h2att; s.N = HID; s.K = HID;
     s.bias = m->b_h2att; s.out_f32 = b->q_att; s.ld_f32 = HID;
     ECHR_TRY(run_gemm(&s, 1, at, wt, 128, EPI_STORE, 1, st, "h2att"));
   }
+  if (parts & PART_ATT)
   ECHR_CUDA(launch_attention(b->q_att, m->cfg.clip_bf16 ? (const void*)b->proj_bf : (const void*)b->proj_f32,
                              m->cfg.clip_bf16 ? (const void*)b->clip_pl.plane(0) : (const void*)b->c3d,
                              m->cfg.clip_bf16 ? CLIP_PAD : ECHR_VIDEO_DIM, m->cfg.clip_bf16, m->alpha,
                              b->row_start, b->row_len, rows, nullptr, cur.plane(0) + ACT_ATT,
                              at > 1 ? cur.plane(1) + ACT_ATT : nullptr, ACT_LD, st));
-  {
+  if (parts & PART_GATES) {
     GemmSpec s[3];
     const int* kbs[3] = {KB_L0, KB_L1, KB_L2};
     const int K[3] = {24 * 64, 24 * 64, 18 * 64};
@@ -575,7 +578,7 @@ static int enqueue_step(echr_batch* b, int rows, int t, int topk, float* logits_
     }
     ECHR_TRY(run_gemm(s, 3, at, wt, 128, EPI_LSTM, 1, st, "lstm_gates"));
   }
-  {
+  if (parts & PART_LOGIT) {
     GemmSpec s;
     s.A = &nxt; s.a_col0 = ACT_H; s.M = rows; s.W = &m->w_logit; s.N = m->V1; s.K = 3 * HID;
     s.bias = m->b_logit; s.partial = b->partial; s.logits_out = logits_out; s.ld_logits = ld_logits;
@@ -695,6 +698,42 @@ extern "C" int echr_caption_host(echr_batch_t* b, const echr_batch_desc_t* desc,
   ECHR_TRY(copy_results(b, host_tokens, host_logp, beam > 1 ? host_score : nullptr, cudaMemcpyDeviceToHost, st));
   ECHR_CUDA(cudaStreamSynchronize(st));
   return ECHR_OK;
+}
+
+// Average duration (ms) of each kernel of one decode step, measured with CUDA events on `stream`
+// around `iters` back-to-back launches of that kernel (state left by the previous decode).
+extern "C" int echr_time_step_kernels(echr_batch_t* b, int beam, int iters, float* host_ms, void* stream) {
+  ECHR_REQUIRE(b && host_ms && iters >= 1, "echr_time_step_kernels: bad argument");
+  ECHR_REQUIRE(b->encoded && b->n_events > 0, "echr_time_step_kernels: decode a batch first");
+  ECHR_REQUIRE(beam >= 1 && beam <= 4 && (long long)b->n_events * beam <= b->cap.max_rows, "echr_time_step_kernels: bad beam");
+  cudaStream_t st = (cudaStream_t)stream;
+  const int rows = b->n_events * beam;
+  const long long before = g_launches.load();
+  cudaEvent_t e0, e1;
+  ECHR_CUDA(cudaEventCreate(&e0));
+  ECHR_CUDA(cudaEventCreate(&e1));
+  const int parts[4] = {PART_H2ATT, PART_ATT, PART_GATES, PART_LOGIT};
+  int rc = enqueue_init(b, beam, st);  // fresh state (a finished beam decode leaves every slot dead)
+  if (rc == ECHR_OK) rc = enqueue_step(b, rows, 0, beam > 1 ? 4 : 1, nullptr, 0, st);
+  for (int k = 0; k < 5 && rc == ECHR_OK; ++k) {
+    for (int pass = 0; pass < 2 && rc == ECHR_OK; ++pass) {  // pass 0 warms up
+      cudaEventRecord(e0, st);
+      for (int i = 0; i < iters && rc == ECHR_OK; ++i) {
+        if (k < 4) rc = enqueue_step(b, rows, 1, beam > 1 ? 4 : 1, nullptr, 0, st, parts[k]);
+        else if (beam > 1) { if (launch_finalize_beam(b, beam, 1, b->tokens_dev, b->logp_dev, b->score_dev, st) != cudaSuccess) rc = set_error(ECHR_ERR_CUDA, "finalize_beam launch failed"); }
+        else { if (launch_finalize_greedy(b, 1, b->tokens_dev, b->logp_dev, st) != cudaSuccess) rc = set_error(ECHR_ERR_CUDA, "finalize_greedy launch failed"); }
+      }
+      cudaEventRecord(e1, st);
+      if (cudaEventSynchronize(e1) != cudaSuccess) rc = set_error(ECHR_ERR_CUDA, "echr_time_step_kernels: kernel failed: %s", cudaGetErrorString(cudaGetLastError()));
+      float ms = 0.f;
+      cudaEventElapsedTime(&ms, e0, e1);
+      host_ms[k] = ms / iters;
+    }
+  }
+  cudaEventDestroy(e0);
+  cudaEventDestroy(e1);
+  g_launches.store(before);
+  return rc;
 }
 
 extern "C" int64_t echr_launch_count(int reset) {

@@ -422,6 +422,10 @@ finalize_beam_kernel(int beam, int n_tiles, int step, int seq_len, const float* 
           if (pb < 0 || cand_total[b][k] > best) { best = cand_total[b][k]; pb = b; pk = k; }
         }
       }
+      if (pb < 0) {  // no live slot left (only after the last step): keep the slot as it is, dead
+        sel_parent[n] = n; sel_tok[n] = 0; sel_lp[n] = 0.f; sel_total[n] = -INFINITY; sel_fin[n] = 1;
+        continue;
+      }
       used[pb][pk] = true;
       sel_parent[n] = pb;
       sel_tok[n] = cand_tok[pb][pk];

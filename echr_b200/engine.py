@@ -205,5 +205,13 @@ class Engine(object):
                   "echr_caption_host")
         return tokens, logp, score
 
+    def time_step_kernels(self, beam=1, iters=20):
+        """Average ms per launch of the kernels of one decode step (CUDA events inside the library)."""
+        ms = (ctypes.c_float * 5)()
+        with torch.cuda.device(self.device):
+            check(self.lib.echr_time_step_kernels(self._batch, int(beam), int(iters), ms, _stream()),
+                  "echr_time_step_kernels")
+        return dict(zip(("h2att", "attention", "lstm_gates", "logit", "finalize"), [float(x) for x in ms]))
+
     def launch_count(self, reset=False):
         return int(self.lib.echr_launch_count(1 if reset else 0))

@@ -175,6 +175,11 @@ ECHR_API int echr_caption_host(echr_batch_t* batch, const echr_batch_desc_t* des
                       const float* host_tap, const float* host_lda, int beam, int32_t* host_tokens,
                       float* host_logp, float* host_score, void* stream);
 
+/* Measurement aid for bench.py's roofline: average duration in ms of each kernel of one decode step
+ * (host_ms[5] = h2att GEMM, fused attention, LSTM gate GEMM, logit GEMM, finalize), from CUDA
+ * events on `stream` around `iters` back-to-back launches.  Needs a decoded batch; synchronises. */
+ECHR_API int echr_time_step_kernels(echr_batch_t* batch, int beam, int iters, float* host_ms, void* stream);
+
 /* Number of kernel launches this library issued since the last call (graph replays count their
  * kernel nodes); used by bench.py's `gpu_launches`. */
 ECHR_API int64_t echr_launch_count(int reset);

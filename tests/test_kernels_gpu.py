@@ -57,5 +57,5 @@ def test_attention_step_matches_oracle(clip_bf16):
     print("attention max err", err)
     assert err < (2e-2 if clip_bf16 else 2e-5), err
     rec = hi.float() + lo.float()
-    assert (rec[:, :500] - out).abs().max().item() < 1e-5
+    assert ((rec[:, :500] - out).abs() <= 2e-5 * out.abs() + 1e-7).all()  # hi+lo carries 16 mantissa bits
     assert (rec[:, 500:] == 0).all()
