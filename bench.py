@@ -289,7 +289,7 @@ def main():
                            l2_flush_between_steps=True, ms_per_decode_step=ms_dev / args.steps / S),
             "clocks": clocks,
             "e2e": {"value": total_events * args.steps / (ms_host * 1e-3), "unit": UNIT,
-                    "h2d_bytes_per_step": int(h_c3d.numel() + h_tap.numel() + h_lda.numel()) * 4,
+                    "h2d_bytes_per_step": int(h_c3d.numel() + n_events * 512 + h_lda.numel()) * 4 + int(9 * n_events + 2 * len(vids)) * 4,
                     "d2h_bytes_per_step": int(n_events * S * 8 + (n_events * 4 if beam > 1 else 0)),
                     "ms_per_step": ms_host / args.steps},
             "gpu_launches": int(launches),

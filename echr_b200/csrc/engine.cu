@@ -122,7 +122,6 @@ static const char* fill_problem(GemmProblem& pb, const GemmSpec& s, int a_terms,
   pb.ld_bf = s.ld_bf;
   pb.c_in = s.c_in;
   pb.c_out = s.c_out;
-  pb.parent = nullptr;
   pb.hidden = HID;
   pb.partial = s.partial;
   pb.logits_out = s.logits_out;
@@ -287,9 +286,9 @@ static void batch_layout(echr_batch* b, Arena& a) {
   const echr_model* m = b->model;
   const int ap = m->cfg.a_terms;
   const int S = m->cfg.seq_length;
-  const int n_tiles = (m->V1 + 127) / 128;
+  const int n_tiles = ((m->V1 + 127) / 128) * (128 / LOGIT_GROUP);  // partial records per row
   b->c3d = a.take<float>((size_t)c.max_clips * ECHR_VIDEO_DIM);
-  b->tap = a.take<float>((size_t)c.max_clips * HID);
+  b->tap = a.take<float>((size_t)c.max_events * HID);
   b->lda = a.take<float>((size_t)c.max_videos * ECHR_LDA_DIM);
   int32_t* ints = a.take<int32_t>((size_t)7 * c.max_events + 2 * c.max_videos);
   b->ev_video = ints;
@@ -358,7 +357,10 @@ extern "C" int echr_batch_create(const echr_model_t* model, const echr_capacity_
   }
   e = cudaMallocHost(reinterpret_cast<void**>(&b->host_stage),
                      sizeof(int32_t) * ((size_t)7 * cap->max_events + 2 * cap->max_videos));
+  if (e == cudaSuccess)
+    e = cudaMallocHost(reinterpret_cast<void**>(&b->host_tap_stage), sizeof(float) * (size_t)cap->max_events * HID);
   if (e != cudaSuccess) {
+    if (b->host_stage) cudaFreeHost(b->host_stage);
     cudaFree(b->arena);
     delete b;
     return set_error(ECHR_ERR_CUDA, "echr_batch_create: cudaMallocHost failed: %s", cudaGetErrorString(e));
@@ -369,6 +371,7 @@ extern "C" int echr_batch_create(const echr_model_t* model, const echr_capacity_
   e = cudaMemset(b->arena, 0, b->arena_bytes);
   if (e != cudaSuccess) {
     cudaFreeHost(b->host_stage);
+    cudaFreeHost(b->host_tap_stage);
     cudaFree(b->arena);
     delete b;
     return set_error(ECHR_ERR_CUDA, "echr_batch_create: cudaMemset failed: %s", cudaGetErrorString(e));
@@ -380,8 +383,14 @@ extern "C" int echr_batch_create(const echr_model_t* model, const echr_capacity_
 extern "C" int echr_batch_destroy(echr_batch_t* b) {
   if (!b) return ECHR_OK;
   if (b->graph_exec) cudaGraphExecDestroy(b->graph_exec);
-  if (b->cap_stream) cudaStreamDestroy(b->cap_stream);
+  if (b->cap_stream) {
+    cudaStreamDestroy(b->cap_stream);
+    cudaStreamDestroy(b->cap_stream2);
+    cudaEventDestroy(b->cap_events[0]);
+    cudaEventDestroy(b->cap_events[1]);
+  }
   cudaFreeHost(b->host_stage);
+  cudaFreeHost(b->host_tap_stage);
   cudaFree(b->arena);
   delete b;
   return ECHR_OK;
@@ -450,7 +459,16 @@ extern "C" int echr_batch_set_inputs(echr_batch_t* b, const echr_batch_desc_t* d
                             cudaMemcpyHostToDevice, st));
   const cudaMemcpyKind kind = on_host ? cudaMemcpyHostToDevice : cudaMemcpyDeviceToDevice;
   ECHR_CUDA(cudaMemcpyAsync(b->c3d, c3d, sizeof(float) * (size_t)n_clips * ECHR_VIDEO_DIM, kind, st));
-  ECHR_CUDA(cudaMemcpyAsync(b->tap, tap, sizeof(float) * (size_t)n_clips * HID, kind, st));
+  // only tap_feats[ind] is ever read (CaptionGenerator.py:121): gather one row per event
+  if (on_host) {
+    for (int i = 0; i < d->n_events; ++i)
+      memcpy(b->host_tap_stage + (size_t)i * HID, tap + (size_t)hs[3 * E + i] * HID, sizeof(float) * HID);
+    if (d->n_events > 0)
+      ECHR_CUDA(cudaMemcpyAsync(b->tap, b->host_tap_stage, sizeof(float) * (size_t)d->n_events * HID,
+                                cudaMemcpyHostToDevice, st));
+  } else {
+    ECHR_CUDA(launch_gather_tap(b, tap, st));
+  }
   ECHR_CUDA(cudaMemcpyAsync(b->lda, lda, sizeof(float) * (size_t)d->n_videos * ECHR_LDA_DIM, kind, st));
   return ECHR_OK;
 }
@@ -587,16 +605,38 @@ static int enqueue_step(echr_batch* b, int rows, int t, int topk, float* logits_
   return ECHR_OK;
 }
 
-static int enqueue_decode(echr_batch* b, int beam, int mode, cudaStream_t st) {
+static int enqueue_decode(echr_batch* b, int beam, int mode, cudaStream_t st, cudaStream_t side = nullptr) {
   const int rows = b->n_events * beam;
   const int S = b->model->cfg.seq_length;
+  const int topk = mode == MODE_BEAM ? 4 : 1;
   ECHR_TRY(enqueue_init(b, beam, st));
   if (mode == MODE_BEAM) {
     ECHR_CUDA(cudaMemsetAsync(b->tokens_dev, 0, sizeof(int32_t) * (size_t)b->n_events * S, st));
     ECHR_CUDA(cudaMemsetAsync(b->logp_dev, 0, sizeof(float) * (size_t)b->n_events * S, st));
   }
+  if (mode == MODE_GREEDY && side != nullptr) {
+    // Greedy: the next step's attention (h2att GEMM + fused attention) depends only on this step's
+    // h1, not on the token, so it runs on a forked branch next to the vocabulary projection:
+    //   main:  gates(t) -> logits(t) -> finalize(t) -> [join] gates(t+1) ...
+    //   side:           \-> h2att(t+1) -> attention(t+1) -/
+    // The branches touch disjoint columns of the activation matrix.
+    ECHR_TRY(enqueue_step(b, rows, 0, topk, nullptr, 0, st, PART_H2ATT | PART_ATT));
+    for (int t = 0; t < S; ++t) {
+      ECHR_TRY(enqueue_step(b, rows, t, topk, nullptr, 0, st, PART_GATES));
+      if (t + 1 < S) {
+        ECHR_CUDA(cudaEventRecord(b->cap_events[0], st));
+        ECHR_CUDA(cudaStreamWaitEvent(side, b->cap_events[0], 0));
+        ECHR_TRY(enqueue_step(b, rows, t + 1, topk, nullptr, 0, side, PART_H2ATT | PART_ATT));
+        ECHR_CUDA(cudaEventRecord(b->cap_events[1], side));
+      }
+      ECHR_TRY(enqueue_step(b, rows, t, topk, nullptr, 0, st, PART_LOGIT));
+      ECHR_CUDA(launch_finalize_greedy(b, t, b->tokens_dev, b->logp_dev, st));
+      if (t + 1 < S) ECHR_CUDA(cudaStreamWaitEvent(st, b->cap_events[1], 0));
+    }
+    return ECHR_OK;
+  }
   for (int t = 0; t < S; ++t) {
-    ECHR_TRY(enqueue_step(b, rows, t, mode == MODE_BEAM ? 4 : 1, nullptr, 0, st));
+    ECHR_TRY(enqueue_step(b, rows, t, topk, nullptr, 0, st));
     if (mode == MODE_BEAM)
       ECHR_CUDA(launch_finalize_beam(b, beam, t, b->tokens_dev, b->logp_dev, b->score_dev, st));
     else
@@ -619,9 +659,14 @@ static int run_decode(echr_batch* b, int beam, int mode, cudaStream_t st) {
     cudaGraph_t graph = nullptr;
     // capture on a private stream: the caller's stream may be the legacy default stream, which
     // cannot be captured
-    if (b->cap_stream == nullptr) ECHR_CUDA(cudaStreamCreateWithFlags(&b->cap_stream, cudaStreamNonBlocking));
+    if (b->cap_stream == nullptr) {
+      ECHR_CUDA(cudaStreamCreateWithFlags(&b->cap_stream, cudaStreamNonBlocking));
+      ECHR_CUDA(cudaStreamCreateWithFlags(&b->cap_stream2, cudaStreamNonBlocking));
+      ECHR_CUDA(cudaEventCreateWithFlags(&b->cap_events[0], cudaEventDisableTiming));
+      ECHR_CUDA(cudaEventCreateWithFlags(&b->cap_events[1], cudaEventDisableTiming));
+    }
     ECHR_CUDA(cudaStreamBeginCapture(b->cap_stream, cudaStreamCaptureModeRelaxed));
-    int rc = enqueue_decode(b, beam, mode, b->cap_stream);
+    int rc = enqueue_decode(b, beam, mode, b->cap_stream, b->cap_stream2);
     cudaError_t e = cudaStreamEndCapture(b->cap_stream, &graph);
     if (rc != 0) { if (graph) cudaGraphDestroy(graph); return rc; }
     if (e != cudaSuccess) return set_error(ECHR_ERR_CUDA, "decode: graph capture failed: %s", cudaGetErrorString(e));

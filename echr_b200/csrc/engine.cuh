@@ -61,7 +61,8 @@ struct echr_batch {
   int n_videos, n_events, n_clips, n_pairs, max_n;  // max_n = largest events-per-video
   bool encoded;
   // inputs (copies)
-  float *c3d, *tap, *lda;  // [clips,500] [clips,512] [videos,100]
+  float *c3d, *tap, *lda;  // [clips,500]; tap_feats[ind] per event [events,512]; [videos,100]
+  float* host_tap_stage;   // pinned [max_events,512]: host-side gather of the proposal states
   // per-event int arrays on device: video, first clip (global), length, ind (global), pair row
   // offset, first event of the video, events in the video
   int32_t *ev_video, *ev_start, *ev_len, *ev_ind, *ev_pair_off, *ev_first, *ev_n;
@@ -96,7 +97,9 @@ struct echr_batch {
   float* best_score;        // [events]
   // decode graph cache
   cudaGraphExec_t graph_exec;
-  cudaStream_t cap_stream;  // private stream the decode graph is captured on
+  cudaStream_t cap_stream;   // private stream the decode graph is captured on
+  cudaStream_t cap_stream2;  // forked branch inside the capture (next step's attention)
+  cudaEvent_t cap_events[2]; // fork / join markers, reused inside the capture
   int graph_rows, graph_beam;
   int32_t *graph_tokens_out;
   float *graph_logp_out, *graph_score_out;
@@ -111,6 +114,7 @@ namespace echr {
 cudaError_t launch_split(const float* src, int64_t rows, int64_t cols, int64_t ld_src, bf16* hi,
                          bf16* lo, int64_t ld_dst, int64_t cols_dst, cudaStream_t st);
 cudaError_t launch_event_feats(const echr_batch* b, cudaStream_t st);
+cudaError_t launch_gather_tap(const echr_batch* b, const float* tap_src, cudaStream_t st);
 cudaError_t launch_posemb(const echr_batch* b, cudaStream_t st);
 cudaError_t launch_relation_attn(const echr_batch* b, cudaStream_t st);
 // ---- kernels_step.cu

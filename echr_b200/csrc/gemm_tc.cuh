@@ -15,8 +15,12 @@
 //   EPI_LSTM  : columns are gate-interleaved (i,f,g,o of one hidden unit adjacent); applies the
 //               LSTMCell update (reference: nn.LSTMCell in models/OldModel_NEW.py:780-782,
 //               809-817) and writes c (fp32) and h (bf16 hi/lo planes).
-//   EPI_LOGITS: + bias, mask padded vocabulary, per-row/per-tile {sum-exp, top-K} partials for the
-//               fused log-softmax / argmax / beam top-k (reference: OldModel_NEW.py:136,158).
+//   EPI_LOGITS: + bias, mask padded vocabulary, per-row / per-64-column-group {sum-exp, top-K}
+//               partials for the fused log-softmax / argmax / beam top-k (reference:
+//               OldModel_NEW.py:136,158).
+// Eight epilogue warps (two per TMEM lane quarter, each taking half of the tile's columns) keep two
+// warps on every scheduler; the bias tile goes through shared memory and operands that do not depend
+// on the accumulator (c_prev) are fetched before the wait on the MMAs.
 #pragma once
 #include <cuda.h>
 #include "ptx.cuh"
@@ -27,10 +31,12 @@ constexpr int GEMM_BLOCK_M = 128;
 constexpr int GEMM_BLOCK_K = 64;
 constexpr int GEMM_MAX_KB = 32;
 constexpr int GEMM_MAX_GROUPS = 3;
-constexpr int GEMM_THREADS = 256;
+constexpr int GEMM_EPI_WARPS = 8;                       // two warps per TMEM lane quarter
+constexpr int GEMM_THREADS = 128 + GEMM_EPI_WARPS * 32;  // warps 0-3: TMA, MMA, TMEM alloc, spare
+constexpr int LOGIT_GROUP = 64;                          // vocabulary columns per partial record
 
 enum : int { EPI_STORE = 0, EPI_LSTM = 1, EPI_LOGITS = 2 };
-enum : int { ACT_NONE = 0, ACT_TANH = 1, ACT_TANH_FAST = 2 };
+enum : int { ACT_NONE = 0, ACT_TANH = 1 };
 
 struct GemmProblem {
   CUtensorMap tmA;  // 3-D {K cols, M rows, planes}, box {64, 128, 1}, SWIZZLE_128B
@@ -50,10 +56,9 @@ struct GemmProblem {
   // EPI_LSTM
   const float* c_in;   // [M, H]
   float* c_out;        // [M, H]
-  const int* parent;   // optional row indirection for c_in
   int hidden;          // H (N == 4H)
   // EPI_LOGITS
-  float* partial;      // [M, n_tiles, REC]
+  float* partial;      // [M, n_groups, REC]   n_groups = ceil(N / BLOCK_N) * (BLOCK_N / LOGIT_GROUP)
   float* logits_out;   // optional [M, ld_logits]
   long long ld_logits;
 };
@@ -76,17 +81,40 @@ struct GemmCfg {
   static constexpr int STAGES_RAW = (196 * 1024) / STAGE_BYTES;
   static constexpr int STAGES = STAGES_RAW > 8 ? 8 : STAGES_RAW;
   static constexpr int TMEM_COLS = BLOCK_N <= 32 ? 32 : (BLOCK_N <= 64 ? 64 : (BLOCK_N <= 128 ? 128 : 256));
-  static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 /*align slack*/ + 256 /*barriers*/;
+  // stages | barriers (256 B) | bias tile (BLOCK_N floats, 512 B reserved)
+  static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 /*align slack*/ + 256 + 512;
 };
 
-__device__ __forceinline__ float apply_act(float x, int act) {
-  if (act == ACT_TANH) return tanhf(x);
-  if (act == ACT_TANH_FAST) {
-    float y;
-    asm("tanh.approx.f32 %0, %1;" : "=f"(y) : "f"(x));
-    return y;
+// Fast forms for the epilogues: one ex2 + one fast reciprocal each, ~1e-6 relative error.
+__device__ __forceinline__ float sigmoid_fast(float x) { return __fdividef(1.0f, 1.0f + __expf(-x)); }
+__device__ __forceinline__ float tanh_fast_acc(float x) {
+  return 1.0f - __fdividef(2.0f, __expf(2.0f * x) + 1.0f);
+}
+
+// store 32 consecutive values of one row as bf16 hi (and lo) planes
+__device__ __forceinline__ void store_planes32(const float* v, __nv_bfloat16* oh, __nv_bfloat16* ol,
+                                               int valid) {
+  if (valid >= 32 && ((reinterpret_cast<uintptr_t>(oh) & 15) == 0) &&
+      (ol == nullptr || (reinterpret_cast<uintptr_t>(ol) & 15) == 0)) {
+#pragma unroll
+    for (int g = 0; g < 4; ++g) {
+      __align__(16) __nv_bfloat16 h[8];
+      __align__(16) __nv_bfloat16 l[8];
+#pragma unroll
+      for (int i = 0; i < 8; ++i) split_bf16(v[8 * g + i], h[i], l[i]);
+      *reinterpret_cast<uint4*>(oh + 8 * g) = *reinterpret_cast<const uint4*>(h);
+      if (ol != nullptr) *reinterpret_cast<uint4*>(ol + 8 * g) = *reinterpret_cast<const uint4*>(l);
+    }
+  } else {
+    for (int i = 0; i < 32; ++i) {
+      if (i < valid) {
+        __nv_bfloat16 h, l;
+        split_bf16(v[i], h, l);
+        oh[i] = h;
+        if (ol != nullptr) ol[i] = l;
+      }
+    }
   }
-  return x;
 }
 
 template <int A_TERMS, int W_TERMS, int BLOCK_N, int EPI, int TOPK>
@@ -101,17 +129,19 @@ gemm_tc_kernel(const __grid_constant__ GemmParams P) {
   extern __shared__ uint8_t smem_raw[];
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   const uint32_t bar_base = smem_base + Cfg::STAGES * Cfg::STAGE_BYTES;
-  // barriers: full[s] at +8*s, empty[s] at +64+8*s, tmem_full at +128, tmem ptr at +136
+  // barriers: full[s] at +8*s, empty[s] at +64+8*s, tmem_full at +128, tmem ptr at +136; bias at +256
   auto full_bar = [&](int s) { return bar_base + 8u * s; };
   auto empty_bar = [&](int s) { return bar_base + 64u + 8u * s; };
   const uint32_t tmem_full_bar = bar_base + 128u;
   const uint32_t tmem_ptr_smem = bar_base + 136u;
-  volatile uint32_t* tmem_ptr_generic =
-      reinterpret_cast<volatile uint32_t*>(smem_raw + (tmem_ptr_smem - smem_u32(smem_raw)));
+  uint8_t* bar_generic = smem_raw + (bar_base - smem_u32(smem_raw));
+  volatile uint32_t* tmem_ptr_generic = reinterpret_cast<volatile uint32_t*>(bar_generic + 136);
+  float* sbias = reinterpret_cast<float*>(bar_generic + 256);
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
   const int num_kb = pb.num_kb;
+  const int col0 = n_tile * BLOCK_N;
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&pb.tmA);
@@ -126,6 +156,10 @@ gemm_tc_kernel(const __grid_constant__ GemmParams P) {
     fence_mbar_init();
   }
   if (warp == 2) tmem_alloc<Cfg::TMEM_COLS>(tmem_ptr_smem);
+  if (warp >= 4) {  // bias tile -> shared memory (hidden behind the main loop)
+    const int i = threadIdx.x - 128;
+    if (i < BLOCK_N) sbias[i] = (pb.bias != nullptr && col0 + i < pb.N) ? __ldg(pb.bias + col0 + i) : 0.f;
+  }
   tc_fence_before_sync();
   __syncthreads();
   tc_fence_after_sync();
@@ -187,160 +221,215 @@ gemm_tc_kernel(const __grid_constant__ GemmParams P) {
       umma_commit(tmem_full_bar);  // accumulator complete
     }
   } else if (warp >= 4) {
-    // ===================== epilogue: 4 warps, thread = one output row =====================
-    const int q = warp & 3;  // TMEM lane quarter this warp may access
+    // ===================== epilogue: 8 warps; thread = one output row x half the columns ========
+    constexpr int HALF = BLOCK_N >= 64 ? BLOCK_N / 2 : BLOCK_N;  // columns per epilogue thread
+    constexpr int CH = HALF >= 32 ? 32 : 16;
+    constexpr int NCH = HALF / CH;
+    const int q = warp & 3;              // TMEM lane quarter this warp may access
+    const int half = (warp - 4) >> 2;    // which half of the tile's columns
+    const bool active = (BLOCK_N >= 64) || half == 0;
     const int row = m_tile * GEMM_BLOCK_M + q * 32 + lane;
     const bool row_ok = row < pb.M;
+    const int hc0 = half * HALF;         // first column (within the tile) of this thread
+    const uint32_t t_row = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + hc0;
+
+    // ---- operands that do not depend on the accumulator: fetch before waiting for the MMAs
+    float cprev[EPI == EPI_LSTM ? HALF / 4 : 1];
+    if constexpr (EPI == EPI_LSTM) {
+      if (row_ok) {
+        const float4* cp = reinterpret_cast<const float4*>(
+            pb.c_in + static_cast<long long>(row) * pb.hidden + ((col0 + hc0) >> 2));
+#pragma unroll
+        for (int i = 0; i < HALF / 16; ++i) {
+          const float4 c = __ldg(cp + i);
+          cprev[4 * i] = c.x; cprev[4 * i + 1] = c.y; cprev[4 * i + 2] = c.z; cprev[4 * i + 3] = c.w;
+        }
+      } else {
+#pragma unroll
+        for (int i = 0; i < HALF / 4; ++i) cprev[i] = 0.f;
+      }
+    }
+
     mbar_wait(tmem_full_bar, 0);
     tc_fence_after_sync();
-    const uint32_t t_row = tmem_base + (static_cast<uint32_t>(q * 32) << 16);
-    const int col0 = n_tile * BLOCK_N;
 
-    if constexpr (EPI == EPI_STORE) {
-      constexpr int CH = BLOCK_N >= 32 ? 32 : 16;
+    if (active) {
+      if constexpr (EPI == EPI_STORE) {
+        const int act = pb.act;
 #pragma unroll 1
-      for (int c = 0; c < BLOCK_N / CH; ++c) {
-        float v[32];
-        if constexpr (CH == 32) tmem_ld_32x32(t_row + c * CH, v);
-        else tmem_ld_32x16(t_row + c * CH, v);
-        tmem_ld_wait();
-        const int cb = col0 + c * CH;
-        if (row_ok) {
+        for (int c = 0; c < NCH; ++c) {
+          float v[32];
+          if constexpr (CH == 32) tmem_ld_32x32(t_row + c * CH, v);
+          else tmem_ld_32x16(t_row + c * CH, v);
+          tmem_ld_wait();
+          const int tc = hc0 + c * CH;  // column within the tile
+          const int cb = col0 + tc;     // global column
+          if (row_ok && cb < pb.N) {
 #pragma unroll
-          for (int i = 0; i < CH; ++i) {
-            float x = v[i];
-            if (pb.bias != nullptr && cb + i < pb.N) x += __ldg(pb.bias + cb + i);
-            v[i] = apply_act(x, pb.act);
-          }
-          const bool full = (cb + CH <= pb.N);
-          if (pb.out_f32 != nullptr) {
-            float* o = pb.out_f32 + static_cast<long long>(row) * pb.ld_f32 + cb;
-            if (full && ((reinterpret_cast<uintptr_t>(o) & 15) == 0)) {
-#pragma unroll
-              for (int i = 0; i < CH; i += 4)
-                *reinterpret_cast<float4*>(o + i) = make_float4(v[i], v[i + 1], v[i + 2], v[i + 3]);
-            } else {
-              for (int i = 0; i < CH; ++i)
-                if (cb + i < pb.N) o[i] = v[i];
+            for (int i = 0; i < CH; i += 4) {
+              const float4 b4 = *reinterpret_cast<const float4*>(sbias + tc + i);
+              v[i] += b4.x; v[i + 1] += b4.y; v[i + 2] += b4.z; v[i + 3] += b4.w;
             }
-          }
-          if (pb.out_hi != nullptr) {
-            __nv_bfloat16* oh = pb.out_hi + static_cast<long long>(row) * pb.ld_bf + cb;
-            __nv_bfloat16* ol =
-                pb.out_lo ? pb.out_lo + static_cast<long long>(row) * pb.ld_bf + cb : nullptr;
-            for (int i = 0; i < CH; ++i) {
-              if (cb + i < pb.N) {
-                __nv_bfloat16 h, l;
-                split_bf16(v[i], h, l);
-                oh[i] = h;
-                if (ol) ol[i] = l;
+            if (act == ACT_TANH) {
+#pragma unroll
+              for (int i = 0; i < CH; ++i) v[i] = tanh_fast_acc(v[i]);
+            }
+            const int valid = min(CH, pb.N - cb);
+            if (pb.out_f32 != nullptr) {
+              float* o = pb.out_f32 + static_cast<long long>(row) * pb.ld_f32 + cb;
+              if (valid == CH && ((reinterpret_cast<uintptr_t>(o) & 15) == 0)) {
+#pragma unroll
+                for (int i = 0; i < CH; i += 4)
+                  *reinterpret_cast<float4*>(o + i) = make_float4(v[i], v[i + 1], v[i + 2], v[i + 3]);
+              } else {
+                for (int i = 0; i < CH; ++i)
+                  if (i < valid) o[i] = v[i];
+              }
+            }
+            if (pb.out_hi != nullptr) {
+              __nv_bfloat16* oh = pb.out_hi + static_cast<long long>(row) * pb.ld_bf + cb;
+              __nv_bfloat16* ol =
+                  pb.out_lo ? pb.out_lo + static_cast<long long>(row) * pb.ld_bf + cb : nullptr;
+              if constexpr (CH == 32) store_planes32(v, oh, ol, valid);
+              else {
+                for (int i = 0; i < CH; ++i)
+                  if (i < valid) {
+                    __nv_bfloat16 h, l;
+                    split_bf16(v[i], h, l);
+                    oh[i] = h;
+                    if (ol) ol[i] = l;
+                  }
               }
             }
           }
         }
-      }
-    } else if constexpr (EPI == EPI_LSTM) {
-      const int H = pb.hidden;
-      const int src_row = (row_ok && pb.parent != nullptr) ? pb.parent[row] : row;
-#pragma unroll 1
-      for (int c = 0; c < BLOCK_N / 32; ++c) {
-        float v[32];
-        tmem_ld_32x32(t_row + c * 32, v);
-        tmem_ld_wait();
-        if (row_ok) {
-          const int cb = col0 + c * 32;  // gate-interleaved column, multiple of 32
-          const int j0 = cb >> 2;        // first hidden unit of this chunk (8 units)
-          const float4* bp = reinterpret_cast<const float4*>(pb.bias + cb);
-          const float4* cp =
-              reinterpret_cast<const float4*>(pb.c_in + static_cast<long long>(src_row) * H + j0);
-          float cprev[8];
-          {
-            const float4 c0 = __ldg(cp), c1 = __ldg(cp + 1);
-            cprev[0] = c0.x; cprev[1] = c0.y; cprev[2] = c0.z; cprev[3] = c0.w;
-            cprev[4] = c1.x; cprev[5] = c1.y; cprev[6] = c1.z; cprev[7] = c1.w;
-          }
-          float cn[8];
-          __align__(16) __nv_bfloat16 hh[8];
-          __align__(16) __nv_bfloat16 hl[8];
+      } else if constexpr (EPI == EPI_LSTM) {
+        // columns are gate-interleaved: 4 consecutive accumulator columns = i,f,g,o of one unit
+        const int H = pb.hidden;
 #pragma unroll
-          for (int u = 0; u < 8; ++u) {
-            const float4 b = __ldg(bp + u);
-            const float gi = sigmoid_acc(v[4 * u + 0] + b.x);
-            const float gf = sigmoid_acc(v[4 * u + 1] + b.y);
-            const float gg = tanhf(v[4 * u + 2] + b.z);
-            const float go = sigmoid_acc(v[4 * u + 3] + b.w);
-            const float cc = gf * cprev[u] + gi * gg;
-            cn[u] = cc;
-            split_bf16(go * tanhf(cc), hh[u], hl[u]);
-          }
-          float4* co = reinterpret_cast<float4*>(pb.c_out + static_cast<long long>(row) * H + j0);
-          co[0] = make_float4(cn[0], cn[1], cn[2], cn[3]);
-          co[1] = make_float4(cn[4], cn[5], cn[6], cn[7]);
-          *reinterpret_cast<uint4*>(pb.out_hi + static_cast<long long>(row) * pb.ld_bf + j0) =
-              *reinterpret_cast<const uint4*>(hh);
-          if (pb.out_lo != nullptr)
-            *reinterpret_cast<uint4*>(pb.out_lo + static_cast<long long>(row) * pb.ld_bf + j0) =
-                *reinterpret_cast<const uint4*>(hl);
-        }
-      }
-    } else {  // EPI_LOGITS
-      float tv[TOPK];
-      int ti[TOPK];
+        for (int c = 0; c < NCH; ++c) {
+          float v[32];
+          tmem_ld_32x32(t_row + c * 32, v);
+          tmem_ld_wait();
+          if (row_ok) {
+            const int tc = hc0 + c * 32;
+            const int j0 = (col0 + tc) >> 2;  // first hidden unit of this chunk (8 units)
+            float cn[8];
+            __align__(16) __nv_bfloat16 hh[8];
+            __align__(16) __nv_bfloat16 hl[8];
 #pragma unroll
-      for (int k = 0; k < TOPK; ++k) { tv[k] = -INFINITY; ti[k] = 0x7fffffff; }
-      // pass 1: bias, mask, optional store, running top-K (ascending column scan: ties keep the
-      // lower index, like torch.max on the reference path)
-#pragma unroll 1
-      for (int c = 0; c < BLOCK_N / 32; ++c) {
-        float v[32];
-        tmem_ld_32x32(t_row + c * 32, v);
-        tmem_ld_wait();
-        const int cb = col0 + c * 32;
-#pragma unroll
-        for (int i = 0; i < 32; ++i) {
-          const int col = cb + i;
-          const float x = (col < pb.N) ? v[i] + __ldg(pb.bias + col) : -INFINITY;
-          v[i] = x;
-          if (x > tv[TOPK - 1]) {
-#pragma unroll
-            for (int k = TOPK - 1; k >= 1; --k) {
-              const bool shift = x > tv[k - 1];
-              const bool here = !shift && (x > tv[k]);
-              tv[k] = shift ? tv[k - 1] : (here ? x : tv[k]);
-              ti[k] = shift ? ti[k - 1] : (here ? col : ti[k]);
+            for (int u = 0; u < 8; ++u) {
+              const float4 b = *reinterpret_cast<const float4*>(sbias + tc + 4 * u);
+              const float gi = sigmoid_fast(v[4 * u + 0] + b.x);
+              const float gf = sigmoid_fast(v[4 * u + 1] + b.y);
+              const float gg = tanh_fast_acc(v[4 * u + 2] + b.z);
+              const float go = sigmoid_fast(v[4 * u + 3] + b.w);
+              const float cc = gf * cprev[8 * c + u] + gi * gg;
+              cn[u] = cc;
+              split_bf16(go * tanh_fast_acc(cc), hh[u], hl[u]);
             }
-            if (x > tv[0]) { tv[0] = x; ti[0] = col; }
+            float4* co = reinterpret_cast<float4*>(pb.c_out + static_cast<long long>(row) * H + j0);
+            co[0] = make_float4(cn[0], cn[1], cn[2], cn[3]);
+            co[1] = make_float4(cn[4], cn[5], cn[6], cn[7]);
+            *reinterpret_cast<uint4*>(pb.out_hi + static_cast<long long>(row) * pb.ld_bf + j0) =
+                *reinterpret_cast<const uint4*>(hh);
+            if (pb.out_lo != nullptr)
+              *reinterpret_cast<uint4*>(pb.out_lo + static_cast<long long>(row) * pb.ld_bf + j0) =
+                  *reinterpret_cast<const uint4*>(hl);
           }
         }
-        if (row_ok && pb.logits_out != nullptr) {
-          float* o = pb.logits_out + static_cast<long long>(row) * pb.ld_logits + cb;
-          for (int i = 0; i < 32; ++i)
-            if (cb + i < pb.N) o[i] = v[i];
-        }
-      }
-      // pass 2: sum of exp relative to the tile maximum
-      float se = 0.f;
+      } else {  // EPI_LOGITS: one partial record per (row, 64-column group)
+        static_assert(EPI != EPI_LOGITS || HALF == LOGIT_GROUP, "logit records are 64 columns wide");
+        float tv[TOPK];
+        int ti[TOPK];
+#pragma unroll
+        for (int k = 0; k < TOPK; ++k) { tv[k] = -INFINITY; ti[k] = 0x7fffffff; }
+        const int gcol0 = col0 + hc0;
+        const bool full = gcol0 + HALF <= pb.N;  // all columns of this thread are real vocabulary
+        // pass 1: bias, mask, optional store, running top-K (ascending column scan: ties keep the
+        // lower index, like torch.max on the reference path)
 #pragma unroll 1
-      for (int c = 0; c < BLOCK_N / 32; ++c) {
-        float v[32];
-        tmem_ld_32x32(t_row + c * 32, v);
-        tmem_ld_wait();
-        const int cb = col0 + c * 32;
+        for (int c = 0; c < NCH; ++c) {
+          float v[32];
+          tmem_ld_32x32(t_row + c * 32, v);
+          tmem_ld_wait();
+          const int tc = hc0 + c * 32;
+          const int cb = col0 + tc;
 #pragma unroll
-        for (int i = 0; i < 32; ++i) {
-          const int col = cb + i;
-          if (col < pb.N) se += expf(v[i] + __ldg(pb.bias + col) - tv[0]);
+          for (int i = 0; i < 32; i += 4) {
+            const float4 b4 = *reinterpret_cast<const float4*>(sbias + tc + i);
+            v[i] += b4.x; v[i + 1] += b4.y; v[i + 2] += b4.z; v[i + 3] += b4.w;
+          }
+          if (!full) {
+#pragma unroll
+            for (int i = 0; i < 32; ++i)
+              if (cb + i >= pb.N) v[i] = -INFINITY;
+          }
+          if constexpr (TOPK == 1) {
+#pragma unroll
+            for (int i = 0; i < 32; ++i)
+              if (v[i] > tv[0]) { tv[0] = v[i]; ti[0] = cb + i; }
+          } else {
+#pragma unroll
+            for (int i = 0; i < 32; ++i) {
+              const float x = v[i];
+              const int col = cb + i;
+              if (x > tv[TOPK - 1]) {
+#pragma unroll
+                for (int k = TOPK - 1; k >= 1; --k) {
+                  const bool shift = x > tv[k - 1];
+                  const bool here = !shift && (x > tv[k]);
+                  tv[k] = shift ? tv[k - 1] : (here ? x : tv[k]);
+                  ti[k] = shift ? ti[k - 1] : (here ? col : ti[k]);
+                }
+                if (x > tv[0]) { tv[0] = x; ti[0] = col; }
+              }
+            }
+          }
+          if (row_ok && pb.logits_out != nullptr) {
+            float* o = pb.logits_out + static_cast<long long>(row) * pb.ld_logits + cb;
+            for (int i = 0; i < 32; ++i)
+              if (cb + i < pb.N) o[i] = v[i];
+          }
         }
-      }
-      if (row_ok) {
-        const int n_tiles = (pb.N + BLOCK_N - 1) / BLOCK_N;
-        float* rec = pb.partial +
-                     (static_cast<long long>(row) * n_tiles + n_tile) * LogitRec<TOPK>::WORDS;
-        rec[0] = se;
+        // pass 2: sum of exp relative to the group maximum (exp(-inf) = 0 for masked columns)
+        float se = 0.f;
+        const float m2 = tv[0] * 1.4426950408889634f;
+#pragma unroll 1
+        for (int c = 0; c < NCH; ++c) {
+          float v[32];
+          tmem_ld_32x32(t_row + c * 32, v);
+          tmem_ld_wait();
+          const int tc = hc0 + c * 32;
+          const int cb = col0 + tc;
+          float s4[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll
-        for (int k = 0; k < TOPK; ++k) {
-          rec[1 + k] = tv[k];
-          rec[1 + TOPK + k] = __int_as_float(ti[k]);
+          for (int i = 0; i < 32; i += 4) {
+            const float4 b4 = *reinterpret_cast<const float4*>(sbias + tc + i);
+            const float x0 = v[i] + b4.x, x1 = v[i + 1] + b4.y, x2 = v[i + 2] + b4.z, x3 = v[i + 3] + b4.w;
+            const float e0 = exp2f(fmaf(x0, 1.4426950408889634f, -m2));
+            const float e1 = exp2f(fmaf(x1, 1.4426950408889634f, -m2));
+            const float e2 = exp2f(fmaf(x2, 1.4426950408889634f, -m2));
+            const float e3 = exp2f(fmaf(x3, 1.4426950408889634f, -m2));
+            s4[0] += (full || cb + i < pb.N) ? e0 : 0.f;
+            s4[1] += (full || cb + i + 1 < pb.N) ? e1 : 0.f;
+            s4[2] += (full || cb + i + 2 < pb.N) ? e2 : 0.f;
+            s4[3] += (full || cb + i + 3 < pb.N) ? e3 : 0.f;
+          }
+          se += (s4[0] + s4[1]) + (s4[2] + s4[3]);
+        }
+        if (row_ok) {
+          const int groups_per_tile = BLOCK_N / LOGIT_GROUP;
+          const int n_groups = ((pb.N + BLOCK_N - 1) / BLOCK_N) * groups_per_tile;
+          float* rec = pb.partial + (static_cast<long long>(row) * n_groups +
+                                     n_tile * groups_per_tile + half) * LogitRec<TOPK>::WORDS;
+          if (gcol0 >= pb.N) se = 0.f;  // empty group: neutral record
+          rec[0] = se;
+#pragma unroll
+          for (int k = 0; k < TOPK; ++k) {
+            rec[1 + k] = tv[k];
+            rec[1 + TOPK + k] = __int_as_float(ti[k]);
+          }
         }
       }
     }

@@ -42,7 +42,8 @@ event_feats_kernel(const float* __restrict__ c3d, const float* __restrict__ tap,
                    const int32_t* __restrict__ ev_start, const int32_t* __restrict__ ev_len,
                    const int32_t* __restrict__ ev_ind, bf16* __restrict__ hi, bf16* __restrict__ lo) {
   const int e = blockIdx.x;
-  const int s = ev_start[e], len = ev_len[e], ind = ev_ind[e];
+  const int s = ev_start[e], len = ev_len[e];
+  (void)ev_ind;
   const float inv = 1.0f / (float)len;
   for (int c = threadIdx.x; c < FEAT_PAD; c += blockDim.x) {
     float v = 0.f;
@@ -52,13 +53,29 @@ event_feats_kernel(const float* __restrict__ c3d, const float* __restrict__ tap,
       v = acc / (float)len;
       (void)inv;
     } else if (c < ECHR_VIDEO_DIM + HID) {
-      v = __ldg(tap + (long long)ind * HID + (c - ECHR_VIDEO_DIM));
+      v = __ldg(tap + (long long)e * HID + (c - ECHR_VIDEO_DIM));  // tap was gathered by ind at set_inputs
     }
     bf16 h, l2;
     split_bf16(v, h, l2);
     hi[(long long)e * FEAT_PAD + c] = h;
     if (lo != nullptr) lo[(long long)e * FEAT_PAD + c] = l2;
   }
+}
+
+// tap_feats[ind_select_list] (CaptionGenerator.py:121): gather the proposal-encoder state of each
+// event's last clip from the caller's [clips,512] tensor into the compact [events,512] workspace.
+__global__ void __launch_bounds__(128)
+gather_tap_kernel(const float* __restrict__ tap_src, const int32_t* __restrict__ ev_ind, float* __restrict__ dst) {
+  const int e = blockIdx.x;
+  const float4* src = reinterpret_cast<const float4*>(tap_src + (long long)ev_ind[e] * HID);
+  reinterpret_cast<float4*>(dst + (long long)e * HID)[threadIdx.x] = __ldg(src + threadIdx.x);
+}
+
+cudaError_t launch_gather_tap(const echr_batch* b, const float* tap_src, cudaStream_t st) {
+  if (b->n_events == 0) return cudaSuccess;
+  gather_tap_kernel<<<b->n_events, 128, 0, st>>>(tap_src, b->ev_ind, b->tap);
+  count_launch();
+  return cudaGetLastError();
 }
 
 cudaError_t launch_event_feats(const echr_batch* b, cudaStream_t st) {

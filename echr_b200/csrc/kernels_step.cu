@@ -44,8 +44,8 @@ attention_kernel(const float* __restrict__ q, const void* __restrict__ proj_v,
     qv[4 * m] = t.x; qv[4 * m + 1] = t.y; qv[4 * m + 2] = t.z; qv[4 * m + 3] = t.w;
     av[4 * m] = a.x; av[4 * m + 1] = a.y; av[4 * m + 2] = a.z; av[4 * m + 3] = a.w;
   }
-  for (int l = warp; l < L; l += ATT_THREADS / 32) {
-    float pv[16];
+  // two clips per warp iteration: both rows' loads are in flight before the first tanh
+  auto load_proj = [&](int l, float* pv) {
     if (BF16) {
       const bf16* prow = reinterpret_cast<const bf16*>(proj_v) + (long long)(s0 + l) * HID;
 #pragma unroll
@@ -64,11 +64,29 @@ attention_kernel(const float* __restrict__ q, const void* __restrict__ proj_v,
         pv[4 * m] = t.x; pv[4 * m + 1] = t.y; pv[4 * m + 2] = t.z; pv[4 * m + 3] = t.w;
       }
     }
-    float s = 0.f;
+  };
+  constexpr int NW = ATT_THREADS / 32;
+  for (int l = warp; l < L; l += 2 * NW) {
+    const int l2 = l + NW;
+    const bool two = l2 < L;
+    float pa[16], pb2[16];
+    load_proj(l, pa);
+    load_proj(two ? l2 : l, pb2);
+    float sa = 0.f, sb = 0.f;
 #pragma unroll
-    for (int i = 0; i < 16; ++i) s = fmaf(av[i], tanh_fast(pv[i] + qv[i]), s);
-    s = warp_sum(s);
-    if (lane == 0) sc[l] = s;
+    for (int i = 0; i < 16; ++i) {
+      sa = fmaf(av[i], tanh_fast(pa[i] + qv[i]), sa);
+      sb = fmaf(av[i], tanh_fast(pb2[i] + qv[i]), sb);
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      sa += __shfl_xor_sync(0xffffffffu, sa, o);
+      sb += __shfl_xor_sync(0xffffffffu, sb, o);
+    }
+    if (lane == 0) {
+      sc[l] = sa;
+      if (two) sc[l2] = sb;
+    }
   }
   __syncthreads();
   // softmax statistics (every warp computes them redundantly: L is a few hundred at most)
@@ -90,6 +108,7 @@ attention_kernel(const float* __restrict__ q, const void* __restrict__ proj_v,
 #pragma unroll
     for (int i = 0; i < 8; ++i) acc[i] = 0.f;
     const bf16* cbase = reinterpret_cast<const bf16*>(clip_v) + (long long)s0 * ld_clip + 8 * t;
+#pragma unroll 4
     for (int l = grp; l < L; l += 4) {
       const uint4 u = __ldg(reinterpret_cast<const uint4*>(cbase + (long long)l * ld_clip));
       const float w = sc[l];
@@ -108,6 +127,7 @@ attention_kernel(const float* __restrict__ q, const void* __restrict__ proj_v,
     float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
     if (t < ECHR_VIDEO_DIM / 4) {
       const float* cbase = reinterpret_cast<const float*>(clip_v) + (long long)s0 * ld_clip + 4 * t;
+#pragma unroll 4
       for (int l = grp; l < L; l += 2) {
         const float4 c = __ldg(reinterpret_cast<const float4*>(cbase + (long long)l * ld_clip));
         const float w = sc[l];
@@ -288,7 +308,7 @@ cudaError_t launch_finalize_greedy(const echr_batch* b, int step, int32_t* token
   const int rows = b->n_events;
   if (rows == 0) return cudaSuccess;
   const echr_model* m = b->model;
-  const int n_tiles = (m->V1 + 127) / 128;
+  const int n_tiles = ((m->V1 + 127) / 128) * (128 / LOGIT_GROUP);
   const PlaneMat& nxt = b->act[(step + 1) & 1];
   finalize_greedy_kernel<<<(rows + FIN_WARPS - 1) / FIN_WARPS, FIN_WARPS * 32, 0, st>>>(
       rows, n_tiles, step, m->cfg.seq_length, b->partial, m->embed.p, m->embed.plane_stride(), nxt.p,
@@ -325,7 +345,7 @@ cudaError_t launch_finalize_tf(const echr_batch* b, int step, const int32_t* seq
   const int rows = b->n_events;
   if (rows == 0) return cudaSuccess;
   const echr_model* m = b->model;
-  const int n_tiles = (m->V1 + 127) / 128;
+  const int n_tiles = ((m->V1 + 127) / 128) * (128 / LOGIT_GROUP);
   const PlaneMat& nxt = b->act[(step + 1) & 1];
   finalize_tf_kernel<<<(rows + FIN_WARPS - 1) / FIN_WARPS, FIN_WARPS * 32, 0, st>>>(
       rows, n_tiles, step, seq_cols, m->V1, b->partial, seq, m->embed.p, m->embed.plane_stride(), nxt.p,
@@ -364,39 +384,32 @@ finalize_beam_kernel(int beam, int n_tiles, int step, int seq_len, const float* 
     const int r = row0 + warp;
     const float* rec = partial + (long long)r * n_tiles * W;
     const RowStat s = merge_row_stats<4>(rec, n_tiles, lane);
-    // each lane holds the candidates of its tiles (<= 2 tiles x 4)
-    float cv[8];
-    int ci[8];
-#pragma unroll
-    for (int u = 0; u < 2; ++u) {
-      const int t = lane + 32 * u;
-#pragma unroll
-      for (int k = 0; k < 4; ++k) {
-        cv[4 * u + k] = (t < n_tiles) ? rec[t * W + 1 + k] : -INFINITY;
-        ci[4 * u + k] = (t < n_tiles) ? __float_as_int(rec[t * W + 5 + k]) : 0x7fffffff;
-      }
-    }
     const bool live = beam_live[r] != 0;
     const float base = beam_score[r];
+    // k rounds of "best candidate strictly after the previous winner" in (value desc, index asc)
+    // order; every lane rescans the records of its groups (L1-resident), so any vocabulary fits.
+    float last_v = INFINITY;
+    int last_i = -1;
     for (int k = 0; k < beam; ++k) {
-      float bv = -INFINITY;
-      int bi = 0x7fffffff, bslot = -1;
+      float wv = -INFINITY;
+      int wi = 0x7fffffff;
+      for (int t = lane; t < n_tiles; t += 32) {
 #pragma unroll
-      for (int u = 0; u < 8; ++u)
-        if (cv[u] > bv || (cv[u] == bv && ci[u] < bi)) { bv = cv[u]; bi = ci[u]; bslot = u; }
-      float wv = bv;
-      int wi = bi;
+        for (int u = 0; u < 4; ++u) {
+          const float v = rec[t * W + 1 + u];
+          const int i = __float_as_int(rec[t * W + 5 + u]);
+          const bool eligible = (v < last_v) || (v == last_v && i > last_i);
+          if (eligible && (v > wv || (v == wv && i < wi))) { wv = v; wi = i; }
+        }
+      }
 #pragma unroll
       for (int o = 16; o > 0; o >>= 1) {
         const float ov = __shfl_xor_sync(0xffffffffu, wv, o);
         const int oi = __shfl_xor_sync(0xffffffffu, wi, o);
         if (ov > wv || (ov == wv && oi < wi)) { wv = ov; wi = oi; }
       }
-      if (bslot >= 0 && bv == wv && bi == wi) {  // the owning lane retires the winner
-#pragma unroll
-        for (int u = 0; u < 8; ++u)
-          if (u == bslot) { cv[u] = -INFINITY; ci[u] = 0x7fffffff; }
-      }
+      last_v = wv;
+      last_i = wi;
       if (lane == 0) {
         const float lp = (wv - s.max_val) - s.log_sum;
         cand_lp[warp][k] = lp;
@@ -512,8 +525,7 @@ cudaError_t launch_finalize_beam(const echr_batch* b, int beam, int step, int32_
   if (b->n_events == 0) return cudaSuccess;
   if (beam < 1 || beam > BEAM_MAX) return cudaErrorInvalidValue;
   const echr_model* m = b->model;
-  const int n_tiles = (m->V1 + 127) / 128;
-  if (n_tiles > 64) return cudaErrorInvalidValue;
+  const int n_tiles = ((m->V1 + 127) / 128) * (128 / LOGIT_GROUP);
   const int S = m->cfg.seq_length;
   const long long rows = (long long)b->n_events * beam;
   const PlaneMat& nxt = b->act[(step + 1) & 1];
