@@ -158,7 +158,7 @@ def main():
     import torch.distributed as dist
     from echr_b200.caption_generator import CaptionGenerator
     from echr_b200.engine import BatchLayout
-    from echr_b200.parallel import gather_tokens
+    from echr_b200.parallel import exchange_counts, gather_tokens
 
     torch.set_grad_enabled(False)
     torch.cuda.set_device(local)
@@ -191,6 +191,7 @@ def main():
     h_lda = torch.stack([v.lda_feats for v in vids]).contiguous().pin_memory()
     d_c3d, d_tap, d_lda = h_c3d.to(dev), h_tap.to(dev), h_lda.to(dev)
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)  # > 126 MB L2
+    counts = exchange_counts(n_events, dev) if world > 1 else None
 
     def step_device():
         eng.set_inputs(lay, d_c3d, d_tap, d_lda, beam=beam)
@@ -200,7 +201,7 @@ def main():
         else:
             tok, lp = eng.decode_greedy()
         if world > 1:
-            tok = gather_tokens(tok)
+            tok = gather_tokens(tok, counts=counts)
         return tok
 
     host_out = (torch.zeros(n_events, opt.CG_seq_length, dtype=torch.int32).pin_memory(),
@@ -210,7 +211,7 @@ def main():
     def step_host():
         tok, lp, sc = eng.caption_host(lay, h_c3d, h_tap, h_lda, beam=beam, out=host_out)
         if world > 1:
-            tok = gather_tokens(tok.to(dev, non_blocking=True))
+            tok = gather_tokens(tok.to(dev, non_blocking=True), counts=counts)
         return tok
 
     def timed(fn, steps, warm):

@@ -28,6 +28,7 @@ _CTYPES = {
     "float*": ctypes.c_void_p,
     "const float*": ctypes.c_void_p,
     "int32_t*": ctypes.c_void_p,
+    "int64_t*": ctypes.c_void_p,
     "const int32_t*": ctypes.c_void_p,
     "const char*": ctypes.c_char_p,
     "echr_model_t*": ctypes.c_void_p,

@@ -41,13 +41,13 @@ int echr_split_bf16(const float* src, int64_t rows, int64_t cols, int64_t ld_src
 int echr_attention_step(const float* q, const void* proj, const void* clip, int64_t ld_clip,
                         int clip_bf16, const float* alpha, const int32_t* row_start,
                         const int32_t* row_len, int64_t rows, float* out_f32, void* out_hi,
-                        void* out_lo, int64_t ld_bf, void* stream) {
+                        void* out_lo, int64_t ld_bf, int max_len, void* stream) {
   ECHR_REQUIRE(q && proj && clip && alpha && row_start && row_len, "echr_attention_step: null pointer");
   ECHR_REQUIRE(rows >= 0 && rows < (1ll << 31), "echr_attention_step: bad row count");
   ECHR_REQUIRE(ld_clip >= ECHR_VIDEO_DIM && (ld_clip * (clip_bf16 ? 2 : 4)) % 16 == 0,
                "echr_attention_step: clip row stride must be >= 500 and 16-byte aligned");
   ECHR_CUDA(launch_attention(q, proj, clip, ld_clip, clip_bf16, alpha, row_start, row_len, rows, out_f32,
-                             (bf16*)out_hi, (bf16*)out_lo, ld_bf, (cudaStream_t)stream));
+                             (bf16*)out_hi, (bf16*)out_lo, ld_bf, (cudaStream_t)stream, max_len));
   return ECHR_OK;
 }
 

@@ -11,6 +11,12 @@ using namespace echr;
 
 namespace echr {
 
+int trace_next(echr_batch* b, int kind) {
+  if (b->trace_on != 1 || b->trace_n >= TRACE_SLOTS) return 0;
+  b->trace_kind[b->trace_n] = (unsigned char)kind;
+  return b->trace_n++;
+}
+
 static std::atomic<long long> g_launches{0};
 void count_launch(int n) { g_launches.fetch_add(n, std::memory_order_relaxed); }
 
@@ -130,9 +136,10 @@ static const char* fill_problem(GemmProblem& pb, const GemmSpec& s, int a_terms,
 }
 
 static int run_gemm(const GemmSpec* specs, int groups, int a_terms, int w_terms, int block_n, int epi,
-                    int topk, cudaStream_t st, const char* what) {
+                    int topk, cudaStream_t st, const char* what, echr_batch* tb = nullptr, int kind = 5) {
   GemmParams P;
   memset(&P, 0, sizeof(P));
+  if (tb != nullptr && tb->trace_on == 1) { P.trace = tb->trace; P.trace_slot = trace_next(tb, kind); }
   int max_m = 0, max_n = 0;
   for (int g = 0; g < groups; ++g) {
     const char* err = fill_problem(P.prob[g], specs[g], a_terms, w_terms, block_n);
@@ -332,6 +339,7 @@ static void batch_layout(echr_batch* b, Arena& a) {
   b->beam_hist_tok = a.take<int32_t>((size_t)2 * c.max_rows * S);
   b->beam_hist_lp = a.take<float>((size_t)2 * c.max_rows * S);
   b->best_score = a.take<float>(c.max_events);
+  b->trace = a.take<unsigned long long>(2 * TRACE_SLOTS);
 }
 
 extern "C" int echr_batch_create(const echr_model_t* model, const echr_capacity_t* cap, echr_batch_t** out) {
@@ -418,6 +426,7 @@ extern "C" int echr_batch_set_inputs(echr_batch_t* b, const echr_batch_desc_t* d
   int32_t* vid_n = vid_first + b->cap.max_videos;
   for (int v = 0; v < d->n_videos; ++v) { vid_first[v] = 0; vid_n[v] = 0; }
   int prev_v = 0;
+  int max_len = 0;
   for (int i = 0; i < d->n_events; ++i) {
     const int v = d->host_event_video[i];
     ECHR_REQUIRE(v >= prev_v && v < d->n_videos, "echr_batch_set_inputs: event %d: video index %d not non-decreasing / out of range", i, v);
@@ -432,6 +441,7 @@ extern "C" int echr_batch_set_inputs(echr_batch_t* b, const echr_batch_desc_t* d
     hs[0 * E + i] = v;
     hs[1 * E + i] = off[v] + s;
     hs[2 * E + i] = e - s;
+    if (e - s > max_len) max_len = e - s;
     hs[3 * E + i] = off[v] + ind;
   }
   long long pairs = 0;
@@ -454,6 +464,7 @@ extern "C" int echr_batch_set_inputs(echr_batch_t* b, const echr_batch_desc_t* d
   b->n_clips = n_clips;
   b->n_pairs = (int)pairs;
   b->max_n = max_n;
+  b->max_len = max_len;
   b->encoded = false;
   ECHR_CUDA(cudaMemcpyAsync(b->ev_video, hs, sizeof(int32_t) * ((size_t)7 * E + 2 * b->cap.max_videos),
                             cudaMemcpyHostToDevice, st));
@@ -490,6 +501,7 @@ extern "C" int echr_encode(echr_batch_t* b, void* stream) {
     GemmSpec s;
     s.A = &b->clip_pl; s.M = b->n_clips; s.W = &m->w_ctx2att; s.N = HID; s.K = CLIP_PAD;
     s.bias = m->b_ctx2att;
+    s.act = ACT_EXP2X;  // the table holds e^{2P} (see kernels_step.cu)
     if (m->cfg.clip_bf16) { s.out_hi = b->proj_bf; s.ld_bf = HID; }
     else { s.out_f32 = b->proj_f32; s.ld_f32 = HID; }
     ECHR_TRY(run_gemm(&s, 1, at, wt, 128, EPI_STORE, 1, st, "ctx2att"));
@@ -572,15 +584,18 @@ static int enqueue_step(echr_batch* b, int rows, int t, int topk, float* logits_
   if (parts & PART_H2ATT) {
     GemmSpec s;
     s.A = &cur; s.a_col0 = ACT_H + HID; s.M = rows; s.W = &m->w_h2att; s.N = HID; s.K = HID;
-    s.bias = m->b_h2att; s.out_f32 = b->q_att; s.ld_f32 = HID;
-    ECHR_TRY(run_gemm(&s, 1, at, wt, 128, EPI_STORE, 1, st, "h2att"));
+    s.bias = m->b_h2att; s.act = ACT_EXP2X; s.out_f32 = b->q_att; s.ld_f32 = HID;  // e^{2q}
+    PdlScope pdl(PDL_H2ATT);
+    ECHR_TRY(run_gemm(&s, 1, at, wt, 128, EPI_STORE, 1, st, "h2att", b, 0));
   }
-  if (parts & PART_ATT)
+  if (parts & PART_ATT) {
+  PdlScope pdl(PDL_ATT);
   ECHR_CUDA(launch_attention(b->q_att, m->cfg.clip_bf16 ? (const void*)b->proj_bf : (const void*)b->proj_f32,
                              m->cfg.clip_bf16 ? (const void*)b->clip_pl.plane(0) : (const void*)b->c3d,
                              m->cfg.clip_bf16 ? CLIP_PAD : ECHR_VIDEO_DIM, m->cfg.clip_bf16, m->alpha,
                              b->row_start, b->row_len, rows, nullptr, cur.plane(0) + ACT_ATT,
-                             at > 1 ? cur.plane(1) + ACT_ATT : nullptr, ACT_LD, st));
+                             at > 1 ? cur.plane(1) + ACT_ATT : nullptr, ACT_LD, st, b->max_len, trace_ptr(b), trace_next(b, 1)));
+  }
   if (parts & PART_GATES) {
     GemmSpec s[3];
     const int* kbs[3] = {KB_L0, KB_L1, KB_L2};
@@ -594,13 +609,15 @@ static int enqueue_step(echr_batch* b, int rows, int t, int topk, float* logits_
       s[l].out_lo = at > 1 ? nxt.plane(1) + ACT_H + l * HID : nullptr;
       s[l].ld_bf = ACT_LD;
     }
-    ECHR_TRY(run_gemm(s, 3, at, wt, 128, EPI_LSTM, 1, st, "lstm_gates"));
+    PdlScope pdl(PDL_GATES);
+    ECHR_TRY(run_gemm(s, 3, at, wt, 128, EPI_LSTM, 1, st, "lstm_gates", b, 2));
   }
   if (parts & PART_LOGIT) {
     GemmSpec s;
     s.A = &nxt; s.a_col0 = ACT_H; s.M = rows; s.W = &m->w_logit; s.N = m->V1; s.K = 3 * HID;
     s.bias = m->b_logit; s.partial = b->partial; s.logits_out = logits_out; s.ld_logits = ld_logits;
-    ECHR_TRY(run_gemm(&s, 1, at, wt, 128, EPI_LOGITS, topk, st, "logit"));
+    PdlScope pdl(PDL_LOGIT);
+    ECHR_TRY(run_gemm(&s, 1, at, wt, 128, EPI_LOGITS, topk, st, "logit", b, 3));
   }
   return ECHR_OK;
 }
@@ -630,7 +647,10 @@ static int enqueue_decode(echr_batch* b, int beam, int mode, cudaStream_t st, cu
         ECHR_CUDA(cudaEventRecord(b->cap_events[1], side));
       }
       ECHR_TRY(enqueue_step(b, rows, t, topk, nullptr, 0, st, PART_LOGIT));
-      ECHR_CUDA(launch_finalize_greedy(b, t, b->tokens_dev, b->logp_dev, st));
+      {
+        PdlScope pdl(PDL_FINALIZE);
+        ECHR_CUDA(launch_finalize_greedy(b, t, b->tokens_dev, b->logp_dev, st));
+      }
       if (t + 1 < S) ECHR_CUDA(cudaStreamWaitEvent(st, b->cap_events[1], 0));
     }
     return ECHR_OK;
@@ -657,6 +677,11 @@ static int run_decode(echr_batch* b, int beam, int mode, cudaStream_t st) {
     if (b->graph_exec) { cudaGraphExecDestroy(b->graph_exec); b->graph_exec = nullptr; }
     const long long before = g_launches.load();
     cudaGraph_t graph = nullptr;
+    {
+      const char* tr = getenv("ECHR_TRACE");
+      b->trace_on = (tr != nullptr && tr[0] == '1') ? 1 : 0;
+      b->trace_n = 0;
+    }
     // capture on a private stream: the caller's stream may be the legacy default stream, which
     // cannot be captured
     if (b->cap_stream == nullptr) {
@@ -673,10 +698,14 @@ static int run_decode(echr_batch* b, int beam, int mode, cudaStream_t st) {
     e = cudaGraphInstantiate(&b->graph_exec, graph, 0);
     cudaGraphDestroy(graph);
     if (e != cudaSuccess) { b->graph_exec = nullptr; return set_error(ECHR_ERR_CUDA, "decode: graph instantiate failed: %s", cudaGetErrorString(e)); }
+    b->trace_on = b->trace_on ? 2 : 0;  // 2: slots assigned, no more trace_next() calls
     b->graph_kernels = g_launches.load() - before;
     g_launches.store(before);
     b->graph_rows = rows;
     b->graph_beam = key_beam;
+  }
+  if (b->trace_on) {  // reset {min start, max end} before the replay
+    ECHR_CUDA(cudaMemsetAsync(b->trace, 0xff, sizeof(unsigned long long) * TRACE_SLOTS * 2, st));
   }
   ECHR_CUDA(cudaGraphLaunch(b->graph_exec, st));
   count_launch((int)b->graph_kernels);
@@ -779,6 +808,25 @@ extern "C" int echr_time_step_kernels(echr_batch_t* b, int beam, int iters, floa
   cudaEventDestroy(e1);
   g_launches.store(before);
   return rc;
+}
+
+// Timeline of the last decode graph replay (only when the graph was captured with ECHR_TRACE=1):
+// per kernel its kind (0 h2att, 1 attention, 2 gates, 3 logits, 4 finalize), earliest CTA start and
+// latest CTA end in globaltimer ns.  Synchronises the device.  Returns the number of kernels.
+extern "C" int echr_trace_read(echr_batch_t* b, int64_t* host_start_ns, int64_t* host_end_ns, int32_t* host_kind,
+                               int max_entries) {
+  if (!b || !b->trace_on || !host_start_ns || !host_end_ns || !host_kind) return 0;
+  if (cudaDeviceSynchronize() != cudaSuccess) return 0;
+  std::vector<unsigned long long> h(2 * TRACE_SLOTS);
+  if (cudaMemcpy(h.data(), b->trace, sizeof(unsigned long long) * 2 * TRACE_SLOTS, cudaMemcpyDeviceToHost) != cudaSuccess)
+    return 0;
+  int n = b->trace_n < max_entries ? b->trace_n : max_entries;
+  for (int i = 0; i < n; ++i) {
+    host_start_ns[i] = (int64_t)h[2 * i];
+    host_end_ns[i] = (int64_t)(~h[2 * i + 1]);
+    host_kind[i] = b->trace_kind[i];
+  }
+  return n;
 }
 
 extern "C" int64_t echr_launch_count(int reset) {

@@ -59,6 +59,7 @@ struct echr_batch {
   echr_capacity_t cap;
   // current batch
   int n_videos, n_events, n_clips, n_pairs, max_n;  // max_n = largest events-per-video
+  int max_len;                                      // longest event span (clips)
   bool encoded;
   // inputs (copies)
   float *c3d, *tap, *lda;  // [clips,500]; tap_feats[ind] per event [events,512]; [videos,100]
@@ -104,6 +105,10 @@ struct echr_batch {
   int32_t *graph_tokens_out;
   float *graph_logp_out, *graph_score_out;
   int64_t graph_kernels;
+  // timeline trace (ECHR_TRACE=1): device [2*TRACE_SLOTS] u64, host-side kind of every slot
+  unsigned long long* trace;
+  int trace_on, trace_n;
+  unsigned char trace_kind[1024];
   void* arena;
   size_t arena_bytes;
 };
@@ -121,14 +126,20 @@ cudaError_t launch_relation_attn(const echr_batch* b, cudaStream_t st);
 cudaError_t launch_attention(const float* q, const void* proj, const void* clip, int64_t ld_clip,
                              int clip_bf16, const float* alpha, const int32_t* row_start,
                              const int32_t* row_len, int64_t rows, float* out_f32, bf16* out_hi,
-                             bf16* out_lo, int64_t ld_bf, cudaStream_t st);
+                             bf16* out_lo, int64_t ld_bf, cudaStream_t st, int max_len = 0,
+                             unsigned long long* trace = nullptr, int trace_slot = 0);
 cudaError_t launch_decode_init(const echr_batch* b, int beam, cudaStream_t st);
-cudaError_t launch_finalize_greedy(const echr_batch* b, int step, int32_t* tokens, float* logp,
+cudaError_t launch_finalize_greedy(echr_batch* b, int step, int32_t* tokens, float* logp,
                                    cudaStream_t st);
 cudaError_t launch_finalize_beam(const echr_batch* b, int beam, int step, int32_t* tokens,
                                  float* logp, float* score, cudaStream_t st);
 cudaError_t launch_finalize_tf(const echr_batch* b, int step, const int32_t* seq, int seq_cols,
                                float* logprobs, cudaStream_t st);
 void count_launch(int n = 1);
+constexpr int TRACE_SLOTS = 1024;
+// next trace slot of this batch for a kernel of `kind` (0 h2att, 1 attention, 2 gates, 3 logits, 4 finalize,
+// 5 other); returns -1 / nullptr when tracing is off
+int trace_next(echr_batch* b, int kind);
+inline unsigned long long* trace_ptr(const echr_batch* b) { return b->trace_on == 1 ? b->trace : nullptr; }
 
 }  // namespace echr

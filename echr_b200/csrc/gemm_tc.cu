@@ -1,6 +1,7 @@
 // Host side of the tcgen05 GEMM: tensor-map encoding (driver entry point fetched at run time so
 // the library has no link-time libcuda dependency) and the template dispatch table.
 #include "gemm_tc.cuh"
+#include "util.cuh"
 
 #include <mutex>
 
@@ -56,8 +57,7 @@ static cudaError_t launch_one(const GemmParams& P, dim3 grid, cudaStream_t strea
     if (e != cudaSuccess) return e;
     attr_set = true;
   }
-  kern<<<grid, GEMM_THREADS, Cfg::SMEM_BYTES, stream>>>(P);
-  return cudaGetLastError();
+  return launch_pdl(kern, grid, dim3(GEMM_THREADS), Cfg::SMEM_BYTES, stream, P);
 }
 
 template <int A, int W>

@@ -36,7 +36,7 @@ constexpr int GEMM_THREADS = 128 + GEMM_EPI_WARPS * 32;  // warps 0-3: TMA, MMA,
 constexpr int LOGIT_GROUP = 64;                          // vocabulary columns per partial record
 
 enum : int { EPI_STORE = 0, EPI_LSTM = 1, EPI_LOGITS = 2 };
-enum : int { ACT_NONE = 0, ACT_TANH = 1 };
+enum : int { ACT_NONE = 0, ACT_TANH = 1, ACT_EXP2X = 2 };  // ACT_EXP2X: exp(2 * clamp(x, -40, 40))
 
 struct GemmProblem {
   CUtensorMap tmA;  // 3-D {K cols, M rows, planes}, box {64, 128, 1}, SWIZZLE_128B
@@ -65,6 +65,8 @@ struct GemmProblem {
 
 struct GemmParams {
   GemmProblem prob[GEMM_MAX_GROUPS];
+  unsigned long long* trace;  // optional timeline trace (see ptx.cuh)
+  int trace_slot;
 };
 
 template <int TOPK>
@@ -124,6 +126,7 @@ gemm_tc_kernel(const __grid_constant__ GemmParams P) {
   const GemmProblem& pb = P.prob[blockIdx.z];
   const int n_tile = blockIdx.x;
   const int m_tile = blockIdx.y;
+  trace_begin(P.trace, P.trace_slot);
   if (n_tile * BLOCK_N >= pb.N || m_tile * GEMM_BLOCK_M >= pb.M) return;  // whole CTA leaves
 
   extern __shared__ uint8_t smem_raw[];
@@ -164,6 +167,10 @@ gemm_tc_kernel(const __grid_constant__ GemmParams P) {
   __syncthreads();
   tc_fence_after_sync();
   const uint32_t tmem_base = *tmem_ptr_generic;
+  // everything above touched only constants (weights, descriptors): let the next kernel start its
+  // own prologue, then wait for the previous kernel's results
+  pdl_trigger();
+  pdl_wait();
 
   if (warp == 0) {
     // ===================== TMA producer =====================
@@ -273,6 +280,9 @@ gemm_tc_kernel(const __grid_constant__ GemmParams P) {
             if (act == ACT_TANH) {
 #pragma unroll
               for (int i = 0; i < CH; ++i) v[i] = tanh_fast_acc(v[i]);
+            } else if (act == ACT_EXP2X) {
+#pragma unroll
+              for (int i = 0; i < CH; ++i) v[i] = __expf(2.0f * fminf(fmaxf(v[i], -40.f), 40.f));
             }
             const int valid = min(CH, pb.N - cb);
             if (pb.out_f32 != nullptr) {
@@ -441,6 +451,7 @@ gemm_tc_kernel(const __grid_constant__ GemmParams P) {
     tc_fence_after_sync();
     tmem_dealloc<Cfg::TMEM_COLS>(tmem_base);
   }
+  trace_end(P.trace, P.trace_slot);
 }
 
 // ---------------------------------------------------------------- host side

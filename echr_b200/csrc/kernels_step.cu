@@ -4,18 +4,26 @@
 //   finalize_greedy    merge the logit tiles' partials -> argmax / log-prob / next input (OldModel_NEW.py:158,175-183)
 //   finalize_tf        same merge for the teacher-forced path (OldModel_NEW.py:98-130)
 //   finalize_beam      beam selection + state reorder (spec: oracle/echr_oracle.py beam_search)
+#include <type_traits>
+
 #include "engine.cuh"
 #include "util.cuh"
 
 namespace echr {
 
-// tanh with ~4e-7 absolute error from one ex2 and one fast division (inputs here are O(1)).
-__device__ __forceinline__ float tanh_fast(float x) {
-  const float e = __expf(2.0f * x);
-  return 1.0f - __fdividef(2.0f, e + 1.0f);
+// The attention score is sum_k alpha_k * tanh(P_lk + q_k).  With tanh(x) = 1 - 2 / (e^{2x} + 1) and
+// e^{2(P+q)} = e^{2P} * e^{2q}, the tables hold EP = e^{2P} (written once per batch by the ctx2att
+// GEMM epilogue) and EQ = e^{2q} (h2att GEMM epilogue), and a score costs per element one FMUL, one
+// FADD, one MUFU.RCP and one FFMA:  score' = sum_k (-2 alpha_k) / (EP_lk * EQ_k + 1).  The dropped
+// constant sum_k alpha_k is the same for every clip of the row, so the softmax is unchanged.  Both
+// exponents are clamped to +-80 when the tables are written, so the product stays finite.
+__device__ __forceinline__ float rcp_fast(float x) {
+  float y;
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
 }
 
-constexpr int ATT_THREADS = 256;
+constexpr int ATT_THREADS = 512;
 constexpr int ATT_MAX_L = 1024;
 
 // One CTA per decode row.  Pass 1: one warp per clip, lanes across the 512 hidden units (coalesced
@@ -28,11 +36,14 @@ attention_kernel(const float* __restrict__ q, const void* __restrict__ proj_v,
                  const void* __restrict__ clip_v, long long ld_clip, const float* __restrict__ alpha,
                  const int32_t* __restrict__ row_start, const int32_t* __restrict__ row_len,
                  float* __restrict__ out_f32, bf16* __restrict__ out_hi, bf16* __restrict__ out_lo,
-                 long long ld_bf) {
+                 long long ld_bf, unsigned long long* trace, int trace_slot) {
+  trace_begin(trace, trace_slot);
   __shared__ float sc[ATT_MAX_L];
-  __shared__ __align__(16) float red[4][512];
+  __shared__ __align__(16) float red[ATT_THREADS / 64][512];
   const int r = blockIdx.x;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  pdl_trigger();
+  pdl_wait();  // q comes from the h2att GEMM launched just before; nothing but weights is safe earlier
   const int s0 = row_start[r];
   const int L = row_len[r];
   // q and alpha: lane owns hidden units [128*m + 4*lane, +4), m = 0..3
@@ -42,7 +53,7 @@ attention_kernel(const float* __restrict__ q, const void* __restrict__ proj_v,
     const float4 t = __ldg(reinterpret_cast<const float4*>(q + (long long)r * HID + 128 * m + 4 * lane));
     const float4 a = __ldg(reinterpret_cast<const float4*>(alpha + 128 * m + 4 * lane));
     qv[4 * m] = t.x; qv[4 * m + 1] = t.y; qv[4 * m + 2] = t.z; qv[4 * m + 3] = t.w;
-    av[4 * m] = a.x; av[4 * m + 1] = a.y; av[4 * m + 2] = a.z; av[4 * m + 3] = a.w;
+    av[4 * m] = -2.f * a.x; av[4 * m + 1] = -2.f * a.y; av[4 * m + 2] = -2.f * a.z; av[4 * m + 3] = -2.f * a.w;
   }
   // two clips per warp iteration: both rows' loads are in flight before the first tanh
   auto load_proj = [&](int l, float* pv) {
@@ -75,8 +86,8 @@ attention_kernel(const float* __restrict__ q, const void* __restrict__ proj_v,
     float sa = 0.f, sb = 0.f;
 #pragma unroll
     for (int i = 0; i < 16; ++i) {
-      sa = fmaf(av[i], tanh_fast(pa[i] + qv[i]), sa);
-      sb = fmaf(av[i], tanh_fast(pb2[i] + qv[i]), sb);
+      sa = fmaf(av[i], rcp_fast(fmaf(pa[i], qv[i], 1.0f)), sa);
+      sb = fmaf(av[i], rcp_fast(fmaf(pb2[i], qv[i], 1.0f)), sb);
     }
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) {
@@ -102,14 +113,14 @@ attention_kernel(const float* __restrict__ q, const void* __restrict__ proj_v,
   __syncthreads();
   // pass 2
   if (BF16) {
-    // 64 threads per clip row (8 bf16 each), 4 clip groups
+    // 64 threads per clip row (8 bf16 each), ATT_THREADS/64 clip groups
     const int grp = threadIdx.x >> 6, t = threadIdx.x & 63;
     float acc[8];
 #pragma unroll
     for (int i = 0; i < 8; ++i) acc[i] = 0.f;
     const bf16* cbase = reinterpret_cast<const bf16*>(clip_v) + (long long)s0 * ld_clip + 8 * t;
 #pragma unroll 4
-    for (int l = grp; l < L; l += 4) {
+    for (int l = grp; l < L; l += ATT_THREADS / 64) {
       const uint4 u = __ldg(reinterpret_cast<const uint4*>(cbase + (long long)l * ld_clip));
       const float w = sc[l];
       const __nv_bfloat162* b = reinterpret_cast<const __nv_bfloat162*>(&u);
@@ -122,13 +133,13 @@ attention_kernel(const float* __restrict__ q, const void* __restrict__ proj_v,
 #pragma unroll
     for (int i = 0; i < 8; ++i) red[grp][8 * t + i] = acc[i];
   } else {
-    // 128 threads per clip row (4 floats each, 125 active), 2 clip groups
+    // 128 threads per clip row (4 floats each, 125 active), ATT_THREADS/128 clip groups
     const int grp = threadIdx.x >> 7, t = threadIdx.x & 127;
     float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
     if (t < ECHR_VIDEO_DIM / 4) {
       const float* cbase = reinterpret_cast<const float*>(clip_v) + (long long)s0 * ld_clip + 4 * t;
 #pragma unroll 4
-      for (int l = grp; l < L; l += 2) {
+      for (int l = grp; l < L; l += ATT_THREADS / 128) {
         const float4 c = __ldg(reinterpret_cast<const float4*>(cbase + (long long)l * ld_clip));
         const float w = sc[l];
         acc.x = fmaf(w, c.x, acc.x); acc.y = fmaf(w, c.y, acc.y);
@@ -139,8 +150,9 @@ attention_kernel(const float* __restrict__ q, const void* __restrict__ proj_v,
   }
   __syncthreads();
   for (int c = threadIdx.x; c < ECHR_VIDEO_DIM; c += ATT_THREADS) {
-    float v = red[0][c] + red[1][c];
-    if (BF16) v += red[2][c] + red[3][c];
+    float v = 0.f;
+#pragma unroll
+    for (int g = 0; g < (BF16 ? ATT_THREADS / 64 : ATT_THREADS / 128); ++g) v += red[g][c];
     if (out_f32 != nullptr) out_f32[(long long)r * ECHR_VIDEO_DIM + c] = v;
     if (out_hi != nullptr) {
       bf16 h, l2;
@@ -149,21 +161,193 @@ attention_kernel(const float* __restrict__ q, const void* __restrict__ proj_v,
       if (out_lo != nullptr) out_lo[(long long)r * ld_bf + c] = l2;
     }
   }
+  trace_end(trace, trace_slot);
 }
 
+// Staged variant for latency-bound batches (few CTAs per SM): the event's whole window of projected
+// rows and clip features is brought into shared memory by the bulk-copy engine (cp.async.bulk, two
+// mbarriers) right at kernel start — windows are contiguous in HBM, so each is a handful of 1-D bulk
+// copies — and both passes then run out of shared memory.  One global round trip instead of
+// ~L/8 dependent ones.  Requires the window to fit: L * (proj row + clip row) <= ATT_STAGE_BYTES.
+constexpr int ATT_STAGE_BYTES = 200 * 1024;
+constexpr int ATT_BULK_CLIPS = 16;  // clips per bulk copy
+
+template <bool BF16>
+__global__ void __launch_bounds__(ATT_THREADS)
+attention_staged_kernel(const float* __restrict__ q, const void* __restrict__ proj_v,
+                        const void* __restrict__ clip_v, long long ld_clip,
+                        const float* __restrict__ alpha, const int32_t* __restrict__ row_start,
+                        const int32_t* __restrict__ row_len, float* __restrict__ out_f32,
+                        bf16* __restrict__ out_hi, bf16* __restrict__ out_lo, long long ld_bf,
+                        int max_len, unsigned long long* trace, int trace_slot) {
+  trace_begin(trace, trace_slot);
+  typedef typename std::conditional<BF16, bf16, float>::type T;
+  constexpr int CLIP_ROW = BF16 ? CLIP_PAD : ECHR_VIDEO_DIM;  // elements per staged clip row
+  extern __shared__ __align__(128) uint8_t att_smem[];
+  __shared__ float sc[ATT_MAX_L];
+  __shared__ __align__(16) float red[ATT_THREADS / 64][512];
+  __shared__ __align__(8) uint64_t bars[2];
+  T* sproj = reinterpret_cast<T*>(att_smem);                       // [max_len][512]
+  T* sclip = sproj + (size_t)max_len * HID;                        // [max_len][CLIP_ROW]
+  const int r = blockIdx.x;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  pdl_trigger();
+  pdl_wait();
+  const int s0 = row_start[r];
+  const int L = row_len[r];
+  const uint32_t bar_p = smem_u32(&bars[0]), bar_c = smem_u32(&bars[1]);
+  if (threadIdx.x == 0) {
+    mbar_init(bar_p, 1);
+    mbar_init(bar_c, 1);
+    fence_mbar_init();
+    const uint32_t prow_b = HID * sizeof(T), crow_b = CLIP_ROW * sizeof(T);
+    mbar_arrive_expect_tx(bar_p, (uint32_t)L * prow_b);
+    mbar_arrive_expect_tx(bar_c, (uint32_t)L * crow_b);
+    const uint8_t* psrc = reinterpret_cast<const uint8_t*>(proj_v) + (size_t)s0 * prow_b;
+    const uint8_t* csrc = reinterpret_cast<const uint8_t*>(clip_v) + (size_t)s0 * (size_t)ld_clip * sizeof(T);
+    for (int l = 0; l < L; l += ATT_BULK_CLIPS) {
+      const uint32_t n = (uint32_t)min(ATT_BULK_CLIPS, L - l);
+      bulk_load_1d(smem_u32(sproj) + l * prow_b, psrc + (size_t)l * prow_b, n * prow_b, bar_p);
+    }
+    for (int l = 0; l < L; l += ATT_BULK_CLIPS) {
+      const uint32_t n = (uint32_t)min(ATT_BULK_CLIPS, L - l);
+      bulk_load_1d(smem_u32(sclip) + l * crow_b, csrc + (size_t)l * crow_b, n * crow_b, bar_c);
+    }
+  }
+  float qv[16], av[16];
+#pragma unroll
+  for (int m = 0; m < 4; ++m) {
+    const float4 t = __ldg(reinterpret_cast<const float4*>(q + (long long)r * HID + 128 * m + 4 * lane));
+    const float4 a = __ldg(reinterpret_cast<const float4*>(alpha + 128 * m + 4 * lane));
+    qv[4 * m] = t.x; qv[4 * m + 1] = t.y; qv[4 * m + 2] = t.z; qv[4 * m + 3] = t.w;
+    av[4 * m] = -2.f * a.x; av[4 * m + 1] = -2.f * a.y; av[4 * m + 2] = -2.f * a.z; av[4 * m + 3] = -2.f * a.w;
+  }
+  __syncthreads();  // barrier init visible to every thread
+  mbar_wait(bar_p, 0);
+  for (int l = warp; l < L; l += ATT_THREADS / 32) {
+    float s = 0.f;
+    const T* prow = sproj + (size_t)l * HID;
+#pragma unroll
+    for (int m = 0; m < 4; ++m) {
+      float p0, p1, p2, p3;
+      if (BF16) {
+        const uint2 u = *reinterpret_cast<const uint2*>(reinterpret_cast<const bf16*>(prow) + 128 * m + 4 * lane);
+        const __nv_bfloat162 b0 = *reinterpret_cast<const __nv_bfloat162*>(&u.x);
+        const __nv_bfloat162 b1 = *reinterpret_cast<const __nv_bfloat162*>(&u.y);
+        p0 = __low2float(b0); p1 = __high2float(b0); p2 = __low2float(b1); p3 = __high2float(b1);
+      } else {
+        const float4 t = *reinterpret_cast<const float4*>(reinterpret_cast<const float*>(prow) + 128 * m + 4 * lane);
+        p0 = t.x; p1 = t.y; p2 = t.z; p3 = t.w;
+      }
+      s = fmaf(av[4 * m], rcp_fast(fmaf(p0, qv[4 * m], 1.0f)), s);
+      s = fmaf(av[4 * m + 1], rcp_fast(fmaf(p1, qv[4 * m + 1], 1.0f)), s);
+      s = fmaf(av[4 * m + 2], rcp_fast(fmaf(p2, qv[4 * m + 2], 1.0f)), s);
+      s = fmaf(av[4 * m + 3], rcp_fast(fmaf(p3, qv[4 * m + 3], 1.0f)), s);
+    }
+    s = warp_sum(s);
+    if (lane == 0) sc[l] = s;
+  }
+  __syncthreads();
+  float mx = -INFINITY;
+  for (int l = lane; l < L; l += 32) mx = fmaxf(mx, sc[l]);
+  mx = warp_max(mx);
+  float sum = 0.f;
+  for (int l = lane; l < L; l += 32) sum += expf(sc[l] - mx);
+  sum = warp_sum(sum);
+  __syncthreads();
+  const float inv = 1.0f / sum;
+  for (int l = threadIdx.x; l < L; l += ATT_THREADS) sc[l] = expf(sc[l] - mx) * inv;
+  __syncthreads();
+  mbar_wait(bar_c, 0);
+  if (BF16) {
+    const int grp = threadIdx.x >> 6, t = threadIdx.x & 63;
+    float acc[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) acc[i] = 0.f;
+    const bf16* cbase = reinterpret_cast<const bf16*>(sclip) + 8 * t;
+    for (int l = grp; l < L; l += ATT_THREADS / 64) {
+      const uint4 u = *reinterpret_cast<const uint4*>(cbase + (size_t)l * CLIP_ROW);
+      const float w = sc[l];
+      const __nv_bfloat162* b = reinterpret_cast<const __nv_bfloat162*>(&u);
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        acc[2 * i] = fmaf(w, __low2float(b[i]), acc[2 * i]);
+        acc[2 * i + 1] = fmaf(w, __high2float(b[i]), acc[2 * i + 1]);
+      }
+    }
+#pragma unroll
+    for (int i = 0; i < 8; ++i) red[grp][8 * t + i] = acc[i];
+  } else {
+    const int grp = threadIdx.x >> 7, t = threadIdx.x & 127;
+    float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (t < ECHR_VIDEO_DIM / 4) {
+      const float* cbase = reinterpret_cast<const float*>(sclip) + 4 * t;
+      for (int l = grp; l < L; l += ATT_THREADS / 128) {
+        const float4 c = *reinterpret_cast<const float4*>(cbase + (size_t)l * CLIP_ROW);
+        const float w = sc[l];
+        acc.x = fmaf(w, c.x, acc.x); acc.y = fmaf(w, c.y, acc.y);
+        acc.z = fmaf(w, c.z, acc.z); acc.w = fmaf(w, c.w, acc.w);
+      }
+    }
+    *reinterpret_cast<float4*>(&red[grp][4 * t]) = acc;
+  }
+  __syncthreads();
+  for (int c = threadIdx.x; c < ECHR_VIDEO_DIM; c += ATT_THREADS) {
+    float v = 0.f;
+#pragma unroll
+    for (int g = 0; g < (BF16 ? ATT_THREADS / 64 : ATT_THREADS / 128); ++g) v += red[g][c];
+    if (out_f32 != nullptr) out_f32[(long long)r * ECHR_VIDEO_DIM + c] = v;
+    if (out_hi != nullptr) {
+      bf16 h, l2;
+      split_bf16(v, h, l2);
+      out_hi[(long long)r * ld_bf + c] = h;
+      if (out_lo != nullptr) out_lo[(long long)r * ld_bf + c] = l2;
+    }
+  }
+  trace_end(trace, trace_slot);
+}
+
+// max_len: largest window of the launch (0 = unknown).  The staged kernel (one CTA per SM: it owns
+// ~200 KB of shared memory) is used when every window fits and the launch is a single wave
+// (rows <= 148); beyond that the streaming kernel wins because several of its CTAs share an SM and
+// it can co-reside with the concurrent logit GEMM of the decode graph (measured: profiles/).
+// ECHR_ATT_STAGED=1 / ECHR_ATT_STREAM=1 force one or the other.
 cudaError_t launch_attention(const float* q, const void* proj, const void* clip, int64_t ld_clip,
                              int clip_bf16, const float* alpha, const int32_t* row_start,
                              const int32_t* row_len, int64_t rows, float* out_f32, bf16* out_hi,
-                             bf16* out_lo, int64_t ld_bf, cudaStream_t st) {
+                             bf16* out_lo, int64_t ld_bf, cudaStream_t st, int max_len, unsigned long long* trace,
+                             int trace_slot) {
   if (rows == 0) return cudaSuccess;
-  if (clip_bf16)
-    attention_kernel<true><<<(int)rows, ATT_THREADS, 0, st>>>(q, proj, clip, ld_clip, alpha, row_start,
-                                                              row_len, out_f32, out_hi, out_lo, ld_bf);
-  else
-    attention_kernel<false><<<(int)rows, ATT_THREADS, 0, st>>>(q, proj, clip, ld_clip, alpha, row_start,
-                                                               row_len, out_f32, out_hi, out_lo, ld_bf);
+  cudaError_t e;
+  const size_t el = clip_bf16 ? 2 : 4;
+  const size_t clip_row = clip_bf16 ? CLIP_PAD : ECHR_VIDEO_DIM;
+  const size_t stage = (size_t)max_len * (HID + clip_row) * el;
+  // staged rows must be contiguous: fp32 clips have ld 500, bf16 clips ld 512
+  const bool fits = max_len > 0 && max_len <= ATT_MAX_L && stage <= ATT_STAGE_BYTES && (size_t)ld_clip == clip_row;
+  const bool staged = fits && getenv("ECHR_ATT_STREAM") == nullptr && (rows <= 148 || getenv("ECHR_ATT_STAGED") != nullptr);
+  if (staged) {
+    static size_t attr[2] = {0, 0};
+    if (stage > attr[clip_bf16 ? 1 : 0]) {
+      e = clip_bf16 ? cudaFuncSetAttribute(attention_staged_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, ATT_STAGE_BYTES)
+                    : cudaFuncSetAttribute(attention_staged_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, ATT_STAGE_BYTES);
+      if (e != cudaSuccess) return e;
+      attr[clip_bf16 ? 1 : 0] = ATT_STAGE_BYTES;
+    }
+    if (clip_bf16)
+      e = launch_pdl(attention_staged_kernel<true>, dim3((unsigned)rows), dim3(ATT_THREADS), stage, st, q, proj, clip,
+                     (long long)ld_clip, alpha, row_start, row_len, out_f32, out_hi, out_lo, (long long)ld_bf, max_len, trace, trace_slot);
+    else
+      e = launch_pdl(attention_staged_kernel<false>, dim3((unsigned)rows), dim3(ATT_THREADS), stage, st, q, proj, clip,
+                     (long long)ld_clip, alpha, row_start, row_len, out_f32, out_hi, out_lo, (long long)ld_bf, max_len, trace, trace_slot);
+  } else if (clip_bf16) {
+    e = launch_pdl(attention_kernel<true>, dim3((unsigned)rows), dim3(ATT_THREADS), 0, st, q, proj, clip,
+                   (long long)ld_clip, alpha, row_start, row_len, out_f32, out_hi, out_lo, (long long)ld_bf, trace, trace_slot);
+  } else {
+    e = launch_pdl(attention_kernel<false>, dim3((unsigned)rows), dim3(ATT_THREADS), 0, st, q, proj, clip,
+                   (long long)ld_clip, alpha, row_start, row_len, out_f32, out_hi, out_lo, (long long)ld_bf, trace, trace_slot);
+  }
   count_launch();
-  return cudaGetLastError();
+  return e;
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -287,9 +471,13 @@ __global__ void __launch_bounds__(FIN_WARPS * 32)
 finalize_greedy_kernel(int rows, int n_tiles, int step, int seq_len, const float* __restrict__ partial,
                        const bf16* __restrict__ embed, long long embed_plane, bf16* __restrict__ act_next,
                        long long act_plane, int planes, int32_t* __restrict__ unfinished,
-                       int32_t* __restrict__ tokens, float* __restrict__ logp) {
+                       int32_t* __restrict__ tokens, float* __restrict__ logp, unsigned long long* trace,
+                       int trace_slot) {
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int r = blockIdx.x * FIN_WARPS + warp;
+  trace_begin(trace, trace_slot);
+  pdl_trigger();
+  pdl_wait();
   if (r >= rows) return;
   const RowStat s = merge_row_stats<1>(partial + (long long)r * n_tiles * LogitRec<1>::WORDS, n_tiles, lane);
   const int tok = s.max_idx;
@@ -301,20 +489,23 @@ finalize_greedy_kernel(int rows, int n_tiles, int step, int seq_len, const float
   }
   if (step + 1 < seq_len)
     copy_embed_row(embed, embed_plane, tok, act_next + (long long)r * ACT_LD, act_plane, planes, lane);
+  __syncthreads();
+  trace_end(trace, trace_slot);
 }
 
-cudaError_t launch_finalize_greedy(const echr_batch* b, int step, int32_t* tokens, float* logp,
+cudaError_t launch_finalize_greedy(echr_batch* b, int step, int32_t* tokens, float* logp,
                                    cudaStream_t st) {
   const int rows = b->n_events;
   if (rows == 0) return cudaSuccess;
   const echr_model* m = b->model;
   const int n_tiles = ((m->V1 + 127) / 128) * (128 / LOGIT_GROUP);
   const PlaneMat& nxt = b->act[(step + 1) & 1];
-  finalize_greedy_kernel<<<(rows + FIN_WARPS - 1) / FIN_WARPS, FIN_WARPS * 32, 0, st>>>(
-      rows, n_tiles, step, m->cfg.seq_length, b->partial, m->embed.p, m->embed.plane_stride(), nxt.p,
-      nxt.plane_stride(), (int)nxt.planes, b->unfinished, tokens, logp);
+  cudaError_t e = launch_pdl(finalize_greedy_kernel, dim3((rows + FIN_WARPS - 1) / FIN_WARPS), dim3(FIN_WARPS * 32), 0,
+                             st, rows, n_tiles, step, m->cfg.seq_length, b->partial, m->embed.p,
+                             (long long)m->embed.plane_stride(), nxt.p, (long long)nxt.plane_stride(),
+                             (int)nxt.planes, b->unfinished, tokens, logp, trace_ptr(b), trace_next(b, 4));
   count_launch();
-  return cudaGetLastError();
+  return e;
 }
 
 // Teacher-forced step (OldModel_NEW.py:98-130): the logit GEMM stored raw logits into

@@ -51,6 +51,25 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
   }
 }
 
+// ---------------------------------------------------------------- programmatic dependent launch
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+
+// ---------------------------------------------------------------- kernel timeline trace (debug aid)
+// trace[2*slot] = earliest CTA start, trace[2*slot+1] = ~(latest CTA end), in globaltimer nanoseconds
+// (both kept with atomicMin so that one 0xff memset resets the buffer).
+__device__ __forceinline__ unsigned long long global_timer_ns() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
+__device__ __forceinline__ void trace_begin(unsigned long long* trace, int slot) {
+  if (trace != nullptr && threadIdx.x == 0) atomicMin(trace + 2 * slot, global_timer_ns());
+}
+__device__ __forceinline__ void trace_end(unsigned long long* trace, int slot) {
+  if (trace != nullptr && threadIdx.x == 0) atomicMin(trace + 2 * slot + 1, ~global_timer_ns());
+}
+
 // ---------------------------------------------------------------- fences
 __device__ __forceinline__ void fence_proxy_async_smem() {
   asm volatile("fence.proxy.async.shared::cta;" ::: "memory");

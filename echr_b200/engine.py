@@ -213,5 +213,18 @@ class Engine(object):
                   "echr_time_step_kernels")
         return dict(zip(("h2att", "attention", "lstm_gates", "logit", "finalize"), [float(x) for x in ms]))
 
+    def trace(self):
+        """Timeline of the last decode graph replay (needs ECHR_TRACE=1 at capture time):
+        list of (kind, start_us, end_us) relative to the first kernel's start."""
+        n = 1024
+        st, en, kd = np.zeros(n, np.int64), np.zeros(n, np.int64), np.zeros(n, np.int32)
+        with torch.cuda.device(self.device):
+            k = self.lib.echr_trace_read(self._batch, st.ctypes.data, en.ctypes.data, kd.ctypes.data, n)
+        names = ("h2att", "attention", "lstm_gates", "logit", "finalize", "other")
+        if k <= 0:
+            return []
+        t0 = int(st[:k].min())
+        return [(names[int(kd[i])], (int(st[i]) - t0) / 1e3, (int(en[i]) - t0) / 1e3) for i in range(k)]
+
     def launch_count(self, reset=False):
         return int(self.lib.echr_launch_count(1 if reset else 0))

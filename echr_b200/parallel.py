@@ -28,26 +28,38 @@ def shard_videos(event_counts, rank, world):
     return bounds[rank], bounds[rank + 1]
 
 
-def gather_tokens(tokens, group=None):
+def exchange_counts(n_local, device, group=None):
+    """Row count of every rank (one small all_gather + host read; do it once per batch shape)."""
+    if not dist.is_available() or not dist.is_initialized() or dist.get_world_size(group) == 1:
+        return [int(n_local)]
+    world = dist.get_world_size(group)
+    n = torch.tensor([int(n_local)], dtype=torch.int64, device=device)
+    counts = [torch.zeros_like(n) for _ in range(world)]
+    dist.all_gather(counts, n, group=group)
+    return [int(c.item()) for c in counts]
+
+
+def gather_tokens(tokens, group=None, counts=None):
     """tokens [n_local, S] (any integer/float dtype) -> [sum n_local, S] on every rank, in rank
-    order.  Row counts may differ per rank: they are exchanged first and the payload is padded to
-    the largest shard (one small + one payload collective)."""
+    order.  Row counts may differ per rank: pass `counts` (from exchange_counts) to skip the count
+    exchange and its host sync; the payload is padded to the largest shard and moved by ONE
+    all_gather_into_tensor."""
     if not dist.is_available() or not dist.is_initialized():
         return tokens
     world = dist.get_world_size(group)
     if world == 1:
         return tokens
-    n = torch.tensor([tokens.shape[0]], dtype=torch.int64, device=tokens.device)
-    counts = [torch.zeros_like(n) for _ in range(world)]
-    dist.all_gather(counts, n, group=group)
-    counts = [int(c.item()) for c in counts]
+    if counts is None:
+        counts = exchange_counts(tokens.shape[0], tokens.device, group)
     mx = max(counts)
     pad = tokens
     if tokens.shape[0] < mx:
         pad = torch.cat([tokens, tokens.new_zeros((mx - tokens.shape[0],) + tuple(tokens.shape[1:]))], 0)
-    out = [torch.empty_like(pad) for _ in range(world)]
-    dist.all_gather(out, pad.contiguous(), group=group)
-    return torch.cat([o[:c] for o, c in zip(out, counts)], 0)
+    out = torch.empty((world * mx,) + tuple(tokens.shape[1:]), dtype=tokens.dtype, device=tokens.device)
+    dist.all_gather_into_tensor(out, pad.contiguous(), group=group)
+    if all(c == mx for c in counts):
+        return out
+    return torch.cat([out[r * mx:r * mx + c] for r, c in enumerate(counts)], 0)
 
 
 def caption_sharded(model, videos, beam_size=1, group=None):

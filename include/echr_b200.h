@@ -111,7 +111,7 @@ ECHR_API int echr_split_bf16(const float* src, int64_t rows, int64_t cols, int64
  * Replaces every nn.Linear on the path (models/MA_attention_8_NEW.py:29,93-96;
  * models/OldModel_NEW.py:51,372-374).  A and W are bf16 plane stacks ([planes][rows][ld]):
  * planes=1 is the plain bf16 operand, planes=2 adds the low-order plane (fp32-grade product).
- * k must be a multiple of 64 (pad with zeros), k <= 2048.  act: 0 none, 1 tanh.
+ * k must be a multiple of 64 (pad with zeros), k <= 2048.  act: 0 none, 1 tanh, 2 exp(2*clamp(x,+-40)).
  * Outputs: out_f32 (may be NULL) and/or bf16 planes out_hi/out_lo (may be NULL). */
 ECHR_API int echr_gemm_planes(const void* a, int64_t m, int64_t k, int64_t a_ld, int a_planes,
                      int64_t a_plane_stride, const void* w, int64_t n, int64_t w_ld, int w_planes,
@@ -121,13 +121,18 @@ ECHR_API int echr_gemm_planes(const void* a, int64_t m, int64_t k, int64_t a_ld,
 
 /* One late-fusion attention step (models/OldModel_NEW.py:376-401 with ctx2att hoisted):
  * for each row r: window = clips [row_start[r], row_start[r]+row_len[r]) of proj/clip;
- * score_l = alpha . tanh(proj[l] + q[r]); att[r] = sum_l softmax(score)_l * clip[l].
- * proj [n_clips,512], clip [n_clips, ld_clip] are fp32 (clip_bf16=0) or bf16 (clip_bf16=1);
- * q fp32 [rows,512]; out_f32 [rows,500] (may be NULL); out_hi/out_lo bf16 [rows, ld_bf] (may be NULL). */
-ECHR_API int echr_attention_step(const float* q, const void* proj, const void* clip, int64_t ld_clip,
+ * score_l = alpha . tanh(P[l] + q[r]); att[r] = sum_l softmax(score)_l * clip[l].
+ * The projected operands come in the exponential domain the GEMM epilogues write (act = 2):
+ * proj_exp [n_clips,512] = e^{2P} and q_exp [rows,512] = e^{2q}, exponents clamped to +-80; with them
+ * tanh(P+q) = 1 - 2/(e^{2P} e^{2q} + 1) costs one reciprocal per element.
+ * proj_exp and clip [n_clips, ld_clip] are fp32 (clip_bf16=0) or bf16 (clip_bf16=1); q_exp fp32;
+ * out_f32 [rows,500] (may be NULL); out_hi/out_lo bf16 [rows, ld_bf] (may be NULL).
+ * max_len: the largest row_len of the call if the caller knows it (lets small launches stage whole
+ * windows in shared memory through the bulk-copy engine), 0 if unknown. */
+ECHR_API int echr_attention_step(const float* q_exp, const void* proj_exp, const void* clip, int64_t ld_clip,
                         int clip_bf16, const float* alpha, const int32_t* row_start,
                         const int32_t* row_len, int64_t rows, float* out_f32, void* out_hi,
-                        void* out_lo, int64_t ld_bf, void* stream);
+                        void* out_lo, int64_t ld_bf, int max_len, void* stream);
 
 /* ---- model: packed weights --------------------------------------------------------------- */
 /* Packs the checkpoint into kernel layouts (bf16 planes, gate-interleaved LSTM rows, fused biases).
@@ -179,6 +184,13 @@ ECHR_API int echr_caption_host(echr_batch_t* batch, const echr_batch_desc_t* des
  * (host_ms[5] = h2att GEMM, fused attention, LSTM gate GEMM, logit GEMM, finalize), from CUDA
  * events on `stream` around `iters` back-to-back launches.  Needs a decoded batch; synchronises. */
 ECHR_API int echr_time_step_kernels(echr_batch_t* batch, int beam, int iters, float* host_ms, void* stream);
+
+/* Debug aid: timeline of the last decode-graph replay when the graph was captured with ECHR_TRACE=1 in
+ * the environment: per kernel its kind (0 h2att GEMM, 1 attention, 2 gate GEMM, 3 logit GEMM,
+ * 4 finalize), earliest CTA start and latest CTA end (globaltimer ns).  Synchronises the device;
+ * returns the number of entries written (0 when tracing is off). */
+ECHR_API int echr_trace_read(echr_batch_t* batch, int64_t* host_start_ns, int64_t* host_end_ns, int32_t* host_kind,
+                    int max_entries);
 
 /* Number of kernel launches this library issued since the last call (graph replays count their
  * kernel nodes); used by bench.py's `gpu_launches`. */

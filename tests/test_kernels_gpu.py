@@ -12,8 +12,9 @@ torch.set_grad_enabled(False)
 DEV = "cuda:0"
 
 
+@pytest.mark.parametrize("staged", [0, 1])
 @pytest.mark.parametrize("clip_bf16", [0, 1])
-def test_attention_step_matches_oracle(clip_bf16):
+def test_attention_step_matches_oracle(clip_bf16, staged):
     lib = _lib.load()
     sd = helpers.state_dict("bf16w" if clip_bf16 else "fp32")
     a = "lm_model.core.attention."
@@ -24,6 +25,8 @@ def test_attention_step_matches_oracle(clip_bf16):
         c3d = c3d.bfloat16().float()
     lens = [1, 2, 7, 33, 64, 100, 257, 300, 5]
     starts = [0, 299 - 1, 10, 200, 100, 150, 20, 0, 295]
+    if staged:  # windows that fit in shared memory: the bulk-copy staged kernel
+        lens = [1, 2, 7, 33, 50, 16, 17, 48, 5]
     n = len(lens)
     h = torch.randn(n, 512, generator=g) * 0.3
     lmax = max(lens)
@@ -34,7 +37,8 @@ def test_attention_step_matches_oracle(clip_bf16):
         mask[i, :l] = 1
     want = O.attend(sd, h, clip, mask)
     proj = torch.nn.functional.linear(c3d, sd[a + "ctx2att.weight"], sd[a + "ctx2att.bias"])
-    q = torch.nn.functional.linear(h, sd[a + "h2att.weight"], sd[a + "h2att.bias"]).to(DEV)
+    q = torch.exp(2 * torch.nn.functional.linear(h, sd[a + "h2att.weight"], sd[a + "h2att.bias"])).to(DEV)
+    proj = torch.exp(2 * proj)  # the kernels take e^{2P}, e^{2q} (what the GEMM epilogues write)
     alpha = sd[a + "alpha_net.weight"].reshape(-1).contiguous().to(DEV)
     if clip_bf16:
         clip_d = torch.zeros(T, 512, dtype=torch.bfloat16, device=DEV)
@@ -50,7 +54,7 @@ def test_attention_step_matches_oracle(clip_bf16):
     lo = torch.zeros(n, 512, dtype=torch.bfloat16, device=DEV)
     _lib.check(lib.echr_attention_step(q.data_ptr(), proj_d.data_ptr(), clip_d.data_ptr(), ld, clip_bf16,
                                        alpha.data_ptr(), rs.data_ptr(), rl.data_ptr(), n, out.data_ptr(),
-                                       hi.data_ptr(), lo.data_ptr(), 512,
+                                       hi.data_ptr(), lo.data_ptr(), 512, max(lens) if staged else 0,
                                        torch.cuda.current_stream().cuda_stream), "attention")
     torch.cuda.synchronize()
     err = (out.cpu() - want).abs().max().item()
