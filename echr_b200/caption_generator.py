@@ -10,6 +10,9 @@ The nn.Parameters here are only the checkpoint container (`load_state_dict(stric
 reference `cg_model` works); all arithmetic runs in libechr_b200.so.  Additive API:
 `caption_batch(videos, beam_size)` for many videos per call and `beam_size` in `forward(mode='eval')`.
 """
+import weakref
+
+import numpy as np
 import torch
 from torch import nn
 
@@ -37,6 +40,31 @@ class MA_Attention8(nn.Module):
         self.enc_attn = _EncAttn(opt)
         self.output_dim, self.use_posit, self.d_pos_vec, self.fST_type = opt.d_o, opt.use_posit, opt.d_pos_vec, "fST0"
 
+    def forward(self, feats, soi_select_list):
+        """feats [N,1012] (pooled clip feature | proposal state), soi_select_list [[s,e),...] -> [N,512]
+        (models/MA_attention_8_NEW.py:35-49), computed by the engine's relation-encoder kernels."""
+        return _owner_engine(self).relation_encode(feats, [list(s) for s in soi_select_list])
+
+    # Host-side helpers of the reference kept for callers that use them directly (MA:51-79, numpy
+    # float64 like the reference; the engine evaluates the same formulas on the device in fp64).
+    @staticmethod
+    def extract_position_matrix(bbox, nongt_dim=None):
+        bbox = np.asarray(bbox)
+        start, end = bbox[:, 0:1].astype(np.float64), bbox[:, 1:2].astype(np.float64)
+        center = 0.5 * (start + end)
+        length = (bbox[:, 1:2] - bbox[:, 0:1]).astype(np.float32)
+        delta_center = np.maximum(np.abs((center - center.T) / length), 1e-3)
+        delta_length = np.log(length.T / length)
+        return np.stack([delta_center, delta_length], axis=2)
+
+    @staticmethod
+    def extract_position_embedding(position_mat, feat_dim, wave_length=10000):
+        k = np.arange(feat_dim // 4, dtype=np.float64)
+        div = np.power(float(wave_length), (4.0 / feat_dim) * k)
+        z = (100.0 * position_mat)[..., None] / div
+        emb = np.concatenate([np.sin(z), np.cos(z)], axis=3)
+        return emb.reshape(position_mat.shape[0], position_mat.shape[1], feat_dim)
+
 
 class _Attention(nn.Module):  # OldModel_NEW.py:366-374
     def __init__(self, opt):
@@ -57,15 +85,77 @@ class _ThreeStreamCore(nn.Module):  # OldModel_NEW.py:762-788
         self.attention = _Attention(opt)
 
 
+def _owner_engine(module):
+    ref = getattr(module, "_owner", None)
+    owner = ref() if ref is not None else None
+    if owner is None:
+        raise RuntimeError("this sub-module runs on the engine of the CaptionGenerator that owns it; "
+                           "construct echr_b200.CaptionGenerator(opt) and use its .fusion_model / .lm_model")
+    return owner.engine
+
+
+def _clip_lengths(clip_mask):
+    """The reference's clip_mask (CaptionGenerator.py:140-167) marks a prefix of each row."""
+    m = clip_mask.detach().to("cpu") != 0
+    lens = m.sum(1).to(torch.int64)
+    pos = torch.arange(m.shape[1]).unsqueeze(0)
+    if not bool(((pos < lens.unsqueeze(1)) == m).all()) or int(lens.min()) < 1:
+        raise ValueError("clip_mask must mark a non-empty prefix of every row")
+    return lens.tolist()
+
+
 class ThreestreamModel(nn.Module):
     def __init__(self, opt):
         super().__init__()
         _config.validate(opt)
         self.opt = opt
         self.vocab_size, self.seq_length = opt.CG_vocab_size, opt.CG_seq_length
+        self.num_layers, self.rnn_size = opt.CG_num_layers, opt.CG_rnn_size
         self.embed = nn.Embedding(self.vocab_size + 1, opt.CG_input_encoding_size)
         self.logit = nn.Linear(3 * opt.CG_rnn_size, self.vocab_size + 1)
         self.core = _ThreeStreamCore(opt)
+
+    def init_hidden(self, video, event, clip):
+        """CG_init_feats_type == '' -> zero state (OldModel_NEW.py:72-78)."""
+        n = event.shape[0]
+        z = torch.zeros(self.num_layers, n, self.rnn_size, dtype=torch.float32, device=event.device)
+        return z, z.clone()
+
+    def forward(self, video, event, clip, clip_mask, seq):
+        """Teacher-forced log-probs [N, steps, V+1] (OldModel_NEW.py:98-130), forward only."""
+        with torch.no_grad():
+            eng = _owner_engine(self)
+            eng.set_context(video, event, clip, _clip_lengths(clip_mask))
+            cols = seq.shape[1]
+            for i in range(1, cols - 1):
+                if int(seq[:, i].sum()) == 0:
+                    cols = i + 1
+                    break
+            return eng.teacher_forced(seq[:, :cols])
+
+    def sample(self, video, event, clip, clip_mask, opt={}):
+        """Greedy (default) or beam decode from ready-made contexts (OldModel_NEW.py:139-187).
+        opt: {'sample_max': 1, 'beam_size': k}; multinomial sampling (sample_max=0) is only used by the
+        reference's dead RL branch and is not implemented."""
+        if not opt.get("sample_max", 1):
+            raise ValueError("echr_b200 implements sample_max=1 (greedy / beam) only")
+        beam = int(opt.get("beam_size", 1))
+        with torch.no_grad():
+            eng = _owner_engine(self)
+            eng.set_context(video, event, clip, _clip_lengths(clip_mask), beam=max(1, beam))
+            if beam > 1:
+                tok, lp, score = eng.decode_beam(beam)
+                return tok.long(), lp
+            tok, lp = eng.decode_greedy()
+            return trim_greedy(tok, lp)
+
+    def get_logprobs_state(self, it, video, event, clip, clip_mask, state):
+        """One step with explicit state (OldModel_NEW.py:133-137): returns (logprobs, (h, c))."""
+        with torch.no_grad():
+            eng = _owner_engine(self)
+            eng.set_context(video, event, clip, _clip_lengths(clip_mask))
+            lp, h, c = eng.decode_step(it, state[0], state[1])
+            return lp, (h, c)
 
 
 def setup_lm(opt):
@@ -98,6 +188,8 @@ class CaptionGenerator(nn.Module):
         self.precision = precision
         self.fusion_model = setup_fusion(opt)
         self.lm_model = setup_lm(opt)
+        for sub in (self.fusion_model, self.lm_model):  # the sub-modules run on this module's engine
+            object.__setattr__(sub, "_owner", weakref.ref(self))
         self._engine = None
         self.eval()
 

@@ -404,9 +404,10 @@ extern "C" int echr_batch_destroy(echr_batch_t* b) {
   return ECHR_OK;
 }
 
-extern "C" int echr_batch_set_inputs(echr_batch_t* b, const echr_batch_desc_t* d, const float* c3d,
-                                     const float* tap, const float* lda, int on_host, void* stream) {
-  ECHR_REQUIRE(b && d && c3d && tap && lda, "echr_batch_set_inputs: null argument");
+// Validates the batch description, derives the per-event / per-video index arrays and uploads them.
+// `check_clips` = false is used by the entry points that bring their own (virtual) clip table.
+static int stage_desc(echr_batch_t* b, const echr_batch_desc_t* d, bool check_clips, cudaStream_t st) {
+  ECHR_REQUIRE(b && d, "echr_batch_set_inputs: null argument");
   ECHR_REQUIRE(d->n_videos >= 1 && d->n_videos <= b->cap.max_videos, "echr_batch_set_inputs: n_videos=%d out of range (capacity %lld)", d->n_videos, (long long)b->cap.max_videos);
   ECHR_REQUIRE(d->n_events >= 0 && d->n_events <= b->cap.max_events, "echr_batch_set_inputs: n_events=%d exceeds capacity %lld", d->n_events, (long long)b->cap.max_events);
   ECHR_REQUIRE(d->host_clip_offsets && (d->n_events == 0 || (d->host_event_video && d->host_event_start && d->host_event_end && d->host_event_ind)),
@@ -416,8 +417,7 @@ extern "C" int echr_batch_set_inputs(echr_batch_t* b, const echr_batch_desc_t* d
   for (int v = 0; v < d->n_videos; ++v)
     ECHR_REQUIRE(off[v + 1] > off[v], "echr_batch_set_inputs: video %d has no clips", v);
   const int n_clips = off[d->n_videos];
-  ECHR_REQUIRE(n_clips <= b->cap.max_clips, "echr_batch_set_inputs: %d clips exceed capacity %lld", n_clips, (long long)b->cap.max_clips);
-  cudaStream_t st = (cudaStream_t)stream;
+  ECHR_REQUIRE(!check_clips || n_clips <= b->cap.max_clips, "echr_batch_set_inputs: %d clips exceed capacity %lld", n_clips, (long long)b->cap.max_clips);
   // the pinned staging buffer may still be in flight from the previous call on this stream
   ECHR_CUDA(cudaStreamSynchronize(st));
   const int64_t E = b->cap.max_events;
@@ -468,6 +468,17 @@ extern "C" int echr_batch_set_inputs(echr_batch_t* b, const echr_batch_desc_t* d
   b->encoded = false;
   ECHR_CUDA(cudaMemcpyAsync(b->ev_video, hs, sizeof(int32_t) * ((size_t)7 * E + 2 * b->cap.max_videos),
                             cudaMemcpyHostToDevice, st));
+  return ECHR_OK;
+}
+
+extern "C" int echr_batch_set_inputs(echr_batch_t* b, const echr_batch_desc_t* d, const float* c3d,
+                                     const float* tap, const float* lda, int on_host, void* stream) {
+  ECHR_REQUIRE(b && d && c3d && tap && lda, "echr_batch_set_inputs: null argument");
+  cudaStream_t st = (cudaStream_t)stream;
+  ECHR_TRY(stage_desc(b, d, true, st));
+  const int n_clips = b->n_clips;
+  const int64_t E = b->cap.max_events;
+  const int32_t* hs = b->host_stage;
   const cudaMemcpyKind kind = on_host ? cudaMemcpyHostToDevice : cudaMemcpyDeviceToDevice;
   ECHR_CUDA(cudaMemcpyAsync(b->c3d, c3d, sizeof(float) * (size_t)n_clips * ECHR_VIDEO_DIM, kind, st));
   // only tap_feats[ind] is ever read (CaptionGenerator.py:121): gather one row per event
@@ -487,28 +498,27 @@ extern "C" int echr_batch_set_inputs(echr_batch_t* b, const echr_batch_desc_t* d
 // =============================================================================================
 // Encode: context prologue + relation encoder
 // =============================================================================================
-extern "C" int echr_encode(echr_batch_t* b, void* stream) {
-  ECHR_REQUIRE(b, "echr_encode: null batch");
-  ECHR_REQUIRE(b->n_videos > 0, "echr_encode: no inputs set");
-  cudaStream_t st = (cudaStream_t)stream;
+// clip planes + hoisted ctx2att projection over every clip of the batch (OldModel_NEW.py:381,
+// computed once instead of once per decode step); the table holds e^{2P} (see kernels_step.cu)
+static int encode_clips(echr_batch_t* b, cudaStream_t st) {
   const echr_model* m = b->model;
   const int at = m->cfg.a_terms, wt = m->cfg.w_terms;
-  // clip planes + hoisted ctx2att projection over every clip of the batch (OldModel_NEW.py:381,
-  // computed once instead of once per decode step)
   ECHR_CUDA(launch_split(b->c3d, b->n_clips, ECHR_VIDEO_DIM, ECHR_VIDEO_DIM, b->clip_pl.plane(0),
                          at > 1 ? b->clip_pl.plane(1) : nullptr, CLIP_PAD, CLIP_PAD, st));
-  {
-    GemmSpec s;
-    s.A = &b->clip_pl; s.M = b->n_clips; s.W = &m->w_ctx2att; s.N = HID; s.K = CLIP_PAD;
-    s.bias = m->b_ctx2att;
-    s.act = ACT_EXP2X;  // the table holds e^{2P} (see kernels_step.cu)
-    if (m->cfg.clip_bf16) { s.out_hi = b->proj_bf; s.ld_bf = HID; }
-    else { s.out_f32 = b->proj_f32; s.ld_f32 = HID; }
-    ECHR_TRY(run_gemm(&s, 1, at, wt, 128, EPI_STORE, 1, st, "ctx2att"));
-  }
-  if (b->n_events == 0) { b->encoded = true; return ECHR_OK; }
-  // event features -> embedding -> query | key | value*W_out
-  ECHR_CUDA(launch_event_feats(b, st));
+  GemmSpec s;
+  s.A = &b->clip_pl; s.M = b->n_clips; s.W = &m->w_ctx2att; s.N = HID; s.K = CLIP_PAD;
+  s.bias = m->b_ctx2att;
+  s.act = ACT_EXP2X;
+  if (m->cfg.clip_bf16) { s.out_hi = b->proj_bf; s.ld_bf = HID; }
+  else { s.out_f32 = b->proj_f32; s.ld_f32 = HID; }
+  return run_gemm(&s, 1, at, wt, 128, EPI_STORE, 1, st, "ctx2att");
+}
+
+// event relation encoder from the event feature planes (MA:35-177): embedding -> query | key |
+// value*W_out, pair position embedding -> fc1 + tanh -> fc2, multi-head relation attention
+static int encode_relation(echr_batch_t* b, cudaStream_t st) {
+  const echr_model* m = b->model;
+  const int at = m->cfg.a_terms, wt = m->cfg.w_terms;
   {
     GemmSpec s;
     s.A = &b->feat_pl; s.M = b->n_events; s.W = &m->w_event_emb; s.N = HID; s.K = FEAT_PAD;
@@ -522,7 +532,6 @@ extern "C" int echr_encode(echr_batch_t* b, void* stream) {
     s.bias = m->b_qky; s.out_f32 = b->qky; s.ld_f32 = 3 * HID;
     ECHR_TRY(run_gemm(&s, 1, at, wt, 128, EPI_STORE, 1, st, "query_key_value"));
   }
-  // pair position embedding -> fc1 + tanh -> fc2
   ECHR_CUDA(launch_posemb(b, st));
   {
     GemmSpec s;
@@ -538,6 +547,72 @@ extern "C" int echr_encode(echr_batch_t* b, void* stream) {
     ECHR_TRY(run_gemm(&s, 1, at, wt, 16, EPI_STORE, 1, st, "pair_pos_fc2"));
   }
   ECHR_CUDA(launch_relation_attn(b, st));
+  return ECHR_OK;
+}
+
+extern "C" int echr_encode(echr_batch_t* b, void* stream) {
+  ECHR_REQUIRE(b, "echr_encode: null batch");
+  ECHR_REQUIRE(b->n_videos > 0, "echr_encode: no inputs set");
+  cudaStream_t st = (cudaStream_t)stream;
+  ECHR_TRY(encode_clips(b, st));
+  if (b->n_events > 0) {
+    ECHR_CUDA(launch_event_feats(b, st));
+    ECHR_TRY(encode_relation(b, st));
+  }
+  b->encoded = true;
+  return ECHR_OK;
+}
+
+// MA_Attention8.forward(feats, soi_select_list) on its own (models/MA_attention_8_NEW.py:35-49):
+// feats fp32 device [n,1012] = (pooled clip feature | proposal state) per event, host_soi int32 [n,2]
+// half-open spans of ONE video -> out fp32 device [n,512].
+extern "C" int echr_relation_encode(echr_batch_t* b, const float* feats, const int32_t* host_soi, int n,
+                                    float* out, void* stream) {
+  ECHR_REQUIRE(b && feats && host_soi && out, "echr_relation_encode: null argument");
+  ECHR_REQUIRE(n >= 1 && n <= b->cap.max_events && (long long)n * n <= b->cap.max_pairs,
+               "echr_relation_encode: %d events exceed the batch capacity", n);
+  cudaStream_t st = (cudaStream_t)stream;
+  std::vector<int32_t> ev_video(n, 0), ev_s(n), ev_e(n), ev_ind(n, 0);
+  int32_t T = 1;
+  for (int i = 0; i < n; ++i) {
+    ev_s[i] = host_soi[2 * i];
+    ev_e[i] = host_soi[2 * i + 1];
+    if (ev_e[i] > T) T = ev_e[i];
+  }
+  const int32_t offs[2] = {0, T};
+  echr_batch_desc_t d = {1, n, offs, ev_video.data(), ev_s.data(), ev_e.data(), ev_ind.data()};
+  ECHR_TRY(stage_desc(b, &d, false, st));
+  ECHR_CUDA(launch_split(feats, n, ECHR_VIDEO_DIM + HID, ECHR_VIDEO_DIM + HID, b->feat_pl.plane(0),
+                         b->feat_pl.planes > 1 ? b->feat_pl.plane(1) : nullptr, FEAT_PAD, FEAT_PAD, st));
+  ECHR_TRY(encode_relation(b, st));
+  ECHR_CUDA(cudaMemcpyAsync(out, b->event_ctx, sizeof(float) * (size_t)n * HID, cudaMemcpyDeviceToDevice, st));
+  return ECHR_OK;
+}
+
+// lm_model-level entry (models/OldModel_NEW.py:98,139: forward / sample take ready-made contexts):
+// video fp32 [100], event fp32 [n,512], clip fp32 [n,lmax,500] zero padded, host_clip_len int32 [n] =
+// number of valid clips per event (the reference's clip_mask is a prefix mask).  After this call the
+// decode entry points run on these contexts.
+extern "C" int echr_batch_set_context(echr_batch_t* b, const float* video, const float* event, const float* clip,
+                                      const int32_t* host_clip_len, int n, int lmax, void* stream) {
+  ECHR_REQUIRE(b && video && event && clip && host_clip_len, "echr_batch_set_context: null argument");
+  ECHR_REQUIRE(n >= 1 && n <= b->cap.max_events && lmax >= 1 && (long long)n * lmax <= b->cap.max_clips,
+               "echr_batch_set_context: %d events x %d clips exceed the batch capacity", n, lmax);
+  cudaStream_t st = (cudaStream_t)stream;
+  // one "video" whose clip table is the padded clip tensor itself: event i owns rows [i*lmax, i*lmax+len)
+  std::vector<int32_t> ev_video(n, 0), ev_s(n), ev_e(n), ev_ind(n, 0);
+  for (int i = 0; i < n; ++i) {
+    ECHR_REQUIRE(host_clip_len[i] >= 1 && host_clip_len[i] <= lmax, "echr_batch_set_context: clip_len[%d]=%d out of range", i, host_clip_len[i]);
+    ev_s[i] = i * lmax;
+    ev_e[i] = i * lmax + host_clip_len[i];
+  }
+  const int32_t offs[2] = {0, n * lmax};
+  echr_batch_desc_t d = {1, n, offs, ev_video.data(), ev_s.data(), ev_e.data(), ev_ind.data()};
+  ECHR_TRY(stage_desc(b, &d, true, st));
+  ECHR_CUDA(cudaMemcpyAsync(b->c3d, clip, sizeof(float) * (size_t)n * lmax * ECHR_VIDEO_DIM, cudaMemcpyDeviceToDevice, st));
+  ECHR_CUDA(cudaMemcpyAsync(b->lda, video, sizeof(float) * ECHR_LDA_DIM, cudaMemcpyDeviceToDevice, st));
+  ECHR_CUDA(cudaMemcpyAsync(b->event_ctx, event, sizeof(float) * (size_t)n * HID, cudaMemcpyDeviceToDevice, st));
+  ECHR_TRY(encode_clips(b, st));
   b->encoded = true;
   return ECHR_OK;
 }
@@ -753,6 +828,26 @@ extern "C" int echr_teacher_forced(echr_batch_t* b, const int32_t* seq, int seq_
     ECHR_TRY(enqueue_step(b, rows, t, 1, logprobs + (long long)t * V1, (long long)(seq_cols - 1) * V1, st));
     ECHR_CUDA(launch_finalize_tf(b, t, seq, seq_cols, logprobs, st));
   }
+  return ECHR_OK;
+}
+
+// OldModel.get_logprobs_state (OldModel_NEW.py:133-137) with explicit state: it int32 [n], h_in / c_in
+// fp32 [3,n,512] -> logprobs fp32 [n,V+1], h_out / c_out fp32 [3,n,512].  Contexts come from
+// echr_encode or echr_batch_set_context.  (h passes through the bf16 hi+lo planes: 16 mantissa bits.)
+extern "C" int echr_decode_step(echr_batch_t* b, const int32_t* it, const float* h_in, const float* c_in,
+                                float* logprobs, float* h_out, float* c_out, void* stream) {
+  ECHR_REQUIRE(b && it && h_in && c_in && logprobs && h_out && c_out, "echr_decode_step: null argument");
+  ECHR_REQUIRE(b->encoded && b->n_events > 0, "echr_decode_step: set the contexts first");
+  cudaStream_t st = (cudaStream_t)stream;
+  const int rows = b->n_events;
+  const int V1 = b->model->V1;
+  ECHR_TRY(enqueue_init(b, 1, st));
+  ECHR_CUDA(launch_load_state(b, rows, it, h_in, st));
+  ECHR_CUDA(cudaMemcpyAsync(b->cstate[0], c_in, sizeof(float) * (size_t)3 * rows * HID, cudaMemcpyDeviceToDevice, st));
+  ECHR_TRY(enqueue_step(b, rows, 0, 1, logprobs, V1, st));
+  ECHR_CUDA(launch_finalize_tf(b, 0, it, 2, logprobs, st));  // seq_cols = 2: normalise only
+  ECHR_CUDA(launch_export_state(b, rows, h_out, st));
+  ECHR_CUDA(cudaMemcpyAsync(c_out, b->cstate[1], sizeof(float) * (size_t)3 * rows * HID, cudaMemcpyDeviceToDevice, st));
   return ECHR_OK;
 }
 

@@ -135,6 +135,8 @@ cudaError_t launch_finalize_beam(const echr_batch* b, int beam, int step, int32_
                                  float* logp, float* score, cudaStream_t st);
 cudaError_t launch_finalize_tf(const echr_batch* b, int step, const int32_t* seq, int seq_cols,
                                float* logprobs, cudaStream_t st);
+cudaError_t launch_load_state(const echr_batch* b, int rows, const int32_t* it, const float* h_in, cudaStream_t st);
+cudaError_t launch_export_state(const echr_batch* b, int rows, float* h_out, cudaStream_t st);
 void count_launch(int n = 1);
 constexpr int TRACE_SLOTS = 1024;
 // next trace slot of this batch for a kernel of `kind` (0 h2att, 1 attention, 2 gates, 3 logits, 4 finalize,

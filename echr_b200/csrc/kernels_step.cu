@@ -546,6 +546,56 @@ cudaError_t launch_finalize_tf(const echr_batch* b, int step, const int32_t* seq
 }
 
 // ---------------------------------------------------------------------------------------------
+// Explicit-state single step (OldModel.get_logprobs_state, OldModel_NEW.py:133-137): load the
+// caller's (h, it) into the activation matrix, and read the new h back out of the planes.
+__global__ void __launch_bounds__(128)
+load_state_kernel(int rows, int V1, const int32_t* __restrict__ it, const float* __restrict__ h_in,
+                  const bf16* __restrict__ embed, long long embed_plane, bf16* __restrict__ act,
+                  long long act_plane, int planes) {
+  const int r = blockIdx.x;
+  bf16* row = act + (long long)r * ACT_LD;
+  for (int c = threadIdx.x; c < 3 * HID; c += blockDim.x) {
+    const int l = c / HID, u = c - l * HID;
+    bf16 h, lo;
+    split_bf16(h_in[((long long)l * rows + r) * HID + u], h, lo);
+    row[ACT_H + c] = h;
+    if (planes > 1) row[act_plane + ACT_H + c] = lo;
+  }
+  const int tok = min(max(it[r], 0), V1 - 1);
+  for (int c = threadIdx.x; c < HID; c += blockDim.x) {
+    row[ACT_X + c] = embed[(long long)tok * HID + c];
+    if (planes > 1) row[act_plane + ACT_X + c] = embed[embed_plane + (long long)tok * HID + c];
+  }
+}
+
+__global__ void __launch_bounds__(128)
+export_state_kernel(int rows, const bf16* __restrict__ act, long long act_plane, int planes,
+                    float* __restrict__ h_out) {
+  const int r = blockIdx.x;
+  const bf16* row = act + (long long)r * ACT_LD;
+  for (int c = threadIdx.x; c < 3 * HID; c += blockDim.x) {
+    const int l = c / HID, u = c - l * HID;
+    float v = __bfloat162float(row[ACT_H + c]);
+    if (planes > 1) v += __bfloat162float(row[act_plane + ACT_H + c]);
+    h_out[((long long)l * rows + r) * HID + u] = v;
+  }
+}
+
+cudaError_t launch_load_state(const echr_batch* b, int rows, const int32_t* it, const float* h_in, cudaStream_t st) {
+  const echr_model* m = b->model;
+  load_state_kernel<<<rows, 128, 0, st>>>(rows, m->V1, it, h_in, m->embed.p, m->embed.plane_stride(), b->act[0].p,
+                                          b->act[0].plane_stride(), (int)b->act[0].planes);
+  count_launch();
+  return cudaGetLastError();
+}
+
+cudaError_t launch_export_state(const echr_batch* b, int rows, float* h_out, cudaStream_t st) {
+  export_state_kernel<<<rows, 128, 0, st>>>(rows, b->act[1].p, b->act[1].plane_stride(), (int)b->act[1].planes, h_out);
+  count_launch();
+  return cudaGetLastError();
+}
+
+// ---------------------------------------------------------------------------------------------
 // Beam step (spec: oracle/echr_oracle.py beam_search).  One CTA per event, warp b = slot b.
 constexpr int BEAM_MAX = 4;
 constexpr int BEAM_SEG = 3 * HID;  // 1536 elements: h of the three streams / c of the three streams

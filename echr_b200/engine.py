@@ -187,6 +187,46 @@ class Engine(object):
                   "echr_teacher_forced")
         return out
 
+    # ------------------------------------------------------------------ sub-module level entries
+    def relation_encode(self, feats, soi):
+        """MA_Attention8.forward: feats fp32 [n,1012] on this device, soi [[s,e),...] -> [n,512]."""
+        n = feats.shape[0]
+        soi_np = _i32(soi).reshape(n, 2)
+        self.reserve(1, 1, n, n * n, 1)
+        feats = feats.to(device=self.device, dtype=torch.float32).contiguous()
+        out = torch.empty(n, 512, dtype=torch.float32, device=self.device)
+        with torch.cuda.device(self.device):
+            check(self.lib.echr_relation_encode(self._batch, feats.data_ptr(), soi_np.ctypes.data, n, out.data_ptr(),
+                                                _stream()), "echr_relation_encode")
+        self.layout = None
+        return out
+
+    def set_context(self, video, event, clip, clip_len, beam=1):
+        """lm_model-level contexts: video [100], event [n,512], clip [n,lmax,500] (zero padded),
+        clip_len = valid clips per event."""
+        n, lmax = clip.shape[0], clip.shape[1]
+        lens = _i32(clip_len)
+        self.reserve(1, n * lmax, n, n * n, beam)
+        f32 = lambda t: t.to(device=self.device, dtype=torch.float32).contiguous()
+        video, event, clip = f32(video).reshape(-1), f32(event), f32(clip)
+        with torch.cuda.device(self.device):
+            check(self.lib.echr_batch_set_context(self._batch, video.data_ptr(), event.data_ptr(), clip.data_ptr(),
+                                                  lens.ctypes.data, n, lmax, _stream()), "echr_batch_set_context")
+        self.layout = BatchLayout([n * lmax], [[0] * n], [[[i * lmax, i * lmax + int(l)] for i, l in enumerate(lens)]])
+
+    def decode_step(self, it, h, c):
+        """One step with explicit state: it [n], h/c [3,n,512] -> (logprobs [n,V+1], h', c')."""
+        n = self.layout.n_events
+        it = it.to(device=self.device, dtype=torch.int32).contiguous()
+        h = h.to(device=self.device, dtype=torch.float32).contiguous()
+        c = c.to(device=self.device, dtype=torch.float32).contiguous()
+        lp = torch.empty(n, self.V1, dtype=torch.float32, device=self.device)
+        h2, c2 = torch.empty_like(h), torch.empty_like(c)
+        with torch.cuda.device(self.device):
+            check(self.lib.echr_decode_step(self._batch, it.data_ptr(), h.data_ptr(), c.data_ptr(), lp.data_ptr(),
+                                            h2.data_ptr(), c2.data_ptr(), _stream()), "echr_decode_step")
+        return lp, h2, c2
+
     # ------------------------------------------------------------------ host-buffer path (e2e)
     def caption_host(self, layout, c3d, tap, lda, beam=1, out=None):
         """Everything through one C-ABI call with HOST buffers: H2D, encode, decode, D2H, sync.

@@ -159,6 +159,21 @@ ECHR_API int echr_encode(echr_batch_t* batch, void* stream);
 /* event context [n_events,512] fp32 produced by echr_encode (CaptionGenerator.py:129). */
 ECHR_API int echr_get_event_context(const echr_batch_t* batch, float* out, void* stream);
 
+/* MA_Attention8.forward(feats, soi_select_list) on its own (models/MA_attention_8_NEW.py:35-49):
+ * feats fp32 [n,1012] = (pooled clip feature | proposal state) per event of ONE video, host_soi int32
+ * [n,2] half-open spans -> out fp32 [n,512].  Overwrites the batch's current inputs. */
+ECHR_API int echr_relation_encode(echr_batch_t* batch, const float* feats, const int32_t* host_soi, int n, float* out,
+                         void* stream);
+/* lm_model-level contexts (models/OldModel_NEW.py:98,139 take ready-made video / event / clip):
+ * video fp32 [100], event fp32 [n,512], clip fp32 [n,lmax,500] zero padded, host_clip_len int32 [n] valid
+ * clips per event (the reference's clip_mask is a prefix mask).  Replaces set_inputs + encode. */
+ECHR_API int echr_batch_set_context(echr_batch_t* batch, const float* video, const float* event, const float* clip,
+                           const int32_t* host_clip_len, int n, int lmax, void* stream);
+/* OldModel.get_logprobs_state (models/OldModel_NEW.py:133-137) with explicit state: it int32 [n],
+ * h_in / c_in fp32 [3,n,512] -> logprobs fp32 [n,V+1], h_out / c_out fp32 [3,n,512]. */
+ECHR_API int echr_decode_step(echr_batch_t* batch, const int32_t* it, const float* h_in, const float* c_in,
+                     float* logprobs, float* h_out, float* c_out, void* stream);
+
 /* Greedy decode resident on the device (models/OldModel_NEW.py:139-187, sample_max=1):
  * tokens int32 [n_events, seq_length] with the reference's masking (finished rows -> 0),
  * logp fp32 [n_events, seq_length] UNmasked max log-probabilities (as the reference returns). */

@@ -57,3 +57,20 @@ def test_batch_layout_and_trim():
     s, l = trim_greedy(tok, lp)
     assert s.shape == (2, 2) and s.dtype == torch.int64
     assert trim_greedy(torch.zeros(2, 4, dtype=torch.int32), lp) == ([], [])
+
+
+def test_position_helpers_match_oracle():
+    import numpy as np
+    from echr_b200.caption_generator import MA_Attention8
+    from oracle import echr_oracle as O
+    soi = [[0, 10], [5, 6], [20, 60], [3, 99]]
+    a = MA_Attention8.extract_position_matrix(np.array(soi), len(soi))
+    assert np.array_equal(a, O.position_matrix(soi))
+    assert np.array_equal(MA_Attention8.extract_position_embedding(a, 512), O.position_embedding(O.position_matrix(soi)))
+
+
+def test_submodules_need_their_owner():
+    from echr_b200.caption_generator import setup_fusion
+    fm = setup_fusion(echr_opt())
+    with pytest.raises(RuntimeError):
+        fm(torch.zeros(2, 1012), [[0, 1], [1, 2]])

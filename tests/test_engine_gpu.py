@@ -152,3 +152,42 @@ def test_caption_host_equals_device_path():
         assert torch.equal(lp[r0:r0 + n, : seq.shape[1]], logp.cpu())
         r0 += n
     assert m.engine.launch_count() > 0
+
+
+# ----------------------------------------------------------------------------- sub-module surfaces
+def test_submodule_surfaces_match_oracle():
+    """fusion_model.forward, lm_model.sample / forward / get_logprobs_state / init_hidden with the
+    reference's own argument conventions (MA:35-49, OldModel_NEW.py:98-187)."""
+    sd = helpers.state_dict("fp32")
+    m = model("fp32", "fp32")
+    v = helpers.case_video("sst12")
+    ind, soi = v.ind_select_list, v.soi_select_list
+    pooled = torch.stack([v.c3d_feats[s:e].mean(0) for s, e in soi], 0)
+    feats = torch.cat([pooled, v.tap_feats[torch.as_tensor(ind)]], 1)
+    want_event = O.relation_encode(sd, feats, soi)
+    got_event = m.fusion_model(feats.to(DEV), soi)
+    assert (got_event.cpu() - want_event).abs().max().item() < 2e-5
+    video, event, clip, mask = O.build_context(sd, v.tap_feats, v.c3d_feats, v.lda_feats, ind, soi)
+    seq_ref, lp_ref = O.greedy_decode(sd, video, event, clip, mask)
+    tf_ref = O.teacher_forced_logprobs(sd, video, event, clip, mask, labels_of(seq_ref))
+    seq, lp = m.lm_model.sample(video.to(DEV), event.to(DEV), clip.to(DEV), mask.to(DEV))
+    helpers.check_tokens(seq.cpu().numpy(), seq_ref.numpy(), tf_ref.topk(2, dim=2)[0].numpy(), "lm.sample")
+    tf = m.lm_model(video.to(DEV), event.to(DEV), clip.to(DEV), mask.to(DEV), labels_of(seq_ref).to(DEV))
+    assert tuple(tf.shape) == tuple(tf_ref.shape)
+    assert (tf.cpu() - tf_ref).abs().max().item() < 1e-4
+    # explicit-state stepping
+    n = event.shape[0]
+    state = m.lm_model.init_hidden(video.to(DEV), event.to(DEV), clip.to(DEV))
+    st_ref = O.init_state(n)
+    it = torch.zeros(n, dtype=torch.long)
+    for _ in range(3):
+        lp_step, state = m.lm_model.get_logprobs_state(it.to(DEV), video.to(DEV), event.to(DEV), clip.to(DEV),
+                                                       mask.to(DEV), state)
+        lp_o, st_ref = O.decode_step(sd, it, video, event, clip, mask, st_ref)
+        assert (lp_step.cpu() - lp_o).abs().max().item() < 1e-4
+        assert (state[0].cpu() - st_ref[0]).abs().max().item() < 2e-5
+        assert (state[1].cpu() - st_ref[1]).abs().max().item() < 2e-5
+        it = lp_o.argmax(1)
+    beam_tok, beam_lp = m.lm_model.sample(video.to(DEV), event.to(DEV), clip.to(DEV), mask.to(DEV),
+                                          opt={"beam_size": 3})
+    assert tuple(beam_tok.shape) == (n, 30)
