@@ -40,12 +40,13 @@ struct Arena {
 };
 
 // ---------------------------------------------------------------- packing kernels
-// LSTM weights: dst[4j+g, :] = [ w_ih[g*512+j, 0:512] | w_ih[g*512+j, 512:512+ctx] (zero padded to
-// ctx_pad) | w_hh[g*512+j, :] ]  (gate-interleaved rows so that one epilogue thread sees i,f,g,o of
-// a hidden unit in adjacent accumulator columns).
+// LSTM weights: dst[4j+g, :] = [ w_ih[g*512+j, 0:512] | w_hh[g*512+j, :] | w_ih[g*512+j, 512:512+ctx]
+// (zero padded to ctx_pad) ]  — gate-interleaved rows so that one epilogue thread sees i,f,g,o of a
+// hidden unit in adjacent accumulator columns; the per-step operands (x, h) come first so that the
+// constant-context block (event / video) can be hoisted out of the step GEMM as a column sub-range.
 __global__ void pack_lstm_kernel(const float* __restrict__ w_ih, const float* __restrict__ w_hh, int ctx,
                                  int ctx_pad, bf16* __restrict__ hi, bf16* __restrict__ lo) {
-  const int K = HID + ctx_pad + HID;
+  const int K = HID + HID + ctx_pad;
   const int in_ih = HID + ctx;
   const long long total = (long long)GATES * K;
   for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
@@ -55,8 +56,8 @@ __global__ void pack_lstm_kernel(const float* __restrict__ w_ih, const float* __
     const int src = g * HID + j;
     float x = 0.f;
     if (c < HID) x = w_ih[(long long)src * in_ih + c];
-    else if (c < HID + ctx_pad) { if (c - HID < ctx) x = w_ih[(long long)src * in_ih + c]; }
-    else x = w_hh[(long long)src * HID + (c - HID - ctx_pad)];
+    else if (c < 2 * HID) x = w_hh[(long long)src * HID + (c - HID)];
+    else if (c - 2 * HID < ctx) x = w_ih[(long long)src * in_ih + HID + (c - 2 * HID)];
     bf16 h, l;
     split_bf16(x, h, l);
     hi[i] = h;
@@ -99,6 +100,9 @@ struct GemmSpec {
   // LSTM
   const float* c_in = nullptr;
   float* c_out = nullptr;
+  const float* row_bias = nullptr;
+  long long ld_row_bias = 0;
+  int hi_only_first = 0;  // leading k-blocks whose low-order activation plane is identically zero
   // logits
   float* partial = nullptr;
   float* logits_out = nullptr;
@@ -119,7 +123,7 @@ static const char* fill_problem(GemmProblem& pb, const GemmSpec& s, int a_terms,
   pb.num_kb = s.K / GEMM_BLOCK_K;
   pb.act = s.act;
   for (int i = 0; i < pb.num_kb; ++i)
-    pb.a_kb[i] = (uint16_t)(s.a_kb ? s.a_kb[i] : s.a_col0 / GEMM_BLOCK_K + i);
+    pb.a_kb[i] = (uint16_t)((s.a_kb ? s.a_kb[i] : s.a_col0 / GEMM_BLOCK_K + i) | (i < s.hi_only_first ? GEMM_KB_HI_ONLY : 0));
   pb.bias = s.bias;
   pb.out_f32 = s.out_f32;
   pb.ld_f32 = s.ld_f32;
@@ -128,6 +132,8 @@ static const char* fill_problem(GemmProblem& pb, const GemmSpec& s, int a_terms,
   pb.ld_bf = s.ld_bf;
   pb.c_in = s.c_in;
   pb.c_out = s.c_out;
+  pb.row_bias = s.row_bias;
+  pb.ld_row_bias = s.ld_row_bias;
   pb.hidden = HID;
   pb.partial = s.partial;
   pb.logits_out = s.logits_out;
@@ -139,7 +145,7 @@ static int run_gemm(const GemmSpec* specs, int groups, int a_terms, int w_terms,
                     int topk, cudaStream_t st, const char* what, echr_batch* tb = nullptr, int kind = 5) {
   GemmParams P;
   memset(&P, 0, sizeof(P));
-  if (tb != nullptr && tb->trace_on == 1) { P.trace = tb->trace; P.trace_slot = trace_next(tb, kind); }
+  if (tb != nullptr && tb->trace_on == 1) { P.trace = tb->trace; P.trace_detail = tb->trace_detail; P.trace_slot = trace_next(tb, kind); }
   int max_m = 0, max_n = 0;
   for (int g = 0; g < groups; ++g) {
     const char* err = fill_problem(P.prob[g], specs[g], a_terms, w_terms, block_n);
@@ -179,9 +185,9 @@ static void model_layout(echr_model* m, Arena& a) {
   m->w_fc2 = a.planes(wt, ECHR_HEADS, HID);
   m->w_ctx2att = a.planes(wt, HID, CLIP_PAD);
   m->w_h2att = a.planes(wt, HID, HID);
-  m->w_lstm[0] = a.planes(wt, GATES, HID + HID + HID);
-  m->w_lstm[1] = a.planes(wt, GATES, HID + CLIP_PAD + HID);
-  m->w_lstm[2] = a.planes(wt, GATES, HID + VID_PAD + HID);
+  m->w_lstm[0] = a.planes(wt, GATES, HID + HID + HID);       // x | h0 | event
+  m->w_lstm[1] = a.planes(wt, GATES, HID + HID + CLIP_PAD);  // x | h1 | attended clip
+  m->w_lstm[2] = a.planes(wt, GATES, HID + HID + VID_PAD);   // x | h2 | video
   m->w_logit = a.planes(wt, m->V1, 3 * HID);
   m->embed = a.planes(2, m->V1, HID);
   m->b_event_emb = a.take<float>(HID);
@@ -327,6 +333,7 @@ static void batch_layout(echr_batch* b, Arena& a) {
     b->cstate[i] = a.take<float>((size_t)3 * c.max_rows * HID);
   }
   b->q_att = a.take<float>((size_t)c.max_rows * HID);
+  for (int i = 0; i < 2; ++i) b->row_bias[i] = a.take<float>((size_t)c.max_rows * GATES);
   b->partial = a.take<float>((size_t)c.max_rows * n_tiles * LogitRec<4>::WORDS);
   b->row_start = a.take<int32_t>(c.max_rows);
   b->row_len = a.take<int32_t>(c.max_rows);
@@ -340,6 +347,7 @@ static void batch_layout(echr_batch* b, Arena& a) {
   b->beam_hist_lp = a.take<float>((size_t)2 * c.max_rows * S);
   b->best_score = a.take<float>(c.max_events);
   b->trace = a.take<unsigned long long>(2 * TRACE_SLOTS);
+  b->trace_detail = a.take<unsigned long long>(4 * TRACE_SLOTS);
 }
 
 extern "C" int echr_batch_create(const echr_model_t* model, const echr_capacity_t* cap, echr_batch_t** out) {
@@ -628,9 +636,10 @@ extern "C" int echr_get_event_context(const echr_batch_t* b, float* out, void* s
 // =============================================================================================
 // Decode
 // =============================================================================================
-static const int KB_L0[24] = {0, 1, 2, 3, 4, 5, 6, 7, 8, 9, 10, 11, 12, 13, 14, 15, 26, 27, 28, 29, 30, 31, 32, 33};
-static const int KB_L1[24] = {0, 1, 2, 3, 4, 5, 6, 7, 16, 17, 18, 19, 20, 21, 22, 23, 34, 35, 36, 37, 38, 39, 40, 41};
-static const int KB_L2[18] = {0, 1, 2, 3, 4, 5, 6, 7, 24, 25, 42, 43, 44, 45, 46, 47, 48, 49};
+// k-block tables over the activation matrix, in the weights' column order [x | h | ctx]
+static const int KB_L0[16] = {0, 1, 2, 3, 4, 5, 6, 7, 26, 27, 28, 29, 30, 31, 32, 33};                                   // x, h0
+static const int KB_L1[24] = {0, 1, 2, 3, 4, 5, 6, 7, 34, 35, 36, 37, 38, 39, 40, 41, 16, 17, 18, 19, 20, 21, 22, 23};  // x, h1, att
+static const int KB_L2[16] = {0, 1, 2, 3, 4, 5, 6, 7, 42, 43, 44, 45, 46, 47, 48, 49};                                   // x, h2
 
 enum { MODE_GREEDY = 0, MODE_BEAM = 1, MODE_TF = 2 };
 
@@ -641,6 +650,24 @@ static int enqueue_init(echr_batch* b, int beam, cudaStream_t st) {
       ECHR_CUDA(cudaMemsetAsync(b->act[i].plane(p), 0, sizeof(bf16) * (size_t)rows * ACT_LD, st));
   ECHR_CUDA(cudaMemsetAsync(b->cstate[0], 0, sizeof(float) * (size_t)3 * rows * HID, st));
   ECHR_CUDA(launch_decode_init(b, beam, st));
+  // Hoist the constant-context terms of streams 0 and 2 out of the time loop: per-row gate bias
+  //   row_bias0 = W_ih0[:, event] . event_ctx + (b_ih0 + b_hh0),  row_bias2 = W_ih2[:, video] . lda + (b_ih2 + b_hh2)
+  // (ThreeStream_Core feeds the same event / video context at every step, OldModel_NEW.py:806-817).
+  const echr_model* m = b->model;
+  const int at = m->cfg.a_terms, wt = m->cfg.w_terms;
+  GemmSpec s[2];
+  PlaneMat wv[2];
+  const int layer[2] = {0, 2};
+  const int col0[2] = {ACT_EV, ACT_VID};
+  const int K[2] = {HID, VID_PAD};
+  for (int i = 0; i < 2; ++i) {
+    wv[i] = m->w_lstm[layer[i]];
+    wv[i].p += 2 * HID;  // the context block of [x | h | ctx]; plane stride and ld are unchanged
+    s[i].A = &b->act[0]; s[i].a_col0 = col0[i]; s[i].M = (int)rows; s[i].W = &wv[i]; s[i].N = GATES; s[i].K = K[i];
+    s[i].bias = m->b_lstm[layer[i]];
+    s[i].out_f32 = b->row_bias[i]; s[i].ld_f32 = GATES;
+    ECHR_TRY(run_gemm(&s[i], 1, at, wt, 128, EPI_STORE, 1, st, "hoisted_context"));
+  }
   return ECHR_OK;
 }
 
@@ -674,10 +701,13 @@ static int enqueue_step(echr_batch* b, int rows, int t, int topk, float* logits_
   if (parts & PART_GATES) {
     GemmSpec s[3];
     const int* kbs[3] = {KB_L0, KB_L1, KB_L2};
-    const int K[3] = {24 * 64, 24 * 64, 18 * 64};
+    const int K[3] = {16 * 64, 24 * 64, 16 * 64};
     for (int l = 0; l < 3; ++l) {
       s[l].A = &cur; s[l].a_kb = kbs[l]; s[l].M = rows; s[l].W = &m->w_lstm[l]; s[l].N = GATES; s[l].K = K[l];
       s[l].bias = m->b_lstm[l];
+      if (l != 1) { s[l].row_bias = b->row_bias[l / 2]; s[l].ld_row_bias = GATES; }
+      // with bf16 weights the embedding rows are bf16 values: the x block has no low-order plane
+      if (at == 2 && wt == 1) s[l].hi_only_first = HID / 64;
       s[l].c_in = b->cstate[p] + (long long)l * rows * HID;
       s[l].c_out = b->cstate[n] + (long long)l * rows * HID;
       s[l].out_hi = nxt.plane(0) + ACT_H + l * HID;
@@ -781,6 +811,7 @@ static int run_decode(echr_batch* b, int beam, int mode, cudaStream_t st) {
   }
   if (b->trace_on) {  // reset {min start, max end} before the replay
     ECHR_CUDA(cudaMemsetAsync(b->trace, 0xff, sizeof(unsigned long long) * TRACE_SLOTS * 2, st));
+    ECHR_CUDA(cudaMemsetAsync(b->trace_detail, 0, sizeof(unsigned long long) * TRACE_SLOTS * 4, st));
   }
   ECHR_CUDA(cudaGraphLaunch(b->graph_exec, st));
   count_launch((int)b->graph_kernels);
@@ -909,13 +940,16 @@ extern "C" int echr_time_step_kernels(echr_batch_t* b, int beam, int iters, floa
 // per kernel its kind (0 h2att, 1 attention, 2 gates, 3 logits, 4 finalize), earliest CTA start and
 // latest CTA end in globaltimer ns.  Synchronises the device.  Returns the number of kernels.
 extern "C" int echr_trace_read(echr_batch_t* b, int64_t* host_start_ns, int64_t* host_end_ns, int32_t* host_kind,
-                               int max_entries) {
+                               int64_t* host_detail, int max_entries) {
   if (!b || !b->trace_on || !host_start_ns || !host_end_ns || !host_kind) return 0;
   if (cudaDeviceSynchronize() != cudaSuccess) return 0;
   std::vector<unsigned long long> h(2 * TRACE_SLOTS);
   if (cudaMemcpy(h.data(), b->trace, sizeof(unsigned long long) * 2 * TRACE_SLOTS, cudaMemcpyDeviceToHost) != cudaSuccess)
     return 0;
   int n = b->trace_n < max_entries ? b->trace_n : max_entries;
+  if (host_detail != nullptr &&
+      cudaMemcpy(host_detail, b->trace_detail, sizeof(unsigned long long) * 4 * n, cudaMemcpyDeviceToHost) != cudaSuccess)
+    return 0;
   for (int i = 0; i < n; ++i) {
     host_start_ns[i] = (int64_t)h[2 * i];
     host_end_ns[i] = (int64_t)(~h[2 * i + 1]);

@@ -45,7 +45,7 @@ struct echr_model {
   echr::PlaneMat w_fc2;        // [16, 512]
   echr::PlaneMat w_ctx2att;    // [512, 512(500)]
   echr::PlaneMat w_h2att;      // [512, 512]
-  echr::PlaneMat w_lstm[3];    // [2048 gate-interleaved, K_l]  K = 1536, 1536, 1152 (x | ctx | h)
+  echr::PlaneMat w_lstm[3];    // [2048 gate-interleaved, K_l]  K = 1536, 1536, 1152 (x | h | ctx)
   echr::PlaneMat w_logit;      // [V1, 1536]
   echr::PlaneMat embed;        // [V1, 512] always 2 planes (a_terms are read from it)
   // fp32 vectors
@@ -83,7 +83,8 @@ struct echr_batch {
   // decode workspace (rows = events * beam)
   echr::PlaneMat act[2];    // [rows, ACT_LD]
   float* cstate[2];         // [3][rows][512]
-  float* q_att;             // [rows, 512]
+  float* q_att;             // [rows, 512]   e^{2q}
+  float* row_bias[2];       // [rows, 2048]  hoisted gate bias of streams 0 and 2
   float* partial;           // [rows, n_vtiles, 12]
   int32_t *row_start, *row_len;  // attention window per decode row
   int32_t* unfinished;      // [rows]
@@ -107,6 +108,7 @@ struct echr_batch {
   int64_t graph_kernels;
   // timeline trace (ECHR_TRACE=1): device [2*TRACE_SLOTS] u64, host-side kind of every slot
   unsigned long long* trace;
+  unsigned long long* trace_detail;  // [TRACE_SLOTS][4], GEMM kernels only (see gemm_tc.cuh)
   int trace_on, trace_n;
   unsigned char trace_kind[1024];
   void* arena;

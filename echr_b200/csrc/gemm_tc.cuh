@@ -30,6 +30,7 @@ namespace echr {
 constexpr int GEMM_BLOCK_M = 128;
 constexpr int GEMM_BLOCK_K = 64;
 constexpr int GEMM_MAX_KB = 32;
+constexpr uint16_t GEMM_KB_HI_ONLY = 0x8000;
 constexpr int GEMM_MAX_GROUPS = 3;
 constexpr int GEMM_EPI_WARPS = 8;                       // two warps per TMEM lane quarter
 constexpr int GEMM_THREADS = 128 + GEMM_EPI_WARPS * 32;  // warps 0-3: TMA, MMA, TMEM alloc, spare
@@ -45,7 +46,8 @@ struct GemmProblem {
   int N;            // valid columns of D (rows of W)
   int num_kb;       // K / 64
   int act;          // EPI_STORE activation
-  uint16_t a_kb[GEMM_MAX_KB];  // A column-block index for each k-block
+  uint16_t a_kb[GEMM_MAX_KB];  // A column-block index for each k-block; bit 15: the block's low-order
+                               // plane is identically zero (skip its load and its product)
   const float* bias;           // [N] (EPI_LSTM: gate-interleaved order)
   // EPI_STORE
   float* out_f32;
@@ -56,6 +58,8 @@ struct GemmProblem {
   // EPI_LSTM
   const float* c_in;   // [M, H]
   float* c_out;        // [M, H]
+  const float* row_bias;  // optional [M, N] per-row gate bias (hoisted constant-context terms); replaces bias
+  long long ld_row_bias;
   int hidden;          // H (N == 4H)
   // EPI_LOGITS
   float* partial;      // [M, n_groups, REC]   n_groups = ceil(N / BLOCK_N) * (BLOCK_N / LOGIT_GROUP)
@@ -67,6 +71,8 @@ struct GemmParams {
   GemmProblem prob[GEMM_MAX_GROUPS];
   unsigned long long* trace;  // optional timeline trace (see ptx.cuh)
   int trace_slot;
+  unsigned long long* trace_detail;  // optional [slot][4]: sum over CTAs of (first stage landed, accumulator
+                                     // ready, CTA end) - CTA start in ns, and the CTA count
 };
 
 template <int TOPK>
@@ -140,6 +146,8 @@ gemm_tc_kernel(const __grid_constant__ GemmParams P) {
   uint8_t* bar_generic = smem_raw + (bar_base - smem_u32(smem_raw));
   volatile uint32_t* tmem_ptr_generic = reinterpret_cast<volatile uint32_t*>(bar_generic + 136);
   float* sbias = reinterpret_cast<float*>(bar_generic + 256);
+  volatile unsigned long long* t_start_smem = reinterpret_cast<volatile unsigned long long*>(bar_generic + 144);
+  if (P.trace_detail != nullptr && threadIdx.x == 0) *t_start_smem = global_timer_ns();
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -181,12 +189,15 @@ gemm_tc_kernel(const __grid_constant__ GemmParams P) {
         mbar_wait(empty_bar(stage), phase ^ 1u);
         const uint32_t sa = smem_base + stage * Cfg::STAGE_BYTES;
         const uint32_t sw = sa + A_TERMS * Cfg::A_PLANE_BYTES;
-        mbar_arrive_expect_tx(full_bar(stage), Cfg::STAGE_BYTES);
-        const int a_col = static_cast<int>(pb.a_kb[kb]) * GEMM_BLOCK_K;
+        const uint16_t kbe = pb.a_kb[kb];
+        const bool hi_only = A_TERMS == 2 && (kbe & GEMM_KB_HI_ONLY) != 0;
+        mbar_arrive_expect_tx(full_bar(stage), Cfg::STAGE_BYTES - (hi_only ? Cfg::A_PLANE_BYTES : 0));
+        const int a_col = static_cast<int>(kbe & 0x7fff) * GEMM_BLOCK_K;
 #pragma unroll
         for (int t = 0; t < A_TERMS; ++t)
-          tma_load_3d(sa + t * Cfg::A_PLANE_BYTES, &pb.tmA, full_bar(stage), a_col,
-                      m_tile * GEMM_BLOCK_M, t);
+          if (t == 0 || !hi_only)
+            tma_load_3d(sa + t * Cfg::A_PLANE_BYTES, &pb.tmA, full_bar(stage), a_col,
+                        m_tile * GEMM_BLOCK_M, t);
 #pragma unroll
         for (int t = 0; t < W_TERMS; ++t)
           tma_load_3d(sw + t * Cfg::W_PLANE_BYTES, &pb.tmW, full_bar(stage), kb * GEMM_BLOCK_K,
@@ -204,16 +215,19 @@ gemm_tc_kernel(const __grid_constant__ GemmParams P) {
       for (int kb = 0; kb < num_kb; ++kb) {
         mbar_wait(full_bar(stage), phase);
         tc_fence_after_sync();
+        if (kb == 0 && P.trace_detail != nullptr)
+          atomicAdd(P.trace_detail + 4 * P.trace_slot, global_timer_ns() - *t_start_smem);
         const uint32_t sa = smem_base + stage * Cfg::STAGE_BYTES;
         const uint32_t sw = sa + A_TERMS * Cfg::A_PLANE_BYTES;
         const uint64_t a_hi = umma_desc_k_sw128(sa);
         const uint64_t w_hi = umma_desc_k_sw128(sw);
+        const bool hi_only = A_TERMS == 2 && (pb.a_kb[kb] & GEMM_KB_HI_ONLY) != 0;
 #pragma unroll
         for (int k = 0; k < GEMM_BLOCK_K / 16; ++k) {
           const uint64_t koff = static_cast<uint64_t>(k * 2);  // 32 B per K=16 step, >>4
           umma_bf16(tmem_base, a_hi + koff, w_hi + koff, idesc, accum);
           accum = 1;
-          if (A_TERMS == 2) {
+          if (A_TERMS == 2 && !hi_only) {
             const uint64_t a_lo = umma_desc_k_sw128(sa + Cfg::A_PLANE_BYTES);
             umma_bf16(tmem_base, a_lo + koff, w_hi + koff, idesc, 1);
           }
@@ -242,7 +256,22 @@ gemm_tc_kernel(const __grid_constant__ GemmParams P) {
 
     // ---- operands that do not depend on the accumulator: fetch before waiting for the MMAs
     float cprev[EPI == EPI_LSTM ? HALF / 4 : 1];
+    float rbias[EPI == EPI_LSTM ? HALF : 1];
+    bool has_rbias = false;
     if constexpr (EPI == EPI_LSTM) {
+      has_rbias = pb.row_bias != nullptr;
+      if (has_rbias && row_ok) {
+        const float4* rp = reinterpret_cast<const float4*>(
+            pb.row_bias + static_cast<long long>(row) * pb.ld_row_bias + col0 + hc0);
+#pragma unroll
+        for (int i = 0; i < HALF / 4; ++i) {
+          const float4 t = __ldg(rp + i);
+          rbias[4 * i] = t.x; rbias[4 * i + 1] = t.y; rbias[4 * i + 2] = t.z; rbias[4 * i + 3] = t.w;
+        }
+      } else {
+#pragma unroll
+        for (int i = 0; i < HALF; ++i) rbias[i] = 0.f;
+      }
       if (row_ok) {
         const float4* cp = reinterpret_cast<const float4*>(
             pb.c_in + static_cast<long long>(row) * pb.hidden + ((col0 + hc0) >> 2));
@@ -259,6 +288,8 @@ gemm_tc_kernel(const __grid_constant__ GemmParams P) {
 
     mbar_wait(tmem_full_bar, 0);
     tc_fence_after_sync();
+    if (P.trace_detail != nullptr && threadIdx.x == 128)
+      atomicAdd(P.trace_detail + 4 * P.trace_slot + 1, global_timer_ns() - *t_start_smem);
 
     if (active) {
       if constexpr (EPI == EPI_STORE) {
@@ -329,7 +360,11 @@ gemm_tc_kernel(const __grid_constant__ GemmParams P) {
             __align__(16) __nv_bfloat16 hl[8];
 #pragma unroll
             for (int u = 0; u < 8; ++u) {
-              const float4 b = *reinterpret_cast<const float4*>(sbias + tc + 4 * u);
+              float4 b = *reinterpret_cast<const float4*>(sbias + tc + 4 * u);
+              if (has_rbias) {
+                b.x = rbias[32 * c + 4 * u]; b.y = rbias[32 * c + 4 * u + 1];
+                b.z = rbias[32 * c + 4 * u + 2]; b.w = rbias[32 * c + 4 * u + 3];
+              }
               const float gi = sigmoid_fast(v[4 * u + 0] + b.x);
               const float gf = sigmoid_fast(v[4 * u + 1] + b.y);
               const float gg = tanh_fast_acc(v[4 * u + 2] + b.z);
@@ -452,6 +487,10 @@ gemm_tc_kernel(const __grid_constant__ GemmParams P) {
     tmem_dealloc<Cfg::TMEM_COLS>(tmem_base);
   }
   trace_end(P.trace, P.trace_slot);
+  if (P.trace_detail != nullptr && threadIdx.x == 0) {
+    atomicAdd(P.trace_detail + 4 * P.trace_slot + 2, global_timer_ns() - *t_start_smem);
+    atomicAdd(P.trace_detail + 4 * P.trace_slot + 3, 1ull);
+  }
 }
 
 // ---------------------------------------------------------------- host side

@@ -258,8 +258,10 @@ class Engine(object):
         list of (kind, start_us, end_us) relative to the first kernel's start."""
         n = 1024
         st, en, kd = np.zeros(n, np.int64), np.zeros(n, np.int64), np.zeros(n, np.int32)
+        det = np.zeros((n, 4), np.int64)
         with torch.cuda.device(self.device):
-            k = self.lib.echr_trace_read(self._batch, st.ctypes.data, en.ctypes.data, kd.ctypes.data, n)
+            k = self.lib.echr_trace_read(self._batch, st.ctypes.data, en.ctypes.data, kd.ctypes.data, det.ctypes.data, n)
+        self.trace_detail = det[:max(k, 0)]
         names = ("h2att", "attention", "lstm_gates", "logit", "finalize", "other")
         if k <= 0:
             return []

@@ -202,10 +202,12 @@ ECHR_API int echr_time_step_kernels(echr_batch_t* batch, int beam, int iters, fl
 
 /* Debug aid: timeline of the last decode-graph replay when the graph was captured with ECHR_TRACE=1 in
  * the environment: per kernel its kind (0 h2att GEMM, 1 attention, 2 gate GEMM, 3 logit GEMM,
- * 4 finalize), earliest CTA start and latest CTA end (globaltimer ns).  Synchronises the device;
- * returns the number of entries written (0 when tracing is off). */
+ * 4 finalize), earliest CTA start and latest CTA end (globaltimer ns); host_detail (may be NULL) gets 4
+ * words per kernel, filled by the GEMMs only: sums over CTAs of (first operand stage landed, accumulator
+ * ready, CTA end) minus CTA start in ns, and the CTA count.  Synchronises the device; returns the number
+ * of entries written (0 when tracing is off). */
 ECHR_API int echr_trace_read(echr_batch_t* batch, int64_t* host_start_ns, int64_t* host_end_ns, int32_t* host_kind,
-                    int max_entries);
+                    int64_t* host_detail, int max_entries);
 
 /* Number of kernel launches this library issued since the last call (graph replays count their
  * kernel nodes); used by bench.py's `gpu_launches`. */

@@ -49,3 +49,13 @@ side = [x for x in by if x[0] in ("h2att", "attention")]
 side.sort(key=lambda x: x[1])
 for a, b in list(zip(side, side[1:]))[:4]:
     print("side gap %s->%s %.2f" % (a[0], b[0], b[1] - a[2]))
+
+det = eng.trace_detail
+for kind in ("h2att", "lstm_gates", "logit"):
+    rows = [det[i] for i, (k, s, e) in enumerate(tr) if k == kind and det[i][3] > 0]
+    if rows:
+        import numpy as np
+        a = np.array(rows, dtype=np.float64)
+        c = a[:, 3]
+        print("%-11s per-CTA mean (us): first stage landed %.2f, accumulator ready %.2f, CTA end %.2f  (CTAs %d)"
+              % (kind, (a[:, 0] / c).mean() / 1e3, (a[:, 1] / c).mean() / 1e3, (a[:, 2] / c).mean() / 1e3, int(c.mean())))
