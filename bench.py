@@ -263,14 +263,17 @@ def main():
     pk, pk_kind = peaks()
     rows = n_events * beam
     V1, S = opt.CG_vocab_size + 1, opt.CG_seq_length
-    # dominant kernel: the larger of the two GEMM launches of a step
-    flops = {"lstm_gates": 2.0 * rows * 2048 * (1536 + 1536 + 1152), "logit": 2.0 * rows * V1 * 1536}
+    # dominant kernel: the slower of the two GEMM launches of a step.  Algorithmic FLOPs per row-step
+    # (constant-context terms hoisted): gates 2*2048*[(512+512)+(512+500+512)+(512+512)],
+    # logits 2*1536*(V+1).
+    flops = {"lstm_gates": 2.0 * rows * 2048 * (1024 + 1524 + 1024), "logit": 2.0 * rows * V1 * 1536}
     dom = max(("lstm_gates", "logit"), key=lambda k: kt[k])
     ach = flops[dom] / (kt[dom] * 1e-3) / 1e12
     peak_tf = pk.get("bf16_tflops_sustained", pk["bf16_tflops"])
     roofline = {"bound": "tensor", "kernel": "gemm_tc_kernel<%s>" % dom, "achieved": ach, "peak": peak_tf,
                 "unit": "TFLOP/s", "frac": ach / peak_tf, "traffic": None, "peak_source": pk_kind + " (sustained)",
                 "ms_per_launch": kt[dom], "step_kernel_ms": kt,
+                "per_kernel_tflops": {k: flops[k] / (kt[k] * 1e-3) / 1e12 for k in flops},
                 "note": "algorithmic FLOPs 2*M*N*K of one product; the %s mode issues %d tcgen05 products per k-step"
                         % (args.precision, {"fp32": 3, "bf16w": 2, "bf16": 1}[args.precision])}
     # attention kernel against HBM (2024*L + 4048 bytes per event-step at bf16, fp32 clip doubles the window)

@@ -2,6 +2,7 @@
 // (used for the one-off projections and by the parity tests of the tensor-core kernel).
 #include "../../include/echr_b200.h"
 #include "engine.cuh"
+#include "gemm_tc2.cuh"
 #include "util.cuh"
 
 namespace echr {
@@ -63,7 +64,7 @@ int echr_gemm_planes(const void* a, int64_t m, int64_t k, int64_t a_ld, int a_pl
   ECHR_REQUIRE((a_planes == 1 || a_planes == 2) && (w_planes == 1 || w_planes == 2) &&
                    !(a_planes == 1 && w_planes == 2),
                "echr_gemm_planes: unsupported plane combination a=%d w=%d", a_planes, w_planes);
-  ECHR_REQUIRE(block_n == 128 || block_n == 16, "echr_gemm_planes: block_n must be 16 or 128");
+  ECHR_REQUIRE(block_n == 128 || block_n == 16 || block_n == 256, "echr_gemm_planes: block_n must be 16, 128 or 256 (persistent kernel)");
   ECHR_REQUIRE(m < (1ll << 31) && n < (1ll << 31), "echr_gemm_planes: dimension too large");
   GemmParams P;
   memset(&P, 0, sizeof(P));
@@ -85,6 +86,12 @@ int echr_gemm_planes(const void* a, int64_t m, int64_t k, int64_t a_ld, int a_pl
   pb.out_hi = (__nv_bfloat16*)out_hi;
   pb.out_lo = (__nv_bfloat16*)out_lo;
   pb.ld_bf = ld_bf;
+  if (block_n == 256) {
+    int dev = 0, sms = 148;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    ECHR_CUDA(gemm2_launch(P, 1, a_planes, w_planes, EPI_STORE, 1, sms, (cudaStream_t)stream));
+  } else
   ECHR_CUDA(gemm_launch(P, 1, (int)m, (int)n, a_planes, w_planes, block_n, EPI_STORE, 1,
                         (cudaStream_t)stream));
   count_launch();

@@ -1,6 +1,7 @@
 // Engine: weight packing (echr_model_*), batch workspace (echr_batch_*), the encode pipeline and
 // the device-resident decode loops, exported through the C-ABI of include/echr_b200.h.
 #include "engine.cuh"
+#include "gemm_tc2.cuh"
 #include "util.cuh"
 
 #include <atomic>
@@ -141,20 +142,54 @@ static const char* fill_problem(GemmProblem& pb, const GemmSpec& s, int a_terms,
   return nullptr;
 }
 
+// Row count from which the persistent 128 x 256 kernel (gemm_tc2.cuh) replaces the one-tile-per-CTA
+// 128 x 128 kernel: below it there are not enough tiles to fill the SMs with the wide tile.
+static int gemm2_min_rows() {
+  static int v = -1;
+  if (v < 0) {
+    const char* e = getenv("ECHR_GEMM2_MIN_ROWS");
+    v = e ? atoi(e) : 1024;
+  }
+  return v;
+}
+static bool use_gemm2(int rows, int n, int block_n) { return block_n == 128 && n >= GEMM2_BLOCK_N && rows >= gemm2_min_rows(); }
+static int num_sms() {
+  static int n = 0;
+  if (n == 0) {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev);
+    if (n <= 0) n = 148;
+  }
+  return n;
+}
+// partial records per row the logit GEMM writes for `rows` decode rows
+static int logit_groups(const echr_model* m, int rows) {
+  return use_gemm2(rows, m->V1, 128) ? gemm2_logit_groups(m->V1) : gemm1_logit_groups(m->V1);
+}
+
+int logit_groups_for(const echr_model* m, int rows) { return logit_groups(m, rows); }
+
 static int run_gemm(const GemmSpec* specs, int groups, int a_terms, int w_terms, int block_n, int epi,
                     int topk, cudaStream_t st, const char* what, echr_batch* tb = nullptr, int kind = 5) {
   GemmParams P;
   memset(&P, 0, sizeof(P));
   if (tb != nullptr && tb->trace_on == 1) { P.trace = tb->trace; P.trace_detail = tb->trace_detail; P.trace_slot = trace_next(tb, kind); }
-  int max_m = 0, max_n = 0;
+  int max_m = 0, max_n = 0, min_n = 1 << 30;
   for (int g = 0; g < groups; ++g) {
-    const char* err = fill_problem(P.prob[g], specs[g], a_terms, w_terms, block_n);
+    if (specs[g].M > max_m) max_m = specs[g].M;
+    if (specs[g].N < min_n) min_n = specs[g].N;
+  }
+  const bool two = use_gemm2(max_m, min_n, block_n);
+  for (int g = 0; g < groups; ++g) {
+    const char* err = fill_problem(P.prob[g], specs[g], a_terms, w_terms, two ? GEMM2_BLOCK_N : block_n);
     if (err) return set_error(ECHR_ERR_CUDA, "%s: %s", what, err);
     if (specs[g].M > max_m) max_m = specs[g].M;
     if (specs[g].N > max_n) max_n = specs[g].N;
   }
   if (max_m == 0) return ECHR_OK;
-  cudaError_t e = gemm_launch(P, groups, max_m, max_n, a_terms, w_terms, block_n, epi, topk, st);
+  cudaError_t e = two ? gemm2_launch(P, groups, a_terms, w_terms, epi, topk, num_sms(), st)
+                      : gemm_launch(P, groups, max_m, max_n, a_terms, w_terms, block_n, epi, topk, st);
   if (e != cudaSuccess) return set_error(ECHR_ERR_CUDA, "%s: launch failed: %s", what, cudaGetErrorString(e));
   count_launch();
   return ECHR_OK;
@@ -299,7 +334,8 @@ static void batch_layout(echr_batch* b, Arena& a) {
   const echr_model* m = b->model;
   const int ap = m->cfg.a_terms;
   const int S = m->cfg.seq_length;
-  const int n_tiles = ((m->V1 + 127) / 128) * (128 / LOGIT_GROUP);  // partial records per row
+  const int g1 = gemm1_logit_groups(m->V1), g2 = gemm2_logit_groups(m->V1);
+  const int n_tiles = g1 > g2 ? g1 : g2;  // partial records per row (either GEMM variant)
   b->c3d = a.take<float>((size_t)c.max_clips * ECHR_VIDEO_DIM);
   b->tap = a.take<float>((size_t)c.max_events * HID);
   b->lda = a.take<float>((size_t)c.max_videos * ECHR_LDA_DIM);

@@ -140,6 +140,9 @@ cudaError_t launch_finalize_tf(const echr_batch* b, int step, const int32_t* seq
 cudaError_t launch_load_state(const echr_batch* b, int rows, const int32_t* it, const float* h_in, cudaStream_t st);
 cudaError_t launch_export_state(const echr_batch* b, int rows, float* h_out, cudaStream_t st);
 void count_launch(int n = 1);
+// partial records per row the logit GEMM writes when it runs over `rows` decode rows (depends on the
+// GEMM variant the engine picks for that row count)
+int logit_groups_for(const echr_model* m, int rows);
 constexpr int TRACE_SLOTS = 1024;
 // next trace slot of this batch for a kernel of `kind` (0 h2att, 1 attention, 2 gates, 3 logits, 4 finalize,
 // 5 other); returns -1 / nullptr when tracing is off

@@ -1,6 +1,7 @@
 // Host side of the tcgen05 GEMM: tensor-map encoding (driver entry point fetched at run time so
 // the library has no link-time libcuda dependency) and the template dispatch table.
 #include "gemm_tc.cuh"
+#include "gemm_tc2.cuh"
 #include "util.cuh"
 
 #include <mutex>
@@ -81,6 +82,44 @@ cudaError_t gemm_launch(const GemmParams& P, int groups, int max_m, int max_n, i
   if (a_terms == 1 && w_terms == 1) return launch_aw<1, 1>(P, grid, block_n, epi, topk, stream);
   if (a_terms == 2 && w_terms == 1) return launch_aw<2, 1>(P, grid, block_n, epi, topk, stream);
   if (a_terms == 2 && w_terms == 2) return launch_aw<2, 2>(P, grid, block_n, epi, topk, stream);
+  return cudaErrorInvalidValue;
+}
+
+// ---------------------------------------------------------------- persistent 128 x 256 kernel
+template <int A, int W, int EPI, int TOPK>
+static cudaError_t launch_two(const GemmParams& P, int groups, int total_tiles, int num_sms, cudaStream_t stream) {
+  using Cfg = Gemm2Cfg<A, W>;
+  auto kern = gemm_tc2_kernel<A, W, EPI, TOPK>;
+  static bool attr_set = false;  // per instantiation
+  if (!attr_set) {
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES);
+    if (e != cudaSuccess) return e;
+    attr_set = true;
+  }
+  const int grid = total_tiles < num_sms ? total_tiles : num_sms;
+  return launch_pdl(kern, dim3(grid), dim3(GEMM_THREADS), Cfg::SMEM_BYTES, stream, P, groups, total_tiles);
+}
+
+template <int A, int W>
+static cudaError_t launch_two_aw(const GemmParams& P, int groups, int total, int epi, int topk, int num_sms,
+                                 cudaStream_t stream) {
+  if (epi == EPI_STORE) return launch_two<A, W, EPI_STORE, 1>(P, groups, total, num_sms, stream);
+  if (epi == EPI_LSTM) return launch_two<A, W, EPI_LSTM, 1>(P, groups, total, num_sms, stream);
+  if (epi == EPI_LOGITS && topk == 1) return launch_two<A, W, EPI_LOGITS, 1>(P, groups, total, num_sms, stream);
+  if (epi == EPI_LOGITS && topk == 4) return launch_two<A, W, EPI_LOGITS, 4>(P, groups, total, num_sms, stream);
+  return cudaErrorInvalidValue;
+}
+
+cudaError_t gemm2_launch(const GemmParams& P, int groups, int a_terms, int w_terms, int epi, int topk,
+                         int num_sms, cudaStream_t stream) {
+  if (groups < 1 || groups > GEMM_MAX_GROUPS) return cudaErrorInvalidValue;
+  int total = 0;
+  for (int g = 0; g < groups; ++g)
+    total += ((P.prob[g].M + GEMM_BLOCK_M - 1) / GEMM_BLOCK_M) * ((P.prob[g].N + GEMM2_BLOCK_N - 1) / GEMM2_BLOCK_N);
+  if (total <= 0) return cudaSuccess;
+  if (a_terms == 1 && w_terms == 1) return launch_two_aw<1, 1>(P, groups, total, epi, topk, num_sms, stream);
+  if (a_terms == 2 && w_terms == 1) return launch_two_aw<2, 1>(P, groups, total, epi, topk, num_sms, stream);
+  if (a_terms == 2 && w_terms == 2) return launch_two_aw<2, 2>(P, groups, total, epi, topk, num_sms, stream);
   return cudaErrorInvalidValue;
 }
 

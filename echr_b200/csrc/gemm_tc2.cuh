@@ -1,0 +1,412 @@
+// Persistent tcgen05 GEMM for large row counts (throughput regime):  D[M x N] = A[M x K] * W[N x K]^T
+//
+// Same operands, plane products and epilogues as gemm_tc.cuh, different schedule:
+//   * 128 x 256 output tiles (UMMA M=128, N=256): per k-block a CTA brings in A 16 KB/plane + W 32 KB/plane
+//     for twice the tensor work of the 128 x 128 kernel, i.e. 1/3 fewer L2->SM bytes per FLOP — the
+//     per-phase trace of the 128 x 128 kernel showed its main loop running at 0.42 us per k-block
+//     against 0.26 us of tensor time, bound by operand traffic.
+//   * persistent: one CTA per SM walks a static round-robin list of tiles (all problems of the launch
+//     flattened; m fastest so that CTAs running together share the same weight tile).
+//   * two TMEM accumulators (2 x 256 columns = all of TMEM): the epilogue of tile i overlaps the main
+//     loop of tile i+1 (tmem_full / tmem_empty mbarriers), the TMA ring never drains between tiles.
+// Warp roles: 0 TMA producer, 1 MMA issuer, 2 TMEM allocator, 4..11 epilogue (two warps per TMEM lane
+// quarter; a thread owns one output row x 128 columns).
+#pragma once
+#include "gemm_tc.cuh"
+
+namespace echr {
+
+constexpr int GEMM2_BLOCK_N = 256;
+
+template <int A_TERMS, int W_TERMS>
+struct Gemm2Cfg {
+  static constexpr int A_PLANE_BYTES = GEMM_BLOCK_M * GEMM_BLOCK_K * 2;   // 16 KB
+  static constexpr int W_PLANE_BYTES = GEMM2_BLOCK_N * GEMM_BLOCK_K * 2;  // 32 KB
+  static constexpr int STAGE_BYTES = A_TERMS * A_PLANE_BYTES + W_TERMS * W_PLANE_BYTES;
+  static constexpr int STAGES = (200 * 1024) / STAGE_BYTES;  // (1,1): 4, (2,1): 3, (2,2): 2
+  // stages | barriers (256 B) | bias tiles 2 x 256 floats
+  static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 /*align slack*/ + 256 + 2048;
+};
+
+struct Gemm2Tile {
+  int g, m_tile, n_tile;
+};
+
+// linear tile id -> (problem, m tile, n tile); m fastest
+__device__ __forceinline__ Gemm2Tile gemm2_tile(const GemmParams& P, int groups, int t) {
+  Gemm2Tile r;
+  r.g = 0;
+  for (; r.g < groups - 1; ++r.g) {
+    const int mt = (P.prob[r.g].M + GEMM_BLOCK_M - 1) / GEMM_BLOCK_M;
+    const int nt = (P.prob[r.g].N + GEMM2_BLOCK_N - 1) / GEMM2_BLOCK_N;
+    if (t < mt * nt) break;
+    t -= mt * nt;
+  }
+  const int mt = (P.prob[r.g].M + GEMM_BLOCK_M - 1) / GEMM_BLOCK_M;
+  r.n_tile = t / mt;
+  r.m_tile = t - r.n_tile * mt;
+  return r;
+}
+
+__device__ __forceinline__ void named_bar_sync(int id, int threads) {
+  asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(threads) : "memory");
+}
+
+template <int A_TERMS, int W_TERMS, int EPI, int TOPK>
+__global__ void __launch_bounds__(GEMM_THREADS, 1)
+gemm_tc2_kernel(const __grid_constant__ GemmParams P, int groups, int total_tiles) {
+  using Cfg = Gemm2Cfg<A_TERMS, W_TERMS>;
+  constexpr int BN = GEMM2_BLOCK_N;
+  trace_begin(P.trace, P.trace_slot);
+
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  const uint32_t bar_base = smem_base + Cfg::STAGES * Cfg::STAGE_BYTES;
+  // full[s] +8s | empty[s] +64+8s | tmem_full[b] +128+8b | tmem_empty[b] +144+8b | tmem ptr +160 | bias +256
+  auto full_bar = [&](int s) { return bar_base + 8u * s; };
+  auto empty_bar = [&](int s) { return bar_base + 64u + 8u * s; };
+  auto tmem_full_bar = [&](int b) { return bar_base + 128u + 8u * b; };
+  auto tmem_empty_bar = [&](int b) { return bar_base + 144u + 8u * b; };
+  const uint32_t tmem_ptr_smem = bar_base + 160u;
+  uint8_t* bar_generic = smem_raw + (bar_base - smem_u32(smem_raw));
+  volatile uint32_t* tmem_ptr_generic = reinterpret_cast<volatile uint32_t*>(bar_generic + 160);
+  float* sbias = reinterpret_cast<float*>(bar_generic + 256);  // [2][BN]
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+
+  if (warp == 0 && lane == 0) {
+    for (int g = 0; g < groups; ++g) {
+      tma_prefetch_desc(&P.prob[g].tmA);
+      tma_prefetch_desc(&P.prob[g].tmW);
+    }
+  }
+  if (warp == 1 && lane == 0) {
+    for (int s = 0; s < Cfg::STAGES; ++s) {
+      mbar_init(full_bar(s), 1);
+      mbar_init(empty_bar(s), 1);
+    }
+    for (int b = 0; b < 2; ++b) {
+      mbar_init(tmem_full_bar(b), 1);
+      mbar_init(tmem_empty_bar(b), GEMM_EPI_WARPS);
+    }
+    fence_mbar_init();
+  }
+  if (warp == 2) tmem_alloc<512>(tmem_ptr_smem);
+  tc_fence_before_sync();
+  __syncthreads();
+  tc_fence_after_sync();
+  const uint32_t tmem_base = *tmem_ptr_generic;
+
+  if (warp == 0) {
+    // ===================== TMA producer =====================
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
+        const Gemm2Tile tl = gemm2_tile(P, groups, t);
+        const GemmProblem& pb = P.prob[tl.g];
+        for (int kb = 0; kb < pb.num_kb; ++kb) {
+          mbar_wait(empty_bar(stage), phase ^ 1u);
+          const uint32_t sa = smem_base + stage * Cfg::STAGE_BYTES;
+          const uint32_t sw = sa + A_TERMS * Cfg::A_PLANE_BYTES;
+          const uint16_t kbe = pb.a_kb[kb];
+          const bool hi_only = A_TERMS == 2 && (kbe & GEMM_KB_HI_ONLY) != 0;
+          mbar_arrive_expect_tx(full_bar(stage), Cfg::STAGE_BYTES - (hi_only ? Cfg::A_PLANE_BYTES : 0));
+          const int a_col = static_cast<int>(kbe & 0x7fff) * GEMM_BLOCK_K;
+#pragma unroll
+          for (int p = 0; p < A_TERMS; ++p)
+            if (p == 0 || !hi_only)
+              tma_load_3d(sa + p * Cfg::A_PLANE_BYTES, &pb.tmA, full_bar(stage), a_col,
+                          tl.m_tile * GEMM_BLOCK_M, p);
+#pragma unroll
+          for (int p = 0; p < W_TERMS; ++p)
+            tma_load_3d(sw + p * Cfg::W_PLANE_BYTES, &pb.tmW, full_bar(stage), kb * GEMM_BLOCK_K,
+                        tl.n_tile * BN, p);
+          if (++stage == Cfg::STAGES) { stage = 0; phase ^= 1u; }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===================== MMA issuer (single thread) =====================
+    if (lane == 0) {
+      constexpr uint32_t idesc = umma_idesc_bf16_m128(BN);
+      int stage = 0;
+      uint32_t phase = 0;
+      int it = 0;
+      for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, ++it) {
+        const Gemm2Tile tl = gemm2_tile(P, groups, t);
+        const GemmProblem& pb = P.prob[tl.g];
+        const int buf = it & 1;
+        mbar_wait(tmem_empty_bar(buf), ((it >> 1) & 1) ^ 1u);  // epilogue drained this accumulator
+        tc_fence_after_sync();
+        const uint32_t acc = tmem_base + buf * BN;
+        uint32_t accum = 0;
+        for (int kb = 0; kb < pb.num_kb; ++kb) {
+          mbar_wait(full_bar(stage), phase);
+          tc_fence_after_sync();
+          const uint32_t sa = smem_base + stage * Cfg::STAGE_BYTES;
+          const uint32_t sw = sa + A_TERMS * Cfg::A_PLANE_BYTES;
+          const uint64_t a_hi = umma_desc_k_sw128(sa);
+          const uint64_t w_hi = umma_desc_k_sw128(sw);
+          const bool hi_only = A_TERMS == 2 && (pb.a_kb[kb] & GEMM_KB_HI_ONLY) != 0;
+#pragma unroll
+          for (int k = 0; k < GEMM_BLOCK_K / 16; ++k) {
+            const uint64_t koff = static_cast<uint64_t>(k * 2);
+            umma_bf16(acc, a_hi + koff, w_hi + koff, idesc, accum);
+            accum = 1;
+            if (A_TERMS == 2 && !hi_only) {
+              const uint64_t a_lo = umma_desc_k_sw128(sa + Cfg::A_PLANE_BYTES);
+              umma_bf16(acc, a_lo + koff, w_hi + koff, idesc, 1);
+            }
+            if (W_TERMS == 2) {
+              const uint64_t w_lo = umma_desc_k_sw128(sw + Cfg::W_PLANE_BYTES);
+              umma_bf16(acc, a_hi + koff, w_lo + koff, idesc, 1);
+            }
+          }
+          umma_commit(empty_bar(stage));
+          if (++stage == Cfg::STAGES) { stage = 0; phase ^= 1u; }
+        }
+        umma_commit(tmem_full_bar(buf));
+      }
+    }
+  } else if (warp >= 4) {
+    // ===================== epilogue =====================
+    constexpr int HALF = BN / 2;  // 128 columns per thread
+    constexpr int NCH = HALF / 32;
+    const int q = warp & 3;
+    const int half = (warp - 4) >> 2;
+    const int hc0 = half * HALF;
+    const int et = threadIdx.x - 128;  // 0..255
+    int it = 0;
+    for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, ++it) {
+      const Gemm2Tile tl = gemm2_tile(P, groups, t);
+      const GemmProblem& pb = P.prob[tl.g];
+      const int buf = it & 1;
+      const int col0 = tl.n_tile * BN;
+      const int row = tl.m_tile * GEMM_BLOCK_M + q * 32 + lane;
+      const bool row_ok = row < pb.M;
+      float* sb = sbias + buf * BN;
+      // bias tile -> smem.  The buffer was last read two tiles ago; every epilogue thread has passed
+      // the named barrier of the previous tile since then.
+      sb[et] = (pb.bias != nullptr && col0 + et < pb.N) ? __ldg(pb.bias + col0 + et) : 0.f;
+      named_bar_sync(1, GEMM_EPI_WARPS * 32);
+      const uint32_t t_row = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + buf * BN + hc0;
+      mbar_wait(tmem_full_bar(buf), (it >> 1) & 1);
+      tc_fence_after_sync();
+
+      if constexpr (EPI == EPI_STORE) {
+        const int act = pb.act;
+#pragma unroll 1
+        for (int c = 0; c < NCH; ++c) {
+          float v[32];
+          tmem_ld_32x32(t_row + c * 32, v);
+          tmem_ld_wait();
+          const int tc = hc0 + c * 32;
+          const int cb = col0 + tc;
+          if (row_ok && cb < pb.N) {
+#pragma unroll
+            for (int i = 0; i < 32; i += 4) {
+              const float4 b4 = *reinterpret_cast<const float4*>(sb + tc + i);
+              v[i] += b4.x; v[i + 1] += b4.y; v[i + 2] += b4.z; v[i + 3] += b4.w;
+            }
+            if (act == ACT_TANH) {
+#pragma unroll
+              for (int i = 0; i < 32; ++i) v[i] = tanh_fast_acc(v[i]);
+            } else if (act == ACT_EXP2X) {
+#pragma unroll
+              for (int i = 0; i < 32; ++i) v[i] = __expf(2.0f * fminf(fmaxf(v[i], -40.f), 40.f));
+            }
+            const int valid = min(32, pb.N - cb);
+            if (pb.out_f32 != nullptr) {
+              float* o = pb.out_f32 + static_cast<long long>(row) * pb.ld_f32 + cb;
+              if (valid == 32 && ((reinterpret_cast<uintptr_t>(o) & 15) == 0)) {
+#pragma unroll
+                for (int i = 0; i < 32; i += 4)
+                  *reinterpret_cast<float4*>(o + i) = make_float4(v[i], v[i + 1], v[i + 2], v[i + 3]);
+              } else {
+                for (int i = 0; i < 32; ++i)
+                  if (i < valid) o[i] = v[i];
+              }
+            }
+            if (pb.out_hi != nullptr) {
+              __nv_bfloat16* oh = pb.out_hi + static_cast<long long>(row) * pb.ld_bf + cb;
+              __nv_bfloat16* ol =
+                  pb.out_lo ? pb.out_lo + static_cast<long long>(row) * pb.ld_bf + cb : nullptr;
+              store_planes32(v, oh, ol, valid);
+            }
+          }
+        }
+      } else if constexpr (EPI == EPI_LSTM) {
+        const int H = pb.hidden;
+        const bool has_rbias = pb.row_bias != nullptr;
+#pragma unroll 1
+        for (int c = 0; c < NCH; ++c) {
+          const int tc = hc0 + c * 32;
+          const int j0 = (col0 + tc) >> 2;  // first hidden unit of this chunk (8 units)
+          float cprev[8];
+          float bb[32];
+          if (row_ok) {
+            const float4* cp = reinterpret_cast<const float4*>(pb.c_in + static_cast<long long>(row) * H + j0);
+            const float4 c0 = __ldg(cp), c1 = __ldg(cp + 1);
+            cprev[0] = c0.x; cprev[1] = c0.y; cprev[2] = c0.z; cprev[3] = c0.w;
+            cprev[4] = c1.x; cprev[5] = c1.y; cprev[6] = c1.z; cprev[7] = c1.w;
+            if (has_rbias) {
+              const float4* rp = reinterpret_cast<const float4*>(
+                  pb.row_bias + static_cast<long long>(row) * pb.ld_row_bias + col0 + tc);
+#pragma unroll
+              for (int i = 0; i < 8; ++i) {
+                const float4 r4 = __ldg(rp + i);
+                bb[4 * i] = r4.x; bb[4 * i + 1] = r4.y; bb[4 * i + 2] = r4.z; bb[4 * i + 3] = r4.w;
+              }
+            } else {
+#pragma unroll
+              for (int i = 0; i < 32; i += 4) {
+                const float4 b4 = *reinterpret_cast<const float4*>(sb + tc + i);
+                bb[i] = b4.x; bb[i + 1] = b4.y; bb[i + 2] = b4.z; bb[i + 3] = b4.w;
+              }
+            }
+          }
+          float v[32];
+          tmem_ld_32x32(t_row + c * 32, v);
+          tmem_ld_wait();
+          if (row_ok) {
+            float cn[8];
+            __align__(16) __nv_bfloat16 hh[8];
+            __align__(16) __nv_bfloat16 hl[8];
+#pragma unroll
+            for (int u = 0; u < 8; ++u) {
+              const float gi = sigmoid_fast(v[4 * u + 0] + bb[4 * u + 0]);
+              const float gf = sigmoid_fast(v[4 * u + 1] + bb[4 * u + 1]);
+              const float gg = tanh_fast_acc(v[4 * u + 2] + bb[4 * u + 2]);
+              const float go = sigmoid_fast(v[4 * u + 3] + bb[4 * u + 3]);
+              const float cc = gf * cprev[u] + gi * gg;
+              cn[u] = cc;
+              split_bf16(go * tanh_fast_acc(cc), hh[u], hl[u]);
+            }
+            float4* co = reinterpret_cast<float4*>(pb.c_out + static_cast<long long>(row) * H + j0);
+            co[0] = make_float4(cn[0], cn[1], cn[2], cn[3]);
+            co[1] = make_float4(cn[4], cn[5], cn[6], cn[7]);
+            *reinterpret_cast<uint4*>(pb.out_hi + static_cast<long long>(row) * pb.ld_bf + j0) =
+                *reinterpret_cast<const uint4*>(hh);
+            if (pb.out_lo != nullptr)
+              *reinterpret_cast<uint4*>(pb.out_lo + static_cast<long long>(row) * pb.ld_bf + j0) =
+                  *reinterpret_cast<const uint4*>(hl);
+          }
+        }
+      } else {  // EPI_LOGITS: one record per (row, 64-column group); this thread owns two groups
+        const int n_groups = ((pb.N + BN - 1) / BN) * (BN / LOGIT_GROUP);
+#pragma unroll 1
+        for (int gq = 0; gq < HALF / LOGIT_GROUP; ++gq) {
+          float tv[TOPK];
+          int ti[TOPK];
+#pragma unroll
+          for (int k = 0; k < TOPK; ++k) { tv[k] = -INFINITY; ti[k] = 0x7fffffff; }
+          const int gc0 = hc0 + gq * LOGIT_GROUP;  // first column of the group within the tile
+          const int gcol0 = col0 + gc0;
+          const bool full = gcol0 + LOGIT_GROUP <= pb.N;
+#pragma unroll 1
+          for (int c = 0; c < LOGIT_GROUP / 32; ++c) {
+            float v[32];
+            tmem_ld_32x32(t_row + gq * LOGIT_GROUP + c * 32, v);
+            tmem_ld_wait();
+            const int tc = gc0 + c * 32;
+            const int cb = col0 + tc;
+#pragma unroll
+            for (int i = 0; i < 32; i += 4) {
+              const float4 b4 = *reinterpret_cast<const float4*>(sb + tc + i);
+              v[i] += b4.x; v[i + 1] += b4.y; v[i + 2] += b4.z; v[i + 3] += b4.w;
+            }
+            if (!full) {
+#pragma unroll
+              for (int i = 0; i < 32; ++i)
+                if (cb + i >= pb.N) v[i] = -INFINITY;
+            }
+            if constexpr (TOPK == 1) {
+#pragma unroll
+              for (int i = 0; i < 32; ++i)
+                if (v[i] > tv[0]) { tv[0] = v[i]; ti[0] = cb + i; }
+            } else {
+#pragma unroll
+              for (int i = 0; i < 32; ++i) {
+                const float x = v[i];
+                const int col = cb + i;
+                if (x > tv[TOPK - 1]) {
+#pragma unroll
+                  for (int k = TOPK - 1; k >= 1; --k) {
+                    const bool shift = x > tv[k - 1];
+                    const bool here = !shift && (x > tv[k]);
+                    tv[k] = shift ? tv[k - 1] : (here ? x : tv[k]);
+                    ti[k] = shift ? ti[k - 1] : (here ? col : ti[k]);
+                  }
+                  if (x > tv[0]) { tv[0] = x; ti[0] = col; }
+                }
+              }
+            }
+            if (row_ok && pb.logits_out != nullptr) {
+              float* o = pb.logits_out + static_cast<long long>(row) * pb.ld_logits + cb;
+              for (int i = 0; i < 32; ++i)
+                if (cb + i < pb.N) o[i] = v[i];
+            }
+          }
+          float se = 0.f;
+          const float m2 = tv[0] * 1.4426950408889634f;
+#pragma unroll 1
+          for (int c = 0; c < LOGIT_GROUP / 32; ++c) {
+            float v[32];
+            tmem_ld_32x32(t_row + gq * LOGIT_GROUP + c * 32, v);
+            tmem_ld_wait();
+            const int tc = gc0 + c * 32;
+            const int cb = col0 + tc;
+            float s4[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+            for (int i = 0; i < 32; i += 4) {
+              const float4 b4 = *reinterpret_cast<const float4*>(sb + tc + i);
+              const float e0 = exp2f(fmaf(v[i] + b4.x, 1.4426950408889634f, -m2));
+              const float e1 = exp2f(fmaf(v[i + 1] + b4.y, 1.4426950408889634f, -m2));
+              const float e2 = exp2f(fmaf(v[i + 2] + b4.z, 1.4426950408889634f, -m2));
+              const float e3 = exp2f(fmaf(v[i + 3] + b4.w, 1.4426950408889634f, -m2));
+              s4[0] += (full || cb + i < pb.N) ? e0 : 0.f;
+              s4[1] += (full || cb + i + 1 < pb.N) ? e1 : 0.f;
+              s4[2] += (full || cb + i + 2 < pb.N) ? e2 : 0.f;
+              s4[3] += (full || cb + i + 3 < pb.N) ? e3 : 0.f;
+            }
+            se += (s4[0] + s4[1]) + (s4[2] + s4[3]);
+          }
+          if (row_ok) {
+            float* rec = pb.partial + (static_cast<long long>(row) * n_groups + tl.n_tile * (BN / LOGIT_GROUP) +
+                                       gc0 / LOGIT_GROUP) * LogitRec<TOPK>::WORDS;
+            if (gcol0 >= pb.N) se = 0.f;
+            rec[0] = se;
+#pragma unroll
+            for (int k = 0; k < TOPK; ++k) {
+              rec[1 + k] = tv[k];
+              rec[1 + TOPK + k] = __int_as_float(ti[k]);
+            }
+          }
+        }
+      }
+      // this accumulator may be overwritten by the MMAs of tile it+2
+      tc_fence_before_sync();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(tmem_empty_bar(buf));
+    }
+  }
+
+  tc_fence_before_sync();
+  __syncthreads();
+  if (warp == 2) {
+    tc_fence_after_sync();
+    tmem_dealloc<512>(tmem_base);
+  }
+  trace_end(P.trace, P.trace_slot);
+}
+
+// records per row the logit epilogue of this kernel writes for a vocabulary of n columns
+inline int gemm2_logit_groups(int n) { return ((n + GEMM2_BLOCK_N - 1) / GEMM2_BLOCK_N) * (GEMM2_BLOCK_N / LOGIT_GROUP); }
+inline int gemm1_logit_groups(int n) { return ((n + 127) / 128) * (128 / LOGIT_GROUP); }
+
+cudaError_t gemm2_launch(const GemmParams& P, int groups, int a_terms, int w_terms, int epi, int topk,
+                         int num_sms, cudaStream_t stream);
+
+}  // namespace echr

@@ -23,15 +23,16 @@ __device__ __forceinline__ float rcp_fast(float x) {
   return y;
 }
 
-constexpr int ATT_THREADS = 512;
+constexpr int ATT_THREADS = 512;        // latency-bound launches and long windows
+constexpr int ATT_THREADS_SMALL = 256;  // many short windows: more CTAs per SM
 constexpr int ATT_MAX_L = 1024;
 
 // One CTA per decode row.  Pass 1: one warp per clip, lanes across the 512 hidden units (coalesced
 // 16-byte loads), score_l = alpha . tanh(P_l + q).  Softmax over the window (the reference's
 // softmax-then-mask-then-renormalise over the padded length, OldModel_NEW.py:394-397, is the same
 // function).  Pass 2: threads across the 500 feature columns, att = sum_l w_l * clip_l.
-template <bool BF16>
-__global__ void __launch_bounds__(ATT_THREADS)
+template <bool BF16, int THREADS>
+__global__ void __launch_bounds__(THREADS)
 attention_kernel(const float* __restrict__ q, const void* __restrict__ proj_v,
                  const void* __restrict__ clip_v, long long ld_clip, const float* __restrict__ alpha,
                  const int32_t* __restrict__ row_start, const int32_t* __restrict__ row_len,
@@ -39,7 +40,7 @@ attention_kernel(const float* __restrict__ q, const void* __restrict__ proj_v,
                  long long ld_bf, unsigned long long* trace, int trace_slot) {
   trace_begin(trace, trace_slot);
   __shared__ float sc[ATT_MAX_L];
-  __shared__ __align__(16) float red[ATT_THREADS / 64][512];
+  __shared__ __align__(16) float red[THREADS / 64][512];
   const int r = blockIdx.x;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   pdl_trigger();
@@ -76,7 +77,7 @@ attention_kernel(const float* __restrict__ q, const void* __restrict__ proj_v,
       }
     }
   };
-  constexpr int NW = ATT_THREADS / 32;
+  constexpr int NW = THREADS / 32;
   for (int l = warp; l < L; l += 2 * NW) {
     const int l2 = l + NW;
     const bool two = l2 < L;
@@ -109,18 +110,18 @@ attention_kernel(const float* __restrict__ q, const void* __restrict__ proj_v,
   sum = warp_sum(sum);
   __syncthreads();
   const float inv = 1.0f / sum;
-  for (int l = threadIdx.x; l < L; l += ATT_THREADS) sc[l] = expf(sc[l] - mx) * inv;
+  for (int l = threadIdx.x; l < L; l += THREADS) sc[l] = expf(sc[l] - mx) * inv;
   __syncthreads();
   // pass 2
   if (BF16) {
-    // 64 threads per clip row (8 bf16 each), ATT_THREADS/64 clip groups
+    // 64 threads per clip row (8 bf16 each), THREADS/64 clip groups
     const int grp = threadIdx.x >> 6, t = threadIdx.x & 63;
     float acc[8];
 #pragma unroll
     for (int i = 0; i < 8; ++i) acc[i] = 0.f;
     const bf16* cbase = reinterpret_cast<const bf16*>(clip_v) + (long long)s0 * ld_clip + 8 * t;
 #pragma unroll 4
-    for (int l = grp; l < L; l += ATT_THREADS / 64) {
+    for (int l = grp; l < L; l += THREADS / 64) {
       const uint4 u = __ldg(reinterpret_cast<const uint4*>(cbase + (long long)l * ld_clip));
       const float w = sc[l];
       const __nv_bfloat162* b = reinterpret_cast<const __nv_bfloat162*>(&u);
@@ -133,13 +134,13 @@ attention_kernel(const float* __restrict__ q, const void* __restrict__ proj_v,
 #pragma unroll
     for (int i = 0; i < 8; ++i) red[grp][8 * t + i] = acc[i];
   } else {
-    // 128 threads per clip row (4 floats each, 125 active), ATT_THREADS/128 clip groups
+    // 128 threads per clip row (4 floats each, 125 active), THREADS/128 clip groups
     const int grp = threadIdx.x >> 7, t = threadIdx.x & 127;
     float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
     if (t < ECHR_VIDEO_DIM / 4) {
       const float* cbase = reinterpret_cast<const float*>(clip_v) + (long long)s0 * ld_clip + 4 * t;
 #pragma unroll 4
-      for (int l = grp; l < L; l += ATT_THREADS / 128) {
+      for (int l = grp; l < L; l += THREADS / 128) {
         const float4 c = __ldg(reinterpret_cast<const float4*>(cbase + (long long)l * ld_clip));
         const float w = sc[l];
         acc.x = fmaf(w, c.x, acc.x); acc.y = fmaf(w, c.y, acc.y);
@@ -149,10 +150,10 @@ attention_kernel(const float* __restrict__ q, const void* __restrict__ proj_v,
     *reinterpret_cast<float4*>(&red[grp][4 * t]) = acc;
   }
   __syncthreads();
-  for (int c = threadIdx.x; c < ECHR_VIDEO_DIM; c += ATT_THREADS) {
+  for (int c = threadIdx.x; c < ECHR_VIDEO_DIM; c += THREADS) {
     float v = 0.f;
 #pragma unroll
-    for (int g = 0; g < (BF16 ? ATT_THREADS / 64 : ATT_THREADS / 128); ++g) v += red[g][c];
+    for (int g = 0; g < (BF16 ? THREADS / 64 : THREADS / 128); ++g) v += red[g][c];
     if (out_f32 != nullptr) out_f32[(long long)r * ECHR_VIDEO_DIM + c] = v;
     if (out_hi != nullptr) {
       bf16 h, l2;
@@ -172,8 +173,8 @@ attention_kernel(const float* __restrict__ q, const void* __restrict__ proj_v,
 constexpr int ATT_STAGE_BYTES = 200 * 1024;
 constexpr int ATT_BULK_CLIPS = 16;  // clips per bulk copy
 
-template <bool BF16>
-__global__ void __launch_bounds__(ATT_THREADS)
+template <bool BF16, int THREADS>
+__global__ void __launch_bounds__(THREADS)
 attention_staged_kernel(const float* __restrict__ q, const void* __restrict__ proj_v,
                         const void* __restrict__ clip_v, long long ld_clip,
                         const float* __restrict__ alpha, const int32_t* __restrict__ row_start,
@@ -185,7 +186,7 @@ attention_staged_kernel(const float* __restrict__ q, const void* __restrict__ pr
   constexpr int CLIP_ROW = BF16 ? CLIP_PAD : ECHR_VIDEO_DIM;  // elements per staged clip row
   extern __shared__ __align__(128) uint8_t att_smem[];
   __shared__ float sc[ATT_MAX_L];
-  __shared__ __align__(16) float red[ATT_THREADS / 64][512];
+  __shared__ __align__(16) float red[THREADS / 64][512];
   __shared__ __align__(8) uint64_t bars[2];
   T* sproj = reinterpret_cast<T*>(att_smem);                       // [max_len][512]
   T* sclip = sproj + (size_t)max_len * HID;                        // [max_len][CLIP_ROW]
@@ -224,7 +225,7 @@ attention_staged_kernel(const float* __restrict__ q, const void* __restrict__ pr
   }
   __syncthreads();  // barrier init visible to every thread
   mbar_wait(bar_p, 0);
-  for (int l = warp; l < L; l += ATT_THREADS / 32) {
+  for (int l = warp; l < L; l += THREADS / 32) {
     float s = 0.f;
     const T* prow = sproj + (size_t)l * HID;
 #pragma unroll
@@ -256,7 +257,7 @@ attention_staged_kernel(const float* __restrict__ q, const void* __restrict__ pr
   sum = warp_sum(sum);
   __syncthreads();
   const float inv = 1.0f / sum;
-  for (int l = threadIdx.x; l < L; l += ATT_THREADS) sc[l] = expf(sc[l] - mx) * inv;
+  for (int l = threadIdx.x; l < L; l += THREADS) sc[l] = expf(sc[l] - mx) * inv;
   __syncthreads();
   mbar_wait(bar_c, 0);
   if (BF16) {
@@ -265,7 +266,7 @@ attention_staged_kernel(const float* __restrict__ q, const void* __restrict__ pr
 #pragma unroll
     for (int i = 0; i < 8; ++i) acc[i] = 0.f;
     const bf16* cbase = reinterpret_cast<const bf16*>(sclip) + 8 * t;
-    for (int l = grp; l < L; l += ATT_THREADS / 64) {
+    for (int l = grp; l < L; l += THREADS / 64) {
       const uint4 u = *reinterpret_cast<const uint4*>(cbase + (size_t)l * CLIP_ROW);
       const float w = sc[l];
       const __nv_bfloat162* b = reinterpret_cast<const __nv_bfloat162*>(&u);
@@ -282,7 +283,7 @@ attention_staged_kernel(const float* __restrict__ q, const void* __restrict__ pr
     float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
     if (t < ECHR_VIDEO_DIM / 4) {
       const float* cbase = reinterpret_cast<const float*>(sclip) + 4 * t;
-      for (int l = grp; l < L; l += ATT_THREADS / 128) {
+      for (int l = grp; l < L; l += THREADS / 128) {
         const float4 c = *reinterpret_cast<const float4*>(cbase + (size_t)l * CLIP_ROW);
         const float w = sc[l];
         acc.x = fmaf(w, c.x, acc.x); acc.y = fmaf(w, c.y, acc.y);
@@ -292,10 +293,10 @@ attention_staged_kernel(const float* __restrict__ q, const void* __restrict__ pr
     *reinterpret_cast<float4*>(&red[grp][4 * t]) = acc;
   }
   __syncthreads();
-  for (int c = threadIdx.x; c < ECHR_VIDEO_DIM; c += ATT_THREADS) {
+  for (int c = threadIdx.x; c < ECHR_VIDEO_DIM; c += THREADS) {
     float v = 0.f;
 #pragma unroll
-    for (int g = 0; g < (BF16 ? ATT_THREADS / 64 : ATT_THREADS / 128); ++g) v += red[g][c];
+    for (int g = 0; g < (BF16 ? THREADS / 64 : THREADS / 128); ++g) v += red[g][c];
     if (out_f32 != nullptr) out_f32[(long long)r * ECHR_VIDEO_DIM + c] = v;
     if (out_hi != nullptr) {
       bf16 h, l2;
@@ -328,23 +329,32 @@ cudaError_t launch_attention(const float* q, const void* proj, const void* clip,
   if (staged) {
     static size_t attr[2] = {0, 0};
     if (stage > attr[clip_bf16 ? 1 : 0]) {
-      e = clip_bf16 ? cudaFuncSetAttribute(attention_staged_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, ATT_STAGE_BYTES)
-                    : cudaFuncSetAttribute(attention_staged_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, ATT_STAGE_BYTES);
+      e = clip_bf16 ? cudaFuncSetAttribute(attention_staged_kernel<true, ATT_THREADS>, cudaFuncAttributeMaxDynamicSharedMemorySize, ATT_STAGE_BYTES)
+                    : cudaFuncSetAttribute(attention_staged_kernel<false, ATT_THREADS>, cudaFuncAttributeMaxDynamicSharedMemorySize, ATT_STAGE_BYTES);
       if (e != cudaSuccess) return e;
       attr[clip_bf16 ? 1 : 0] = ATT_STAGE_BYTES;
     }
     if (clip_bf16)
-      e = launch_pdl(attention_staged_kernel<true>, dim3((unsigned)rows), dim3(ATT_THREADS), stage, st, q, proj, clip,
+      e = launch_pdl(attention_staged_kernel<true, ATT_THREADS>, dim3((unsigned)rows), dim3(ATT_THREADS), stage, st, q, proj, clip,
                      (long long)ld_clip, alpha, row_start, row_len, out_f32, out_hi, out_lo, (long long)ld_bf, max_len, trace, trace_slot);
     else
-      e = launch_pdl(attention_staged_kernel<false>, dim3((unsigned)rows), dim3(ATT_THREADS), stage, st, q, proj, clip,
+      e = launch_pdl(attention_staged_kernel<false, ATT_THREADS>, dim3((unsigned)rows), dim3(ATT_THREADS), stage, st, q, proj, clip,
                      (long long)ld_clip, alpha, row_start, row_len, out_f32, out_hi, out_lo, (long long)ld_bf, max_len, trace, trace_slot);
-  } else if (clip_bf16) {
-    e = launch_pdl(attention_kernel<true>, dim3((unsigned)rows), dim3(ATT_THREADS), 0, st, q, proj, clip,
-                   (long long)ld_clip, alpha, row_start, row_len, out_f32, out_hi, out_lo, (long long)ld_bf, trace, trace_slot);
   } else {
-    e = launch_pdl(attention_kernel<false>, dim3((unsigned)rows), dim3(ATT_THREADS), 0, st, q, proj, clip,
-                   (long long)ld_clip, alpha, row_start, row_len, out_f32, out_hi, out_lo, (long long)ld_bf, trace, trace_slot);
+    // many short windows (throughput regime): 256-thread CTAs pack more rows per SM; otherwise 512
+    const bool small = rows > 148 * 4 && max_len > 0 && max_len <= 64;
+    if (clip_bf16 && small)
+      e = launch_pdl(attention_kernel<true, ATT_THREADS_SMALL>, dim3((unsigned)rows), dim3(ATT_THREADS_SMALL), 0, st, q, proj,
+                     clip, (long long)ld_clip, alpha, row_start, row_len, out_f32, out_hi, out_lo, (long long)ld_bf, trace, trace_slot);
+    else if (clip_bf16)
+      e = launch_pdl(attention_kernel<true, ATT_THREADS>, dim3((unsigned)rows), dim3(ATT_THREADS), 0, st, q, proj, clip,
+                     (long long)ld_clip, alpha, row_start, row_len, out_f32, out_hi, out_lo, (long long)ld_bf, trace, trace_slot);
+    else if (small)
+      e = launch_pdl(attention_kernel<false, ATT_THREADS_SMALL>, dim3((unsigned)rows), dim3(ATT_THREADS_SMALL), 0, st, q, proj,
+                     clip, (long long)ld_clip, alpha, row_start, row_len, out_f32, out_hi, out_lo, (long long)ld_bf, trace, trace_slot);
+    else
+      e = launch_pdl(attention_kernel<false, ATT_THREADS>, dim3((unsigned)rows), dim3(ATT_THREADS), 0, st, q, proj, clip,
+                     (long long)ld_clip, alpha, row_start, row_len, out_f32, out_hi, out_lo, (long long)ld_bf, trace, trace_slot);
   }
   count_launch();
   return e;
@@ -498,7 +508,7 @@ cudaError_t launch_finalize_greedy(echr_batch* b, int step, int32_t* tokens, flo
   const int rows = b->n_events;
   if (rows == 0) return cudaSuccess;
   const echr_model* m = b->model;
-  const int n_tiles = ((m->V1 + 127) / 128) * (128 / LOGIT_GROUP);
+  const int n_tiles = logit_groups_for(m, b->n_events);
   const PlaneMat& nxt = b->act[(step + 1) & 1];
   cudaError_t e = launch_pdl(finalize_greedy_kernel, dim3((rows + FIN_WARPS - 1) / FIN_WARPS), dim3(FIN_WARPS * 32), 0,
                              st, rows, n_tiles, step, m->cfg.seq_length, b->partial, m->embed.p,
@@ -536,7 +546,7 @@ cudaError_t launch_finalize_tf(const echr_batch* b, int step, const int32_t* seq
   const int rows = b->n_events;
   if (rows == 0) return cudaSuccess;
   const echr_model* m = b->model;
-  const int n_tiles = ((m->V1 + 127) / 128) * (128 / LOGIT_GROUP);
+  const int n_tiles = logit_groups_for(m, b->n_events);
   const PlaneMat& nxt = b->act[(step + 1) & 1];
   finalize_tf_kernel<<<(rows + FIN_WARPS - 1) / FIN_WARPS, FIN_WARPS * 32, 0, st>>>(
       rows, n_tiles, step, seq_cols, m->V1, b->partial, seq, m->embed.p, m->embed.plane_stride(), nxt.p,
@@ -766,7 +776,7 @@ cudaError_t launch_finalize_beam(const echr_batch* b, int beam, int step, int32_
   if (b->n_events == 0) return cudaSuccess;
   if (beam < 1 || beam > BEAM_MAX) return cudaErrorInvalidValue;
   const echr_model* m = b->model;
-  const int n_tiles = ((m->V1 + 127) / 128) * (128 / LOGIT_GROUP);
+  const int n_tiles = logit_groups_for(m, b->n_events * beam);
   const int S = m->cfg.seq_length;
   const long long rows = (long long)b->n_events * beam;
   const PlaneMat& nxt = b->act[(step + 1) & 1];

@@ -22,6 +22,10 @@ eng = m.engine
 for _ in range(3):
     eng.set_inputs(lay, c3d, tap, lda); eng.encode(); eng.decode_greedy()
 torch.cuda.synchronize()
+ev = [torch.cuda.Event(enable_timing=True) for _ in range(4)]
+ev[0].record(); eng.set_inputs(lay, c3d, tap, lda); ev[1].record(); eng.encode(); ev[2].record(); eng.decode_greedy(); ev[3].record()
+torch.cuda.synchronize()
+print("set_inputs %.3f ms, encode %.3f ms, decode %.3f ms" % (ev[0].elapsed_time(ev[1]), ev[1].elapsed_time(ev[2]), ev[2].elapsed_time(ev[3])))
 tr = eng.trace()
 print("kernels:", len(tr))
 for i, (k, s, e) in enumerate(tr):
