@@ -625,7 +625,6 @@ finalize_beam_kernel(int beam, int n_tiles, int step, int seq_len, const float* 
   __shared__ int cand_tok[BEAM_MAX][BEAM_MAX];
   __shared__ int sel_parent[BEAM_MAX], sel_tok[BEAM_MAX], sel_fin[BEAM_MAX];
   __shared__ float sel_lp[BEAM_MAX], sel_total[BEAM_MAX];
-  __shared__ __align__(16) float stage[BEAM_MAX * BEAM_SEG];  // 24 KB
   const int e = blockIdx.x;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int row0 = e * beam;
@@ -742,32 +741,47 @@ finalize_beam_kernel(int beam, int n_tiles, int step, int seq_len, const float* 
   bool identity = true;
   for (int n = 0; n < beam; ++n) identity = identity && (sel_parent[n] == n);
   if (identity) return;  // uniform across the CTA
-  // h planes: 1536 bf16 = 768 words per row
+  // Reorder h (bf16 planes of the next activation buffer) and c by parent slot.  A thread owns a column
+  // across all slots of the event (reads the <= 4 values, writes them permuted): no staging, no barriers.
+  int par[BEAM_MAX];
+#pragma unroll
+  for (int n = 0; n < BEAM_MAX; ++n) par[n] = n < beam ? sel_parent[n] : n;
   for (int p = 0; p < planes; ++p) {
-    uint32_t* st32 = reinterpret_cast<uint32_t*>(stage);
-    for (int i = threadIdx.x; i < beam * (BEAM_SEG / 2); i += blockDim.x) {
-      const int b = i / (BEAM_SEG / 2), c = i - b * (BEAM_SEG / 2);
-      st32[i] = *reinterpret_cast<const uint32_t*>(act_next + p * act_plane + (long long)(row0 + b) * ACT_LD + ACT_H + 2 * c);
+    bf16* base = act_next + p * act_plane + (long long)row0 * ACT_LD + ACT_H;
+    for (int c = threadIdx.x; c < BEAM_SEG / 8; c += blockDim.x) {  // 16-byte words
+      uint4 v[BEAM_MAX];
+#pragma unroll
+      for (int n = 0; n < BEAM_MAX; ++n)
+        if (n < beam) v[n] = *reinterpret_cast<const uint4*>(base + (long long)n * ACT_LD + 8 * c);
+#pragma unroll
+      for (int n = 0; n < BEAM_MAX; ++n) {
+        if (n < beam && par[n] != n) {
+          uint4 w = v[0];
+#pragma unroll
+          for (int q = 1; q < BEAM_MAX; ++q)
+            if (par[n] == q) w = v[q];
+          *reinterpret_cast<uint4*>(base + (long long)n * ACT_LD + 8 * c) = w;
+        }
+      }
     }
-    __syncthreads();
-    for (int i = threadIdx.x; i < beam * (BEAM_SEG / 2); i += blockDim.x) {
-      const int b = i / (BEAM_SEG / 2), c = i - b * (BEAM_SEG / 2);
-      *reinterpret_cast<uint32_t*>(act_next + p * act_plane + (long long)(row0 + b) * ACT_LD + ACT_H + 2 * c) =
-          st32[sel_parent[b] * (BEAM_SEG / 2) + c];
+  }
+  for (int c = threadIdx.x; c < BEAM_SEG / 4; c += blockDim.x) {  // float4 words of [layer][unit]
+    const int layer = (4 * c) / HID, u = 4 * c - layer * HID;
+    float* base = c_next + layer * c_layer_stride + (long long)row0 * HID + u;
+    float4 v[BEAM_MAX];
+#pragma unroll
+    for (int n = 0; n < BEAM_MAX; ++n)
+      if (n < beam) v[n] = *reinterpret_cast<const float4*>(base + (long long)n * HID);
+#pragma unroll
+    for (int n = 0; n < BEAM_MAX; ++n) {
+      if (n < beam && par[n] != n) {
+        float4 w = v[0];
+#pragma unroll
+        for (int q = 1; q < BEAM_MAX; ++q)
+          if (par[n] == q) w = v[q];
+        *reinterpret_cast<float4*>(base + (long long)n * HID) = w;
+      }
     }
-    __syncthreads();
-  }
-  // c state: [3][rows][512] fp32
-  for (int i = threadIdx.x; i < beam * BEAM_SEG; i += blockDim.x) {
-    const int b = i / BEAM_SEG, c = i - b * BEAM_SEG;
-    const int layer = c / HID, u = c - layer * HID;
-    stage[i] = c_next[layer * c_layer_stride + (long long)(row0 + b) * HID + u];
-  }
-  __syncthreads();
-  for (int i = threadIdx.x; i < beam * BEAM_SEG; i += blockDim.x) {
-    const int b = i / BEAM_SEG, c = i - b * BEAM_SEG;
-    const int layer = c / HID, u = c - layer * HID;
-    c_next[layer * c_layer_stride + (long long)(row0 + b) * HID + u] = stage[sel_parent[b] * BEAM_SEG + c];
   }
 }
 

@@ -191,3 +191,93 @@ def test_submodule_surfaces_match_oracle():
     beam_tok, beam_lp = m.lm_model.sample(video.to(DEV), event.to(DEV), clip.to(DEV), mask.to(DEV),
                                           opt={"beam_size": 3})
     assert tuple(beam_tok.shape) == (n, 30)
+
+
+# ----------------------------------------------------------------------------- edge cases
+def _oracle_greedy(sd, v, seq_length=30):
+    ctx = O.build_context(sd, v.tap_feats, v.c3d_feats, v.lda_feats, v.ind_select_list, v.soi_select_list)
+    s_ref, l_ref = O.greedy_decode(sd, *ctx, seq_length=seq_length)
+    tf = O.teacher_forced_logprobs(sd, *ctx, labels_of(s_ref))
+    return s_ref, l_ref, tf.topk(2, dim=2)[0].numpy()
+
+
+def test_edge_shapes_single_event_unit_spans_whole_video_and_empty_videos():
+    sd = helpers.state_dict("fp32")
+    m = model("fp32", "fp32")
+    base = synth.make_video(60, T=40, n_events=3)
+    one = synth.Video(base.tap_feats, base.c3d_feats, base.lda_feats, [39], [[0, 40]])        # 1 event = whole video
+    unit = synth.Video(base.tap_feats, base.c3d_feats, base.lda_feats, [0, 5, 39], [[0, 1], [5, 6], [39, 40]])  # 1-clip spans
+    dup = synth.Video(base.tap_feats, base.c3d_feats, base.lda_feats, [9, 9], [[2, 10], [2, 10]])  # identical proposals
+    none = synth.Video(base.tap_feats, base.c3d_feats, base.lda_feats, [], [])                 # no proposals
+    vids = [one, none, unit, dup, none]
+    out = m.caption_batch([helpers.video_tuple(v, DEV) for v in vids])
+    assert out[1] == ([], []) and out[4] == ([], [])
+    for v, (seq, logp) in zip(vids, out):
+        if v.n_events == 0:
+            continue
+        s_ref, l_ref, top2 = _oracle_greedy(sd, v)
+        helpers.check_tokens(seq.cpu().numpy(), s_ref.numpy(), top2, "edge")
+    # identical proposals decode identically
+    assert torch.equal(out[3][0][0], out[3][0][1])
+    # a batch with no events at all
+    assert m.caption_batch([helpers.video_tuple(none, DEV)]) == [([], [])]
+
+
+def test_workspace_growth_and_reuse():
+    sd = helpers.state_dict("fp32")
+    m = CaptionGenerator(echr_opt(), precision="fp32")
+    m.load_state_dict(sd, strict=True)
+    m = m.to(DEV)
+    small = [synth.make_video(70, n_events=2)]
+    big = [synth.make_video(71 + i, n_events=9, style="sst") for i in range(5)]
+    a1 = m.caption_batch([helpers.video_tuple(v, DEV) for v in small])
+    b1 = m.caption_batch([helpers.video_tuple(v, DEV) for v in big])      # grows the workspace, new graph
+    a2 = m.caption_batch([helpers.video_tuple(v, DEV) for v in small])    # smaller batch in the bigger workspace
+    b2 = m.caption_batch([helpers.video_tuple(v, DEV) for v in big])
+    assert torch.equal(a1[0][0], a2[0][0]) and torch.equal(a1[0][1], a2[0][1])
+    for x, y in zip(b1, b2):
+        assert torch.equal(x[0], y[0]) and torch.equal(x[1], y[1])
+    s_ref, _, top2 = _oracle_greedy(sd, small[0])
+    helpers.check_tokens(a2[0][0].cpu().numpy(), s_ref.numpy(), top2, "reuse")
+
+
+@pytest.mark.parametrize("beam", [2, 4])
+def test_beam_widths(beam):
+    sd = helpers.state_dict("fp32")
+    m = model("fp32", "fp32")
+    v = helpers.case_video("gt5")
+    tok, lp, score = m.caption_batch([helpers.video_tuple(v, DEV)], beam_size=beam)[0]
+    ctx = O.build_context(sd, v.tap_feats, v.c3d_feats, v.lda_feats, v.ind_select_list, v.soi_select_list)
+    t_ref, l_ref, s_ref = O.beam_search(sd, *ctx, beam=beam)
+    assert np.abs(score.cpu().numpy() - s_ref.numpy()).max() < 5e-3
+    same = (tok.cpu() == t_ref).all(1)
+    assert float(same.float().mean()) >= 0.5
+    assert np.allclose(lp.cpu().sum(1).numpy(), score.cpu().numpy(), atol=1e-3)
+
+
+def test_short_seq_length_and_small_vocab():
+    """CG_seq_length / CG_vocab_size are the two free sizes of the recipe."""
+    opt = echr_opt(CG_seq_length=12, CG_vocab_size=1000)
+    sd = synth.init_state_dict(opt, seed=3)
+    m = CaptionGenerator(opt, precision="fp32")
+    m.load_state_dict(sd, strict=True)
+    m = m.to(DEV)
+    v = synth.make_video(80, n_events=4)
+    seq, logp = m.caption_batch([helpers.video_tuple(v, DEV)])[0]
+    s_ref, l_ref, top2 = _oracle_greedy(sd, v, seq_length=12)
+    assert tuple(seq.shape) == tuple(s_ref.shape) == (4, 12)
+    helpers.check_tokens(seq.cpu().numpy(), s_ref.numpy(), top2, "short")
+    assert int(seq.max()) <= 1000
+
+
+def test_bad_inputs_raise():
+    from echr_b200._lib import EchrError
+    m = model("fp32", "fp32")
+    v = synth.make_video(81, T=30, n_events=2)
+    bad = synth.Video(v.tap_feats, v.c3d_feats, v.lda_feats, [5, 50], [[0, 5], [10, 31]])  # span beyond the video
+    with pytest.raises(EchrError):
+        m.caption_batch([helpers.video_tuple(bad, DEV)])
+    with pytest.raises(EchrError):
+        m.caption_batch([helpers.video_tuple(v, DEV)], beam_size=5)
+    # the engine still works afterwards
+    assert len(m.caption_batch([helpers.video_tuple(v, DEV)])[0][0]) == 2
