@@ -64,7 +64,7 @@ int echr_gemm_planes(const void* a, int64_t m, int64_t k, int64_t a_ld, int a_pl
   ECHR_REQUIRE((a_planes == 1 || a_planes == 2) && (w_planes == 1 || w_planes == 2) &&
                    !(a_planes == 1 && w_planes == 2),
                "echr_gemm_planes: unsupported plane combination a=%d w=%d", a_planes, w_planes);
-  ECHR_REQUIRE(block_n == 128 || block_n == 16 || block_n == 256, "echr_gemm_planes: block_n must be 16, 128 or 256 (persistent kernel)");
+  ECHR_REQUIRE(block_n == 128 || block_n == 64 || block_n == 32 || block_n == 16 || block_n == 256, "echr_gemm_planes: block_n must be 16, 32, 64, 128 or 256 (persistent kernel)");
   ECHR_REQUIRE(m < (1ll << 31) && n < (1ll << 31), "echr_gemm_planes: dimension too large");
   GemmParams P;
   memset(&P, 0, sizeof(P));

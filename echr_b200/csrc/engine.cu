@@ -104,6 +104,9 @@ struct GemmSpec {
   const float* row_bias = nullptr;
   long long ld_row_bias = 0;
   int hi_only_first = 0;  // leading k-blocks whose low-order activation plane is identically zero
+  const int32_t* row_tok = nullptr;
+  const float* tok_table = nullptr;
+  long long ld_tok_table = 0;
   // logits
   float* partial = nullptr;
   float* logits_out = nullptr;
@@ -135,6 +138,9 @@ static const char* fill_problem(GemmProblem& pb, const GemmSpec& s, int a_terms,
   pb.c_out = s.c_out;
   pb.row_bias = s.row_bias;
   pb.ld_row_bias = s.ld_row_bias;
+  pb.row_tok = s.row_tok;
+  pb.tok_table = s.tok_table;
+  pb.ld_tok_table = s.ld_tok_table;
   pb.hidden = HID;
   pb.partial = s.partial;
   pb.logits_out = s.logits_out;
@@ -235,6 +241,7 @@ static void model_layout(echr_model* m, Arena& a) {
   m->b_logit = a.take<float>(m->V1);
   m->b_out = a.take<float>(HID);
   m->alpha = a.take<float>(HID);
+  for (int l = 0; l < 3; ++l) m->tok_gates[l] = a.take<float>((size_t)m->V1 * GATES);
 }
 
 static cudaError_t pack_linear(const float* w, int out_f, int in_f, const PlaneMat& dst, int row0,
@@ -313,6 +320,22 @@ extern "C" int echr_model_create(const echr_config_t* config, const echr_weights
   PK(copy_vec(w->logit_b, m->b_logit, m->V1, st));
   PK(copy_vec(w->out_b, m->b_out, HID, st));
   PK(copy_vec(w->alpha_w, m->alpha, HID, st));
+  // token -> gate tables (see engine.cuh): embed [V1,512] (hi+lo planes) x the x block of each stream's
+  // packed weights, fp32-grade products whatever the run-time precision
+  for (int l = 0; l < 3; ++l) {
+    PlaneMat wx = m->w_lstm[l];  // columns 0..511 of [x | h | ctx]
+    GemmSpec s;
+    s.A = &m->embed; s.M = m->V1; s.W = &wx; s.N = GATES; s.K = HID;
+    s.bias = (l == 1) ? m->b_lstm[1] : nullptr;
+    s.out_f32 = m->tok_gates[l]; s.ld_f32 = GATES;
+    const int rc = run_gemm(&s, 1, 2, m->cfg.w_terms, 128, EPI_STORE, 1, st, "token_gate_table");
+    if (rc != ECHR_OK) {
+      cudaStreamSynchronize(st);
+      cudaFree(m->arena);
+      delete m;
+      return rc;
+    }
+  }
   PK(cudaStreamSynchronize(st));
 #undef PK
   *out = m;
@@ -374,6 +397,7 @@ static void batch_layout(echr_batch* b, Arena& a) {
   b->row_start = a.take<int32_t>(c.max_rows);
   b->row_len = a.take<int32_t>(c.max_rows);
   b->unfinished = a.take<int32_t>(c.max_rows);
+  b->row_tok = a.take<int32_t>(c.max_rows);
   b->tokens_dev = a.take<int32_t>((size_t)c.max_events * S);
   b->logp_dev = a.take<float>((size_t)c.max_events * S);
   b->score_dev = a.take<float>(c.max_events);
@@ -673,9 +697,10 @@ extern "C" int echr_get_event_context(const echr_batch_t* b, float* out, void* s
 // Decode
 // =============================================================================================
 // k-block tables over the activation matrix, in the weights' column order [x | h | ctx]
-static const int KB_L0[16] = {0, 1, 2, 3, 4, 5, 6, 7, 26, 27, 28, 29, 30, 31, 32, 33};                                   // x, h0
-static const int KB_L1[24] = {0, 1, 2, 3, 4, 5, 6, 7, 34, 35, 36, 37, 38, 39, 40, 41, 16, 17, 18, 19, 20, 21, 22, 23};  // x, h1, att
-static const int KB_L2[16] = {0, 1, 2, 3, 4, 5, 6, 7, 42, 43, 44, 45, 46, 47, 48, 49};                                   // x, h2
+// (the x block is not part of the step GEMM: it is the token gate table, gathered in the epilogue)
+static const int KB_L0[8] = {26, 27, 28, 29, 30, 31, 32, 33};                                   // h0
+static const int KB_L1[16] = {34, 35, 36, 37, 38, 39, 40, 41, 16, 17, 18, 19, 20, 21, 22, 23};  // h1, att
+static const int KB_L2[8] = {42, 43, 44, 45, 46, 47, 48, 49};                                   // h2
 
 enum { MODE_GREEDY = 0, MODE_BEAM = 1, MODE_TF = 2 };
 
@@ -724,7 +749,11 @@ static int enqueue_step(echr_batch* b, int rows, int t, int topk, float* logits_
     s.A = &cur; s.a_col0 = ACT_H + HID; s.M = rows; s.W = &m->w_h2att; s.N = HID; s.K = HID;
     s.bias = m->b_h2att; s.act = ACT_EXP2X; s.out_f32 = b->q_att; s.ld_f32 = HID;  // e^{2q}
     PdlScope pdl(PDL_H2ATT);
-    ECHR_TRY(run_gemm(&s, 1, at, wt, 128, EPI_STORE, 1, st, "h2att", b, 0));
+    // latency regime: narrow tiles spread the [rows,512] x [512,512] product over 4x the SMs (a CTA's
+    // main loop is bound by its own L2->SM operand stream, dominated by the 2-plane activation tile)
+    static const int bn_small = getenv("ECHR_H2ATT_BN") ? atoi(getenv("ECHR_H2ATT_BN")) : 32;
+    const int bn = rows < gemm2_min_rows() ? bn_small : 128;
+    ECHR_TRY(run_gemm(&s, 1, at, wt, bn, EPI_STORE, 1, st, "h2att", b, 0));
   }
   if (parts & PART_ATT) {
   PdlScope pdl(PDL_ATT);
@@ -736,14 +765,16 @@ static int enqueue_step(echr_batch* b, int rows, int t, int topk, float* logits_
   }
   if (parts & PART_GATES) {
     GemmSpec s[3];
+    PlaneMat wv[3];
     const int* kbs[3] = {KB_L0, KB_L1, KB_L2};
-    const int K[3] = {16 * 64, 24 * 64, 16 * 64};
+    const int K[3] = {8 * 64, 16 * 64, 8 * 64};
     for (int l = 0; l < 3; ++l) {
-      s[l].A = &cur; s[l].a_kb = kbs[l]; s[l].M = rows; s[l].W = &m->w_lstm[l]; s[l].N = GATES; s[l].K = K[l];
+      wv[l] = m->w_lstm[l];
+      wv[l].p += HID;  // skip the x block of [x | h | ctx]; plane stride and ld are unchanged
+      s[l].A = &cur; s[l].a_kb = kbs[l]; s[l].M = rows; s[l].W = &wv[l]; s[l].N = GATES; s[l].K = K[l];
       s[l].bias = m->b_lstm[l];
       if (l != 1) { s[l].row_bias = b->row_bias[l / 2]; s[l].ld_row_bias = GATES; }
-      // with bf16 weights the embedding rows are bf16 values: the x block has no low-order plane
-      if (at == 2 && wt == 1) s[l].hi_only_first = HID / 64;
+      s[l].row_tok = b->row_tok; s[l].tok_table = m->tok_gates[l]; s[l].ld_tok_table = GATES;
       s[l].c_in = b->cstate[p] + (long long)l * rows * HID;
       s[l].c_out = b->cstate[n] + (long long)l * rows * HID;
       s[l].out_hi = nxt.plane(0) + ACT_H + l * HID;

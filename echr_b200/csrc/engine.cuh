@@ -51,6 +51,11 @@ struct echr_model {
   // fp32 vectors
   float *b_event_emb, *b_qky, *b_fc1, *b_fc2, *b_ctx2att, *b_h2att, *b_lstm[3], *b_logit, *b_out,
       *alpha;
+  // token -> gate pre-activation tables, [V1, 2048] fp32 per stream, gate-interleaved columns:
+  // tok_gates[l][v] = W_ih_l[:, 0:512] . embed[v]  (+ b_ih + b_hh for stream 1, whose other input terms
+  // all go through the step GEMM).  The embedding lookup and the x block of every gate GEMM become one
+  // row gather in the LSTM epilogue.
+  float* tok_gates[3];
   void* arena;  // one allocation behind everything above
 };
 
@@ -88,6 +93,7 @@ struct echr_batch {
   float* partial;           // [rows, n_vtiles, 12]
   int32_t *row_start, *row_len;  // attention window per decode row
   int32_t* unfinished;      // [rows]
+  int32_t* row_tok;         // [rows] input token of the next step (BOS = 0 at step 0)
   int32_t* tokens_dev;      // [events, S] scratch outputs for echr_caption_host
   float* logp_dev;
   float* score_dev;

@@ -65,6 +65,8 @@ template <int A, int W>
 static cudaError_t launch_aw(const GemmParams& P, dim3 grid, int block_n, int epi, int topk,
                              cudaStream_t stream) {
   if (epi == EPI_STORE && block_n == 128) return launch_one<A, W, 128, EPI_STORE, 1>(P, grid, stream);
+  if (epi == EPI_STORE && block_n == 64) return launch_one<A, W, 64, EPI_STORE, 1>(P, grid, stream);
+  if (epi == EPI_STORE && block_n == 32) return launch_one<A, W, 32, EPI_STORE, 1>(P, grid, stream);
   if (epi == EPI_STORE && block_n == 16) return launch_one<A, W, 16, EPI_STORE, 1>(P, grid, stream);
   if (epi == EPI_LSTM && block_n == 128) return launch_one<A, W, 128, EPI_LSTM, 1>(P, grid, stream);
   if (epi == EPI_LOGITS && block_n == 128 && topk == 1)

@@ -60,6 +60,11 @@ struct GemmProblem {
   float* c_out;        // [M, H]
   const float* row_bias;  // optional [M, N] per-row gate bias (hoisted constant-context terms); replaces bias
   long long ld_row_bias;
+  // optional token-indexed gate table [vocab, N]: W_ih[:, x] . embed[token] (+ bias when there is no
+  // row_bias), added to the pre-activations of row r from row tok_table[row_tok[r]].  Replaces bias.
+  const int32_t* row_tok;
+  const float* tok_table;
+  long long ld_tok_table;
   int hidden;          // H (N == 4H)
   // EPI_LOGITS
   float* partial;      // [M, n_groups, REC]   n_groups = ceil(N / BLOCK_N) * (BLOCK_N / LOGIT_GROUP)
@@ -259,8 +264,10 @@ gemm_tc_kernel(const __grid_constant__ GemmParams P) {
     float rbias[EPI == EPI_LSTM ? HALF : 1];
     bool has_rbias = false;
     if constexpr (EPI == EPI_LSTM) {
-      has_rbias = pb.row_bias != nullptr;
-      if (has_rbias && row_ok) {
+      has_rbias = pb.row_bias != nullptr || pb.tok_table != nullptr;
+#pragma unroll
+      for (int i = 0; i < HALF; ++i) rbias[i] = 0.f;
+      if (pb.row_bias != nullptr && row_ok) {
         const float4* rp = reinterpret_cast<const float4*>(
             pb.row_bias + static_cast<long long>(row) * pb.ld_row_bias + col0 + hc0);
 #pragma unroll
@@ -268,9 +275,16 @@ gemm_tc_kernel(const __grid_constant__ GemmParams P) {
           const float4 t = __ldg(rp + i);
           rbias[4 * i] = t.x; rbias[4 * i + 1] = t.y; rbias[4 * i + 2] = t.z; rbias[4 * i + 3] = t.w;
         }
-      } else {
+      }
+      if (pb.tok_table != nullptr && row_ok) {
+        const int tk = __ldg(pb.row_tok + row);
+        const float4* tp = reinterpret_cast<const float4*>(
+            pb.tok_table + static_cast<long long>(tk) * pb.ld_tok_table + col0 + hc0);
 #pragma unroll
-        for (int i = 0; i < HALF; ++i) rbias[i] = 0.f;
+        for (int i = 0; i < HALF / 4; ++i) {
+          const float4 t = __ldg(tp + i);
+          rbias[4 * i] += t.x; rbias[4 * i + 1] += t.y; rbias[4 * i + 2] += t.z; rbias[4 * i + 3] += t.w;
+        }
       }
       if (row_ok) {
         const float4* cp = reinterpret_cast<const float4*>(

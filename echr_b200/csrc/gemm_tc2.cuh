@@ -239,7 +239,10 @@ gemm_tc2_kernel(const __grid_constant__ GemmParams P, int groups, int total_tile
         }
       } else if constexpr (EPI == EPI_LSTM) {
         const int H = pb.hidden;
-        const bool has_rbias = pb.row_bias != nullptr;
+        const bool has_rbias = pb.row_bias != nullptr || pb.tok_table != nullptr;
+        const float* tok_row = nullptr;
+        if (pb.tok_table != nullptr && row_ok)
+          tok_row = pb.tok_table + static_cast<long long>(__ldg(pb.row_tok + row)) * pb.ld_tok_table + col0;
 #pragma unroll 1
         for (int c = 0; c < NCH; ++c) {
           const int tc = hc0 + c * 32;
@@ -252,12 +255,24 @@ gemm_tc2_kernel(const __grid_constant__ GemmParams P, int groups, int total_tile
             cprev[0] = c0.x; cprev[1] = c0.y; cprev[2] = c0.z; cprev[3] = c0.w;
             cprev[4] = c1.x; cprev[5] = c1.y; cprev[6] = c1.z; cprev[7] = c1.w;
             if (has_rbias) {
-              const float4* rp = reinterpret_cast<const float4*>(
-                  pb.row_bias + static_cast<long long>(row) * pb.ld_row_bias + col0 + tc);
 #pragma unroll
-              for (int i = 0; i < 8; ++i) {
-                const float4 r4 = __ldg(rp + i);
-                bb[4 * i] = r4.x; bb[4 * i + 1] = r4.y; bb[4 * i + 2] = r4.z; bb[4 * i + 3] = r4.w;
+              for (int i = 0; i < 32; ++i) bb[i] = 0.f;
+              if (pb.row_bias != nullptr) {
+                const float4* rp = reinterpret_cast<const float4*>(
+                    pb.row_bias + static_cast<long long>(row) * pb.ld_row_bias + col0 + tc);
+#pragma unroll
+                for (int i = 0; i < 8; ++i) {
+                  const float4 r4 = __ldg(rp + i);
+                  bb[4 * i] = r4.x; bb[4 * i + 1] = r4.y; bb[4 * i + 2] = r4.z; bb[4 * i + 3] = r4.w;
+                }
+              }
+              if (tok_row != nullptr) {
+                const float4* tp = reinterpret_cast<const float4*>(tok_row + tc);
+#pragma unroll
+                for (int i = 0; i < 8; ++i) {
+                  const float4 r4 = __ldg(tp + i);
+                  bb[4 * i] += r4.x; bb[4 * i + 1] += r4.y; bb[4 * i + 2] += r4.z; bb[4 * i + 3] += r4.w;
+                }
               }
             } else {
 #pragma unroll

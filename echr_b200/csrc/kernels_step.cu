@@ -367,9 +367,9 @@ __global__ void __launch_bounds__(128)
 decode_init_kernel(int beam, int a_planes, const float* __restrict__ event_ctx,
                    const float* __restrict__ lda, const int32_t* __restrict__ ev_video,
                    const int32_t* __restrict__ ev_start, const int32_t* __restrict__ ev_len,
-                   const bf16* __restrict__ embed, long long embed_plane, bf16* __restrict__ act0,
+                   bf16* __restrict__ act0,
                    bf16* __restrict__ act1, long long act_plane, int32_t* __restrict__ row_start,
-                   int32_t* __restrict__ row_len, int32_t* __restrict__ unfinished,
+                   int32_t* __restrict__ row_len, int32_t* __restrict__ unfinished, int32_t* __restrict__ row_tok,
                    float* __restrict__ beam_score, int32_t* __restrict__ beam_live,
                    float* __restrict__ best_score) {
   const int r = blockIdx.x;
@@ -395,12 +395,8 @@ decode_init_kernel(int beam, int a_planes, const float* __restrict__ event_ctx,
       if (a_planes > 1) rows[b][act_plane + col] = l;
     }
   }
-  // BOS embedding (token 0) into buffer 0
-  for (int c = threadIdx.x; c < HID; c += blockDim.x) {
-    rows[0][ACT_X + c] = embed[c];
-    if (a_planes > 1) rows[0][act_plane + ACT_X + c] = embed[embed_plane + c];
-  }
   if (threadIdx.x == 0) {
+    row_tok[r] = 0;  // BOS (token 0)
     row_start[r] = ev_start[e];
     row_len[r] = ev_len[e];
     unfinished[r] = 1;
@@ -416,8 +412,8 @@ cudaError_t launch_decode_init(const echr_batch* b, int beam, cudaStream_t st) {
   const echr_model* m = b->model;
   decode_init_kernel<<<rows, 128, 0, st>>>(
       beam, (int)b->act[0].planes, b->event_ctx, b->lda, b->ev_video, b->ev_start, b->ev_len,
-      m->embed.p, m->embed.plane_stride(), b->act[0].p, b->act[1].p, b->act[0].plane_stride(),
-      b->row_start, b->row_len, b->unfinished, b->beam_score, b->beam_live, b->best_score);
+      b->act[0].p, b->act[1].p, b->act[0].plane_stride(),
+      b->row_start, b->row_len, b->unfinished, b->row_tok, b->beam_score, b->beam_live, b->best_score);
   count_launch();
   return cudaGetLastError();
 }
@@ -459,18 +455,6 @@ __device__ __forceinline__ RowStat merge_row_stats(const float* __restrict__ rec
   return s;
 }
 
-// copy one embedding row (512 bf16 per plane) into the X columns of an activation row
-__device__ __forceinline__ void copy_embed_row(const bf16* __restrict__ embed, long long embed_plane,
-                                               int tok, bf16* __restrict__ act_row, long long act_plane,
-                                               int planes, int lane) {
-  for (int p = 0; p < planes; ++p) {
-    const uint4* src = reinterpret_cast<const uint4*>(embed + p * embed_plane + (long long)tok * HID);
-    uint4* dst = reinterpret_cast<uint4*>(act_row + p * act_plane + ACT_X);
-    dst[lane] = __ldg(src + lane);
-    dst[lane + 32] = __ldg(src + lane + 32);
-  }
-}
-
 constexpr int FIN_WARPS = 4;
 
 // Greedy bookkeeping of OldModel.sample (OldModel_NEW.py:154-183): step `t` here is the
@@ -479,8 +463,7 @@ constexpr int FIN_WARPS = 4;
 // gets embedded for the next step.
 __global__ void __launch_bounds__(FIN_WARPS * 32)
 finalize_greedy_kernel(int rows, int n_tiles, int step, int seq_len, const float* __restrict__ partial,
-                       const bf16* __restrict__ embed, long long embed_plane, bf16* __restrict__ act_next,
-                       long long act_plane, int planes, int32_t* __restrict__ unfinished,
+                       int32_t* __restrict__ row_tok, int32_t* __restrict__ unfinished,
                        int32_t* __restrict__ tokens, float* __restrict__ logp, unsigned long long* trace,
                        int trace_slot) {
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -496,9 +479,8 @@ finalize_greedy_kernel(int rows, int n_tiles, int step, int seq_len, const float
     unfinished[r] = unf;
     tokens[(long long)r * seq_len + step] = unf ? tok : 0;
     logp[(long long)r * seq_len + step] = -s.log_sum;
+    row_tok[r] = tok;  // the raw argmax is the next step's input
   }
-  if (step + 1 < seq_len)
-    copy_embed_row(embed, embed_plane, tok, act_next + (long long)r * ACT_LD, act_plane, planes, lane);
   __syncthreads();
   trace_end(trace, trace_slot);
 }
@@ -509,11 +491,9 @@ cudaError_t launch_finalize_greedy(echr_batch* b, int step, int32_t* tokens, flo
   if (rows == 0) return cudaSuccess;
   const echr_model* m = b->model;
   const int n_tiles = logit_groups_for(m, b->n_events);
-  const PlaneMat& nxt = b->act[(step + 1) & 1];
   cudaError_t e = launch_pdl(finalize_greedy_kernel, dim3((rows + FIN_WARPS - 1) / FIN_WARPS), dim3(FIN_WARPS * 32), 0,
-                             st, rows, n_tiles, step, m->cfg.seq_length, b->partial, m->embed.p,
-                             (long long)m->embed.plane_stride(), nxt.p, (long long)nxt.plane_stride(),
-                             (int)nxt.planes, b->unfinished, tokens, logp, trace_ptr(b), trace_next(b, 4));
+                             st, rows, n_tiles, step, m->cfg.seq_length, b->partial, b->row_tok,
+                             b->unfinished, tokens, logp, trace_ptr(b), trace_next(b, 4));
   count_launch();
   return e;
 }
@@ -522,8 +502,7 @@ cudaError_t launch_finalize_greedy(echr_batch* b, int step, int32_t* tokens, flo
 // logprobs[r, step, :]; subtract the row's log-sum-exp in place and embed seq[r, step+1].
 __global__ void __launch_bounds__(FIN_WARPS * 32)
 finalize_tf_kernel(int rows, int n_tiles, int step, int seq_cols, int V1, const float* __restrict__ partial,
-                   const int32_t* __restrict__ seq, const bf16* __restrict__ embed, long long embed_plane,
-                   bf16* __restrict__ act_next, long long act_plane, int planes,
+                   const int32_t* __restrict__ seq, int32_t* __restrict__ row_tok,
                    float* __restrict__ logprobs) {
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int r = blockIdx.x * FIN_WARPS + warp;
@@ -537,7 +516,7 @@ finalize_tf_kernel(int rows, int n_tiles, int step, int seq_cols, int V1, const 
   if (step + 1 < seq_cols - 1) {
     int tok = seq[(long long)r * seq_cols + step + 1];
     tok = min(max(tok, 0), V1 - 1);
-    copy_embed_row(embed, embed_plane, tok, act_next + (long long)r * ACT_LD, act_plane, planes, lane);
+    if (lane == 0) row_tok[r] = tok;
   }
 }
 
@@ -547,10 +526,8 @@ cudaError_t launch_finalize_tf(const echr_batch* b, int step, const int32_t* seq
   if (rows == 0) return cudaSuccess;
   const echr_model* m = b->model;
   const int n_tiles = logit_groups_for(m, b->n_events);
-  const PlaneMat& nxt = b->act[(step + 1) & 1];
   finalize_tf_kernel<<<(rows + FIN_WARPS - 1) / FIN_WARPS, FIN_WARPS * 32, 0, st>>>(
-      rows, n_tiles, step, seq_cols, m->V1, b->partial, seq, m->embed.p, m->embed.plane_stride(), nxt.p,
-      nxt.plane_stride(), (int)nxt.planes, logprobs);
+      rows, n_tiles, step, seq_cols, m->V1, b->partial, seq, b->row_tok, logprobs);
   count_launch();
   return cudaGetLastError();
 }
@@ -560,8 +537,7 @@ cudaError_t launch_finalize_tf(const echr_batch* b, int step, const int32_t* seq
 // caller's (h, it) into the activation matrix, and read the new h back out of the planes.
 __global__ void __launch_bounds__(128)
 load_state_kernel(int rows, int V1, const int32_t* __restrict__ it, const float* __restrict__ h_in,
-                  const bf16* __restrict__ embed, long long embed_plane, bf16* __restrict__ act,
-                  long long act_plane, int planes) {
+                  int32_t* __restrict__ row_tok, bf16* __restrict__ act, long long act_plane, int planes) {
   const int r = blockIdx.x;
   bf16* row = act + (long long)r * ACT_LD;
   for (int c = threadIdx.x; c < 3 * HID; c += blockDim.x) {
@@ -571,11 +547,7 @@ load_state_kernel(int rows, int V1, const int32_t* __restrict__ it, const float*
     row[ACT_H + c] = h;
     if (planes > 1) row[act_plane + ACT_H + c] = lo;
   }
-  const int tok = min(max(it[r], 0), V1 - 1);
-  for (int c = threadIdx.x; c < HID; c += blockDim.x) {
-    row[ACT_X + c] = embed[(long long)tok * HID + c];
-    if (planes > 1) row[act_plane + ACT_X + c] = embed[embed_plane + (long long)tok * HID + c];
-  }
+  if (threadIdx.x == 0) row_tok[r] = min(max(it[r], 0), V1 - 1);
 }
 
 __global__ void __launch_bounds__(128)
@@ -593,7 +565,7 @@ export_state_kernel(int rows, const bf16* __restrict__ act, long long act_plane,
 
 cudaError_t launch_load_state(const echr_batch* b, int rows, const int32_t* it, const float* h_in, cudaStream_t st) {
   const echr_model* m = b->model;
-  load_state_kernel<<<rows, 128, 0, st>>>(rows, m->V1, it, h_in, m->embed.p, m->embed.plane_stride(), b->act[0].p,
+  load_state_kernel<<<rows, 128, 0, st>>>(rows, m->V1, it, h_in, b->row_tok, b->act[0].p,
                                           b->act[0].plane_stride(), (int)b->act[0].planes);
   count_launch();
   return cudaGetLastError();
@@ -612,7 +584,7 @@ constexpr int BEAM_SEG = 3 * HID;  // 1536 elements: h of the three streams / c 
 
 __global__ void __launch_bounds__(BEAM_MAX * 32)
 finalize_beam_kernel(int beam, int n_tiles, int step, int seq_len, const float* __restrict__ partial,
-                     const bf16* __restrict__ embed, long long embed_plane, bf16* __restrict__ act_next,
+                     int32_t* __restrict__ row_tok, bf16* __restrict__ act_next,
                      long long act_plane, int planes, float* __restrict__ c_next, long long c_layer_stride,
                      float* __restrict__ beam_score, int32_t* __restrict__ beam_live,
                      const int32_t* __restrict__ hist_tok_in, int32_t* __restrict__ hist_tok_out,
@@ -735,9 +707,7 @@ finalize_beam_kernel(int beam, int n_tiles, int step, int seq_len, const float* 
   if (step + 1 >= seq_len) return;
 
   // ---- 4. next inputs and state reorder
-  if (warp < beam)
-    copy_embed_row(embed, embed_plane, sel_tok[warp], act_next + (long long)(row0 + warp) * ACT_LD,
-                   act_plane, planes, lane);
+  if (warp < beam && lane == 0) row_tok[row0 + warp] = sel_tok[warp];
   bool identity = true;
   for (int n = 0; n < beam; ++n) identity = identity && (sel_parent[n] == n);
   if (identity) return;  // uniform across the CTA
@@ -797,7 +767,7 @@ cudaError_t launch_finalize_beam(const echr_batch* b, int beam, int step, int32_
   const long long hist = (long long)b->cap.max_rows * S;
   const int in = step & 1, out = in ^ 1;
   finalize_beam_kernel<<<b->n_events, BEAM_MAX * 32, 0, st>>>(
-      beam, n_tiles, step, S, b->partial, m->embed.p, m->embed.plane_stride(), nxt.p,
+      beam, n_tiles, step, S, b->partial, b->row_tok, nxt.p,
       nxt.plane_stride(), (int)nxt.planes, b->cstate[(step + 1) & 1], rows * HID, b->beam_score,
       b->beam_live, b->beam_hist_tok + in * hist, b->beam_hist_tok + out * hist,
       b->beam_hist_lp + in * hist, b->beam_hist_lp + out * hist, b->best_score, tokens, logp, score);

@@ -113,7 +113,7 @@ ECHR_API int echr_split_bf16(const float* src, int64_t rows, int64_t cols, int64
  * planes=1 is the plain bf16 operand, planes=2 adds the low-order plane (fp32-grade product).
  * k must be a multiple of 64 (pad with zeros), k <= 2048.  act: 0 none, 1 tanh, 2 exp(2*clamp(x,+-40)).
  * Outputs: out_f32 (may be NULL) and/or bf16 planes out_hi/out_lo (may be NULL).
- * block_n: 128 or 16 = one 128 x block_n tile per CTA; 256 = the persistent 128 x 256 kernel with
+ * block_n: 128, 64, 32 or 16 = one 128 x block_n tile per CTA; 256 = the persistent 128 x 256 kernel with
  * double-buffered TMEM accumulators the engine uses from 1024 rows up. */
 ECHR_API int echr_gemm_planes(const void* a, int64_t m, int64_t k, int64_t a_ld, int a_planes,
                      int64_t a_plane_stride, const void* w, int64_t n, int64_t w_ld, int w_planes,

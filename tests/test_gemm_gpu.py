@@ -38,7 +38,7 @@ def _gemm(a_planes, w_planes, m, n, k, bias, act, block_n, want_bf=False):
 
 @pytest.mark.parametrize("m,n,k,block_n", [
     (128, 128, 64, 128), (128, 128, 512, 128), (256, 512, 1024, 128), (3, 2048, 1536, 128),
-    (300, 5748, 1536, 128), (77, 16, 512, 16), (1000, 16, 512, 16), (130, 500, 128, 128),
+    (300, 5748, 1536, 128), (77, 16, 512, 16), (251, 512, 512, 32), (251, 512, 512, 64), (130, 100, 128, 32), (1000, 16, 512, 16), (130, 500, 128, 128),
     (300, 5748, 1536, 256), (4000, 2048, 1024, 256), (129, 300, 64, 256), (20000, 512, 512, 256),
 ])
 @pytest.mark.parametrize("terms", [(1, 1), (2, 1), (2, 2)])
