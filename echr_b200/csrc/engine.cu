@@ -107,6 +107,7 @@ struct GemmSpec {
   const int32_t* row_tok = nullptr;
   const float* tok_table = nullptr;
   long long ld_tok_table = 0;
+  int ksplit = 1;  // 2: cluster split-K (run_gemm then launches the SPLIT == 2 kernel for the whole group)
   // logits
   float* partial = nullptr;
   float* logits_out = nullptr;
@@ -126,6 +127,7 @@ static const char* fill_problem(GemmProblem& pb, const GemmSpec& s, int a_terms,
   pb.N = s.N;
   pb.num_kb = s.K / GEMM_BLOCK_K;
   pb.act = s.act;
+  pb.ksplit = s.ksplit;
   for (int i = 0; i < pb.num_kb; ++i)
     pb.a_kb[i] = (uint16_t)((s.a_kb ? s.a_kb[i] : s.a_col0 / GEMM_BLOCK_K + i) | (i < s.hi_only_first ? GEMM_KB_HI_ONLY : 0));
   pb.bias = s.bias;
@@ -169,9 +171,27 @@ static int num_sms() {
   }
   return n;
 }
+// Cluster split-K in the latency regime (ECHR_KSPLIT bit 0: gate GEMMs, bit 1: logit GEMM), used while the
+// split launch still fits the SMs in one wave.  Default: gates only — measured on cfg2 (251 rows) the gate
+// launch gains 1.3 us per step, while the logit launch (128 x 256 tiles, 64 KB of partial sums per CTA over
+// DSMEM at ~17 B/clk) loses 2 us against the unsplit 128 x 128 tiles.
+static int ksplit_mask() {
+  static int v = -1;
+  if (v < 0) {
+    const char* e = getenv("ECHR_KSPLIT");
+    v = e ? atoi(e) : 1;
+  }
+  return v;
+}
+static int m_tiles_of(int rows) { return (rows + GEMM_BLOCK_M - 1) / GEMM_BLOCK_M; }
+// logit GEMM as 128 x 256 tiles shared by CTA pairs (23 x 2 CTAs per 128 rows at the ECHR vocabulary)
+static bool logit_split(const echr_model* m, int rows) {
+  const int n_tiles = (m->V1 + 255) / 256;
+  return (ksplit_mask() & 2) != 0 && rows < gemm2_min_rows() && m_tiles_of(rows) * n_tiles * 2 <= num_sms();
+}
 // partial records per row the logit GEMM writes for `rows` decode rows
 static int logit_groups(const echr_model* m, int rows) {
-  return use_gemm2(rows, m->V1, 128) ? gemm2_logit_groups(m->V1) : gemm1_logit_groups(m->V1);
+  return (use_gemm2(rows, m->V1, 128) || logit_split(m, rows)) ? gemm2_logit_groups(m->V1) : gemm1_logit_groups(m->V1);
 }
 
 int logit_groups_for(const echr_model* m, int rows) { return logit_groups(m, rows); }
@@ -186,16 +206,26 @@ static int run_gemm(const GemmSpec* specs, int groups, int a_terms, int w_terms,
     if (specs[g].M > max_m) max_m = specs[g].M;
     if (specs[g].N < min_n) min_n = specs[g].N;
   }
-  const bool two = use_gemm2(max_m, min_n, block_n);
+  bool any_split = false;
+  int grid_x = 0;
+  for (int g = 0; g < groups; ++g) {
+    any_split = any_split || specs[g].ksplit == 2;
+    const int gx = ((specs[g].N + block_n - 1) / block_n) * specs[g].ksplit;
+    if (gx > grid_x) grid_x = gx;
+  }
+  const bool two = !any_split && use_gemm2(max_m, min_n, block_n);
   for (int g = 0; g < groups; ++g) {
     const char* err = fill_problem(P.prob[g], specs[g], a_terms, w_terms, two ? GEMM2_BLOCK_N : block_n);
     if (err) return set_error(ECHR_ERR_CUDA, "%s: %s", what, err);
+    if (specs[g].ksplit == 2 && (P.prob[g].num_kb < 2 || (P.prob[g].num_kb & 1)))
+      return set_error(ECHR_ERR_INVALID, "%s: split-K needs an even number of k-blocks", what);
     if (specs[g].M > max_m) max_m = specs[g].M;
     if (specs[g].N > max_n) max_n = specs[g].N;
   }
   if (max_m == 0) return ECHR_OK;
-  cudaError_t e = two ? gemm2_launch(P, groups, a_terms, w_terms, epi, topk, num_sms(), st)
-                      : gemm_launch(P, groups, max_m, max_n, a_terms, w_terms, block_n, epi, topk, st);
+  cudaError_t e = any_split ? gemm_launch_split(P, groups, max_m, grid_x, a_terms, w_terms, block_n, epi, topk, st)
+                  : two     ? gemm2_launch(P, groups, a_terms, w_terms, epi, topk, num_sms(), st)
+                            : gemm_launch(P, groups, max_m, max_n, a_terms, w_terms, block_n, epi, topk, st);
   if (e != cudaSuccess) return set_error(ECHR_ERR_CUDA, "%s: launch failed: %s", what, cudaGetErrorString(e));
   count_launch();
   return ECHR_OK;
@@ -766,6 +796,14 @@ static int enqueue_step(echr_batch* b, int rows, int t, int topk, float* logits_
   if (parts & PART_GATES) {
     GemmSpec s[3];
     PlaneMat wv[3];
+    // latency regime: stream 1 has twice the k-blocks of the others; give its tiles to CTA pairs (and the
+    // other streams' too while everything still fits one wave)
+    int ks[3] = {1, 1, 1};
+    if ((ksplit_mask() & 1) != 0 && rows < gemm2_min_rows()) {
+      const int mt = m_tiles_of(rows), nt = GATES / 128;
+      if (mt * nt * 6 <= num_sms()) ks[0] = ks[1] = ks[2] = 2;
+      else if (mt * nt * 4 <= num_sms()) ks[1] = 2;
+    }
     const int* kbs[3] = {KB_L0, KB_L1, KB_L2};
     const int K[3] = {8 * 64, 16 * 64, 8 * 64};
     for (int l = 0; l < 3; ++l) {
@@ -775,6 +813,7 @@ static int enqueue_step(echr_batch* b, int rows, int t, int topk, float* logits_
       s[l].bias = m->b_lstm[l];
       if (l != 1) { s[l].row_bias = b->row_bias[l / 2]; s[l].ld_row_bias = GATES; }
       s[l].row_tok = b->row_tok; s[l].tok_table = m->tok_gates[l]; s[l].ld_tok_table = GATES;
+      s[l].ksplit = ks[l];
       s[l].c_in = b->cstate[p] + (long long)l * rows * HID;
       s[l].c_out = b->cstate[n] + (long long)l * rows * HID;
       s[l].out_hi = nxt.plane(0) + ACT_H + l * HID;
@@ -788,8 +827,10 @@ static int enqueue_step(echr_batch* b, int rows, int t, int topk, float* logits_
     GemmSpec s;
     s.A = &nxt; s.a_col0 = ACT_H; s.M = rows; s.W = &m->w_logit; s.N = m->V1; s.K = 3 * HID;
     s.bias = m->b_logit; s.partial = b->partial; s.logits_out = logits_out; s.ld_logits = ld_logits;
+    const bool sp = logit_split(m, rows);
+    if (sp) s.ksplit = 2;
     PdlScope pdl(PDL_LOGIT);
-    ECHR_TRY(run_gemm(&s, 1, at, wt, 128, EPI_LOGITS, topk, st, "logit", b, 3));
+    ECHR_TRY(run_gemm(&s, 1, at, wt, sp ? 256 : 128, EPI_LOGITS, topk, st, "logit", b, 3));
   }
   return ECHR_OK;
 }

@@ -87,6 +87,52 @@ cudaError_t gemm_launch(const GemmParams& P, int groups, int max_m, int max_n, i
   return cudaErrorInvalidValue;
 }
 
+// ---------------------------------------------------------------- cluster split-K variant
+template <int A, int W, int BN, int EPI, int TOPK>
+static cudaError_t launch_split_one(const GemmParams& P, dim3 grid, cudaStream_t stream) {
+  using Cfg = GemmCfg<A, W, BN>;
+  auto kern = gemm_tc_kernel<A, W, BN, EPI, TOPK, 2>;
+  static bool attr_set = false;  // per instantiation
+  if (!attr_set) {
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES);
+    if (e != cudaSuccess) return e;
+    attr_set = true;
+  }
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid;
+  cfg.blockDim = dim3(GEMM_THREADS);
+  cfg.dynamicSmemBytes = Cfg::SMEM_BYTES;
+  cfg.stream = stream;
+  cudaLaunchAttribute at[2];
+  at[0].id = cudaLaunchAttributeClusterDimension;
+  at[0].val.clusterDim.x = 2;
+  at[0].val.clusterDim.y = 1;
+  at[0].val.clusterDim.z = 1;
+  at[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  at[1].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = at;
+  cfg.numAttrs = pdl_enabled() ? 2 : 1;
+  return cudaLaunchKernelEx(&cfg, kern, P);
+}
+
+template <int A, int W>
+static cudaError_t launch_split_aw(const GemmParams& P, dim3 grid, int block_n, int epi, int topk, cudaStream_t stream) {
+  if (epi == EPI_LSTM && block_n == 128) return launch_split_one<A, W, 128, EPI_LSTM, 1>(P, grid, stream);
+  if (epi == EPI_LOGITS && block_n == 256 && topk == 1) return launch_split_one<A, W, 256, EPI_LOGITS, 1>(P, grid, stream);
+  if (epi == EPI_LOGITS && block_n == 256 && topk == 4) return launch_split_one<A, W, 256, EPI_LOGITS, 4>(P, grid, stream);
+  return cudaErrorInvalidValue;
+}
+
+cudaError_t gemm_launch_split(const GemmParams& P, int groups, int max_m, int grid_x, int a_terms, int w_terms,
+                              int block_n, int epi, int topk, cudaStream_t stream) {
+  if (groups < 1 || groups > GEMM_MAX_GROUPS || max_m <= 0 || grid_x <= 0) return cudaErrorInvalidValue;
+  dim3 grid((grid_x + 1) & ~1, (max_m + GEMM_BLOCK_M - 1) / GEMM_BLOCK_M, groups);
+  if (a_terms == 1 && w_terms == 1) return launch_split_aw<1, 1>(P, grid, block_n, epi, topk, stream);
+  if (a_terms == 2 && w_terms == 1) return launch_split_aw<2, 1>(P, grid, block_n, epi, topk, stream);
+  if (a_terms == 2 && w_terms == 2) return launch_split_aw<2, 2>(P, grid, block_n, epi, topk, stream);
+  return cudaErrorInvalidValue;
+}
+
 // ---------------------------------------------------------------- persistent 128 x 256 kernel
 template <int A, int W, int EPI, int TOPK>
 static cudaError_t launch_two(const GemmParams& P, int groups, int total_tiles, int num_sms, cudaStream_t stream) {

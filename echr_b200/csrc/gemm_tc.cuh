@@ -46,6 +46,8 @@ struct GemmProblem {
   int N;            // valid columns of D (rows of W)
   int num_kb;       // K / 64
   int act;          // EPI_STORE activation
+  int ksplit;       // SPLIT == 2 kernels: 2 = the two CTAs of a cluster each take half of the k-blocks of one
+                    // tile and exchange partial accumulators through DSMEM; 1 = every CTA owns its tile
   uint16_t a_kb[GEMM_MAX_KB];  // A column-block index for each k-block; bit 15: the block's low-order
                                // plane is identically zero (skip its load and its product)
   const float* bias;           // [N] (EPI_LSTM: gate-interleaved order)
@@ -94,8 +96,8 @@ struct GemmCfg {
   static constexpr int STAGES_RAW = (196 * 1024) / STAGE_BYTES;
   static constexpr int STAGES = STAGES_RAW > 8 ? 8 : STAGES_RAW;
   static constexpr int TMEM_COLS = BLOCK_N <= 32 ? 32 : (BLOCK_N <= 64 ? 64 : (BLOCK_N <= 128 ? 128 : 256));
-  // stages | barriers (256 B) | bias tile (BLOCK_N floats, 512 B reserved)
-  static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 /*align slack*/ + 256 + 512;
+  // stages | barriers (256 B) | bias tile (BLOCK_N floats, 1 KB reserved)
+  static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 /*align slack*/ + 256 + 1024;
 };
 
 // Fast forms for the epilogues: one ex2 + one fast reciprocal each, ~1e-6 relative error.
@@ -130,12 +132,22 @@ __device__ __forceinline__ void store_planes32(const float* v, __nv_bfloat16* oh
   }
 }
 
-template <int A_TERMS, int W_TERMS, int BLOCK_N, int EPI, int TOPK>
+// SPLIT == 2: launched with cluster dims (2,1,1).  For a problem with ksplit == 2 the CTA pair shares one
+// output tile: CTA `rank` runs the k-blocks [rank*num_kb/2, (rank+1)*num_kb/2) and finalises the column half
+// [rank*BLOCK_N/2, +BLOCK_N/2) of the tile after receiving the peer's partial sums for that half through
+// distributed shared memory.  Halving the bytes a CTA pulls from L2 halves its main loop, which in the
+// latency regime (a few hundred rows) is bound by the per-SM L2->SM operand stream.
+template <int A_TERMS, int W_TERMS, int BLOCK_N, int EPI, int TOPK, int SPLIT = 1>
 __global__ void __launch_bounds__(GEMM_THREADS, 1)
 gemm_tc_kernel(const __grid_constant__ GemmParams P) {
   using Cfg = GemmCfg<A_TERMS, W_TERMS, BLOCK_N>;
+  static_assert(SPLIT == 1 || SPLIT == 2, "cluster size 1 or 2");
+  static_assert(SPLIT == 1 || EPI != EPI_STORE, "split-K is wired for the LSTM and logit epilogues");
+  static_assert(SPLIT == 1 || (BLOCK_N / 2) * 512 <= Cfg::STAGES * Cfg::STAGE_BYTES, "exchange buffer aliases the stage ring");
   const GemmProblem& pb = P.prob[blockIdx.z];
-  const int n_tile = blockIdx.x;
+  const bool split = SPLIT == 2 && pb.ksplit == 2;
+  const int rank = SPLIT == 2 ? static_cast<int>(blockIdx.x & 1) : 0;  // == %cluster_ctarank for cluster dims (2,1,1)
+  const int n_tile = split ? static_cast<int>(blockIdx.x >> 1) : static_cast<int>(blockIdx.x);
   const int m_tile = blockIdx.y;
   trace_begin(P.trace, P.trace_slot);
   if (n_tile * BLOCK_N >= pb.N || m_tile * GEMM_BLOCK_M >= pb.M) return;  // whole CTA leaves
@@ -148,6 +160,8 @@ gemm_tc_kernel(const __grid_constant__ GemmParams P) {
   auto empty_bar = [&](int s) { return bar_base + 64u + 8u * s; };
   const uint32_t tmem_full_bar = bar_base + 128u;
   const uint32_t tmem_ptr_smem = bar_base + 136u;
+  const uint32_t peer_done_bar = bar_base + 152u;  // SPLIT: the peer's MMAs have retired (its stage ring is free)
+  const uint32_t xfer_bar = bar_base + 160u;       // SPLIT: the peer's partial sums have landed in my exchange buffer
   uint8_t* bar_generic = smem_raw + (bar_base - smem_u32(smem_raw));
   volatile uint32_t* tmem_ptr_generic = reinterpret_cast<volatile uint32_t*>(bar_generic + 136);
   float* sbias = reinterpret_cast<float*>(bar_generic + 256);
@@ -157,6 +171,8 @@ gemm_tc_kernel(const __grid_constant__ GemmParams P) {
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
   const int num_kb = pb.num_kb;
+  const int kb_begin = split ? rank * (num_kb >> 1) : 0;
+  const int kb_end = split ? (rank == 0 ? (num_kb >> 1) : num_kb) : num_kb;
   const int col0 = n_tile * BLOCK_N;
 
   if (warp == 0 && lane == 0) {
@@ -169,6 +185,10 @@ gemm_tc_kernel(const __grid_constant__ GemmParams P) {
       mbar_init(empty_bar(s), 1);
     }
     mbar_init(tmem_full_bar, 1);
+    if (SPLIT == 2) {
+      mbar_init(peer_done_bar, 1);
+      mbar_init(xfer_bar, GEMM_EPI_WARPS * 32);
+    }
     fence_mbar_init();
   }
   if (warp == 2) tmem_alloc<Cfg::TMEM_COLS>(tmem_ptr_smem);
@@ -178,6 +198,7 @@ gemm_tc_kernel(const __grid_constant__ GemmParams P) {
   }
   tc_fence_before_sync();
   __syncthreads();
+  if (SPLIT == 2) cluster_sync_all();  // the peer's barriers are initialised before anyone arrives on them
   tc_fence_after_sync();
   const uint32_t tmem_base = *tmem_ptr_generic;
   // everything above touched only constants (weights, descriptors): let the next kernel start its
@@ -190,7 +211,7 @@ gemm_tc_kernel(const __grid_constant__ GemmParams P) {
     if (lane == 0) {
       int stage = 0;
       uint32_t phase = 0;
-      for (int kb = 0; kb < num_kb; ++kb) {
+      for (int kb = kb_begin; kb < kb_end; ++kb) {
         mbar_wait(empty_bar(stage), phase ^ 1u);
         const uint32_t sa = smem_base + stage * Cfg::STAGE_BYTES;
         const uint32_t sw = sa + A_TERMS * Cfg::A_PLANE_BYTES;
@@ -217,10 +238,10 @@ gemm_tc_kernel(const __grid_constant__ GemmParams P) {
       int stage = 0;
       uint32_t phase = 0;
       uint32_t accum = 0;
-      for (int kb = 0; kb < num_kb; ++kb) {
+      for (int kb = kb_begin; kb < kb_end; ++kb) {
         mbar_wait(full_bar(stage), phase);
         tc_fence_after_sync();
-        if (kb == 0 && P.trace_detail != nullptr)
+        if (kb == kb_begin && P.trace_detail != nullptr)
           atomicAdd(P.trace_detail + 4 * P.trace_slot, global_timer_ns() - *t_start_smem);
         const uint32_t sa = smem_base + stage * Cfg::STAGE_BYTES;
         const uint32_t sw = sa + A_TERMS * Cfg::A_PLANE_BYTES;
@@ -248,16 +269,32 @@ gemm_tc_kernel(const __grid_constant__ GemmParams P) {
     }
   } else if (warp >= 4) {
     // ===================== epilogue: 8 warps; thread = one output row x half the columns ========
-    constexpr int HALF = BLOCK_N >= 64 ? BLOCK_N / 2 : BLOCK_N;  // columns per epilogue thread
+    // (split tiles: x a quarter of the columns — this CTA finalises only its half of the tile)
+    constexpr int HALF = BLOCK_N >= 64 ? BLOCK_N / 2 : BLOCK_N;  // columns per epilogue thread (unsplit)
     constexpr int CH = HALF >= 32 ? 32 : 16;
     constexpr int NCH = HALF / CH;
     const int q = warp & 3;              // TMEM lane quarter this warp may access
-    const int half = (warp - 4) >> 2;    // which half of the tile's columns
+    const int half = (warp - 4) >> 2;    // which half of the (CTA's share of the) tile's columns
     const bool active = (BLOCK_N >= 64) || half == 0;
-    const int row = m_tile * GEMM_BLOCK_M + q * 32 + lane;
+    const int row_in_tile = q * 32 + lane;
+    const int row = m_tile * GEMM_BLOCK_M + row_in_tile;
     const bool row_ok = row < pb.M;
-    const int hc0 = half * HALF;         // first column (within the tile) of this thread
-    const uint32_t t_row = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + hc0;
+    const int cpt = split ? HALF / 2 : HALF;                       // columns this thread finalises
+    const int hc0 = split ? rank * HALF + half * cpt : half * HALF;  // first of them (within the tile)
+    const int xc0 = half * cpt;          // split: the same column within this CTA's exchange buffer
+    const uint32_t t_lane = tmem_base + (static_cast<uint32_t>(q * 32) << 16);
+    const uint32_t t_row = t_lane + hc0;
+    // exchange buffer [HALF/4][128 rows] float4 at the start of the (by then idle) stage ring
+    const float4* xbuf = reinterpret_cast<const float4*>(smem_raw + (smem_base - smem_u32(smem_raw)));
+    auto add_peer = [&](float* v, int c) {  // v[0..31] += the peer's partial sums of chunk c of this thread
+      if (SPLIT == 2 && split) {
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          const float4 t = xbuf[((xc0 + c * 32) / 4 + i) * GEMM_BLOCK_M + row_in_tile];
+          v[4 * i] += t.x; v[4 * i + 1] += t.y; v[4 * i + 2] += t.z; v[4 * i + 3] += t.w;
+        }
+      }
+    };
 
     // ---- operands that do not depend on the accumulator: fetch before waiting for the MMAs
     float cprev[EPI == EPI_LSTM ? HALF / 4 : 1];
@@ -272,8 +309,10 @@ gemm_tc_kernel(const __grid_constant__ GemmParams P) {
             pb.row_bias + static_cast<long long>(row) * pb.ld_row_bias + col0 + hc0);
 #pragma unroll
         for (int i = 0; i < HALF / 4; ++i) {
-          const float4 t = __ldg(rp + i);
-          rbias[4 * i] = t.x; rbias[4 * i + 1] = t.y; rbias[4 * i + 2] = t.z; rbias[4 * i + 3] = t.w;
+          if (4 * i < cpt) {
+            const float4 t = __ldg(rp + i);
+            rbias[4 * i] = t.x; rbias[4 * i + 1] = t.y; rbias[4 * i + 2] = t.z; rbias[4 * i + 3] = t.w;
+          }
         }
       }
       if (pb.tok_table != nullptr && row_ok) {
@@ -282,8 +321,10 @@ gemm_tc_kernel(const __grid_constant__ GemmParams P) {
             pb.tok_table + static_cast<long long>(tk) * pb.ld_tok_table + col0 + hc0);
 #pragma unroll
         for (int i = 0; i < HALF / 4; ++i) {
-          const float4 t = __ldg(tp + i);
-          rbias[4 * i] += t.x; rbias[4 * i + 1] += t.y; rbias[4 * i + 2] += t.z; rbias[4 * i + 3] += t.w;
+          if (4 * i < cpt) {
+            const float4 t = __ldg(tp + i);
+            rbias[4 * i] += t.x; rbias[4 * i + 1] += t.y; rbias[4 * i + 2] += t.z; rbias[4 * i + 3] += t.w;
+          }
         }
       }
       if (row_ok) {
@@ -291,8 +332,10 @@ gemm_tc_kernel(const __grid_constant__ GemmParams P) {
             pb.c_in + static_cast<long long>(row) * pb.hidden + ((col0 + hc0) >> 2));
 #pragma unroll
         for (int i = 0; i < HALF / 16; ++i) {
-          const float4 c = __ldg(cp + i);
-          cprev[4 * i] = c.x; cprev[4 * i + 1] = c.y; cprev[4 * i + 2] = c.z; cprev[4 * i + 3] = c.w;
+          if (16 * i < cpt) {
+            const float4 c = __ldg(cp + i);
+            cprev[4 * i] = c.x; cprev[4 * i + 1] = c.y; cprev[4 * i + 2] = c.z; cprev[4 * i + 3] = c.w;
+          }
         }
       } else {
 #pragma unroll
@@ -304,6 +347,31 @@ gemm_tc_kernel(const __grid_constant__ GemmParams P) {
     tc_fence_after_sync();
     if (P.trace_detail != nullptr && threadIdx.x == 128)
       atomicAdd(P.trace_detail + 4 * P.trace_slot + 1, global_timer_ns() - *t_start_smem);
+
+    if (SPLIT == 2 && split) {
+      // 1. tell the peer that my MMAs have retired (my stage ring may now be overwritten by its partial
+      //    sums), wait for the same news from the peer
+      const uint32_t peer = static_cast<uint32_t>(rank ^ 1);
+      if (threadIdx.x == 128) mbar_arrive_cluster(mapa_shared(peer_done_bar, peer));
+      mbar_wait_cluster(peer_done_bar, 0);
+      // 2. ship my partial sums of the PEER's column half: thread = row x cpt columns, written as
+      //    [column/4][row] float4 so that a warp's stores (and the peer's loads) are conflict-free
+      const uint32_t xb_remote = mapa_shared(smem_base, peer);
+      const int pc0 = static_cast<int>(peer) * HALF + half * cpt;
+#pragma unroll 1
+      for (int c = 0; c * 32 < cpt; ++c) {
+        float v[32];
+        tmem_ld_32x32(t_lane + pc0 + c * 32, v);
+        tmem_ld_wait();
+#pragma unroll
+        for (int i = 0; i < 8; ++i)
+          st_cluster_f32x4(xb_remote + static_cast<uint32_t>((((xc0 + c * 32) / 4 + i) * GEMM_BLOCK_M + row_in_tile) * 16),
+                           v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
+      }
+      mbar_arrive_cluster(mapa_shared(xfer_bar, peer));
+      // 3. wait for the peer's partial sums of my half
+      mbar_wait_cluster(xfer_bar, 0);
+    }
 
     if (active) {
       if constexpr (EPI == EPI_STORE) {
@@ -363,9 +431,11 @@ gemm_tc_kernel(const __grid_constant__ GemmParams P) {
         const int H = pb.hidden;
 #pragma unroll
         for (int c = 0; c < NCH; ++c) {
+          if (c * 32 >= cpt) break;
           float v[32];
           tmem_ld_32x32(t_row + c * 32, v);
           tmem_ld_wait();
+          add_peer(v, c);
           if (row_ok) {
             const int tc = hc0 + c * 32;
             const int j0 = (col0 + tc) >> 2;  // first hidden unit of this chunk (8 units)
@@ -398,20 +468,23 @@ gemm_tc_kernel(const __grid_constant__ GemmParams P) {
           }
         }
       } else {  // EPI_LOGITS: one partial record per (row, 64-column group)
-        static_assert(EPI != EPI_LOGITS || HALF == LOGIT_GROUP, "logit records are 64 columns wide");
+        static_assert(EPI != EPI_LOGITS || (SPLIT == 1 && HALF == LOGIT_GROUP) || (SPLIT == 2 && HALF == 2 * LOGIT_GROUP),
+                      "logit records are 64 columns wide (split kernels: every problem must have ksplit == 2)");
+        constexpr int NCL = LOGIT_GROUP / 32;
         float tv[TOPK];
         int ti[TOPK];
 #pragma unroll
         for (int k = 0; k < TOPK; ++k) { tv[k] = -INFINITY; ti[k] = 0x7fffffff; }
         const int gcol0 = col0 + hc0;
-        const bool full = gcol0 + HALF <= pb.N;  // all columns of this thread are real vocabulary
+        const bool full = gcol0 + LOGIT_GROUP <= pb.N;  // all columns of this thread are real vocabulary
         // pass 1: bias, mask, optional store, running top-K (ascending column scan: ties keep the
         // lower index, like torch.max on the reference path)
 #pragma unroll 1
-        for (int c = 0; c < NCH; ++c) {
+        for (int c = 0; c < NCL; ++c) {
           float v[32];
           tmem_ld_32x32(t_row + c * 32, v);
           tmem_ld_wait();
+          add_peer(v, c);
           const int tc = hc0 + c * 32;
           const int cb = col0 + tc;
 #pragma unroll
@@ -455,10 +528,11 @@ gemm_tc_kernel(const __grid_constant__ GemmParams P) {
         float se = 0.f;
         const float m2 = tv[0] * 1.4426950408889634f;
 #pragma unroll 1
-        for (int c = 0; c < NCH; ++c) {
+        for (int c = 0; c < NCL; ++c) {
           float v[32];
           tmem_ld_32x32(t_row + c * 32, v);
           tmem_ld_wait();
+          add_peer(v, c);
           const int tc = hc0 + c * 32;
           const int cb = col0 + tc;
           float s4[4] = {0.f, 0.f, 0.f, 0.f};
@@ -481,7 +555,7 @@ gemm_tc_kernel(const __grid_constant__ GemmParams P) {
           const int groups_per_tile = BLOCK_N / LOGIT_GROUP;
           const int n_groups = ((pb.N + BLOCK_N - 1) / BLOCK_N) * groups_per_tile;
           float* rec = pb.partial + (static_cast<long long>(row) * n_groups +
-                                     n_tile * groups_per_tile + half) * LogitRec<TOPK>::WORDS;
+                                     n_tile * groups_per_tile + hc0 / LOGIT_GROUP) * LogitRec<TOPK>::WORDS;
           if (gcol0 >= pb.N) se = 0.f;  // empty group: neutral record
           rec[0] = se;
 #pragma unroll
@@ -516,5 +590,9 @@ const char* make_tmap_bf16(CUtensorMap* out, const void* ptr, uint64_t cols, uin
 // Dispatch to the instantiated kernel. grid = (max n_tiles, max m_tiles, groups).
 cudaError_t gemm_launch(const GemmParams& P, int groups, int max_m, int max_n, int a_terms,
                         int w_terms, int block_n, int epi, int topk, cudaStream_t stream);
+// Cluster (2,1,1) split-K variant: EPI_LSTM with block_n 128 (per-problem ksplit 1 or 2) or EPI_LOGITS with
+// block_n 256 (ksplit 2).  grid_x = max over problems of n_tiles * ksplit, rounded up to even.
+cudaError_t gemm_launch_split(const GemmParams& P, int groups, int max_m, int grid_x, int a_terms, int w_terms,
+                              int block_n, int epi, int topk, cudaStream_t stream);
 
 }  // namespace echr

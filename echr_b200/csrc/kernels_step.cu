@@ -308,11 +308,160 @@ attention_staged_kernel(const float* __restrict__ q, const void* __restrict__ pr
   trace_end(trace, trace_slot);
 }
 
+// ---------------------------------------------------------------------------------------------
+// Latency-regime variant (short windows, a few hundred rows): one CTA per decode row, every warp owns
+// clips (warp, warp+NW, ...) in BOTH passes, so the clip features of the warp's first two clips are
+// requested before the softmax and are in flight while the block agrees on the statistics.  A row
+// costs two dependent global round trips (window descriptor -> everything else) and two block
+// barriers; the streaming kernel above takes one round trip per 4 clips of pass 2 and four barriers.
+template <bool BF16, int THREADS>
+__global__ void __launch_bounds__(THREADS, 1024 / THREADS)
+attention_v2_kernel(const float* __restrict__ q, const void* __restrict__ proj_v,
+                    const void* __restrict__ clip_v, long long ld_clip, const float* __restrict__ alpha,
+                    const int32_t* __restrict__ row_start, const int32_t* __restrict__ row_len,
+                    float* __restrict__ out_f32, bf16* __restrict__ out_hi, bf16* __restrict__ out_lo,
+                    long long ld_bf, unsigned long long* trace, int trace_slot) {
+  trace_begin(trace, trace_slot);
+  constexpr int NW = THREADS / 32;
+  __shared__ float sc[ATT_MAX_L];
+  __shared__ __align__(16) float red[NW][512];
+  __shared__ __align__(16) float s_alpha[HID];
+  const int r = blockIdx.x;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  for (int i = threadIdx.x; i < HID; i += THREADS) s_alpha[i] = -2.f * __ldg(alpha + i);
+  pdl_trigger();
+  pdl_wait();
+  const int s0 = row_start[r];
+  const int L = row_len[r];
+  // lane owns hidden units [128*m + 4*lane, +4), m = 0..3, and clip columns float4 #(lane + 32*m)
+  float qv[16];
+#pragma unroll
+  for (int m = 0; m < 4; ++m) {
+    const float4 t = __ldg(reinterpret_cast<const float4*>(q + (long long)r * HID + 128 * m + 4 * lane));
+    qv[4 * m] = t.x; qv[4 * m + 1] = t.y; qv[4 * m + 2] = t.z; qv[4 * m + 3] = t.w;
+  }
+  auto load_row16 = [&](const void* base, long long ld, int cols, int l, float* v) {
+    if (BF16) {
+      const bf16* row = reinterpret_cast<const bf16*>(base) + (long long)(s0 + l) * ld;
+#pragma unroll
+      for (int m = 0; m < 4; ++m) {
+        const uint2 u = __ldg(reinterpret_cast<const uint2*>(row + 128 * m + 4 * lane));
+        const __nv_bfloat162 b0 = *reinterpret_cast<const __nv_bfloat162*>(&u.x);
+        const __nv_bfloat162 b1 = *reinterpret_cast<const __nv_bfloat162*>(&u.y);
+        v[4 * m] = __low2float(b0); v[4 * m + 1] = __high2float(b0);
+        v[4 * m + 2] = __low2float(b1); v[4 * m + 3] = __high2float(b1);
+      }
+    } else {
+      const float* row = reinterpret_cast<const float*>(base) + (long long)(s0 + l) * ld;
+#pragma unroll
+      for (int m = 0; m < 4; ++m) {
+        float4 t = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (128 * m + 4 * lane < cols) t = __ldg(reinterpret_cast<const float4*>(row + 128 * m + 4 * lane));
+        v[4 * m] = t.x; v[4 * m + 1] = t.y; v[4 * m + 2] = t.z; v[4 * m + 3] = t.w;
+      }
+    }
+  };
+  const int clip_cols = BF16 ? CLIP_PAD : ECHR_VIDEO_DIM;
+  // ---- pass 1: scores of this warp's clips, two at a time
+  for (int l = warp; l < L; l += 2 * NW) {
+    const int l2 = l + NW;
+    const bool two = l2 < L;
+    float pa[16], pb2[16];
+    load_row16(proj_v, HID, HID, l, pa);
+    load_row16(proj_v, HID, HID, two ? l2 : l, pb2);
+    float sa = 0.f, sb = 0.f;
+#pragma unroll
+    for (int m = 0; m < 4; ++m) {
+      const float4 a4 = *reinterpret_cast<const float4*>(s_alpha + 128 * m + 4 * lane);
+      const float av[4] = {a4.x, a4.y, a4.z, a4.w};
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        sa = fmaf(av[i], rcp_fast(fmaf(pa[4 * m + i], qv[4 * m + i], 1.0f)), sa);
+        sb = fmaf(av[i], rcp_fast(fmaf(pb2[4 * m + i], qv[4 * m + i], 1.0f)), sb);
+      }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      sa += __shfl_xor_sync(0xffffffffu, sa, o);
+      sb += __shfl_xor_sync(0xffffffffu, sb, o);
+    }
+    if (lane == 0) {
+      sc[l] = sa;
+      if (two) sc[l2] = sb;
+    }
+  }
+  // ---- request the first two clip rows of this warp before the block agrees on the softmax
+  float ca[16], cb[16];
+  const bool has_a = warp < L, has_b = warp + NW < L;
+  if (has_a) load_row16(clip_v, ld_clip, clip_cols, warp, ca);
+  if (has_b) load_row16(clip_v, ld_clip, clip_cols, warp + NW, cb);
+  __syncthreads();
+  float mx = -INFINITY;
+  for (int l = lane; l < L; l += 32) mx = fmaxf(mx, sc[l]);
+  mx = warp_max(mx);
+  float sum = 0.f;
+  for (int l = lane; l < L; l += 32) sum += __expf(sc[l] - mx);
+  sum = warp_sum(sum);
+  const float inv = 1.0f / sum;
+  // ---- pass 2: weighted sum of this warp's clips
+  float acc[16];
+#pragma unroll
+  for (int i = 0; i < 16; ++i) acc[i] = 0.f;
+  if (has_a) {
+    const float w = __expf(sc[warp] - mx) * inv;
+#pragma unroll
+    for (int i = 0; i < 16; ++i) acc[i] = w * ca[i];
+  }
+  if (has_b) {
+    const float w = __expf(sc[warp + NW] - mx) * inv;
+#pragma unroll
+    for (int i = 0; i < 16; ++i) acc[i] = fmaf(w, cb[i], acc[i]);
+  }
+  for (int l = warp + 2 * NW; l < L; l += 2 * NW) {
+    const int l2 = l + NW;
+    const bool two = l2 < L;
+    load_row16(clip_v, ld_clip, clip_cols, l, ca);
+    load_row16(clip_v, ld_clip, clip_cols, two ? l2 : l, cb);
+    const float wa = __expf(sc[l] - mx) * inv;
+    const float wb = two ? __expf(sc[l2] - mx) * inv : 0.f;
+#pragma unroll
+    for (int i = 0; i < 16; ++i) acc[i] = fmaf(wa, ca[i], fmaf(wb, cb[i], acc[i]));
+  }
+#pragma unroll
+  for (int m = 0; m < 4; ++m)
+    *reinterpret_cast<float4*>(&red[warp][128 * m + 4 * lane]) =
+        make_float4(acc[4 * m], acc[4 * m + 1], acc[4 * m + 2], acc[4 * m + 3]);
+  __syncthreads();
+  const int nw_used = L < NW ? L : NW;  // warps beyond the window hold zeros
+  for (int c = threadIdx.x; c < ECHR_VIDEO_DIM; c += THREADS) {
+    float v = 0.f;
+    for (int g = 0; g < nw_used; ++g) v += red[g][c];
+    if (out_f32 != nullptr) out_f32[(long long)r * ECHR_VIDEO_DIM + c] = v;
+    if (out_hi != nullptr) {
+      bf16 h, l2;
+      split_bf16(v, h, l2);
+      out_hi[(long long)r * ld_bf + c] = h;
+      if (out_lo != nullptr) out_lo[(long long)r * ld_bf + c] = l2;
+    }
+  }
+  trace_end(trace, trace_slot);
+}
+
 // max_len: largest window of the launch (0 = unknown).  The staged kernel (one CTA per SM: it owns
 // ~200 KB of shared memory) is used when every window fits and the launch is a single wave
 // (rows <= 148); beyond that the streaming kernel wins because several of its CTAs share an SM and
 // it can co-reside with the concurrent logit GEMM of the decode graph (measured: profiles/).
 // ECHR_ATT_STAGED=1 / ECHR_ATT_STREAM=1 force one or the other.
+// rows up to which the latency-regime kernel is used (ECHR_ATT_V2_ROWS; 0 disables it)
+static int att_v2_rows() {
+  static int v = -1;
+  if (v < 0) {
+    const char* e = getenv("ECHR_ATT_V2_ROWS");
+    v = e ? atoi(e) : 1024;
+  }
+  return v;
+}
+
 cudaError_t launch_attention(const float* q, const void* proj, const void* clip, int64_t ld_clip,
                              int clip_bf16, const float* alpha, const int32_t* row_start,
                              const int32_t* row_len, int64_t rows, float* out_f32, bf16* out_hi,
@@ -340,6 +489,14 @@ cudaError_t launch_attention(const float* q, const void* proj, const void* clip,
     else
       e = launch_pdl(attention_staged_kernel<false, ATT_THREADS>, dim3((unsigned)rows), dim3(ATT_THREADS), stage, st, q, proj, clip,
                      (long long)ld_clip, alpha, row_start, row_len, out_f32, out_hi, out_lo, (long long)ld_bf, max_len, trace, trace_slot);
+  } else if (att_v2_rows() > 0 && rows <= att_v2_rows() && max_len > 0 && max_len <= 128) {
+    // latency regime: short windows, at most a couple of CTAs per SM
+    if (clip_bf16)
+      e = launch_pdl(attention_v2_kernel<true, ATT_THREADS>, dim3((unsigned)rows), dim3(ATT_THREADS), 0, st, q, proj, clip,
+                     (long long)ld_clip, alpha, row_start, row_len, out_f32, out_hi, out_lo, (long long)ld_bf, trace, trace_slot);
+    else
+      e = launch_pdl(attention_v2_kernel<false, ATT_THREADS>, dim3((unsigned)rows), dim3(ATT_THREADS), 0, st, q, proj, clip,
+                     (long long)ld_clip, alpha, row_start, row_len, out_f32, out_hi, out_lo, (long long)ld_bf, trace, trace_slot);
   } else {
     // many short windows (throughput regime): 256-thread CTAs pack more rows per SM; otherwise 512
     const bool small = rows > 148 * 4 && max_len > 0 && max_len <= 64;

@@ -85,7 +85,9 @@ def test_batched_videos_match_oracle_and_single_calls():
         tf = O.teacher_forced_logprobs(sd, *ctx, labels_of(s_ref))
         helpers.check_tokens(seq.cpu().numpy(), s_ref.numpy(), tf.topk(2, dim=2)[0].numpy(), "batched")
         single = m.caption_batch([helpers.video_tuple(v, DEV)])[0]
-        assert torch.equal(single[0], seq) and torch.equal(single[1], logp)  # rows are independent: bit-exact
+        # rows are independent; the engine may pick another attention / GEMM variant for another batch
+        # size (different fp32 summation order), so log-probs agree to rounding, tokens exactly
+        assert torch.equal(single[0], seq) and (single[1] - logp).abs().max().item() < 1e-5
 
 
 def test_empty_result_and_early_stop_trim():
