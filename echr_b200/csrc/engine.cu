@@ -183,6 +183,8 @@ static int ksplit_mask() {
   }
   return v;
 }
+// window-length bucket baked into a decode graph (attention variant and its shared-memory staging size)
+static int len_bucket(int max_len) { return ((max_len + 31) / 32) * 32; }
 static int m_tiles_of(int rows) { return (rows + GEMM_BLOCK_M - 1) / GEMM_BLOCK_M; }
 // logit GEMM as 128 x 256 tiles shared by CTA pairs (23 x 2 CTAs per 128 rows at the ECHR vocabulary)
 static bool logit_split(const echr_model* m, int rows) {
@@ -488,12 +490,13 @@ extern "C" int echr_batch_create(const echr_model_t* model, const echr_capacity_
 
 extern "C" int echr_batch_destroy(echr_batch_t* b) {
   if (!b) return ECHR_OK;
-  if (b->graph_exec) cudaGraphExecDestroy(b->graph_exec);
+  for (int i = 0; i < echr_batch::GRAPH_SLOTS; ++i)
+    if (b->graphs[i].exec) cudaGraphExecDestroy(b->graphs[i].exec);
   if (b->cap_stream) {
     cudaStreamDestroy(b->cap_stream);
     cudaStreamDestroy(b->cap_stream2);
-    cudaEventDestroy(b->cap_events[0]);
-    cudaEventDestroy(b->cap_events[1]);
+    cudaStreamDestroy(b->cap_stream3);
+    for (int i = 0; i < 4; ++i) cudaEventDestroy(b->cap_events[i]);
   }
   cudaFreeHost(b->host_stage);
   cudaFreeHost(b->host_tap_stage);
@@ -593,6 +596,70 @@ extern "C" int echr_batch_set_inputs(echr_batch_t* b, const echr_batch_desc_t* d
   return ECHR_OK;
 }
 
+// Graph cache: look `key` up, or capture `enqueue(capture stream)` into a new graph (evicting the least
+// recently used slot), then launch it on `st`.
+static int ensure_capture_streams(echr_batch* b) {
+  if (b->cap_stream != nullptr) return ECHR_OK;
+  // capture on private streams: the caller's stream may be the legacy default stream, which cannot be captured
+  ECHR_CUDA(cudaStreamCreateWithFlags(&b->cap_stream, cudaStreamNonBlocking));
+  ECHR_CUDA(cudaStreamCreateWithFlags(&b->cap_stream2, cudaStreamNonBlocking));
+  ECHR_CUDA(cudaStreamCreateWithFlags(&b->cap_stream3, cudaStreamNonBlocking));
+  for (int i = 0; i < 4; ++i) ECHR_CUDA(cudaEventCreateWithFlags(&b->cap_events[i], cudaEventDisableTiming));
+  return ECHR_OK;
+}
+
+template <typename F>
+static int run_graph(echr_batch* b, const long long (&key)[6], cudaStream_t st, const char* what, bool traced, F&& enqueue) {
+  echr_batch::GraphSlot* slot = nullptr;
+  for (int i = 0; i < echr_batch::GRAPH_SLOTS; ++i) {
+    echr_batch::GraphSlot& g = b->graphs[i];
+    if (g.exec != nullptr && memcmp(g.key, key, sizeof(g.key)) == 0) { slot = &g; break; }
+  }
+  if (slot == nullptr) {
+    ECHR_TRY(ensure_capture_streams(b));
+    slot = &b->graphs[0];
+    for (int i = 0; i < echr_batch::GRAPH_SLOTS; ++i) {
+      echr_batch::GraphSlot& g = b->graphs[i];
+      if (g.exec == nullptr) { slot = &g; break; }
+      if (g.stamp < slot->stamp) slot = &g;
+    }
+    if (slot->exec) { cudaGraphExecDestroy(slot->exec); slot->exec = nullptr; }
+    if (traced) {
+      const char* tr = getenv("ECHR_TRACE");
+      b->trace_on = (tr != nullptr && tr[0] == '1') ? 1 : 0;
+      b->trace_n = 0;
+      if (b->trace_on)  // the trace slots belong to one graph: drop every other cached graph
+        for (int i = 0; i < echr_batch::GRAPH_SLOTS; ++i)
+          if (b->graphs[i].exec) { cudaGraphExecDestroy(b->graphs[i].exec); b->graphs[i].exec = nullptr; }
+    }
+    const int saved_trace = b->trace_on;
+    if (!traced) b->trace_on = 0;
+    const long long before = g_launches.load();
+    cudaGraph_t graph = nullptr;
+    ECHR_CUDA(cudaStreamBeginCapture(b->cap_stream, cudaStreamCaptureModeRelaxed));
+    const int rc = enqueue(b->cap_stream);
+    cudaError_t e = cudaStreamEndCapture(b->cap_stream, &graph);
+    if (!traced) b->trace_on = saved_trace;
+    if (rc != 0) { if (graph) cudaGraphDestroy(graph); return rc; }
+    if (e != cudaSuccess) return set_error(ECHR_ERR_CUDA, "%s: graph capture failed: %s", what, cudaGetErrorString(e));
+    e = cudaGraphInstantiate(&slot->exec, graph, 0);
+    cudaGraphDestroy(graph);
+    if (e != cudaSuccess) { slot->exec = nullptr; return set_error(ECHR_ERR_CUDA, "%s: graph instantiate failed: %s", what, cudaGetErrorString(e)); }
+    if (traced) b->trace_on = b->trace_on ? 2 : 0;  // 2: slots assigned, no more trace_next() calls
+    slot->kernels = g_launches.load() - before;
+    g_launches.store(before);
+    memcpy(slot->key, key, sizeof(slot->key));
+  }
+  slot->stamp = ++b->graph_clock;
+  if (traced && b->trace_on) {  // reset {min start, max end} before the replay
+    ECHR_CUDA(cudaMemsetAsync(b->trace, 0xff, sizeof(unsigned long long) * TRACE_SLOTS * 2, st));
+    ECHR_CUDA(cudaMemsetAsync(b->trace_detail, 0, sizeof(unsigned long long) * TRACE_SLOTS * 4, st));
+  }
+  ECHR_CUDA(cudaGraphLaunch(slot->exec, st));
+  count_launch((int)slot->kernels);
+  return ECHR_OK;
+}
+
 // =============================================================================================
 // Encode: context prologue + relation encoder
 // =============================================================================================
@@ -614,9 +681,17 @@ static int encode_clips(echr_batch_t* b, cudaStream_t st) {
 
 // event relation encoder from the event feature planes (MA:35-177): embedding -> query | key |
 // value*W_out, pair position embedding -> fc1 + tanh -> fc2, multi-head relation attention
-static int encode_relation(echr_batch_t* b, cudaStream_t st) {
+// `side` (optional, with the two events): the pair-position chain (embedding -> fc1 -> fc2) runs next to the
+// event chain (embedding -> query | key | value); they meet at the relation attention.
+static int encode_relation(echr_batch_t* b, cudaStream_t st, cudaStream_t side = nullptr, cudaEvent_t fork_ev = nullptr,
+                           cudaEvent_t join_ev = nullptr) {
   const echr_model* m = b->model;
   const int at = m->cfg.a_terms, wt = m->cfg.w_terms;
+  cudaStream_t ps = side != nullptr ? side : st;  // stream of the pair-position chain
+  if (side != nullptr) {
+    ECHR_CUDA(cudaEventRecord(fork_ev, st));
+    ECHR_CUDA(cudaStreamWaitEvent(side, fork_ev, 0));
+  }
   {
     GemmSpec s;
     s.A = &b->feat_pl; s.M = b->n_events; s.W = &m->w_event_emb; s.N = HID; s.K = FEAT_PAD;
@@ -630,21 +705,39 @@ static int encode_relation(echr_batch_t* b, cudaStream_t st) {
     s.bias = m->b_qky; s.out_f32 = b->qky; s.ld_f32 = 3 * HID;
     ECHR_TRY(run_gemm(&s, 1, at, wt, 128, EPI_STORE, 1, st, "query_key_value"));
   }
-  ECHR_CUDA(launch_posemb(b, st));
+  ECHR_CUDA(launch_posemb(b, ps));
   {
     GemmSpec s;
     s.A = &b->pe_pl; s.M = b->n_pairs; s.W = &m->w_fc1; s.N = HID; s.K = HID;
     s.bias = m->b_fc1; s.act = ACT_TANH;
     s.out_hi = b->hid_pl.plane(0); s.out_lo = at > 1 ? b->hid_pl.plane(1) : nullptr; s.ld_bf = HID;
-    ECHR_TRY(run_gemm(&s, 1, at, wt, 128, EPI_STORE, 1, st, "pair_pos_fc1"));
+    ECHR_TRY(run_gemm(&s, 1, at, wt, 128, EPI_STORE, 1, ps, "pair_pos_fc1"));
   }
   {
     GemmSpec s;
     s.A = &b->hid_pl; s.M = b->n_pairs; s.W = &m->w_fc2; s.N = ECHR_HEADS; s.K = HID;
     s.bias = m->b_fc2; s.out_f32 = b->pair_w; s.ld_f32 = ECHR_HEADS;
-    ECHR_TRY(run_gemm(&s, 1, at, wt, 16, EPI_STORE, 1, st, "pair_pos_fc2"));
+    ECHR_TRY(run_gemm(&s, 1, at, wt, 16, EPI_STORE, 1, ps, "pair_pos_fc2"));
+  }
+  if (side != nullptr) {
+    ECHR_CUDA(cudaEventRecord(join_ev, side));
+    ECHR_CUDA(cudaStreamWaitEvent(st, join_ev, 0));
   }
   ECHR_CUDA(launch_relation_attn(b, st));
+  return ECHR_OK;
+}
+
+// The encode pipeline as three concurrent chains: clips (plane split -> ctx2att), events, event pairs.
+static int enqueue_encode(echr_batch_t* b, cudaStream_t st, cudaStream_t s2, cudaStream_t s3, cudaEvent_t* ev) {
+  ECHR_CUDA(cudaEventRecord(ev[0], st));
+  ECHR_CUDA(cudaStreamWaitEvent(s2, ev[0], 0));
+  ECHR_TRY(encode_clips(b, s2));
+  ECHR_CUDA(cudaEventRecord(ev[1], s2));
+  if (b->n_events > 0) {
+    ECHR_CUDA(launch_event_feats(b, st));
+    ECHR_TRY(encode_relation(b, st, s3, ev[2], ev[3]));
+  }
+  ECHR_CUDA(cudaStreamWaitEvent(st, ev[1], 0));
   return ECHR_OK;
 }
 
@@ -652,10 +745,19 @@ extern "C" int echr_encode(echr_batch_t* b, void* stream) {
   ECHR_REQUIRE(b, "echr_encode: null batch");
   ECHR_REQUIRE(b->n_videos > 0, "echr_encode: no inputs set");
   cudaStream_t st = (cudaStream_t)stream;
-  ECHR_TRY(encode_clips(b, st));
-  if (b->n_events > 0) {
-    ECHR_CUDA(launch_event_feats(b, st));
-    ECHR_TRY(encode_relation(b, st));
+  ECHR_CUDA(init_pos_table());
+  static const bool graphed = !(getenv("ECHR_ENCODE_GRAPH") && getenv("ECHR_ENCODE_GRAPH")[0] == '0');
+  if (graphed) {
+    const long long key[6] = {2, b->n_videos, b->n_events, b->n_clips, b->n_pairs, b->max_n};
+    ECHR_TRY(run_graph(b, key, st, "encode", false, [&](cudaStream_t cs) {
+      return enqueue_encode(b, cs, b->cap_stream2, b->cap_stream3, b->cap_events);
+    }));
+  } else {
+    ECHR_TRY(encode_clips(b, st));
+    if (b->n_events > 0) {
+      ECHR_CUDA(launch_event_feats(b, st));
+      ECHR_TRY(encode_relation(b, st));
+    }
   }
   b->encoded = true;
   return ECHR_OK;
@@ -757,8 +859,8 @@ static int enqueue_init(echr_batch* b, int beam, cudaStream_t st) {
     s[i].A = &b->act[0]; s[i].a_col0 = col0[i]; s[i].M = (int)rows; s[i].W = &wv[i]; s[i].N = GATES; s[i].K = K[i];
     s[i].bias = m->b_lstm[layer[i]];
     s[i].out_f32 = b->row_bias[i]; s[i].ld_f32 = GATES;
-    ECHR_TRY(run_gemm(&s[i], 1, at, wt, 128, EPI_STORE, 1, st, "hoisted_context"));
   }
+  ECHR_TRY(run_gemm(s, 2, at, wt, 128, EPI_STORE, 1, st, "hoisted_context"));  // both streams in one launch
   return ECHR_OK;
 }
 
@@ -791,7 +893,7 @@ static int enqueue_step(echr_batch* b, int rows, int t, int topk, float* logits_
                              m->cfg.clip_bf16 ? (const void*)b->clip_pl.plane(0) : (const void*)b->c3d,
                              m->cfg.clip_bf16 ? CLIP_PAD : ECHR_VIDEO_DIM, m->cfg.clip_bf16, m->alpha,
                              b->row_start, b->row_len, rows, nullptr, cur.plane(0) + ACT_ATT,
-                             at > 1 ? cur.plane(1) + ACT_ATT : nullptr, ACT_LD, st, b->max_len, trace_ptr(b), trace_next(b, 1)));
+                             at > 1 ? cur.plane(1) + ACT_ATT : nullptr, ACT_LD, st, len_bucket(b->max_len), trace_ptr(b), trace_next(b, 1)));
   }
   if (parts & PART_GATES) {
     GemmSpec s[3];
@@ -878,52 +980,16 @@ static int enqueue_decode(echr_batch* b, int beam, int mode, cudaStream_t st, cu
   return ECHR_OK;
 }
 
-// Capture the whole decode (init + seq_length steps) into one CUDA graph per (rows, beam, mode)
-// and replay it: one launch from the host per batch instead of ~150.
+// The whole decode (init + seq_length steps) is one CUDA graph per (rows, beam mode, window bucket): one
+// launch from the host per batch instead of ~150.
 static int run_decode(echr_batch* b, int beam, int mode, cudaStream_t st) {
   ECHR_REQUIRE(b->encoded, "decode: call echr_encode first");
   ECHR_REQUIRE((long long)b->n_events * beam <= b->cap.max_rows, "decode: %d events x beam %d exceed max_rows %lld", b->n_events, beam, (long long)b->cap.max_rows);
   if (b->n_events == 0) return ECHR_OK;
   const int rows = b->n_events * beam;
-  const int key_beam = mode == MODE_BEAM ? beam : 0;
-  if (b->graph_exec == nullptr || b->graph_rows != rows || b->graph_beam != key_beam) {
-    if (b->graph_exec) { cudaGraphExecDestroy(b->graph_exec); b->graph_exec = nullptr; }
-    const long long before = g_launches.load();
-    cudaGraph_t graph = nullptr;
-    {
-      const char* tr = getenv("ECHR_TRACE");
-      b->trace_on = (tr != nullptr && tr[0] == '1') ? 1 : 0;
-      b->trace_n = 0;
-    }
-    // capture on a private stream: the caller's stream may be the legacy default stream, which
-    // cannot be captured
-    if (b->cap_stream == nullptr) {
-      ECHR_CUDA(cudaStreamCreateWithFlags(&b->cap_stream, cudaStreamNonBlocking));
-      ECHR_CUDA(cudaStreamCreateWithFlags(&b->cap_stream2, cudaStreamNonBlocking));
-      ECHR_CUDA(cudaEventCreateWithFlags(&b->cap_events[0], cudaEventDisableTiming));
-      ECHR_CUDA(cudaEventCreateWithFlags(&b->cap_events[1], cudaEventDisableTiming));
-    }
-    ECHR_CUDA(cudaStreamBeginCapture(b->cap_stream, cudaStreamCaptureModeRelaxed));
-    int rc = enqueue_decode(b, beam, mode, b->cap_stream, b->cap_stream2);
-    cudaError_t e = cudaStreamEndCapture(b->cap_stream, &graph);
-    if (rc != 0) { if (graph) cudaGraphDestroy(graph); return rc; }
-    if (e != cudaSuccess) return set_error(ECHR_ERR_CUDA, "decode: graph capture failed: %s", cudaGetErrorString(e));
-    e = cudaGraphInstantiate(&b->graph_exec, graph, 0);
-    cudaGraphDestroy(graph);
-    if (e != cudaSuccess) { b->graph_exec = nullptr; return set_error(ECHR_ERR_CUDA, "decode: graph instantiate failed: %s", cudaGetErrorString(e)); }
-    b->trace_on = b->trace_on ? 2 : 0;  // 2: slots assigned, no more trace_next() calls
-    b->graph_kernels = g_launches.load() - before;
-    g_launches.store(before);
-    b->graph_rows = rows;
-    b->graph_beam = key_beam;
-  }
-  if (b->trace_on) {  // reset {min start, max end} before the replay
-    ECHR_CUDA(cudaMemsetAsync(b->trace, 0xff, sizeof(unsigned long long) * TRACE_SLOTS * 2, st));
-    ECHR_CUDA(cudaMemsetAsync(b->trace_detail, 0, sizeof(unsigned long long) * TRACE_SLOTS * 4, st));
-  }
-  ECHR_CUDA(cudaGraphLaunch(b->graph_exec, st));
-  count_launch((int)b->graph_kernels);
-  return ECHR_OK;
+  const long long key[6] = {1, rows, mode == MODE_BEAM ? beam : 0, len_bucket(b->max_len), 0, 0};
+  return run_graph(b, key, st, "decode", true,
+                   [&](cudaStream_t cs) { return enqueue_decode(b, beam, mode, cs, b->cap_stream2); });
 }
 
 static int copy_results(echr_batch* b, int32_t* tokens, float* logp, float* score, cudaMemcpyKind kind,

@@ -103,15 +103,21 @@ struct echr_batch {
   int32_t* beam_hist_tok;   // [2][rows][S]
   float* beam_hist_lp;      // [2][rows][S]
   float* best_score;        // [events]
-  // decode graph cache
-  cudaGraphExec_t graph_exec;
-  cudaStream_t cap_stream;   // private stream the decode graph is captured on
-  cudaStream_t cap_stream2;  // forked branch inside the capture (next step's attention)
-  cudaEvent_t cap_events[2]; // fork / join markers, reused inside the capture
-  int graph_rows, graph_beam;
-  int32_t *graph_tokens_out;
-  float *graph_logp_out, *graph_score_out;
-  int64_t graph_kernels;
+  // CUDA graph cache (LRU): decode graphs keyed by (rows, beam mode, window-length bucket), encode graphs
+  // keyed by the batch shape.  A key holds every host-side value the enqueue code bakes into the launches.
+  struct GraphSlot {
+    long long key[6];
+    cudaGraphExec_t exec;
+    long long kernels;  // kernel nodes in the graph
+    unsigned long long stamp;
+  };
+  static constexpr int GRAPH_SLOTS = 8;
+  GraphSlot graphs[GRAPH_SLOTS];
+  unsigned long long graph_clock;
+  cudaStream_t cap_stream;   // private stream graphs are captured on
+  cudaStream_t cap_stream2;  // forked branches inside a capture
+  cudaStream_t cap_stream3;
+  cudaEvent_t cap_events[4]; // fork / join markers, reused inside a capture
   // timeline trace (ECHR_TRACE=1): device [2*TRACE_SLOTS] u64, host-side kind of every slot
   unsigned long long* trace;
   unsigned long long* trace_detail;  // [TRACE_SLOTS][4], GEMM kernels only (see gemm_tc.cuh)
@@ -129,6 +135,7 @@ cudaError_t launch_split(const float* src, int64_t rows, int64_t cols, int64_t l
 cudaError_t launch_event_feats(const echr_batch* b, cudaStream_t st);
 cudaError_t launch_gather_tap(const echr_batch* b, const float* tap_src, cudaStream_t st);
 cudaError_t launch_posemb(const echr_batch* b, cudaStream_t st);
+cudaError_t init_pos_table();  // uploads the position-embedding divisors (once per device; synchronous)
 cudaError_t launch_relation_attn(const echr_batch* b, cudaStream_t st);
 // ---- kernels_step.cu
 cudaError_t launch_attention(const float* q, const void* proj, const void* clip, int64_t ld_clip,

@@ -24,9 +24,40 @@ __global__ void split_planes_kernel(const float* __restrict__ src, long long row
   }
 }
 
+// 4 columns per thread: one 16-byte load, one 8-byte store per plane (rows of 4k columns, 16-byte aligned)
+__global__ void split_planes_vec4_kernel(const float* __restrict__ src, long long rows, int cols, long long ld_src,
+                                         bf16* __restrict__ hi, bf16* __restrict__ lo, long long ld_dst,
+                                         int cols_dst) {
+  const int q_per_row = cols_dst >> 2;
+  const long long total = rows * q_per_row;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x) {
+    const long long r = i / q_per_row;
+    const int c = static_cast<int>(i - r * q_per_row) << 2;
+    float4 x = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (c < cols) x = __ldg(reinterpret_cast<const float4*>(src + r * ld_src + c));
+    __align__(8) bf16 h[4], l[4];
+    split_bf16(x.x, h[0], l[0]); split_bf16(x.y, h[1], l[1]);
+    split_bf16(x.z, h[2], l[2]); split_bf16(x.w, h[3], l[3]);
+    *reinterpret_cast<uint2*>(hi + r * ld_dst + c) = *reinterpret_cast<const uint2*>(h);
+    if (lo != nullptr) *reinterpret_cast<uint2*>(lo + r * ld_dst + c) = *reinterpret_cast<const uint2*>(l);
+  }
+}
+
 cudaError_t launch_split(const float* src, int64_t rows, int64_t cols, int64_t ld_src, bf16* hi,
                          bf16* lo, int64_t ld_dst, int64_t cols_dst, cudaStream_t st) {
   if (rows == 0 || cols_dst == 0) return cudaSuccess;
+  const bool vec = (cols % 4 == 0) && (ld_src % 4 == 0) && (cols_dst % 4 == 0) && (ld_dst % 4 == 0) &&
+                   ((reinterpret_cast<uintptr_t>(src) & 15) == 0) && ((reinterpret_cast<uintptr_t>(hi) & 7) == 0) &&
+                   (lo == nullptr || (reinterpret_cast<uintptr_t>(lo) & 7) == 0);
+  if (vec) {
+    const long long total = rows * (cols_dst / 4);
+    long long blocks = (total + 255) / 256;
+    if (blocks > 148 * 16) blocks = 148 * 16;
+    split_planes_vec4_kernel<<<(int)blocks, 256, 0, st>>>(src, rows, (int)cols, ld_src, hi, lo, ld_dst, (int)cols_dst);
+    count_launch();
+    return cudaGetLastError();
+  }
   const long long total = rows * cols_dst;
   long long blocks = (total + 255) / 256;
   if (blocks > 148 * 16) blocks = 148 * 16;
@@ -36,29 +67,42 @@ cudaError_t launch_split(const float* src, int64_t rows, int64_t cols, int64_t l
 }
 
 // ---------------------------------------------------------------------------------------------
-// one block per event, 256 threads, 4 columns each of the 1024-wide feature row
-__global__ void __launch_bounds__(256)
+// one block per event: 4 clip groups x 128 threads (one float4 of the 500 columns each) accumulate the
+// span in parallel, then 256 threads write the 1024-wide feature row (mean clip feature | proposal state)
+__global__ void __launch_bounds__(512)
 event_feats_kernel(const float* __restrict__ c3d, const float* __restrict__ tap,
                    const int32_t* __restrict__ ev_start, const int32_t* __restrict__ ev_len,
-                   const int32_t* __restrict__ ev_ind, bf16* __restrict__ hi, bf16* __restrict__ lo) {
+                   bf16* __restrict__ hi, bf16* __restrict__ lo) {
+  __shared__ __align__(16) float part[4][512];
   const int e = blockIdx.x;
   const int s = ev_start[e], len = ev_len[e];
-  (void)ev_ind;
-  const float inv = 1.0f / (float)len;
-  for (int c = threadIdx.x; c < FEAT_PAD; c += blockDim.x) {
-    float v = 0.f;
-    if (c < ECHR_VIDEO_DIM) {
-      float acc = 0.f;
-      for (int l = 0; l < len; ++l) acc += __ldg(c3d + (long long)(s + l) * ECHR_VIDEO_DIM + c);
-      v = acc / (float)len;
-      (void)inv;
-    } else if (c < ECHR_VIDEO_DIM + HID) {
-      v = __ldg(tap + (long long)e * HID + (c - ECHR_VIDEO_DIM));  // tap was gathered by ind at set_inputs
+  const int grp = threadIdx.x >> 7, t = threadIdx.x & 127;
+  float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+  if (t < ECHR_VIDEO_DIM / 4) {
+    const float* base = c3d + (long long)s * ECHR_VIDEO_DIM + 4 * t;
+#pragma unroll 4
+    for (int l = grp; l < len; l += 4) {
+      const float4 c = __ldg(reinterpret_cast<const float4*>(base + (long long)l * ECHR_VIDEO_DIM));
+      acc.x += c.x; acc.y += c.y; acc.z += c.z; acc.w += c.w;
     }
-    bf16 h, l2;
-    split_bf16(v, h, l2);
-    hi[(long long)e * FEAT_PAD + c] = h;
-    if (lo != nullptr) lo[(long long)e * FEAT_PAD + c] = l2;
+  }
+  *reinterpret_cast<float4*>(&part[grp][4 * t]) = acc;
+  __syncthreads();
+  if (threadIdx.x < 256) {
+    const int c0 = 4 * threadIdx.x;
+    float v[4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const int c = c0 + i;
+      if (c < ECHR_VIDEO_DIM) v[i] = ((part[0][c] + part[1][c]) + (part[2][c] + part[3][c])) / (float)len;
+      else if (c < ECHR_VIDEO_DIM + HID) v[i] = __ldg(tap + (long long)e * HID + (c - ECHR_VIDEO_DIM));  // gathered by ind at set_inputs
+      else v[i] = 0.f;
+    }
+    __align__(8) bf16 h[4], l2[4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) split_bf16(v[i], h[i], l2[i]);
+    *reinterpret_cast<uint2*>(hi + (long long)e * FEAT_PAD + c0) = *reinterpret_cast<const uint2*>(h);
+    if (lo != nullptr) *reinterpret_cast<uint2*>(lo + (long long)e * FEAT_PAD + c0) = *reinterpret_cast<const uint2*>(l2);
   }
 }
 
@@ -80,7 +124,7 @@ cudaError_t launch_gather_tap(const echr_batch* b, const float* tap_src, cudaStr
 
 cudaError_t launch_event_feats(const echr_batch* b, cudaStream_t st) {
   if (b->n_events == 0) return cudaSuccess;
-  event_feats_kernel<<<b->n_events, 256, 0, st>>>(b->c3d, b->tap, b->ev_start, b->ev_len, b->ev_ind,
+  event_feats_kernel<<<b->n_events, 512, 0, st>>>(b->c3d, b->tap, b->ev_start, b->ev_len,
                                                   b->feat_pl.plane(0),
                                                   b->feat_pl.planes > 1 ? b->feat_pl.plane(1) : nullptr);
   count_launch();
@@ -138,7 +182,7 @@ posemb_kernel(const int32_t* __restrict__ ev_start, const int32_t* __restrict__ 
   }
 }
 
-static cudaError_t upload_pos_div() {
+cudaError_t init_pos_table() {
   static bool done = false;  // per process; the table is device-constant per context
   static int done_dev = -1;
   int dev = 0;
@@ -153,7 +197,7 @@ static cudaError_t upload_pos_div() {
 
 cudaError_t launch_posemb(const echr_batch* b, cudaStream_t st) {
   if (b->n_events == 0) return cudaSuccess;
-  cudaError_t e = upload_pos_div();
+  cudaError_t e = init_pos_table();
   if (e != cudaSuccess) return e;
   const int j_chunk = 32;
   dim3 grid(b->n_events, (b->max_n + j_chunk - 1) / j_chunk);

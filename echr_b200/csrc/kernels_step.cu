@@ -323,8 +323,10 @@ attention_v2_kernel(const float* __restrict__ q, const void* __restrict__ proj_v
                     long long ld_bf, unsigned long long* trace, int trace_slot) {
   trace_begin(trace, trace_slot);
   constexpr int NW = THREADS / 32;
+  // shared memory is kept at 22 KB so that a CTA fits next to a resident GEMM CTA (~195 KB) of the
+  // concurrent logit branch of the decode graph
   __shared__ float sc[ATT_MAX_L];
-  __shared__ __align__(16) float red[NW][512];
+  __shared__ __align__(16) float red[NW / 2][512];
   __shared__ __align__(16) float s_alpha[HID];
   const int r = blockIdx.x;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -427,12 +429,28 @@ attention_v2_kernel(const float* __restrict__ q, const void* __restrict__ proj_v
 #pragma unroll
     for (int i = 0; i < 16; ++i) acc[i] = fmaf(wa, ca[i], fmaf(wb, cb[i], acc[i]));
   }
+  // cross-warp sum in two rounds (upper half of the warps hands its partial sums to the lower half)
+  if (warp >= NW / 2) {
 #pragma unroll
-  for (int m = 0; m < 4; ++m)
-    *reinterpret_cast<float4*>(&red[warp][128 * m + 4 * lane]) =
-        make_float4(acc[4 * m], acc[4 * m + 1], acc[4 * m + 2], acc[4 * m + 3]);
+    for (int m = 0; m < 4; ++m)
+      *reinterpret_cast<float4*>(&red[warp - NW / 2][128 * m + 4 * lane]) =
+          make_float4(acc[4 * m], acc[4 * m + 1], acc[4 * m + 2], acc[4 * m + 3]);
+  }
   __syncthreads();
-  const int nw_used = L < NW ? L : NW;  // warps beyond the window hold zeros
+  if (warp < NW / 2) {
+#pragma unroll
+    for (int m = 0; m < 4; ++m) {
+      float4* p = reinterpret_cast<float4*>(&red[warp][128 * m + 4 * lane]);
+      float4 t = make_float4(acc[4 * m], acc[4 * m + 1], acc[4 * m + 2], acc[4 * m + 3]);
+      if (warp + NW / 2 < L) {  // the partner warp owned at least one clip
+        const float4 o = *p;
+        t.x += o.x; t.y += o.y; t.z += o.z; t.w += o.w;
+      }
+      *p = t;
+    }
+  }
+  __syncthreads();
+  const int nw_used = L < NW / 2 ? L : NW / 2;  // warps beyond the window hold zeros
   for (int c = threadIdx.x; c < ECHR_VIDEO_DIM; c += THREADS) {
     float v = 0.f;
     for (int g = 0; g < nw_used; ++g) v += red[g][c];
@@ -490,8 +508,17 @@ cudaError_t launch_attention(const float* q, const void* proj, const void* clip,
       e = launch_pdl(attention_staged_kernel<false, ATT_THREADS>, dim3((unsigned)rows), dim3(ATT_THREADS), stage, st, q, proj, clip,
                      (long long)ld_clip, alpha, row_start, row_len, out_f32, out_hi, out_lo, (long long)ld_bf, max_len, trace, trace_slot);
   } else if (att_v2_rows() > 0 && rows <= att_v2_rows() && max_len > 0 && max_len <= 128) {
-    // latency regime: short windows, at most a couple of CTAs per SM
-    if (clip_bf16)
+    // latency regime: short windows.  256-thread CTAs (16 K registers, 13 KB) also fit next to a resident
+    // CTA of the concurrent logit GEMM, so the launch is one wave even while that GEMM holds 90 SMs.
+    static const int v2_threads = getenv("ECHR_ATT_V2_THREADS") ? atoi(getenv("ECHR_ATT_V2_THREADS")) : 256;
+    if (v2_threads == 256) {
+      if (clip_bf16)
+        e = launch_pdl(attention_v2_kernel<true, 256>, dim3((unsigned)rows), dim3(256), 0, st, q, proj, clip,
+                       (long long)ld_clip, alpha, row_start, row_len, out_f32, out_hi, out_lo, (long long)ld_bf, trace, trace_slot);
+      else
+        e = launch_pdl(attention_v2_kernel<false, 256>, dim3((unsigned)rows), dim3(256), 0, st, q, proj, clip,
+                       (long long)ld_clip, alpha, row_start, row_len, out_f32, out_hi, out_lo, (long long)ld_bf, trace, trace_slot);
+    } else if (clip_bf16)
       e = launch_pdl(attention_v2_kernel<true, ATT_THREADS>, dim3((unsigned)rows), dim3(ATT_THREADS), 0, st, q, proj, clip,
                      (long long)ld_clip, alpha, row_start, row_len, out_f32, out_hi, out_lo, (long long)ld_bf, trace, trace_slot);
     else
