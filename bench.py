@@ -193,13 +193,12 @@ def main():
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)  # > 126 MB L2
     counts = exchange_counts(n_events, dev) if world > 1 else None
 
+    dev_out = (torch.zeros(n_events, opt.CG_seq_length, dtype=torch.int32, device=dev),
+               torch.zeros(n_events, opt.CG_seq_length, dtype=torch.float32, device=dev),
+               torch.zeros(n_events, dtype=torch.float32, device=dev))
+
     def step_device():
-        eng.set_inputs(lay, d_c3d, d_tap, d_lda, beam=beam)
-        eng.encode()
-        if beam > 1:
-            tok, lp, sc = eng.decode_beam(beam)
-        else:
-            tok, lp = eng.decode_greedy()
+        tok, lp, sc = eng.caption_device(lay, d_c3d, d_tap, d_lda, beam=beam, out=dev_out)
         if world > 1:
             tok = gather_tokens(tok, counts=counts)
         return tok

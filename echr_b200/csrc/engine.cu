@@ -463,23 +463,27 @@ extern "C" int echr_batch_create(const echr_model_t* model, const echr_capacity_
     delete b;
     return set_error(ECHR_ERR_CUDA, "echr_batch_create: cudaMalloc(%zu) failed: %s", sizing.off, cudaGetErrorString(e));
   }
-  e = cudaMallocHost(reinterpret_cast<void**>(&b->host_stage),
-                     sizeof(int32_t) * ((size_t)7 * cap->max_events + 2 * cap->max_videos));
+  e = cudaMallocHost(reinterpret_cast<void**>(&b->host_stage_base),
+                     2 * sizeof(int32_t) * ((size_t)7 * cap->max_events + 2 * cap->max_videos));
   if (e == cudaSuccess)
-    e = cudaMallocHost(reinterpret_cast<void**>(&b->host_tap_stage), sizeof(float) * (size_t)cap->max_events * HID);
+    e = cudaMallocHost(reinterpret_cast<void**>(&b->host_tap_base), 2 * sizeof(float) * (size_t)cap->max_events * HID);
+  for (int i = 0; i < 2 && e == cudaSuccess; ++i) e = cudaEventCreateWithFlags(&b->stage_ev[i], cudaEventDisableTiming);
   if (e != cudaSuccess) {
-    if (b->host_stage) cudaFreeHost(b->host_stage);
+    if (b->host_stage_base) cudaFreeHost(b->host_stage_base);
+    if (b->host_tap_base) cudaFreeHost(b->host_tap_base);
     cudaFree(b->arena);
     delete b;
-    return set_error(ECHR_ERR_CUDA, "echr_batch_create: cudaMallocHost failed: %s", cudaGetErrorString(e));
+    return set_error(ECHR_ERR_CUDA, "echr_batch_create: pinned staging allocation failed: %s", cudaGetErrorString(e));
   }
+  b->host_stage = b->host_stage_base;
+  b->host_tap_stage = b->host_tap_base;
   Arena a;
   a.base = reinterpret_cast<char*>(b->arena);
   batch_layout(b, a);
   e = cudaMemset(b->arena, 0, b->arena_bytes);
   if (e != cudaSuccess) {
-    cudaFreeHost(b->host_stage);
-    cudaFreeHost(b->host_tap_stage);
+    cudaFreeHost(b->host_stage_base);
+    cudaFreeHost(b->host_tap_base);
     cudaFree(b->arena);
     delete b;
     return set_error(ECHR_ERR_CUDA, "echr_batch_create: cudaMemset failed: %s", cudaGetErrorString(e));
@@ -498,8 +502,10 @@ extern "C" int echr_batch_destroy(echr_batch_t* b) {
     cudaStreamDestroy(b->cap_stream3);
     for (int i = 0; i < 4; ++i) cudaEventDestroy(b->cap_events[i]);
   }
-  cudaFreeHost(b->host_stage);
-  cudaFreeHost(b->host_tap_stage);
+  cudaFreeHost(b->host_stage_base);
+  cudaFreeHost(b->host_tap_base);
+  for (int i = 0; i < 2; ++i)
+    if (b->stage_ev[i]) cudaEventDestroy(b->stage_ev[i]);
   cudaFree(b->arena);
   delete b;
   return ECHR_OK;
@@ -519,9 +525,12 @@ static int stage_desc(echr_batch_t* b, const echr_batch_desc_t* d, bool check_cl
     ECHR_REQUIRE(off[v + 1] > off[v], "echr_batch_set_inputs: video %d has no clips", v);
   const int n_clips = off[d->n_videos];
   ECHR_REQUIRE(!check_clips || n_clips <= b->cap.max_clips, "echr_batch_set_inputs: %d clips exceed capacity %lld", n_clips, (long long)b->cap.max_clips);
-  // the pinned staging buffer may still be in flight from the previous call on this stream
-  ECHR_CUDA(cudaStreamSynchronize(st));
+  // switch to the other half of the pinned staging areas; the copies that read it were enqueued two calls ago
+  b->stage_idx ^= 1;
+  ECHR_CUDA(cudaEventSynchronize(b->stage_ev[b->stage_idx]));
   const int64_t E = b->cap.max_events;
+  b->host_stage = b->host_stage_base + (size_t)b->stage_idx * ((size_t)7 * E + 2 * b->cap.max_videos);
+  b->host_tap_stage = b->host_tap_base + (size_t)b->stage_idx * (size_t)E * HID;
   int32_t* hs = b->host_stage;
   int32_t* vid_first = hs + 7 * E;
   int32_t* vid_n = vid_first + b->cap.max_videos;
@@ -569,6 +578,7 @@ static int stage_desc(echr_batch_t* b, const echr_batch_desc_t* d, bool check_cl
   b->encoded = false;
   ECHR_CUDA(cudaMemcpyAsync(b->ev_video, hs, sizeof(int32_t) * ((size_t)7 * E + 2 * b->cap.max_videos),
                             cudaMemcpyHostToDevice, st));
+  ECHR_CUDA(cudaEventRecord(b->stage_ev[b->stage_idx], st));
   return ECHR_OK;
 }
 
@@ -587,8 +597,11 @@ extern "C" int echr_batch_set_inputs(echr_batch_t* b, const echr_batch_desc_t* d
     for (int i = 0; i < d->n_events; ++i)
       memcpy(b->host_tap_stage + (size_t)i * HID, tap + (size_t)hs[3 * E + i] * HID, sizeof(float) * HID);
     if (d->n_events > 0)
+    {
       ECHR_CUDA(cudaMemcpyAsync(b->tap, b->host_tap_stage, sizeof(float) * (size_t)d->n_events * HID,
                                 cudaMemcpyHostToDevice, st));
+      ECHR_CUDA(cudaEventRecord(b->stage_ev[b->stage_idx], st));
+    }
   } else {
     ECHR_CUDA(launch_gather_tap(b, tap, st));
   }
@@ -1072,6 +1085,18 @@ extern "C" int echr_caption_host(echr_batch_t* b, const echr_batch_desc_t* desc,
   ECHR_TRY(copy_results(b, host_tokens, host_logp, beam > 1 ? host_score : nullptr, cudaMemcpyDeviceToHost, st));
   ECHR_CUDA(cudaStreamSynchronize(st));
   return ECHR_OK;
+}
+
+extern "C" int echr_caption_device(echr_batch_t* b, const echr_batch_desc_t* desc, const float* c3d, const float* tap,
+                                   const float* lda, int beam, int32_t* tokens, float* logp, float* score,
+                                   void* stream) {
+  ECHR_REQUIRE(b && tokens && logp, "echr_caption_device: null argument");
+  ECHR_REQUIRE(beam >= 1 && beam <= 4, "echr_caption_device: beam must be in 1..4");
+  cudaStream_t st = (cudaStream_t)stream;
+  ECHR_TRY(echr_batch_set_inputs(b, desc, c3d, tap, lda, 0, st));
+  ECHR_TRY(echr_encode(b, st));
+  ECHR_TRY(run_decode(b, beam, beam > 1 ? MODE_BEAM : MODE_GREEDY, st));
+  return copy_results(b, tokens, logp, beam > 1 ? score : nullptr, cudaMemcpyDeviceToDevice, st);
 }
 
 // Average duration (ms) of each kernel of one decode step, measured with CUDA events on `stream`

@@ -69,6 +69,12 @@ struct echr_batch {
   // inputs (copies)
   float *c3d, *tap, *lda;  // [clips,500]; tap_feats[ind] per event [events,512]; [videos,100]
   float* host_tap_stage;   // pinned [max_events,512]: host-side gather of the proposal states
+  // both pinned staging areas are double-buffered: a call fills the half the previous call did not use and
+  // only waits (stage_ev) for the copy that read that half two calls ago
+  float* host_tap_base;
+  int32_t* host_stage_base;
+  cudaEvent_t stage_ev[2];
+  int stage_idx;
   // per-event int arrays on device: video, first clip (global), length, ind (global), pair row
   // offset, first event of the video, events in the video
   int32_t *ev_video, *ev_start, *ev_len, *ev_ind, *ev_pair_off, *ev_first, *ev_n;

@@ -227,6 +227,25 @@ class Engine(object):
                                             h2.data_ptr(), c2.data_ptr(), _stream()), "echr_decode_step")
         return lp, h2, c2
 
+    # ------------------------------------------------------------------ whole call, device buffers
+    def caption_device(self, layout, c3d, tap, lda, beam=1, out=None):
+        """set_inputs + encode + decode through one C-ABI call; c3d/tap/lda fp32 tensors on this device.
+        Returns device tensors (tokens int32 [n,S], logp [n,S], score [n]); nothing is synchronised."""
+        self.reserve(layout.n_videos, layout.n_clips, layout.n_events, layout.n_pairs, beam)
+        self.layout = layout
+        n, S = layout.n_events, self.seq_length
+        if out is None:
+            out = (torch.empty(n, S, dtype=torch.int32, device=self.device),
+                   torch.empty(n, S, dtype=torch.float32, device=self.device),
+                   torch.empty(n, dtype=torch.float32, device=self.device))
+        tokens, logp, score = out
+        d = layout.desc()
+        with torch.cuda.device(self.device):
+            check(self.lib.echr_caption_device(self._batch, ctypes.byref(d), c3d.data_ptr(), tap.data_ptr(),
+                                               lda.data_ptr(), int(beam), tokens.data_ptr(), logp.data_ptr(),
+                                               score.data_ptr(), _stream()), "echr_caption_device")
+        return tokens, logp, score
+
     # ------------------------------------------------------------------ host-buffer path (e2e)
     def caption_host(self, layout, c3d, tap, lda, beam=1, out=None):
         """Everything through one C-ABI call with HOST buffers: H2D, encode, decode, D2H, sync.

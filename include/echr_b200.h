@@ -197,6 +197,14 @@ ECHR_API int echr_caption_host(echr_batch_t* batch, const echr_batch_desc_t* des
                       const float* host_tap, const float* host_lda, int beam, int32_t* host_tokens,
                       float* host_logp, float* host_score, void* stream);
 
+/* The same call with DEVICE buffers and nothing synchronised: inputs are copied into the workspace
+ * (they may be reused as soon as the call returns in stream order), results are written to the device
+ * arrays tokens/logp [n_events, seq_length] and score [n_events] (may be NULL).  One entry into the
+ * library per batch: the host-side cost of a step is one description pass and two graph launches. */
+ECHR_API int echr_caption_device(echr_batch_t* batch, const echr_batch_desc_t* desc, const float* c3d,
+                        const float* tap, const float* lda, int beam, int32_t* tokens, float* logp,
+                        float* score, void* stream);
+
 /* Measurement aid for bench.py's roofline: average duration in ms of each kernel of one decode step
  * (host_ms[5] = h2att GEMM, fused attention, LSTM gate GEMM, logit GEMM, finalize), from CUDA
  * events on `stream` around `iters` back-to-back launches.  Needs a decoded batch; synchronises. */

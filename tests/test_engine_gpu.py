@@ -154,6 +154,15 @@ def test_caption_host_equals_device_path():
         assert torch.equal(lp[r0:r0 + n, : seq.shape[1]], logp.cpu())
         r0 += n
     assert m.engine.launch_count() > 0
+    # the one-call device-buffer entry (echr_caption_device), greedy and beam, replayed twice (graph cache)
+    for _ in range(2):
+        tok_d, lp_d, _ = m.engine.caption_device(lay, c3d.to(DEV), tap.to(DEV), lda.to(DEV), beam=1)
+        assert torch.equal(tok_d.cpu(), tok) and torch.equal(lp_d.cpu(), lp)
+    tb, lb, sb = m.engine.caption_device(lay, c3d.to(DEV), tap.to(DEV), lda.to(DEV), beam=3)
+    m.engine.set_inputs(lay, c3d.to(DEV), tap.to(DEV), lda.to(DEV), beam=3)
+    m.engine.encode()
+    tb2, lb2, sb2 = m.engine.decode_beam(3)
+    assert torch.equal(tb, tb2) and torch.equal(lb, lb2) and torch.equal(sb, sb2)
 
 
 # ----------------------------------------------------------------------------- sub-module surfaces
