@@ -78,6 +78,8 @@ struct GemmParams {
   GemmProblem prob[GEMM_MAX_GROUPS];
   unsigned long long* trace;  // optional timeline trace (see ptx.cuh)
   int trace_slot;
+  int pdl_late;  // 1: release the programmatic dependents when the accumulator is ready (their launch and
+                 // prologue overlap this kernel's epilogue) instead of right after this kernel's prologue
   unsigned long long* trace_detail;  // optional [slot][4]: sum over CTAs of (first stage landed, accumulator
                                      // ready, CTA end) - CTA start in ns, and the CTA count
 };
@@ -203,7 +205,7 @@ gemm_tc_kernel(const __grid_constant__ GemmParams P) {
   const uint32_t tmem_base = *tmem_ptr_generic;
   // everything above touched only constants (weights, descriptors): let the next kernel start its
   // own prologue, then wait for the previous kernel's results
-  pdl_trigger();
+  if (!P.pdl_late) pdl_trigger();
   pdl_wait();
 
   if (warp == 0) {
@@ -345,6 +347,7 @@ gemm_tc_kernel(const __grid_constant__ GemmParams P) {
 
     mbar_wait(tmem_full_bar, 0);
     tc_fence_after_sync();
+    if (P.pdl_late && threadIdx.x == 128) pdl_trigger();
     if (P.trace_detail != nullptr && threadIdx.x == 128)
       atomicAdd(P.trace_detail + 4 * P.trace_slot + 1, global_timer_ns() - *t_start_smem);
 

@@ -43,11 +43,14 @@ inline int set_error(int code, const char* fmt, ...) {
 // Programmatic dependent launch: the kernel may start (prologue only) while its stream predecessor
 // is still running; it calls pdl_wait() before touching anything the predecessor writes.
 // ECHR_NO_PDL=1 in the environment falls back to plain stream order.
-// ECHR_PDL_MASK selects which step kernels use it (bit 0 h2att, 1 attention, 2 gates, 3 logits,
-// 4 finalize); kernels with large shared memory that become resident early can starve a
-// concurrent graph branch: measured on cfg2 every non-zero mask was slower than plain stream order
-// inside the fork/join decode graph (profiles/r01_pdl_sweep.md), so the default is off.
-enum { PDL_H2ATT = 1, PDL_ATT = 2, PDL_GATES = 4, PDL_LOGIT = 8, PDL_FINALIZE = 16, PDL_DEFAULT_MASK = 0 };
+// ECHR_PDL_MASK selects which step kernels are launched as programmatic dependents (bit 0 h2att, 1 attention,
+// 2 gates, 3 logits, 4 finalize).  What matters is WHEN the primary releases them: released right after the
+// primary's prologue (ECHR_PDL_LATE=0) the dependents' CTAs sit on SMs (and ~200 KB of shared memory each) for
+// the whole primary and starve the concurrent graph branch — every mask is slower than plain stream order
+// (cfg2: 186k vs 232k events/s).  Released when the primary's accumulators are ready (the default), only the
+// launch latency and the prologue of the dependent overlap the primary's epilogue: 232k -> 255k events/s with
+// mask 30; h2att stays a plain launch (its early CTAs take SMs from the gate GEMM's tail).
+enum { PDL_H2ATT = 1, PDL_ATT = 2, PDL_GATES = 4, PDL_LOGIT = 8, PDL_FINALIZE = 16, PDL_DEFAULT_MASK = 30 };
 inline int pdl_mask() {
   static int mask = -1;
   if (mask < 0) {
@@ -62,9 +65,13 @@ inline bool& pdl_next() {  // whether the next launch_pdl() on this thread may u
   static thread_local bool on = false;
   return on;
 }
+inline bool& pdl_regime() {  // set by the decode enqueue: programmatic launches pay off in the latency regime only
+  static thread_local bool on = true;
+  return on;
+}
 struct PdlScope {
   bool prev;
-  explicit PdlScope(int bit) : prev(pdl_next()) { pdl_next() = (pdl_mask() & bit) != 0; }
+  explicit PdlScope(int bit) : prev(pdl_next()) { pdl_next() = pdl_regime() && (pdl_mask() & bit) != 0; }
   ~PdlScope() { pdl_next() = prev; }
 };
 inline bool pdl_enabled() { return pdl_next(); }
