@@ -969,26 +969,37 @@ static int enqueue_decode(echr_batch* b, int beam, int mode, cudaStream_t st, cu
     ECHR_CUDA(cudaMemsetAsync(b->logp_dev, 0, sizeof(float) * (size_t)b->n_events * S, st));
   }
   if (mode == MODE_GREEDY && side != nullptr) {
-    // Greedy: the next step's attention (h2att GEMM + fused attention) depends only on this step's
-    // h1, not on the token, so it runs on a forked branch next to the vocabulary projection:
-    //   main:  gates(t) -> logits(t) -> finalize(t) -> [join] gates(t+1) ...
-    //   side:           \-> h2att(t+1) -> attention(t+1) -/
-    // The branches touch disjoint columns of the activation matrix.
+    // Greedy: the next step's attention (h2att GEMM + fused attention) depends only on this step's h1, not
+    // on the token, so it runs next to the vocabulary projection.  The recurrent chain
+    //   gates(t) -> h2att(t+1) -> attention(t+1) -> gates(t+1)
+    // is the critical one and stays on one stream, so each of its kernels is a programmatic dependent of the
+    // previous one (launch latency and prologue hidden behind the predecessor's epilogue); the token chain
+    //   gates(t) -> logits(t) -> finalize(t) -> gates(t+1)
+    // forks off and joins by events.  The branches touch disjoint columns of the activation matrix.
+    static const bool crit_main = !(getenv("ECHR_CRIT_MAIN") && getenv("ECHR_CRIT_MAIN")[0] == '0');
     ECHR_TRY(enqueue_step(b, rows, 0, topk, nullptr, 0, st, PART_H2ATT | PART_ATT));
     for (int t = 0; t < S; ++t) {
       ECHR_TRY(enqueue_step(b, rows, t, topk, nullptr, 0, st, PART_GATES));
-      if (t + 1 < S) {
-        ECHR_CUDA(cudaEventRecord(b->cap_events[0], st));
-        ECHR_CUDA(cudaStreamWaitEvent(side, b->cap_events[0], 0));
-        ECHR_TRY(enqueue_step(b, rows, t + 1, topk, nullptr, 0, side, PART_H2ATT | PART_ATT));
-        ECHR_CUDA(cudaEventRecord(b->cap_events[1], side));
+      ECHR_CUDA(cudaEventRecord(b->cap_events[0], st));
+      ECHR_CUDA(cudaStreamWaitEvent(side, b->cap_events[0], 0));
+      cudaStream_t tok_st = crit_main ? side : st;  // token chain
+      cudaStream_t att_st = crit_main ? st : side;  // recurrent attention chain
+      if (!crit_main && t + 1 < S) {
+        ECHR_TRY(enqueue_step(b, rows, t + 1, topk, nullptr, 0, att_st, PART_H2ATT | PART_ATT));
+        ECHR_CUDA(cudaEventRecord(b->cap_events[1], att_st));
       }
-      ECHR_TRY(enqueue_step(b, rows, t, topk, nullptr, 0, st, PART_LOGIT));
+      ECHR_TRY(enqueue_step(b, rows, t, topk, nullptr, 0, tok_st, PART_LOGIT));
       {
         PdlScope pdl(PDL_FINALIZE);
-        ECHR_CUDA(launch_finalize_greedy(b, t, b->tokens_dev, b->logp_dev, st));
+        ECHR_CUDA(launch_finalize_greedy(b, t, b->tokens_dev, b->logp_dev, tok_st));
       }
-      if (t + 1 < S) ECHR_CUDA(cudaStreamWaitEvent(st, b->cap_events[1], 0));
+      if (crit_main) {
+        ECHR_CUDA(cudaEventRecord(b->cap_events[1], tok_st));
+        if (t + 1 < S) ECHR_TRY(enqueue_step(b, rows, t + 1, topk, nullptr, 0, att_st, PART_H2ATT | PART_ATT));
+        ECHR_CUDA(cudaStreamWaitEvent(st, b->cap_events[1], 0));
+      } else if (t + 1 < S) {
+        ECHR_CUDA(cudaStreamWaitEvent(st, b->cap_events[1], 0));
+      }
     }
     return ECHR_OK;
   }

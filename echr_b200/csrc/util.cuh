@@ -48,9 +48,10 @@ inline int set_error(int code, const char* fmt, ...) {
 // primary's prologue (ECHR_PDL_LATE=0) the dependents' CTAs sit on SMs (and ~200 KB of shared memory each) for
 // the whole primary and starve the concurrent graph branch — every mask is slower than plain stream order
 // (cfg2: 186k vs 232k events/s).  Released when the primary's accumulators are ready (the default), only the
-// launch latency and the prologue of the dependent overlap the primary's epilogue: 232k -> 255k events/s with
-// mask 30; h2att stays a plain launch (its early CTAs take SMs from the gate GEMM's tail).
-enum { PDL_H2ATT = 1, PDL_ATT = 2, PDL_GATES = 4, PDL_LOGIT = 8, PDL_FINALIZE = 16, PDL_DEFAULT_MASK = 30 };
+// launch latency and the prologue of the dependent overlap the primary's epilogue: 232k -> 254k events/s.
+// Default mask 23 = the recurrent chain gates -> h2att -> attention -> gates (one stream) plus finalize; the
+// logit GEMM follows an event from another stream, where the attribute has no primary to hang on.
+enum { PDL_H2ATT = 1, PDL_ATT = 2, PDL_GATES = 4, PDL_LOGIT = 8, PDL_FINALIZE = 16, PDL_DEFAULT_MASK = 23 };
 inline int pdl_mask() {
   static int mask = -1;
   if (mask < 0) {
