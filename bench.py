@@ -130,7 +130,7 @@ def main_reference(args, rank, world):
     vids, w = synth.make_workload(args.workload, n_videos=args.videos)
     if args.beam is not None:
         w["beam"] = args.beam
-    sample = args.cpu_sample or {"cfg1": 1, "cfg2": 16, "cfg3": 1, "cfg4": 1, "cfg5": 16}[args.workload]
+    sample = args.cpu_sample or {"cfg1": 1, "cfg2": 64, "cfg3": 1, "cfg4": 1, "cfg5": 64}[args.workload]
     sub = vids[:sample]
     n_ev = sum(v.n_events for v in sub)
     value, sec = cpu_reference_run(sub, sd, w["beam"], reps=max(1, args.steps), warm=max(0, args.warmup))
@@ -269,8 +269,18 @@ def main():
     dom = max(("lstm_gates", "logit"), key=lambda k: kt[k])
     ach = flops[dom] / (kt[dom] * 1e-3) / 1e12
     peak_tf = pk.get("bf16_tflops_sustained", pk["bf16_tflops"])
+    # DRAM bytes per launch of that kernel from the committed `ncu --set full` capture of this command
+    # (profiles/r01_traffic.json; cold-cache replays, so the weights count once per launch)
+    traffic = None
+    try:
+        tj = json.load(open(os.path.join(ROOT, "profiles", "r01_traffic.json")))
+        key = "%s/%s/beam%d" % (args.workload if args.videos is None else "%s-%d" % (args.workload, args.videos),
+                                args.precision, beam)
+        traffic = tj.get(key, {}).get(dom)
+    except Exception:
+        traffic = None
     roofline = {"bound": "tensor", "kernel": "gemm_tc_kernel<%s>" % dom, "achieved": ach, "peak": peak_tf,
-                "unit": "TFLOP/s", "frac": ach / peak_tf, "traffic": None, "peak_source": pk_kind + " (sustained)",
+                "unit": "TFLOP/s", "frac": ach / peak_tf, "traffic": traffic, "peak_source": pk_kind + " (sustained)",
                 "ms_per_launch": kt[dom], "step_kernel_ms": kt,
                 "per_kernel_tflops": {k: flops[k] / (kt[k] * 1e-3) / 1e12 for k in flops},
                 "note": "algorithmic FLOPs 2*M*N*K of one product; the %s mode issues %d tcgen05 products per k-step"
@@ -298,13 +308,15 @@ def main():
             "gpu_launches": int(launches),
             "roofline": roofline}
     if not args.no_cpu_baseline and world >= 1:
-        sample = args.cpu_sample or {"cfg1": 1, "cfg2": 8, "cfg3": 1, "cfg4": 1, "cfg5": 8}[args.workload]
+        # bounded sample sized for ~10-20 s of CPU work: the whole cfg2 workload (64 videos) takes ~2 s per pass
+        sample = args.cpu_sample or {"cfg1": 1, "cfg2": 64, "cfg3": 1, "cfg4": 1, "cfg5": 64}[args.workload]
+        reps = 5 if args.workload in ("cfg2", "cfg5") else 3
         sub = [synth.make_video(i, T=w["T"], n_events=w0["n_events"], style=w["style"]) for i in range(sample)]
-        v, sec = cpu_reference_run(sub, sd_full, beam, reps=3, warm=1)
+        v, sec = cpu_reference_run(sub, sd_full, beam, reps=reps, warm=1)
         line["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": os.cpu_count() or 1, "kind": "port",
                                 "sample": "first %d videos (%d events) of the workload, one video per call, "
-                                          "median of 3 passes after 1 warm-up (%.2f s per pass)"
-                                          % (sample, sum(x.n_events for x in sub), sec)}
+                                          "median of %d passes after 1 warm-up (%.2f s per pass)"
+                                          % (sample, sum(x.n_events for x in sub), reps, sec)}
     print(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()
