@@ -335,6 +335,7 @@ attention_v2_kernel(const float* __restrict__ q, const void* __restrict__ proj_v
   pdl_wait();
   const int s0 = row_start[r];
   const int L = row_len[r];
+  __syncthreads();  // s_alpha is read across warps in pass 1
   // lane owns hidden units [128*m + 4*lane, +4), m = 0..3, and clip columns float4 #(lane + 32*m)
   float qv[16];
 #pragma unroll

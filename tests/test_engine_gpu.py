@@ -136,6 +136,28 @@ def test_beam_matches_oracle_spec(beam):
         assert np.abs(picked.numpy() - lp.cpu()[:, : tf.shape[1]].numpy()).max() < 1e-3
 
 
+def test_replay_is_bitwise_deterministic():
+    """Race hunt (tools/stress_determinism.py in small): the same batch replayed through the cached graphs
+    must give bit-identical tokens and log-probs — every kernel has a fixed summation order."""
+    from echr_b200.engine import BatchLayout
+    m = model("bf16w", "bf16w")
+    for n_videos, iters in ((76, 40), (300, 6)):
+        vids, _ = synth.make_workload("cfg2", n_videos=n_videos)
+        lay = BatchLayout([v.c3d_feats.shape[0] for v in vids], [v.ind_select_list for v in vids],
+                          [v.soi_select_list for v in vids])
+        c3d = torch.cat([v.c3d_feats for v in vids]).to(DEV)
+        tap = torch.cat([v.tap_feats for v in vids]).to(DEV)
+        lda = torch.stack([v.lda_feats for v in vids]).to(DEV)
+        for beam in (1, 3):
+            ref = None
+            for _ in range(iters):
+                tok, lp, _sc = m.engine.caption_device(lay, c3d, tap, lda, beam=beam)
+                tok, lp = tok.clone(), lp.clone()
+                if ref is None:
+                    ref = (tok, lp)
+                assert torch.equal(tok, ref[0]) and torch.equal(lp, ref[1])
+
+
 # ----------------------------------------------------------------------------- host-buffer path
 def test_caption_host_equals_device_path():
     from echr_b200.engine import BatchLayout
