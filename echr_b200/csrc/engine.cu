@@ -976,7 +976,9 @@ static int enqueue_decode(echr_batch* b, int beam, int mode, cudaStream_t st, cu
     // previous one (launch latency and prologue hidden behind the predecessor's epilogue); the token chain
     //   gates(t) -> logits(t) -> finalize(t) -> gates(t+1)
     // forks off and joins by events.  The branches touch disjoint columns of the activation matrix.
-    static const bool crit_main = !(getenv("ECHR_CRIT_MAIN") && getenv("ECHR_CRIT_MAIN")[0] == '0');
+    // (throughput regime: persistent GEMMs; measured better with the attention chain on the forked stream)
+    static const bool crit_main_env = !(getenv("ECHR_CRIT_MAIN") && getenv("ECHR_CRIT_MAIN")[0] == '0');
+    const bool crit_main = crit_main_env && rows < gemm2_min_rows();
     ECHR_TRY(enqueue_step(b, rows, 0, topk, nullptr, 0, st, PART_H2ATT | PART_ATT));
     for (int t = 0; t < S; ++t) {
       ECHR_TRY(enqueue_step(b, rows, t, topk, nullptr, 0, st, PART_GATES));

@@ -187,6 +187,38 @@ gemm_tc2_kernel(const __grid_constant__ GemmParams P, int groups, int total_tile
       const int row = tl.m_tile * GEMM_BLOCK_M + q * 32 + lane;
       const bool row_ok = row < pb.M;
       float* sb = sbias + buf * BN;
+      // LSTM epilogue operands that do not depend on the accumulator (see the chunk pipeline below)
+      float bbA[EPI == EPI_LSTM ? 32 : 1], bbB[EPI == EPI_LSTM ? 32 : 1], cpA[EPI == EPI_LSTM ? 8 : 1], cpB[EPI == EPI_LSTM ? 8 : 1];
+      const bool lstm_rb = EPI == EPI_LSTM && (pb.row_bias != nullptr || pb.tok_table != nullptr);
+      const long long rowc = row_ok ? row : (pb.M - 1);  // clamped: the loads below are unconditional
+      const float* rb_row = nullptr;
+      const float* tk_row = nullptr;
+      const float* c_row = nullptr;
+      if constexpr (EPI == EPI_LSTM) {
+        if (pb.row_bias != nullptr) rb_row = pb.row_bias + rowc * pb.ld_row_bias + col0 + hc0;
+        if (pb.tok_table != nullptr)
+          tk_row = pb.tok_table + static_cast<long long>(__ldg(pb.row_tok + rowc)) * pb.ld_tok_table + col0 + hc0;
+        c_row = pb.c_in + rowc * pb.hidden + ((col0 + hc0) >> 2);
+      }
+      auto lstm_load = [&](int c, float (&bb)[32], float (&cp)[8]) {
+        if constexpr (EPI == EPI_LSTM) {
+          ldg_nc_f32x8(c_row + 8 * c, cp);
+#pragma unroll
+          for (int i = 0; i < 4; ++i) {
+            float r8[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+            if (rb_row != nullptr) ldg_nc_f32x8(rb_row + 32 * c + 8 * i, r8);
+            if (tk_row != nullptr) {
+              float t8[8];
+              ldg_nc_f32x8(tk_row + 32 * c + 8 * i, t8);
+#pragma unroll
+              for (int k = 0; k < 8; ++k) r8[k] += t8[k];
+            }
+#pragma unroll
+            for (int k = 0; k < 8; ++k) bb[8 * i + k] = r8[k];
+          }
+        }
+      };
+      if constexpr (EPI == EPI_LSTM) lstm_load(0, bbA, cpA);
       // bias tile -> smem.  The buffer was last read two tiles ago; every epilogue thread has passed
       // the named barrier of the previous tile since then.
       sb[et] = (pb.bias != nullptr && col0 + et < pb.N) ? __ldg(pb.bias + col0 + et) : 0.f;
@@ -238,50 +270,15 @@ gemm_tc2_kernel(const __grid_constant__ GemmParams P, int groups, int total_tile
           }
         }
       } else if constexpr (EPI == EPI_LSTM) {
-        const int H = pb.hidden;
-        const bool has_rbias = pb.row_bias != nullptr || pb.tok_table != nullptr;
-        const float* tok_row = nullptr;
-        if (pb.tok_table != nullptr && row_ok)
-          tok_row = pb.tok_table + static_cast<long long>(__ldg(pb.row_tok + row)) * pb.ld_tok_table + col0;
-#pragma unroll 1
-        for (int c = 0; c < NCH; ++c) {
+        // Software-pipelined over the four 32-column chunks of this thread: the gathers of chunk c+1 (token
+        // gate table row, per-row bias, c_prev: 18 x 16 B per thread, scattered 8 KB rows in HBM / L2) are in
+        // flight while chunk c is read from TMEM and pushed through the cell update.  Chunk 0 was requested
+        // before the wait on the accumulator (lstm_prefetch above).
+        static_assert(NCH == 4, "the chunk pipeline below is unrolled by hand");
+        auto lstm_chunk = [&](int c, float (&bb)[32], float (&cp)[8], float (&nbb)[32], float (&ncp)[8]) {
+          if (c + 1 < NCH) lstm_load(c + 1, nbb, ncp);
           const int tc = hc0 + c * 32;
           const int j0 = (col0 + tc) >> 2;  // first hidden unit of this chunk (8 units)
-          float cprev[8];
-          float bb[32];
-          if (row_ok) {
-            const float4* cp = reinterpret_cast<const float4*>(pb.c_in + static_cast<long long>(row) * H + j0);
-            const float4 c0 = __ldg(cp), c1 = __ldg(cp + 1);
-            cprev[0] = c0.x; cprev[1] = c0.y; cprev[2] = c0.z; cprev[3] = c0.w;
-            cprev[4] = c1.x; cprev[5] = c1.y; cprev[6] = c1.z; cprev[7] = c1.w;
-            if (has_rbias) {
-#pragma unroll
-              for (int i = 0; i < 32; ++i) bb[i] = 0.f;
-              if (pb.row_bias != nullptr) {
-                const float4* rp = reinterpret_cast<const float4*>(
-                    pb.row_bias + static_cast<long long>(row) * pb.ld_row_bias + col0 + tc);
-#pragma unroll
-                for (int i = 0; i < 8; ++i) {
-                  const float4 r4 = __ldg(rp + i);
-                  bb[4 * i] = r4.x; bb[4 * i + 1] = r4.y; bb[4 * i + 2] = r4.z; bb[4 * i + 3] = r4.w;
-                }
-              }
-              if (tok_row != nullptr) {
-                const float4* tp = reinterpret_cast<const float4*>(tok_row + tc);
-#pragma unroll
-                for (int i = 0; i < 8; ++i) {
-                  const float4 r4 = __ldg(tp + i);
-                  bb[4 * i] += r4.x; bb[4 * i + 1] += r4.y; bb[4 * i + 2] += r4.z; bb[4 * i + 3] += r4.w;
-                }
-              }
-            } else {
-#pragma unroll
-              for (int i = 0; i < 32; i += 4) {
-                const float4 b4 = *reinterpret_cast<const float4*>(sb + tc + i);
-                bb[i] = b4.x; bb[i + 1] = b4.y; bb[i + 2] = b4.z; bb[i + 3] = b4.w;
-              }
-            }
-          }
           float v[32];
           tmem_ld_32x32(t_row + c * 32, v);
           tmem_ld_wait();
@@ -291,24 +288,31 @@ gemm_tc2_kernel(const __grid_constant__ GemmParams P, int groups, int total_tile
             __align__(16) __nv_bfloat16 hl[8];
 #pragma unroll
             for (int u = 0; u < 8; ++u) {
-              const float gi = sigmoid_fast(v[4 * u + 0] + bb[4 * u + 0]);
-              const float gf = sigmoid_fast(v[4 * u + 1] + bb[4 * u + 1]);
-              const float gg = tanh_fast_acc(v[4 * u + 2] + bb[4 * u + 2]);
-              const float go = sigmoid_fast(v[4 * u + 3] + bb[4 * u + 3]);
-              const float cc = gf * cprev[u] + gi * gg;
+              float b0 = bb[4 * u], b1 = bb[4 * u + 1], b2 = bb[4 * u + 2], b3 = bb[4 * u + 3];
+              if (!lstm_rb) {
+                const float4 b4 = *reinterpret_cast<const float4*>(sb + tc + 4 * u);
+                b0 = b4.x; b1 = b4.y; b2 = b4.z; b3 = b4.w;
+              }
+              const float gi = sigmoid_fast(v[4 * u + 0] + b0);
+              const float gf = sigmoid_fast(v[4 * u + 1] + b1);
+              const float gg = tanh_fast_acc(v[4 * u + 2] + b2);
+              const float go = sigmoid_fast(v[4 * u + 3] + b3);
+              const float cc = gf * cp[u] + gi * gg;
               cn[u] = cc;
               split_bf16(go * tanh_fast_acc(cc), hh[u], hl[u]);
             }
-            float4* co = reinterpret_cast<float4*>(pb.c_out + static_cast<long long>(row) * H + j0);
-            co[0] = make_float4(cn[0], cn[1], cn[2], cn[3]);
-            co[1] = make_float4(cn[4], cn[5], cn[6], cn[7]);
+            stg_f32x8(pb.c_out + static_cast<long long>(row) * pb.hidden + j0, cn);
             *reinterpret_cast<uint4*>(pb.out_hi + static_cast<long long>(row) * pb.ld_bf + j0) =
                 *reinterpret_cast<const uint4*>(hh);
             if (pb.out_lo != nullptr)
               *reinterpret_cast<uint4*>(pb.out_lo + static_cast<long long>(row) * pb.ld_bf + j0) =
                   *reinterpret_cast<const uint4*>(hl);
           }
-        }
+        };
+        lstm_chunk(0, bbA, cpA, bbB, cpB);
+        lstm_chunk(1, bbB, cpB, bbA, cpA);
+        lstm_chunk(2, bbA, cpA, bbB, cpB);
+        lstm_chunk(3, bbB, cpB, bbA, cpA);
       } else {  // EPI_LOGITS: one record per (row, 64-column group); this thread owns two groups
         const int n_groups = ((pb.N + BN - 1) / BN) * (BN / LOGIT_GROUP);
 #pragma unroll 1

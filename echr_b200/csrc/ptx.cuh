@@ -225,6 +225,21 @@ __device__ __forceinline__ void tmem_ld_wait() {
   asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
 }
 
+// ---------------------------------------------------------------- 256-bit global accesses (sm_100)
+// One instruction per 32-byte sector.  The epilogues read "one row per thread" operands (bias / table rows,
+// cell state), so a warp-wide access touches 32 different lines whatever its width: halving the number of
+// instructions halves the L1 wavefronts.  Addresses must be 32-byte aligned.
+__device__ __forceinline__ void ldg_nc_f32x8(const float* p, float* v) {
+  asm volatile("ld.global.nc.v8.f32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];"
+               : "=f"(v[0]), "=f"(v[1]), "=f"(v[2]), "=f"(v[3]), "=f"(v[4]), "=f"(v[5]), "=f"(v[6]), "=f"(v[7])
+               : "l"(p));
+}
+__device__ __forceinline__ void stg_f32x8(float* p, const float* v) {
+  asm volatile("st.global.v8.f32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};" ::"l"(p), "f"(v[0]), "f"(v[1]), "f"(v[2]),
+               "f"(v[3]), "f"(v[4]), "f"(v[5]), "f"(v[6]), "f"(v[7])
+               : "memory");
+}
+
 // ---------------------------------------------------------------- misc math helpers
 // Split an fp32 value into a bf16 "hi" (round-to-nearest) and the bf16 of the remainder; hi+lo
 // carries 16 mantissa bits, which is what the two-term tensor-core products consume.
