@@ -165,6 +165,8 @@ def main():
     dev = torch.device("cuda", local)
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        # stdout carries exactly one JSON line: keep NCCL's banner (NCCL_DEBUG=VERSION/INFO prints to stdout) out of it
+        os.environ["NCCL_DEBUG"] = os.environ.get("ECHR_NCCL_DEBUG", "WARN")
         dist.init_process_group("nccl", device_id=dev)
 
     opt = echr_opt()

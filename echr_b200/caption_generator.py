@@ -224,13 +224,22 @@ class CaptionGenerator(nn.Module):
         return self._engine
 
     # -- batched API (additive)
-    def _stage(self, videos, beam):
+    def _gather(self, videos):
+        """Batch layout + the three feature tensors of a list of videos, on the engine's device."""
         eng = self.engine
         layout = BatchLayout([v[1].shape[0] for v in videos], [v[3] for v in videos], [v[4] for v in videos])
         f32 = lambda t: t.to(device=eng.device, dtype=torch.float32)
-        c3d = torch.cat([f32(v[1]) for v in videos], 0).contiguous()
-        tap = torch.cat([f32(v[0]) for v in videos], 0).contiguous()
-        lda = torch.stack([f32(v[2]).reshape(-1) for v in videos], 0).contiguous()
+        if len(videos) == 1:  # the reference's call shape: no concatenation copies
+            v = videos[0]
+            c3d, tap, lda = f32(v[1]).contiguous(), f32(v[0]).contiguous(), f32(v[2]).reshape(1, -1).contiguous()
+        else:
+            c3d = torch.cat([f32(v[1]) for v in videos], 0).contiguous()
+            tap = torch.cat([f32(v[0]) for v in videos], 0).contiguous()
+            lda = torch.stack([f32(v[2]).reshape(-1) for v in videos], 0).contiguous()
+        return eng, layout, c3d, tap, lda
+
+    def _stage(self, videos, beam):
+        eng, layout, c3d, tap, lda = self._gather(videos)
         eng.set_inputs(layout, c3d, tap, lda, beam=beam)
         eng.encode()
         return eng, layout
@@ -240,11 +249,12 @@ class CaptionGenerator(nn.Module):
         soi_select_list).  Returns one (seq, logp) per video with the reference's per-call trimming
         (greedy) or (seq[N,S], logp[N,S], score[N]) per video (beam_size > 1)."""
         with torch.no_grad():
-            eng, layout = self._stage(videos, max(1, beam_size))
-            if beam_size > 1:
-                tokens, logp, score = eng.decode_beam(beam_size)
-            else:
-                tokens, logp = eng.decode_greedy()
+            eng, layout, c3d, tap, lda = self._gather(videos)
+            if layout.n_events == 0:
+                return [([], []) if beam_size <= 1 else (torch.zeros(0, eng.seq_length, dtype=torch.long, device=eng.device),
+                                                        torch.zeros(0, eng.seq_length, device=eng.device),
+                                                        torch.zeros(0, device=eng.device)) for _ in videos]
+            tokens, logp, score = eng.caption_device(layout, c3d, tap, lda, beam=max(1, beam_size))  # one library call
             out, r0 = [], 0
             for n in layout.events_per_video:
                 if beam_size > 1:

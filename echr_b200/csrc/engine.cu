@@ -108,6 +108,8 @@ struct GemmSpec {
   const float* tok_table = nullptr;
   long long ld_tok_table = 0;
   int ksplit = 1;  // 2: cluster split-K (run_gemm then launches the SPLIT == 2 kernel for the whole group)
+  const unsigned long long* row_key = nullptr;  // token from the packed arg-max keys instead of row_tok
+  unsigned long long* argmax_key = nullptr;     // logits: running arg-max keys
   // logits
   float* partial = nullptr;
   float* logits_out = nullptr;
@@ -143,6 +145,8 @@ static const char* fill_problem(GemmProblem& pb, const GemmSpec& s, int a_terms,
   pb.row_tok = s.row_tok;
   pb.tok_table = s.tok_table;
   pb.ld_tok_table = s.ld_tok_table;
+  pb.row_key = s.row_key;
+  pb.argmax_key = s.argmax_key;
   pb.hidden = HID;
   pb.partial = s.partial;
   pb.logits_out = s.logits_out;
@@ -432,6 +436,7 @@ static void batch_layout(echr_batch* b, Arena& a) {
   b->row_len = a.take<int32_t>(c.max_rows);
   b->unfinished = a.take<int32_t>(c.max_rows);
   b->row_tok = a.take<int32_t>(c.max_rows);
+  for (int i = 0; i < 2; ++i) b->argmax_key[i] = a.take<unsigned long long>((size_t)c.max_rows * KEY_STRIDE);
   b->tokens_dev = a.take<int32_t>((size_t)c.max_events * S);
   b->logp_dev = a.take<float>((size_t)c.max_events * S);
   b->score_dev = a.take<float>(c.max_events);
@@ -884,8 +889,10 @@ static int enqueue_init(echr_batch* b, int beam, cudaStream_t st) {
 // log-softmax / top-k.  The caller appends the mode's finalize kernel.
 enum { PART_H2ATT = 1, PART_ATT = 2, PART_GATES = 4, PART_LOGIT = 8, PART_ALL = 15 };
 
+// use_keys (greedy decode): the logit epilogue keeps a packed running arg-max per row (argmax_key[t & 1]) and the
+// gate GEMM of step t + 1 takes its input token from it, so the token chain does not pass through finalize.
 static int enqueue_step(echr_batch* b, int rows, int t, int topk, float* logits_out, long long ld_logits,
-                        cudaStream_t st, int parts = PART_ALL) {
+                        cudaStream_t st, int parts = PART_ALL, bool use_keys = false) {
   const echr_model* m = b->model;
   const int at = m->cfg.a_terms, wt = m->cfg.w_terms;
   const int p = t & 1, n = p ^ 1;
@@ -930,6 +937,7 @@ static int enqueue_step(echr_batch* b, int rows, int t, int topk, float* logits_
       s[l].bias = m->b_lstm[l];
       if (l != 1) { s[l].row_bias = b->row_bias[l / 2]; s[l].ld_row_bias = GATES; }
       s[l].row_tok = b->row_tok; s[l].tok_table = m->tok_gates[l]; s[l].ld_tok_table = GATES;
+      if (use_keys) s[l].row_key = b->argmax_key[(t + 1) & 1];  // written by the logits of step t - 1 (BOS at t = 0)
       s[l].ksplit = ks[l];
       s[l].c_in = b->cstate[p] + (long long)l * rows * HID;
       s[l].c_out = b->cstate[n] + (long long)l * rows * HID;
@@ -946,6 +954,7 @@ static int enqueue_step(echr_batch* b, int rows, int t, int topk, float* logits_
     s.bias = m->b_logit; s.partial = b->partial; s.logits_out = logits_out; s.ld_logits = ld_logits;
     const bool sp = logit_split(m, rows);
     if (sp) s.ksplit = 2;
+    if (use_keys) s.argmax_key = b->argmax_key[t & 1];
     PdlScope pdl(PDL_LOGIT);
     ECHR_TRY(run_gemm(&s, 1, at, wt, sp ? 256 : 128, EPI_LOGITS, topk, st, "logit", b, 3));
   }
@@ -979,28 +988,36 @@ static int enqueue_decode(echr_batch* b, int beam, int mode, cudaStream_t st, cu
     // (throughput regime: persistent GEMMs; measured better with the attention chain on the forked stream)
     static const bool crit_main_env = !(getenv("ECHR_CRIT_MAIN") && getenv("ECHR_CRIT_MAIN")[0] == '0');
     const bool crit_main = crit_main_env && rows < gemm2_min_rows();
+    // The gate GEMM of step t+1 reads its token from the arg-max keys the logit epilogue of step t maintains
+    // with atomics (ECHR_ARGMAX_KEYS=0: from finalize's row_tok), so the join waits for the logits only;
+    // finalize (log-sum-exp, outputs, `unfinished`) runs beside the next gate GEMM.
+    static const bool keys = !(getenv("ECHR_ARGMAX_KEYS") && getenv("ECHR_ARGMAX_KEYS")[0] == '0');
     ECHR_TRY(enqueue_step(b, rows, 0, topk, nullptr, 0, st, PART_H2ATT | PART_ATT));
+    cudaStream_t tok_st = crit_main ? side : st;  // token chain
+    cudaStream_t att_st = crit_main ? st : side;  // recurrent attention chain
     for (int t = 0; t < S; ++t) {
-      ECHR_TRY(enqueue_step(b, rows, t, topk, nullptr, 0, st, PART_GATES));
+      ECHR_TRY(enqueue_step(b, rows, t, topk, nullptr, 0, st, PART_GATES, keys));
       ECHR_CUDA(cudaEventRecord(b->cap_events[0], st));
       ECHR_CUDA(cudaStreamWaitEvent(side, b->cap_events[0], 0));
-      cudaStream_t tok_st = crit_main ? side : st;  // token chain
-      cudaStream_t att_st = crit_main ? st : side;  // recurrent attention chain
       if (!crit_main && t + 1 < S) {
         ECHR_TRY(enqueue_step(b, rows, t + 1, topk, nullptr, 0, att_st, PART_H2ATT | PART_ATT));
         ECHR_CUDA(cudaEventRecord(b->cap_events[1], att_st));
       }
-      ECHR_TRY(enqueue_step(b, rows, t, topk, nullptr, 0, tok_st, PART_LOGIT));
+      ECHR_TRY(enqueue_step(b, rows, t, topk, nullptr, 0, tok_st, PART_LOGIT, keys));
+      const bool last = t + 1 == S;
+      if (keys && !last) ECHR_CUDA(cudaEventRecord(b->cap_events[2], tok_st));  // logits(t) done
       {
         PdlScope pdl(PDL_FINALIZE);
-        ECHR_CUDA(launch_finalize_greedy(b, t, b->tokens_dev, b->logp_dev, tok_st));
+        ECHR_CUDA(launch_finalize_greedy(b, t, b->tokens_dev, b->logp_dev, tok_st, keys));
       }
       if (crit_main) {
-        ECHR_CUDA(cudaEventRecord(b->cap_events[1], tok_st));
-        if (t + 1 < S) ECHR_TRY(enqueue_step(b, rows, t + 1, topk, nullptr, 0, att_st, PART_H2ATT | PART_ATT));
-        ECHR_CUDA(cudaStreamWaitEvent(st, b->cap_events[1], 0));
-      } else if (t + 1 < S) {
-        ECHR_CUDA(cudaStreamWaitEvent(st, b->cap_events[1], 0));
+        if (!keys || last) ECHR_CUDA(cudaEventRecord(b->cap_events[2], tok_st));  // finalize(t) done
+        if (!last) ECHR_TRY(enqueue_step(b, rows, t + 1, topk, nullptr, 0, att_st, PART_H2ATT | PART_ATT));
+        ECHR_CUDA(cudaStreamWaitEvent(st, b->cap_events[2], 0));
+      } else {
+        // token chain on st itself: with keys the next gates would still follow finalize in stream order, so
+        // this arrangement gains nothing from them; join the attention chain
+        if (!last) ECHR_CUDA(cudaStreamWaitEvent(st, b->cap_events[1], 0));
       }
     }
     return ECHR_OK;

@@ -100,6 +100,7 @@ struct echr_batch {
   int32_t *row_start, *row_len;  // attention window per decode row
   int32_t* unfinished;      // [rows]
   int32_t* row_tok;         // [rows] input token of the next step (BOS = 0 at step 0)
+  unsigned long long* argmax_key[2];  // [rows * KEY_STRIDE] packed running arg-max of the logits (greedy), by step parity
   int32_t* tokens_dev;      // [events, S] scratch outputs for echr_caption_host
   float* logp_dev;
   float* score_dev;
@@ -151,7 +152,7 @@ cudaError_t launch_attention(const float* q, const void* proj, const void* clip,
                              unsigned long long* trace = nullptr, int trace_slot = 0);
 cudaError_t launch_decode_init(const echr_batch* b, int beam, cudaStream_t st);
 cudaError_t launch_finalize_greedy(echr_batch* b, int step, int32_t* tokens, float* logp,
-                                   cudaStream_t st);
+                                   cudaStream_t st, bool keys = false);
 cudaError_t launch_finalize_beam(const echr_batch* b, int beam, int step, int32_t* tokens,
                                  float* logp, float* score, cudaStream_t st);
 cudaError_t launch_finalize_tf(const echr_batch* b, int step, const int32_t* seq, int seq_cols,

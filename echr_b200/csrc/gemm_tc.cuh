@@ -67,12 +67,31 @@ struct GemmProblem {
   const int32_t* row_tok;
   const float* tok_table;
   long long ld_tok_table;
+  // alternative source of the token: packed arg-max keys written by the logit epilogue of the previous step
+  // (see argmax_key below); one key every KEY_STRIDE words
+  const unsigned long long* row_key;
   int hidden;          // H (N == 4H)
   // EPI_LOGITS
   float* partial;      // [M, n_groups, REC]   n_groups = ceil(N / BLOCK_N) * (BLOCK_N / LOGIT_GROUP)
   float* logits_out;   // optional [M, ld_logits]
   long long ld_logits;
+  // optional (TOPK == 1): running arg-max of the row over all tiles, as one 64-bit atomicMax per thread on
+  // argmax_key[row * KEY_STRIDE] = (orderable bits of the value) << 32 | (0xFFFFFFFF - column): the largest value
+  // wins, the lowest column among equals (torch.max).  Lets the next step's gate GEMM read its input token
+  // without waiting for the finalize kernel.  The key must be zero before the launch.
+  unsigned long long* argmax_key;
 };
+
+constexpr int KEY_STRIDE = 16;  // one key per 128-byte line: the 90 atomics of a row do not share a line with other rows
+
+__device__ __forceinline__ unsigned long long pack_argmax_key(float v, int col) {
+  unsigned int u = __float_as_uint(v);
+  u = (u & 0x80000000u) ? ~u : (u | 0x80000000u);  // monotone map float -> unsigned
+  return (static_cast<unsigned long long>(u) << 32) | static_cast<unsigned long long>(0xFFFFFFFFu - static_cast<unsigned int>(col));
+}
+__device__ __forceinline__ int token_of_key(unsigned long long key) {
+  return static_cast<int>(0xFFFFFFFFu - static_cast<unsigned int>(key & 0xFFFFFFFFull));
+}
 
 struct GemmParams {
   GemmProblem prob[GEMM_MAX_GROUPS];
@@ -318,7 +337,8 @@ gemm_tc_kernel(const __grid_constant__ GemmParams P) {
         }
       }
       if (pb.tok_table != nullptr && row_ok) {
-        const int tk = __ldg(pb.row_tok + row);
+        const int tk = pb.row_key != nullptr ? token_of_key(pb.row_key[static_cast<long long>(row) * KEY_STRIDE])
+                                             : __ldg(pb.row_tok + row);
         const float4* tp = reinterpret_cast<const float4*>(
             pb.tok_table + static_cast<long long>(tk) * pb.ld_tok_table + col0 + hc0);
 #pragma unroll
@@ -526,6 +546,10 @@ gemm_tc_kernel(const __grid_constant__ GemmParams P) {
             for (int i = 0; i < 32; ++i)
               if (cb + i < pb.N) o[i] = v[i];
           }
+        }
+        if constexpr (TOPK == 1) {
+          if (pb.argmax_key != nullptr && row_ok && gcol0 < pb.N)
+            atomicMax(pb.argmax_key + static_cast<long long>(row) * KEY_STRIDE, pack_argmax_key(tv[0], ti[0]));
         }
         // pass 2: sum of exp relative to the group maximum (exp(-inf) = 0 for masked columns)
         float se = 0.f;

@@ -197,7 +197,9 @@ gemm_tc2_kernel(const __grid_constant__ GemmParams P, int groups, int total_tile
       if constexpr (EPI == EPI_LSTM) {
         if (pb.row_bias != nullptr) rb_row = pb.row_bias + rowc * pb.ld_row_bias + col0 + hc0;
         if (pb.tok_table != nullptr)
-          tk_row = pb.tok_table + static_cast<long long>(__ldg(pb.row_tok + rowc)) * pb.ld_tok_table + col0 + hc0;
+          tk_row = pb.tok_table +
+                   static_cast<long long>(pb.row_key != nullptr ? token_of_key(pb.row_key[rowc * KEY_STRIDE])
+                                                                : __ldg(pb.row_tok + rowc)) * pb.ld_tok_table + col0 + hc0;
         c_row = pb.c_in + rowc * pb.hidden + ((col0 + hc0) >> 2);
       }
       auto lstm_load = [&](int c, float (&bb)[32], float (&cp)[8]) {
@@ -367,6 +369,10 @@ gemm_tc2_kernel(const __grid_constant__ GemmParams P, int groups, int total_tile
               for (int i = 0; i < 32; ++i)
                 if (cb + i < pb.N) o[i] = v[i];
             }
+          }
+          if constexpr (TOPK == 1) {
+            if (pb.argmax_key != nullptr && row_ok && gcol0 < pb.N)
+              atomicMax(pb.argmax_key + static_cast<long long>(row) * KEY_STRIDE, pack_argmax_key(tv[0], ti[0]));
           }
           float se = 0.f;
           const float m2 = tv[0] * 1.4426950408889634f;

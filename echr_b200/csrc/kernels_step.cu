@@ -555,6 +555,7 @@ decode_init_kernel(int beam, int a_planes, const float* __restrict__ event_ctx,
                    bf16* __restrict__ act0,
                    bf16* __restrict__ act1, long long act_plane, int32_t* __restrict__ row_start,
                    int32_t* __restrict__ row_len, int32_t* __restrict__ unfinished, int32_t* __restrict__ row_tok,
+                   unsigned long long* __restrict__ key0, unsigned long long* __restrict__ key1,
                    float* __restrict__ beam_score, int32_t* __restrict__ beam_live,
                    float* __restrict__ best_score) {
   const int r = blockIdx.x;
@@ -582,6 +583,8 @@ decode_init_kernel(int beam, int a_planes, const float* __restrict__ event_ctx,
   }
   if (threadIdx.x == 0) {
     row_tok[r] = 0;  // BOS (token 0)
+    key0[(long long)r * KEY_STRIDE] = 0ull;                           // running arg-max of the logits of step 0
+    key1[(long long)r * KEY_STRIDE] = pack_argmax_key(0.f, 0);        // "previous arg-max" read by step 0: BOS
     row_start[r] = ev_start[e];
     row_len[r] = ev_len[e];
     unfinished[r] = 1;
@@ -598,7 +601,8 @@ cudaError_t launch_decode_init(const echr_batch* b, int beam, cudaStream_t st) {
   decode_init_kernel<<<rows, 128, 0, st>>>(
       beam, (int)b->act[0].planes, b->event_ctx, b->lda, b->ev_video, b->ev_start, b->ev_len,
       b->act[0].p, b->act[1].p, b->act[0].plane_stride(),
-      b->row_start, b->row_len, b->unfinished, b->row_tok, b->beam_score, b->beam_live, b->best_score);
+      b->row_start, b->row_len, b->unfinished, b->row_tok, b->argmax_key[0], b->argmax_key[1], b->beam_score,
+      b->beam_live, b->best_score);
   count_launch();
   return cudaGetLastError();
 }
@@ -649,8 +653,8 @@ constexpr int FIN_WARPS = 4;
 __global__ void __launch_bounds__(FIN_WARPS * 32)
 finalize_greedy_kernel(int rows, int n_tiles, int step, int seq_len, const float* __restrict__ partial,
                        int32_t* __restrict__ row_tok, int32_t* __restrict__ unfinished,
-                       int32_t* __restrict__ tokens, float* __restrict__ logp, unsigned long long* trace,
-                       int trace_slot) {
+                       int32_t* __restrict__ tokens, float* __restrict__ logp, unsigned long long* __restrict__ key_next,
+                       unsigned long long* trace, int trace_slot) {
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int r = blockIdx.x * FIN_WARPS + warp;
   trace_begin(trace, trace_slot);
@@ -665,20 +669,23 @@ finalize_greedy_kernel(int rows, int n_tiles, int step, int seq_len, const float
     tokens[(long long)r * seq_len + step] = unf ? tok : 0;
     logp[(long long)r * seq_len + step] = -s.log_sum;
     row_tok[r] = tok;  // the raw argmax is the next step's input
+    // the arg-max keys the NEXT logit launch accumulates into (last read by the gate GEMM of this step)
+    if (key_next != nullptr) key_next[(long long)r * KEY_STRIDE] = 0ull;
   }
   __syncthreads();
   trace_end(trace, trace_slot);
 }
 
 cudaError_t launch_finalize_greedy(echr_batch* b, int step, int32_t* tokens, float* logp,
-                                   cudaStream_t st) {
+                                   cudaStream_t st, bool keys) {
   const int rows = b->n_events;
   if (rows == 0) return cudaSuccess;
   const echr_model* m = b->model;
   const int n_tiles = logit_groups_for(m, b->n_events);
   cudaError_t e = launch_pdl(finalize_greedy_kernel, dim3((rows + FIN_WARPS - 1) / FIN_WARPS), dim3(FIN_WARPS * 32), 0,
                              st, rows, n_tiles, step, m->cfg.seq_length, b->partial, b->row_tok,
-                             b->unfinished, tokens, logp, trace_ptr(b), trace_next(b, 4));
+                             b->unfinished, tokens, logp, keys ? b->argmax_key[(step + 1) & 1] : nullptr,
+                             trace_ptr(b), trace_next(b, 4));
   count_launch();
   return e;
 }

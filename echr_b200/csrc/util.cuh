@@ -49,9 +49,11 @@ inline int set_error(int code, const char* fmt, ...) {
 // the whole primary and starve the concurrent graph branch — every mask is slower than plain stream order
 // (cfg2: 186k vs 232k events/s).  Released when the primary's accumulators are ready (the default), only the
 // launch latency and the prologue of the dependent overlap the primary's epilogue: 232k -> 254k events/s.
-// Default mask 23 = the recurrent chain gates -> h2att -> attention -> gates (one stream) plus finalize; the
-// logit GEMM follows an event from another stream, where the attribute has no primary to hang on.
-enum { PDL_H2ATT = 1, PDL_ATT = 2, PDL_GATES = 4, PDL_LOGIT = 8, PDL_FINALIZE = 16, PDL_DEFAULT_MASK = 23 };
+// Default mask 7 = the recurrent chain gates -> h2att -> attention -> gates (one stream).  The logit GEMM
+// follows an event from another stream, where the attribute has no primary to hang on; finalize stays a plain
+// launch: as a programmatic dependent of the logits it sat between them and the event the next gate GEMM waits
+// for, and that GEMM then lost its own early launch (cfg2 with arg-max keys: 250k with it, 265k without).
+enum { PDL_H2ATT = 1, PDL_ATT = 2, PDL_GATES = 4, PDL_LOGIT = 8, PDL_FINALIZE = 16, PDL_DEFAULT_MASK = 7 };
 inline int pdl_mask() {
   static int mask = -1;
   if (mask < 0) {
