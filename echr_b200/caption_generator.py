@@ -173,9 +173,9 @@ def setup_fusion(opt):
 def trim_greedy(tokens, logp):
     """The reference stops (and so trims the columns) at the first step where every row of the call
     has already produced token 0 (OldModel_NEW.py:175-183); an empty result is ([], [])."""
-    alive = (tokens != 0).any(dim=0)
-    dead = (~alive).nonzero()
-    ncols = int(dead[0]) if dead.numel() else tokens.shape[1]
+    alive = (tokens.cpu() != 0).any(dim=0).numpy()  # one small D2H (the call's only sync), the rest on the host
+    dead = np.flatnonzero(~alive)
+    ncols = int(dead[0]) if dead.size else tokens.shape[1]
     if ncols == 0:
         return [], []
     return tokens[:, :ncols].long(), logp[:, :ncols]

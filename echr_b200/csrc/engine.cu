@@ -188,7 +188,12 @@ static int ksplit_mask() {
   return v;
 }
 // window-length bucket baked into a decode graph (attention variant and its shared-memory staging size)
-static int len_bucket(int max_len) { return ((max_len + 31) / 32) * 32; }
+// (powers of two from 32: few distinct decode graphs for a stream of videos with different spans)
+static int len_bucket(int max_len) {
+  int bkt = 32;
+  while (bkt < max_len) bkt <<= 1;
+  return bkt;
+}
 static int m_tiles_of(int rows) { return (rows + GEMM_BLOCK_M - 1) / GEMM_BLOCK_M; }
 // logit GEMM as 128 x 256 tiles shared by CTA pairs (23 x 2 CTAs per 128 rows at the ECHR vocabulary)
 static bool logit_split(const echr_model* m, int rows) {
@@ -628,6 +633,17 @@ static int ensure_capture_streams(echr_batch* b) {
   return ECHR_OK;
 }
 
+// True when `key` has a cached graph or was seen before (second sight: worth capturing); remembers it otherwise.
+static bool worth_a_graph(echr_batch* b, const long long (&key)[6]) {
+  for (int i = 0; i < echr_batch::GRAPH_SLOTS; ++i)
+    if (b->graphs[i].exec != nullptr && memcmp(b->graphs[i].key, key, sizeof(key)) == 0) return true;
+  for (int i = 0; i < echr_batch::SEEN_KEYS; ++i)
+    if (memcmp(b->seen_keys[i], key, sizeof(key)) == 0) return true;
+  memcpy(b->seen_keys[b->seen_next], key, sizeof(key));
+  b->seen_next = (b->seen_next + 1) % echr_batch::SEEN_KEYS;
+  return false;
+}
+
 template <typename F>
 static int run_graph(echr_batch* b, const long long (&key)[6], cudaStream_t st, const char* what, bool traced, F&& enqueue) {
   echr_batch::GraphSlot* slot = nullptr;
@@ -767,17 +783,16 @@ extern "C" int echr_encode(echr_batch_t* b, void* stream) {
   cudaStream_t st = (cudaStream_t)stream;
   ECHR_CUDA(init_pos_table());
   static const bool graphed = !(getenv("ECHR_ENCODE_GRAPH") && getenv("ECHR_ENCODE_GRAPH")[0] == '0');
-  if (graphed) {
-    const long long key[6] = {2, b->n_videos, b->n_events, b->n_clips, b->n_pairs, b->max_n};
+  const long long key[6] = {2, b->n_videos, b->n_events, b->n_clips, b->n_pairs, b->max_n};
+  const bool use_graph = graphed && worth_a_graph(b, key);
+  if (use_graph) {
     ECHR_TRY(run_graph(b, key, st, "encode", false, [&](cudaStream_t cs) {
       return enqueue_encode(b, cs, b->cap_stream2, b->cap_stream3, b->cap_events);
     }));
   } else {
-    ECHR_TRY(encode_clips(b, st));
-    if (b->n_events > 0) {
-      ECHR_CUDA(launch_event_feats(b, st));
-      ECHR_TRY(encode_relation(b, st));
-    }
+    // eager: the same three chains on the batch's side streams
+    ECHR_TRY(ensure_capture_streams(b));
+    ECHR_TRY(enqueue_encode(b, st, b->cap_stream2, b->cap_stream3, b->cap_events));
   }
   b->encoded = true;
   return ECHR_OK;
@@ -1040,6 +1055,12 @@ static int run_decode(echr_batch* b, int beam, int mode, cudaStream_t st) {
   if (b->n_events == 0) return ECHR_OK;
   const int rows = b->n_events * beam;
   const long long key[6] = {1, rows, mode == MODE_BEAM ? beam : 0, len_bucket(b->max_len), 0, 0};
+  const char* tr = getenv("ECHR_TRACE");
+  if (!(tr != nullptr && tr[0] == '1') && !worth_a_graph(b, key)) {
+    // first sight of this shape: the same fork/join schedule, enqueued eagerly on the caller's stream
+    ECHR_TRY(ensure_capture_streams(b));
+    return enqueue_decode(b, beam, mode, st, b->cap_stream2);
+  }
   return run_graph(b, key, st, "decode", true,
                    [&](cudaStream_t cs) { return enqueue_decode(b, beam, mode, cs, b->cap_stream2); });
 }

@@ -118,9 +118,14 @@ struct echr_batch {
     long long kernels;  // kernel nodes in the graph
     unsigned long long stamp;
   };
-  static constexpr int GRAPH_SLOTS = 8;
+  static constexpr int GRAPH_SLOTS = 64;
   GraphSlot graphs[GRAPH_SLOTS];
   unsigned long long graph_clock;
+  // shapes seen once are run eagerly: a shape is only captured when it comes back (a per-video eval loop sees a
+  // new clip count on almost every call, and capturing + instantiating a 150-node graph costs ~20 ms)
+  static constexpr int SEEN_KEYS = 64;
+  long long seen_keys[SEEN_KEYS][6];
+  int seen_next;
   cudaStream_t cap_stream;   // private stream graphs are captured on
   cudaStream_t cap_stream2;  // forked branches inside a capture
   cudaStream_t cap_stream3;

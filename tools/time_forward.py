@@ -10,7 +10,8 @@ torch.set_grad_enabled(False)
 opt = echr_opt()
 sd = synth.init_state_dict(opt, 0)
 m = CaptionGenerator(opt, precision=sys.argv[1] if len(sys.argv) > 1 else "fp32"); m.load_state_dict(sd); m = m.cuda()
-vids = [synth.make_video(i, T=100, n_events=3 + i % 3, style="gt") for i in range(64)]
+# an eval-loop-like stream: every video has its own clip count and number of events
+vids = [synth.make_video(i, T=60 + 11 * (i % 29), n_events=1 + (i * 7) % 9, style="gt") for i in range(64)]
 args = [v.args("cuda:0") for v in vids]
 for a in args[:8]:
     m(*a, mode="eval")
@@ -25,3 +26,14 @@ for rep in range(3):
 torch.cuda.synchronize()
 dt = time.perf_counter() - t0
 print("forward(mode='eval'), one video per call: %.3f ms per call (%d calls), %.0f events/s" % (dt / n * 1e3, n, sum(len(v.ind_select_list) for v in vids) * 3 / dt))
+
+import cProfile, pstats, io
+pr = cProfile.Profile()
+pr.enable()
+for a in args:
+    seq, lp = m(*a, mode="eval")
+    s = lp.sum(1).cpu()
+pr.disable()
+st = io.StringIO()
+pstats.Stats(pr, stream=st).sort_stats("cumulative").print_stats(25)
+print(st.getvalue())
