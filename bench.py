@@ -143,12 +143,31 @@ def main_reference(args, rank, world):
                              "sample": "first %d videos (%d events) of the workload, one video per call, median of %d passes"
                                        % (sample, n_ev, max(1, args.steps))},
             "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
-    print(json.dumps(line))
+    _RESULT.append(json.dumps(line))
     return 0
 
 
 def main():
     args = parse()
+    # stdout carries exactly one JSON line: anything a library prints there meanwhile (NCCL's version banner, ...)
+    # is sent to stderr; the real stdout comes back for the final print
+    sys.stdout.flush()
+    real_stdout = os.dup(1)
+    os.dup2(2, 1)
+    try:
+        return _main(args)
+    finally:
+        sys.stdout.flush()
+        os.dup2(real_stdout, 1)
+        os.close(real_stdout)
+        if _RESULT:
+            print(_RESULT[0], flush=True)
+
+
+_RESULT = []
+
+
+def _main(args):
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
@@ -222,16 +241,18 @@ def main():
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize()
-        ms = 0.0
+        # every step is bracketed by its own pair of CUDA events; the host does not wait between steps (a job
+        # that captions batch after batch keeps the stream fed), the L2 flush sits between the pairs, untimed
+        pairs = []
         for _ in range(steps):
             flush.zero_()  # L2 flush between timed iterations (not timed)
             e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             e0.record()
             fn()
             e1.record()
-            e1.synchronize()
-            ms += e0.elapsed_time(e1)
+            pairs.append((e0, e1))
         torch.cuda.synchronize()
+        ms = sum(a.elapsed_time(b) for a, b in pairs)
         if world > 1:
             dist.barrier()
             t = torch.tensor([ms], dtype=torch.float64, device=dev)
@@ -319,7 +340,7 @@ def main():
                                 "sample": "first %d videos (%d events) of the workload, one video per call, "
                                           "median of %d passes after 1 warm-up (%.2f s per pass)"
                                           % (sample, sum(x.n_events for x in sub), reps, sec)}
-    print(json.dumps(line))
+    _RESULT.append(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()
     return 0
