@@ -466,17 +466,29 @@ attention_v2_kernel(const float* __restrict__ q, const void* __restrict__ proj_v
   trace_end(trace, trace_slot);
 }
 
-// max_len: largest window of the launch (0 = unknown).  The staged kernel (one CTA per SM: it owns
-// ~200 KB of shared memory) is used when every window fits and the launch is a single wave
-// (rows <= 148); beyond that the streaming kernel wins because several of its CTAs share an SM and
-// it can co-reside with the concurrent logit GEMM of the decode graph (measured: profiles/).
-// ECHR_ATT_STAGED=1 / ECHR_ATT_STREAM=1 force one or the other.
+// max_len: largest window of the launch (0 = unknown).  Variant choice (measured, profiles/r01_notes.md):
+//   * staged kernel (one CTA per SM, ~200 KB of shared memory): every window fits and the launch is a single
+//     wave (rows <= 148);
+//   * attention_v2_kernel (warps own clips, clip rows requested before the softmax barrier, 256 threads): every
+//     other launch whose longest window is known — 8.1 vs 10.1 us at 251 rows, 55 vs 71 us at 4072 rows, 82 vs
+//     101 us at 3200 rows x 256-clip windows against the streaming kernel;
+//   * streaming attention_kernel: max_len unknown (stand-alone echr_attention_step calls), or forced.
+// ECHR_ATT_STAGED=1 / ECHR_ATT_STREAM=1 / ECHR_ATT_V2_ROWS=0 force one or the other.
 // rows up to which the latency-regime kernel is used (ECHR_ATT_V2_ROWS; 0 disables it)
 static int att_v2_rows() {
   static int v = -1;
   if (v < 0) {
     const char* e = getenv("ECHR_ATT_V2_ROWS");
-    v = e ? atoi(e) : 1024;
+    v = e ? atoi(e) : (1 << 30);
+  }
+  return v;
+}
+// longest window the latency kernel takes (ECHR_ATT_V2_MAXLEN)
+static int att_v2_maxlen() {
+  static int v = -1;
+  if (v < 0) {
+    const char* e = getenv("ECHR_ATT_V2_MAXLEN");
+    v = e ? atoi(e) : ATT_MAX_L;
   }
   return v;
 }
@@ -508,7 +520,7 @@ cudaError_t launch_attention(const float* q, const void* proj, const void* clip,
     else
       e = launch_pdl(attention_staged_kernel<false, ATT_THREADS>, dim3((unsigned)rows), dim3(ATT_THREADS), stage, st, q, proj, clip,
                      (long long)ld_clip, alpha, row_start, row_len, out_f32, out_hi, out_lo, (long long)ld_bf, max_len, trace, trace_slot);
-  } else if (att_v2_rows() > 0 && rows <= att_v2_rows() && max_len > 0 && max_len <= 128) {
+  } else if (att_v2_rows() > 0 && rows <= att_v2_rows() && max_len > 0 && max_len <= att_v2_maxlen()) {
     // latency regime: short windows.  256-thread CTAs (16 K registers, 13 KB) also fit next to a resident
     // CTA of the concurrent logit GEMM, so the launch is one wave even while that GEMM holds 90 SMs.
     static const int v2_threads = getenv("ECHR_ATT_V2_THREADS") ? atoi(getenv("ECHR_ATT_V2_THREADS")) : 256;
