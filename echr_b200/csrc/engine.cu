@@ -194,6 +194,15 @@ static int len_bucket(int max_len) {
   while (bkt < max_len) bkt <<= 1;
   return bkt;
 }
+// Constant-context terms (event / video inputs of streams 0 and 2): hoisted into a per-row gate bias in the
+// latency regime, where a gate CTA is bound by its operand stream; kept inside the step GEMM (10 more k-blocks)
+// in the throughput regime, where the persistent kernel is bound by the row-per-thread gathers of its epilogue
+// and the tensor pipe has room (ECHR_HOIST_CTX=0/1 forces).
+static bool hoist_context(int rows) {
+  static const int forced = getenv("ECHR_HOIST_CTX") ? atoi(getenv("ECHR_HOIST_CTX")) : -1;
+  if (forced >= 0) return forced != 0;
+  return rows < gemm2_min_rows();
+}
 static int m_tiles_of(int rows) { return (rows + GEMM_BLOCK_M - 1) / GEMM_BLOCK_M; }
 // logit GEMM as 128 x 256 tiles shared by CTA pairs (23 x 2 CTAs per 128 rows at the ECHR vocabulary)
 static bool logit_split(const echr_model* m, int rows) {
@@ -369,7 +378,7 @@ extern "C" int echr_model_create(const echr_config_t* config, const echr_weights
     PlaneMat wx = m->w_lstm[l];  // columns 0..511 of [x | h | ctx]
     GemmSpec s;
     s.A = &m->embed; s.M = m->V1; s.W = &wx; s.N = GATES; s.K = HID;
-    s.bias = (l == 1) ? m->b_lstm[1] : nullptr;
+    s.bias = m->b_lstm[l];  // b_ih + b_hh ride in the table for every stream
     s.out_f32 = m->tok_gates[l]; s.ld_f32 = GATES;
     const int rc = run_gemm(&s, 1, 2, m->cfg.w_terms, 128, EPI_STORE, 1, st, "token_gate_table");
     if (rc != ECHR_OK) {
@@ -868,6 +877,9 @@ extern "C" int echr_get_event_context(const echr_batch_t* b, float* out, void* s
 static const int KB_L0[8] = {26, 27, 28, 29, 30, 31, 32, 33};                                   // h0
 static const int KB_L1[16] = {34, 35, 36, 37, 38, 39, 40, 41, 16, 17, 18, 19, 20, 21, 22, 23};  // h1, att
 static const int KB_L2[8] = {42, 43, 44, 45, 46, 47, 48, 49};                                   // h2
+// with the constant-context blocks kept in the step GEMM (weights' column order [x | h | ctx])
+static const int KB_L0C[16] = {26, 27, 28, 29, 30, 31, 32, 33, 8, 9, 10, 11, 12, 13, 14, 15};   // h0, event
+static const int KB_L2C[10] = {42, 43, 44, 45, 46, 47, 48, 49, 24, 25};                         // h2, video
 
 enum { MODE_GREEDY = 0, MODE_BEAM = 1, MODE_TF = 2 };
 
@@ -881,6 +893,7 @@ static int enqueue_init(echr_batch* b, int beam, cudaStream_t st) {
   // Hoist the constant-context terms of streams 0 and 2 out of the time loop: per-row gate bias
   //   row_bias0 = W_ih0[:, event] . event_ctx + (b_ih0 + b_hh0),  row_bias2 = W_ih2[:, video] . lda + (b_ih2 + b_hh2)
   // (ThreeStream_Core feeds the same event / video context at every step, OldModel_NEW.py:806-817).
+  if (!hoist_context((int)rows)) return ECHR_OK;
   const echr_model* m = b->model;
   const int at = m->cfg.a_terms, wt = m->cfg.w_terms;
   GemmSpec s[2];
@@ -892,7 +905,7 @@ static int enqueue_init(echr_batch* b, int beam, cudaStream_t st) {
     wv[i] = m->w_lstm[layer[i]];
     wv[i].p += 2 * HID;  // the context block of [x | h | ctx]; plane stride and ld are unchanged
     s[i].A = &b->act[0]; s[i].a_col0 = col0[i]; s[i].M = (int)rows; s[i].W = &wv[i]; s[i].N = GATES; s[i].K = K[i];
-    s[i].bias = m->b_lstm[layer[i]];
+    s[i].bias = nullptr;  // the fused bias is part of the token gate tables
     s[i].out_f32 = b->row_bias[i]; s[i].ld_f32 = GATES;
   }
   ECHR_TRY(run_gemm(s, 2, at, wt, 128, EPI_STORE, 1, st, "hoisted_context"));  // both streams in one launch
@@ -943,14 +956,15 @@ static int enqueue_step(echr_batch* b, int rows, int t, int topk, float* logits_
       if (mt * nt * 6 <= num_sms()) ks[0] = ks[1] = ks[2] = 2;
       else if (mt * nt * 4 <= num_sms()) ks[1] = 2;
     }
-    const int* kbs[3] = {KB_L0, KB_L1, KB_L2};
-    const int K[3] = {8 * 64, 16 * 64, 8 * 64};
+    const bool hoist = hoist_context(rows);
+    const int* kbs[3] = {hoist ? KB_L0 : KB_L0C, KB_L1, hoist ? KB_L2 : KB_L2C};
+    const int K[3] = {(hoist ? 8 : 16) * 64, 16 * 64, (hoist ? 8 : 10) * 64};
     for (int l = 0; l < 3; ++l) {
       wv[l] = m->w_lstm[l];
       wv[l].p += HID;  // skip the x block of [x | h | ctx]; plane stride and ld are unchanged
       s[l].A = &cur; s[l].a_kb = kbs[l]; s[l].M = rows; s[l].W = &wv[l]; s[l].N = GATES; s[l].K = K[l];
       s[l].bias = m->b_lstm[l];
-      if (l != 1) { s[l].row_bias = b->row_bias[l / 2]; s[l].ld_row_bias = GATES; }
+      if (l != 1 && hoist) { s[l].row_bias = b->row_bias[l / 2]; s[l].ld_row_bias = GATES; }
       s[l].row_tok = b->row_tok; s[l].tok_table = m->tok_gates[l]; s[l].ld_tok_table = GATES;
       if (use_keys) s[l].row_key = b->argmax_key[(t + 1) & 1];  // written by the logits of step t - 1 (BOS at t = 0)
       s[l].ksplit = ks[l];
