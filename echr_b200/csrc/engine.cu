@@ -1188,21 +1188,37 @@ extern "C" int echr_time_step_kernels(echr_batch_t* b, int beam, int iters, floa
   const int parts[4] = {PART_H2ATT, PART_ATT, PART_GATES, PART_LOGIT};
   int rc = enqueue_init(b, beam, st);  // fresh state (a finished beam decode leaves every slot dead)
   if (rc == ECHR_OK) rc = enqueue_step(b, rows, 0, beam > 1 ? 4 : 1, nullptr, 0, st);
+  // each kernel: `iters` launches captured into one graph (no host launch gaps between them, like inside the
+  // decode graph), replayed once to warm up and once between the two events
+  if (rc == ECHR_OK) rc = ensure_capture_streams(b);
+  if (rc == ECHR_OK && cudaStreamSynchronize(st) != cudaSuccess) rc = set_error(ECHR_ERR_CUDA, "echr_time_step_kernels: sync failed");
+  const bool saved_regime = pdl_regime();
+  pdl_regime() = false;  // plain launches: a launch must not overlap the tail of its identical predecessor
   for (int k = 0; k < 5 && rc == ECHR_OK; ++k) {
+    cudaGraph_t graph = nullptr;
+    cudaGraphExec_t exec = nullptr;
+    if (cudaStreamBeginCapture(b->cap_stream, cudaStreamCaptureModeRelaxed) != cudaSuccess) { rc = set_error(ECHR_ERR_CUDA, "echr_time_step_kernels: capture failed"); break; }
+    for (int i = 0; i < iters && rc == ECHR_OK; ++i) {
+      if (k < 4) rc = enqueue_step(b, rows, 1, beam > 1 ? 4 : 1, nullptr, 0, b->cap_stream, parts[k]);
+      else if (beam > 1) { if (launch_finalize_beam(b, beam, 1, b->tokens_dev, b->logp_dev, b->score_dev, b->cap_stream) != cudaSuccess) rc = set_error(ECHR_ERR_CUDA, "finalize_beam launch failed"); }
+      else { if (launch_finalize_greedy(b, 1, b->tokens_dev, b->logp_dev, b->cap_stream) != cudaSuccess) rc = set_error(ECHR_ERR_CUDA, "finalize_greedy launch failed"); }
+    }
+    cudaError_t ce = cudaStreamEndCapture(b->cap_stream, &graph);
+    if (rc == ECHR_OK && ce != cudaSuccess) rc = set_error(ECHR_ERR_CUDA, "echr_time_step_kernels: end capture: %s", cudaGetErrorString(ce));
+    if (rc == ECHR_OK && cudaGraphInstantiate(&exec, graph, 0) != cudaSuccess) rc = set_error(ECHR_ERR_CUDA, "echr_time_step_kernels: instantiate failed");
+    if (graph) cudaGraphDestroy(graph);
     for (int pass = 0; pass < 2 && rc == ECHR_OK; ++pass) {  // pass 0 warms up
       cudaEventRecord(e0, st);
-      for (int i = 0; i < iters && rc == ECHR_OK; ++i) {
-        if (k < 4) rc = enqueue_step(b, rows, 1, beam > 1 ? 4 : 1, nullptr, 0, st, parts[k]);
-        else if (beam > 1) { if (launch_finalize_beam(b, beam, 1, b->tokens_dev, b->logp_dev, b->score_dev, st) != cudaSuccess) rc = set_error(ECHR_ERR_CUDA, "finalize_beam launch failed"); }
-        else { if (launch_finalize_greedy(b, 1, b->tokens_dev, b->logp_dev, st) != cudaSuccess) rc = set_error(ECHR_ERR_CUDA, "finalize_greedy launch failed"); }
-      }
+      cudaGraphLaunch(exec, st);
       cudaEventRecord(e1, st);
       if (cudaEventSynchronize(e1) != cudaSuccess) rc = set_error(ECHR_ERR_CUDA, "echr_time_step_kernels: kernel failed: %s", cudaGetErrorString(cudaGetLastError()));
       float ms = 0.f;
       cudaEventElapsedTime(&ms, e0, e1);
       host_ms[k] = ms / iters;
     }
+    if (exec) cudaGraphExecDestroy(exec);
   }
+  pdl_regime() = saved_regime;
   cudaEventDestroy(e0);
   cudaEventDestroy(e1);
   g_launches.store(before);

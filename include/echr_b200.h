@@ -207,7 +207,8 @@ ECHR_API int echr_caption_device(echr_batch_t* batch, const echr_batch_desc_t* d
 
 /* Measurement aid for bench.py's roofline: average duration in ms of each kernel of one decode step
  * (host_ms[5] = h2att GEMM, fused attention, LSTM gate GEMM, logit GEMM, finalize), from CUDA
- * events on `stream` around `iters` back-to-back launches.  Needs a decoded batch; synchronises. */
+ * events on `stream` around a captured graph of `iters` back-to-back plain launches of that kernel
+ * (no host launch gaps, as in the decode graph).  Needs a decoded batch; synchronises. */
 ECHR_API int echr_time_step_kernels(echr_batch_t* batch, int beam, int iters, float* host_ms, void* stream);
 
 /* Debug aid: timeline of the last decode-graph replay when the graph was captured with ECHR_TRACE=1 in

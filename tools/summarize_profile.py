@@ -1,4 +1,4 @@
-"""Turns gpurun_out/prof_launches.csv and gpurun_out/prof_step.ncu-rep (tools/gpu_profile.sh) into the
+"""Turns gpurun_out/prof_launches.csv (tools/gpu_profile.sh) and gpurun_out/prof_step.ncu-rep (tools/gpu_profile_full.sh) into the
 tracked summaries under profiles/:  python tools/summarize_profile.py <tag>"""
 import collections
 import csv
@@ -24,8 +24,8 @@ for r in rows[1:]:
     seq.append((name, r[iG], ns))
 tot = sum(a[1] for a in agg.values())
 with open("profiles/%s_launch_shares_cfg2_bf16w.md" % tag, "w") as f:
-    f.write("# ncu launch list of `python bench.py --steps 2 --warmup 1 --no-cpu-baseline` (cfg2, bf16w)\n\n")
-    f.write("`ncu --metrics gpu__time_duration.sum --clock-control none -c 800` (cold-cache, serialised: compare shares). "
+    f.write("# ncu launch list of `python bench.py --steps 2 --warmup 2 --no-cpu-baseline` (cfg2, bf16w)\n\n")
+    f.write("`ncu --metrics gpu__time_duration.sum --clock-control none -c 2000` (cold-cache, serialised: compare shares). "
             "Raw list: %s_launches_cfg2_bf16w.csv\n\n" % tag)
     f.write("| kernel | grid | launches | total us | avg us | share |\n|---|---|---|---|---|---|\n")
     for (name, grid), (n, ns) in sorted(agg.items(), key=lambda kv: -kv[1][1]):
