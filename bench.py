@@ -39,7 +39,7 @@ def parse():
     ap.add_argument("--workload", default="cfg2", choices=sorted(synth.WORKLOADS))
     ap.add_argument("--videos", type=int, default=None, help="override the workload's video count (per GPU)")
     ap.add_argument("--beam", type=int, default=None)
-    ap.add_argument("--precision", default="bf16w", choices=["fp32", "bf16w", "bf16"])
+    ap.add_argument("--precision", default="bf16w", choices=["fp32", "bf16w", "f16"])
     ap.add_argument("--cpu-sample", type=int, default=None, help="videos in the CPU-baseline sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     return ap.parse_args()
@@ -307,9 +307,9 @@ def _main(args):
                 "ms_per_launch": kt[dom], "step_kernel_ms": kt,
                 "per_kernel_tflops": {k: flops[k] / (kt[k] * 1e-3) / 1e12 for k in flops},
                 "note": "algorithmic FLOPs 2*M*N*K of one product; the %s mode issues %d tcgen05 products per k-step"
-                        % (args.precision, {"fp32": 3, "bf16w": 2, "bf16": 1}[args.precision])}
+                        % (args.precision, {"fp32": 3, "bf16w": 2, "f16": 1}[args.precision])}
     # attention kernel against HBM (2024*L + 4048 bytes per event-step at bf16, fp32 clip doubles the window)
-    el = 2 if args.precision == "bf16" else 4
+    el = 4  # clip features and the e^{2P} table are read as fp32 in every precision
     win = sum((s[1] - s[0]) for v in vids for s in v.soi_select_list) * beam
     att_bytes = win * (500 + 512) * el + rows * (512 * 4 + 500 * 4)
     roofline["attention"] = {"bound": "hbm", "achieved": att_bytes / (kt["attention"] * 1e-3) / 1e9,
@@ -319,7 +319,7 @@ def _main(args):
     line = {"metric": METRIC, "value": total_events * args.steps / (ms_dev * 1e-3), "unit": UNIT, "n_gpus": world,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_dev / args.steps,
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-            "dtype": {"fp32": "bf16x3 (fp32-grade)", "bf16w": "bf16", "bf16": "bf16"}[args.precision],
+            "dtype": {"fp32": "bf16x3 (fp32-grade)", "bf16w": "bf16", "f16": "fp16"}[args.precision],
             "data": "synthetic",
             "config": dict(workload_config(args, w, n_events, world), precision=args.precision,
                            l2_flush_between_steps=True, ms_per_decode_step=ms_dev / args.steps / S),

@@ -35,7 +35,16 @@ int echr_split_bf16(const float* src, int64_t rows, int64_t cols, int64_t ld_src
   ECHR_REQUIRE(src && hi, "echr_split_bf16: null pointer");
   ECHR_REQUIRE(rows >= 0 && cols >= 0 && cols_dst >= cols && ld_dst >= cols_dst && ld_src >= cols,
                "echr_split_bf16: bad shape");
-  ECHR_CUDA(launch_split(src, rows, cols, ld_src, (bf16*)hi, (bf16*)lo, ld_dst, cols_dst, (cudaStream_t)stream));
+  ECHR_CUDA(launch_split(src, rows, cols, ld_src, (bf16*)hi, (bf16*)lo, ld_dst, cols_dst, false, (cudaStream_t)stream));
+  return ECHR_OK;
+}
+
+int echr_split_f16(const float* src, int64_t rows, int64_t cols, int64_t ld_src, void* dst, int64_t ld_dst,
+                   int64_t cols_dst, void* stream) {
+  ECHR_REQUIRE(src && dst, "echr_split_f16: null pointer");
+  ECHR_REQUIRE(rows >= 0 && cols >= 0 && cols_dst >= cols && ld_dst >= cols_dst && ld_src >= cols,
+               "echr_split_f16: bad shape");
+  ECHR_CUDA(launch_split(src, rows, cols, ld_src, (bf16*)dst, nullptr, ld_dst, cols_dst, true, (cudaStream_t)stream));
   return ECHR_OK;
 }
 

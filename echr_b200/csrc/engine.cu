@@ -46,7 +46,7 @@ struct Arena {
 // hidden unit in adjacent accumulator columns; the per-step operands (x, h) come first so that the
 // constant-context block (event / video) can be hoisted out of the step GEMM as a column sub-range.
 __global__ void pack_lstm_kernel(const float* __restrict__ w_ih, const float* __restrict__ w_hh, int ctx,
-                                 int ctx_pad, bf16* __restrict__ hi, bf16* __restrict__ lo) {
+                                 int ctx_pad, bf16* __restrict__ hi, bf16* __restrict__ lo, bool f16) {
   const int K = HID + HID + ctx_pad;
   const int in_ih = HID + ctx;
   const long long total = (long long)GATES * K;
@@ -60,7 +60,7 @@ __global__ void pack_lstm_kernel(const float* __restrict__ w_ih, const float* __
     else if (c < 2 * HID) x = w_hh[(long long)src * HID + (c - HID)];
     else if (c - 2 * HID < ctx) x = w_ih[(long long)src * in_ih + HID + (c - 2 * HID)];
     bf16 h, l;
-    split_bf16(x, h, l);
+    split16(x, f16, h, l);
     hi[i] = h;
     if (lo != nullptr) lo[i] = l;
   }
@@ -282,7 +282,7 @@ static void model_layout(echr_model* m, Arena& a) {
   m->w_lstm[1] = a.planes(wt, GATES, HID + HID + CLIP_PAD);  // x | h1 | attended clip
   m->w_lstm[2] = a.planes(wt, GATES, HID + HID + VID_PAD);   // x | h2 | video
   m->w_logit = a.planes(wt, m->V1, 3 * HID);
-  m->embed = a.planes(2, m->V1, HID);
+  m->embed = a.planes(m->cfg.a_terms == 1 ? 1 : 2, m->V1, HID);  // an A operand of the table build
   m->b_event_emb = a.take<float>(HID);
   m->b_qky = a.take<float>(3 * HID);
   m->b_fc1 = a.take<float>(HID);
@@ -296,11 +296,12 @@ static void model_layout(echr_model* m, Arena& a) {
   for (int l = 0; l < 3; ++l) m->tok_gates[l] = a.take<float>((size_t)m->V1 * GATES);
 }
 
-static cudaError_t pack_linear(const float* w, int out_f, int in_f, const PlaneMat& dst, int row0,
+// f16: the single-plane precision (a_terms == 1) keeps every operand, weights included, as fp16
+static cudaError_t pack_linear(const float* w, int out_f, int in_f, const PlaneMat& dst, int row0, bool f16,
                                cudaStream_t st) {
   bf16* hi = dst.plane(0) + (long long)row0 * dst.ld;
   bf16* lo = dst.planes > 1 ? dst.plane(1) + (long long)row0 * dst.ld : nullptr;
-  return launch_split(w, out_f, in_f, in_f, hi, lo, dst.ld, dst.ld, st);
+  return launch_split(w, out_f, in_f, in_f, hi, lo, dst.ld, dst.ld, f16, st);
 }
 
 extern "C" int echr_model_create(const echr_config_t* config, const echr_weights_t* w, void* stream,
@@ -311,6 +312,9 @@ extern "C" int echr_model_create(const echr_config_t* config, const echr_weights
   ECHR_REQUIRE((config->a_terms == 1 || config->a_terms == 2) && (config->w_terms == 1 || config->w_terms == 2) &&
                    !(config->a_terms == 1 && config->w_terms == 2),
                "echr_model_create: (a_terms, w_terms) must be (1,1), (2,1) or (2,2)");
+  ECHR_REQUIRE(config->clip_bf16 == 0,
+               "echr_model_create: clip_bf16 is retired (the single-plane operand format is fp16, whose range cannot "
+               "hold the e^{2P} table); pass 0");
   const float* const* wp = reinterpret_cast<const float* const*>(w);
   for (size_t i = 0; i < sizeof(echr_weights_t) / sizeof(float*); ++i)
     ECHR_REQUIRE(wp[i] != nullptr, "echr_model_create: weight pointer %d is null", (int)i);
@@ -341,22 +345,23 @@ extern "C" int echr_model_create(const echr_config_t* config, const echr_weights
     }                                                                                   \
   } while (0)
   PK(cudaMemsetAsync(m->arena, 0, sizing.off, st));
-  PK(pack_linear(w->event_emb_w, HID, ECHR_VIDEO_DIM + HID, m->w_event_emb, 0, st));
-  PK(pack_linear(w->query_w, HID, HID, m->w_qky, 0, st));
-  PK(pack_linear(w->key_w, HID, HID, m->w_qky, HID, st));
-  PK(pack_linear(w->out_w, HID, HID, m->w_qky, 2 * HID, st));
-  PK(pack_linear(w->pos_fc1_w, HID, HID, m->w_fc1, 0, st));
-  PK(pack_linear(w->pos_fc2_w, ECHR_HEADS, HID, m->w_fc2, 0, st));
-  PK(pack_linear(w->ctx2att_w, HID, ECHR_VIDEO_DIM, m->w_ctx2att, 0, st));
-  PK(pack_linear(w->h2att_w, HID, HID, m->w_h2att, 0, st));
-  PK(pack_linear(w->logit_w, m->V1, 3 * HID, m->w_logit, 0, st));
-  PK(pack_linear(w->embed_w, m->V1, HID, m->embed, 0, st));
+  const bool f16 = config->a_terms == 1;
+  PK(pack_linear(w->event_emb_w, HID, ECHR_VIDEO_DIM + HID, m->w_event_emb, 0, f16, st));
+  PK(pack_linear(w->query_w, HID, HID, m->w_qky, 0, f16, st));
+  PK(pack_linear(w->key_w, HID, HID, m->w_qky, HID, f16, st));
+  PK(pack_linear(w->out_w, HID, HID, m->w_qky, 2 * HID, f16, st));
+  PK(pack_linear(w->pos_fc1_w, HID, HID, m->w_fc1, 0, f16, st));
+  PK(pack_linear(w->pos_fc2_w, ECHR_HEADS, HID, m->w_fc2, 0, f16, st));
+  PK(pack_linear(w->ctx2att_w, HID, ECHR_VIDEO_DIM, m->w_ctx2att, 0, f16, st));
+  PK(pack_linear(w->h2att_w, HID, HID, m->w_h2att, 0, f16, st));
+  PK(pack_linear(w->logit_w, m->V1, 3 * HID, m->w_logit, 0, f16, st));
+  PK(pack_linear(w->embed_w, m->V1, HID, m->embed, 0, f16, st));
   const int ctx[3] = {HID, ECHR_VIDEO_DIM, ECHR_LDA_DIM};
   const int ctx_pad[3] = {HID, CLIP_PAD, VID_PAD};
   for (int l = 0; l < 3; ++l) {
     pack_lstm_kernel<<<148 * 8, 256, 0, st>>>(w->lstm_w_ih[l], w->lstm_w_hh[l], ctx[l], ctx_pad[l],
                                               m->w_lstm[l].plane(0),
-                                              m->w_lstm[l].planes > 1 ? m->w_lstm[l].plane(1) : nullptr);
+                                              m->w_lstm[l].planes > 1 ? m->w_lstm[l].plane(1) : nullptr, f16);
     PK(cudaGetLastError());
     pack_lstm_bias_kernel<<<GATES / 256, 256, 0, st>>>(w->lstm_b_ih[l], w->lstm_b_hh[l], m->b_lstm[l]);
     PK(cudaGetLastError());
@@ -372,15 +377,15 @@ extern "C" int echr_model_create(const echr_config_t* config, const echr_weights
   PK(copy_vec(w->logit_b, m->b_logit, m->V1, st));
   PK(copy_vec(w->out_b, m->b_out, HID, st));
   PK(copy_vec(w->alpha_w, m->alpha, HID, st));
-  // token -> gate tables (see engine.cuh): embed [V1,512] (hi+lo planes) x the x block of each stream's
-  // packed weights, fp32-grade products whatever the run-time precision
+  // token -> gate tables (see engine.cuh): embed [V1,512] (hi+lo planes; one fp16 plane in the single-plane
+  // precision) x the x block of each stream's packed weights
   for (int l = 0; l < 3; ++l) {
     PlaneMat wx = m->w_lstm[l];  // columns 0..511 of [x | h | ctx]
     GemmSpec s;
     s.A = &m->embed; s.M = m->V1; s.W = &wx; s.N = GATES; s.K = HID;
     s.bias = m->b_lstm[l];  // b_ih + b_hh ride in the table for every stream
     s.out_f32 = m->tok_gates[l]; s.ld_f32 = GATES;
-    const int rc = run_gemm(&s, 1, 2, m->cfg.w_terms, 128, EPI_STORE, 1, st, "token_gate_table");
+    const int rc = run_gemm(&s, 1, f16 ? 1 : 2, m->cfg.w_terms, 128, EPI_STORE, 1, st, "token_gate_table");
     if (rc != ECHR_OK) {
       cudaStreamSynchronize(st);
       cudaFree(m->arena);
@@ -714,7 +719,7 @@ static int encode_clips(echr_batch_t* b, cudaStream_t st) {
   const echr_model* m = b->model;
   const int at = m->cfg.a_terms, wt = m->cfg.w_terms;
   ECHR_CUDA(launch_split(b->c3d, b->n_clips, ECHR_VIDEO_DIM, ECHR_VIDEO_DIM, b->clip_pl.plane(0),
-                         at > 1 ? b->clip_pl.plane(1) : nullptr, CLIP_PAD, CLIP_PAD, st));
+                         at > 1 ? b->clip_pl.plane(1) : nullptr, CLIP_PAD, CLIP_PAD, at == 1, st));
   GemmSpec s;
   s.A = &b->clip_pl; s.M = b->n_clips; s.W = &m->w_ctx2att; s.N = HID; s.K = CLIP_PAD;
   s.bias = m->b_ctx2att;
@@ -827,7 +832,7 @@ extern "C" int echr_relation_encode(echr_batch_t* b, const float* feats, const i
   echr_batch_desc_t d = {1, n, offs, ev_video.data(), ev_s.data(), ev_e.data(), ev_ind.data()};
   ECHR_TRY(stage_desc(b, &d, false, st));
   ECHR_CUDA(launch_split(feats, n, ECHR_VIDEO_DIM + HID, ECHR_VIDEO_DIM + HID, b->feat_pl.plane(0),
-                         b->feat_pl.planes > 1 ? b->feat_pl.plane(1) : nullptr, FEAT_PAD, FEAT_PAD, st));
+                         b->feat_pl.planes > 1 ? b->feat_pl.plane(1) : nullptr, FEAT_PAD, FEAT_PAD, b->feat_pl.planes == 1, st));
   ECHR_TRY(encode_relation(b, st));
   ECHR_CUDA(cudaMemcpyAsync(out, b->event_ctx, sizeof(float) * (size_t)n * HID, cudaMemcpyDeviceToDevice, st));
   return ECHR_OK;

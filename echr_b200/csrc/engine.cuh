@@ -143,7 +143,7 @@ namespace echr {
 
 // ---- kernels_ctx.cu
 cudaError_t launch_split(const float* src, int64_t rows, int64_t cols, int64_t ld_src, bf16* hi,
-                         bf16* lo, int64_t ld_dst, int64_t cols_dst, cudaStream_t st);
+                         bf16* lo, int64_t ld_dst, int64_t cols_dst, bool f16, cudaStream_t st);
 cudaError_t launch_event_feats(const echr_batch* b, cudaStream_t st);
 cudaError_t launch_gather_tap(const echr_batch* b, const float* tap_src, cudaStream_t st);
 cudaError_t launch_posemb(const echr_batch* b, cudaStream_t st);

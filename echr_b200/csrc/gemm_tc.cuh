@@ -127,9 +127,10 @@ __device__ __forceinline__ float tanh_fast_acc(float x) {
   return 1.0f - __fdividef(2.0f, __expf(2.0f * x) + 1.0f);
 }
 
-// store 32 consecutive values of one row as bf16 hi (and lo) planes
+// store 32 consecutive values of one row as bf16 hi+lo planes, or as one fp16 plane when ol is null
 __device__ __forceinline__ void store_planes32(const float* v, __nv_bfloat16* oh, __nv_bfloat16* ol,
                                                int valid) {
+  const bool single = ol == nullptr;
   if (valid >= 32 && ((reinterpret_cast<uintptr_t>(oh) & 15) == 0) &&
       (ol == nullptr || (reinterpret_cast<uintptr_t>(ol) & 15) == 0)) {
 #pragma unroll
@@ -137,7 +138,7 @@ __device__ __forceinline__ void store_planes32(const float* v, __nv_bfloat16* oh
       __align__(16) __nv_bfloat16 h[8];
       __align__(16) __nv_bfloat16 l[8];
 #pragma unroll
-      for (int i = 0; i < 8; ++i) split_bf16(v[8 * g + i], h[i], l[i]);
+      for (int i = 0; i < 8; ++i) split16(v[8 * g + i], single, h[i], l[i]);
       *reinterpret_cast<uint4*>(oh + 8 * g) = *reinterpret_cast<const uint4*>(h);
       if (ol != nullptr) *reinterpret_cast<uint4*>(ol + 8 * g) = *reinterpret_cast<const uint4*>(l);
     }
@@ -145,7 +146,7 @@ __device__ __forceinline__ void store_planes32(const float* v, __nv_bfloat16* oh
     for (int i = 0; i < 32; ++i) {
       if (i < valid) {
         __nv_bfloat16 h, l;
-        split_bf16(v[i], h, l);
+        split16(v[i], single, h, l);
         oh[i] = h;
         if (ol != nullptr) ol[i] = l;
       }
@@ -255,7 +256,7 @@ gemm_tc_kernel(const __grid_constant__ GemmParams P) {
   } else if (warp == 1) {
     // ===================== MMA issuer (single thread) =====================
     if (lane == 0) {
-      constexpr uint32_t idesc = umma_idesc_bf16_m128(BLOCK_N);
+      constexpr uint32_t idesc = umma_idesc_m128(BLOCK_N, A_TERMS > 1);
       int stage = 0;
       uint32_t phase = 0;
       uint32_t accum = 0;
@@ -272,15 +273,15 @@ gemm_tc_kernel(const __grid_constant__ GemmParams P) {
 #pragma unroll
         for (int k = 0; k < GEMM_BLOCK_K / 16; ++k) {
           const uint64_t koff = static_cast<uint64_t>(k * 2);  // 32 B per K=16 step, >>4
-          umma_bf16(tmem_base, a_hi + koff, w_hi + koff, idesc, accum);
+          umma_f16(tmem_base, a_hi + koff, w_hi + koff, idesc, accum);
           accum = 1;
           if (A_TERMS == 2 && !hi_only) {
             const uint64_t a_lo = umma_desc_k_sw128(sa + Cfg::A_PLANE_BYTES);
-            umma_bf16(tmem_base, a_lo + koff, w_hi + koff, idesc, 1);
+            umma_f16(tmem_base, a_lo + koff, w_hi + koff, idesc, 1);
           }
           if (W_TERMS == 2) {
             const uint64_t w_lo = umma_desc_k_sw128(sw + Cfg::W_PLANE_BYTES);
-            umma_bf16(tmem_base, a_hi + koff, w_lo + koff, idesc, 1);
+            umma_f16(tmem_base, a_hi + koff, w_lo + koff, idesc, 1);
           }
         }
         umma_commit(empty_bar(stage));  // frees the smem slot when these MMAs retire
@@ -441,7 +442,7 @@ gemm_tc_kernel(const __grid_constant__ GemmParams P) {
                 for (int i = 0; i < CH; ++i)
                   if (i < valid) {
                     __nv_bfloat16 h, l;
-                    split_bf16(v[i], h, l);
+                    split16(v[i], ol == nullptr, h, l);
                     oh[i] = h;
                     if (ol) ol[i] = l;
                   }
@@ -478,7 +479,7 @@ gemm_tc_kernel(const __grid_constant__ GemmParams P) {
               const float go = sigmoid_fast(v[4 * u + 3] + b.w);
               const float cc = gf * cprev[8 * c + u] + gi * gg;
               cn[u] = cc;
-              split_bf16(go * tanh_fast_acc(cc), hh[u], hl[u]);
+              split16(go * tanh_fast_acc(cc), pb.out_lo == nullptr, hh[u], hl[u]);
             }
             float4* co = reinterpret_cast<float4*>(pb.c_out + static_cast<long long>(row) * H + j0);
             co[0] = make_float4(cn[0], cn[1], cn[2], cn[3]);

@@ -130,7 +130,7 @@ gemm_tc2_kernel(const __grid_constant__ GemmParams P, int groups, int total_tile
   } else if (warp == 1) {
     // ===================== MMA issuer (single thread) =====================
     if (lane == 0) {
-      constexpr uint32_t idesc = umma_idesc_bf16_m128(BN);
+      constexpr uint32_t idesc = umma_idesc_m128(BN, A_TERMS > 1);
       int stage = 0;
       uint32_t phase = 0;
       int it = 0;
@@ -153,15 +153,15 @@ gemm_tc2_kernel(const __grid_constant__ GemmParams P, int groups, int total_tile
 #pragma unroll
           for (int k = 0; k < GEMM_BLOCK_K / 16; ++k) {
             const uint64_t koff = static_cast<uint64_t>(k * 2);
-            umma_bf16(acc, a_hi + koff, w_hi + koff, idesc, accum);
+            umma_f16(acc, a_hi + koff, w_hi + koff, idesc, accum);
             accum = 1;
             if (A_TERMS == 2 && !hi_only) {
               const uint64_t a_lo = umma_desc_k_sw128(sa + Cfg::A_PLANE_BYTES);
-              umma_bf16(acc, a_lo + koff, w_hi + koff, idesc, 1);
+              umma_f16(acc, a_lo + koff, w_hi + koff, idesc, 1);
             }
             if (W_TERMS == 2) {
               const uint64_t w_lo = umma_desc_k_sw128(sw + Cfg::W_PLANE_BYTES);
-              umma_bf16(acc, a_hi + koff, w_lo + koff, idesc, 1);
+              umma_f16(acc, a_hi + koff, w_lo + koff, idesc, 1);
             }
           }
           umma_commit(empty_bar(stage));
@@ -301,7 +301,7 @@ gemm_tc2_kernel(const __grid_constant__ GemmParams P, int groups, int total_tile
               const float go = sigmoid_fast(v[4 * u + 3] + b3);
               const float cc = gf * cp[u] + gi * gg;
               cn[u] = cc;
-              split_bf16(go * tanh_fast_acc(cc), hh[u], hl[u]);
+              split16(go * tanh_fast_acc(cc), pb.out_lo == nullptr, hh[u], hl[u]);
             }
             stg_f32x8(pb.c_out + static_cast<long long>(row) * pb.hidden + j0, cn);
             *reinterpret_cast<uint4*>(pb.out_hi + static_cast<long long>(row) * pb.ld_bf + j0) =

@@ -1,5 +1,5 @@
 // Context prologue and event relation encoder kernels (everything that runs once per batch):
-//   split_planes        fp32 -> bf16 hi/lo planes (tensor-core operand staging)
+//   split_planes        fp32 -> bf16 hi/lo planes, or one fp16 plane (tensor-core operand staging)
 //   event_feats         mean-pooled clip feature | proposal state per event (CaptionGenerator.py:106-127)
 //   posemb              pairwise temporal position embedding (MA_attention_8_NEW.py:51-79), fp64 math
 //   relation_attn       multi-head relation attention with the pair weights (MA:122-175)
@@ -11,14 +11,14 @@ namespace echr {
 
 __global__ void split_planes_kernel(const float* __restrict__ src, long long rows, long long cols,
                                     long long ld_src, bf16* __restrict__ hi, bf16* __restrict__ lo,
-                                    long long ld_dst, long long cols_dst) {
+                                    long long ld_dst, long long cols_dst, bool f16) {
   const long long total = rows * cols_dst;
   for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
        i += (long long)gridDim.x * blockDim.x) {
     const long long r = i / cols_dst, c = i - r * cols_dst;
     const float x = (c < cols) ? src[r * ld_src + c] : 0.f;
     bf16 h, l;
-    split_bf16(x, h, l);
+    split16(x, f16, h, l);
     hi[r * ld_dst + c] = h;
     if (lo != nullptr) lo[r * ld_dst + c] = l;
   }
@@ -27,7 +27,7 @@ __global__ void split_planes_kernel(const float* __restrict__ src, long long row
 // 4 columns per thread: one 16-byte load, one 8-byte store per plane (rows of 4k columns, 16-byte aligned)
 __global__ void split_planes_vec4_kernel(const float* __restrict__ src, long long rows, int cols, long long ld_src,
                                          bf16* __restrict__ hi, bf16* __restrict__ lo, long long ld_dst,
-                                         int cols_dst) {
+                                         int cols_dst, bool f16) {
   const int q_per_row = cols_dst >> 2;
   const long long total = rows * q_per_row;
   for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
@@ -37,16 +37,18 @@ __global__ void split_planes_vec4_kernel(const float* __restrict__ src, long lon
     float4 x = make_float4(0.f, 0.f, 0.f, 0.f);
     if (c < cols) x = __ldg(reinterpret_cast<const float4*>(src + r * ld_src + c));
     __align__(8) bf16 h[4], l[4];
-    split_bf16(x.x, h[0], l[0]); split_bf16(x.y, h[1], l[1]);
-    split_bf16(x.z, h[2], l[2]); split_bf16(x.w, h[3], l[3]);
+    split16(x.x, f16, h[0], l[0]); split16(x.y, f16, h[1], l[1]);
+    split16(x.z, f16, h[2], l[2]); split16(x.w, f16, h[3], l[3]);
     *reinterpret_cast<uint2*>(hi + r * ld_dst + c) = *reinterpret_cast<const uint2*>(h);
     if (lo != nullptr) *reinterpret_cast<uint2*>(lo + r * ld_dst + c) = *reinterpret_cast<const uint2*>(l);
   }
 }
 
+// f16: write one fp16 plane (lo must be null) instead of bf16 hi (+ lo)
 cudaError_t launch_split(const float* src, int64_t rows, int64_t cols, int64_t ld_src, bf16* hi,
-                         bf16* lo, int64_t ld_dst, int64_t cols_dst, cudaStream_t st) {
+                         bf16* lo, int64_t ld_dst, int64_t cols_dst, bool f16, cudaStream_t st) {
   if (rows == 0 || cols_dst == 0) return cudaSuccess;
+  if (f16 && lo != nullptr) return cudaErrorInvalidValue;
   const bool vec = (cols % 4 == 0) && (ld_src % 4 == 0) && (cols_dst % 4 == 0) && (ld_dst % 4 == 0) &&
                    ((reinterpret_cast<uintptr_t>(src) & 15) == 0) && ((reinterpret_cast<uintptr_t>(hi) & 7) == 0) &&
                    (lo == nullptr || (reinterpret_cast<uintptr_t>(lo) & 7) == 0);
@@ -54,14 +56,14 @@ cudaError_t launch_split(const float* src, int64_t rows, int64_t cols, int64_t l
     const long long total = rows * (cols_dst / 4);
     long long blocks = (total + 255) / 256;
     if (blocks > 148 * 16) blocks = 148 * 16;
-    split_planes_vec4_kernel<<<(int)blocks, 256, 0, st>>>(src, rows, (int)cols, ld_src, hi, lo, ld_dst, (int)cols_dst);
+    split_planes_vec4_kernel<<<(int)blocks, 256, 0, st>>>(src, rows, (int)cols, ld_src, hi, lo, ld_dst, (int)cols_dst, f16);
     count_launch();
     return cudaGetLastError();
   }
   const long long total = rows * cols_dst;
   long long blocks = (total + 255) / 256;
   if (blocks > 148 * 16) blocks = 148 * 16;
-  split_planes_kernel<<<(int)blocks, 256, 0, st>>>(src, rows, cols, ld_src, hi, lo, ld_dst, cols_dst);
+  split_planes_kernel<<<(int)blocks, 256, 0, st>>>(src, rows, cols, ld_src, hi, lo, ld_dst, cols_dst, f16);
   count_launch();
   return cudaGetLastError();
 }
@@ -100,7 +102,7 @@ event_feats_kernel(const float* __restrict__ c3d, const float* __restrict__ tap,
     }
     __align__(8) bf16 h[4], l2[4];
 #pragma unroll
-    for (int i = 0; i < 4; ++i) split_bf16(v[i], h[i], l2[i]);
+    for (int i = 0; i < 4; ++i) split16(v[i], lo == nullptr, h[i], l2[i]);
     *reinterpret_cast<uint2*>(hi + (long long)e * FEAT_PAD + c0) = *reinterpret_cast<const uint2*>(h);
     if (lo != nullptr) *reinterpret_cast<uint2*>(lo + (long long)e * FEAT_PAD + c0) = *reinterpret_cast<const uint2*>(l2);
   }
@@ -170,8 +172,8 @@ posemb_kernel(const int32_t* __restrict__ ev_start, const int32_t* __restrict__ 
     double sn, cs;
     sincos(z, &sn, &cs);
     bf16 sh, sl, ch, cl;
-    split_bf16((float)sn, sh, sl);
-    split_bf16((float)cs, ch, cl);
+    split16((float)sn, lo == nullptr, sh, sl);
+    split16((float)cs, lo == nullptr, ch, cl);
     const long long base = (row0 + j) * HID + which * 256 + k;
     hi[base] = sh;
     hi[base + 128] = ch;

@@ -157,7 +157,7 @@ attention_kernel(const float* __restrict__ q, const void* __restrict__ proj_v,
     if (out_f32 != nullptr) out_f32[(long long)r * ECHR_VIDEO_DIM + c] = v;
     if (out_hi != nullptr) {
       bf16 h, l2;
-      split_bf16(v, h, l2);
+      split16(v, out_lo == nullptr, h, l2);
       out_hi[(long long)r * ld_bf + c] = h;
       if (out_lo != nullptr) out_lo[(long long)r * ld_bf + c] = l2;
     }
@@ -300,7 +300,7 @@ attention_staged_kernel(const float* __restrict__ q, const void* __restrict__ pr
     if (out_f32 != nullptr) out_f32[(long long)r * ECHR_VIDEO_DIM + c] = v;
     if (out_hi != nullptr) {
       bf16 h, l2;
-      split_bf16(v, h, l2);
+      split16(v, out_lo == nullptr, h, l2);
       out_hi[(long long)r * ld_bf + c] = h;
       if (out_lo != nullptr) out_lo[(long long)r * ld_bf + c] = l2;
     }
@@ -458,7 +458,7 @@ attention_v2_kernel(const float* __restrict__ q, const void* __restrict__ proj_v
     if (out_f32 != nullptr) out_f32[(long long)r * ECHR_VIDEO_DIM + c] = v;
     if (out_hi != nullptr) {
       bf16 h, l2;
-      split_bf16(v, h, l2);
+      split16(v, out_lo == nullptr, h, l2);
       out_hi[(long long)r * ld_bf + c] = h;
       if (out_lo != nullptr) out_lo[(long long)r * ld_bf + c] = l2;
     }
@@ -586,7 +586,7 @@ decode_init_kernel(int beam, int a_planes, const float* __restrict__ event_ctx,
       col = ACT_VID + d;
     }
     bf16 h, l;
-    split_bf16(x, h, l);
+    split16(x, a_planes == 1, h, l);
 #pragma unroll
     for (int b = 0; b < 2; ++b) {
       rows[b][col] = h;
@@ -747,7 +747,7 @@ load_state_kernel(int rows, int V1, const int32_t* __restrict__ it, const float*
   for (int c = threadIdx.x; c < 3 * HID; c += blockDim.x) {
     const int l = c / HID, u = c - l * HID;
     bf16 h, lo;
-    split_bf16(h_in[((long long)l * rows + r) * HID + u], h, lo);
+    split16(h_in[((long long)l * rows + r) * HID + u], planes == 1, h, lo);
     row[ACT_H + c] = h;
     if (planes > 1) row[act_plane + ACT_H + c] = lo;
   }
@@ -761,8 +761,8 @@ export_state_kernel(int rows, const bf16* __restrict__ act, long long act_plane,
   const bf16* row = act + (long long)r * ACT_LD;
   for (int c = threadIdx.x; c < 3 * HID; c += blockDim.x) {
     const int l = c / HID, u = c - l * HID;
-    float v = __bfloat162float(row[ACT_H + c]);
-    if (planes > 1) v += __bfloat162float(row[act_plane + ACT_H + c]);
+    float v = planes > 1 ? __bfloat162float(row[ACT_H + c]) + __bfloat162float(row[act_plane + ACT_H + c])
+                         : f16_value(row[ACT_H + c]);
     h_out[((long long)l * rows + r) * HID + u] = v;
   }
 }

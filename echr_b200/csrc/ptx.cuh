@@ -4,6 +4,7 @@
 #pragma once
 #include <cuda_runtime.h>
 #include <cuda_bf16.h>
+#include <cuda_fp16.h>
 #include <stdint.h>
 #include <stdio.h>
 
@@ -175,12 +176,13 @@ __device__ __forceinline__ uint64_t umma_desc_k_sw128(uint32_t smem_addr) {
   d |= static_cast<uint64_t>(2) << 61;                     // layout type SWIZZLE_128B
   return d;
 }
-// Instruction descriptor: bf16 x bf16 -> f32, both operands K-major, M=128.
-__host__ __device__ constexpr uint32_t umma_idesc_bf16_m128(int n) {
-  return (1u << 4) | (1u << 7) | (1u << 10) | (static_cast<uint32_t>(n >> 3) << 17) |
+// Instruction descriptor of kind::f16: 16-bit x 16-bit -> f32, both operands K-major, M=128.
+// Operand format field: 1 = bf16 (the hi/lo planes), 0 = fp16 (single-plane storage).
+__host__ __device__ constexpr uint32_t umma_idesc_m128(int n, bool bf) {
+  return (1u << 4) | ((bf ? 1u : 0u) << 7) | ((bf ? 1u : 0u) << 10) | (static_cast<uint32_t>(n >> 3) << 17) |
          (static_cast<uint32_t>(128 >> 4) << 24);
 }
-__device__ __forceinline__ void umma_bf16(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc,
+__device__ __forceinline__ void umma_f16(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc,
                                           uint32_t idesc, uint32_t accumulate) {
   asm volatile(
       "{\n\t.reg .pred p;\n\t"
@@ -241,11 +243,28 @@ __device__ __forceinline__ void stg_f32x8(float* p, const float* v) {
 }
 
 // ---------------------------------------------------------------- misc math helpers
-// Split an fp32 value into a bf16 "hi" (round-to-nearest) and the bf16 of the remainder; hi+lo
-// carries 16 mantissa bits, which is what the two-term tensor-core products consume.
-__device__ __forceinline__ void split_bf16(float x, __nv_bfloat16& hi, __nv_bfloat16& lo) {
-  hi = __float2bfloat16_rn(x);
-  lo = __float2bfloat16_rn(x - __bfloat162float(hi));
+// Operand storage for the tensor-core products.  Two planes: bf16 "hi" (round-to-nearest) and the bf16 of
+// the remainder, hi+lo carries 16 mantissa bits (the two-/three-term products).  One plane (`single`):
+// IEEE fp16 (11 mantissa bits, saturated to the fp16 range) in the same 16-bit container.
+__device__ __forceinline__ __nv_bfloat16 f16_bits(float x) {
+  const __half h = __float2half_rn(fminf(fmaxf(x, -65504.0f), 65504.0f));
+  return __ushort_as_bfloat16(__half_as_ushort(h));
+}
+__device__ __forceinline__ float f16_value(__nv_bfloat16 b) {
+  return __half2float(__ushort_as_half(__bfloat16_as_ushort(b)));
+}
+__device__ __forceinline__ void split16(float x, bool single, __nv_bfloat16& hi, __nv_bfloat16& lo) {
+  if (single) {
+    hi = f16_bits(x);
+    lo = hi;
+  } else {
+    hi = __float2bfloat16_rn(x);
+    lo = __float2bfloat16_rn(x - __bfloat162float(hi));
+  }
+}
+// two packed 16-bit operand values -> float2 (single-plane storage = fp16)
+__device__ __forceinline__ float2 f16x2_value(uint32_t u) {
+  return __half22float2(*reinterpret_cast<const __half2*>(&u));
 }
 __device__ __forceinline__ float sigmoid_acc(float x) { return 1.0f / (1.0f + expf(-x)); }
 

@@ -17,8 +17,10 @@ PRECISIONS = {
     "fp32": (2, 2, 0),
     # weights rounded to bf16 (exact when the checkpoint is bf16-representable), activations hi+lo
     "bf16w": (2, 1, 0),
-    # everything single-plane bf16, attention reads bf16 clip features / projections
-    "bf16": (1, 1, 1),
+    # every operand (activations and weights) as ONE fp16 plane: a single tensor-core product per k-step.
+    # 11 mantissa bits, and a bf16-representable checkpoint is fp16-exact (|w| in [6.1e-5, 65504]); state,
+    # accumulators, softmax and the attention inputs stay fp32
+    "f16": (1, 1, 0),
 }
 
 

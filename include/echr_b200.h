@@ -42,9 +42,11 @@ typedef struct echr_batch echr_batch_t;
 typedef struct echr_config {
   int32_t vocab_size; /* CG_vocab_size; the logit/embedding tables have vocab_size+1 rows        */
   int32_t seq_length; /* CG_seq_length (30)                                                       */
-  int32_t a_terms;    /* 1: activations as one bf16 plane, 2: bf16 hi+lo planes (fp32-grade)      */
-  int32_t w_terms;    /* 1: weights rounded to bf16,        2: bf16 hi+lo planes (fp32-grade)     */
-  int32_t clip_bf16;  /* 1: the step attention reads bf16 clip features/projections, 0: fp32      */
+  int32_t a_terms;    /* 2: activations as bf16 hi+lo planes (fp32-grade); 1: one fp16 plane, and then   */
+                      /*    the weights are fp16 too (one tcgen05 product per k-step)                 */
+  int32_t w_terms;    /* 1: weights rounded to bf16 (fp16 when a_terms == 1), 2: bf16 hi+lo planes      */
+  int32_t clip_bf16;  /* must be 0 (the step attention reads fp32 clip features and projections; the     */
+                      /*    16-bit table was retired with the fp16 single-plane format)                  */
 } echr_config_t;
 
 /* fp32 device pointers into the reference checkpoint's `cg_model` state_dict (train.py:456-461;
@@ -106,13 +108,18 @@ ECHR_API int echr_device_check(int device);
  * zero-padded to cols_dst columns, row stride ld_dst. */
 ECHR_API int echr_split_bf16(const float* src, int64_t rows, int64_t cols, int64_t ld_src, void* hi, void* lo,
                     int64_t ld_dst, int64_t cols_dst, void* stream);
+/* fp32 [rows, cols] -> ONE IEEE fp16 plane (saturated to +-65504), zero-padded like the above.  This is the
+ * operand format of the single-plane products (a_planes == 1 in echr_gemm, a_terms == 1 in echr_config_t). */
+ECHR_API int echr_split_f16(const float* src, int64_t rows, int64_t cols, int64_t ld_src, void* dst, int64_t ld_dst,
+                   int64_t cols_dst, void* stream);
 
 /* out[m, n] = act( A[m, k] * W[n, k]^T + bias[n] ) on the tcgen05 tensor cores.
  * Replaces every nn.Linear on the path (models/MA_attention_8_NEW.py:29,93-96;
- * models/OldModel_NEW.py:51,372-374).  A and W are bf16 plane stacks ([planes][rows][ld]):
- * planes=1 is the plain bf16 operand, planes=2 adds the low-order plane (fp32-grade product).
+ * models/OldModel_NEW.py:51,372-374).  A and W are 16-bit plane stacks ([planes][rows][ld]):
+ * a_planes=2 is bf16 hi+lo (echr_split_bf16; W then bf16 with 1 or 2 planes, fp32-grade product);
+ * a_planes=1 is ONE fp16 plane for A and for W (echr_split_f16; w_planes must be 1).
  * k must be a multiple of 64 (pad with zeros), k <= 2048.  act: 0 none, 1 tanh, 2 exp(2*clamp(x,+-40)).
- * Outputs: out_f32 (may be NULL) and/or bf16 planes out_hi/out_lo (may be NULL).
+ * Outputs: out_f32 (may be NULL) and/or planes out_hi/out_lo (out_hi alone = one fp16 plane, both = bf16 hi+lo).
  * block_n: 128, 64, 32 or 16 = one 128 x block_n tile per CTA; 256 = the persistent 128 x 256 kernel with
  * double-buffered TMEM accumulators the engine uses from 1024 rows up. */
 ECHR_API int echr_gemm_planes(const void* a, int64_t m, int64_t k, int64_t a_ld, int a_planes,
@@ -128,7 +135,8 @@ ECHR_API int echr_gemm_planes(const void* a, int64_t m, int64_t k, int64_t a_ld,
  * proj_exp [n_clips,512] = e^{2P} and q_exp [rows,512] = e^{2q}, exponents clamped to +-80; with them
  * tanh(P+q) = 1 - 2/(e^{2P} e^{2q} + 1) costs one reciprocal per element.
  * proj_exp and clip [n_clips, ld_clip] are fp32 (clip_bf16=0) or bf16 (clip_bf16=1); q_exp fp32;
- * out_f32 [rows,500] (may be NULL); out_hi/out_lo bf16 [rows, ld_bf] (may be NULL).
+ * out_f32 [rows,500] (may be NULL); out_hi/out_lo [rows, ld_bf] (may be NULL; out_hi alone = one fp16 plane,
+ * both = bf16 hi+lo).
  * max_len: the largest row_len of the call if the caller knows it (lets small launches stage whole
  * windows in shared memory through the bulk-copy engine), 0 if unknown. */
 ECHR_API int echr_attention_step(const float* q_exp, const void* proj_exp, const void* clip, int64_t ld_clip,

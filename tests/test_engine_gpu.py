@@ -15,7 +15,7 @@ from oracle import echr_oracle as O
 pytestmark = pytest.mark.gpu
 torch.set_grad_enabled(False)
 DEV = "cuda:0"
-LOGIT_TOL = {"fp32": 1e-4, "bf16w": 1e-4, "bf16": 2e-2}
+LOGIT_TOL = {"fp32": 1e-4, "bf16w": 1e-4, "f16": 2e-3}
 _models = {}
 
 
@@ -57,19 +57,27 @@ def test_golden_greedy_and_logits(name, precision, kind):
         assert np.abs(logp.cpu().numpy() - g["logp"]).max() < LOGIT_TOL[precision]
 
 
-@pytest.mark.parametrize("name", ["cfg1", "sst12"])
-def test_golden_bf16_logits(name):
-    """Plain bf16 mode: per-step log-probs within 2e-2 of the reference on the same (bf16-rounded)
-    weights and features; tokens are compared with the near-tie rule only up to the first divergence."""
+@pytest.mark.parametrize("name", ["cfg1", "gt5", "sst12", "long30"])
+def test_golden_f16(name):
+    """Single-plane fp16 precision (one tensor-core product): greedy tokens equal the reference's except at
+    near ties (top-2 gap < 1e-3, BASELINE north_star), teacher-forced log-probs within 2e-3 (allowed: 2e-2) of
+    the reference on the same bf16-rounded weights and features."""
     g, v = helpers.golden(name, "bf16w"), helpers.case_video(name, "bf16w")
-    m = model("bf16", "bf16w")
+    m = model("f16", "bf16w")
     vt = helpers.video_tuple(v, DEV)
+    seq, logp = m(vt[0], vt[1], vt[2], [], vt[3], vt[4], mode="eval")
+    excused = helpers.check_tokens(seq.cpu().numpy(), g["seq"], g["tf_top2"], name)
+    ev = m.engine.event_context().cpu().numpy()
+    assert np.abs(ev - g["event"]).max() < 2e-3, np.abs(ev - g["event"]).max()
     tf = m(vt[0], vt[1], vt[2], labels_of(g["seq"]).to(DEV), vt[3], vt[4], mode="train").cpu()
     steps = list(g["tf_steps"])
     ne = g["tf_logprobs"].shape[0]
     err = np.abs(tf[:ne][:, steps].numpy() - g["tf_logprobs"]).max()
-    print("bf16 teacher-forced max |dlogp| =", err)
-    assert err < 2e-2
+    print("f16 teacher-forced max |dlogp| = %.2e, event ctx %.2e, excused tokens %d"
+          % (err, np.abs(ev - g["event"]).max(), excused))
+    assert err < LOGIT_TOL["f16"]
+    if excused == 0:
+        assert np.abs(logp.cpu().numpy() - g["logp"]).max() < LOGIT_TOL["f16"]
 
 
 # ----------------------------------------------------------------------------- oracle, batched

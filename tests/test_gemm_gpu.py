@@ -17,6 +17,15 @@ def _split(x, cols_dst):
     return hi, lo
 
 
+def _split_f16(x, cols_dst):
+    lib = _lib.load()
+    rows, cols = x.shape
+    out = torch.empty(rows, cols_dst, dtype=torch.float16, device=x.device)
+    _lib.check(lib.echr_split_f16(x.data_ptr(), rows, cols, x.stride(0), out.data_ptr(), cols_dst, cols_dst,
+                                  torch.cuda.current_stream().cuda_stream), "split_f16")
+    return out
+
+
 def _gemm(a_planes, w_planes, m, n, k, bias, act, block_n, want_bf=False):
     lib = _lib.load()
     dev = a_planes.device
@@ -48,13 +57,18 @@ def test_gemm_planes(m, n, k, block_n, terms):
     a = torch.randn(m, k, device=dev)
     w = torch.randn(n, k, device=dev) * 0.05
     bias = torch.randn(n, device=dev)
-    ah, al = _split(a, k)
-    wh, wl = _split(w, k)
     at, wt = terms
+    if at == 1:  # single-plane operands are fp16 (echr_split_f16), A and W alike
+        ah, wh = _split_f16(a, k), _split_f16(w, k)
+        assert torch.equal(ah, a.half()) and torch.equal(wh, w.half())
+        al, wl = ah, wh
+    else:
+        ah, al = _split(a, k)
+        wh, wl = _split(w, k)
     a_pl = torch.stack([ah, al])[:at].contiguous()
     w_pl = torch.stack([wh, wl])[:wt].contiguous()
     out, _, _ = _gemm(a_pl, w_pl, m, n, k, bias, 0, block_n)
-    # exact model of what the kernel computes (products of bf16 values are exact in fp32; only the
+    # exact model of what the kernel computes (products of bf16 / fp16 values are exact in fp32; only the
     # accumulation order differs), evaluated in fp64
     A = [ah.double(), al.double()]
     W = [wh.double(), wl.double()]
@@ -87,3 +101,27 @@ def test_gemm_tanh_and_bf16_out():
     assert (out.double() - ref).abs().max().item() < 1e-4
     rec = oh.double() + ol.double()
     assert (rec - out.double()).abs().max().item() < 1e-5
+
+
+@pytest.mark.parametrize("block_n", [128, 256])
+def test_gemm_f16_single_plane_out(block_n):
+    """out_hi without out_lo = one fp16 plane (saturating), the operand format of the single-plane precision."""
+    lib = _lib.load()
+    dev = torch.device("cuda:0")
+    torch.manual_seed(9)
+    m, n, k = 1300, 512, 256
+    a = torch.randn(m, k, device=dev)
+    w = torch.randn(n, k, device=dev) * 0.05
+    bias = torch.randn(n, device=dev) * 0.1
+    bias[0] = 1e6  # column 0 overflows fp16: must saturate, not become inf
+    ah, wh = _split_f16(a, k), _split_f16(w, k)
+    out = torch.empty(m, n, device=dev)
+    oh = torch.zeros(m, n, dtype=torch.float16, device=dev)
+    _lib.check(lib.echr_gemm_planes(ah.data_ptr(), m, k, k, 1, 0, wh.data_ptr(), n, k, 1, 0, bias.data_ptr(), 0,
+                                    out.data_ptr(), n, oh.data_ptr(), None, n, block_n,
+                                    torch.cuda.current_stream().cuda_stream), "gemm")
+    torch.cuda.synchronize()
+    ref = ah.double() @ wh.double().T + bias.double()
+    assert (out.double() - ref)[:, 1:].abs().max().item() < 2e-4
+    assert torch.equal(oh[:, 1:], out[:, 1:].half())
+    assert (oh[:, 0] == 65504).all()
