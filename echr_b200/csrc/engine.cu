@@ -1148,22 +1148,31 @@ extern "C" int echr_decode_step(echr_batch_t* b, const int32_t* it, const float*
   return ECHR_OK;
 }
 
+static int caption_host(echr_batch_t* b, const echr_batch_desc_t* desc, const float* host_c3d,
+                        const float* host_tap, const float* host_lda, int beam, int32_t* host_tokens,
+                        float* host_logp, float* host_score, cudaStream_t st, bool sync) {
+  ECHR_REQUIRE(b && host_tokens && host_logp, "echr_caption_host: null argument");
+  ECHR_REQUIRE(beam <= 4, "echr_caption_host: beam must be in 1..4");
+  ECHR_TRY(echr_batch_set_inputs(b, desc, host_c3d, host_tap, host_lda, 1, st));
+  ECHR_TRY(echr_encode(b, st));
+  ECHR_TRY(run_decode(b, beam > 1 ? beam : 1, beam > 1 ? MODE_BEAM : MODE_GREEDY, st));
+  ECHR_TRY(copy_results(b, host_tokens, host_logp, beam > 1 ? host_score : nullptr, cudaMemcpyDeviceToHost, st));
+  if (sync) ECHR_CUDA(cudaStreamSynchronize(st));
+  return ECHR_OK;
+}
+
 extern "C" int echr_caption_host(echr_batch_t* b, const echr_batch_desc_t* desc, const float* host_c3d,
                                  const float* host_tap, const float* host_lda, int beam,
                                  int32_t* host_tokens, float* host_logp, float* host_score, void* stream) {
-  ECHR_REQUIRE(b && host_tokens && host_logp, "echr_caption_host: null argument");
-  cudaStream_t st = (cudaStream_t)stream;
-  ECHR_TRY(echr_batch_set_inputs(b, desc, host_c3d, host_tap, host_lda, 1, st));
-  ECHR_TRY(echr_encode(b, st));
-  if (beam > 1) {
-    ECHR_REQUIRE(beam <= 4, "echr_caption_host: beam must be in 1..4");
-    ECHR_TRY(run_decode(b, beam, MODE_BEAM, st));
-  } else {
-    ECHR_TRY(run_decode(b, 1, MODE_GREEDY, st));
-  }
-  ECHR_TRY(copy_results(b, host_tokens, host_logp, beam > 1 ? host_score : nullptr, cudaMemcpyDeviceToHost, st));
-  ECHR_CUDA(cudaStreamSynchronize(st));
-  return ECHR_OK;
+  return caption_host(b, desc, host_c3d, host_tap, host_lda, beam, host_tokens, host_logp, host_score,
+                      (cudaStream_t)stream, true);
+}
+
+extern "C" int echr_caption_host_async(echr_batch_t* b, const echr_batch_desc_t* desc, const float* host_c3d,
+                                       const float* host_tap, const float* host_lda, int beam,
+                                       int32_t* host_tokens, float* host_logp, float* host_score, void* stream) {
+  return caption_host(b, desc, host_c3d, host_tap, host_lda, beam, host_tokens, host_logp, host_score,
+                      (cudaStream_t)stream, false);
 }
 
 extern "C" int echr_caption_device(echr_batch_t* b, const echr_batch_desc_t* desc, const float* c3d, const float* tap,

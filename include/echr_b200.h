@@ -204,6 +204,12 @@ ECHR_API int echr_teacher_forced(echr_batch_t* batch, const int32_t* seq, int se
 ECHR_API int echr_caption_host(echr_batch_t* batch, const echr_batch_desc_t* desc, const float* host_c3d,
                       const float* host_tap, const float* host_lda, int beam, int32_t* host_tokens,
                       float* host_logp, float* host_score, void* stream);
+/* The same without the final synchronisation: the host buffers (pinned memory, or the copies are not
+ * asynchronous) must stay valid and the outputs unread until `stream` has drained.  With two batches of one
+ * model on two streams, the copies of one batch overlap the decode of the other. */
+ECHR_API int echr_caption_host_async(echr_batch_t* batch, const echr_batch_desc_t* desc, const float* host_c3d,
+                      const float* host_tap, const float* host_lda, int beam, int32_t* host_tokens,
+                      float* host_logp, float* host_score, void* stream);
 
 /* The same call with DEVICE buffers and nothing synchronised: inputs are copied into the workspace
  * (they may be reused as soon as the call returns in stream order), results are written to the device

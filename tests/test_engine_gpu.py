@@ -195,6 +195,43 @@ def test_caption_host_equals_device_path():
     assert torch.equal(tb, tb2) and torch.equal(lb, lb2) and torch.equal(sb, sb2)
 
 
+@pytest.mark.parametrize("depth", [1, 2, 3])
+def test_pipeline_batches_in_flight_equal_single_calls(depth):
+    """CaptionPipeline: batches of different shapes kept in flight on separate lanes (one workspace + stream
+    each, one shared model) return exactly what the blocking single-batch call returns, from host and from
+    device buffers, greedy and beam."""
+    from echr_b200.engine import BatchLayout, CaptionPipeline
+    m = model("bf16w", "bf16w")
+    batches = []
+    for b, nv in enumerate([5, 2, 9, 5, 1, 7]):
+        vids = [synth.make_video(60 + 10 * b + i, bf16_features=True) for i in range(nv)]
+        lay = BatchLayout([v.c3d_feats.shape[0] for v in vids], [v.ind_select_list for v in vids],
+                          [v.soi_select_list for v in vids])
+        host = (torch.cat([v.c3d_feats for v in vids]).pin_memory(), torch.cat([v.tap_feats for v in vids]).pin_memory(),
+                torch.stack([v.lda_feats for v in vids]).pin_memory())
+        batches.append((lay, host, tuple(t.to(DEV) for t in host)))
+    for beam in (1, 3):
+        want = []
+        for lay, host, dev in batches:
+            want.append(tuple(t.clone() for t in m.engine.caption_host(lay, *host, beam=beam)))
+        pipe = CaptionPipeline(m.engine, depth=depth)
+        for rounds in range(2):  # second round replays the lanes' graphs
+            for side in (1, 2):
+                tickets = []
+                for i, bt in enumerate(batches):
+                    tickets.append(pipe.submit(bt[0], *bt[side], beam=beam))
+                    if len(tickets) >= depth:  # consume the oldest before its lane is reused
+                        j = i - depth + 1
+                        got = tickets[j].wait()
+                        for g, w in zip(got, want[j]):
+                            assert torch.equal(g.cpu(), w), (depth, beam, side, j)
+                for j in range(max(0, len(batches) - depth + 1), len(batches)):
+                    got = tickets[j].wait()
+                    for g, w in zip(got, want[j]):
+                        assert torch.equal(g.cpu(), w), (depth, beam, side, j)
+        pipe.close()
+
+
 # ----------------------------------------------------------------------------- sub-module surfaces
 def test_submodule_surfaces_match_oracle():
     """fusion_model.forward, lm_model.sample / forward / get_logprobs_state / init_hidden with the
