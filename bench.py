@@ -89,6 +89,19 @@ class ClockSampler(object):
                 "reasons": reasons, "samples": len(sm)}
 
 
+def nvml_state(index):
+    """One NVML reading of this rank's GPU (diagnosis line on stderr under torchrun)."""
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        h = pynvml.nvmlDeviceGetHandleByIndex(index)
+        return "sm %d MHz, mem %d MHz, %.0f W, event reasons 0x%x" % (
+            pynvml.nvmlDeviceGetClockInfo(h, pynvml.NVML_CLOCK_SM), pynvml.nvmlDeviceGetClockInfo(h, pynvml.NVML_CLOCK_MEM),
+            pynvml.nvmlDeviceGetPowerUsage(h) / 1e3, pynvml.nvmlDeviceGetCurrentClocksEventReasons(h))
+    except Exception as e:  # noqa: BLE001
+        return "nvml unavailable (%s)" % type(e).__name__
+
+
 def cpu_reference_run(vids, sd, beam, reps, warm):
     """The reference algorithm's own work shape on the host cores (oracle port, torch CPU fp32):
     one video per call, looped.  Returns (events/s, seconds per pass)."""
@@ -215,6 +228,8 @@ def _main(args):
     d_c3d, d_tap, d_lda = h_c3d.to(dev), h_tap.to(dev), h_lda.to(dev)
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)  # > 126 MB L2
     counts = exchange_counts(n_events, dev) if world > 1 else None
+    align = torch.zeros(1, device=dev)
+    no_gather = os.environ.get("ECHR_BENCH_NO_GATHER") == "1"  # diagnosis only: the line then says so
 
     # the public call of a captioning job: batches submitted one after the other to a CaptionPipeline, which
     # keeps `--in-flight` of them on the GPU (one workspace + stream per lane, one packed model)
@@ -227,10 +242,10 @@ def _main(args):
         return (gather_tokens(res[0].to(dev, non_blocking=True), counts=counts),) + tuple(res[1:])
 
     def step_device():
-        return pipe.submit(lay, d_c3d, d_tap, d_lda, beam=beam, before=flush.zero_, after=gather if world > 1 else None)
+        return pipe.submit(lay, d_c3d, d_tap, d_lda, beam=beam, before=flush.zero_, after=gather if world > 1 and not no_gather else None)
 
     def step_host():
-        return pipe.submit(lay, h_c3d, h_tap, h_lda, beam=beam, before=flush.zero_, after=gather_host if world > 1 else None)
+        return pipe.submit(lay, h_c3d, h_tap, h_lda, beam=beam, before=flush.zero_, after=gather_host if world > 1 and not no_gather else None)
 
     def timed(fn, steps, warm):
         for _ in range(max(warm, 2 * pipe.depth)):  # every lane sees the shape twice (eager, then captured)
@@ -243,8 +258,17 @@ def _main(args):
         # batch after batch keeps the lanes fed); each step starts with the L2 flush on its lane's stream, so
         # the flush is INSIDE the timed region (it overlaps the other lane's decode when in_flight > 1).
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        if world > 1:  # device-side rendezvous: every rank's start event sits right behind the same all-reduce,
+            dist.all_reduce(align)  # so a rank whose host left the barrier late does not stretch the others' region
         e0.record()
-        tickets = [fn() for _ in range(steps)]
+        tickets, host_us = [], []
+        for _ in range(steps):
+            t0 = time.perf_counter()
+            tickets.append(fn())
+            host_us.append((time.perf_counter() - t0) * 1e6)
+        host_us.sort()
+        sys.stderr.write("[bench rank %d] host time per submit: min %.0f / median %.0f / max %.0f us\n"
+                         % (rank, host_us[0], host_us[len(host_us) // 2], host_us[-1]))
         pipe.drain()
         e1.record()
         torch.cuda.synchronize()
@@ -252,6 +276,7 @@ def _main(args):
             t.wait()
         ms = e0.elapsed_time(e1)
         if world > 1:
+            sys.stderr.write("[bench rank %d] %.4f ms per step on this rank; %s\n" % (rank, ms / steps, nvml_state(local)))
             dist.barrier()
             t = torch.tensor([ms], dtype=torch.float64, device=dev)
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
@@ -259,7 +284,7 @@ def _main(args):
         return ms
 
     sampler = ClockSampler(local)
-    if rank == 0:
+    if rank == 0 and os.environ.get("ECHR_BENCH_NO_SAMPLER") != "1":  # (diagnosis switch; the line then has no clocks)
         sampler.start()
     eng.launch_count(reset=True)
     ms_dev = timed(step_device, args.steps, args.warmup)
@@ -321,6 +346,7 @@ def _main(args):
             "data": "synthetic",
             "config": dict(workload_config(args, w, n_events, world), precision=args.precision,
                            l2_flush_between_steps=True, in_flight=pipe.depth,
+                           **({"DIAGNOSIS_no_token_gather": True} if no_gather and world > 1 else {}),
                            l2_flush="256 MB write at the head of every step, on the step's stream, inside the timed region",
                            ms_per_decode_step=ms_dev / args.steps / S),
             "clocks": clocks,
