@@ -23,6 +23,9 @@ _CTYPES = {
     "int": ctypes.c_int,
     "int64_t": ctypes.c_int64,
     "float": ctypes.c_float,
+    "double": ctypes.c_double,
+    "const double*": ctypes.c_void_p,
+    "const int64_t*": ctypes.c_void_p,
     "void*": ctypes.c_void_p,
     "const void*": ctypes.c_void_p,
     "float*": ctypes.c_void_p,

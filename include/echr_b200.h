@@ -219,6 +219,44 @@ ECHR_API int echr_caption_device(echr_batch_t* batch, const echr_batch_desc_t* d
                         const float* tap, const float* lda, int beam, int32_t* tokens, float* logp,
                         float* score, void* stream);
 
+/* ---- proposal selection between the proposal module and the path ------- */
+/* All pointers are DEVICE pointers unless named host_*.  One CTA per video; the [T,K] score matrix stays in
+ * HBM and only the selected records come out.  Outputs are fixed-capacity slots: video v writes its records
+ * to [v*cap, v*cap + count[v]) of each output array, in the order the reference's lists have.
+ *
+ * gettop1000 (eval_utils.py:263-292).  scores, mask: fp32 [sum_v T_v, K] (mask may be NULL = all ones);
+ * clip_offsets: int32 [n_videos+1].  Per video: p = scores*mask; thr = the topn-th largest p over all T_v*K
+ * cells (the smallest when there are fewer); every cell (n,k) with n >= k and p >= max(thr, val_score_thres)
+ * is emitted in (n,k) row-major order: out_ind = n (index_select_list), [out_start,out_end) = [n-k, n+1)
+ * (featstamp_list), out_conf = p (confidence).  out_count[v] = number found; records past `cap` are dropped. */
+ECHR_API int echr_select_topn(const float* scores, const float* mask, const int32_t* clip_offsets, int n_videos,
+                     int K, int topn, float val_score_thres, int32_t* out_ind, int32_t* out_start,
+                     int32_t* out_end, float* out_conf, int32_t* out_count, int cap, void* stream);
+
+/* gettop1000_nms (eval_utils.py:295-331): greedy 1-D NMS over the proposals (n,k), n in [0,T), k in
+ * [0,min(n,K)), [start,end) = [n-k, n+1), score = scores[n,k]: take the best remaining proposal, drop every
+ * remaining one whose overlap (intersection+1)/(union) with it exceeds `overlap`, until none is left or topn
+ * are taken.  Equal scores: the later proposal in enumeration order first (numpy's unstable argsort leaves
+ * that case open).  Overlaps are evaluated in fp64 in numpy's operation order.
+ * workspace: 8 bytes per proposal of the batch; workspace_offsets: int64 [n_videos] = first proposal of each
+ * video (prefix sums of echr_select_nms_proposals(T_v, K)); total_proposals = their sum.
+ * Outputs per pick, in pick order: out_ind = n (index_select_list), out_start/out_end (nms_props), out_score
+ * (nms_scores), out_pick = the proposal's enumeration index (what indexes prop_gts). */
+ECHR_API int64_t echr_select_nms_proposals(int T, int K);
+ECHR_API int echr_select_nms(const float* scores, const int32_t* clip_offsets, int n_videos, int K, double overlap,
+                    int topn, void* workspace, const int64_t* workspace_offsets, int64_t total_proposals,
+                    int32_t* out_ind, int32_t* out_start, int32_t* out_end, float* out_score,
+                    int32_t* out_pick, int32_t* out_count, int cap, void* stream);
+
+/* gettopN_nms (eval_utils.py:230-260): fp64 t1, t2, prop_scores, sent_scores [sum_v n_v]; offsets int32
+ * [n_videos+1].  While proposals remain (and fewer than topn are picked): i = best remaining by prop_score;
+ * cluster = remaining with overlap(i,.) >= nms_overlap, overlap = (inter+1e-3)/(union); the pick is the cluster
+ * member with the largest sent_score (first in ascending prop_score order on ties); remaining = those with
+ * overlap(i,.) <= nms_overlap.  out_pick: video-local indices in pick order.  workspace: 1 byte per proposal. */
+ECHR_API int echr_rerank_nms(const double* t1, const double* t2, const double* prop_scores,
+                    const double* sent_scores, const int32_t* offsets, int n_videos, double nms_overlap,
+                    int topn, void* workspace, int32_t* out_pick, int32_t* out_count, int cap, void* stream);
+
 /* Measurement aid for bench.py's roofline: average duration in ms of each kernel of one decode step
  * (host_ms[5] = h2att GEMM, fused attention, LSTM gate GEMM, logit GEMM, finalize), from CUDA
  * events on `stream` around a captured graph of `iters` back-to-back plain launches of that kernel
