@@ -44,6 +44,9 @@ _CTYPES = {
     "const echr_weights_t*": ctypes.c_void_p,
     "const echr_capacity_t*": ctypes.c_void_p,
     "const echr_batch_desc_t*": ctypes.c_void_p,
+    "echr_sst_t*": ctypes.c_void_p,
+    "echr_sst_t**": ctypes.c_void_p,
+    "const echr_sst_weights_t*": ctypes.c_void_p,
 }
 
 

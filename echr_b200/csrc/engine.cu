@@ -21,25 +21,6 @@ int trace_next(echr_batch* b, int kind) {
 static std::atomic<long long> g_launches{0};
 void count_launch(int n) { g_launches.fetch_add(n, std::memory_order_relaxed); }
 
-// ---------------------------------------------------------------- arena helper
-struct Arena {
-  size_t off = 0;
-  char* base = nullptr;
-  template <typename T>
-  T* take(size_t n) {
-    off = (off + 255) & ~(size_t)255;
-    T* p = base ? reinterpret_cast<T*>(base + off) : nullptr;
-    off += n * sizeof(T);
-    return p;
-  }
-  PlaneMat planes(int64_t planes_, int64_t rows, int64_t ld) {
-    PlaneMat m;
-    m.rows = rows; m.ld = ld; m.planes = planes_;
-    m.p = take<bf16>((size_t)planes_ * rows * ld);
-    return m;
-  }
-};
-
 // ---------------------------------------------------------------- packing kernels
 // LSTM weights: dst[4j+g, :] = [ w_ih[g*512+j, 0:512] | w_hh[g*512+j, :] | w_ih[g*512+j, 512:512+ctx]
 // (zero padded to ctx_pad) ]  — gate-interleaved rows so that one epilogue thread sees i,f,g,o of a
@@ -82,39 +63,6 @@ static cudaError_t copy_vec(const float* src, float* dst, int n, cudaStream_t st
   copy_f32_kernel<<<(n + 255) / 256, 256, 0, st>>>(src, dst, n);
   return cudaGetLastError();
 }
-
-// ---------------------------------------------------------------- GEMM problem helper
-struct GemmSpec {
-  const PlaneMat* A = nullptr;
-  int a_col0 = 0;        // first activation column (multiple of 64) when the k-blocks are contiguous
-  const int* a_kb = nullptr;  // or an explicit k-block table
-  int M = 0;
-  const PlaneMat* W = nullptr;
-  int N = 0, K = 0;
-  const float* bias = nullptr;
-  int act = ACT_NONE;
-  float* out_f32 = nullptr;
-  long long ld_f32 = 0;
-  bf16* out_hi = nullptr;
-  bf16* out_lo = nullptr;
-  long long ld_bf = 0;
-  // LSTM
-  const float* c_in = nullptr;
-  float* c_out = nullptr;
-  const float* row_bias = nullptr;
-  long long ld_row_bias = 0;
-  int hi_only_first = 0;  // leading k-blocks whose low-order activation plane is identically zero
-  const int32_t* row_tok = nullptr;
-  const float* tok_table = nullptr;
-  long long ld_tok_table = 0;
-  int ksplit = 1;  // 2: cluster split-K (run_gemm then launches the SPLIT == 2 kernel for the whole group)
-  const unsigned long long* row_key = nullptr;  // token from the packed arg-max keys instead of row_tok
-  unsigned long long* argmax_key = nullptr;     // logits: running arg-max keys
-  // logits
-  float* partial = nullptr;
-  float* logits_out = nullptr;
-  long long ld_logits = 0;
-};
 
 static const char* fill_problem(GemmProblem& pb, const GemmSpec& s, int a_terms, int w_terms, int block_n) {
   if (s.K % GEMM_BLOCK_K != 0 || s.K / GEMM_BLOCK_K > GEMM_MAX_KB) return "bad K";
@@ -216,8 +164,8 @@ static int logit_groups(const echr_model* m, int rows) {
 
 int logit_groups_for(const echr_model* m, int rows) { return logit_groups(m, rows); }
 
-static int run_gemm(const GemmSpec* specs, int groups, int a_terms, int w_terms, int block_n, int epi,
-                    int topk, cudaStream_t st, const char* what, echr_batch* tb = nullptr, int kind = 5) {
+int run_gemm(const GemmSpec* specs, int groups, int a_terms, int w_terms, int block_n, int epi,
+             int topk, cudaStream_t st, const char* what, echr_batch* tb, int kind) {
   GemmParams P;
   memset(&P, 0, sizeof(P));
   static const int pdl_late = getenv("ECHR_PDL_LATE") ? atoi(getenv("ECHR_PDL_LATE")) : 1;
@@ -253,7 +201,7 @@ static int run_gemm(const GemmSpec* specs, int groups, int a_terms, int w_terms,
   return ECHR_OK;
 }
 
-static int check_device() {
+int check_device() {
   int dev = 0;
   ECHR_CUDA(cudaGetDevice(&dev));
   return echr_device_check(dev);

@@ -26,10 +26,18 @@ constexpr int CLIP_PAD = 512;   // 500 -> 512
 constexpr int FEAT_PAD = 1024;  // 1012 -> 1024
 constexpr int GATES = 2048;
 
-struct PlaneMat {  // [planes][rows][ld] bf16
+struct PlaneMat {  // [planes][rows][ld] 16-bit (bf16 hi/lo planes, or one fp16 plane)
   bf16* p = nullptr;
   int64_t rows = 0, ld = 0, planes = 0;
-  int64_t plane_stride() const { return rows * ld; }
+  int64_t stride = 0;  // elements between planes; 0 = rows * ld (a row-range view keeps its parent's stride)
+  int64_t plane_stride() const { return stride ? stride : rows * ld; }
+  PlaneMat row_view(int64_t row0, int64_t n) const {
+    PlaneMat v = *this;
+    v.p = p + row0 * ld;
+    v.rows = n;
+    v.stride = plane_stride();
+    return v;
+  }
   bf16* plane(int i) const { return p + i * plane_stride(); }
 };
 
@@ -165,6 +173,65 @@ cudaError_t launch_finalize_tf(const echr_batch* b, int step, const int32_t* seq
 cudaError_t launch_load_state(const echr_batch* b, int rows, const int32_t* it, const float* h_in, cudaStream_t st);
 cudaError_t launch_export_state(const echr_batch* b, int rows, float* h_out, cudaStream_t st);
 void count_launch(int n = 1);
+
+// ---------------------------------------------------------------- arena helper
+struct Arena {
+  size_t off = 0;
+  char* base = nullptr;
+  template <typename T>
+  T* take(size_t n) {
+    off = (off + 255) & ~(size_t)255;
+    T* p = base ? reinterpret_cast<T*>(base + off) : nullptr;
+    off += n * sizeof(T);
+    return p;
+  }
+  PlaneMat planes(int64_t planes_, int64_t rows, int64_t ld) {
+    PlaneMat m;
+    m.rows = rows; m.ld = ld; m.planes = planes_;
+    m.p = take<bf16>((size_t)planes_ * rows * ld);
+    return m;
+  }
+};
+
+
+// ---------------------------------------------------------------- GEMM problem helper
+struct GemmSpec {
+  const PlaneMat* A = nullptr;
+  int a_col0 = 0;        // first activation column (multiple of 64) when the k-blocks are contiguous
+  const int* a_kb = nullptr;  // or an explicit k-block table
+  int M = 0;
+  const PlaneMat* W = nullptr;
+  int N = 0, K = 0;
+  const float* bias = nullptr;
+  int act = 0;  // ACT_NONE
+  float* out_f32 = nullptr;
+  long long ld_f32 = 0;
+  bf16* out_hi = nullptr;
+  bf16* out_lo = nullptr;
+  long long ld_bf = 0;
+  // LSTM
+  const float* c_in = nullptr;
+  float* c_out = nullptr;
+  const float* row_bias = nullptr;
+  long long ld_row_bias = 0;
+  int hi_only_first = 0;  // leading k-blocks whose low-order activation plane is identically zero
+  const int32_t* row_tok = nullptr;
+  const float* tok_table = nullptr;
+  long long ld_tok_table = 0;
+  int ksplit = 1;  // 2: cluster split-K (run_gemm then launches the SPLIT == 2 kernel for the whole group)
+  const unsigned long long* row_key = nullptr;  // token from the packed arg-max keys instead of row_tok
+  unsigned long long* argmax_key = nullptr;     // logits: running arg-max keys
+  // logits
+  float* partial = nullptr;
+  float* logits_out = nullptr;
+  long long ld_logits = 0;
+};
+
+
+// One launch of `groups` independent GEMM problems (see gemm_tc.cuh); epi = EPI_STORE / EPI_LSTM / EPI_LOGITS.
+int run_gemm(const GemmSpec* specs, int groups, int a_terms, int w_terms, int block_n, int epi, int topk,
+             cudaStream_t st, const char* what, echr_batch* tb = nullptr, int kind = 5);
+int check_device();
 // partial records per row the logit GEMM writes when it runs over `rows` decode rows (depends on the
 // GEMM variant the engine picks for that row count)
 int logit_groups_for(const echr_model* m, int rows);

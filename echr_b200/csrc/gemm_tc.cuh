@@ -37,7 +37,7 @@ constexpr int GEMM_THREADS = 128 + GEMM_EPI_WARPS * 32;  // warps 0-3: TMA, MMA,
 constexpr int LOGIT_GROUP = 64;                          // vocabulary columns per partial record
 
 enum : int { EPI_STORE = 0, EPI_LSTM = 1, EPI_LOGITS = 2 };
-enum : int { ACT_NONE = 0, ACT_TANH = 1, ACT_EXP2X = 2 };  // ACT_EXP2X: exp(2 * clamp(x, -40, 40))
+enum : int { ACT_NONE = 0, ACT_TANH = 1, ACT_EXP2X = 2, ACT_SIGMOID = 3 };  // ACT_EXP2X: exp(2 * clamp(x, -40, 40))
 
 struct GemmProblem {
   CUtensorMap tmA;  // 3-D {K cols, M rows, planes}, box {64, 128, 1}, SWIZZLE_128B
@@ -420,6 +420,9 @@ gemm_tc_kernel(const __grid_constant__ GemmParams P) {
             } else if (act == ACT_EXP2X) {
 #pragma unroll
               for (int i = 0; i < CH; ++i) v[i] = __expf(2.0f * fminf(fmaxf(v[i], -40.f), 40.f));
+            } else if (act == ACT_SIGMOID) {
+#pragma unroll
+              for (int i = 0; i < CH; ++i) v[i] = __fdividef(1.0f, 1.0f + __expf(-v[i]));
             }
             const int valid = min(CH, pb.N - cb);
             if (pb.out_f32 != nullptr) {

@@ -250,6 +250,9 @@ gemm_tc2_kernel(const __grid_constant__ GemmParams P, int groups, int total_tile
             } else if (act == ACT_EXP2X) {
 #pragma unroll
               for (int i = 0; i < 32; ++i) v[i] = __expf(2.0f * fminf(fmaxf(v[i], -40.f), 40.f));
+            } else if (act == ACT_SIGMOID) {
+#pragma unroll
+              for (int i = 0; i < 32; ++i) v[i] = __fdividef(1.0f, 1.0f + __expf(-v[i]));
             }
             const int valid = min(32, pb.N - cb);
             if (pb.out_f32 != nullptr) {

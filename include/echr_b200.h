@@ -219,6 +219,33 @@ ECHR_API int echr_caption_device(echr_batch_t* batch, const echr_batch_desc_t* d
                         const float* tap, const float* lda, int beam, int32_t* tokens, float* logp,
                         float* score, void* stream);
 
+/* ---- SST proposal encoder in front of the path -------------------------- */
+/* models/sst_model.py:5-40: nn.LSTM(500 -> 512, 2 layers) over the clips of a video, then
+ * sigmoid(Linear(512 -> K)).  fp32 DEVICE pointers into the tap_model state_dict. */
+typedef struct echr_sst echr_sst_t;
+typedef struct echr_sst_weights {
+  const float* w_ih0;    /* rnn.weight_ih_l0 [2048, 500]  (gate order i,f,g,o as in nn.LSTM) */
+  const float* w_hh0;    /* rnn.weight_hh_l0 [2048, 512] */
+  const float* b_ih0;    /* rnn.bias_ih_l0   [2048]      */
+  const float* b_hh0;    /* rnn.bias_hh_l0   [2048]      */
+  const float* w_ih1;    /* rnn.weight_ih_l1 [2048, 512] */
+  const float* w_hh1;    /* rnn.weight_hh_l1 [2048, 512] */
+  const float* b_ih1;    /* rnn.bias_ih_l1   [2048]      */
+  const float* b_hh1;    /* rnn.bias_hh_l1   [2048]      */
+  const float* scores_w; /* scores.weight    [K, 512]    */
+  const float* scores_b; /* scores.bias      [K]         */
+} echr_sst_weights_t;
+/* Packs the weights (a_terms / w_terms as in echr_config_t).  Synchronises `stream`. */
+ECHR_API int echr_sst_create(int K, int a_terms, int w_terms, const echr_sst_weights_t* weights, void* stream,
+                    echr_sst_t** out);
+ECHR_API int echr_sst_destroy(echr_sst_t* sst);
+/* SST.forward (sst_model.py:31-40, eval mode) for a batch of videos in one call: c3d fp32 [sum_v T_v, 500]
+ * (device), host_clip_offsets int32 [n_videos+1] (host).  Outputs (device): tap_feats [sum_v T_v, 512] =
+ * rnn_output, pred_proposals [sum_v T_v, K].  Videos of different length run together: the recurrent step t
+ * covers the videos that still have a clip t.  The workspace grows on demand (that call synchronises). */
+ECHR_API int echr_sst_forward(echr_sst_t* sst, const float* c3d, const int32_t* host_clip_offsets, int n_videos,
+                     float* tap_feats, float* pred_proposals, void* stream);
+
 /* ---- proposal selection between the proposal module and the path ------- */
 /* All pointers are DEVICE pointers unless named host_*.  One CTA per video; the [T,K] score matrix stays in
  * HBM and only the selected records come out.  Outputs are fixed-capacity slots: video v writes its records
