@@ -1,7 +1,7 @@
 #!/usr/bin/env python
 """Benchmark of the ECHR caption-generation hot path (BASELINE.json metric: events captioned / s).
 
-    python bench.py [--gpus N] [--steps K] [--warmup W] [--workload cfg2] [--beam 1] [--precision f16] [--in-flight 3]
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--workload cfg2] [--beam 1] [--precision f16] [--in-flight 4]
     python bench.py --impl reference ...      # the reference algorithm's CPU path (oracle port) on the host cores
 
 One "step" = one pass of the hot path (context assembly + relation encoder + 30-token decode) over
@@ -42,7 +42,7 @@ def parse():
     ap.add_argument("--precision", default="f16", choices=["fp32", "bf16w", "f16"])
     ap.add_argument("--cpu-sample", type=int, default=None, help="videos in the CPU-baseline sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--in-flight", type=int, default=3,
+    ap.add_argument("--in-flight", type=int, default=4,
                     help="batches kept in flight per GPU (CaptionPipeline lanes); 1 = one blocking batch at a time")
     return ap.parse_args()
 
