@@ -181,6 +181,16 @@ def trim_greedy(tokens, logp):
     return tokens[:, :ncols].long(), logp[:, :ncols]
 
 
+def _teacher_forced_cols(seq):
+    """OldModel.forward (OldModel_NEW.py:98-130) stops at the first all-zero label column i >= 1: the columns
+    of `seq` it consumes (it then returns that many minus one steps)."""
+    cols = seq.shape[1]
+    for i in range(1, cols - 1):
+        if int(seq[:, i].sum()) == 0:
+            return i + 1
+    return cols
+
+
 class CaptionGenerator(nn.Module):
     def __init__(self, opt, precision="fp32"):
         super().__init__()
@@ -278,6 +288,18 @@ class CaptionGenerator(nn.Module):
                 r0 += n
             return out
 
+    def lm_loss(self, tap_feats, c3d_feats, lda_feats, lm_labels, lm_masks, ind_select_list, soi_select_list):
+        """The validation LM loss of eval_utils.py:139-152 in one pass:
+        `cg_crit(cg_model(..., lm_labels, ..., mode='train'), lm_labels[:, 1:], lm_masks[:, 1:])` with
+        cg_crit = LanguageModelCriterion (misc/utils.py:62-75), without the [N, S-1, V+1] log-prob tensor."""
+        from .criterion import LanguageModelCriterion
+        video = (tap_feats, c3d_feats, lda_feats, list(ind_select_list), [list(s) for s in soi_select_list])
+        with torch.no_grad():
+            eng, _ = self._stage([video], 1)
+            cols = _teacher_forced_cols(lm_labels)
+            tlp = eng.teacher_forced_nll(lm_labels[:, :cols])
+            return LanguageModelCriterion.from_target_logp(tlp, lm_masks[:, 1:].to(tlp.device))
+
     # -- the reference's call (eval_utils.py:129, train.py:298)
     def forward(self, tap_feats, c3d_feats, lda_feats, lm_labels, ind_select_list, soi_select_list, mode="train",
                 beam_size=1):
@@ -288,10 +310,5 @@ class CaptionGenerator(nn.Module):
         if mode == "train":
             # OldModel.forward (OldModel_NEW.py:98-130): stop at the first all-zero label column i >= 1
             seq = lm_labels
-            cols = seq.shape[1]
-            for i in range(1, cols - 1):
-                if int(seq[:, i].sum()) == 0:
-                    cols = i + 1
-                    break
-            return self.teacher_forced([video], [seq[:, :cols]])[0]
+            return self.teacher_forced([video], [seq[:, :_teacher_forced_cols(seq)]])[0]
         raise ValueError("echr_b200.CaptionGenerator supports mode='eval' and mode='train' (forward only); got %r" % mode)

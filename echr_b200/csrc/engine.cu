@@ -4,6 +4,7 @@
 #include "gemm_tc2.cuh"
 #include "util.cuh"
 
+#include <algorithm>
 #include <atomic>
 #include <new>
 #include <vector>
@@ -480,6 +481,7 @@ extern "C" int echr_batch_destroy(echr_batch_t* b) {
   cudaFreeHost(b->host_tap_base);
   for (int i = 0; i < 2; ++i)
     if (b->stage_ev[i]) cudaEventDestroy(b->stage_ev[i]);
+  cudaFree(b->nll_logits);
   cudaFree(b->arena);
   delete b;
   return ECHR_OK;
@@ -1072,6 +1074,38 @@ extern "C" int echr_teacher_forced(echr_batch_t* b, const int32_t* seq, int seq_
   for (int t = 0; t < seq_cols - 1; ++t) {
     ECHR_TRY(enqueue_step(b, rows, t, 1, logprobs + (long long)t * V1, (long long)(seq_cols - 1) * V1, st));
     ECHR_CUDA(launch_finalize_tf(b, t, seq, seq_cols, logprobs, st));
+  }
+  return ECHR_OK;
+}
+
+// The teacher-forced pass as the loss needs it (eval_utils.py:139-152, train.py:298-300: cg_crit(cg_model(...,
+// mode='train'), labels[:,1:], masks[:,1:])): instead of the [n, S-1, V+1] log-prob tensor (173 MB at 251 events)
+// only target_logp[r, t] = log p(seq[r, t+1] | seq[r, :t+1]) is produced, [n_events, seq_cols-1]: exactly the
+// entries LanguageModelCriterion gathers (misc/utils.py:62-75).
+extern "C" int echr_teacher_forced_nll(echr_batch_t* b, const int32_t* seq, int seq_cols, float* target_logp,
+                                       void* stream) {
+  ECHR_REQUIRE(b && seq && target_logp, "echr_teacher_forced_nll: null argument");
+  ECHR_REQUIRE(b->encoded, "echr_teacher_forced_nll: call echr_encode first");
+  ECHR_REQUIRE(seq_cols >= 2 && seq_cols <= 65, "echr_teacher_forced_nll: seq_cols must be in 2..65");
+  cudaStream_t st = (cudaStream_t)stream;
+  if (b->n_events == 0) return ECHR_OK;
+  const int rows = b->n_events;
+  const int V1 = b->model->V1;
+  if (b->nll_rows < rows) {
+    ECHR_CUDA(cudaStreamSynchronize(st));
+    cudaFree(b->nll_logits);
+    b->nll_logits = nullptr;
+    b->nll_rows = 0;
+    const long long want = std::max<long long>(rows, b->cap.max_events);
+    if (cudaMalloc(&b->nll_logits, sizeof(float) * (size_t)want * V1) != cudaSuccess)
+      return set_error(ECHR_ERR_WORKSPACE, "echr_teacher_forced_nll: cudaMalloc of %lld logit rows failed", want);
+    b->nll_rows = want;
+  }
+  ECHR_TRY(enqueue_init(b, 1, st));
+  ECHR_CUDA(launch_finalize_nll(b, -1, seq, seq_cols, b->nll_logits, target_logp, st));
+  for (int t = 0; t < seq_cols - 1; ++t) {
+    ECHR_TRY(enqueue_step(b, rows, t, 1, b->nll_logits, V1, st));
+    ECHR_CUDA(launch_finalize_nll(b, t, seq, seq_cols, b->nll_logits, target_logp, st));
   }
   return ECHR_OK;
 }

@@ -126,6 +126,9 @@ struct echr_batch {
     long long kernels;  // kernel nodes in the graph
     unsigned long long stamp;
   };
+  // scratch rows of raw logits for the teacher-forced loss path (allocated on its first use)
+  float* nll_logits;
+  long long nll_rows;
   static constexpr int GRAPH_SLOTS = 64;
   GraphSlot graphs[GRAPH_SLOTS];
   unsigned long long graph_clock;
@@ -170,6 +173,8 @@ cudaError_t launch_finalize_beam(const echr_batch* b, int beam, int step, int32_
                                  float* logp, float* score, cudaStream_t st);
 cudaError_t launch_finalize_tf(const echr_batch* b, int step, const int32_t* seq, int seq_cols,
                                float* logprobs, cudaStream_t st);
+cudaError_t launch_finalize_nll(const echr_batch* b, int step, const int32_t* seq, int seq_cols,
+                                const float* logits, float* target_logp, cudaStream_t st);
 cudaError_t launch_load_state(const echr_batch* b, int rows, const int32_t* it, const float* h_in, cudaStream_t st);
 cudaError_t launch_export_state(const echr_batch* b, int rows, float* h_out, cudaStream_t st);
 void count_launch(int n = 1);

@@ -736,6 +736,38 @@ cudaError_t launch_finalize_tf(const echr_batch* b, int step, const int32_t* seq
   return cudaGetLastError();
 }
 
+// Teacher-forced step of the loss path: the logit GEMM stored raw logits into the scratch rows `logits`;
+// keep only what LanguageModelCriterion gathers (misc/utils.py:62-75): the log-prob of the NEXT label,
+// target_logp[r, step] = logits[r, seq[r, step+1]] - logsumexp(logits[r, :]), and embed that label.
+__global__ void __launch_bounds__(FIN_WARPS * 32)
+finalize_nll_kernel(int rows, int n_tiles, int step, int seq_cols, int V1, const float* __restrict__ partial,
+                    const int32_t* __restrict__ seq, int32_t* __restrict__ row_tok,
+                    const float* __restrict__ logits, float* __restrict__ target_logp) {
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int r = blockIdx.x * FIN_WARPS + warp;
+  if (r >= rows) return;
+  int tok = seq[(long long)r * seq_cols + step + 1];
+  tok = min(max(tok, 0), V1 - 1);
+  if (step >= 0) {  // step == -1: only embed seq[:, 0]
+    const RowStat s = merge_row_stats<1>(partial + (long long)r * n_tiles * LogitRec<1>::WORDS, n_tiles, lane);
+    if (lane == 0)
+      target_logp[(long long)r * (seq_cols - 1) + step] = logits[(long long)r * V1 + tok] - (s.max_val + s.log_sum);
+  }
+  if (step + 1 < seq_cols - 1 && lane == 0) row_tok[r] = tok;
+}
+
+cudaError_t launch_finalize_nll(const echr_batch* b, int step, const int32_t* seq, int seq_cols,
+                                const float* logits, float* target_logp, cudaStream_t st) {
+  const int rows = b->n_events;
+  if (rows == 0) return cudaSuccess;
+  const echr_model* m = b->model;
+  const int n_tiles = logit_groups_for(m, b->n_events);
+  finalize_nll_kernel<<<(rows + FIN_WARPS - 1) / FIN_WARPS, FIN_WARPS * 32, 0, st>>>(
+      rows, n_tiles, step, seq_cols, m->V1, b->partial, seq, b->row_tok, logits, target_logp);
+  count_launch();
+  return cudaGetLastError();
+}
+
 // ---------------------------------------------------------------------------------------------
 // Explicit-state single step (OldModel.get_logprobs_state, OldModel_NEW.py:133-137): load the
 // caller's (h, it) into the activation matrix, and read the new h back out of the planes.

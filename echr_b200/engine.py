@@ -204,6 +204,19 @@ class Engine(object):
                   "echr_teacher_forced")
         return out
 
+    def teacher_forced_nll(self, seq):
+        """seq int [n_events, S] (column 0 = BOS) -> fp32 [n_events, S-1]: the log-prob of the next label at every
+        step (what LanguageModelCriterion gathers), without materialising the [n, S-1, V+1] tensor."""
+        seq = seq.to(device=self.device, dtype=torch.int32).contiguous()
+        n, cols = seq.shape
+        if n != self.layout.n_events:
+            raise ValueError("seq has %d rows, batch has %d events" % (n, self.layout.n_events))
+        out = torch.zeros(n, cols - 1, dtype=torch.float32, device=self.device)
+        with torch.cuda.device(self.device):
+            check(self.lib.echr_teacher_forced_nll(self._batch, seq.data_ptr(), cols, out.data_ptr(), _stream()),
+                  "echr_teacher_forced_nll")
+        return out
+
     # ------------------------------------------------------------------ sub-module level entries
     def relation_encode(self, feats, soi):
         """MA_Attention8.forward: feats fp32 [n,1012] on this device, soi [[s,e),...] -> [n,512]."""

@@ -198,6 +198,13 @@ ECHR_API int echr_decode_beam(echr_batch_t* batch, int beam, int32_t* tokens, fl
 ECHR_API int echr_teacher_forced(echr_batch_t* batch, const int32_t* seq, int seq_cols, float* logprobs,
                         void* stream);
 
+/* The teacher-forced pass as the LM loss needs it (eval_utils.py:139-152; misc/utils.py:62-75
+ * LanguageModelCriterion gathers one entry per step): target_logp fp32 [n_events, seq_cols-1],
+ * target_logp[r, t] = log p(seq[r, t+1] | seq[r, 0..t]).  The [n, S-1, V+1] tensor is never written.
+ * Allocates its scratch logit rows on first use (that call synchronises). */
+ECHR_API int echr_teacher_forced_nll(echr_batch_t* batch, const int32_t* seq, int seq_cols, float* target_logp,
+                            void* stream);
+
 /* End-to-end call with HOST buffers (eval_utils.py:52,129-136 for a whole batch of videos):
  * H2D of the features, encode, decode (beam<=1: greedy), D2H of the results, stream synchronised
  * before returning.  host_score may be NULL. */
