@@ -889,7 +889,9 @@ static int enqueue_step(echr_batch* b, int rows, int t, int topk, float* logits_
     // latency regime: narrow tiles spread the [rows,512] x [512,512] product over 4x the SMs (a CTA's
     // main loop is bound by its own L2->SM operand stream, dominated by the 2-plane activation tile)
     static const int bn_small = getenv("ECHR_H2ATT_BN") ? atoi(getenv("ECHR_H2ATT_BN")) : 32;
-    const int bn = rows < gemm2_min_rows() ? bn_small : 128;
+    // (lanes sharing the GPU: one wide tile per 128 rows costs a third of the SM time of four narrow ones)
+    static const int bn_shared = getenv("ECHR_H2ATT_BN_SHARED") ? atoi(getenv("ECHR_H2ATT_BN_SHARED")) : 128;
+    const int bn = rows < gemm2_min_rows() ? (b->concurrency > 1 ? bn_shared : bn_small) : 128;
     ECHR_TRY(run_gemm(&s, 1, at, wt, bn, EPI_STORE, 1, st, "h2att", b, 0));
   }
   if (parts & PART_ATT) {
@@ -906,7 +908,7 @@ static int enqueue_step(echr_batch* b, int rows, int t, int topk, float* logits_
     // latency regime: stream 1 has twice the k-blocks of the others; give its tiles to CTA pairs (and the
     // other streams' too while everything still fits one wave)
     int ks[3] = {1, 1, 1};
-    if ((ksplit_mask() & 1) != 0 && rows < gemm2_min_rows()) {
+    if ((ksplit_mask() & 1) != 0 && b->concurrency <= 1 && rows < gemm2_min_rows()) {
       const int mt = m_tiles_of(rows), nt = GATES / 128;
       if (mt * nt * 6 <= num_sms()) ks[0] = ks[1] = ks[2] = 2;
       else if (mt * nt * 4 <= num_sms()) ks[1] = 2;
@@ -1023,7 +1025,7 @@ static int run_decode(echr_batch* b, int beam, int mode, cudaStream_t st) {
   ECHR_REQUIRE((long long)b->n_events * beam <= b->cap.max_rows, "decode: %d events x beam %d exceed max_rows %lld", b->n_events, beam, (long long)b->cap.max_rows);
   if (b->n_events == 0) return ECHR_OK;
   const int rows = b->n_events * beam;
-  const long long key[6] = {1, rows, mode == MODE_BEAM ? beam : 0, len_bucket(b->max_len), 0, 0};
+  const long long key[6] = {1, rows, mode == MODE_BEAM ? beam : 0, len_bucket(b->max_len), b->concurrency > 1 ? 1 : 0, 0};
   const char* tr = getenv("ECHR_TRACE");
   if (!(tr != nullptr && tr[0] == '1') && !worth_a_graph(b, key)) {
     // first sight of this shape: the same fork/join schedule, enqueued eagerly on the caller's stream
@@ -1127,6 +1129,12 @@ extern "C" int echr_decode_step(echr_batch_t* b, const int32_t* it, const float*
   ECHR_CUDA(launch_finalize_tf(b, 0, it, 2, logprobs, st));  // seq_cols = 2: normalise only
   ECHR_CUDA(launch_export_state(b, rows, h_out, st));
   ECHR_CUDA(cudaMemcpyAsync(c_out, b->cstate[1], sizeof(float) * (size_t)3 * rows * HID, cudaMemcpyDeviceToDevice, st));
+  return ECHR_OK;
+}
+
+extern "C" int echr_batch_set_concurrency(echr_batch_t* b, int lanes) {
+  ECHR_REQUIRE(b && lanes >= 1, "echr_batch_set_concurrency: bad argument");
+  b->concurrency = lanes;
   return ECHR_OK;
 }
 

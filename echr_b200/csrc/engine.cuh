@@ -126,6 +126,11 @@ struct echr_batch {
     long long kernels;  // kernel nodes in the graph
     unsigned long long stamp;
   };
+  // > 1: other batches of the job run concurrently on this GPU (CaptionPipeline lanes).  Choices that buy latency
+  // with extra SM time (cluster split-K of the gate GEMMs: two CTAs and a DSMEM exchange per tile; narrow h2att
+  // tiles) are then off: with the SMs shared by several decode chains, SM time is the budget (cfg2, 4 lanes:
+  // 329k -> 381k events/s).
+  int concurrency;
   // scratch rows of raw logits for the teacher-forced loss path (allocated on its first use)
   float* nll_logits;
   long long nll_rows;

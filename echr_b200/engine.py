@@ -98,6 +98,12 @@ class Engine(object):
             del keep  # echr_model_create synchronises; the packed copy is what the kernels read
         self._parent = None  # set on a fork(): the engine that owns the packed model
 
+    def set_concurrency(self, lanes):
+        """Tell the workspace how many batches of the job share the GPU (see echr_batch_set_concurrency)."""
+        self._lanes = int(lanes)
+        if self._batch.value:
+            check(self.lib.echr_batch_set_concurrency(self._batch, self._lanes), "echr_batch_set_concurrency")
+
     def fork(self):
         """A second engine on the SAME packed model with its own batch workspace (echr_batch_t): batches of
         one model are independent, so forks may run concurrently on different streams (CaptionPipeline)."""
@@ -142,6 +148,8 @@ class Engine(object):
             cap = Capacity(*need)
             check(self.lib.echr_batch_create(self._model, ctypes.byref(cap), ctypes.byref(self._batch)),
                   "echr_batch_create")
+            if getattr(self, "_lanes", 1) > 1:
+                check(self.lib.echr_batch_set_concurrency(self._batch, int(self._lanes)), "echr_batch_set_concurrency")
         self._cap = need
 
     # ------------------------------------------------------------------ device-input path
@@ -355,6 +363,8 @@ class CaptionPipeline(object):
             raise ValueError("depth must be >= 1")
         self.engine = engine
         self.lanes = [engine] + [engine.fork() for _ in range(depth - 1)]
+        for e in self.lanes:
+            e.set_concurrency(depth)
         self.streams = [torch.cuda.Stream(device=engine.device) for _ in self.lanes]
         self.events = [None] * depth
         self.bufs = [{} for _ in self.lanes]
@@ -416,3 +426,4 @@ class CaptionPipeline(object):
         for e in self.lanes[1:]:
             e.close()
         self.lanes = self.lanes[:1]
+        self.lanes[0].set_concurrency(1)

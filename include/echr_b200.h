@@ -198,6 +198,11 @@ ECHR_API int echr_decode_beam(echr_batch_t* batch, int beam, int32_t* tokens, fl
 ECHR_API int echr_teacher_forced(echr_batch_t* batch, const int32_t* seq, int seq_cols, float* logprobs,
                         void* stream);
 
+/* Hint: `lanes` batches of this job run concurrently on the GPU (1 = this batch has it to itself, the
+ * default).  With lanes > 1 the decode drops the choices that trade SM time for latency (cluster split-K of
+ * the gate GEMMs, narrow h2att tiles).  Results do not change beyond fp32 summation order (tokens identical, |dlogp| < 1e-5). */
+ECHR_API int echr_batch_set_concurrency(echr_batch_t* batch, int lanes);
+
 /* The teacher-forced pass as the LM loss needs it (eval_utils.py:139-152; misc/utils.py:62-75
  * LanguageModelCriterion gathers one entry per step): target_logp fp32 [n_events, seq_cols-1],
  * target_logp[r, t] = log p(seq[r, t+1] | seq[r, 0..t]).  The [n, S-1, V+1] tensor is never written.

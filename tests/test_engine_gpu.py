@@ -210,6 +210,16 @@ def test_pipeline_batches_in_flight_equal_single_calls(depth):
         host = (torch.cat([v.c3d_feats for v in vids]).pin_memory(), torch.cat([v.tap_feats for v in vids]).pin_memory(),
                 torch.stack([v.lda_feats for v in vids]).pin_memory())
         batches.append((lay, host, tuple(t.to(DEV) for t in host)))
+    def same(got, want, what):
+        # lanes that share the GPU run the gate GEMMs unsplit (echr_batch_set_concurrency): same tokens, fp32
+        # summation order of the gates differs from the single-batch schedule
+        assert torch.equal(got[0].cpu(), want[0]), what
+        for g, w in zip(got[1:], want[1:]):
+            if depth == 1:
+                assert torch.equal(g.cpu(), w), what
+            else:
+                assert (g.cpu() - w).abs().max().item() <= 1e-5 * max(1.0, w.abs().max().item()), what
+
     for beam in (1, 3):
         want = []
         for lay, host, dev in batches:
@@ -222,13 +232,9 @@ def test_pipeline_batches_in_flight_equal_single_calls(depth):
                     tickets.append(pipe.submit(bt[0], *bt[side], beam=beam))
                     if len(tickets) >= depth:  # consume the oldest before its lane is reused
                         j = i - depth + 1
-                        got = tickets[j].wait()
-                        for g, w in zip(got, want[j]):
-                            assert torch.equal(g.cpu(), w), (depth, beam, side, j)
+                        same(tickets[j].wait(), want[j], (depth, beam, side, j))
                 for j in range(max(0, len(batches) - depth + 1), len(batches)):
-                    got = tickets[j].wait()
-                    for g, w in zip(got, want[j]):
-                        assert torch.equal(g.cpu(), w), (depth, beam, side, j)
+                    same(tickets[j].wait(), want[j], (depth, beam, side, j))
         pipe.close()
 
 
