@@ -148,3 +148,89 @@ def test_gpu_selection_feeds_the_caption_path():
     model = model.cuda()
     seq, logp = model(v.tap_feats.cuda(), v.c3d_feats.cuda(), v.lda_feats.cuda(), [], ind, feat, mode="eval")
     assert seq.shape[0] == 12 and torch.isfinite(logp).all()
+
+
+# ----------------------------------------------------------------------------- size-independent properties (CPU)
+@pytest.mark.parametrize("seed", range(6))
+def test_oracle_selection_properties(seed):
+    """Invariants the domain offers, on shapes the golden cases do not cover."""
+    rng = np.random.RandomState(50 + seed)
+    T, K = int(rng.randint(2, 90)), int(rng.choice([4, 16, 64, 256]))
+    s = C.distinct_scores(rng, T, K)
+    m = (np.arange(T)[:, None] >= np.arange(K)[None, :]).astype(np.float32)
+    topn = int(rng.randint(1, 300))
+    ind, start, end, conf = PO.topn_select(s, m, topn=topn)
+    # every emitted cell is a valid (n >= k) cell at or above the topn-th largest masked score, in row-major order
+    p = s * m
+    thr = np.sort(p.reshape(-1))[-min(p.size, topn)]
+    assert (conf >= thr).all() and (ind - start >= 0).all() and (end == ind + 1).all()
+    order = ind * K + (ind - start)
+    assert (np.diff(order) > 0).all()
+    assert len(ind) == int(((p >= max(thr, 0)) & (m > 0)).sum() + ((p >= max(thr, 0)) & (m == 0) & (np.arange(T)[:, None] >= np.arange(K)[None, :])).sum())
+    # NMS: scores come out in descending order, no two picks overlap by more than the threshold, and every
+    # proposal left out overlaps an earlier-picked, better-scored one (unless the pick budget ran out)
+    ov = float(rng.choice([0.3, 0.6, 0.8]))
+    budget = int(rng.randint(1, 200))
+    pick, props, sc = PO.nms_select(s, overlap=ov, topn=budget)
+    assert (np.diff(sc) < 0).all()
+
+    def iou(a, b):
+        wh = max(0.0, min(a[1], b[1]) - max(a[0], b[0]) + 1.0)
+        return wh / ((a[1] - a[0] + 1.0) + (b[1] - b[0] + 1.0) - wh)
+    for i in range(len(props)):
+        for j in range(i):
+            assert iou(props[i], props[j]) <= ov
+    if len(pick) < budget:
+        n, k = PO.enumerate_proposals(T, K)
+        picked = set(pick.tolist())
+        for q in rng.choice(n.size, size=min(40, n.size), replace=False):
+            if int(q) in picked:
+                continue
+            box = (n[q] - k[q], n[q] + 1)
+            assert any(iou(box, props[j]) > ov and sc[j] > s[n[q], k[q]] for j in range(len(props)))
+    # idempotence: selecting again among the picks alone changes nothing
+    keep = np.full_like(s, -1.0)
+    n, k = PO.enumerate_proposals(T, K)
+    keep[n[pick], k[pick]] = s[n[pick], k[pick]]
+    pick2, props2, _ = PO.nms_select(keep, overlap=ov, topn=len(pick))
+    assert np.array_equal(props2, props)
+
+
+@pytest.mark.gpu
+def test_gpu_selection_properties_at_full_size():
+    """BASELINE-size matrices (64 videos x T=400 x K=256, 69.5k proposals per video) are too slow for the numpy
+    oracle: check what must hold at any size — descending scores, pairwise overlap of the picks <= threshold,
+    the pick budget, top-N threshold / order / count — and the oracle itself on two of the videos."""
+    from echr_b200 import proposals as P
+    rng = np.random.RandomState(8)
+    V, T, K, ov, topn = 64, 400, 256, 0.7, 300
+    s = np.stack([C.distinct_scores(rng, T, K) for _ in range(V)]).reshape(V * T, K)
+    off = np.arange(V + 1) * T
+    d_s = torch.from_numpy(s).cuda()
+    ind, start, end, sc, pick, count = P.select_nms(d_s, off, overlap=ov, topN=topn)
+    assert int(count.min()) >= 1 and int(count.max()) <= topn
+    valid = torch.arange(sc.shape[1], device="cuda")[None, :] < count[:, None]
+    assert bool(((sc[:, 1:] < sc[:, :-1]) | ~valid[:, 1:]).all())
+    a0, a1 = start.double(), end.double()
+    wh = (torch.minimum(a1[:, :, None], a1[:, None, :]) - torch.maximum(a0[:, :, None], a0[:, None, :]) + 1.0).clamp(min=0)
+    area = a1 - a0 + 1.0
+    o = wh / (area[:, :, None] + area[:, None, :] - wh)
+    pair = valid[:, :, None] & valid[:, None, :] & ~torch.eye(sc.shape[1], dtype=torch.bool, device="cuda")[None]
+    assert float(o[pair].max()) <= ov
+    assert bool((ind == end - 1)[valid].all())
+    got_score = d_s.view(V, T, K)[torch.arange(V, device="cuda")[:, None], ind.long(), (ind - start).long()]
+    assert torch.equal(got_score[valid], sc[valid])
+    for v in (0, V - 1):
+        wp, wprops, wsc = PO.nms_select(s[off[v]:off[v + 1]], overlap=ov, topn=topn)
+        c = int(count[v])
+        assert c == wp.size and np.array_equal(pick[v, :c].cpu().numpy(), wp)
+    # top-N
+    m = np.tile((np.arange(T)[:, None] >= np.arange(K)[None, :]).astype(np.float32), (V, 1))
+    ti, ts, te, tc, tcount = P.select_topn(d_s, torch.from_numpy(m).cuda(), off, topN=1000)
+    assert bool((tcount == 1000).all())  # distinct scores, mask = the valid cells: exactly topN cells qualify
+    p = torch.from_numpy(s * m).cuda().view(V, -1)
+    thr = p.topk(1000, dim=1)[0][:, -1]
+    assert bool((tc[:, :1000] >= thr[:, None]).all())
+    order = ti[:, :1000].long() * K + (ti - ts)[:, :1000].long()
+    assert bool((order[:, 1:] > order[:, :-1]).all())
+    assert torch.equal(p.gather(1, order), tc[:, :1000])
