@@ -2,7 +2,6 @@
 (eval_utils.py:139-152).  `forward` keeps the reference's signature on the full [N, S, V+1] log-prob tensor
 (plain tensor glue); `from_target_logp` is the form the B200 path uses: the gather already happened inside the
 teacher-forced pass (echr_teacher_forced_nll), so only the masked mean is left."""
-import torch
 import torch.nn as nn
 
 

@@ -11,7 +11,6 @@ thousand ints) come back.  `select_topn` / `select_nms` are the batched forms (m
 tensors out) for feeding the path without any round trip.  There is no CPU path: without the CUDA library or
 a B200 these functions raise.
 """
-import ctypes
 
 import numpy as np
 import torch
