@@ -346,6 +346,13 @@ def _main(args):
             "data": "synthetic",
             "config": dict(workload_config(args, w, n_events, world), precision=args.precision,
                            l2_flush_between_steps=True, in_flight=pipe.depth,
+                           precision_note={"f16": "every tensor-core operand one fp16 plane (11-bit mantissa >= bf16's 8; a "
+                                                  "bf16-representable checkpoint is exact in fp16), fp32 accumulation, state and "
+                                                  "softmax; tokens equal the fp32-grade path except at top-2 gaps < 1e-4 "
+                                                  "(profiles/r01_precision_token_agreement.txt)",
+                                           "bf16w": "activations bf16 hi+lo planes, weights bf16: bit-identical to the fp32-grade "
+                                                    "path on a bf16-representable checkpoint",
+                                           "fp32": "bf16 hi+lo planes on both operands (3 products): fp32-grade"}[args.precision],
                            **({"DIAGNOSIS_no_token_gather": True} if no_gather and world > 1 else {}),
                            l2_flush="256 MB write at the head of every step, on the step's stream, inside the timed region",
                            ms_per_decode_step=ms_dev / args.steps / S),
