@@ -71,6 +71,8 @@ def select_nms(scores, clip_offsets, overlap=0.8, topN=1000):
     K = scores.shape[1]
     off = np.asarray(clip_offsets, dtype=np.int32)
     V = off.size - 1
+    if V and (int(np.diff(off).max()) > 65535 or K > 65535):
+        raise ValueError("select_nms packs (n, k) into 16 bits each: videos of more than 65535 clips are not supported")
     per = np.array([lib.echr_select_nms_proposals(int(t), K) for t in np.diff(off)], dtype=np.int64)
     ws_off = np.concatenate([[0], np.cumsum(per)]).astype(np.int64)
     total = int(ws_off[-1])

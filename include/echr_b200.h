@@ -277,7 +277,7 @@ ECHR_API int echr_select_topn(const float* scores, const float* mask, const int3
  * remaining one whose overlap (intersection+1)/(union) with it exceeds `overlap`, until none is left or topn
  * are taken.  Equal scores: the later proposal in enumeration order first (numpy's unstable argsort leaves
  * that case open).  Overlaps are evaluated in fp64 in numpy's operation order.
- * workspace: 8 bytes per proposal of the batch; workspace_offsets: int64 [n_videos] = first proposal of each
+ * T_v and K at most 65535.  workspace: 8 bytes per proposal of the batch; workspace_offsets: int64 [n_videos] = first proposal of each
  * video (prefix sums of echr_select_nms_proposals(T_v, K)); total_proposals = their sum.
  * Outputs per pick, in pick order: out_ind = n (index_select_list), out_start/out_end (nms_props), out_score
  * (nms_scores), out_pick = the proposal's enumeration index (what indexes prop_gts). */
