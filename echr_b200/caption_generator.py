@@ -126,12 +126,7 @@ class ThreestreamModel(nn.Module):
         with torch.no_grad():
             eng = _owner_engine(self)
             eng.set_context(video, event, clip, _clip_lengths(clip_mask))
-            cols = seq.shape[1]
-            for i in range(1, cols - 1):
-                if int(seq[:, i].sum()) == 0:
-                    cols = i + 1
-                    break
-            return eng.teacher_forced(seq[:, :cols])
+            return eng.teacher_forced(seq[:, :_teacher_forced_cols(seq)])
 
     def sample(self, video, event, clip, clip_mask, opt={}):
         """Greedy (default) or beam decode from ready-made contexts (OldModel_NEW.py:139-187).
@@ -183,11 +178,14 @@ def trim_greedy(tokens, logp):
 
 def _teacher_forced_cols(seq):
     """OldModel.forward (OldModel_NEW.py:98-130) stops at the first all-zero label column i >= 1: the columns
-    of `seq` it consumes (it then returns that many minus one steps)."""
+    of `seq` it consumes (it then returns that many minus one steps).  One reduction and one device-to-host
+    copy instead of the reference's `.sum()` test per step."""
     cols = seq.shape[1]
-    for i in range(1, cols - 1):
-        if int(seq[:, i].sum()) == 0:
-            return i + 1
+    if cols > 2:
+        sums = seq[:, 1:cols - 1].sum(0).tolist()
+        for i, v in enumerate(sums, start=1):
+            if v == 0:
+                return i + 1
     return cols
 
 

@@ -85,3 +85,26 @@ def test_gpu_lm_loss_matches_reference(name, precision, kind, tol):
     assert full2.shape[1] == 6
     u2 = LanguageModelCriterion()(full2, short[:, 1:].cuda(), smask[:, 1:].cuda())
     assert abs(float(f2) - float(u2)) < 1e-6
+
+
+def test_teacher_forced_column_rule_matches_the_reference_loop():
+    """OldModel_NEW.py:104-123: the step loop breaks at the first i >= 1 whose label column sums to zero."""
+    from echr_b200.caption_generator import _teacher_forced_cols
+
+    def reference_steps(seq):
+        steps = 0
+        for i in range(seq.size(1) - 1):
+            if i >= 1 and seq[:, i].sum() == 0:
+                break
+            steps += 1
+        return steps
+    g = torch.Generator().manual_seed(3)
+    for cols in (2, 3, 5, 17, 32):
+        for cut in (None, 1, 2, cols - 2, cols - 1):
+            seq = torch.randint(1, 50, (4, cols), generator=g)
+            seq[:, 0] = 0
+            if cut is not None and 0 < cut < cols:
+                seq[:, cut:] = 0
+            assert _teacher_forced_cols(seq) - 1 == reference_steps(seq), (cols, cut)
+    ragged = torch.tensor([[0, 5, 0, 0, 0], [0, 7, 8, 0, 0]])
+    assert _teacher_forced_cols(ragged) - 1 == reference_steps(ragged) == 3
