@@ -74,3 +74,21 @@ def test_submodules_need_their_owner():
     fm = setup_fusion(echr_opt())
     with pytest.raises(RuntimeError):
         fm(torch.zeros(2, 1012), [[0, 1], [1, 2]])
+
+
+def test_header_is_plain_c99_and_links_from_c(tmp_path):
+    """The boundary is a C ABI: the header compiles as strict C99 and a C program links against the library."""
+    import os
+    import shutil
+    if shutil.which("gcc") is None:
+        pytest.skip("gcc not available")
+    src = tmp_path / "abi.c"
+    src.write_text('#include "echr_b200.h"\n'
+                   'int main(void) { echr_config_t c; echr_sst_weights_t w; (void)c; (void)w;\n'
+                   '  return echr_abi_version() == ECHR_B200_ABI_VERSION ? 0 : 1; }\n')
+    inc = os.path.dirname(_lib.HEADER_PATH)
+    exe = tmp_path / "abi"
+    libdir = os.path.dirname(_lib.LIB_PATH)
+    subprocess.check_call(["gcc", "-std=c99", "-Wall", "-Wextra", "-pedantic", "-Werror", "-I", inc, str(src), "-o", str(exe),
+                           "-L", libdir, "-l:libechr_b200.so", "-Wl,-rpath," + libdir])
+    assert subprocess.run([str(exe)]).returncode == 0
