@@ -4,6 +4,7 @@ torch is used for device memory and streams only; every computation happens insi
 libechr_b200.so.  There is no fallback path: a missing library or a non-sm_100 device raises.
 """
 import ctypes
+import itertools
 
 import numpy as np
 import torch
@@ -36,22 +37,20 @@ class BatchLayout(object):
     """Host-side index arrays of a batch of independent videos (echr_batch_desc_t)."""
 
     def __init__(self, clip_counts, ind_lists, soi_lists):
+        # (flat C-level iteration: this runs once per batch inside a captioning job's submit loop)
         self.n_videos = len(clip_counts)
-        self.clip_offsets = _i32(np.concatenate([[0], np.cumsum(clip_counts)]))
-        ev_video, ev_s, ev_e, ev_ind = [], [], [], []
-        self.events_per_video = []
-        for v, (inds, sois) in enumerate(zip(ind_lists, soi_lists)):
-            if len(inds) != len(sois):
-                raise ValueError("video %d: ind_select_list and soi_select_list differ in length" % v)
-            self.events_per_video.append(len(sois))
-            for ind, soi in zip(inds, sois):
-                ev_video.append(v)
-                ev_s.append(int(soi[0]))
-                ev_e.append(int(soi[1]))
-                ev_ind.append(int(ind))
-        self.event_video, self.event_start = _i32(ev_video), _i32(ev_s)
-        self.event_end, self.event_ind = _i32(ev_e), _i32(ev_ind)
-        self.n_events = len(ev_video)
+        self.clip_offsets = np.zeros(self.n_videos + 1, dtype=np.int32)
+        np.cumsum(np.fromiter(clip_counts, dtype=np.int64, count=self.n_videos), out=self.clip_offsets[1:])
+        self.events_per_video = [len(s) for s in soi_lists]
+        if [len(i) for i in ind_lists] != self.events_per_video:
+            v = [len(i) == n for i, n in zip(ind_lists, self.events_per_video)].index(False)
+            raise ValueError("video %d: ind_select_list and soi_select_list differ in length" % v)
+        self.n_events = int(sum(self.events_per_video))
+        flat = itertools.chain.from_iterable
+        soi = np.fromiter(flat(flat(soi_lists)), dtype=np.int32, count=2 * self.n_events).reshape(-1, 2)
+        self.event_start, self.event_end = np.ascontiguousarray(soi[:, 0]), np.ascontiguousarray(soi[:, 1])
+        self.event_ind = np.fromiter(flat(ind_lists), dtype=np.int32, count=self.n_events)
+        self.event_video = np.repeat(np.arange(self.n_videos, dtype=np.int32), self.events_per_video)
         self.n_clips = int(self.clip_offsets[-1])
         self.n_pairs = int(sum(n * n for n in self.events_per_video))
 

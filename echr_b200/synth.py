@@ -82,20 +82,10 @@ class Video(object):
                 list(self.ind_select_list), [list(s) for s in self.soi_select_list])
 
 
-def make_video(seed, T=100, n_events=None, style="gt", K=256, bf16_features=False):
-    """Synthetic video `seed`: c3d ~ N(0,1) (the loader standardises, dataloader.py:49-51), tap_feats
-    ~ U(-1,1) (an LSTM output range, sst_model.py:36-38), lda = softmax(N(0,1)).
-    style 'gt'  : n in {3,4,5} (or n_events), s~U{0..T-2}, len~U{1..T/2}, e=min(s+len,T), ind=e-1
-                  (dataloader.py:496-499).
-    style 'sst' : n_events distinct proposals ending at clip n with k clips before it:
-                  soi=[n-k, n+1), ind=n, k < min(n+1, K) (eval_utils.py:278-284; K caps the span).
-    """
-    g = torch.Generator().manual_seed(1000 + seed)
-    c3d = torch.randn((T, 500), generator=g, dtype=torch.float32)
-    tap = torch.rand((T, 512), generator=g, dtype=torch.float32) * 2.0 - 1.0
-    lda = torch.softmax(torch.randn((100,), generator=g, dtype=torch.float32), 0)
-    if bf16_features:
-        c3d, tap, lda = round_bf16(c3d), round_bf16(tap), round_bf16(lda)
+def video_events(seed, T=100, n_events=None, style="gt", K=256):
+    """The proposals of synthetic video `seed` without its features: (ind_select_list, soi_select_list).  The
+    event generator (numpy RandomState) is independent of the feature generator (torch), so a job can lay out
+    its shards from the event counts of every video before any rank builds features."""
     rs = np.random.RandomState(1000 + seed)
     ind, soi = [], []
     if style == "gt":
@@ -119,6 +109,24 @@ def make_video(seed, T=100, n_events=None, style="gt", K=256, bf16_features=Fals
             ind.append(end)
     else:
         raise ValueError(style)
+    return ind, soi
+
+
+def make_video(seed, T=100, n_events=None, style="gt", K=256, bf16_features=False):
+    """Synthetic video `seed`: c3d ~ N(0,1) (the loader standardises, dataloader.py:49-51), tap_feats
+    ~ U(-1,1) (an LSTM output range, sst_model.py:36-38), lda = softmax(N(0,1)).
+    style 'gt'  : n in {3,4,5} (or n_events), s~U{0..T-2}, len~U{1..T/2}, e=min(s+len,T), ind=e-1
+                  (dataloader.py:496-499).
+    style 'sst' : n_events distinct proposals ending at clip n with k clips before it:
+                  soi=[n-k, n+1), ind=n, k < min(n+1, K) (eval_utils.py:278-284; K caps the span).
+    """
+    g = torch.Generator().manual_seed(1000 + seed)
+    c3d = torch.randn((T, 500), generator=g, dtype=torch.float32)
+    tap = torch.rand((T, 512), generator=g, dtype=torch.float32) * 2.0 - 1.0
+    lda = torch.softmax(torch.randn((100,), generator=g, dtype=torch.float32), 0)
+    if bf16_features:
+        c3d, tap, lda = round_bf16(c3d), round_bf16(tap), round_bf16(lda)
+    ind, soi = video_events(seed, T, n_events, style, K)
     return Video(tap, c3d, lda, ind, soi)
 
 

@@ -138,6 +138,40 @@ def init_state(n, hidden=512):
     return torch.zeros(3, n, hidden), torch.zeros(3, n, hidden)
 
 
+def position_embedding_f32(soi, rows=None):
+    """float32 [len(rows) or N, N, 512] position embedding of the given query rows (default: all).  For large N
+    (the reference's default topN = 1000, eval_utils.py:21) the float64 [N,N,512] intermediate of MA:39-41 is
+    4 GB, so big cases are evaluated in row tiles; the values are those of `position_embedding`."""
+    pos = position_matrix(soi)
+    if rows is not None:
+        pos = pos[rows]
+    return torch.from_numpy(position_embedding(pos)).to(torch.float32)
+
+
+def relation_encode_tiled(sd, feats, soi, tile=64):
+    """`relation_encode` evaluated in tiles of query events: same arithmetic per row (every reduction is over
+    the keys j of one query row i), bounded memory.  Used for N up to the reference's topN = 1000."""
+    p = "fusion_model."
+    q = p + "enc_attn."
+    n = feats.shape[0]
+    dh = D_MODEL // N_HEAD
+    x = F.linear(feats, sd[p + "event_emb.weight"], sd[p + "event_emb.bias"])
+    qd = F.linear(x, sd[q + "query_1.weight"], sd[q + "query_1.bias"]).reshape(n, N_HEAD, dh)
+    kd = F.linear(x, sd[q + "key_1.weight"], sd[q + "key_1.bias"]).reshape(n, N_HEAD, dh)
+    wo = sd[q + "linear_out_1.weight"].reshape(N_HEAD, dh, D_MODEL)
+    outs = []
+    for r0 in range(0, n, tile):
+        rows = np.arange(r0, min(n, r0 + tile))
+        pe = position_embedding_f32(soi, rows)  # [r,N,512]
+        hid = torch.tanh(F.linear(pe.reshape(-1, D_MODEL), sd[q + "pair_pos_fc1.weight"], sd[q + "pair_pos_fc1.bias"]))
+        w = F.linear(hid, sd[q + "pair_pos_fc2.weight"], sd[q + "pair_pos_fc2.bias"]).reshape(len(rows), n, N_HEAD).permute(0, 2, 1)
+        aff = torch.einsum("igd,jgd->igj", qd[r0:r0 + len(rows)], kd) * (1.0 / math.sqrt(float(dh)))
+        prob = torch.softmax(w * aff, dim=2)
+        mixed = torch.einsum("igj,jc->igc", prob, x)
+        outs.append(torch.einsum("igc,goc->igo", mixed, wo).reshape(len(rows), D_MODEL) + sd[q + "linear_out_1.bias"])
+    return torch.cat(outs, 0)
+
+
 # ------------------------------------------------------------------------------------------------
 # S: greedy sampling loop with the reference's bookkeeping (OldModel_NEW.py:139-187)
 # ------------------------------------------------------------------------------------------------
@@ -194,7 +228,8 @@ def caption_video(sd, tap_feats, c3d_feats, lda_feats, ind, soi, seq_length=30):
 # Beam search — THIS REPO'S SPEC (parity unpinned: the reference has no beam search,
 # OldModel_NEW.py:144-146).  All arithmetic is the pinned `decode_step`.
 # ------------------------------------------------------------------------------------------------
-def beam_search(sd, video, event, clip, mask, beam=3, seq_length=30, return_all=False):
+def beam_search(sd, video, event, clip, mask, beam=3, seq_length=30, return_all=False, step_fn=None,
+                return_trace=False):
     """Per event keep `beam` slots (decode rows n*beam+b).  Spec:
       * t=0: every slot is fed BOS (token 0) from the zero state; only slot 0 counts as live.
       * each step, every LIVE slot proposes its `beam` best next tokens (log-prob descending, equal
@@ -208,7 +243,12 @@ def beam_search(sd, video, event, clip, mask, beam=3, seq_length=30, return_all=
         for the next step (dead slots propose nothing and are refilled by the next selection).
       * always runs seq_length steps; result = best finished hypothesis.
     Returns (seq int64 [N,seq_length] zero padded, logp f32 [N,seq_length] zero padded incl. the EOS
-    term, score f32 [N])."""
+    term, score f32 [N]).
+    step_fn(it, ev, cl, mk, state) -> (logprobs, state): the step function to drive (default: this module's
+    pinned `decode_step`; bench.py passes the reference's own `get_logprobs_state`).
+    return_trace: additionally a list with one dict per step — `kept_tok` [N,beam,t+1] / `kept_score` [N,beam]
+    (the new slots), `reject` [N] (best score that was NOT kept, over all live x (V+1) proposals; -inf if
+    none) — what tests/helpers.check_beam uses to decide whether a differing row is excused by a near tie."""
     n = event.shape[0]
     rows = n * beam
     rep = lambda x: x.repeat_interleave(beam, 0)
@@ -224,11 +264,17 @@ def beam_search(sd, video, event, clip, mask, beam=3, seq_length=30, return_all=
     best_tok = torch.zeros(n, seq_length, dtype=torch.long)
     best_lp = torch.zeros(n, seq_length)
     done_all = [[] for _ in range(n)]
+    trace = []
     for t in range(seq_length):
-        logprobs, state = decode_step(sd, it, video, ev, cl, mk, state)
+        if step_fn is None:
+            logprobs, state = decode_step(sd, it, video, ev, cl, mk, state)
+        else:
+            logprobs, state = step_fn(it, ev, cl, mk, state)
         # per-row top-`beam`: sort is stable on (-value, index) through a two-key trick
         vals, idx = torch.sort(logprobs, dim=1, descending=True, stable=True)
+        next_val = vals[:, beam].reshape(n, beam)  # each row's best proposal outside its own top-`beam`
         vals, idx = vals[:, :beam].reshape(n, beam, beam), idx[:, :beam].reshape(n, beam, beam)
+        reject = torch.full((n,), -float("inf"))
         parent = torch.zeros(n, beam, dtype=torch.long)
         new_tok = torch.zeros(n, beam, dtype=torch.long)
         new_lp = torch.zeros(n, beam)
@@ -243,6 +289,10 @@ def beam_search(sd, video, event, clip, mask, beam=3, seq_length=30, return_all=
                     cand.append((-float(score[e, b] + lp), b, r, int(idx[e, b, r]), float(lp),
                                  float(score[e, b] + lp)))
             cand.sort(key=lambda c: (c[0], c[1], c[2]))
+            if return_trace:
+                outside = [float(score[e, b] + next_val[e, b]) for b in range(beam) if bool(live[e, b])]
+                outside += [c[5] for c in cand[beam:]]
+                reject[e] = max(outside) if outside else -float("inf")
             for k in range(beam):
                 _, b, r, tok, lp, tot = cand[k]
                 parent[e, k], new_tok[e, k], new_lp[e, k], new_score[e, k] = b, tok, lp, tot
@@ -254,6 +304,8 @@ def beam_search(sd, video, event, clip, mask, beam=3, seq_length=30, return_all=
         hist_tok[:, :, t] = new_tok
         hist_lp[:, :, t] = new_lp
         score = new_score
+        if return_trace:
+            trace.append(dict(kept_tok=hist_tok[:, :, :t + 1].clone(), kept_score=score.clone(), reject=reject))
         fin = (new_tok == 0) | (t == seq_length - 1)
         for e in range(n):
             for k in range(beam):
@@ -266,9 +318,12 @@ def beam_search(sd, video, event, clip, mask, beam=3, seq_length=30, return_all=
                         best_lp[e] = hist_lp[e, k]
         live = ~fin
         it = new_tok.reshape(-1)
+    out = (best_tok, best_lp, best_score)
     if return_all:
-        return best_tok, best_lp, best_score, done_all
-    return best_tok, best_lp, best_score
+        out = out + (done_all,)
+    if return_trace:
+        out = out + (trace,)
+    return out
 
 
 def caption_video_beam(sd, tap_feats, c3d_feats, lda_feats, ind, soi, beam=3, seq_length=30):

@@ -1,9 +1,11 @@
-"""Loads the UNMODIFIED reference hot path from /root/reference for differential testing (authoring
-container only; the GPU box has no /root/reference and uses tests/golden/ instead).
+"""Loads the UNMODIFIED reference hot path for differential testing and as the timed CPU baseline.
 
-Test infrastructure — never imported by the product.  Nothing is copied: the reference sources are
-read where they lie, three py3/CPU incompatibilities are patched in memory, and the modules are
-executed under their own names:
+Two sources, in this order: /root/reference (authoring container: sources read where they lie, patched in
+memory) or oracle/_ref/ (staged, already patched, by oracle/make_ref.py; git-ignored, travels to the GPU box,
+which has no /root/reference).  tests/golden/ carries the pin where neither exists.
+
+Test infrastructure — never imported by the product.  Three py3/CPU incompatibilities and one print are
+patched, and the modules are executed under their own names:
   * models/MA_attention_8_NEW.py:41   hard `.cuda()` on the position embedding -> follow `feats`
   * models/MA_attention_8_NEW.py:125,133  py2 integer `/` in `.view(...)`      -> `//`
   * CaptionGenerator.py:43            per-call `print` of timings               -> dropped
@@ -13,11 +15,22 @@ import os
 import sys
 import types
 
+STAGED_ROOT = os.path.join(os.path.dirname(os.path.abspath(__file__)), "_ref")
 REF_ROOT = os.environ.get("ECHR_REFERENCE_ROOT", "/root/reference")
+if not os.path.isfile(os.path.join(REF_ROOT, "CaptionGenerator.py")) and os.path.isfile(os.path.join(STAGED_ROOT, "PATCHED")):
+    REF_ROOT = STAGED_ROOT
+PREPATCHED = os.path.isfile(os.path.join(REF_ROOT, "PATCHED"))
 
 
 def available():
     return os.path.isfile(os.path.join(REF_ROOT, "CaptionGenerator.py"))
+
+
+def source():
+    """'checkout' (sources under /root/reference), 'staged' (oracle/_ref) or None."""
+    if not available():
+        return None
+    return "staged" if PREPATCHED else "checkout"
 
 
 _PATCHES = {
@@ -37,7 +50,7 @@ _loaded = None
 def _exec_patched(modname, relpath, package=None):
     path = os.path.join(REF_ROOT, relpath)
     src = open(path).read()
-    for old, new in _PATCHES.get(relpath, []):
+    for old, new in ([] if PREPATCHED else _PATCHES.get(relpath, [])):
         if old not in src:
             raise RuntimeError("reference changed: %r not found in %s" % (old, relpath))
         src = src.replace(old, new)

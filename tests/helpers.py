@@ -61,3 +61,111 @@ def video_tuple(v, device=None):
     mv = (lambda t: t.to(device)) if device is not None else (lambda t: t)
     return (mv(v.tap_feats), mv(v.c3d_feats), mv(v.lda_feats), list(v.ind_select_list),
             [list(s) for s in v.soi_select_list])
+
+
+def labels_of(seq):
+    """[N,S] tokens -> [N,S+1] labels with the BOS column the teacher-forced forward expects."""
+    seq = torch.as_tensor(np.asarray(seq)).long()
+    return torch.cat([torch.zeros(seq.shape[0], 1, dtype=torch.long), seq], 1)
+
+
+def batch_of(vids, device=None, pin=False):
+    """(BatchLayout, c3d, tap, lda) of a list of synth videos, concatenated."""
+    from echr_b200.engine import BatchLayout
+    lay = BatchLayout([v.c3d_feats.shape[0] for v in vids], [v.ind_select_list for v in vids],
+                      [v.soi_select_list for v in vids])
+    ts = (torch.cat([v.c3d_feats for v in vids]).contiguous(), torch.cat([v.tap_feats for v in vids]).contiguous(),
+          torch.stack([v.lda_feats for v in vids]).contiguous())
+    if pin:
+        ts = tuple(t.pin_memory() for t in ts)
+    if device is not None:
+        ts = tuple(t.to(device) for t in ts)
+    return (lay,) + ts
+
+
+def oracle_greedy_rows(sd, vids, seq_length=30):
+    """Oracle greedy decode + teacher-forced log-probs of a list of videos (one video per call, like the
+    reference), padded to full width: (tokens int64 [rows,S], logp [rows,S], per_video) with per_video a list of
+    (events, columns the reference returned, teacher-forced log-probs [events, columns, V+1] or None)."""
+    from oracle import echr_oracle as O
+    toks, lps, per_video = [], [], []
+    for v in vids:
+        ctx = O.build_context(sd, v.tap_feats, v.c3d_feats, v.lda_feats, v.ind_select_list, v.soi_select_list)
+        s, l = O.greedy_decode(sd, *ctx, seq_length=seq_length)
+        n = v.n_events
+        t = torch.zeros(n, seq_length, dtype=torch.long)
+        p = torch.zeros(n, seq_length)
+        c, tf = 0, None
+        if len(s):
+            c = s.shape[1]
+            t[:, :c], p[:, :c] = s, l
+            tf = O.teacher_forced_logprobs(sd, *ctx, labels_of(s))
+        toks.append(t)
+        lps.append(p)
+        per_video.append((n, c, tf))
+    return torch.cat(toks), torch.cat(lps), per_video
+
+
+def check_greedy_rows(got_tok, got_lp, want_tok, want_lp, per_video, lp_tol, what=""):
+    """Rows of the CUDA path (full width, tokens masked after EOS) against oracle_greedy_rows(): tokens under the
+    near-tie rule over the columns the reference returned; returned log-probs of rows that did not diverge
+    within lp_tol.  Returns (excused rows, max |dlogp| over the compared entries)."""
+    got_tok, got_lp = np.asarray(got_tok), np.asarray(got_lp)
+    want_tok, want_lp = want_tok.numpy(), want_lp.numpy()
+    excused, worst, r0 = 0, 0.0, 0
+    for n, c, tf in per_video:
+        if tf is None:  # the reference returned ([], []): every row's first token is EOS
+            assert (got_tok[r0:r0 + n, 0] == 0).all(), what
+            r0 += n
+            continue
+        top2 = tf.topk(2, dim=2)[0].numpy()
+        for r in range(n):
+            g, w = got_tok[r0 + r, :c], want_tok[r0 + r, :c]
+            diff = np.nonzero(g != w)[0]
+            if diff.size:
+                t = int(diff[0])
+                gap = float(top2[r, t, 0] - top2[r, t, 1])
+                assert gap < NEAR_TIE, "%s row %d diverges at step %d (got %d want %d) with top-2 gap %.3e" % (
+                    what, r0 + r, t, g[t], w[t], gap)
+                excused += 1
+                continue
+            d = float(np.abs(got_lp[r0 + r, :c] - want_lp[r0 + r, :c]).max())
+            worst = max(worst, d)
+            assert d < lp_tol, "%s row %d: |dlogp| %.3e" % (what, r0 + r, d)
+        r0 += n
+    return excused, worst
+
+
+def beam_len(row):
+    """Tokens of a zero-padded beam hypothesis including its EOS."""
+    z = np.nonzero(np.asarray(row) == 0)[0]
+    return int(z[0]) + 1 if z.size else len(row)
+
+
+def check_beam(got_tok, want_tok, want_score, trace, cum_got, what=""):
+    """Beam rule (BASELINE north_star, applied to cumulative scores): a returned hypothesis must be the oracle's
+    unless the FIRST decision that separates them is a near tie in the oracle's own arithmetic:
+      * the first step t at which the oracle's beam does not keep got[:t+1]: the worst kept score at t must be
+        within NEAR_TIE of the oracle's score of got[:t+1] (`cum_got[r,t]`, teacher-forced along got), or
+      * got stays in the oracle's beam to its end: it was a finished hypothesis there, and the oracle's best
+        must be within NEAR_TIE of got's score.
+    trace = oracle beam_search(..., return_trace=True)[-1].  Returns (identical rows, excused rows)."""
+    got_tok, want_tok = np.asarray(got_tok), np.asarray(want_tok)
+    same = excused = 0
+    for r in range(want_tok.shape[0]):
+        if (got_tok[r] == want_tok[r]).all():
+            same += 1
+            continue
+        L = beam_len(got_tok[r])
+        for t in range(L):
+            kept = trace[t]["kept_tok"][r].numpy()  # [beam, t+1]
+            if not (kept == got_tok[r, :t + 1][None, :]).all(1).any():
+                gap = float(trace[t]["kept_score"][r].min()) - float(cum_got[r, t])
+                assert gap < NEAR_TIE, "%s row %d: prefix dropped by the oracle at step %d with score gap %.3e" % (
+                    what, r, t, gap)
+                break
+        else:
+            gap = float(want_score[r]) - float(cum_got[r, L - 1])
+            assert gap < NEAR_TIE, "%s row %d: finished hypothesis loses to the oracle's best by %.3e" % (what, r, gap)
+        excused += 1
+    return same, excused

@@ -1,0 +1,236 @@
+"""GPU parity tests at the shapes and schedules every benchmark number rests on (collected first: `test_0_`).
+
+Each test drives the C-ABI path and compares it with oracle/echr_oracle.py (pinned to the reference, see
+tests/test_oracle_vs_reference.py and tests/golden/) on the same seeded weights and inputs:
+  * cfg2 whole (BASELINE configs[1]: 64 videos / 251 events) in the benched precision (f16) through a
+    CaptionPipeline of depth 4 — the shared-GPU schedule of bench.py — from device and from host buffers;
+  * >= 1024 decode rows: the persistent 128 x 256 GEMM with its LSTM / logit epilogues and the streaming attention;
+  * one cfg3 video (100 SST-style proposals, beam 3) and the whole cfg3 batch (9600 beam rows);
+  * one cfg4 video (400 clips, 200 proposals, spans up to 256 clips).
+Tolerances are BASELINE.json's: tokens identical except where the oracle's top-2 (greedy) / kept-vs-dropped (beam)
+gap is below 1e-3; per-step log-probs within 1e-4 (fp32-grade) or 2e-2 (16-bit operands)."""
+import numpy as np
+import pytest
+import torch
+
+import helpers
+from echr_b200 import synth
+from echr_b200.caption_generator import CaptionGenerator
+from echr_b200.config import echr_opt
+from echr_b200.engine import CaptionPipeline
+from oracle import echr_oracle as O
+
+pytestmark = pytest.mark.gpu
+torch.set_grad_enabled(False)
+DEV = "cuda:0"
+# per-step log-prob tolerance (north_star) and the bound this implementation actually holds
+LOGP_ALLOWED = {"fp32": 1e-4, "bf16w": 1e-4, "f16": 2e-2}
+LOGP_HELD = {"fp32": 1e-4, "bf16w": 1e-4, "f16": 2e-3}
+_models = {}
+
+
+def model(precision):
+    """fp32 precision on the fp32 checkpoint; bf16w / f16 on the bf16-rounded checkpoint (both sides of a 16-bit
+    run use the same rounded weights and features)."""
+    if precision not in _models:
+        m = CaptionGenerator(echr_opt(), precision=precision)
+        m.load_state_dict(helpers.state_dict("fp32" if precision == "fp32" else "bf16w"), strict=True)
+        _models[precision] = m.to(DEV)
+    return _models[precision]
+
+
+def sd_of(precision):
+    return helpers.state_dict("fp32" if precision == "fp32" else "bf16w")
+
+
+def tf_check(eng, want_tok, per_video, precision, rows=None):
+    """Teacher-forced log-probs of the staged batch along the ORACLE's tokens vs the oracle's, over the steps the
+    reference evaluates (OldModel_NEW.py:98-130).  rows: only the first `rows` rows are compared."""
+    tf = eng.teacher_forced(helpers.labels_of(want_tok).to(DEV))
+    worst, r0 = 0.0, 0
+    for n, c, want in per_video:
+        if rows is not None and r0 >= rows:
+            break
+        if want is not None:
+            got = tf[r0:r0 + n, :want.shape[1]].cpu()
+            worst = max(worst, float((got - want).abs().max()))
+        r0 += n
+    assert worst < LOGP_HELD[precision] <= LOGP_ALLOWED[precision], worst
+    return worst
+
+
+# ------------------------------------------------------------------------------------------------ cfg2, benched schedule
+def test_cfg2_f16_four_lanes_matches_oracle():
+    precision = "f16"
+    sd = sd_of(precision)
+    vids, _ = synth.make_workload("cfg2", bf16_features=True)
+    assert len(vids) == 64
+    want_tok, want_lp, per_video = helpers.oracle_greedy_rows(sd, vids)
+    m = model(precision)
+    lay, d_c3d, d_tap, d_lda = helpers.batch_of(vids, DEV)
+    _, h_c3d, h_tap, h_lda = helpers.batch_of(vids, pin=True)
+    pipe = CaptionPipeline(m.engine, depth=4)
+    try:
+        # every lane sees the shape three times: eager, captured, replayed (bench.py's steady state)
+        tickets = []
+        for i in range(12):
+            tickets.append(pipe.submit(lay, d_c3d, d_tap, d_lda, beam=1))
+            if i >= 8:
+                tok, lp, _ = tickets[-1].wait()
+                torch.cuda.synchronize()
+                exc, worst = helpers.check_greedy_rows(tok.cpu().numpy(), lp.cpu().numpy(), want_tok, want_lp, per_video,
+                                                       LOGP_HELD[precision], "cfg2/f16/lane%d" % (i % 4))
+                print("cfg2 f16 4 lanes (device buffers): %d of %d rows excused by a near tie, max |dlogp| %.2e"
+                      % (exc, lay.n_events, worst))
+        dev_tok = tok.cpu().clone()
+        for i in range(8):
+            t = pipe.submit(lay, h_c3d, h_tap, h_lda, beam=1)
+        tok, lp, _ = t.wait()
+        assert torch.equal(tok, dev_tok), "host-buffer path differs from the device-buffer path"
+        # teacher-forced log-probs with the lanes' (shared-GPU) kernel schedule
+        lane = pipe.lanes[1]
+        lane.set_inputs(lay, d_c3d, d_tap, d_lda)
+        lane.encode()
+        worst = tf_check(lane, want_tok, per_video, precision)
+        print("cfg2 f16 teacher-forced max |dlogp| vs oracle = %.2e (allowed %.0e)" % (worst, LOGP_ALLOWED[precision]))
+    finally:
+        pipe.close()
+
+
+# ------------------------------------------------------------------------------------------------ >= 1024 rows
+@pytest.mark.parametrize("precision", ["f16", "bf16w"])
+def test_throughput_regime_matches_oracle(precision):
+    """300 GT-style videos (~1190 rows >= 1024): persistent GEMM kernels + un-hoisted context k-blocks + streaming
+    attention.  Oracle greedy + teacher-forced on the first 40 videos (rows are independent of the batch)."""
+    sd = sd_of(precision)
+    vids, _ = synth.make_workload("cfg2", n_videos=300, first_seed=5000, bf16_features=True)
+    sub = vids[:40]
+    want_tok, want_lp, per_video = helpers.oracle_greedy_rows(sd, sub)
+    n_sub = want_tok.shape[0]
+    m = model(precision)
+    lay, c3d, tap, lda = helpers.batch_of(vids, DEV)
+    assert lay.n_events >= 1024
+    for _ in range(3):  # eager, captured, replayed
+        tok, lp, _ = m.engine.caption_device(lay, c3d, tap, lda, beam=1)
+    exc, worst = helpers.check_greedy_rows(tok[:n_sub].cpu().numpy(), lp[:n_sub].cpu().numpy(), want_tok, want_lp,
+                                           per_video, LOGP_HELD[precision], "rows%d/%s" % (lay.n_events, precision))
+    # teacher-forced: oracle tokens on the sub-sample rows, the path's own tokens elsewhere
+    labels = tok.cpu().long()
+    labels[:n_sub] = want_tok
+    m.engine.set_inputs(lay, c3d, tap, lda)
+    m.engine.encode()
+    w = tf_check(m.engine, labels, per_video, precision, rows=n_sub)
+    print("%d rows %s: %d of %d sampled rows excused, max |dlogp| %.2e, teacher-forced %.2e"
+          % (lay.n_events, precision, exc, n_sub, worst, w))
+    # the same videos alone (latency-regime kernels) give the same tokens except at near ties
+    tok_small, _, _ = m.engine.caption_device(*helpers.batch_of(sub, DEV), beam=1)
+    helpers.check_greedy_rows(tok_small.cpu().numpy(), want_lp.numpy(), want_tok, want_lp, per_video, 1.0, "sub-sample alone")
+
+
+# ------------------------------------------------------------------------------------------------ cfg3
+def _beam_case(precision, vids_gpu, vids_oracle, beam=3):
+    sd = sd_of(precision)
+    m = model(precision)
+    lay, c3d, tap, lda = helpers.batch_of(vids_gpu, DEV)
+    for _ in range(2):
+        tok, lp, score = m.engine.caption_device(lay, c3d, tap, lda, beam=beam)
+    tok, lp, score = tok.cpu(), lp.cpu(), score.cpu()
+    r0 = 0
+    stats = [0, 0, 0]
+    for v in vids_oracle:
+        n = v.n_events
+        ctx = O.build_context(sd, v.tap_feats, v.c3d_feats, v.lda_feats, v.ind_select_list, v.soi_select_list)
+        t_ref, l_ref, s_ref, trace = O.beam_search(sd, *ctx, beam=beam, return_trace=True)
+        g_tok, g_lp, g_score = tok[r0:r0 + n], lp[r0:r0 + n], score[r0:r0 + n]
+        # the returned log-probs are the teacher-forced ones of the returned hypothesis (oracle arithmetic)
+        tf = O.teacher_forced_logprobs(sd, *ctx, helpers.labels_of(g_tok))
+        steps = tf.shape[1]
+        picked = torch.gather(tf, 2, g_tok.long()[:, :steps].unsqueeze(2)).squeeze(2)
+        valid = torch.zeros(n, steps, dtype=torch.bool)
+        for r in range(n):
+            valid[r, :min(steps, helpers.beam_len(g_tok[r].numpy()))] = True
+        picked = picked * valid
+        assert float((picked - g_lp[:, :steps] * valid).abs().max()) < LOGP_HELD[precision]
+        cum = torch.cumsum(picked, 1).numpy()
+        last = np.array([min(steps, helpers.beam_len(g_tok[r].numpy())) - 1 for r in range(n)])
+        assert np.abs(cum[np.arange(n), last] - g_score.numpy()).max() < 30 * LOGP_HELD[precision]
+        same, exc = helpers.check_beam(g_tok.numpy(), t_ref.numpy(), s_ref.numpy(), trace, cum, "beam%d/%s" % (beam, precision))
+        stats[0] += same
+        stats[1] += exc
+        stats[2] += n
+        r0 += n
+    return stats
+
+
+@pytest.mark.parametrize("precision", ["fp32", "f16"])
+def test_cfg3_video_relation_encoder_and_beam3(precision):
+    """One cfg3 video: 100 SST-style proposals (100 x 100 pairs x 16 heads), greedy and beam = 3."""
+    sd = sd_of(precision)
+    v = synth.make_video(7000, T=100, n_events=100, style="sst", bf16_features=(precision != "fp32"))
+    m = model(precision)
+    want_tok, want_lp, per_video = helpers.oracle_greedy_rows(sd, [v])
+    lay, c3d, tap, lda = helpers.batch_of([v], DEV)
+    tok, lp, _ = m.engine.caption_device(lay, c3d, tap, lda, beam=1)
+    ev = m.engine.event_context().cpu()
+    ctx = O.build_context(sd, v.tap_feats, v.c3d_feats, v.lda_feats, v.ind_select_list, v.soi_select_list)
+    ev_err = float((ev - ctx[1]).abs().max())
+    assert ev_err < (2e-5 if precision == "fp32" else 2e-3), ev_err
+    exc, worst = helpers.check_greedy_rows(tok.cpu().numpy(), lp.cpu().numpy(), want_tok, want_lp, per_video,
+                                           LOGP_HELD[precision], "cfg3 video/" + precision)
+    m.engine.set_inputs(lay, c3d, tap, lda)
+    m.engine.encode()
+    w = tf_check(m.engine, want_tok, per_video, precision)
+    same, bexc, n = _beam_case(precision, [v], [v])
+    print("cfg3 video %s: event ctx %.2e; greedy %d excused, |dlogp| %.2e, teacher-forced %.2e; beam 3: %d identical, "
+          "%d excused of %d" % (precision, ev_err, exc, worst, w, same, bexc, n))
+
+
+def test_cfg3_whole_batch_beam3_9600_rows():
+    """BASELINE configs[2] whole: 32 videos x 100 proposals x beam 3 = 9600 decode rows (f16, the benched precision);
+    oracle beam search on the first two videos."""
+    vids, w = synth.make_workload("cfg3", bf16_features=True)
+    assert len(vids) == 32 and w["beam"] == 3
+    same, exc, n = _beam_case("f16", vids, vids[:2])
+    print("cfg3 whole (9600 rows) f16 beam 3: %d identical, %d excused of %d sampled rows" % (same, exc, n))
+
+
+# ------------------------------------------------------------------------------------------------ cfg4
+@pytest.mark.parametrize("precision", ["fp32", "f16"])
+def test_cfg4_video_long_spans(precision):
+    """One cfg4 video: T = 400 clips, 200 SST-style proposals with spans up to K = 256 clips."""
+    sd = sd_of(precision)
+    v = synth.make_video(7100, T=400, n_events=200, style="sst", bf16_features=(precision != "fp32"))
+    assert max(e - s for s, e in v.soi_select_list) > 200
+    m = model(precision)
+    want_tok, want_lp, per_video = helpers.oracle_greedy_rows(sd, [v])
+    lay, c3d, tap, lda = helpers.batch_of([v], DEV)
+    tok, lp, _ = m.engine.caption_device(lay, c3d, tap, lda, beam=1)
+    ev = m.engine.event_context().cpu()
+    ctx = O.build_context(sd, v.tap_feats, v.c3d_feats, v.lda_feats, v.ind_select_list, v.soi_select_list)
+    ev_err = float((ev - ctx[1]).abs().max())
+    assert ev_err < (2e-5 if precision == "fp32" else 2e-3), ev_err
+    exc, worst = helpers.check_greedy_rows(tok.cpu().numpy(), lp.cpu().numpy(), want_tok, want_lp, per_video,
+                                           LOGP_HELD[precision], "cfg4 video/" + precision)
+    m.engine.set_inputs(lay, c3d, tap, lda)
+    m.engine.encode()
+    w = tf_check(m.engine, want_tok, per_video, precision)
+    print("cfg4 video %s: event ctx %.2e; greedy %d of 200 excused, |dlogp| %.2e, teacher-forced %.2e"
+          % (precision, ev_err, exc, worst, w))
+
+
+def test_cfg4_whole_batch_matches_single_videos():
+    """BASELINE configs[3] whole (16 videos, 3200 rows, f16) against the same videos decoded one per call (whose
+    kernels the test above pins to the oracle): tokens equal except at near ties of the oracle on video 0."""
+    vids, _ = synth.make_workload("cfg4", bf16_features=True)
+    m = model("f16")
+    lay, c3d, tap, lda = helpers.batch_of(vids, DEV)
+    for _ in range(2):
+        tok, lp, _ = m.engine.caption_device(lay, c3d, tap, lda, beam=1)
+    tok, lp = tok.cpu(), lp.cpu()
+    want_tok, want_lp, per_video = helpers.oracle_greedy_rows(sd_of("f16"), vids[:1])
+    exc, worst = helpers.check_greedy_rows(tok[:200].numpy(), lp[:200].numpy(), want_tok, want_lp, per_video,
+                                           LOGP_HELD["f16"], "cfg4 whole")
+    print("cfg4 whole f16: video 0 vs oracle: %d of 200 excused, |dlogp| %.2e" % (exc, worst))
+    single = m.engine.caption_device(*helpers.batch_of(vids[3:4], DEV), beam=1)[0].cpu()
+    agree = float((single == tok[600:800]).all(1).float().mean())
+    assert agree > 0.9, agree

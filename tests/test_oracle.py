@@ -5,6 +5,7 @@ import pytest
 import torch
 
 import helpers
+from echr_b200 import synth
 from oracle import echr_oracle as O
 
 torch.set_grad_enabled(False)
@@ -68,3 +69,35 @@ def test_greedy_empty_and_trim():
     v = helpers.case_video("cfg1")
     seq, logp = O.caption_video(sd, v.tap_feats, v.c3d_feats, v.lda_feats, v.ind_select_list, v.soi_select_list)
     assert seq == [] and logp == []
+
+
+def test_regime_helpers_accept_the_oracle_and_reject_a_wrong_row():
+    """The checkers of tests/test_0_regimes_gpu.py on CPU: the oracle's own output passes; a row changed at a step
+    with a clear top-2 gap / a clearly worse beam hypothesis is refused."""
+    import pytest
+    sd = helpers.state_dict("fp32")
+    vids = [synth.make_video(300 + i, n_events=n) for i, n in enumerate((3, 4))]
+    tok, lp, per_video = helpers.oracle_greedy_rows(sd, vids)
+    exc, worst = helpers.check_greedy_rows(tok.numpy(), lp.numpy(), tok, lp, per_video, 1e-6)
+    assert exc == 0 and worst == 0.0
+    bad = tok.numpy().copy()
+    top2 = per_video[0][2].topk(2, dim=2)[0].numpy()
+    t = int(np.argmax(top2[0, :, 0] - top2[0, :, 1]))  # the clearest decision of row 0
+    bad[0, t] = (bad[0, t] + 1) % 5748
+    with pytest.raises(AssertionError):
+        helpers.check_greedy_rows(bad, lp.numpy(), tok, lp, per_video, 1e-6)
+    v = vids[1]
+    ctx = O.build_context(sd, v.tap_feats, v.c3d_feats, v.lda_feats, v.ind_select_list, v.soi_select_list)
+    t_ref, l_ref, s_ref, trace = O.beam_search(sd, *ctx, beam=3, return_trace=True)
+    cum = torch.cumsum(l_ref, 1).numpy()
+    assert helpers.check_beam(t_ref.numpy(), t_ref.numpy(), s_ref.numpy(), trace, cum) == (4, 0)
+    # the greedy hypothesis instead of the beam's best: refused unless it is the same or a near tie
+    g_tok = tok[3:7].numpy()
+    if not (g_tok == t_ref.numpy()).all():
+        tf = O.teacher_forced_logprobs(sd, *ctx, helpers.labels_of(g_tok))
+        picked = torch.gather(tf, 2, torch.as_tensor(g_tok)[:, :tf.shape[1]].unsqueeze(2)).squeeze(2)
+        cum_g = np.zeros((4, 30), np.float32)
+        cum_g[:, :tf.shape[1]] = torch.cumsum(picked, 1).numpy()
+        cum_g[:, tf.shape[1]:] = cum_g[:, tf.shape[1] - 1:tf.shape[1]]
+        with pytest.raises(AssertionError):
+            helpers.check_beam(g_tok, t_ref.numpy(), s_ref.numpy(), trace, cum_g)

@@ -1,0 +1,34 @@
+# One GPU-box pass of the round: parity tests, the driver's bench line, the other configurations, a PCIe probe and
+# the ncu launch list of a (shortened) bench command.   usage: bash tools/gpu_round.sh <tag> [tests|bench|ncu ...]
+TAG=${1:-run}; shift
+WHAT=${@:-tests bench ncu}
+O=gpurun_out/$TAG
+mkdir -p $O
+for w in $WHAT; do case $w in
+tests)
+  timeout 1500 python -m pytest tests -m gpu -q --tb=short -p no:cacheprovider -rA > $O/pytest.log 2>&1; echo "pytest exit=$?" >> $O/pytest.log ;;
+bench)
+  timeout 900 python bench.py > $O/bench_cfg5.json 2> $O/bench_cfg5.err
+  timeout 600 python bench.py --impl reference --steps 3 --warmup 1 > $O/bench_ref.json 2> $O/bench_ref.err
+  timeout 600 python bench.py --workload cfg2 --batch-videos 64 --no-cpu-baseline > $O/bench_cfg2.json 2> $O/bench_cfg2.err
+  timeout 600 python bench.py --workload cfg3 --steps 5 --no-cpu-baseline > $O/bench_cfg3.json 2> $O/bench_cfg3.err
+  timeout 600 python bench.py --workload cfg4 --steps 5 --no-cpu-baseline > $O/bench_cfg4.json 2> $O/bench_cfg4.err
+  python - > $O/pcie.txt 2>&1 <<'PY'
+import torch, time
+h = torch.empty(256 << 20, dtype=torch.uint8).pin_memory(); d = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
+for name, a, b in (("h2d", d, h), ("d2h", h, d)):
+    for _ in range(2): a.copy_(b, non_blocking=True)
+    torch.cuda.synchronize(); t0 = time.perf_counter()
+    for _ in range(10): a.copy_(b, non_blocking=True)
+    torch.cuda.synchronize(); print(name, "%.1f GB/s" % (10 * 0.268435456 / (time.perf_counter() - t0)))
+PY
+  ;;
+sweep)
+  for bv in 128 256 1024; do timeout 600 python bench.py --batch-videos $bv --steps 10 --no-cpu-baseline --no-second-beam > $O/sweep_bv$bv.json 2> $O/sweep_bv$bv.err; done
+  for fl in 2 3; do timeout 600 python bench.py --in-flight $fl --steps 10 --no-cpu-baseline --no-second-beam > $O/sweep_fl$fl.json 2> $O/sweep_fl$fl.err; done ;;
+ncu)
+  CMD="python bench.py --videos 1024 --steps 1 --warmup 1 --no-cpu-baseline --no-second-beam"
+  $CMD > $O/ncu_plain.json 2> $O/ncu_plain.err &&
+  timeout 1200 ncu --metrics gpu__time_duration.sum --clock-control none -c 6000 --csv --log-file $O/launches.csv $CMD > $O/ncu_launches.log 2>&1 ;;
+esac; done
+echo done
