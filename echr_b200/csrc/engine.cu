@@ -108,22 +108,12 @@ static const char* fill_problem(GemmProblem& pb, const GemmSpec& s, int a_terms,
 static int gemm2_min_rows() {
   static int v = -1;
   if (v < 0) {
-    const char* e = getenv("ECHR_GEMM2_MIN_ROWS");
+    const char* e = knob("ECHR_GEMM2_MIN_ROWS");
     v = e ? atoi(e) : 1024;
   }
   return v;
 }
 static bool use_gemm2(int rows, int n, int block_n) { return block_n == 128 && n >= GEMM2_BLOCK_N && rows >= gemm2_min_rows(); }
-static int num_sms() {
-  static int n = 0;
-  if (n == 0) {
-    int dev = 0;
-    cudaGetDevice(&dev);
-    cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev);
-    if (n <= 0) n = 148;
-  }
-  return n;
-}
 // Cluster split-K in the latency regime (ECHR_KSPLIT bit 0: gate GEMMs, bit 1: logit GEMM), used while the
 // split launch still fits the SMs in one wave.  Default: gates only — measured on cfg2 (251 rows) the gate
 // launch gains 1.3 us per step, while the logit launch (128 x 256 tiles, 64 KB of partial sums per CTA over
@@ -131,7 +121,7 @@ static int num_sms() {
 static int ksplit_mask() {
   static int v = -1;
   if (v < 0) {
-    const char* e = getenv("ECHR_KSPLIT");
+    const char* e = knob("ECHR_KSPLIT");
     v = e ? atoi(e) : 1;
   }
   return v;
@@ -148,9 +138,14 @@ static int len_bucket(int max_len) {
 // in the throughput regime, where the persistent kernel is bound by the row-per-thread gathers of its epilogue
 // and the tensor pipe has room (ECHR_HOIST_CTX=0/1 forces).
 static bool hoist_context(int rows) {
-  static const int forced = getenv("ECHR_HOIST_CTX") ? atoi(getenv("ECHR_HOIST_CTX")) : -1;
+  static const int forced = knob("ECHR_HOIST_CTX") ? atoi(knob("ECHR_HOIST_CTX")) : -1;
   if (forced >= 0) return forced != 0;
   return rows < gemm2_min_rows();
+}
+// Greedy decode with the attention of step t+1 on extra warps of the persistent logit GEMM of step t
+// (single-plane precision, throughput regime).
+static bool fused_attention(const echr_batch* b, int rows) {
+  return b->model->cfg.a_terms == 1 && use_gemm2(rows, b->model->V1, 128);
 }
 static int m_tiles_of(int rows) { return (rows + GEMM_BLOCK_M - 1) / GEMM_BLOCK_M; }
 // logit GEMM as 128 x 256 tiles shared by CTA pairs (23 x 2 CTAs per 128 rows at the ECHR vocabulary)
@@ -169,7 +164,7 @@ int run_gemm(const GemmSpec* specs, int groups, int a_terms, int w_terms, int bl
              int topk, cudaStream_t st, const char* what, echr_batch* tb, int kind) {
   GemmParams P;
   memset(&P, 0, sizeof(P));
-  static const int pdl_late = getenv("ECHR_PDL_LATE") ? atoi(getenv("ECHR_PDL_LATE")) : 1;
+  static const int pdl_late = knob("ECHR_PDL_LATE") ? atoi(knob("ECHR_PDL_LATE")) : 1;
   P.pdl_late = pdl_late;
   if (tb != nullptr && tb->trace_on == 1) { P.trace = tb->trace; P.trace_detail = tb->trace_detail; P.trace_slot = trace_next(tb, kind); }
   int max_m = 0, max_n = 0, min_n = 1 << 30;
@@ -185,6 +180,7 @@ int run_gemm(const GemmSpec* specs, int groups, int a_terms, int w_terms, int bl
     if (gx > grid_x) grid_x = gx;
   }
   const bool two = !any_split && use_gemm2(max_m, min_n, block_n);
+  if (two && groups == 1 && specs[0].att != nullptr) P.att = *specs[0].att;
   for (int g = 0; g < groups; ++g) {
     const char* err = fill_problem(P.prob[g], specs[g], a_terms, w_terms, two ? GEMM2_BLOCK_N : block_n);
     if (err) return set_error(ECHR_ERR_CUDA, "%s: %s", what, err);
@@ -379,18 +375,17 @@ static void batch_layout(echr_batch* b, Arena& a) {
   b->vid_first = ints + 7 * c.max_events;
   b->vid_n = b->vid_first + c.max_videos;
   b->clip_pl = a.planes(ap, c.max_clips, CLIP_PAD);
-  if (m->cfg.clip_bf16) {
-    b->proj_bf = a.take<bf16>((size_t)c.max_clips * HID);
+  if (ap == 1) {
+    b->proj_h = a.take<bf16>((size_t)c.max_clips * HID);
     b->proj_f32 = nullptr;
   } else {
     b->proj_f32 = a.take<float>((size_t)c.max_clips * HID);
-    b->proj_bf = nullptr;
+    b->proj_h = nullptr;
   }
+  b->att_counter = a.take<int32_t>(S + 1);
   b->feat_pl = a.planes(ap, c.max_events, FEAT_PAD);
   b->x_pl = a.planes(ap, c.max_events, HID);
   b->qky = a.take<float>((size_t)c.max_events * 3 * HID);
-  b->pe_pl = a.planes(ap, c.max_pairs, HID);
-  b->hid_pl = a.planes(ap, c.max_pairs, HID);
   b->pair_w = a.take<float>((size_t)c.max_pairs * ECHR_HEADS);
   b->event_ctx = a.take<float>((size_t)c.max_events * HID);
   for (int i = 0; i < 2; ++i) {
@@ -520,7 +515,7 @@ static int stage_desc(echr_batch_t* b, const echr_batch_desc_t* d, bool check_cl
     const int T = off[v + 1] - off[v];
     const int s = d->host_event_start[i], e = d->host_event_end[i], ind = d->host_event_ind[i];
     ECHR_REQUIRE(s >= 0 && e > s && e <= T, "echr_batch_set_inputs: event %d: span [%d,%d) invalid for a video of %d clips", i, s, e, T);
-    ECHR_REQUIRE(e - s <= 1024, "echr_batch_set_inputs: event %d: span of %d clips exceeds 1024", i, e - s);
+    ECHR_REQUIRE(e - s <= ECHR_MAX_SPAN_CLIPS, "echr_batch_set_inputs: event %d: span of %d clips exceeds %d", i, e - s, ECHR_MAX_SPAN_CLIPS);
     ECHR_REQUIRE(ind >= 0 && ind < T, "echr_batch_set_inputs: event %d: ind %d out of range", i, ind);
     if (vid_n[v] == 0) vid_first[v] = i;
     vid_n[v] += 1;
@@ -534,7 +529,7 @@ static int stage_desc(echr_batch_t* b, const echr_batch_desc_t* d, bool check_cl
   int max_n = 0;
   for (int v = 0; v < d->n_videos; ++v) {
     const int n = vid_n[v];
-    ECHR_REQUIRE(n <= 512, "echr_batch_set_inputs: video %d has %d events (limit 512)", v, n);
+    ECHR_REQUIRE(n <= ECHR_MAX_EVENTS_PER_VIDEO, "echr_batch_set_inputs: video %d has %d events (limit %d)", v, n, ECHR_MAX_EVENTS_PER_VIDEO);
     if (n > max_n) max_n = n;
     for (int j = 0; j < n; ++j) {
       const int i = vid_first[v] + j;
@@ -625,7 +620,7 @@ static int run_graph(echr_batch* b, const long long (&key)[6], cudaStream_t st, 
     }
     if (slot->exec) { cudaGraphExecDestroy(slot->exec); slot->exec = nullptr; }
     if (traced) {
-      const char* tr = getenv("ECHR_TRACE");
+      const char* tr = knob("ECHR_TRACE");
       b->trace_on = (tr != nullptr && tr[0] == '1') ? 1 : 0;
       b->trace_n = 0;
       if (b->trace_on)  // the trace slots belong to one graph: drop every other cached graph
@@ -673,9 +668,9 @@ static int encode_clips(echr_batch_t* b, cudaStream_t st) {
   GemmSpec s;
   s.A = &b->clip_pl; s.M = b->n_clips; s.W = &m->w_ctx2att; s.N = HID; s.K = CLIP_PAD;
   s.bias = m->b_ctx2att;
-  s.act = ACT_EXP2X;
-  if (m->cfg.clip_bf16) { s.out_hi = b->proj_bf; s.ld_bf = HID; }
-  else { s.out_f32 = b->proj_f32; s.ld_f32 = HID; }
+  // single-plane precision: the projection itself as one fp16 plane (attention_f16.cuh); otherwise the fp32 table e^{2P}
+  if (at == 1) { s.out_hi = b->proj_h; s.ld_bf = HID; }
+  else { s.act = ACT_EXP2X; s.out_f32 = b->proj_f32; s.ld_f32 = HID; }
   return run_gemm(&s, 1, at, wt, 128, EPI_STORE, 1, st, "ctx2att");
 }
 
@@ -705,20 +700,8 @@ static int encode_relation(echr_batch_t* b, cudaStream_t st, cudaStream_t side =
     s.bias = m->b_qky; s.out_f32 = b->qky; s.ld_f32 = 3 * HID;
     ECHR_TRY(run_gemm(&s, 1, at, wt, 128, EPI_STORE, 1, st, "query_key_value"));
   }
-  ECHR_CUDA(launch_posemb(b, ps));
-  {
-    GemmSpec s;
-    s.A = &b->pe_pl; s.M = b->n_pairs; s.W = &m->w_fc1; s.N = HID; s.K = HID;
-    s.bias = m->b_fc1; s.act = ACT_TANH;
-    s.out_hi = b->hid_pl.plane(0); s.out_lo = at > 1 ? b->hid_pl.plane(1) : nullptr; s.ld_bf = HID;
-    ECHR_TRY(run_gemm(&s, 1, at, wt, 128, EPI_STORE, 1, ps, "pair_pos_fc1"));
-  }
-  {
-    GemmSpec s;
-    s.A = &b->hid_pl; s.M = b->n_pairs; s.W = &m->w_fc2; s.N = ECHR_HEADS; s.K = HID;
-    s.bias = m->b_fc2; s.out_f32 = b->pair_w; s.ld_f32 = ECHR_HEADS;
-    ECHR_TRY(run_gemm(&s, 1, at, wt, 16, EPI_STORE, 1, ps, "pair_pos_fc2"));
-  }
+  // pair chain: position embedding -> fc1 + tanh -> fc2 in one kernel, nothing of size [pairs,512] touches HBM
+  ECHR_TRY(launch_pair_mlp(b, ps));
   if (side != nullptr) {
     ECHR_CUDA(cudaEventRecord(join_ev, side));
     ECHR_CUDA(cudaStreamWaitEvent(st, join_ev, 0));
@@ -745,8 +728,7 @@ extern "C" int echr_encode(echr_batch_t* b, void* stream) {
   ECHR_REQUIRE(b, "echr_encode: null batch");
   ECHR_REQUIRE(b->n_videos > 0, "echr_encode: no inputs set");
   cudaStream_t st = (cudaStream_t)stream;
-  ECHR_CUDA(init_pos_table());
-  static const bool graphed = !(getenv("ECHR_ENCODE_GRAPH") && getenv("ECHR_ENCODE_GRAPH")[0] == '0');
+  static const bool graphed = !(knob("ECHR_ENCODE_GRAPH") && knob("ECHR_ENCODE_GRAPH")[0] == '0');
   const long long key[6] = {2, b->n_videos, b->n_events, b->n_clips, b->n_pairs, b->max_n};
   const bool use_graph = graphed && worth_a_graph(b, key);
   if (use_graph) {
@@ -844,6 +826,7 @@ static int enqueue_init(echr_batch* b, int beam, cudaStream_t st) {
     for (int p = 0; p < b->act[i].planes; ++p)
       ECHR_CUDA(cudaMemsetAsync(b->act[i].plane(p), 0, sizeof(bf16) * (size_t)rows * ACT_LD, st));
   ECHR_CUDA(cudaMemsetAsync(b->cstate[0], 0, sizeof(float) * (size_t)3 * rows * HID, st));
+  ECHR_CUDA(cudaMemsetAsync(b->att_counter, 0, sizeof(int32_t) * (size_t)(b->model->cfg.seq_length + 1), st));
   ECHR_CUDA(launch_decode_init(b, beam, st));
   // Hoist the constant-context terms of streams 0 and 2 out of the time loop: per-row gate bias
   //   row_bias0 = W_ih0[:, event] . event_ctx + (b_ih0 + b_hh0),  row_bias2 = W_ih2[:, video] . lda + (b_ih2 + b_hh2)
@@ -872,35 +855,58 @@ static int enqueue_init(echr_batch* b, int beam, cudaStream_t st) {
 // log-softmax / top-k.  The caller appends the mode's finalize kernel.
 enum { PART_H2ATT = 1, PART_ATT = 2, PART_GATES = 4, PART_LOGIT = 8, PART_ALL = 15 };
 
+// Attention of decode step t over the 16-bit tables (single-plane precision): reads the query the h2att GEMM of
+// step t wrote, writes the ATT block of activation buffer t & 1.
+static AttF16Params attention_params(const echr_batch* b, int rows, int t, int32_t* counter) {
+  AttF16Params ap;
+  ap.q = b->q_att;
+  ap.proj = b->proj_h;
+  ap.clip = b->clip_pl.plane(0);
+  ap.alpha = b->model->alpha;
+  ap.row_start = b->row_start;
+  ap.row_len = b->row_len;
+  ap.rows = rows;
+  ap.out = b->act[t & 1].plane(0) + ACT_ATT;
+  ap.ld_out = ACT_LD;
+  ap.out_f32 = nullptr;
+  ap.row_counter = counter;
+  return ap;
+}
+
 // use_keys (greedy decode): the logit epilogue keeps a packed running arg-max per row (argmax_key[t & 1]) and the
 // gate GEMM of step t + 1 takes its input token from it, so the token chain does not pass through finalize.
+// att_next: the logit launch also runs the attention of step t + 1 on its extra warps (persistent kernel only).
 static int enqueue_step(echr_batch* b, int rows, int t, int topk, float* logits_out, long long ld_logits,
-                        cudaStream_t st, int parts = PART_ALL, bool use_keys = false) {
+                        cudaStream_t st, int parts = PART_ALL, bool use_keys = false, bool att_next = false) {
   const echr_model* m = b->model;
   const int at = m->cfg.a_terms, wt = m->cfg.w_terms;
   const int p = t & 1, n = p ^ 1;
   PlaneMat& cur = b->act[p];
   PlaneMat& nxt = b->act[n];
+  const bool att16 = at == 1;  // single-plane precision: 16-bit tables, attention_f16.cuh
   if (parts & PART_H2ATT) {
     GemmSpec s;
     s.A = &cur; s.a_col0 = ACT_H + HID; s.M = rows; s.W = &m->w_h2att; s.N = HID; s.K = HID;
-    s.bias = m->b_h2att; s.act = ACT_EXP2X; s.out_f32 = b->q_att; s.ld_f32 = HID;  // e^{2q}
+    s.bias = m->b_h2att; s.out_f32 = b->q_att; s.ld_f32 = HID;
+    if (!att16) s.act = ACT_EXP2X;  // fp32 tables: e^{2q}
     PdlScope pdl(PDL_H2ATT);
     // latency regime: narrow tiles spread the [rows,512] x [512,512] product over 4x the SMs (a CTA's
     // main loop is bound by its own L2->SM operand stream, dominated by the 2-plane activation tile)
-    static const int bn_small = getenv("ECHR_H2ATT_BN") ? atoi(getenv("ECHR_H2ATT_BN")) : 32;
     // (lanes sharing the GPU: one wide tile per 128 rows costs a third of the SM time of four narrow ones)
-    static const int bn_shared = getenv("ECHR_H2ATT_BN_SHARED") ? atoi(getenv("ECHR_H2ATT_BN_SHARED")) : 128;
-    const int bn = rows < gemm2_min_rows() ? (b->concurrency > 1 ? bn_shared : bn_small) : 128;
+    const int bn = rows < gemm2_min_rows() ? (b->concurrency > 1 ? 128 : 32) : 128;
     ECHR_TRY(run_gemm(&s, 1, at, wt, bn, EPI_STORE, 1, st, "h2att", b, 0));
   }
   if (parts & PART_ATT) {
-  PdlScope pdl(PDL_ATT);
-  ECHR_CUDA(launch_attention(b->q_att, m->cfg.clip_bf16 ? (const void*)b->proj_bf : (const void*)b->proj_f32,
-                             m->cfg.clip_bf16 ? (const void*)b->clip_pl.plane(0) : (const void*)b->c3d,
-                             m->cfg.clip_bf16 ? CLIP_PAD : ECHR_VIDEO_DIM, m->cfg.clip_bf16, m->alpha,
-                             b->row_start, b->row_len, rows, nullptr, cur.plane(0) + ACT_ATT,
-                             at > 1 ? cur.plane(1) + ACT_ATT : nullptr, ACT_LD, st, len_bucket(b->max_len), trace_ptr(b), trace_next(b, 1)));
+    PdlScope pdl(PDL_ATT);
+    if (att16) {
+      const AttF16Params ap = attention_params(b, rows, t, nullptr);
+      ECHR_CUDA(launch_attention_f16(ap, st, trace_ptr(b), trace_next(b, 1)));
+    } else {
+      ECHR_CUDA(launch_attention(b->q_att, (const void*)b->proj_f32, (const void*)b->c3d, ECHR_VIDEO_DIM, 0, m->alpha,
+                                 b->row_start, b->row_len, rows, nullptr, cur.plane(0) + ACT_ATT,
+                                 at > 1 ? cur.plane(1) + ACT_ATT : nullptr, ACT_LD, st, len_bucket(b->max_len), trace_ptr(b),
+                                 trace_next(b, 1)));
+    }
   }
   if (parts & PART_GATES) {
     GemmSpec s[3];
@@ -941,6 +947,11 @@ static int enqueue_step(echr_batch* b, int rows, int t, int topk, float* logits_
     const bool sp = logit_split(m, rows);
     if (sp) s.ksplit = 2;
     if (use_keys) s.argmax_key = b->argmax_key[t & 1];
+    AttF16Params ap;
+    if (att_next) {
+      ap = attention_params(b, rows, t + 1, b->att_counter + t + 1);
+      s.att = &ap;
+    }
     PdlScope pdl(PDL_LOGIT);
     ECHR_TRY(run_gemm(&s, 1, at, wt, sp ? 256 : 128, EPI_LOGITS, topk, st, "logit", b, 3));
   }
@@ -972,13 +983,31 @@ static int enqueue_decode(echr_batch* b, int beam, int mode, cudaStream_t st, cu
     //   gates(t) -> logits(t) -> finalize(t) -> gates(t+1)
     // forks off and joins by events.  The branches touch disjoint columns of the activation matrix.
     // (throughput regime: persistent GEMMs; measured better with the attention chain on the forked stream)
-    static const bool crit_main_env = !(getenv("ECHR_CRIT_MAIN") && getenv("ECHR_CRIT_MAIN")[0] == '0');
-    const bool crit_main = crit_main_env && rows < gemm2_min_rows();
+    const bool crit_main = rows < gemm2_min_rows();
     // The gate GEMM of step t+1 reads its token from the arg-max keys the logit epilogue of step t maintains
     // with atomics (ECHR_ARGMAX_KEYS=0: from finalize's row_tok), so the join waits for the logits only;
     // finalize (log-sum-exp, outputs, `unfinished`) runs beside the next gate GEMM.
-    static const bool keys = !(getenv("ECHR_ARGMAX_KEYS") && getenv("ECHR_ARGMAX_KEYS")[0] == '0');
+    const bool keys = true;
     ECHR_TRY(enqueue_step(b, rows, 0, topk, nullptr, 0, st, PART_H2ATT | PART_ATT));
+    if (fused_attention(b, rows)) {
+      // Throughput regime, 16-bit tables: one stream,
+      //   gates(t) -> h2att(t+1) -> [logits(t) || attention(t+1)] in ONE persistent kernel -> gates(t+1),
+      // finalize(t) beside gates(t+1) / h2att(t+2) on the side stream (it must precede logits(t+1), which reuses
+      // the partial records and accumulates into the arg-max keys finalize(t) clears).
+      for (int t = 0; t < S; ++t) {
+        const bool last = t + 1 == S;
+        ECHR_TRY(enqueue_step(b, rows, t, topk, nullptr, 0, st, PART_GATES, true));
+        if (!last) ECHR_TRY(enqueue_step(b, rows, t + 1, topk, nullptr, 0, st, PART_H2ATT));
+        if (t > 0) ECHR_CUDA(cudaStreamWaitEvent(st, b->cap_events[2], 0));  // finalize(t-1) done
+        ECHR_TRY(enqueue_step(b, rows, t, topk, nullptr, 0, st, PART_LOGIT, true, !last));
+        ECHR_CUDA(cudaEventRecord(b->cap_events[0], st));
+        ECHR_CUDA(cudaStreamWaitEvent(side, b->cap_events[0], 0));
+        ECHR_CUDA(launch_finalize_greedy(b, t, b->tokens_dev, b->logp_dev, side, true));
+        ECHR_CUDA(cudaEventRecord(b->cap_events[2], side));
+      }
+      ECHR_CUDA(cudaStreamWaitEvent(st, b->cap_events[2], 0));
+      return ECHR_OK;
+    }
     cudaStream_t tok_st = crit_main ? side : st;  // token chain
     cudaStream_t att_st = crit_main ? st : side;  // recurrent attention chain
     for (int t = 0; t < S; ++t) {
@@ -1026,7 +1055,7 @@ static int run_decode(echr_batch* b, int beam, int mode, cudaStream_t st) {
   if (b->n_events == 0) return ECHR_OK;
   const int rows = b->n_events * beam;
   const long long key[6] = {1, rows, mode == MODE_BEAM ? beam : 0, len_bucket(b->max_len), b->concurrency > 1 ? 1 : 0, 0};
-  const char* tr = getenv("ECHR_TRACE");
+  const char* tr = knob("ECHR_TRACE");
   if (!(tr != nullptr && tr[0] == '1') && !worth_a_graph(b, key)) {
     // first sight of this shape: the same fork/join schedule, enqueued eagerly on the caller's stream
     ECHR_TRY(ensure_capture_streams(b));
@@ -1198,12 +1227,19 @@ extern "C" int echr_time_step_kernels(echr_batch_t* b, int beam, int iters, floa
   if (rc == ECHR_OK && cudaStreamSynchronize(st) != cudaSuccess) rc = set_error(ECHR_ERR_CUDA, "echr_time_step_kernels: sync failed");
   const bool saved_regime = pdl_regime();
   pdl_regime() = false;  // plain launches: a launch must not overlap the tail of its identical predecessor
-  for (int k = 0; k < 5 && rc == ECHR_OK; ++k) {
+  host_ms[5] = 0.f;
+  const bool fused = beam == 1 && fused_attention(b, rows);
+  for (int k = 0; k < 6 && rc == ECHR_OK; ++k) {
+    if (k == 5 && !fused) break;
     cudaGraph_t graph = nullptr;
     cudaGraphExec_t exec = nullptr;
     if (cudaStreamBeginCapture(b->cap_stream, cudaStreamCaptureModeRelaxed) != cudaSuccess) { rc = set_error(ECHR_ERR_CUDA, "echr_time_step_kernels: capture failed"); break; }
     for (int i = 0; i < iters && rc == ECHR_OK; ++i) {
-      if (k < 4) rc = enqueue_step(b, rows, 1, beam > 1 ? 4 : 1, nullptr, 0, b->cap_stream, parts[k]);
+      if (k == 5) {  // logits(1) with the attention of step 2 on the extra warps (its row counter re-armed per launch)
+        if (cudaMemsetAsync(b->att_counter + 2, 0, sizeof(int32_t), b->cap_stream) != cudaSuccess) rc = set_error(ECHR_ERR_CUDA, "memset failed");
+        if (rc == ECHR_OK) rc = enqueue_step(b, rows, 1, 1, nullptr, 0, b->cap_stream, PART_LOGIT, false, true);
+      }
+      else if (k < 4) rc = enqueue_step(b, rows, 1, beam > 1 ? 4 : 1, nullptr, 0, b->cap_stream, parts[k]);
       else if (beam > 1) { if (launch_finalize_beam(b, beam, 1, b->tokens_dev, b->logp_dev, b->score_dev, b->cap_stream) != cudaSuccess) rc = set_error(ECHR_ERR_CUDA, "finalize_beam launch failed"); }
       else { if (launch_finalize_greedy(b, 1, b->tokens_dev, b->logp_dev, b->cap_stream) != cudaSuccess) rc = set_error(ECHR_ERR_CUDA, "finalize_greedy launch failed"); }
     }

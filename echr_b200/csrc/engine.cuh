@@ -90,14 +90,13 @@ struct echr_batch {
   int32_t* host_stage;  // pinned staging for the arrays above
   // encode workspace
   echr::PlaneMat clip_pl;   // [clips, 512]   c3d planes (A of ctx2att; plane 0 doubles as bf16 clip)
-  float* proj_f32;          // [clips, 512]   ctx2att(c3d)+b    (clip_bf16 == 0)
-  echr::bf16* proj_bf;      // [clips, 512]                     (clip_bf16 == 1)
+  float* proj_f32;          // [clips, 512]   e^{2 (ctx2att(c3d)+b)} fp32      (two-plane precisions)
+  echr::bf16* proj_h;       // [clips, 512]   ctx2att(c3d)+b as fp16           (single-plane precision, a_terms == 1)
+  int32_t* att_counter;     // [seq_length + 1] row counters of the attention warps inside the logit GEMM
   echr::PlaneMat feat_pl;   // [events, 1024] (mean c3d | tap[ind])
   echr::PlaneMat x_pl;      // [events, 512]  event_emb output
   float* qky;               // [events, 1536]
-  echr::PlaneMat pe_pl;     // [pairs, 512]   position embedding
-  echr::PlaneMat hid_pl;    // [pairs, 512]   tanh(fc1)
-  float* pair_w;            // [pairs, 16]
+  float* pair_w;            // [16][n_pairs]  pair weights, head-major (pair_mlp.cu)
   float* event_ctx;         // [events, 512]
   // decode workspace (rows = events * beam)
   echr::PlaneMat act[2];    // [rows, ACT_LD]
@@ -162,15 +161,16 @@ cudaError_t launch_split(const float* src, int64_t rows, int64_t cols, int64_t l
                          bf16* lo, int64_t ld_dst, int64_t cols_dst, bool f16, cudaStream_t st);
 cudaError_t launch_event_feats(const echr_batch* b, cudaStream_t st);
 cudaError_t launch_gather_tap(const echr_batch* b, const float* tap_src, cudaStream_t st);
-cudaError_t launch_posemb(const echr_batch* b, cudaStream_t st);
-cudaError_t init_pos_table();  // uploads the position-embedding divisors (once per device; synchronous)
 cudaError_t launch_relation_attn(const echr_batch* b, cudaStream_t st);
+// ---- pair_mlp.cu: position embedding -> fc1 + tanh -> fc2 fused over tiles of 128 event pairs
+int launch_pair_mlp(const echr_batch* b, cudaStream_t st);
 // ---- kernels_step.cu
 cudaError_t launch_attention(const float* q, const void* proj, const void* clip, int64_t ld_clip,
                              int clip_bf16, const float* alpha, const int32_t* row_start,
                              const int32_t* row_len, int64_t rows, float* out_f32, bf16* out_hi,
                              bf16* out_lo, int64_t ld_bf, cudaStream_t st, int max_len = 0,
                              unsigned long long* trace = nullptr, int trace_slot = 0);
+cudaError_t launch_attention_f16(const AttF16Params& P, cudaStream_t st, unsigned long long* trace = nullptr, int trace_slot = 0);
 cudaError_t launch_decode_init(const echr_batch* b, int beam, cudaStream_t st);
 cudaError_t launch_finalize_greedy(echr_batch* b, int step, int32_t* tokens, float* logp,
                                    cudaStream_t st, bool keys = false);
@@ -231,6 +231,7 @@ struct GemmSpec {
   int ksplit = 1;  // 2: cluster split-K (run_gemm then launches the SPLIT == 2 kernel for the whole group)
   const unsigned long long* row_key = nullptr;  // token from the packed arg-max keys instead of row_tok
   unsigned long long* argmax_key = nullptr;     // logits: running arg-max keys
+  const AttF16Params* att = nullptr;            // logits (persistent kernel): attention rows for its extra warps
   // logits
   float* partial = nullptr;
   float* logits_out = nullptr;

@@ -51,13 +51,8 @@ template <int A, int W, int BN, int EPI, int TOPK>
 static cudaError_t launch_one(const GemmParams& P, dim3 grid, cudaStream_t stream) {
   using Cfg = GemmCfg<A, W, BN>;
   auto kern = gemm_tc_kernel<A, W, BN, EPI, TOPK>;
-  static bool attr_set = false;  // per instantiation
-  if (!attr_set) {
-    cudaError_t e =
-        cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES);
-    if (e != cudaSuccess) return e;
-    attr_set = true;
-  }
+  static int attr[MAX_DEVICES] = {};  // per instantiation and device
+  if (cudaError_t e = set_max_dynamic_smem(kern, Cfg::SMEM_BYTES, attr); e != cudaSuccess) return e;
   return launch_pdl(kern, grid, dim3(GEMM_THREADS), Cfg::SMEM_BYTES, stream, P);
 }
 
@@ -92,12 +87,8 @@ template <int A, int W, int BN, int EPI, int TOPK>
 static cudaError_t launch_split_one(const GemmParams& P, dim3 grid, cudaStream_t stream) {
   using Cfg = GemmCfg<A, W, BN>;
   auto kern = gemm_tc_kernel<A, W, BN, EPI, TOPK, 2>;
-  static bool attr_set = false;  // per instantiation
-  if (!attr_set) {
-    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES);
-    if (e != cudaSuccess) return e;
-    attr_set = true;
-  }
+  static int attr[MAX_DEVICES] = {};  // per instantiation and device
+  if (cudaError_t e = set_max_dynamic_smem(kern, Cfg::SMEM_BYTES, attr); e != cudaSuccess) return e;
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = grid;
   cfg.blockDim = dim3(GEMM_THREADS);
@@ -137,14 +128,18 @@ cudaError_t gemm_launch_split(const GemmParams& P, int groups, int max_m, int gr
 template <int A, int W, int EPI, int TOPK>
 static cudaError_t launch_two(const GemmParams& P, int groups, int total_tiles, int num_sms, cudaStream_t stream) {
   using Cfg = Gemm2Cfg<A, W>;
-  auto kern = gemm_tc2_kernel<A, W, EPI, TOPK>;
-  static bool attr_set = false;  // per instantiation
-  if (!attr_set) {
-    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES);
-    if (e != cudaSuccess) return e;
-    attr_set = true;
-  }
   const int grid = total_tiles < num_sms ? total_tiles : num_sms;
+  if constexpr (EPI == EPI_LOGITS && A == 1 && W == 1) {
+    if (P.att.rows > 0) {  // vocabulary projection + the next step's attention on four extra warps
+      auto kern = gemm_tc2_kernel<A, W, EPI, TOPK, true>;
+      static int attr[MAX_DEVICES] = {};
+      if (cudaError_t e = set_max_dynamic_smem(kern, Cfg::SMEM_BYTES_ATT, attr); e != cudaSuccess) return e;
+      return launch_pdl(kern, dim3(grid), dim3(GEMM_THREADS + 128), Cfg::SMEM_BYTES_ATT, stream, P, groups, total_tiles);
+    }
+  }
+  auto kern = gemm_tc2_kernel<A, W, EPI, TOPK>;
+  static int attr[MAX_DEVICES] = {};  // per instantiation and device
+  if (cudaError_t e = set_max_dynamic_smem(kern, Cfg::SMEM_BYTES, attr); e != cudaSuccess) return e;
   return launch_pdl(kern, dim3(grid), dim3(GEMM_THREADS), Cfg::SMEM_BYTES, stream, P, groups, total_tiles);
 }
 

@@ -1,7 +1,6 @@
 // Context prologue and event relation encoder kernels (everything that runs once per batch):
 //   split_planes        fp32 -> bf16 hi/lo planes, or one fp16 plane (tensor-core operand staging)
 //   event_feats         mean-pooled clip feature | proposal state per event (CaptionGenerator.py:106-127)
-//   posemb              pairwise temporal position embedding (MA_attention_8_NEW.py:51-79), fp64 math
 //   relation_attn       multi-head relation attention with the pair weights (MA:122-175)
 //   fill_video          LDA video context into the activation matrix (CaptionGenerator.py:87-104)
 #include "engine.cuh"
@@ -134,161 +133,110 @@ cudaError_t launch_event_feats(const echr_batch* b, cudaStream_t st) {
 }
 
 // ---------------------------------------------------------------------------------------------
-// Position embedding.  The reference builds it in numpy float64 on the host (MA:39-41,51-79):
-//   dc = max(|c_i - c_j| / len_i, 1e-3)               (float64; len cast to float32 first)
-//   dl = log(len_j / len_i)                            (float32 division and float32 log)
-//   z  = 100 * p / 10000^(k/128),  k = 0..127          (float64)
-//   row(i,j) = [sin z(dc) | cos z(dc) | sin z(dl) | cos z(dl)]  -> float32
-// Arguments reach ~4e4, so the sine/cosine are evaluated in float64 here too.
-__constant__ double c_pos_div[128];
-
-__global__ void __launch_bounds__(256)
-posemb_kernel(const int32_t* __restrict__ ev_start, const int32_t* __restrict__ ev_len,
-              const int32_t* __restrict__ ev_pair_off, const int32_t* __restrict__ ev_first,
-              const int32_t* __restrict__ ev_n, bf16* __restrict__ hi, bf16* __restrict__ lo,
-              int j_chunk) {
-  const int i = blockIdx.x;
-  const int n = ev_n[i], first = ev_first[i];
-  const int j0 = blockIdx.y * j_chunk;
-  if (j0 >= n) return;
-  const int j1 = min(n, j0 + j_chunk);
-  const int k = threadIdx.x & 127;
-  const int which = threadIdx.x >> 7;  // 0: centre distance, 1: length ratio
-  const double ci = 0.5 * ((double)ev_start[i] + (double)(ev_start[i] + ev_len[i]));
-  const float li = (float)ev_len[i];
-  const double div = c_pos_div[k];
-  const long long row0 = ev_pair_off[i];
-  for (int j = j0; j < j1; ++j) {
-    const int ej = first + j;
-    double p;
-    if (which == 0) {
-      const double cj = 0.5 * ((double)ev_start[ej] + (double)(ev_start[ej] + ev_len[ej]));
-      p = fmax(fabs((ci - cj) / (double)li), 1e-3);
-    } else {
-      const float r = (float)ev_len[ej] / li;
-      p = (double)(float)log((double)r);
-    }
-    const double z = (100.0 * p) / div;
-    double sn, cs;
-    sincos(z, &sn, &cs);
-    bf16 sh, sl, ch, cl;
-    split16((float)sn, lo == nullptr, sh, sl);
-    split16((float)cs, lo == nullptr, ch, cl);
-    const long long base = (row0 + j) * HID + which * 256 + k;
-    hi[base] = sh;
-    hi[base + 128] = ch;
-    if (lo != nullptr) {
-      lo[base] = sl;
-      lo[base + 128] = cl;
-    }
-  }
-}
-
-cudaError_t init_pos_table() {
-  static bool done = false;  // per process; the table is device-constant per context
-  static int done_dev = -1;
-  int dev = 0;
-  cudaGetDevice(&dev);
-  if (done && done_dev == dev) return cudaSuccess;
-  double h[128];
-  for (int k = 0; k < 128; ++k) h[k] = pow(10000.0, (4.0 / 512.0) * (double)k);
-  cudaError_t e = cudaMemcpyToSymbol(c_pos_div, h, sizeof(h));
-  if (e == cudaSuccess) { done = true; done_dev = dev; }
-  return e;
-}
-
-cudaError_t launch_posemb(const echr_batch* b, cudaStream_t st) {
-  if (b->n_events == 0) return cudaSuccess;
-  cudaError_t e = init_pos_table();
-  if (e != cudaSuccess) return e;
-  const int j_chunk = 32;
-  dim3 grid(b->n_events, (b->max_n + j_chunk - 1) / j_chunk);
-  posemb_kernel<<<grid, 256, 0, st>>>(b->ev_start, b->ev_len, b->ev_pair_off, b->ev_first, b->ev_n,
-                                      b->pe_pl.plane(0),
-                                      b->pe_pl.planes > 1 ? b->pe_pl.plane(1) : nullptr, j_chunk);
-  count_launch();
-  return cudaGetLastError();
-}
-
-// ---------------------------------------------------------------------------------------------
-// Relation attention (MA:122-175), one CTA per (video, head):
+// Relation attention (MA:122-175), one CTA per (video, head, block of REL_QB query events):
 //   s[i,j] = w[i,j,g] * (Q_i,g . K_j,g) / sqrt(32)         fST0: multiplicative fusion (MA:148-149)
 //   p[i,:] = softmax_j(s[i,:])                               (MA:160)
 //   out[i, 32g+d] = sum_j p[i,j] * Y[j, 32g+d] + b[32g+d]    with Y = x * W_out^T  (grouped 1x1 conv,
 //                                                            MA:98,167-175, re-associated)
-// K_g and Y_g of the whole video sit in shared memory (rows padded to 33 words: conflict-free for
-// both the per-lane row walk of the scores and the per-lane column walk of the mix); one warp per
-// query event, warp-shuffle softmax.
+// Keys are walked in chunks of REL_JC events whose K_g / Y_g rows sit in shared memory (rows padded to 33
+// words: conflict-free for both the per-lane row walk of the scores and the per-lane column walk of the mix);
+// one warp per query event, warp-shuffle softmax, running (max, sum, mix) per query kept in shared memory
+// between chunks — so the number of events per video is not bounded by shared memory (the reference's default
+// selection feeds up to topN = 1000 proposals, eval_utils.py:21).  Videos of up to REL_JC events take a single
+// chunk: plain two-pass softmax.  The pair weights come head-major [16][n_pairs] from pair_mlp.cu.
 constexpr int REL_WARPS = 8;
-constexpr int REL_MAX_N = 512;
+constexpr int REL_QB = 128;
+constexpr int REL_JC = 256;
 
 __global__ void __launch_bounds__(REL_WARPS * 32)
-relation_attn_kernel(const float* __restrict__ qky, const float* __restrict__ pair_w,
+relation_attn_kernel(const float* __restrict__ qky, const float* __restrict__ pair_w, long long n_pairs,
                      const int32_t* __restrict__ ev_pair_off, const int32_t* __restrict__ vid_first,
                      const int32_t* __restrict__ vid_n, const float* __restrict__ b_out,
-                     float* __restrict__ event_ctx) {
+                     float* __restrict__ event_ctx, int jc, int qb) {
   extern __shared__ float rel_smem[];
   const int v = blockIdx.x, g = blockIdx.y;
   const int first = vid_first[v], n = vid_n[v];
-  float* Ks = rel_smem;                 // [n][33]
-  float* Ys = Ks + (size_t)n * 33;      // [n][33]
-  float* Ss = Ys + (size_t)n * 33;      // [REL_WARPS][n]
-  float* Qs = Ss + (size_t)REL_WARPS * n;  // [REL_WARPS][32]
+  const int q0 = blockIdx.z * qb;
+  if (q0 >= n) return;
+  const int q1 = min(n, q0 + qb);
+  float* Ks = rel_smem;                      // [jc][33]
+  float* Ys = Ks + (size_t)jc * 33;          // [jc][33]
+  float* Ss = Ys + (size_t)jc * 33;          // [REL_WARPS][jc]
+  float* Qs = Ss + (size_t)REL_WARPS * jc;   // [REL_WARPS][32]
+  float* Ms = Qs + REL_WARPS * 32;           // [qb] running max
+  float* Ls = Ms + qb;                       // [qb] running sum
+  float* As = Ls + qb;                       // [qb][32] running mix
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  for (int idx = threadIdx.x; idx < n * 32; idx += blockDim.x) {
-    const int j = idx >> 5, d = idx & 31;
-    const float* row = qky + (long long)(first + j) * 1536 + 32 * g + d;
-    Ks[j * 33 + d] = __ldg(row + 512);
-    Ys[j * 33 + d] = __ldg(row + 1024);
-  }
-  __syncthreads();
   const float scale = 1.0f / sqrtf(32.0f);
-  float* S = Ss + (size_t)warp * n;
+  float* S = Ss + (size_t)warp * jc;
   float* Q = Qs + warp * 32;
-  for (int i = warp; i < n; i += REL_WARPS) {
-    Q[lane] = __ldg(qky + (long long)(first + i) * 1536 + 32 * g + lane);
-    __syncwarp();
-    const float* wrow = pair_w + (long long)ev_pair_off[first + i] * ECHR_HEADS + g;
-    float m = -INFINITY;
-    for (int j = lane; j < n; j += 32) {
-      float dot = 0.f;
+  for (int j0 = 0; j0 < n; j0 += jc) {
+    const int jn = min(jc, n - j0);
+    const bool first_chunk = j0 == 0, last_chunk = j0 + jc >= n;
+    __syncthreads();  // every warp is done with the previous chunk
+    for (int idx = threadIdx.x; idx < jn * 32; idx += blockDim.x) {
+      const int j = idx >> 5, d = idx & 31;
+      const float* row = qky + (long long)(first + j0 + j) * 1536 + 32 * g + d;
+      Ks[j * 33 + d] = __ldg(row + 512);
+      Ys[j * 33 + d] = __ldg(row + 1024);
+    }
+    __syncthreads();
+    for (int i = q0 + warp; i < q1; i += REL_WARPS) {
+      const int li = i - q0;
+      Q[lane] = __ldg(qky + (long long)(first + i) * 1536 + 32 * g + lane);
+      __syncwarp();
+      const float* wrow = pair_w + (long long)g * n_pairs + ev_pair_off[first + i] + j0;
+      float m_loc = -INFINITY;
+      for (int j = lane; j < jn; j += 32) {
+        float dot = 0.f;
 #pragma unroll
-      for (int d = 0; d < 32; ++d) dot = fmaf(Q[d], Ks[j * 33 + d], dot);
-      const float s = __ldg(wrow + (long long)j * ECHR_HEADS) * (scale * dot);
-      S[j] = s;
-      m = fmaxf(m, s);
+        for (int d = 0; d < 32; ++d) dot = fmaf(Q[d], Ks[j * 33 + d], dot);
+        const float s = __ldg(wrow + j) * (scale * dot);
+        S[j] = s;
+        m_loc = fmaxf(m_loc, s);
+      }
+      m_loc = warp_max(m_loc);
+      const float m_old = first_chunk ? -INFINITY : Ms[li];
+      const float m = fmaxf(m_old, m_loc);
+      float sum = 0.f;
+      for (int j = lane; j < jn; j += 32) {
+        const float e = expf(S[j] - m);
+        S[j] = e;
+        sum += e;
+      }
+      sum = warp_sum(sum);
+      __syncwarp();
+      float acc = 0.f;
+      if (!first_chunk) {
+        const float corr = expf(m_old - m);
+        acc = As[li * 32 + lane] * corr;
+        sum += Ls[li] * corr;
+      }
+      for (int j = 0; j < jn; ++j) acc = fmaf(S[j], Ys[j * 33 + lane], acc);
+      if (last_chunk) {
+        event_ctx[(long long)(first + i) * HID + 32 * g + lane] = acc / sum + __ldg(b_out + 32 * g + lane);
+      } else {
+        As[li * 32 + lane] = acc;
+        if (lane == 0) { Ms[li] = m; Ls[li] = sum; }
+      }
+      __syncwarp();
     }
-    m = warp_max(m);
-    float sum = 0.f;
-    for (int j = lane; j < n; j += 32) {
-      const float e = expf(S[j] - m);
-      S[j] = e;
-      sum += e;
-    }
-    sum = warp_sum(sum);
-    __syncwarp();
-    float acc = 0.f;
-    for (int j = 0; j < n; ++j) acc = fmaf(S[j], Ys[j * 33 + lane], acc);
-    event_ctx[(long long)(first + i) * HID + 32 * g + lane] = acc / sum + __ldg(b_out + 32 * g + lane);
-    __syncwarp();
   }
 }
 
 cudaError_t launch_relation_attn(const echr_batch* b, cudaStream_t st) {
   if (b->n_events == 0) return cudaSuccess;
-  if (b->max_n > REL_MAX_N) return cudaErrorInvalidValue;
-  const size_t smem = ((size_t)b->max_n * 66 + (size_t)REL_WARPS * b->max_n + REL_WARPS * 32) * sizeof(float);
-  static size_t attr = 0;
-  if (smem > 48 * 1024 && smem > attr) {
-    cudaError_t e = cudaFuncSetAttribute(relation_attn_kernel,
-                                         cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  const int jc = b->max_n < REL_JC ? b->max_n : REL_JC;
+  const int qb = b->max_n < REL_QB ? b->max_n : REL_QB;
+  const size_t smem = ((size_t)jc * 66 + (size_t)REL_WARPS * jc + REL_WARPS * 32 + (size_t)qb * 34) * sizeof(float);
+  static int attr[MAX_DEVICES] = {};
+  if (smem > 48 * 1024) {
+    cudaError_t e = set_max_dynamic_smem(relation_attn_kernel, (int)smem, attr);
     if (e != cudaSuccess) return e;
-    attr = smem;
   }
-  dim3 grid(b->n_videos, ECHR_HEADS);
-  relation_attn_kernel<<<grid, REL_WARPS * 32, smem, st>>>(b->qky, b->pair_w, b->ev_pair_off,
-                                                          b->vid_first, b->vid_n, b->model->b_out,
-                                                          b->event_ctx);
+  dim3 grid(b->n_videos, ECHR_HEADS, (b->max_n + qb - 1) / qb);
+  relation_attn_kernel<<<grid, REL_WARPS * 32, smem, st>>>(b->qky, b->pair_w, (long long)b->n_pairs, b->ev_pair_off,
+                                                          b->vid_first, b->vid_n, b->model->b_out, b->event_ctx, jc, qb);
   count_launch();
   return cudaGetLastError();
 }

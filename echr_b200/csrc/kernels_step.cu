@@ -478,7 +478,7 @@ attention_v2_kernel(const float* __restrict__ q, const void* __restrict__ proj_v
 static int att_v2_rows() {
   static int v = -1;
   if (v < 0) {
-    const char* e = getenv("ECHR_ATT_V2_ROWS");
+    const char* e = knob("ECHR_ATT_V2_ROWS");
     v = e ? atoi(e) : (1 << 30);
   }
   return v;
@@ -487,7 +487,7 @@ static int att_v2_rows() {
 static int att_v2_maxlen() {
   static int v = -1;
   if (v < 0) {
-    const char* e = getenv("ECHR_ATT_V2_MAXLEN");
+    const char* e = knob("ECHR_ATT_V2_MAXLEN");
     v = e ? atoi(e) : ATT_MAX_L;
   }
   return v;
@@ -505,7 +505,7 @@ cudaError_t launch_attention(const float* q, const void* proj, const void* clip,
   const size_t stage = (size_t)max_len * (HID + clip_row) * el;
   // staged rows must be contiguous: fp32 clips have ld 500, bf16 clips ld 512
   const bool fits = max_len > 0 && max_len <= ATT_MAX_L && stage <= ATT_STAGE_BYTES && (size_t)ld_clip == clip_row;
-  const bool staged = fits && getenv("ECHR_ATT_STREAM") == nullptr && (rows <= 148 || getenv("ECHR_ATT_STAGED") != nullptr);
+  const bool staged = fits && knob("ECHR_ATT_STREAM") == nullptr && (rows <= 148 || knob("ECHR_ATT_STAGED") != nullptr);
   if (staged) {
     static size_t attr[2] = {0, 0};
     if (stage > attr[clip_bf16 ? 1 : 0]) {
@@ -523,7 +523,7 @@ cudaError_t launch_attention(const float* q, const void* proj, const void* clip,
   } else if (att_v2_rows() > 0 && rows <= att_v2_rows() && max_len > 0 && max_len <= att_v2_maxlen()) {
     // latency regime: short windows.  256-thread CTAs (16 K registers, 13 KB) also fit next to a resident
     // CTA of the concurrent logit GEMM, so the launch is one wave even while that GEMM holds 90 SMs.
-    static const int v2_threads = getenv("ECHR_ATT_V2_THREADS") ? atoi(getenv("ECHR_ATT_V2_THREADS")) : 256;
+    static const int v2_threads = knob("ECHR_ATT_V2_THREADS") ? atoi(knob("ECHR_ATT_V2_THREADS")) : 256;
     if (v2_threads == 256) {
       if (clip_bf16)
         e = launch_pdl(attention_v2_kernel<true, 256>, dim3((unsigned)rows), dim3(256), 0, st, q, proj, clip,
@@ -553,6 +553,44 @@ cudaError_t launch_attention(const float* q, const void* proj, const void* clip,
       e = launch_pdl(attention_kernel<false, ATT_THREADS>, dim3((unsigned)rows), dim3(ATT_THREADS), 0, st, q, proj, clip,
                      (long long)ld_clip, alpha, row_start, row_len, out_f32, out_hi, out_lo, (long long)ld_bf, trace, trace_slot);
   }
+  count_launch();
+  return e;
+}
+
+// ---------------------------------------------------------------------------------------------
+// 16-bit, bulk-copy staged attention (attention_f16.cuh) as a stand-alone kernel: ATT16_WARPS warps per CTA, a
+// private ring each, rows round-robin over the warps of the grid (or handed out by P.row_counter).
+constexpr int ATT16_WARPS = 8;
+constexpr int ATT16_SMEM = ATT16_WARPS * ATT_WARP_SMEM + ATT16_WARPS * ATT_SLOTS * 8;
+
+__global__ void __launch_bounds__(ATT16_WARPS * 32)
+attention_f16_kernel(const __grid_constant__ AttF16Params P, unsigned long long* trace, int trace_slot) {
+  extern __shared__ __align__(128) uint8_t att16_smem[];
+  trace_begin(trace, trace_slot);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const uint32_t ring = smem_u32(att16_smem) + warp * ATT_WARP_SMEM;
+  const uint32_t bars = smem_u32(att16_smem) + ATT16_WARPS * ATT_WARP_SMEM + warp * ATT_SLOTS * 8;
+  if (lane == 0) {
+    for (int i = 0; i < ATT_SLOTS; ++i) mbar_init(bars + 8u * i, 1);
+    fence_mbar_init();
+  }
+  __syncwarp();
+  pdl_trigger();
+  pdl_wait();  // q comes from the h2att GEMM launched just before
+  att_f16_warp(P, ring, bars, static_cast<int>(blockIdx.x) * ATT16_WARPS + warp, static_cast<int>(gridDim.x) * ATT16_WARPS, 0u);
+  __syncthreads();
+  trace_end(trace, trace_slot);
+}
+
+cudaError_t launch_attention_f16(const AttF16Params& P, cudaStream_t st, unsigned long long* trace, int trace_slot) {
+  if (P.rows == 0) return cudaSuccess;
+  static int attr[MAX_DEVICES] = {};
+  cudaError_t e = set_max_dynamic_smem(attention_f16_kernel, ATT16_SMEM, attr);
+  if (e != cudaSuccess) return e;
+  const int want = (P.rows + ATT16_WARPS - 1) / ATT16_WARPS;
+  const int cap = num_sms() * 4;  // 4 CTAs of 48 KB per SM
+  e = launch_pdl(attention_f16_kernel, dim3((unsigned)(want < cap ? want : cap)), dim3(ATT16_WARPS * 32), (size_t)ATT16_SMEM, st,
+                 P, trace, trace_slot);
   count_launch();
   return e;
 }

@@ -299,7 +299,7 @@ extern "C" int echr_sst_forward(echr_sst_t* m, const float* c3d, const int32_t* 
   key |= 1ull;
   echr_sst::Slot* hit = nullptr;
   for (auto& sl : m->slots) if (sl.exec != nullptr && sl.key == key) hit = &sl;
-  static const bool use_graph = !(getenv("ECHR_SST_GRAPH") && atoi(getenv("ECHR_SST_GRAPH")) == 0);
+  static const bool use_graph = !(knob("ECHR_SST_GRAPH") && atoi(knob("ECHR_SST_GRAPH")) == 0);
   if (hit == nullptr && use_graph) {
     bool seen_before = false;
     for (unsigned long long k : m->seen) seen_before = seen_before || k == key;

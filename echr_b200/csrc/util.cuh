@@ -35,6 +35,45 @@ inline int set_error(int code, const char* fmt, ...) {
                                cudaGetErrorString(_e), __FILE__, __LINE__);                 \
   } while (0)
 
+// Experiment knobs (ECHR_TRACE, ECHR_KSPLIT, ECHR_PDL_MASK, ...: the variables named next to each knob() call)
+// exist only in a debug build, `make DEBUG_KNOBS=1`: the shipped library reads no environment variable, every
+// schedule choice is a function of the batch shape alone.
+#ifdef ECHR_DEBUG_KNOBS
+inline const char* knob(const char* name) { return getenv(name); }
+#else
+inline const char* knob(const char*) { return nullptr; }
+#endif
+
+// ---- per-device launch state.  cudaFuncSetAttribute and the SM count are per DEVICE; one process may drive
+// several GPUs (Engine(device=...)), so "already set" is tracked per device ordinal, not per process.
+constexpr int MAX_DEVICES = 64;
+
+// Opt a kernel in to `bytes` of dynamic shared memory on the current device (no-op once done there).
+// `state` is a zero-initialised int[MAX_DEVICES] owned by the caller, one per kernel instantiation.
+template <typename K>
+inline cudaError_t set_max_dynamic_smem(K kern, int bytes, int* state) {
+  int dev = 0;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return e;
+  if (dev < 0 || dev >= MAX_DEVICES) return cudaErrorInvalidDevice;
+  if (state[dev] >= bytes) return cudaSuccess;
+  e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+  if (e == cudaSuccess) state[dev] = bytes;
+  return e;
+}
+
+inline int num_sms() {  // of the current device
+  static int n[MAX_DEVICES] = {};
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= MAX_DEVICES) return 148;
+  if (n[dev] == 0) {
+    int v = 0;
+    cudaDeviceGetAttribute(&v, cudaDevAttrMultiProcessorCount, dev);
+    n[dev] = v > 0 ? v : 148;
+  }
+  return n[dev];
+}
+
 #define ECHR_REQUIRE(cond, ...)                                                             \
   do {                                                                                      \
     if (!(cond)) return ::echr::set_error(::echr::ECHR_ERR_INVALID, __VA_ARGS__);           \
@@ -57,9 +96,9 @@ enum { PDL_H2ATT = 1, PDL_ATT = 2, PDL_GATES = 4, PDL_LOGIT = 8, PDL_FINALIZE = 
 inline int pdl_mask() {
   static int mask = -1;
   if (mask < 0) {
-    const char* e = getenv("ECHR_PDL_MASK");
+    const char* e = knob("ECHR_PDL_MASK");
     mask = e ? atoi(e) : PDL_DEFAULT_MASK;
-    const char* off = getenv("ECHR_NO_PDL");
+    const char* off = knob("ECHR_NO_PDL");
     if (off != nullptr && off[0] == '1') mask = 0;
   }
   return mask;

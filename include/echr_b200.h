@@ -22,7 +22,7 @@
 extern "C" {
 #endif
 
-#define ECHR_B200_ABI_VERSION 3
+#define ECHR_B200_ABI_VERSION 4
 
 #if defined(__GNUC__)
 #define ECHR_API __attribute__((visibility("default")))
@@ -35,6 +35,14 @@ extern "C" {
 #define ECHR_HIDDEN 512     /* every hidden / embedding size on the path */
 #define ECHR_LDA_DIM 100
 #define ECHR_HEADS 16
+/* limits of one batch (checked by echr_batch_set_inputs, which fails with ECHR_ERR_INVALID beyond them):
+ * events (proposals) per video — the reference's default selection feeds up to topN = 1000 (eval_utils.py:21,
+ * 107-115); the relation encoder walks keys in shared-memory chunks, so the bound is the int32 pair count
+ * (events^2 summed over the batch < 2^30), not shared memory;
+ * clips per event span — the reference caps proposal spans at K = 256 clips (dataloader.py:515-520); the
+ * attention kernels keep one score per clip of a window in shared memory. */
+#define ECHR_MAX_EVENTS_PER_VIDEO 8192
+#define ECHR_MAX_SPAN_CLIPS 1024
 
 typedef struct echr_model echr_model_t;
 typedef struct echr_batch echr_batch_t;
@@ -45,8 +53,8 @@ typedef struct echr_config {
   int32_t a_terms;    /* 2: activations as bf16 hi+lo planes (fp32-grade); 1: one fp16 plane, and then   */
                       /*    the weights are fp16 too (one tcgen05 product per k-step)                 */
   int32_t w_terms;    /* 1: weights rounded to bf16 (fp16 when a_terms == 1), 2: bf16 hi+lo planes      */
-  int32_t clip_bf16;  /* must be 0 (the step attention reads fp32 clip features and projections; the     */
-                      /*    16-bit table was retired with the fp16 single-plane format)                  */
+  int32_t clip_bf16;  /* must be 0 (reserved).  The attention tables follow a_terms: fp32 (e^{2P}, fp32   */
+                      /*    clips) with two planes, fp16 (P, fp16 clips) with one                        */
 } echr_config_t;
 
 /* fp32 device pointers into the reference checkpoint's `cg_model` state_dict (train.py:456-461;
@@ -143,6 +151,15 @@ ECHR_API int echr_attention_step(const float* q_exp, const void* proj_exp, const
                         int clip_bf16, const float* alpha, const int32_t* row_start,
                         const int32_t* row_len, int64_t rows, float* out_f32, void* out_hi,
                         void* out_lo, int64_t ld_bf, int max_len, void* stream);
+
+/* The same step over 16-bit tables (what the single-plane precision runs; csrc/attention_f16.cuh):
+ * q [rows,512] fp32 = h2att(h1) + b (NOT exponentiated); proj16 [n_clips,512] fp16 = ctx2att(c3d) + b;
+ * clip16 [n_clips,512] fp16, columns 500..511 zero.  One warp per row: the window is streamed through a
+ * per-warp shared-memory ring by cp.async.bulk (1 KB projected row + 1 KB clip row per clip) and consumed in one
+ * pass with an online softmax.  out_f32 [rows,500] (may be NULL); out16 [rows, ld_out] fp16 (may be NULL). */
+ECHR_API int echr_attention_step_f16(const float* q, const void* proj16, const void* clip16, const float* alpha,
+                            const int32_t* row_start, const int32_t* row_len, int64_t rows, float* out_f32,
+                            void* out16, int64_t ld_out, void* stream);
 
 /* ---- model: packed weights --------------------------------------------------------------- */
 /* Packs the checkpoint into kernel layouts (bf16 planes, gate-interleaved LSTM rows, fused biases).
@@ -297,9 +314,11 @@ ECHR_API int echr_rerank_nms(const double* t1, const double* t2, const double* p
                     int topn, void* workspace, int32_t* out_pick, int32_t* out_count, int cap, void* stream);
 
 /* Measurement aid for bench.py's roofline: average duration in ms of each kernel of one decode step
- * (host_ms[5] = h2att GEMM, fused attention, LSTM gate GEMM, logit GEMM, finalize), from CUDA
- * events on `stream` around a captured graph of `iters` back-to-back plain launches of that kernel
- * (no host launch gaps, as in the decode graph).  Needs a decoded batch; synchronises. */
+ * (host_ms[6] = h2att GEMM, attention (stand-alone kernel), LSTM gate GEMM, logit GEMM, finalize, and the
+ * logit GEMM with the next step's attention on its extra warps — 0 when the batch does not decode with that
+ * kernel), from CUDA events on `stream` around a captured graph of `iters` back-to-back plain launches of that
+ * kernel (no host launch gaps, as in the decode graph), with the schedule the batch's decode uses (see
+ * echr_batch_set_concurrency).  Needs a decoded batch; synchronises. */
 ECHR_API int echr_time_step_kernels(echr_batch_t* batch, int beam, int iters, float* host_ms, void* stream);
 
 /* Debug aid: timeline of the last decode-graph replay when the graph was captured with ECHR_TRACE=1 in

@@ -234,3 +234,40 @@ def test_cfg4_whole_batch_matches_single_videos():
     single = m.engine.caption_device(*helpers.batch_of(vids[3:4], DEV), beam=1)[0].cpu()
     agree = float((single == tok[600:800]).all(1).float().mean())
     assert agree > 0.9, agree
+
+
+# ------------------------------------------------------------------------------------------------ topN = 1000
+def test_one_video_with_1000_proposals():
+    """The reference's default selection hands up to topN = 1000 proposals of one video to the caption call
+    (eval_utils.py:21,107-115): relation encoder over 1000 x 1000 pairs (key chunks + query blocks of the relation
+    attention, 7813 tiles of the fused pair kernel) against the oracle evaluated in query tiles, then the decode of
+    the first 24 proposals against the oracle's decode of those rows."""
+    precision = "fp32"
+    sd = sd_of(precision)
+    v = synth.make_video(7200, T=400, n_events=1000, style="sst")
+    m = model(precision)
+    lay, c3d, tap, lda = helpers.batch_of([v], DEV)
+    tok, lp, _ = m.engine.caption_device(lay, c3d, tap, lda, beam=1)
+    ev = m.engine.event_context().cpu()
+    soi, ind = v.soi_select_list, v.ind_select_list
+    pooled = torch.stack([v.c3d_feats[s:e].mean(0) for s, e in soi], 0)
+    feats = torch.cat([pooled, v.tap_feats[torch.as_tensor(ind)]], 1)
+    want_ev = O.relation_encode_tiled(sd, feats, soi, tile=50)
+    err = float((ev - want_ev).abs().max())
+    assert err < 2e-5, err
+    n_sub = 24
+    lmax = max(e - s for s, e in soi[:n_sub])
+    clip = torch.zeros(n_sub, lmax, 500)
+    mask = torch.zeros(n_sub, lmax)
+    for i, (s, e) in enumerate(soi[:n_sub]):
+        clip[i, :e - s] = v.c3d_feats[s:e]
+        mask[i, :e - s] = 1
+    s_ref, l_ref = O.greedy_decode(sd, v.lda_feats, want_ev[:n_sub], clip, mask)
+    tf = O.teacher_forced_logprobs(sd, v.lda_feats, want_ev[:n_sub], clip, mask, helpers.labels_of(s_ref))
+    c = s_ref.shape[1]
+    want_tok = torch.zeros(n_sub, 30, dtype=torch.long)
+    want_lp = torch.zeros(n_sub, 30)
+    want_tok[:, :c], want_lp[:, :c] = s_ref, l_ref
+    exc, worst = helpers.check_greedy_rows(tok[:n_sub].cpu().numpy(), lp[:n_sub].cpu().numpy(), want_tok, want_lp,
+                                           [(n_sub, c, tf)], LOGP_HELD[precision], "topN=1000")
+    print("1000 proposals: event ctx max |d| %.2e; first %d rows: %d excused, |dlogp| %.2e" % (err, n_sub, exc, worst))

@@ -63,3 +63,51 @@ def test_attention_step_matches_oracle(clip_bf16, staged):
     rec = hi.float() + lo.float()
     assert ((rec[:, :500] - out).abs() <= 2e-5 * out.abs() + 1e-7).all()  # hi+lo carries 16 mantissa bits
     assert (rec[:, 500:] == 0).all()
+
+
+@pytest.mark.parametrize("rows_mult", [1, 40])
+def test_attention_step_f16_matches_oracle(rows_mult):
+    """The 16-bit bulk-copy staged attention (csrc/attention_f16.cuh: fp16 projection and clip tables, one warp per
+    row, online softmax) against the oracle's `attend` on the same fp16-rounded tables: windows of 1 ... 300 clips,
+    a few rows (one per warp) and many rows (every warp walks several rows, the ring runs across row boundaries)."""
+    lib = _lib.load()
+    sd = helpers.state_dict("bf16w")
+    a = "lm_model.core.attention."
+    g = torch.Generator().manual_seed(5)
+    T = 300
+    c3d = torch.randn(T, 500, generator=g).half().float()
+    lens = [1, 2, 7, 33, 64, 100, 257, 300, 5] * rows_mult
+    starts = [0, 299 - 1, 10, 200, 100, 150, 20, 0, 295] * rows_mult
+    n = len(lens)
+    h = torch.randn(n, 512, generator=g) * 0.3
+    proj = torch.nn.functional.linear(c3d, sd[a + "ctx2att.weight"], sd[a + "ctx2att.bias"]).half()
+    q = torch.nn.functional.linear(h, sd[a + "h2att.weight"], sd[a + "h2att.bias"])
+    alpha = sd[a + "alpha_net.weight"].reshape(-1).contiguous()
+    # oracle on the rounded tables: scores from the fp16 projection, features from the fp16 clips
+    want = torch.zeros(n, 500)
+    for i, (s, l) in enumerate(zip(starts, lens)):
+        sc = torch.tanh(proj[s:s + l].float() + q[i]) @ alpha
+        want[i] = torch.softmax(sc, 0) @ c3d[s:s + l]
+    clip_d = torch.zeros(T, 512, dtype=torch.float16, device=DEV)
+    clip_d[:, :500] = c3d.to(DEV).half()
+    rs = torch.tensor(starts, dtype=torch.int32, device=DEV)
+    rl = torch.tensor(lens, dtype=torch.int32, device=DEV)
+    out = torch.full((n, 500), float("nan"), device=DEV)
+    out16 = torch.full((n, 512), float("nan"), dtype=torch.float16, device=DEV)
+    _lib.check(lib.echr_attention_step_f16(q.to(DEV).data_ptr(), proj.to(DEV).contiguous().data_ptr(), clip_d.data_ptr(),
+                                           alpha.to(DEV).data_ptr(), rs.data_ptr(), rl.data_ptr(), n, out.data_ptr(),
+                                           out16.data_ptr(), 512, torch.cuda.current_stream().cuda_stream), "attention_f16")
+    torch.cuda.synchronize()
+    err = (out.cpu() - want).abs().max().item()
+    print("attention_f16 max err", err)
+    assert err < 2e-5, err
+    assert ((out16[:, :500].float() - out).abs() <= 1e-3 * out.abs() + 1e-6).all()
+    assert (out16[:, 500:] == 0).all()
+    # against the reference arithmetic on unrounded inputs: the fp16 tables cost < 2e-3
+    clip = torch.zeros(9, 300, 500)
+    mask = torch.zeros(9, 300)
+    for i, (s, l) in enumerate(zip(starts[:9], lens[:9])):
+        clip[i, :l] = c3d[s:s + l]
+        mask[i, :l] = 1
+    ref = O.attend(sd, h[:9], clip, mask)
+    assert (out[:9].cpu() - ref).abs().max().item() < 2e-3
