@@ -199,6 +199,7 @@ class CaptionGenerator(nn.Module):
         for sub in (self.fusion_model, self.lm_model):  # the sub-modules run on this module's engine
             object.__setattr__(sub, "_owner", weakref.ref(self))
         self._engine = None
+        self._engine_versions = None
         self.eval()
 
     # -- engine lifetime: rebuilt whenever the parameters may have changed
@@ -221,14 +222,22 @@ class CaptionGenerator(nn.Module):
         self.precision = precision
         self._invalidate()
 
+    def _param_versions(self):
+        # torch bumps a tensor's _version on every in-place write (optimizer steps, p.data.copy_, sub-module
+        # load_state_dict): the packed engine is stale as soon as any of them moves
+        return tuple(p._version for p in self.parameters())
+
     @property
     def engine(self):
+        if self._engine is not None and self._engine_versions != self._param_versions():
+            self._invalidate()
         if self._engine is None:
             dev = next(self.parameters()).device
             if dev.type != "cuda":
                 raise RuntimeError("echr_b200.CaptionGenerator has no CPU path: call .cuda() first")
             self._engine = Engine(self.state_dict(), self.opt.CG_vocab_size, self.opt.CG_seq_length,
                                   precision=self.precision, device=dev)
+            self._engine_versions = self._param_versions()
         return self._engine
 
     # -- batched API (additive)

@@ -408,6 +408,7 @@ static void batch_layout(echr_batch* b, Arena& a) {
   b->beam_hist_tok = a.take<int32_t>((size_t)2 * c.max_rows * S);
   b->beam_hist_lp = a.take<float>((size_t)2 * c.max_rows * S);
   b->best_score = a.take<float>(c.max_events);
+  b->beam_trace = a.take<int32_t>((size_t)2 * S * c.max_rows);
   b->trace = a.take<unsigned long long>(2 * TRACE_SLOTS);
   b->trace_detail = a.take<unsigned long long>(4 * TRACE_SLOTS);
 }
@@ -893,7 +894,9 @@ static int enqueue_step(echr_batch* b, int rows, int t, int topk, float* logits_
     // latency regime: narrow tiles spread the [rows,512] x [512,512] product over 4x the SMs (a CTA's
     // main loop is bound by its own L2->SM operand stream, dominated by the 2-plane activation tile)
     // (lanes sharing the GPU: one wide tile per 128 rows costs a third of the SM time of four narrow ones)
-    const int bn = rows < gemm2_min_rows() ? (b->concurrency > 1 ? 128 : 32) : 128;
+    // (throughput regime: 128 x 64 tiles, one per CTA: a [rows,512] x [512,512] product has only rows/64 tiles of
+    // the persistent kernel's 128 x 256 shape, 32 CTAs at 2048 rows)
+    const int bn = rows < gemm2_min_rows() ? (b->concurrency > 1 ? 128 : 32) : 64;
     ECHR_TRY(run_gemm(&s, 1, at, wt, bn, EPI_STORE, 1, st, "h2att", b, 0));
   }
   if (parts & PART_ATT) {
@@ -1089,6 +1092,23 @@ extern "C" int echr_decode_beam(echr_batch_t* b, int beam, int32_t* tokens, floa
   cudaStream_t st = (cudaStream_t)stream;
   ECHR_TRY(run_decode(b, beam, MODE_BEAM, st));
   return copy_results(b, tokens, logp, score, cudaMemcpyDeviceToDevice, st);
+}
+
+// The decisions of the last echr_decode_beam / beam caption call: for every step t and decode row r = event * beam +
+// slot, the parent slot (within the event) and the token the new slot r was built from.  parent / tok: int32 device
+// [seq_length, rows].  This is what the parity tests replay with the oracle's arithmetic.
+extern "C" int echr_get_beam_trace(const echr_batch_t* b, int beam, int32_t* parent, int32_t* tok, void* stream) {
+  ECHR_REQUIRE(b && parent && tok, "echr_get_beam_trace: null argument");
+  ECHR_REQUIRE(beam >= 1 && (long long)b->n_events * beam <= b->cap.max_rows, "echr_get_beam_trace: bad beam");
+  const int S = b->model->cfg.seq_length;
+  const size_t rows = (size_t)b->n_events * beam;
+  if (rows == 0) return ECHR_OK;
+  cudaStream_t st = (cudaStream_t)stream;
+  ECHR_CUDA(cudaMemcpy2DAsync(parent, rows * sizeof(int32_t), b->beam_trace, (size_t)b->cap.max_rows * sizeof(int32_t),
+                              rows * sizeof(int32_t), S, cudaMemcpyDeviceToDevice, st));
+  ECHR_CUDA(cudaMemcpy2DAsync(tok, rows * sizeof(int32_t), b->beam_trace + (size_t)S * b->cap.max_rows,
+                              (size_t)b->cap.max_rows * sizeof(int32_t), rows * sizeof(int32_t), S, cudaMemcpyDeviceToDevice, st));
+  return ECHR_OK;
 }
 
 extern "C" int echr_teacher_forced(echr_batch_t* b, const int32_t* seq, int seq_cols, float* logprobs,

@@ -117,6 +117,7 @@ struct echr_batch {
   int32_t* beam_hist_tok;   // [2][rows][S]
   float* beam_hist_lp;      // [2][rows][S]
   float* best_score;        // [events]
+  int32_t* beam_trace;      // [2][S][max_rows]: parent slot / token every new slot was built from, per step
   // CUDA graph cache (LRU): decode graphs keyed by (rows, beam mode, window-length bucket), encode graphs
   // keyed by the batch shape.  A key holds every host-side value the enqueue code bakes into the launches.
   struct GraphSlot {

@@ -864,7 +864,8 @@ finalize_beam_kernel(int beam, int n_tiles, int step, int seq_len, const float* 
                      const int32_t* __restrict__ hist_tok_in, int32_t* __restrict__ hist_tok_out,
                      const float* __restrict__ hist_lp_in, float* __restrict__ hist_lp_out,
                      float* __restrict__ best_score, int32_t* __restrict__ tokens,
-                     float* __restrict__ logp, float* __restrict__ score_out) {
+                     float* __restrict__ logp, float* __restrict__ score_out,
+                     int32_t* __restrict__ trace_parent, int32_t* __restrict__ trace_tok) {
   constexpr int W = LogitRec<4>::WORDS;
   __shared__ float cand_total[BEAM_MAX][BEAM_MAX];
   __shared__ float cand_lp[BEAM_MAX][BEAM_MAX];
@@ -946,6 +947,10 @@ finalize_beam_kernel(int beam, int n_tiles, int step, int seq_len, const float* 
   __syncthreads();
 
   // ---- 3. histories (ping-pong), scores, live flags, result update
+  if (warp < beam && lane == 0) {  // the step's decisions, for echr_get_beam_trace (what the parity tests verify)
+    trace_parent[row0 + warp] = sel_parent[warp];
+    trace_tok[row0 + warp] = sel_tok[warp];
+  }
   if (warp < beam) {
     const int r = row0 + warp, pr = row0 + sel_parent[warp];
     for (int t = lane; t < seq_len; t += 32) {
@@ -1044,7 +1049,8 @@ cudaError_t launch_finalize_beam(const echr_batch* b, int beam, int step, int32_
       beam, n_tiles, step, S, b->partial, b->row_tok, nxt.p,
       nxt.plane_stride(), (int)nxt.planes, b->cstate[(step + 1) & 1], rows * HID, b->beam_score,
       b->beam_live, b->beam_hist_tok + in * hist, b->beam_hist_tok + out * hist,
-      b->beam_hist_lp + in * hist, b->beam_hist_lp + out * hist, b->best_score, tokens, logp, score);
+      b->beam_hist_lp + in * hist, b->beam_hist_lp + out * hist, b->best_score, tokens, logp, score,
+      b->beam_trace + (long long)step * b->cap.max_rows, b->beam_trace + ((long long)S + step) * b->cap.max_rows);
   count_launch();
   return cudaGetLastError();
 }

@@ -5,6 +5,7 @@ libechr_b200.so.  There is no fallback path: a missing library or a non-sm_100 d
 """
 import ctypes
 import itertools
+import weakref
 
 import numpy as np
 import torch
@@ -96,6 +97,7 @@ class Engine(object):
                                              ctypes.byref(self._model)), "echr_model_create")
             del keep  # echr_model_create synchronises; the packed copy is what the kernels read
         self._parent = None  # set on a fork(): the engine that owns the packed model
+        self._forks = []     # weak references to the forks sharing this engine's packed model
 
     def set_concurrency(self, lanes):
         """Tell the workspace how many batches of the job share the GPU (see echr_batch_set_concurrency)."""
@@ -112,11 +114,23 @@ class Engine(object):
         e._cap = None
         e.layout = None
         e._parent = self._parent or self
+        e._forks = []
+        e._parent._forks.append(weakref.ref(e))
         return e
 
     # ------------------------------------------------------------------ lifetime
     def close(self):
+        """Frees the workspace and, for the owning engine, the packed model.  Forks still alive (the lanes of a
+        CaptionPipeline) are closed first: they point into the model that is about to be destroyed, and any later
+        call on them raises instead of touching freed memory."""
+        for ref in getattr(self, "_forks", []):
+            f = ref()
+            if f is not None and f is not self:
+                f.close()
+        self._forks = []
         if getattr(self, "_batch", None) is not None and self._batch.value:
+            if torch.cuda.is_available():
+                torch.cuda.synchronize(self.device)
             self.lib.echr_batch_destroy(self._batch)
             self._batch = ctypes.c_void_p()
         if getattr(self, "_parent", None) is not None:
@@ -135,6 +149,8 @@ class Engine(object):
     def reserve(self, n_videos, n_clips, n_events, n_pairs, beam=1):
         """Make sure the workspace holds a batch of this size (re-allocates only when it grows)."""
         need = (n_videos, n_clips, max(n_events, 1), max(n_pairs, 1), max(n_events, 1) * beam)
+        if not self._model.value:
+            raise EchrError("this engine was closed (its model was re-packed or moved): build a new CaptionPipeline / engine")
         if self._cap is not None and all(c >= n for c, n in zip(self._cap, need)):
             return
         if self._cap is not None:
@@ -198,6 +214,16 @@ class Engine(object):
             check(self.lib.echr_decode_beam(self._batch, int(beam), tokens.data_ptr(), logp.data_ptr(),
                                             score.data_ptr(), _stream()), "echr_decode_beam")
         return tokens, logp, score
+
+    def beam_trace(self, beam):
+        """(parent, token) decisions of the last beam decode: two int32 tensors [S, n_events, beam]."""
+        n, S = self.layout.n_events, self.seq_length
+        parent = torch.zeros(S, n, beam, dtype=torch.int32, device=self.device)
+        tok = torch.zeros(S, n, beam, dtype=torch.int32, device=self.device)
+        with torch.cuda.device(self.device):
+            check(self.lib.echr_get_beam_trace(self._batch, int(beam), parent.data_ptr(), tok.data_ptr(), _stream()),
+                  "echr_get_beam_trace")
+        return parent, tok
 
     def teacher_forced(self, seq):
         """seq int [n_events, S] (column 0 = BOS) -> log-probs fp32 [n_events, S-1, V+1]."""

@@ -210,6 +210,10 @@ ECHR_API int echr_decode_greedy(echr_batch_t* batch, int32_t* tokens, float* log
  * padded, score [n_events] = cumulative log-probability of the returned hypothesis. */
 ECHR_API int echr_decode_beam(echr_batch_t* batch, int beam, int32_t* tokens, float* logp, float* score,
                      void* stream);
+/* The decisions of the last beam decode of this batch: for every step t and decode row r = event * beam + slot,
+ * the parent slot (within the event) and the token the new slot was built from; parent / tok: int32 device
+ * [seq_length, n_events * beam].  Lets a caller (the parity tests) replay the search with reference arithmetic. */
+ECHR_API int echr_get_beam_trace(const echr_batch_t* batch, int beam, int32_t* parent, int32_t* tok, void* stream);
 /* Teacher-forced log-probabilities (models/OldModel_NEW.py:98-130): seq int32 [n_events, seq_cols]
  * (column 0 = BOS = 0); logprobs fp32 [n_events, seq_cols-1, vocab_size+1]. */
 ECHR_API int echr_teacher_forced(echr_batch_t* batch, const int32_t* seq, int seq_cols, float* logprobs,

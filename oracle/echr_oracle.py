@@ -329,3 +329,73 @@ def beam_search(sd, video, event, clip, mask, beam=3, seq_length=30, return_all=
 def caption_video_beam(sd, tap_feats, c3d_feats, lda_feats, ind, soi, beam=3, seq_length=30):
     video, event, clip, mask = build_context(sd, tap_feats, c3d_feats, lda_feats, ind, soi)
     return beam_search(sd, video, event, clip, mask, beam, seq_length)
+
+
+def replay_beam_trace(sd, video, event, clip, mask, parent, tok, beam, seq_length=30):
+    """Replays a beam search whose per-step decisions (parent slot, token of every new slot: int [S,N,beam]) were
+    made elsewhere — the CUDA path, echr_get_beam_trace — with THIS module's arithmetic, and measures how far each
+    decision is from the one the spec (`beam_search`) would have made on the same beam state:
+      * `regret` [S,N]: (score of the beam-th best proposal of the step) - (score of the worst proposal the trace
+        kept), clipped at 0.  0 = the trace kept a best-`beam` set; a value below the near-tie threshold means the
+        two differ by a near tie; anything larger is a wrong decision.
+      * `invalid`: steps where the trace chose a dead parent or the same proposal twice (must be empty).
+      * the finished hypotheses along the trace (per event: list of (score, tokens[S], logp[S])) and, from them,
+        the best one per event by the spec's rule (strictly greater score; earlier step / lower slot wins ties).
+    Returns dict(regret, invalid, best_tok [N,S], best_lp [N,S], best_score [N], finished)."""
+    n = event.shape[0]
+    parent = torch.as_tensor(np.asarray(parent)).long()
+    tok = torch.as_tensor(np.asarray(tok)).long()
+    rep = lambda x: x.repeat_interleave(beam, 0)
+    ev, cl, mk = rep(event), rep(clip), rep(mask)
+    state = init_state(n * beam)
+    it = torch.zeros(n * beam, dtype=torch.long)
+    live = torch.zeros(n, beam, dtype=torch.bool)
+    live[:, 0] = True
+    score = torch.zeros(n, beam)
+    hist_tok = torch.zeros(n, beam, seq_length, dtype=torch.long)
+    hist_lp = torch.zeros(n, beam, seq_length)
+    regret = torch.zeros(seq_length, n)
+    invalid = []
+    finished = [[] for _ in range(n)]
+    best_score = torch.full((n,), -float("inf"))
+    best_tok = torch.zeros(n, seq_length, dtype=torch.long)
+    best_lp = torch.zeros(n, seq_length)
+    for t in range(seq_length):
+        logprobs, state = decode_step(sd, it, video, ev, cl, mk, state)
+        lp3 = logprobs.reshape(n, beam, -1)
+        total = score.unsqueeze(2) + lp3  # [n, beam, V+1] proposal scores
+        total = torch.where(live.unsqueeze(2), total, torch.full_like(total, -float("inf")))
+        kth = torch.topk(total.reshape(n, -1), beam, dim=1)[0][:, beam - 1]  # beam-th best proposal
+        p_t, k_t = parent[t], tok[t]  # [n, beam]
+        chosen = torch.gather(total.reshape(n, -1), 1, p_t * lp3.shape[2] + k_t)  # [n, beam]
+        chosen_lp = torch.gather(lp3.reshape(n, -1), 1, p_t * lp3.shape[2] + k_t)
+        any_live = live.any(1)
+        for e in range(n):
+            if not bool(any_live[e]):
+                continue  # every slot finished: nothing to choose (only possible after the last step)
+            pairs = set()
+            for k in range(beam):
+                key = (int(p_t[e, k]), int(k_t[e, k]))
+                if not bool(live[e, key[0]]) or key in pairs:
+                    invalid.append((t, e, k))
+                pairs.add(key)
+        regret[t] = torch.where(any_live, (kth - chosen.min(1)[0]).clamp(min=0), torch.zeros(n))
+        src = (torch.arange(n).unsqueeze(1) * beam + p_t).reshape(-1)
+        state = (state[0][:, src], state[1][:, src])
+        hist_tok = torch.gather(hist_tok, 1, p_t.unsqueeze(2).expand(-1, -1, seq_length)).clone()
+        hist_lp = torch.gather(hist_lp, 1, p_t.unsqueeze(2).expand(-1, -1, seq_length)).clone()
+        hist_tok[:, :, t] = k_t
+        hist_lp[:, :, t] = chosen_lp
+        score = chosen
+        fin = ((k_t == 0) | (t == seq_length - 1)) & any_live.unsqueeze(1)
+        for e in range(n):
+            for k in range(beam):
+                if bool(fin[e, k]) and float(score[e, k]) > -float("inf"):
+                    finished[e].append((float(score[e, k]), hist_tok[e, k].clone(), hist_lp[e, k].clone()))
+                    if float(score[e, k]) > float(best_score[e]):
+                        best_score[e] = score[e, k]
+                        best_tok[e] = hist_tok[e, k]
+                        best_lp[e] = hist_lp[e, k]
+        live = ~fin & any_live.unsqueeze(1)
+        it = k_t.reshape(-1)
+    return dict(regret=regret, invalid=invalid, best_tok=best_tok, best_lp=best_lp, best_score=best_score, finished=finished)

@@ -142,30 +142,30 @@ def beam_len(row):
     return int(z[0]) + 1 if z.size else len(row)
 
 
-def check_beam(got_tok, want_tok, want_score, trace, cum_got, what=""):
-    """Beam rule (BASELINE north_star, applied to cumulative scores): a returned hypothesis must be the oracle's
-    unless the FIRST decision that separates them is a near tie in the oracle's own arithmetic:
-      * the first step t at which the oracle's beam does not keep got[:t+1]: the worst kept score at t must be
-        within NEAR_TIE of the oracle's score of got[:t+1] (`cum_got[r,t]`, teacher-forced along got), or
-      * got stays in the oracle's beam to its end: it was a finished hypothesis there, and the oracle's best
-        must be within NEAR_TIE of got's score.
-    trace = oracle beam_search(..., return_trace=True)[-1].  Returns (identical rows, excused rows)."""
-    got_tok, want_tok = np.asarray(got_tok), np.asarray(want_tok)
-    same = excused = 0
-    for r in range(want_tok.shape[0]):
-        if (got_tok[r] == want_tok[r]).all():
-            same += 1
-            continue
-        L = beam_len(got_tok[r])
-        for t in range(L):
-            kept = trace[t]["kept_tok"][r].numpy()  # [beam, t+1]
-            if not (kept == got_tok[r, :t + 1][None, :]).all(1).any():
-                gap = float(trace[t]["kept_score"][r].min()) - float(cum_got[r, t])
-                assert gap < NEAR_TIE, "%s row %d: prefix dropped by the oracle at step %d with score gap %.3e" % (
-                    what, r, t, gap)
-                break
-        else:
-            gap = float(want_score[r]) - float(cum_got[r, L - 1])
-            assert gap < NEAR_TIE, "%s row %d: finished hypothesis loses to the oracle's best by %.3e" % (what, r, gap)
-        excused += 1
-    return same, excused
+def check_beam_replay(sd, v, beam, got_tok, got_lp, got_score, parent, tok, lp_tol, what=""):
+    """Beam rule (BASELINE north_star, applied to the search's decisions): the CUDA path's per-step decisions
+    (echr_get_beam_trace) are replayed with the oracle's arithmetic (oracle.replay_beam_trace).  Every step must
+    keep a best-`beam` set of proposals up to a near tie (the worst kept proposal within NEAR_TIE of the beam-th
+    best one), from live parents, without duplicates; the returned hypothesis must be the best finished one along
+    the trace (or within NEAR_TIE of it); its log-probs / score must be the oracle's within lp_tol.
+    Returns (rows whose decisions all had zero regret, max regret, rows equal to the spec's own search)."""
+    from oracle import echr_oracle as O
+    ctx = O.build_context(sd, v.tap_feats, v.c3d_feats, v.lda_feats, v.ind_select_list, v.soi_select_list)
+    r = O.replay_beam_trace(sd, *ctx, parent, tok, beam)
+    assert not r["invalid"], "%s: invalid decisions (dead parent / duplicate proposal) at %s" % (what, r["invalid"][:5])
+    regret = r["regret"].numpy()  # [S, N]
+    worst = float(regret.max())
+    assert worst < NEAR_TIE, "%s: a step kept a proposal %.3e below the beam-th best one (step %d, event %d)" % (
+        what, worst, *np.unravel_index(regret.argmax(), regret.shape))
+    got_tok, got_lp, got_score = np.asarray(got_tok), np.asarray(got_lp), np.asarray(got_score)
+    for e in range(got_tok.shape[0]):
+        match = [f for f in r["finished"][e] if (f[1].numpy() == got_tok[e]).all()]
+        assert match, "%s event %d: the returned hypothesis is not a finished hypothesis of its own trace" % (what, e)
+        sc, _, lps = match[0]
+        assert float(r["best_score"][e]) - sc < NEAR_TIE, "%s event %d: returned hypothesis loses to the best finished one by %.3e" % (
+            what, e, float(r["best_score"][e]) - sc)
+        L = beam_len(got_tok[e])
+        assert np.abs(lps.numpy()[:L] - got_lp[e, :L]).max() < lp_tol, (what, e)
+        assert abs(sc - float(got_score[e])) < 30 * lp_tol, (what, e, sc, float(got_score[e]))
+    t_ref = O.beam_search(sd, *ctx, beam=beam)[0].numpy()
+    return int((regret.max(0) == 0).sum()), worst, int((t_ref == got_tok).all(1).sum())

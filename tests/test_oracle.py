@@ -86,18 +86,26 @@ def test_regime_helpers_accept_the_oracle_and_reject_a_wrong_row():
     bad[0, t] = (bad[0, t] + 1) % 5748
     with pytest.raises(AssertionError):
         helpers.check_greedy_rows(bad, lp.numpy(), tok, lp, per_video, 1e-6)
+    # beam: a trace of the spec's own decisions replays with zero regret; a trace that keeps a clearly worse proposal
+    # is measured as such
     v = vids[1]
     ctx = O.build_context(sd, v.tap_feats, v.c3d_feats, v.lda_feats, v.ind_select_list, v.soi_select_list)
     t_ref, l_ref, s_ref, trace = O.beam_search(sd, *ctx, beam=3, return_trace=True)
-    cum = torch.cumsum(l_ref, 1).numpy()
-    assert helpers.check_beam(t_ref.numpy(), t_ref.numpy(), s_ref.numpy(), trace, cum) == (4, 0)
-    # the greedy hypothesis instead of the beam's best: refused unless it is the same or a near tie
-    g_tok = tok[3:7].numpy()
-    if not (g_tok == t_ref.numpy()).all():
-        tf = O.teacher_forced_logprobs(sd, *ctx, helpers.labels_of(g_tok))
-        picked = torch.gather(tf, 2, torch.as_tensor(g_tok)[:, :tf.shape[1]].unsqueeze(2)).squeeze(2)
-        cum_g = np.zeros((4, 30), np.float32)
-        cum_g[:, :tf.shape[1]] = torch.cumsum(picked, 1).numpy()
-        cum_g[:, tf.shape[1]:] = cum_g[:, tf.shape[1] - 1:tf.shape[1]]
-        with pytest.raises(AssertionError):
-            helpers.check_beam(g_tok, t_ref.numpy(), s_ref.numpy(), trace, cum_g)
+    S, n, B = 30, 4, 3
+    parent, tok = np.zeros((S, n, B), int), np.zeros((S, n, B), int)
+    prev = None
+    for t in range(S):
+        kt = trace[t]["kept_tok"].numpy()
+        tok[t] = kt[:, :, t]
+        for e in range(n):
+            for k in range(B):
+                if t > 0:
+                    parent[t, e, k] = [b for b in range(B) if (prev[e, b] == kt[e, k, :t]).all()][0]
+        prev = kt
+    r = O.replay_beam_trace(sd, *ctx, parent, tok, 3)
+    assert float(r["regret"].max()) == 0.0 and not r["invalid"] and torch.equal(r["best_tok"], t_ref)
+    clean, worst, same = helpers.check_beam_replay(sd, v, 3, t_ref.numpy(), l_ref.numpy(), s_ref.numpy(), parent, tok, 1e-5)
+    assert (clean, worst, same) == (4, 0.0, 4)
+    bad = tok.copy()
+    bad[3, 0, 2] = 17  # an arbitrary token instead of the third-best proposal
+    assert float(O.replay_beam_trace(sd, *ctx, parent, bad, 3)["regret"][3, 0]) > 1e-2

@@ -1,51 +1,70 @@
-"""Turns gpurun_out/prof_launches.csv (tools/gpu_profile.sh) and gpurun_out/prof_step.ncu-rep (tools/gpu_profile_full.sh) into the
-tracked summaries under profiles/:  python tools/summarize_profile.py <tag>"""
+"""Turns ncu output brought back in gpurun_out/ into the tracked summaries under profiles/.
+
+    python tools/summarize_profile.py launches <launches.csv> <out.md> "<command the list was taken from>"
+    python tools/summarize_profile.py full <report.ncu-rep> <out_prefix> "<title>"     (needs ncu on this machine)
+"""
 import collections
 import csv
+import re
 import subprocess
 import sys
 
-tag = sys.argv[1] if len(sys.argv) > 1 else "r01_final"
-rows = [r for r in csv.reader(open("gpurun_out/prof_launches.csv")) if len(r) > 5]
-hdr = rows[0]
-iK, iV, iG = hdr.index("Kernel Name"), hdr.index("Metric Value"), hdr.index("Grid Size")
-agg = collections.OrderedDict()
-seq = []
-for r in rows[1:]:
-    try:
-        ns = float(r[iV].replace(",", ""))
-    except ValueError:
-        continue
-    name = r[iK]
-    key = (name[:64], r[iG])
-    a = agg.setdefault(key, [0, 0.0])
-    a[0] += 1
-    a[1] += ns
-    seq.append((name, r[iG], ns))
-tot = sum(a[1] for a in agg.values())
-with open("profiles/%s_launch_shares_cfg2_f16.md" % tag, "w") as f:
-    f.write("# ncu launch list of `python bench.py --steps 2 --warmup 2 --no-cpu-baseline` (cfg2, f16, 3 batches in flight)\n\n")
-    f.write("`ncu --metrics gpu__time_duration.sum --clock-control none -c 2000` (cold-cache, serialised: compare shares). "
-            "Raw list: %s_launches_cfg2_f16.csv\n\n" % tag)
-    f.write("| kernel | grid | launches | total us | avg us | share |\n|---|---|---|---|---|---|\n")
-    for (name, grid), (n, ns) in sorted(agg.items(), key=lambda kv: -kv[1][1]):
-        f.write("| `%s` | %s | %d | %.1f | %.2f | %.1f%% |\n" % (name, grid, n, ns / 1e3, ns / n / 1e3, 100 * ns / tot))
-    f.write("\nTemplate args of gemm_tc_kernel: <A_TERMS, W_TERMS, BLOCK_N, EPI (0 store, 1 LSTM, 2 logits), TOPK, SPLIT (cluster size)>.\n")
-subprocess.check_call("cp gpurun_out/prof_launches.csv profiles/%s_launches_cfg2_f16.csv" % tag, shell=True)
-
-raw = subprocess.run(["ncu", "-i", "gpurun_out/prof_step.ncu-rep", "--page", "raw", "--csv"], capture_output=True, text=True).stdout
-open("profiles/%s_ncu_step_kernels_raw.csv" % tag, "w").write(raw)
-rr = list(csv.reader(raw.splitlines()))
-h, u = rr[0], rr[1]
-keys = ["Kernel Name", "launch__grid_size", "launch__cluster_dim_x", "gpu__time_duration.sum", "dram__bytes_read.sum", "dram__bytes_write.sum",
-        "l1tex__m_xbar2l1tex_read_bytes.sum", "lts__t_sector_hit_rate.pct",
+KEYS = ["Kernel Name", "launch__grid_size", "launch__block_size", "gpu__time_duration.sum", "dram__bytes_read.sum", "dram__bytes_write.sum",
+        "lts__t_bytes.sum", "l1tex__m_xbar2l1tex_read_bytes.sum", "lts__t_sector_hit_rate.pct",
         "sm__pipe_tensor_cycles_active.avg.pct_of_peak_sustained_active", "sm__warps_active.avg.pct_of_peak_sustained_active",
-        "launch__registers_per_thread", "launch__shared_mem_per_block_dynamic", "sm__cycles_active.avg"]
-with open("profiles/%s_ncu_step_kernels.md" % tag, "w") as f:
-    f.write("# `ncu --set full --clock-control none` of the decode-step kernels (cfg2, f16, 251 rows)\n\n"
-            "Cold-cache replays (ncu flushes L2 between passes): DRAM bytes include the weights, which stay in L2 "
-            "inside the real decode graph.  Raw page: %s_ncu_step_kernels_raw.csv\n\n" % tag)
-    f.write("| " + " | ".join(k.split(".")[0] for k in keys) + " |\n|" + "---|" * len(keys) + "\n")
-    for r in rr[2:]:
-        f.write("| " + " | ".join((r[h.index(k)][:60] + " " + u[h.index(k)]) if k in h else "-" for k in keys) + " |\n")
-print("wrote profiles/%s_*" % tag)
+        "sm__throughput.avg.pct_of_peak_sustained_elapsed", "dram__throughput.avg.pct_of_peak_sustained_elapsed",
+        "launch__registers_per_thread", "launch__shared_mem_per_block_dynamic"]
+
+
+def short(name):
+    name = re.sub(r"\(.*", "", name).replace("echr::", "").replace("void ", "")
+    return name[:90]
+
+
+def launches(path, out, cmd):
+    rows = [r for r in csv.reader(open(path)) if len(r) > 5]
+    hdr = rows[0]
+    iK, iV, iG = hdr.index("Kernel Name"), hdr.index("Metric Value"), hdr.index("Grid Size")
+    agg = collections.OrderedDict()
+    for r in rows[1:]:
+        try:
+            ns = float(r[iV].replace(",", ""))
+        except ValueError:
+            continue
+        a = agg.setdefault((short(r[iK]), r[iG]), [0, 0.0])
+        a[0] += 1
+        a[1] += ns
+    tot = sum(a[1] for a in agg.values())
+    with open(out, "w") as f:
+        f.write("# ncu launch list of `%s`\n\n" % cmd)
+        f.write("`ncu --metrics gpu__time_duration.sum --clock-control none` (per-launch times are cold-cache and serialised: "
+                "compare SHARES, not absolutes).  %d launches, %.2f ms in total.\n\n" % (sum(a[0] for a in agg.values()), tot / 1e6))
+        f.write("| kernel | grid | launches | total us | avg us | share |\n|---|---|---|---|---|---|\n")
+        for (name, grid), (n, ns) in sorted(agg.items(), key=lambda kv: -kv[1][1]):
+            f.write("| `%s` | %s | %d | %.1f | %.2f | %.1f%% |\n" % (name, grid, n, ns / 1e3, ns / n / 1e3, 100 * ns / tot))
+        f.write("\nTemplate arguments: gemm_tc_kernel<A_TERMS, W_TERMS, BLOCK_N, EPI (0 store, 1 LSTM, 2 logits), TOPK, SPLIT>; "
+                "gemm_tc2_kernel<A_TERMS, W_TERMS, EPI, TOPK, ATT>; pair_mlp_kernel<A_TERMS, W_TERMS>.\n")
+    print("wrote", out)
+
+
+def full(rep, prefix, title):
+    raw = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
+    open(prefix + "_raw.csv", "w").write(raw)
+    rr = list(csv.reader(raw.splitlines()))
+    h, u = rr[0], rr[1]
+    with open(prefix + ".md", "w") as f:
+        f.write("# %s\n\n`ncu --set full --clock-control none` (cold-cache replays: ncu flushes L2 between passes, so DRAM bytes include "
+                "operands that are L2-resident inside the real decode graph).  Raw page: %s_raw.csv\n\n" % (title, prefix.split("/")[-1]))
+        keys = [k for k in KEYS if k in h]
+        f.write("| " + " | ".join(k.split(".")[0] for k in keys) + " |\n|" + "---|" * len(keys) + "\n")
+        for r in rr[2:]:
+            f.write("| " + " | ".join((short(r[h.index(k)]) if k == "Kernel Name" else r[h.index(k)][:24] + " " + u[h.index(k)]) for k in keys) + " |\n")
+    print("wrote", prefix + ".md")
+
+
+if __name__ == "__main__":
+    mode = sys.argv[1]
+    if mode == "launches":
+        launches(sys.argv[2], sys.argv[3], sys.argv[4])
+    else:
+        full(sys.argv[2], sys.argv[3], sys.argv[4])
