@@ -183,7 +183,7 @@ gemm_tc2_kernel(const __grid_constant__ GemmParams P, int groups, int total_tile
         umma_commit(tmem_full_bar(buf));
       }
     }
-  } else if (warp >= 4) {
+  } else if (warp >= 4 && warp < 4 + GEMM_EPI_WARPS) {
     // ===================== epilogue =====================
     constexpr int HALF = BN / 2;  // 128 columns per thread
     constexpr int NCH = HALF / 32;

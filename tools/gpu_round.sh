@@ -6,7 +6,9 @@ O=gpurun_out/$TAG
 mkdir -p $O
 for w in $WHAT; do case $w in
 tests)
-  timeout 1500 python -m pytest tests -m gpu -q --tb=short -p no:cacheprovider -rA > $O/pytest.log 2>&1; echo "pytest exit=$?" >> $O/pytest.log ;;
+  # (the regime tests in their own process: a crashed kernel there must not poison the rest of the suite)
+  timeout 1200 python -m pytest tests/test_0_regimes_gpu.py tests/test_kernels_gpu.py -m gpu -q --tb=short -p no:cacheprovider -rA > $O/pytest_regimes.log 2>&1; echo "pytest exit=$?" >> $O/pytest_regimes.log
+  timeout 1500 python -m pytest tests -m gpu -q --tb=short -p no:cacheprovider -rA --deselect tests/test_0_regimes_gpu.py --deselect tests/test_kernels_gpu.py > $O/pytest.log 2>&1; echo "pytest exit=$?" >> $O/pytest.log ;;
 bench)
   timeout 900 python bench.py > $O/bench_cfg5.json 2> $O/bench_cfg5.err
   timeout 600 python bench.py --impl reference --steps 3 --warmup 1 > $O/bench_ref.json 2> $O/bench_ref.err
