@@ -458,9 +458,6 @@ def _main(args):
     k_walked = (8 + 16 + 8) * 64 if hoisted else (16 + 16 + 10) * 64
     issued = {"lstm_gates": 2.0 * rows * 2048 * k_walked, "logit": 2.0 * rows * V1 * 1536}
     algorithmic = {"lstm_gates": 2.0 * rows * 2048 * (1024 + 1524 + 1024), "logit": 2.0 * rows * V1 * 1536}
-    fused = kt.get("logit_with_attention", 0.0) > 0.0  # the logit launch also runs the next step's attention
-    if fused:
-        kt = dict(kt, logit_alone=kt["logit"], logit=kt["logit_with_attention"])
     dom = max(("lstm_gates", "logit"), key=lambda k: kt[k])
     sustained = (ms_dev / args.steps) > 5.0  # a step of many back-to-back launches: the sustained peak applies
     peak_tf = pk.get("bf16_tflops_sustained", pk["bf16_tflops"]) if sustained else pk["bf16_tflops"]
@@ -468,7 +465,7 @@ def _main(args):
     traffic_all = json.load(open(TRAFFIC_FILE)) if os.path.isfile(TRAFFIC_FILE) else {}
     tkey = "%s/%s/beam%d/rows%d" % (args.workload, args.precision, beam, rows)
     tr = traffic_all.get(tkey, {})
-    roofline = {"bound": "tensor", "kernel": "gemm_tc%s_kernel<%s%s>" % ("" if hoisted else "2", dom, " + attention warps" if fused and dom == "logit" else ""),
+    roofline = {"bound": "tensor", "kernel": "gemm_tc%s_kernel<%s>" % ("" if hoisted else "2", dom),
                 "achieved": ach,
                 "peak": peak_tf, "unit": "TFLOP/s", "frac": ach / peak_tf, "traffic": tr.get(dom),
                 "peak_source": pk_kind + (", sustained" if sustained else ", burst"), "rows": rows,
@@ -492,9 +489,7 @@ def _main(args):
                              "summed_window_bytes": summed, "summed_window_gbs": summed / att_s / 1e9,
                              "traffic": tr.get("attention"), "l2_bytes": tr.get("attention_l2"),
                              "bytes_per_element": el, "ms_per_launch": kt["attention"],
-                             "note": ("stand-alone kernel timing; inside the decode the attention of step t+1 runs on extra warps of "
-                                      "the logit GEMM of step t (step_kernel_ms.logit = that fused launch, logit_alone = the GEMM by itself)")
-                                     if fused else "stand-alone kernel, one launch per decode step"}
+                             "kernel": "attention_f16_kernel" if el == 2 else "attention_v2_kernel"}
 
     line = {"metric": METRIC, "value": total_events * args.steps / (ms_dev * 1e-3), "unit": UNIT, "n_gpus": world,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_dev / args.steps,

@@ -218,6 +218,11 @@ class CaptionGenerator(nn.Module):
         self._invalidate()
         return out
 
+    def refresh(self):
+        """Re-pack the weights on the next call.  Needed only after edits torch cannot see: writes through
+        `param.data` (they bypass the tensor version counters the engine watches)."""
+        self._invalidate()
+
     def set_precision(self, precision):
         self.precision = precision
         self._invalidate()

@@ -72,7 +72,7 @@ int echr_attention_step_f16(const float* q, const void* proj16, const void* clip
   AttF16Params P;
   P.q = q; P.proj = (const bf16*)proj16; P.clip = (const bf16*)clip16; P.alpha = alpha;
   P.row_start = row_start; P.row_len = row_len; P.rows = (int)rows;
-  P.out = (bf16*)out16; P.ld_out = ld_out; P.out_f32 = out_f32; P.row_counter = nullptr;
+  P.out = (bf16*)out16; P.ld_out = ld_out; P.out_f32 = out_f32;
   ECHR_CUDA(launch_attention_f16(P, (cudaStream_t)stream));
   return ECHR_OK;
 }

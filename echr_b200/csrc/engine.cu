@@ -142,11 +142,6 @@ static bool hoist_context(int rows) {
   if (forced >= 0) return forced != 0;
   return rows < gemm2_min_rows();
 }
-// Greedy decode with the attention of step t+1 on extra warps of the persistent logit GEMM of step t
-// (single-plane precision, throughput regime).
-static bool fused_attention(const echr_batch* b, int rows) {
-  return b->model->cfg.a_terms == 1 && use_gemm2(rows, b->model->V1, 128);
-}
 static int m_tiles_of(int rows) { return (rows + GEMM_BLOCK_M - 1) / GEMM_BLOCK_M; }
 // logit GEMM as 128 x 256 tiles shared by CTA pairs (23 x 2 CTAs per 128 rows at the ECHR vocabulary)
 static bool logit_split(const echr_model* m, int rows) {
@@ -180,7 +175,6 @@ int run_gemm(const GemmSpec* specs, int groups, int a_terms, int w_terms, int bl
     if (gx > grid_x) grid_x = gx;
   }
   const bool two = !any_split && use_gemm2(max_m, min_n, block_n);
-  if (two && groups == 1 && specs[0].att != nullptr) P.att = *specs[0].att;
   for (int g = 0; g < groups; ++g) {
     const char* err = fill_problem(P.prob[g], specs[g], a_terms, w_terms, two ? GEMM2_BLOCK_N : block_n);
     if (err) return set_error(ECHR_ERR_CUDA, "%s: %s", what, err);
@@ -382,7 +376,7 @@ static void batch_layout(echr_batch* b, Arena& a) {
     b->proj_f32 = a.take<float>((size_t)c.max_clips * HID);
     b->proj_h = nullptr;
   }
-  b->att_counter = a.take<int32_t>(S + 1);
+
   b->feat_pl = a.planes(ap, c.max_events, FEAT_PAD);
   b->x_pl = a.planes(ap, c.max_events, HID);
   b->qky = a.take<float>((size_t)c.max_events * 3 * HID);
@@ -827,7 +821,6 @@ static int enqueue_init(echr_batch* b, int beam, cudaStream_t st) {
     for (int p = 0; p < b->act[i].planes; ++p)
       ECHR_CUDA(cudaMemsetAsync(b->act[i].plane(p), 0, sizeof(bf16) * (size_t)rows * ACT_LD, st));
   ECHR_CUDA(cudaMemsetAsync(b->cstate[0], 0, sizeof(float) * (size_t)3 * rows * HID, st));
-  ECHR_CUDA(cudaMemsetAsync(b->att_counter, 0, sizeof(int32_t) * (size_t)(b->model->cfg.seq_length + 1), st));
   ECHR_CUDA(launch_decode_init(b, beam, st));
   // Hoist the constant-context terms of streams 0 and 2 out of the time loop: per-row gate bias
   //   row_bias0 = W_ih0[:, event] . event_ctx + (b_ih0 + b_hh0),  row_bias2 = W_ih2[:, video] . lda + (b_ih2 + b_hh2)
@@ -858,7 +851,7 @@ enum { PART_H2ATT = 1, PART_ATT = 2, PART_GATES = 4, PART_LOGIT = 8, PART_ALL = 
 
 // Attention of decode step t over the 16-bit tables (single-plane precision): reads the query the h2att GEMM of
 // step t wrote, writes the ATT block of activation buffer t & 1.
-static AttF16Params attention_params(const echr_batch* b, int rows, int t, int32_t* counter) {
+static AttF16Params attention_params(const echr_batch* b, int rows, int t) {
   AttF16Params ap;
   ap.q = b->q_att;
   ap.proj = b->proj_h;
@@ -870,15 +863,13 @@ static AttF16Params attention_params(const echr_batch* b, int rows, int t, int32
   ap.out = b->act[t & 1].plane(0) + ACT_ATT;
   ap.ld_out = ACT_LD;
   ap.out_f32 = nullptr;
-  ap.row_counter = counter;
   return ap;
 }
 
 // use_keys (greedy decode): the logit epilogue keeps a packed running arg-max per row (argmax_key[t & 1]) and the
 // gate GEMM of step t + 1 takes its input token from it, so the token chain does not pass through finalize.
-// att_next: the logit launch also runs the attention of step t + 1 on its extra warps (persistent kernel only).
 static int enqueue_step(echr_batch* b, int rows, int t, int topk, float* logits_out, long long ld_logits,
-                        cudaStream_t st, int parts = PART_ALL, bool use_keys = false, bool att_next = false) {
+                        cudaStream_t st, int parts = PART_ALL, bool use_keys = false) {
   const echr_model* m = b->model;
   const int at = m->cfg.a_terms, wt = m->cfg.w_terms;
   const int p = t & 1, n = p ^ 1;
@@ -902,7 +893,7 @@ static int enqueue_step(echr_batch* b, int rows, int t, int topk, float* logits_
   if (parts & PART_ATT) {
     PdlScope pdl(PDL_ATT);
     if (att16) {
-      const AttF16Params ap = attention_params(b, rows, t, nullptr);
+      const AttF16Params ap = attention_params(b, rows, t);
       ECHR_CUDA(launch_attention_f16(ap, st, trace_ptr(b), trace_next(b, 1)));
     } else {
       ECHR_CUDA(launch_attention(b->q_att, (const void*)b->proj_f32, (const void*)b->c3d, ECHR_VIDEO_DIM, 0, m->alpha,
@@ -950,11 +941,6 @@ static int enqueue_step(echr_batch* b, int rows, int t, int topk, float* logits_
     const bool sp = logit_split(m, rows);
     if (sp) s.ksplit = 2;
     if (use_keys) s.argmax_key = b->argmax_key[t & 1];
-    AttF16Params ap;
-    if (att_next) {
-      ap = attention_params(b, rows, t + 1, b->att_counter + t + 1);
-      s.att = &ap;
-    }
     PdlScope pdl(PDL_LOGIT);
     ECHR_TRY(run_gemm(&s, 1, at, wt, sp ? 256 : 128, EPI_LOGITS, topk, st, "logit", b, 3));
   }
@@ -992,25 +978,6 @@ static int enqueue_decode(echr_batch* b, int beam, int mode, cudaStream_t st, cu
     // finalize (log-sum-exp, outputs, `unfinished`) runs beside the next gate GEMM.
     const bool keys = true;
     ECHR_TRY(enqueue_step(b, rows, 0, topk, nullptr, 0, st, PART_H2ATT | PART_ATT));
-    if (fused_attention(b, rows)) {
-      // Throughput regime, 16-bit tables: one stream,
-      //   gates(t) -> h2att(t+1) -> [logits(t) || attention(t+1)] in ONE persistent kernel -> gates(t+1),
-      // finalize(t) beside gates(t+1) / h2att(t+2) on the side stream (it must precede logits(t+1), which reuses
-      // the partial records and accumulates into the arg-max keys finalize(t) clears).
-      for (int t = 0; t < S; ++t) {
-        const bool last = t + 1 == S;
-        ECHR_TRY(enqueue_step(b, rows, t, topk, nullptr, 0, st, PART_GATES, true));
-        if (!last) ECHR_TRY(enqueue_step(b, rows, t + 1, topk, nullptr, 0, st, PART_H2ATT));
-        if (t > 0) ECHR_CUDA(cudaStreamWaitEvent(st, b->cap_events[2], 0));  // finalize(t-1) done
-        ECHR_TRY(enqueue_step(b, rows, t, topk, nullptr, 0, st, PART_LOGIT, true, !last));
-        ECHR_CUDA(cudaEventRecord(b->cap_events[0], st));
-        ECHR_CUDA(cudaStreamWaitEvent(side, b->cap_events[0], 0));
-        ECHR_CUDA(launch_finalize_greedy(b, t, b->tokens_dev, b->logp_dev, side, true));
-        ECHR_CUDA(cudaEventRecord(b->cap_events[2], side));
-      }
-      ECHR_CUDA(cudaStreamWaitEvent(st, b->cap_events[2], 0));
-      return ECHR_OK;
-    }
     cudaStream_t tok_st = crit_main ? side : st;  // token chain
     cudaStream_t att_st = crit_main ? st : side;  // recurrent attention chain
     for (int t = 0; t < S; ++t) {
@@ -1247,19 +1214,12 @@ extern "C" int echr_time_step_kernels(echr_batch_t* b, int beam, int iters, floa
   if (rc == ECHR_OK && cudaStreamSynchronize(st) != cudaSuccess) rc = set_error(ECHR_ERR_CUDA, "echr_time_step_kernels: sync failed");
   const bool saved_regime = pdl_regime();
   pdl_regime() = false;  // plain launches: a launch must not overlap the tail of its identical predecessor
-  host_ms[5] = 0.f;
-  const bool fused = beam == 1 && fused_attention(b, rows);
-  for (int k = 0; k < 6 && rc == ECHR_OK; ++k) {
-    if (k == 5 && !fused) break;
+  for (int k = 0; k < 5 && rc == ECHR_OK; ++k) {
     cudaGraph_t graph = nullptr;
     cudaGraphExec_t exec = nullptr;
     if (cudaStreamBeginCapture(b->cap_stream, cudaStreamCaptureModeRelaxed) != cudaSuccess) { rc = set_error(ECHR_ERR_CUDA, "echr_time_step_kernels: capture failed"); break; }
     for (int i = 0; i < iters && rc == ECHR_OK; ++i) {
-      if (k == 5) {  // logits(1) with the attention of step 2 on the extra warps (its row counter re-armed per launch)
-        if (cudaMemsetAsync(b->att_counter + 2, 0, sizeof(int32_t), b->cap_stream) != cudaSuccess) rc = set_error(ECHR_ERR_CUDA, "memset failed");
-        if (rc == ECHR_OK) rc = enqueue_step(b, rows, 1, 1, nullptr, 0, b->cap_stream, PART_LOGIT, false, true);
-      }
-      else if (k < 4) rc = enqueue_step(b, rows, 1, beam > 1 ? 4 : 1, nullptr, 0, b->cap_stream, parts[k]);
+      if (k < 4) rc = enqueue_step(b, rows, 1, beam > 1 ? 4 : 1, nullptr, 0, b->cap_stream, parts[k]);
       else if (beam > 1) { if (launch_finalize_beam(b, beam, 1, b->tokens_dev, b->logp_dev, b->score_dev, b->cap_stream) != cudaSuccess) rc = set_error(ECHR_ERR_CUDA, "finalize_beam launch failed"); }
       else { if (launch_finalize_greedy(b, 1, b->tokens_dev, b->logp_dev, b->cap_stream) != cudaSuccess) rc = set_error(ECHR_ERR_CUDA, "finalize_greedy launch failed"); }
     }

@@ -92,7 +92,6 @@ struct echr_batch {
   echr::PlaneMat clip_pl;   // [clips, 512]   c3d planes (A of ctx2att; plane 0 doubles as bf16 clip)
   float* proj_f32;          // [clips, 512]   e^{2 (ctx2att(c3d)+b)} fp32      (two-plane precisions)
   echr::bf16* proj_h;       // [clips, 512]   ctx2att(c3d)+b as fp16           (single-plane precision, a_terms == 1)
-  int32_t* att_counter;     // [seq_length + 1] row counters of the attention warps inside the logit GEMM
   echr::PlaneMat feat_pl;   // [events, 1024] (mean c3d | tap[ind])
   echr::PlaneMat x_pl;      // [events, 512]  event_emb output
   float* qky;               // [events, 1536]
@@ -232,7 +231,6 @@ struct GemmSpec {
   int ksplit = 1;  // 2: cluster split-K (run_gemm then launches the SPLIT == 2 kernel for the whole group)
   const unsigned long long* row_key = nullptr;  // token from the packed arg-max keys instead of row_tok
   unsigned long long* argmax_key = nullptr;     // logits: running arg-max keys
-  const AttF16Params* att = nullptr;            // logits (persistent kernel): attention rows for its extra warps
   // logits
   float* partial = nullptr;
   float* logits_out = nullptr;

@@ -129,14 +129,6 @@ template <int A, int W, int EPI, int TOPK>
 static cudaError_t launch_two(const GemmParams& P, int groups, int total_tiles, int num_sms, cudaStream_t stream) {
   using Cfg = Gemm2Cfg<A, W>;
   const int grid = total_tiles < num_sms ? total_tiles : num_sms;
-  if constexpr (EPI == EPI_LOGITS && A == 1 && W == 1) {
-    if (P.att.rows > 0) {  // vocabulary projection + the next step's attention on four extra warps
-      auto kern = gemm_tc2_kernel<A, W, EPI, TOPK, true>;
-      static int attr[MAX_DEVICES] = {};
-      if (cudaError_t e = set_max_dynamic_smem(kern, Cfg::SMEM_BYTES_ATT, attr); e != cudaSuccess) return e;
-      return launch_pdl(kern, dim3(grid), dim3(GEMM_THREADS + 128), Cfg::SMEM_BYTES_ATT, stream, P, groups, total_tiles);
-    }
-  }
   auto kern = gemm_tc2_kernel<A, W, EPI, TOPK>;
   static int attr[MAX_DEVICES] = {};  // per instantiation and device
   if (cudaError_t e = set_max_dynamic_smem(kern, Cfg::SMEM_BYTES, attr); e != cudaSuccess) return e;

@@ -102,7 +102,6 @@ struct GemmParams {
                  // prologue overlap this kernel's epilogue) instead of right after this kernel's prologue
   unsigned long long* trace_detail;  // optional [slot][4]: sum over CTAs of (first stage landed, accumulator
                                      // ready, CTA end) - CTA start in ns, and the CTA count
-  AttF16Params att;  // persistent kernel with ATT = true: the attention rows its four extra warps walk
 };
 
 template <int TOPK>

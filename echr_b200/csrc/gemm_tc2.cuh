@@ -11,11 +11,6 @@
 //     loop of tile i+1 (tmem_full / tmem_empty mbarriers), the TMA ring never drains between tiles.
 // Warp roles: 0 TMA producer, 1 MMA issuer, 2 TMEM allocator, 4..11 epilogue (two warps per TMEM lane
 // quarter; a thread owns one output row x 128 columns).
-//   * ATT = true (vocabulary projection of a greedy decode step): four more warps (12..15) run the late-fusion
-//     attention of the NEXT step (attention_f16.cuh) over rows handed out by an atomic counter, each with a
-//     private bulk-copy ring in the shared memory the GEMM stages leave free.  The attention is bound by
-//     HBM/L2 bytes and the MUFU pipe, the projection by the tensor pipe: inside one kernel they overlap, which
-//     two persistent kernels (one CTA per SM each) cannot do.
 #pragma once
 #include "gemm_tc.cuh"
 
@@ -29,11 +24,8 @@ struct Gemm2Cfg {
   static constexpr int W_PLANE_BYTES = GEMM2_BLOCK_N * GEMM_BLOCK_K * 2;  // 32 KB
   static constexpr int STAGE_BYTES = A_TERMS * A_PLANE_BYTES + W_TERMS * W_PLANE_BYTES;
   static constexpr int STAGES = (200 * 1024) / STAGE_BYTES;  // (1,1): 4, (2,1): 3, (2,2): 2
-  // stages | barriers (256 B) | bias tiles 2 x 256 floats | ATT: 4 warp rings + their barriers
+  // stages | barriers (256 B) | bias tiles 2 x 256 floats
   static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 /*align slack*/ + 256 + 2048;
-  static constexpr int ATT_WARPS = 4;
-  static constexpr int SMEM_BYTES_ATT = SMEM_BYTES + ATT_WARPS * ATT_WARP_SMEM + 128;
-  static_assert(SMEM_BYTES_ATT <= 227 * 1024 || STAGES < 4, "attention rings do not fit next to the GEMM stages");
 };
 
 struct Gemm2Tile {
@@ -60,11 +52,10 @@ __device__ __forceinline__ void named_bar_sync(int id, int threads) {
   asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(threads) : "memory");
 }
 
-template <int A_TERMS, int W_TERMS, int EPI, int TOPK, bool ATT = false>
-__global__ void __launch_bounds__(ATT ? GEMM_THREADS + 128 : GEMM_THREADS, 1)
+template <int A_TERMS, int W_TERMS, int EPI, int TOPK>
+__global__ void __launch_bounds__(GEMM_THREADS, 1)
 gemm_tc2_kernel(const __grid_constant__ GemmParams P, int groups, int total_tiles) {
   using Cfg = Gemm2Cfg<A_TERMS, W_TERMS>;
-  static_assert(!ATT || EPI == EPI_LOGITS, "the attention warps ride on the vocabulary projection");
   constexpr int BN = GEMM2_BLOCK_N;
   trace_begin(P.trace, P.trace_slot);
 
@@ -80,8 +71,6 @@ gemm_tc2_kernel(const __grid_constant__ GemmParams P, int groups, int total_tile
   uint8_t* bar_generic = smem_raw + (bar_base - smem_u32(smem_raw));
   volatile uint32_t* tmem_ptr_generic = reinterpret_cast<volatile uint32_t*>(bar_generic + 160);
   float* sbias = reinterpret_cast<float*>(bar_generic + 256);  // [2][BN]
-  const uint32_t att_ring = bar_base + 256u + 2048u;                 // ATT: [4 warps][ATT_SLOTS][2 KB]
-  const uint32_t att_bars = att_ring + Cfg::ATT_WARPS * ATT_WARP_SMEM;  // ATT: [4 warps][ATT_SLOTS] mbarriers
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -101,8 +90,6 @@ gemm_tc2_kernel(const __grid_constant__ GemmParams P, int groups, int total_tile
       mbar_init(tmem_full_bar(b), 1);
       mbar_init(tmem_empty_bar(b), GEMM_EPI_WARPS);
     }
-    if (ATT)
-      for (int i = 0; i < Cfg::ATT_WARPS * ATT_SLOTS; ++i) mbar_init(att_bars + 8u * i, 1);
     fence_mbar_init();
   }
   if (warp == 2) tmem_alloc<512>(tmem_ptr_smem);
@@ -110,6 +97,11 @@ gemm_tc2_kernel(const __grid_constant__ GemmParams P, int groups, int total_tile
   __syncthreads();
   tc_fence_after_sync();
   const uint32_t tmem_base = *tmem_ptr_generic;
+  // Everything above touched only constants.  When the launch is a programmatic dependent of its stream
+  // predecessor (util.cuh: launch_pdl) it may have started early: nothing the predecessor writes (activation
+  // rows, cell state, attention queries, arg-max keys) is read before this point.  No explicit trigger: the
+  // next kernel is released when this one exits.
+  pdl_wait();
 
   if (warp == 0) {
     // ===================== TMA producer =====================
@@ -183,7 +175,7 @@ gemm_tc2_kernel(const __grid_constant__ GemmParams P, int groups, int total_tile
         umma_commit(tmem_full_bar(buf));
       }
     }
-  } else if (warp >= 4 && warp < 4 + GEMM_EPI_WARPS) {
+  } else if (warp >= 4) {
     // ===================== epilogue =====================
     constexpr int HALF = BN / 2;  // 128 columns per thread
     constexpr int NCH = HALF / 32;
@@ -433,15 +425,6 @@ gemm_tc2_kernel(const __grid_constant__ GemmParams P, int groups, int total_tile
       if (lane == 0) mbar_arrive(tmem_empty_bar(buf));
     }
   }
-  if constexpr (ATT) {
-    if (warp >= 12) {
-      // ===================== attention of the next decode step (see attention_f16.cuh) =====================
-      const int aw = warp - 12;
-      att_f16_warp(P.att, att_ring + aw * ATT_WARP_SMEM, att_bars + 8u * aw * ATT_SLOTS,
-                   static_cast<int>(blockIdx.x) * Cfg::ATT_WARPS + aw, static_cast<int>(gridDim.x) * Cfg::ATT_WARPS, 0u);
-    }
-  }
-
   tc_fence_before_sync();
   __syncthreads();
   if (warp == 2) {

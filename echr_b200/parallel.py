@@ -28,6 +28,41 @@ def shard_videos(event_counts, rank, world):
     return bounds[rank], bounds[rank + 1]
 
 
+class JobPlan(object):
+    """How a captioning job over `event_counts` (events per video, the whole job, known to every rank) is laid
+    out on `world` ranks: rank r takes the contiguous block of videos `bounds[r]` (balanced by events) and feeds
+    it in `n_batches` batches of at most `batch_videos` videos.  Every rank uses the SAME number of batches (a
+    rank with fewer videos has smaller, possibly empty, ones), because each batch ends in one collective: the
+    all_gather of that batch's token ids.  `batches[r][b]` = (first video, end video); `events[r][b]` = decode
+    rows of that batch, i.e. the row counts `gather_tokens` needs without a count exchange.  Everything here is
+    a pure function of (event_counts, world, batch_videos): no communication."""
+
+    def __init__(self, event_counts, world, batch_videos):
+        self.world = max(1, int(world))
+        self.bounds = [shard_videos(event_counts, r, self.world) for r in range(self.world)]
+        self.n_batches = max(1, max(-(-(hi - lo) // int(batch_videos)) for lo, hi in self.bounds))
+        self.batches, self.events = [], []
+        for lo, hi in self.bounds:
+            cuts = [lo + ((hi - lo) * b + self.n_batches // 2) // self.n_batches for b in range(self.n_batches + 1)]
+            cuts[0], cuts[-1] = lo, hi
+            self.batches.append([(cuts[b], cuts[b + 1]) for b in range(self.n_batches)])
+            self.events.append([int(sum(event_counts[a:b])) for a, b in self.batches[-1]])
+
+    def counts(self, b):
+        """Rows every rank contributes to the gather of batch slot b."""
+        return [self.events[r][b] for r in range(self.world)]
+
+    def assemble(self, gathered):
+        """gathered[b] = the token matrix gather_tokens returned for batch slot b (rows in rank order) -> the
+        job's [n_events, S] matrix in video order."""
+        parts = []
+        for r in range(self.world):
+            for b in range(self.n_batches):
+                row0 = sum(self.events[q][b] for q in range(r))
+                parts.append(gathered[b][row0:row0 + self.events[r][b]])
+        return torch.cat(parts, 0)
+
+
 def exchange_counts(n_local, device, group=None):
     """Row count of every rank (one small all_gather + host read; do it once per batch shape)."""
     if not dist.is_available() or not dist.is_initialized() or dist.get_world_size(group) == 1:

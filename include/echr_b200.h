@@ -154,9 +154,9 @@ ECHR_API int echr_attention_step(const float* q_exp, const void* proj_exp, const
 
 /* The same step over 16-bit tables (what the single-plane precision runs; csrc/attention_f16.cuh):
  * q [rows,512] fp32 = h2att(h1) + b (NOT exponentiated); proj16 [n_clips,512] fp16 = ctx2att(c3d) + b;
- * clip16 [n_clips,512] fp16, columns 500..511 zero.  One warp per row: the window is streamed through a
- * per-warp shared-memory ring by cp.async.bulk (1 KB projected row + 1 KB clip row per clip) and consumed in one
- * pass with an online softmax.  out_f32 [rows,500] (may be NULL); out16 [rows, ld_out] fp16 (may be NULL). */
+ * clip16 [n_clips,512] fp16, columns 500..511 zero.  One CTA per row: the window is streamed in chunks of 8 clips
+ * through a shared-memory ring by cp.async.bulk, one warp per clip of a chunk, online softmax per warp, merged at
+ * the end.  out_f32 [rows,500] (may be NULL); out16 [rows, ld_out] fp16 (may be NULL). */
 ECHR_API int echr_attention_step_f16(const float* q, const void* proj16, const void* clip16, const float* alpha,
                             const int32_t* row_start, const int32_t* row_len, int64_t rows, float* out_f32,
                             void* out16, int64_t ld_out, void* stream);
@@ -318,9 +318,7 @@ ECHR_API int echr_rerank_nms(const double* t1, const double* t2, const double* p
                     int topn, void* workspace, int32_t* out_pick, int32_t* out_count, int cap, void* stream);
 
 /* Measurement aid for bench.py's roofline: average duration in ms of each kernel of one decode step
- * (host_ms[6] = h2att GEMM, attention (stand-alone kernel), LSTM gate GEMM, logit GEMM, finalize, and the
- * logit GEMM with the next step's attention on its extra warps — 0 when the batch does not decode with that
- * kernel), from CUDA events on `stream` around a captured graph of `iters` back-to-back plain launches of that
+ * (host_ms[5] = h2att GEMM, attention, LSTM gate GEMM, logit GEMM, finalize), from CUDA events on `stream` around a captured graph of `iters` back-to-back plain launches of that
  * kernel (no host launch gaps, as in the decode graph), with the schedule the batch's decode uses (see
  * echr_batch_set_concurrency).  Needs a decoded batch; synchronises. */
 ECHR_API int echr_time_step_kernels(echr_batch_t* batch, int beam, int iters, float* host_ms, void* stream);

@@ -371,9 +371,14 @@ def test_inplace_weight_edit_and_pipeline_after_repack():
     assert len(seq) == 3
     old = m.engine
     with torch.no_grad():
-        m.lm_model.logit.bias.data[0] = 50.0  # EOS wins at every step from now on
+        m.lm_model.logit.bias[0] = 50.0  # EOS wins at every step from now on (an optimizer step looks the same to torch)
     assert m(vt[0], vt[1], vt[2], [], vt[3], vt[4], mode="eval") == ([], [])
     assert m.engine is not old
+    m.lm_model.logit.bias.data[0] = 0.0  # through .data: invisible to the version counters -> refresh()
+    m.refresh()
+    assert len(m(vt[0], vt[1], vt[2], [], vt[3], vt[4], mode="eval")[0]) == 3
+    with torch.no_grad():
+        m.lm_model.logit.bias[0] = 50.0
     pipe = CaptionPipeline(m.engine, depth=2)
     lay, c3d, tap, lda = helpers.batch_of([v], DEV)
     pipe.submit(lay, c3d, tap, lda).wait()

@@ -32,5 +32,19 @@ ncu)
   CMD="python bench.py --videos 1024 --steps 1 --warmup 1 --no-cpu-baseline --no-second-beam"
   $CMD > $O/ncu_plain.json 2> $O/ncu_plain.err &&
   timeout 1200 ncu --metrics gpu__time_duration.sum --clock-control none -c 6000 --csv --log-file $O/launches.csv $CMD > $O/ncu_launches.log 2>&1 ;;
+ncufull)
+  # ncu --set full of every kernel family (tools/profile_targets.py); the raw page is exported on the box, the
+  # report itself only comes back when it fits the 64 MiB return channel
+  CMD="python tools/profile_targets.py"
+  $CMD > $O/targets_plain.log 2>&1 &&
+  timeout 2400 ncu --set full --clock-control none -k regex:"gemm_tc|attention|pair_mlp|relation_attn|finalize|select_|rerank|sst_|event_feats|decode_init|split_planes|gather_tap" \
+      -c 500 -o $O/targets -f $CMD > $O/targets_ncu.log 2>&1
+  ncu -i $O/targets.ncu-rep --page raw --csv > $O/targets_raw.csv 2> $O/targets_export.log
+  if [ $(stat -c %s $O/targets.ncu-rep 2>/dev/null || echo 0) -gt 40000000 ]; then rm -f $O/targets.ncu-rep; fi ;;
+sanitize)
+  # compute-sanitizer over smoke(): encode, greedy decode, SST encoder, selection, caption of selected proposals
+  timeout 1500 compute-sanitizer --tool memcheck --error-exitcode 7 python -c "import __graft_entry__ as g; g.smoke()" > $O/sanitizer_memcheck.log 2>&1; echo "exit=$?" >> $O/sanitizer_memcheck.log
+  timeout 1500 compute-sanitizer --tool racecheck --error-exitcode 7 python -c "import __graft_entry__ as g; g.smoke()" > $O/sanitizer_racecheck.log 2>&1; echo "exit=$?" >> $O/sanitizer_racecheck.log
+  timeout 1500 compute-sanitizer --tool memcheck --error-exitcode 7 python tools/profile_targets.py > $O/sanitizer_memcheck_targets.log 2>&1; echo "exit=$?" >> $O/sanitizer_memcheck_targets.log ;;
 esac; done
 echo done
