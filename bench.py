@@ -259,7 +259,7 @@ def _main(args):
     import torch.distributed as dist
     from echr_b200.caption_generator import CaptionGenerator
     from echr_b200.engine import CaptionPipeline
-    from echr_b200.parallel import gather_tokens, shard_videos
+    from echr_b200.parallel import JobPlan, gather_tokens
 
     torch.set_grad_enabled(False)
     torch.cuda.set_device(local)
@@ -279,16 +279,8 @@ def _main(args):
 
     # ---- the job: every rank derives the same plan from the videos' event counts
     w, events, counts_all, config = workload_plan(args)
-    bounds = [shard_videos(counts_all, r, world) for r in range(world)]
-    n_batches = max(1, max(-(-(hi - lo) // args.batch_videos) for lo, hi in bounds))
-
-    def batches_of(r):  # video index ranges of rank r's batches (every rank has n_batches of them, some may be empty)
-        lo, hi = bounds[r]
-        cuts = np.linspace(lo, hi, n_batches + 1).round().astype(int)
-        return [(int(cuts[b]), int(cuts[b + 1])) for b in range(n_batches)]
-
-    plan = [batches_of(r) for r in range(world)]
-    ev_counts = [[sum(counts_all[a:b]) for a, b in plan[r]] for r in range(world)]  # [rank][batch]
+    job = JobPlan(counts_all, world, args.batch_videos)  # the same plan on every rank, no communication
+    n_batches, plan, ev_counts = job.n_batches, job.batches, job.events
     feats16 = args.precision != "fp32"
 
     def build(a, b):

@@ -559,130 +559,153 @@ cudaError_t launch_attention(const float* q, const void* proj, const void* clip,
 
 // ---------------------------------------------------------------------------------------------
 // 16-bit, bulk-copy staged attention: design notes in attention_f16.cuh.
-__global__ void __launch_bounds__(ATR_WARPS * 32, 4)
+__global__ void __launch_bounds__(ATR_WARPS * 32, 2)
 attention_f16_kernel(const __grid_constant__ AttF16Params P, unsigned long long* trace, int trace_slot) {
   extern __shared__ __align__(128) uint8_t atr_smem[];
   trace_begin(trace, trace_slot);
   constexpr float C2 = 2.0f * 1.4426950408889634f;  // 2 log2(e)
   constexpr float L2E = 1.4426950408889634f;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int r = blockIdx.x;
   const uint32_t ring = smem_u32(atr_smem);
-  float* s_alpha = reinterpret_cast<float*>(atr_smem + ATR_STAGES * ATR_STAGE_BYTES);
-  uint8_t* tail = atr_smem + ATR_STAGES * ATR_STAGE_BYTES + 2048;
-  const uint32_t bars = ring + ATR_STAGES * ATR_STAGE_BYTES + 2048;  // full[s] +8s, empty[s] +16+8s
-  float* s_m = reinterpret_cast<float*>(tail + 32);                   // [8] per-warp running max
-  float* s_l = reinterpret_cast<float*>(tail + 64);                   // [8] per-warp running sum
+  float* red = reinterpret_cast<float*>(atr_smem + ATR_STAGES * ATR_STAGE_BYTES);             // [8][512]
+  float* s_alpha = red + ATR_WARPS * 512;
+  int2* s_rows = reinterpret_cast<int2*>(s_alpha + 512);                                      // (first clip, clips)
+  uint8_t* tail = reinterpret_cast<uint8_t*>(s_rows + ATR_MAX_ROWS_PER_CTA);
+  const uint32_t bars = smem_u32(tail);  // full[s] +8s, empty[s] +32+8s
+  float* s_m = reinterpret_cast<float*>(tail + 64);   // [8] per-warp running max
+  float* s_l = reinterpret_cast<float*>(tail + 96);   // [8] per-warp running sum
   if (threadIdx.x == 0) {
     for (int s = 0; s < ATR_STAGES; ++s) {
       mbar_init(bars + 8u * s, 1);
-      mbar_init(bars + 16u + 8u * s, ATR_WARPS);
+      mbar_init(bars + 32u + 8u * s, ATR_WARPS);
     }
     fence_mbar_init();
   }
   for (int i = threadIdx.x; i < 512; i += ATR_WARPS * 32) s_alpha[i] = -2.f * __ldg(P.alpha + i);
+  // this CTA's rows: blockIdx.x, + gridDim.x, ...  (the launcher sizes the grid so that they fit the table)
+  const int n_rows = (P.rows - static_cast<int>(blockIdx.x) + static_cast<int>(gridDim.x) - 1) / static_cast<int>(gridDim.x);
+  for (int k = threadIdx.x; k < n_rows; k += ATR_WARPS * 32) {
+    const int r = blockIdx.x + k * gridDim.x;
+    s_rows[k] = make_int2(__ldg(P.row_start + r), __ldg(P.row_len + r));
+  }
   __syncthreads();
   pdl_trigger();
-  pdl_wait();  // q comes from the h2att GEMM launched just before; nothing but weights is read earlier
-  const int s0 = __ldg(P.row_start + r);
-  const int L = __ldg(P.row_len + r);
-  const int n_chunks = (L + ATR_WARPS - 1) / ATR_WARPS;
-  auto issue = [&](int c) {  // thread 0: bring chunk c into its stage
-    const int st = c % ATR_STAGES;
-    const int n = min(ATR_WARPS, L - c * ATR_WARPS);
-    const uint32_t dst = ring + st * ATR_STAGE_BYTES;
-    const uint32_t bar = bars + 8u * st;
-    mbar_arrive_expect_tx(bar, static_cast<uint32_t>(n) * 2048u);
-    const long long row = static_cast<long long>(s0 + c * ATR_WARPS) * 512;
-    bulk_load_1d(dst, P.proj + row, static_cast<uint32_t>(n) * 1024u, bar);
-    bulk_load_1d(dst + ATR_WARPS * 1024, P.clip + row, static_cast<uint32_t>(n) * 1024u, bar);
+  pdl_wait();  // q comes from the h2att GEMM launched just before; nothing but weights and windows is read earlier
+  // ---- producer state (thread 0): next chunk to issue = chunk pc of row pk; `issued` counts chunks of all rows
+  int pk = 0, pc = 0;
+  unsigned issued = 0;
+  while (pk < n_rows && s_rows[pk].y <= 0) ++pk;  // (empty windows have nothing to load)
+  auto top_up = [&](unsigned upto) {  // thread 0: issue chunks until `upto` have been issued or the rows run out
+    while (issued < upto && pk < n_rows) {
+      const int2 rw = s_rows[pk];
+      const unsigned st = issued % ATR_STAGES;
+      if (issued >= ATR_STAGES) {
+        mbar_wait(bars + 32u + 8u * st, ((issued / ATR_STAGES) - 1) & 1u);  // all eight warps are done with the stage
+        fence_proxy_async_smem();  // their generic reads before the async-proxy write
+      }
+      const int n = min(ATR_WARPS, rw.y - pc * ATR_WARPS);
+      const uint32_t dst = ring + st * ATR_STAGE_BYTES;
+      const uint32_t bar = bars + 8u * st;
+      mbar_arrive_expect_tx(bar, static_cast<uint32_t>(n) * 2048u);
+      const long long row = static_cast<long long>(rw.x + pc * ATR_WARPS) * 512;
+      bulk_load_1d(dst, P.proj + row, static_cast<uint32_t>(n) * 1024u, bar);
+      bulk_load_1d(dst + ATR_WARPS * 1024, P.clip + row, static_cast<uint32_t>(n) * 1024u, bar);
+      ++issued;
+      if ((++pc) * ATR_WARPS >= rw.y) {
+        pc = 0;
+        do { ++pk; } while (pk < n_rows && s_rows[pk].y <= 0);
+      }
+    }
   };
-  if (threadIdx.x == 0 && n_chunks > 0) issue(0);
-  // lane's hidden units / clip columns: [8 lane + 256 m, +8), m = 0, 1 (16-byte chunks lane and lane + 32 of a row)
-  float qc[16];
-#pragma unroll
-  for (int m = 0; m < 2; ++m) {
-    const float* qp = P.q + static_cast<long long>(r) * 512 + 256 * m + 8 * lane;
-    const float4 q0 = __ldg(reinterpret_cast<const float4*>(qp));
-    const float4 q1 = __ldg(reinterpret_cast<const float4*>(qp + 4));
-    qc[8 * m + 0] = q0.x * C2; qc[8 * m + 1] = q0.y * C2; qc[8 * m + 2] = q0.z * C2; qc[8 * m + 3] = q0.w * C2;
-    qc[8 * m + 4] = q1.x * C2; qc[8 * m + 5] = q1.y * C2; qc[8 * m + 6] = q1.z * C2; qc[8 * m + 7] = q1.w * C2;
-  }
   auto unpack8 = [](const uint4& u, float* f) {
     const float2 a = f16x2_value(u.x), b = f16x2_value(u.y), c = f16x2_value(u.z), d = f16x2_value(u.w);
     f[0] = a.x; f[1] = a.y; f[2] = b.x; f[3] = b.y; f[4] = c.x; f[5] = c.y; f[6] = d.x; f[7] = d.y;
   };
-  float mx = -INFINITY, sum = 0.f;
-  float acc[16];
+  // lane's hidden units / clip columns: [8 lane + 256 m, +8), m = 0, 1 (16-byte chunks lane and lane + 32 of a row)
+  auto load_q = [&](int k, float* qc) {
+    const int r = blockIdx.x + k * gridDim.x;
 #pragma unroll
-  for (int i = 0; i < 16; ++i) acc[i] = 0.f;
-  for (int c = 0; c < n_chunks; ++c) {
-    const int st = c % ATR_STAGES;
-    if (threadIdx.x == 0 && c + 1 < n_chunks) {
-      // the stage of chunk c+1 held chunk c-1: wait until all eight warps are done with it
-      if (c + 1 >= ATR_STAGES) mbar_wait(bars + 16u + 8u * ((c + 1) % ATR_STAGES), (((c + 1) / ATR_STAGES) - 1) & 1u);
-      fence_proxy_async_smem();  // their generic reads before the async-proxy write
-      issue(c + 1);
+    for (int m = 0; m < 2; ++m) {
+      const float* qp = P.q + static_cast<long long>(r) * 512 + 256 * m + 8 * lane;
+      const float4 q0 = __ldg(reinterpret_cast<const float4*>(qp));
+      const float4 q1 = __ldg(reinterpret_cast<const float4*>(qp + 4));
+      qc[8 * m + 0] = q0.x * C2; qc[8 * m + 1] = q0.y * C2; qc[8 * m + 2] = q0.z * C2; qc[8 * m + 3] = q0.w * C2;
+      qc[8 * m + 4] = q1.x * C2; qc[8 * m + 5] = q1.y * C2; qc[8 * m + 6] = q1.z * C2; qc[8 * m + 7] = q1.w * C2;
     }
-    mbar_wait(bars + 8u * st, (c / ATR_STAGES) & 1u);
-    const int l = c * ATR_WARPS + warp;
-    if (l < L) {
-      const uint32_t sp = ring + st * ATR_STAGE_BYTES + warp * 1024;
-      float s = 0.f;
-      float cf[16];
+  };
+  unsigned g = 0;  // chunks consumed so far (all rows)
+  if (threadIdx.x == 0) top_up(ATR_STAGES);
+  float qc[16];
+  if (n_rows > 0) load_q(0, qc);
+  for (int k = 0; k < n_rows; ++k) {
+    const int r = blockIdx.x + k * gridDim.x;
+    const int L = s_rows[k].y;
+    const int n_chunks = L > 0 ? (L + ATR_WARPS - 1) / ATR_WARPS : 0;
+    float mx = -INFINITY, sum = 0.f;
+    float acc[16];
 #pragma unroll
-      for (int m = 0; m < 2; ++m) {
-        uint4 pu, cu;
-        asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(pu.x), "=r"(pu.y), "=r"(pu.z), "=r"(pu.w)
-                     : "r"(sp + 16u * (lane + 32 * m)));
-        asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(cu.x), "=r"(cu.y), "=r"(cu.z), "=r"(cu.w)
-                     : "r"(sp + ATR_WARPS * 1024u + 16u * (lane + 32 * m)));
-        float pf[8];
-        unpack8(pu, pf);
-        unpack8(cu, cf + 8 * m);
-        const float4 a0 = *reinterpret_cast<const float4*>(s_alpha + 256 * m + 8 * lane);
-        const float4 a1 = *reinterpret_cast<const float4*>(s_alpha + 256 * m + 8 * lane + 4);
-        const float av[8] = {a0.x, a0.y, a0.z, a0.w, a1.x, a1.y, a1.z, a1.w};
+    for (int i = 0; i < 16; ++i) acc[i] = 0.f;
+    for (int c = 0; c < n_chunks; ++c, ++g) {
+      if (threadIdx.x == 0) top_up(g + ATR_STAGES);  // keeps ATR_STAGES - 1 chunks in flight behind this one
+      const unsigned st = g % ATR_STAGES;
+      mbar_wait(bars + 8u * st, (g / ATR_STAGES) & 1u);
+      const int l = c * ATR_WARPS + warp;
+      if (l < L) {
+        const uint32_t sp = ring + st * ATR_STAGE_BYTES + warp * 1024;
+        float s = 0.f;
+        float cf[16];
 #pragma unroll
-        for (int i = 0; i < 8; ++i) {
-          const float e = exp2f(fmaf(pf[i], C2, qc[8 * m + i]));
-          float rc;
-          asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(rc) : "f"(e + 1.0f));
-          s = fmaf(av[i], rc, s);
+        for (int m = 0; m < 2; ++m) {
+          uint4 pu, cu;
+          asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(pu.x), "=r"(pu.y), "=r"(pu.z), "=r"(pu.w)
+                       : "r"(sp + 16u * (lane + 32 * m)));
+          asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(cu.x), "=r"(cu.y), "=r"(cu.z), "=r"(cu.w)
+                       : "r"(sp + ATR_WARPS * 1024u + 16u * (lane + 32 * m)));
+          float pf[8];
+          unpack8(pu, pf);
+          unpack8(cu, cf + 8 * m);
+          const float4 a0 = *reinterpret_cast<const float4*>(s_alpha + 256 * m + 8 * lane);
+          const float4 a1 = *reinterpret_cast<const float4*>(s_alpha + 256 * m + 8 * lane + 4);
+          const float av[8] = {a0.x, a0.y, a0.z, a0.w, a1.x, a1.y, a1.z, a1.w};
+#pragma unroll
+          for (int i = 0; i < 8; ++i) {
+            const float e = exp2f(fmaf(pf[i], C2, qc[8 * m + i]));
+            float rc;
+            asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(rc) : "f"(e + 1.0f));
+            s = fmaf(av[i], rc, s);
+          }
         }
+        s = warp_sum(s);
+        const float m_new = fmaxf(mx, s);
+        const float corr = exp2f((mx - m_new) * L2E);  // exp2(-inf) = 0 on the warp's first clip
+        const float p = exp2f((s - m_new) * L2E);
+        sum = fmaf(sum, corr, p);
+#pragma unroll
+        for (int i = 0; i < 16; ++i) acc[i] = fmaf(acc[i], corr, p * cf[i]);
+        mx = m_new;
       }
-      s = warp_sum(s);
-      const float m_new = fmaxf(mx, s);
-      const float corr = exp2f((mx - m_new) * L2E);  // exp2(-inf) = 0 on the warp's first clip
-      const float p = exp2f((s - m_new) * L2E);
-      sum = fmaf(sum, corr, p);
-#pragma unroll
-      for (int i = 0; i < 16; ++i) acc[i] = fmaf(acc[i], corr, p * cf[i]);
-      mx = m_new;
+      __syncwarp();
+      if (lane == 0) mbar_arrive(bars + 32u + 8u * st);
     }
-    __syncwarp();
-    if (lane == 0) mbar_arrive(bars + 16u + 8u * st);
-  }
-  // ---- merge the eight warps' (max, sum, weighted sum): att = sum_w e^{m_w - M} acc_w / sum_w e^{m_w - M} sum_w
-  if (lane == 0) { s_m[warp] = mx; s_l[warp] = sum; }
-  __syncthreads();  // also: every warp is past its last slot, no copy is in flight -> the ring is free
-  float M = -INFINITY;
+    if (k + 1 < n_rows) load_q(k + 1, qc);  // in flight during the merge
+    // ---- merge the eight warps' (max, sum, weighted sum): att = sum_w e^{m_w - M} acc_w / sum_w e^{m_w - M} sum_w
+    if (lane == 0) { s_m[warp] = mx; s_l[warp] = sum; }
+    __syncthreads();
+    float M = -INFINITY;
 #pragma unroll
-  for (int w = 0; w < ATR_WARPS; ++w) M = fmaxf(M, s_m[w]);
-  float total = 0.f;
+    for (int w = 0; w < ATR_WARPS; ++w) M = fmaxf(M, s_m[w]);
+    float total = 0.f;
 #pragma unroll
-  for (int w = 0; w < ATR_WARPS; ++w) total += s_m[w] == -INFINITY ? 0.f : s_l[w] * exp2f((s_m[w] - M) * L2E);
-  const float my = mx == -INFINITY ? 0.f : exp2f((mx - M) * L2E);
-  float* red = reinterpret_cast<float*>(atr_smem);  // [8][512] over the first ring stage
+    for (int w = 0; w < ATR_WARPS; ++w) total += s_m[w] == -INFINITY ? 0.f : s_l[w] * exp2f((s_m[w] - M) * L2E);
+    const float my = mx == -INFINITY ? 0.f : exp2f((mx - M) * L2E);
 #pragma unroll
-  for (int m = 0; m < 2; ++m) {
-    float* d = red + warp * 512 + 256 * m + 8 * lane;
-    *reinterpret_cast<float4*>(d) = make_float4(acc[8 * m] * my, acc[8 * m + 1] * my, acc[8 * m + 2] * my, acc[8 * m + 3] * my);
-    *reinterpret_cast<float4*>(d + 4) = make_float4(acc[8 * m + 4] * my, acc[8 * m + 5] * my, acc[8 * m + 6] * my, acc[8 * m + 7] * my);
-  }
-  __syncthreads();
-  const float inv = total > 0.f ? 1.0f / total : 0.f;  // (an empty window gives a zero feature)
-  {
+    for (int m = 0; m < 2; ++m) {
+      float* d = red + warp * 512 + 256 * m + 8 * lane;
+      *reinterpret_cast<float4*>(d) = make_float4(acc[8 * m] * my, acc[8 * m + 1] * my, acc[8 * m + 2] * my, acc[8 * m + 3] * my);
+      *reinterpret_cast<float4*>(d + 4) = make_float4(acc[8 * m + 4] * my, acc[8 * m + 5] * my, acc[8 * m + 6] * my, acc[8 * m + 7] * my);
+    }
+    __syncthreads();
+    const float inv = total > 0.f ? 1.0f / total : 0.f;  // (an empty window gives a zero feature)
     const int c0 = 2 * threadIdx.x;  // 256 threads x 2 columns
     float v0 = 0.f, v1 = 0.f;
 #pragma unroll
@@ -705,13 +728,16 @@ attention_f16_kernel(const __grid_constant__ AttF16Params P, unsigned long long*
   trace_end(trace, trace_slot);
 }
 
-
 cudaError_t launch_attention_f16(const AttF16Params& P, cudaStream_t st, unsigned long long* trace, int trace_slot) {
   if (P.rows == 0) return cudaSuccess;
   static int attr[MAX_DEVICES] = {};
   cudaError_t e = set_max_dynamic_smem(attention_f16_kernel, ATR_SMEM, attr);
   if (e != cudaSuccess) return e;
-  e = launch_pdl(attention_f16_kernel, dim3((unsigned)P.rows), dim3(ATR_WARPS * 32), (size_t)ATR_SMEM, st, P, trace, trace_slot);
+  int grid = num_sms() * 2;  // two persistent CTAs per SM
+  if (grid > P.rows) grid = P.rows;
+  const int need = (P.rows + ATR_MAX_ROWS_PER_CTA - 1) / ATR_MAX_ROWS_PER_CTA;  // rows per CTA must fit its table
+  if (grid < need) grid = need;
+  e = launch_pdl(attention_f16_kernel, dim3((unsigned)grid), dim3(ATR_WARPS * 32), (size_t)ATR_SMEM, st, P, trace, trace_slot);
   count_launch();
   return e;
 }

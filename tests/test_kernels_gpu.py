@@ -94,8 +94,9 @@ def test_attention_step_f16_matches_oracle(rows_mult):
     rl = torch.tensor(lens, dtype=torch.int32, device=DEV)
     out = torch.full((n, 500), float("nan"), device=DEV)
     out16 = torch.full((n, 512), float("nan"), dtype=torch.float16, device=DEV)
-    _lib.check(lib.echr_attention_step_f16(q.to(DEV).data_ptr(), proj.to(DEV).contiguous().data_ptr(), clip_d.data_ptr(),
-                                           alpha.to(DEV).data_ptr(), rs.data_ptr(), rl.data_ptr(), n, out.data_ptr(),
+    q_d, proj_d, alpha_d = q.to(DEV), proj.to(DEV).contiguous(), alpha.to(DEV)  # (kept alive until the kernel ran)
+    _lib.check(lib.echr_attention_step_f16(q_d.data_ptr(), proj_d.data_ptr(), clip_d.data_ptr(),
+                                           alpha_d.data_ptr(), rs.data_ptr(), rl.data_ptr(), n, out.data_ptr(),
                                            out16.data_ptr(), 512, torch.cuda.current_stream().cuda_stream), "attention_f16")
     torch.cuda.synchronize()
     err = (out.cpu() - want).abs().max().item()
