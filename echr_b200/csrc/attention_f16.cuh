@@ -1,39 +1,41 @@
 // Late-fusion attention step (models/OldModel_NEW.py:376-401, ctx2att hoisted) over 16-bit tables, staged through
 // shared memory by the bulk-copy engine — the form BASELINE.json's north_star (2) asks for.
 //
-//   score_l = alpha . tanh(P_l + q)        P = ctx2att(c3d) + b   fp16 [clips,512], written once per batch
+//   score_l = alpha . tanh(P_l + q)        P = ctx2att(c3d) + b
 //   w       = softmax_l(score)             over the event's clip window [s0, s0 + L)
 //   att     = sum_l w_l * clip_l           clip fp16 [clips,512] (500 used): plane 0 of the ctx2att operand
 //
-// Persistent CTAs (8 warps, two per SM) walk the decode rows round robin.  A row's window is contiguous in HBM, so
-// it is streamed in chunks of 8 clips by cp.async.bulk — two copies per chunk (8 projected rows, 8 clip rows:
-// 16 KB) on one mbarrier — through a four-stage ring that thread 0 keeps full ACROSS row boundaries (the first
-// chunks of the next row are in flight while the current row is being finished): ~96 KB of HBM/L2 reads in flight
-// per SM without a register held for them, which is what a 6.5 TB/s stream at ~2 us loaded latency needs.  Warp w
-// consumes clip w of every chunk, so a row's clips are processed eight at a time.  Each warp folds its clips into
-// an online softmax (running max / sum / weighted feature sum, rescaled when the max moves); the eight partial
-// states are merged through shared memory at the end of the row.  Every byte of a window is read exactly once: no
-// score buffer, no second pass over the clip rows.  Algorithmic bytes per event-step: 2048 L + 2048 (q in) + 1000
-// (att out).
+// Tables (written once per batch by the encoder).  tanh(x) = 1 - 2 / (e^{2x} + 1) and e^{2(P+q)} = e^{2P} e^{2q}, so
+// with the projection stored in the exponential domain a score element costs ONE special-function operation (the
+// reciprocal) instead of two.  e^{2P} does not fit fp16 as it is, so every clip row is stored relative to its own
+// maximum: E_lk = e^{2 (P_lk - m_l)} in (0, 1] as fp16 [clips,512] plus S_l = e^{2 m_l} as fp32 [clips];
+// e^{2(P+q)} = (E_lk S_l) e^{2 q_k}, the last factor coming from the h2att GEMM epilogue.  The fp16 rounding of E
+// (2^-12 relative) moves tanh by at most 1.3e-4; entries more than 8 below the row maximum flush towards 0, where
+// tanh = -1 to within e^{2(P+q)} itself.  No clamp is needed on the product: inf gives rcp -> 0, tanh = 1.
 //
-// tanh(P + q) = 1 - 2 / (e^{2(P+q)} + 1): one FFMA + EX2 + FADD + RCP + FFMA per element, all in fp32; the
-// constant sum_k alpha_k and the alpha_net bias drop out of the softmax.  No clamp is needed: e^{2x} -> inf gives
-// rcp -> 0, tanh = 1.  The only 16-bit roundings are those of the stored tables (fp16: 2^-12 relative).
+// Schedule.  One CTA (8 warps, three CTAs per SM) per decode row; warp w owns clips w, w+8, ... of the window and
+// folds them into an online softmax (running max / sum / weighted feature sum, rescaled when the max moves); the
+// eight partial states are merged through shared memory at the end.  Every warp keeps a PRIVATE two-slot ring in
+// shared memory that its lane 0 fills with cp.async.bulk (one slot = the 1 KB table row + the 1 KB clip row of one
+// clip, two copies on one mbarrier) two clips ahead: 24 warps x 4 KB = 96 KB of HBM/L2 reads in flight per SM
+// with no register held for them and no block-wide barrier inside a row.  Every byte of a window is read exactly
+// once: no score buffer (so no bound on the window length), no second pass over the clip rows.
+// Algorithmic bytes per event-step: 2052 L + 2048 (e^{2q} in) + 1000 (att out).
 #pragma once
 #include "ptx.cuh"
 
 namespace echr {
 
-constexpr int ATR_WARPS = 8;                             // = clips per chunk
-constexpr int ATR_STAGES = 4;
-constexpr int ATR_STAGE_BYTES = ATR_WARPS * 2048;        // 8 projected rows | 8 clip rows
-constexpr int ATR_MAX_ROWS_PER_CTA = 256;                // row table in shared memory
-// ring | merge buffer [8][512] f32 | alpha | row table (first clip, length) | barriers + merge scalars
-constexpr int ATR_SMEM = ATR_STAGES * ATR_STAGE_BYTES + ATR_WARPS * 2048 + 2048 + ATR_MAX_ROWS_PER_CTA * 8 + 128;
+constexpr int ATR_WARPS = 8;
+constexpr int ATR_SLOTS = 2;                              // clips in flight per warp
+constexpr int ATR_SLOT_BYTES = 2048;                      // table row | clip row
+constexpr int ATR_RING_BYTES = ATR_WARPS * ATR_SLOTS * ATR_SLOT_BYTES;   // 32 KB (re-used as the merge buffer)
+constexpr int ATR_SMEM = ATR_RING_BYTES + 256;            // + mbarriers and merge scalars
 
 struct AttF16Params {
-  const float* q;                // [rows, 512] fp32: h2att(h1) + b  (NOT exponentiated)
-  const __nv_bfloat16* proj;     // [clips, 512] fp16 bits
+  const float* q_exp;            // [rows, 512] fp32: e^{2 (h2att(h1) + b)}
+  const __nv_bfloat16* proj;     // [clips, 512] fp16 bits: E = e^{2 (P - rowmax P)}
+  const float* proj_scale;       // [clips] fp32: S = e^{2 rowmax P}
   const __nv_bfloat16* clip;     // [clips, 512] fp16 bits, columns 500..511 zero
   const float* alpha;            // [512]
   const int32_t* row_start;      // [rows] first clip of the row's window

@@ -369,13 +369,9 @@ static void batch_layout(echr_batch* b, Arena& a) {
   b->vid_first = ints + 7 * c.max_events;
   b->vid_n = b->vid_first + c.max_videos;
   b->clip_pl = a.planes(ap, c.max_clips, CLIP_PAD);
-  if (ap == 1) {
-    b->proj_h = a.take<bf16>((size_t)c.max_clips * HID);
-    b->proj_f32 = nullptr;
-  } else {
-    b->proj_f32 = a.take<float>((size_t)c.max_clips * HID);
-    b->proj_h = nullptr;
-  }
+  b->proj_f32 = a.take<float>((size_t)c.max_clips * HID);
+  b->proj_h = ap == 1 ? a.take<bf16>((size_t)c.max_clips * HID) : nullptr;
+  b->proj_scale = ap == 1 ? a.take<float>((size_t)c.max_clips) : nullptr;
 
   b->feat_pl = a.planes(ap, c.max_events, FEAT_PAD);
   b->x_pl = a.planes(ap, c.max_events, HID);
@@ -663,10 +659,12 @@ static int encode_clips(echr_batch_t* b, cudaStream_t st) {
   GemmSpec s;
   s.A = &b->clip_pl; s.M = b->n_clips; s.W = &m->w_ctx2att; s.N = HID; s.K = CLIP_PAD;
   s.bias = m->b_ctx2att;
-  // single-plane precision: the projection itself as one fp16 plane (attention_f16.cuh); otherwise the fp32 table e^{2P}
-  if (at == 1) { s.out_hi = b->proj_h; s.ld_bf = HID; }
-  else { s.act = ACT_EXP2X; s.out_f32 = b->proj_f32; s.ld_f32 = HID; }
-  return run_gemm(&s, 1, at, wt, 128, EPI_STORE, 1, st, "ctx2att");
+  // two-plane precisions: the fp32 table e^{2P}; single-plane: P, then the row-scaled fp16 table (attention_f16.cuh)
+  s.out_f32 = b->proj_f32; s.ld_f32 = HID;
+  if (at != 1) s.act = ACT_EXP2X;
+  ECHR_TRY(run_gemm(&s, 1, at, wt, 128, EPI_STORE, 1, st, "ctx2att"));
+  if (at == 1) ECHR_CUDA(launch_attention_table(b->proj_f32, b->n_clips, b->proj_h, b->proj_scale, st));
+  return ECHR_OK;
 }
 
 // event relation encoder from the event feature planes (MA:35-177): embedding -> query | key |
@@ -853,8 +851,9 @@ enum { PART_H2ATT = 1, PART_ATT = 2, PART_GATES = 4, PART_LOGIT = 8, PART_ALL = 
 // step t wrote, writes the ATT block of activation buffer t & 1.
 static AttF16Params attention_params(const echr_batch* b, int rows, int t) {
   AttF16Params ap;
-  ap.q = b->q_att;
+  ap.q_exp = b->q_att;
   ap.proj = b->proj_h;
+  ap.proj_scale = b->proj_scale;
   ap.clip = b->clip_pl.plane(0);
   ap.alpha = b->model->alpha;
   ap.row_start = b->row_start;
@@ -879,8 +878,7 @@ static int enqueue_step(echr_batch* b, int rows, int t, int topk, float* logits_
   if (parts & PART_H2ATT) {
     GemmSpec s;
     s.A = &cur; s.a_col0 = ACT_H + HID; s.M = rows; s.W = &m->w_h2att; s.N = HID; s.K = HID;
-    s.bias = m->b_h2att; s.out_f32 = b->q_att; s.ld_f32 = HID;
-    if (!att16) s.act = ACT_EXP2X;  // fp32 tables: e^{2q}
+    s.bias = m->b_h2att; s.act = ACT_EXP2X; s.out_f32 = b->q_att; s.ld_f32 = HID;  // e^{2q}
     PdlScope pdl(PDL_H2ATT);
     // latency regime: narrow tiles spread the [rows,512] x [512,512] product over 4x the SMs (a CTA's
     // main loop is bound by its own L2->SM operand stream, dominated by the 2-plane activation tile)

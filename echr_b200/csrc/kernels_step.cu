@@ -559,171 +559,146 @@ cudaError_t launch_attention(const float* q, const void* proj, const void* clip,
 
 // ---------------------------------------------------------------------------------------------
 // 16-bit, bulk-copy staged attention: design notes in attention_f16.cuh.
-__global__ void __launch_bounds__(ATR_WARPS * 32, 2)
+__global__ void __launch_bounds__(ATR_WARPS * 32, 3)
 attention_f16_kernel(const __grid_constant__ AttF16Params P, unsigned long long* trace, int trace_slot) {
   extern __shared__ __align__(128) uint8_t atr_smem[];
   trace_begin(trace, trace_slot);
-  constexpr float C2 = 2.0f * 1.4426950408889634f;  // 2 log2(e)
   constexpr float L2E = 1.4426950408889634f;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const uint32_t ring = smem_u32(atr_smem);
-  float* red = reinterpret_cast<float*>(atr_smem + ATR_STAGES * ATR_STAGE_BYTES);             // [8][512]
-  float* s_alpha = red + ATR_WARPS * 512;
-  int2* s_rows = reinterpret_cast<int2*>(s_alpha + 512);                                      // (first clip, clips)
-  uint8_t* tail = reinterpret_cast<uint8_t*>(s_rows + ATR_MAX_ROWS_PER_CTA);
-  const uint32_t bars = smem_u32(tail);  // full[s] +8s, empty[s] +32+8s
-  float* s_m = reinterpret_cast<float*>(tail + 64);   // [8] per-warp running max
-  float* s_l = reinterpret_cast<float*>(tail + 96);   // [8] per-warp running sum
-  if (threadIdx.x == 0) {
-    for (int s = 0; s < ATR_STAGES; ++s) {
-      mbar_init(bars + 8u * s, 1);
-      mbar_init(bars + 32u + 8u * s, ATR_WARPS);
-    }
+  const int r = blockIdx.x;
+  const uint32_t ring = smem_u32(atr_smem) + warp * (ATR_SLOTS * ATR_SLOT_BYTES);   // this warp's slots
+  uint8_t* tail = atr_smem + ATR_RING_BYTES;
+  const uint32_t bars = smem_u32(tail) + warp * (ATR_SLOTS * 8);                     // this warp's mbarriers
+  float* s_m = reinterpret_cast<float*>(tail + 128);   // [8] per-warp running max
+  float* s_l = reinterpret_cast<float*>(tail + 160);   // [8] per-warp running sum
+  if (lane == 0) {
+    for (int i = 0; i < ATR_SLOTS; ++i) mbar_init(bars + 8u * i, 1);
     fence_mbar_init();
   }
-  for (int i = threadIdx.x; i < 512; i += ATR_WARPS * 32) s_alpha[i] = -2.f * __ldg(P.alpha + i);
-  // this CTA's rows: blockIdx.x, + gridDim.x, ...  (the launcher sizes the grid so that they fit the table)
-  const int n_rows = (P.rows - static_cast<int>(blockIdx.x) + static_cast<int>(gridDim.x) - 1) / static_cast<int>(gridDim.x);
-  for (int k = threadIdx.x; k < n_rows; k += ATR_WARPS * 32) {
-    const int r = blockIdx.x + k * gridDim.x;
-    s_rows[k] = make_int2(__ldg(P.row_start + r), __ldg(P.row_len + r));
+  __syncwarp();
+  // lane's hidden units / clip columns: [8 lane + 256 m, +8), m = 0, 1 (16-byte chunks lane and lane + 32 of a row)
+  float av[16];
+#pragma unroll
+  for (int m = 0; m < 2; ++m) {
+    const float4 a0 = __ldg(reinterpret_cast<const float4*>(P.alpha + 256 * m + 8 * lane));
+    const float4 a1 = __ldg(reinterpret_cast<const float4*>(P.alpha + 256 * m + 8 * lane + 4));
+    av[8 * m + 0] = -2.f * a0.x; av[8 * m + 1] = -2.f * a0.y; av[8 * m + 2] = -2.f * a0.z; av[8 * m + 3] = -2.f * a0.w;
+    av[8 * m + 4] = -2.f * a1.x; av[8 * m + 5] = -2.f * a1.y; av[8 * m + 6] = -2.f * a1.z; av[8 * m + 7] = -2.f * a1.w;
+  }
+  pdl_trigger();
+  pdl_wait();  // e^{2q} comes from the h2att GEMM launched just before; nothing but weights is read earlier
+  const int s0 = __ldg(P.row_start + r);
+  const int L = __ldg(P.row_len + r);
+  const int n_mine = L > warp ? (L - warp + ATR_WARPS - 1) / ATR_WARPS : 0;  // clips warp, warp + 8, ...
+  auto issue = [&](int i) {  // lane 0: bring this warp's i-th clip into slot i % ATR_SLOTS
+    const uint32_t dst = ring + (i % ATR_SLOTS) * ATR_SLOT_BYTES;
+    const uint32_t bar = bars + 8u * (i % ATR_SLOTS);
+    mbar_arrive_expect_tx(bar, ATR_SLOT_BYTES);
+    const long long row = static_cast<long long>(s0 + warp + i * ATR_WARPS) * 512;
+    bulk_load_1d(dst, P.proj + row, 1024, bar);
+    bulk_load_1d(dst + 1024, P.clip + row, 1024, bar);
+  };
+  if (lane == 0)
+    for (int i = 0; i < ATR_SLOTS && i < n_mine; ++i) issue(i);
+  float qe[16];
+#pragma unroll
+  for (int m = 0; m < 2; ++m) {
+    const float* qp = P.q_exp + static_cast<long long>(r) * 512 + 256 * m + 8 * lane;
+    const float4 q0 = __ldg(reinterpret_cast<const float4*>(qp));
+    const float4 q1 = __ldg(reinterpret_cast<const float4*>(qp + 4));
+    qe[8 * m + 0] = q0.x; qe[8 * m + 1] = q0.y; qe[8 * m + 2] = q0.z; qe[8 * m + 3] = q0.w;
+    qe[8 * m + 4] = q1.x; qe[8 * m + 5] = q1.y; qe[8 * m + 6] = q1.z; qe[8 * m + 7] = q1.w;
+  }
+  float sc_next = n_mine > 0 ? __ldg(P.proj_scale + s0 + warp) : 0.f;
+  float mx = -INFINITY, sum = 0.f;
+  float acc[16];
+#pragma unroll
+  for (int i = 0; i < 16; ++i) acc[i] = 0.f;
+  for (int i = 0; i < n_mine; ++i) {
+    const float sc = sc_next;
+    if (i + 1 < n_mine) sc_next = __ldg(P.proj_scale + s0 + warp + (i + 1) * ATR_WARPS);
+    mbar_wait(bars + 8u * (i % ATR_SLOTS), (i / ATR_SLOTS) & 1u);
+    const uint32_t sp = ring + (i % ATR_SLOTS) * ATR_SLOT_BYTES;
+    uint4 pu[2], cu[2];
+#pragma unroll
+    for (int m = 0; m < 2; ++m) {
+      asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(pu[m].x), "=r"(pu[m].y), "=r"(pu[m].z), "=r"(pu[m].w)
+                   : "r"(sp + 16u * (lane + 32 * m)));
+      asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(cu[m].x), "=r"(cu[m].y), "=r"(cu[m].z), "=r"(cu[m].w)
+                   : "r"(sp + 1024u + 16u * (lane + 32 * m)));
+    }
+    __syncwarp();  // every lane holds its part of the slot in registers: refill it
+    if (lane == 0 && i + ATR_SLOTS < n_mine) {
+      fence_proxy_async_smem();  // the lanes' generic reads before the async-proxy write
+      issue(i + ATR_SLOTS);
+    }
+    float s = 0.f;
+#pragma unroll
+    for (int m = 0; m < 2; ++m) {
+      const uint32_t w4[4] = {pu[m].x, pu[m].y, pu[m].z, pu[m].w};
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const float2 e2 = f16x2_value(w4[j]);
+        float r0, r1;
+        asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r0) : "f"(fmaf(e2.x * sc, qe[8 * m + 2 * j], 1.0f)));
+        asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r1) : "f"(fmaf(e2.y * sc, qe[8 * m + 2 * j + 1], 1.0f)));
+        s = fmaf(av[8 * m + 2 * j], r0, s);
+        s = fmaf(av[8 * m + 2 * j + 1], r1, s);
+      }
+    }
+    s = warp_sum(s);
+    const float m_new = fmaxf(mx, s);
+    const float corr = exp2f((mx - m_new) * L2E);  // exp2(-inf) = 0 on the warp's first clip
+    const float p = exp2f((s - m_new) * L2E);
+    sum = fmaf(sum, corr, p);
+#pragma unroll
+    for (int m = 0; m < 2; ++m) {
+      const uint32_t w4[4] = {cu[m].x, cu[m].y, cu[m].z, cu[m].w};
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const float2 c2 = f16x2_value(w4[j]);
+        acc[8 * m + 2 * j] = fmaf(acc[8 * m + 2 * j], corr, p * c2.x);
+        acc[8 * m + 2 * j + 1] = fmaf(acc[8 * m + 2 * j + 1], corr, p * c2.y);
+      }
+    }
+    mx = m_new;
+  }
+  // ---- merge the eight warps' (max, sum, weighted sum): att = sum_w e^{m_w - M} acc_w / sum_w e^{m_w - M} sum_w
+  if (lane == 0) { s_m[warp] = mx; s_l[warp] = sum; }
+  __syncthreads();  // also: every warp is past its last slot and no copy is in flight -> the rings are free
+  float M = -INFINITY;
+#pragma unroll
+  for (int w = 0; w < ATR_WARPS; ++w) M = fmaxf(M, s_m[w]);
+  float total = 0.f;
+#pragma unroll
+  for (int w = 0; w < ATR_WARPS; ++w) total += s_m[w] == -INFINITY ? 0.f : s_l[w] * exp2f((s_m[w] - M) * L2E);
+  const float my = mx == -INFINITY ? 0.f : exp2f((mx - M) * L2E);
+  float* red = reinterpret_cast<float*>(atr_smem);  // [8][512] over the first 16 KB of the rings
+#pragma unroll
+  for (int m = 0; m < 2; ++m) {
+    float* d = red + warp * 512 + 256 * m + 8 * lane;
+    *reinterpret_cast<float4*>(d) = make_float4(acc[8 * m] * my, acc[8 * m + 1] * my, acc[8 * m + 2] * my, acc[8 * m + 3] * my);
+    *reinterpret_cast<float4*>(d + 4) = make_float4(acc[8 * m + 4] * my, acc[8 * m + 5] * my, acc[8 * m + 6] * my, acc[8 * m + 7] * my);
   }
   __syncthreads();
-  pdl_trigger();
-  pdl_wait();  // q comes from the h2att GEMM launched just before; nothing but weights and windows is read earlier
-  // ---- producer state (thread 0): next chunk to issue = chunk pc of row pk; `issued` counts chunks of all rows
-  int pk = 0, pc = 0;
-  unsigned issued = 0;
-  while (pk < n_rows && s_rows[pk].y <= 0) ++pk;  // (empty windows have nothing to load)
-  auto top_up = [&](unsigned upto) {  // thread 0: issue chunks until `upto` have been issued or the rows run out
-    while (issued < upto && pk < n_rows) {
-      const int2 rw = s_rows[pk];
-      const unsigned st = issued % ATR_STAGES;
-      if (issued >= ATR_STAGES) {
-        mbar_wait(bars + 32u + 8u * st, ((issued / ATR_STAGES) - 1) & 1u);  // all eight warps are done with the stage
-        fence_proxy_async_smem();  // their generic reads before the async-proxy write
-      }
-      const int n = min(ATR_WARPS, rw.y - pc * ATR_WARPS);
-      const uint32_t dst = ring + st * ATR_STAGE_BYTES;
-      const uint32_t bar = bars + 8u * st;
-      mbar_arrive_expect_tx(bar, static_cast<uint32_t>(n) * 2048u);
-      const long long row = static_cast<long long>(rw.x + pc * ATR_WARPS) * 512;
-      bulk_load_1d(dst, P.proj + row, static_cast<uint32_t>(n) * 1024u, bar);
-      bulk_load_1d(dst + ATR_WARPS * 1024, P.clip + row, static_cast<uint32_t>(n) * 1024u, bar);
-      ++issued;
-      if ((++pc) * ATR_WARPS >= rw.y) {
-        pc = 0;
-        do { ++pk; } while (pk < n_rows && s_rows[pk].y <= 0);
-      }
-    }
-  };
-  auto unpack8 = [](const uint4& u, float* f) {
-    const float2 a = f16x2_value(u.x), b = f16x2_value(u.y), c = f16x2_value(u.z), d = f16x2_value(u.w);
-    f[0] = a.x; f[1] = a.y; f[2] = b.x; f[3] = b.y; f[4] = c.x; f[5] = c.y; f[6] = d.x; f[7] = d.y;
-  };
-  // lane's hidden units / clip columns: [8 lane + 256 m, +8), m = 0, 1 (16-byte chunks lane and lane + 32 of a row)
-  auto load_q = [&](int k, float* qc) {
-    const int r = blockIdx.x + k * gridDim.x;
+  const float inv = total > 0.f ? 1.0f / total : 0.f;  // (an empty window gives a zero feature)
+  const int c0 = 2 * threadIdx.x;  // 256 threads x 2 columns
+  float v0 = 0.f, v1 = 0.f;
 #pragma unroll
-    for (int m = 0; m < 2; ++m) {
-      const float* qp = P.q + static_cast<long long>(r) * 512 + 256 * m + 8 * lane;
-      const float4 q0 = __ldg(reinterpret_cast<const float4*>(qp));
-      const float4 q1 = __ldg(reinterpret_cast<const float4*>(qp + 4));
-      qc[8 * m + 0] = q0.x * C2; qc[8 * m + 1] = q0.y * C2; qc[8 * m + 2] = q0.z * C2; qc[8 * m + 3] = q0.w * C2;
-      qc[8 * m + 4] = q1.x * C2; qc[8 * m + 5] = q1.y * C2; qc[8 * m + 6] = q1.z * C2; qc[8 * m + 7] = q1.w * C2;
-    }
-  };
-  unsigned g = 0;  // chunks consumed so far (all rows)
-  if (threadIdx.x == 0) top_up(ATR_STAGES);
-  float qc[16];
-  if (n_rows > 0) load_q(0, qc);
-  for (int k = 0; k < n_rows; ++k) {
-    const int r = blockIdx.x + k * gridDim.x;
-    const int L = s_rows[k].y;
-    const int n_chunks = L > 0 ? (L + ATR_WARPS - 1) / ATR_WARPS : 0;
-    float mx = -INFINITY, sum = 0.f;
-    float acc[16];
-#pragma unroll
-    for (int i = 0; i < 16; ++i) acc[i] = 0.f;
-    for (int c = 0; c < n_chunks; ++c, ++g) {
-      if (threadIdx.x == 0) top_up(g + ATR_STAGES);  // keeps ATR_STAGES - 1 chunks in flight behind this one
-      const unsigned st = g % ATR_STAGES;
-      mbar_wait(bars + 8u * st, (g / ATR_STAGES) & 1u);
-      const int l = c * ATR_WARPS + warp;
-      if (l < L) {
-        const uint32_t sp = ring + st * ATR_STAGE_BYTES + warp * 1024;
-        float s = 0.f;
-        float cf[16];
-#pragma unroll
-        for (int m = 0; m < 2; ++m) {
-          uint4 pu, cu;
-          asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(pu.x), "=r"(pu.y), "=r"(pu.z), "=r"(pu.w)
-                       : "r"(sp + 16u * (lane + 32 * m)));
-          asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(cu.x), "=r"(cu.y), "=r"(cu.z), "=r"(cu.w)
-                       : "r"(sp + ATR_WARPS * 1024u + 16u * (lane + 32 * m)));
-          float pf[8];
-          unpack8(pu, pf);
-          unpack8(cu, cf + 8 * m);
-          const float4 a0 = *reinterpret_cast<const float4*>(s_alpha + 256 * m + 8 * lane);
-          const float4 a1 = *reinterpret_cast<const float4*>(s_alpha + 256 * m + 8 * lane + 4);
-          const float av[8] = {a0.x, a0.y, a0.z, a0.w, a1.x, a1.y, a1.z, a1.w};
-#pragma unroll
-          for (int i = 0; i < 8; ++i) {
-            const float e = exp2f(fmaf(pf[i], C2, qc[8 * m + i]));
-            float rc;
-            asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(rc) : "f"(e + 1.0f));
-            s = fmaf(av[i], rc, s);
-          }
-        }
-        s = warp_sum(s);
-        const float m_new = fmaxf(mx, s);
-        const float corr = exp2f((mx - m_new) * L2E);  // exp2(-inf) = 0 on the warp's first clip
-        const float p = exp2f((s - m_new) * L2E);
-        sum = fmaf(sum, corr, p);
-#pragma unroll
-        for (int i = 0; i < 16; ++i) acc[i] = fmaf(acc[i], corr, p * cf[i]);
-        mx = m_new;
-      }
-      __syncwarp();
-      if (lane == 0) mbar_arrive(bars + 32u + 8u * st);
-    }
-    if (k + 1 < n_rows) load_q(k + 1, qc);  // in flight during the merge
-    // ---- merge the eight warps' (max, sum, weighted sum): att = sum_w e^{m_w - M} acc_w / sum_w e^{m_w - M} sum_w
-    if (lane == 0) { s_m[warp] = mx; s_l[warp] = sum; }
-    __syncthreads();
-    float M = -INFINITY;
-#pragma unroll
-    for (int w = 0; w < ATR_WARPS; ++w) M = fmaxf(M, s_m[w]);
-    float total = 0.f;
-#pragma unroll
-    for (int w = 0; w < ATR_WARPS; ++w) total += s_m[w] == -INFINITY ? 0.f : s_l[w] * exp2f((s_m[w] - M) * L2E);
-    const float my = mx == -INFINITY ? 0.f : exp2f((mx - M) * L2E);
-#pragma unroll
-    for (int m = 0; m < 2; ++m) {
-      float* d = red + warp * 512 + 256 * m + 8 * lane;
-      *reinterpret_cast<float4*>(d) = make_float4(acc[8 * m] * my, acc[8 * m + 1] * my, acc[8 * m + 2] * my, acc[8 * m + 3] * my);
-      *reinterpret_cast<float4*>(d + 4) = make_float4(acc[8 * m + 4] * my, acc[8 * m + 5] * my, acc[8 * m + 6] * my, acc[8 * m + 7] * my);
-    }
-    __syncthreads();
-    const float inv = total > 0.f ? 1.0f / total : 0.f;  // (an empty window gives a zero feature)
-    const int c0 = 2 * threadIdx.x;  // 256 threads x 2 columns
-    float v0 = 0.f, v1 = 0.f;
-#pragma unroll
-    for (int w = 0; w < ATR_WARPS; ++w) {
-      const float2 t = *reinterpret_cast<const float2*>(red + w * 512 + c0);
-      v0 += t.x;
-      v1 += t.y;
-    }
-    v0 *= inv;
-    v1 *= inv;
-    if (P.out != nullptr) {
-      __align__(4) __nv_bfloat16 h[2] = {f16_bits(v0), f16_bits(v1)};
-      *reinterpret_cast<uint32_t*>(P.out + static_cast<long long>(r) * P.ld_out + c0) = *reinterpret_cast<const uint32_t*>(h);
-    }
-    if (P.out_f32 != nullptr && c0 < 500) {
-      P.out_f32[static_cast<long long>(r) * 500 + c0] = v0;
-      P.out_f32[static_cast<long long>(r) * 500 + c0 + 1] = v1;
-    }
+  for (int w = 0; w < ATR_WARPS; ++w) {
+    const float2 t = *reinterpret_cast<const float2*>(red + w * 512 + c0);
+    v0 += t.x;
+    v1 += t.y;
+  }
+  v0 *= inv;
+  v1 *= inv;
+  if (P.out != nullptr) {
+    __align__(4) __nv_bfloat16 h[2] = {f16_bits(v0), f16_bits(v1)};
+    *reinterpret_cast<uint32_t*>(P.out + static_cast<long long>(r) * P.ld_out + c0) = *reinterpret_cast<const uint32_t*>(h);
+  }
+  if (P.out_f32 != nullptr && c0 < 500) {
+    P.out_f32[static_cast<long long>(r) * 500 + c0] = v0;
+    P.out_f32[static_cast<long long>(r) * 500 + c0 + 1] = v1;
   }
   trace_end(trace, trace_slot);
 }
@@ -733,13 +708,44 @@ cudaError_t launch_attention_f16(const AttF16Params& P, cudaStream_t st, unsigne
   static int attr[MAX_DEVICES] = {};
   cudaError_t e = set_max_dynamic_smem(attention_f16_kernel, ATR_SMEM, attr);
   if (e != cudaSuccess) return e;
-  int grid = num_sms() * 2;  // two persistent CTAs per SM
-  if (grid > P.rows) grid = P.rows;
-  const int need = (P.rows + ATR_MAX_ROWS_PER_CTA - 1) / ATR_MAX_ROWS_PER_CTA;  // rows per CTA must fit its table
-  if (grid < need) grid = need;
-  e = launch_pdl(attention_f16_kernel, dim3((unsigned)grid), dim3(ATR_WARPS * 32), (size_t)ATR_SMEM, st, P, trace, trace_slot);
+  e = launch_pdl(attention_f16_kernel, dim3((unsigned)P.rows), dim3(ATR_WARPS * 32), (size_t)ATR_SMEM, st, P, trace, trace_slot);
   count_launch();
   return e;
+}
+
+// Attention table of the single-plane precision (attention_f16.cuh): one warp per clip row,
+// P fp32 [clips,512] -> E = e^{2 (P - rowmax)} as fp16 and S = e^{2 rowmax} as fp32.
+__global__ void __launch_bounds__(256)
+attention_table_kernel(const float* __restrict__ proj, int clips, bf16* __restrict__ table, float* __restrict__ scale) {
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int l = blockIdx.x * 8 + warp;
+  if (l >= clips) return;
+  const float* row = proj + static_cast<long long>(l) * HID;
+  float v[16];
+#pragma unroll
+  for (int m = 0; m < 4; ++m) {
+    const float4 t = __ldg(reinterpret_cast<const float4*>(row + 128 * m + 4 * lane));
+    v[4 * m] = t.x; v[4 * m + 1] = t.y; v[4 * m + 2] = t.z; v[4 * m + 3] = t.w;
+  }
+  float mx = v[0];
+#pragma unroll
+  for (int i = 1; i < 16; ++i) mx = fmaxf(mx, v[i]);
+  mx = warp_max(mx);
+#pragma unroll
+  for (int m = 0; m < 4; ++m) {
+    __align__(8) bf16 h[4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) h[i] = f16_bits(__expf(2.0f * (v[4 * m + i] - mx)));
+    *reinterpret_cast<uint2*>(table + static_cast<long long>(l) * HID + 128 * m + 4 * lane) = *reinterpret_cast<const uint2*>(h);
+  }
+  if (lane == 0) scale[l] = __expf(2.0f * fminf(mx, 43.0f));  // (finite for any finite projection)
+}
+
+cudaError_t launch_attention_table(const float* proj, int clips, bf16* table, float* scale, cudaStream_t st) {
+  if (clips == 0) return cudaSuccess;
+  attention_table_kernel<<<(clips + 7) / 8, 256, 0, st>>>(proj, clips, table, scale);
+  count_launch();
+  return cudaGetLastError();
 }
 
 // ---------------------------------------------------------------------------------------------

@@ -153,13 +153,14 @@ ECHR_API int echr_attention_step(const float* q_exp, const void* proj_exp, const
                         void* out_lo, int64_t ld_bf, int max_len, void* stream);
 
 /* The same step over 16-bit tables (what the single-plane precision runs; csrc/attention_f16.cuh):
- * q [rows,512] fp32 = h2att(h1) + b (NOT exponentiated); proj16 [n_clips,512] fp16 = ctx2att(c3d) + b;
- * clip16 [n_clips,512] fp16, columns 500..511 zero.  One CTA per row: the window is streamed in chunks of 8 clips
- * through a shared-memory ring by cp.async.bulk, one warp per clip of a chunk, online softmax per warp, merged at
- * the end.  out_f32 [rows,500] (may be NULL); out16 [rows, ld_out] fp16 (may be NULL). */
-ECHR_API int echr_attention_step_f16(const float* q, const void* proj16, const void* clip16, const float* alpha,
-                            const int32_t* row_start, const int32_t* row_len, int64_t rows, float* out_f32,
-                            void* out16, int64_t ld_out, void* stream);
+ * q_exp [rows,512] fp32 = e^{2 (h2att(h1) + b)}; proj16 [n_clips,512] fp16 = e^{2 (P - rowmax P)} with
+ * P = ctx2att(c3d) + b, proj_scale [n_clips] fp32 = e^{2 rowmax P}; clip16 [n_clips,512] fp16, columns 500..511
+ * zero.  One CTA per row; every warp streams its clips through a private shared-memory ring filled by
+ * cp.async.bulk and folds them into an online softmax; any window length.
+ * out_f32 [rows,500] (may be NULL); out16 [rows, ld_out] fp16 (may be NULL). */
+ECHR_API int echr_attention_step_f16(const float* q_exp, const void* proj16, const float* proj_scale, const void* clip16,
+                            const float* alpha, const int32_t* row_start, const int32_t* row_len, int64_t rows,
+                            float* out_f32, void* out16, int64_t ld_out, void* stream);
 
 /* ---- model: packed weights --------------------------------------------------------------- */
 /* Packs the checkpoint into kernel layouts (bf16 planes, gate-interleaved LSTM rows, fused biases).

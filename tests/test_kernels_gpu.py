@@ -80,13 +80,18 @@ def test_attention_step_f16_matches_oracle(rows_mult):
     starts = [0, 299 - 1, 10, 200, 100, 150, 20, 0, 295] * rows_mult
     n = len(lens)
     h = torch.randn(n, 512, generator=g) * 0.3
-    proj = torch.nn.functional.linear(c3d, sd[a + "ctx2att.weight"], sd[a + "ctx2att.bias"]).half()
+    P = torch.nn.functional.linear(c3d, sd[a + "ctx2att.weight"], sd[a + "ctx2att.bias"])
     q = torch.nn.functional.linear(h, sd[a + "h2att.weight"], sd[a + "h2att.bias"])
     alpha = sd[a + "alpha_net.weight"].reshape(-1).contiguous()
-    # oracle on the rounded tables: scores from the fp16 projection, features from the fp16 clips
+    # the table format of csrc/attention_f16.cuh: E = e^{2 (P - rowmax)} as fp16, S = e^{2 rowmax} as fp32
+    pmax = P.max(1, keepdim=True)[0]
+    proj = torch.exp(2 * (P - pmax)).half()
+    scale = torch.exp(2 * pmax).reshape(-1).contiguous()
+    # oracle on the rounded tables: tanh(x) = 1 - 2 / (e^{2x} + 1) with e^{2(P+q)} = E S e^{2q}
     want = torch.zeros(n, 500)
     for i, (s, l) in enumerate(zip(starts, lens)):
-        sc = torch.tanh(proj[s:s + l].float() + q[i]) @ alpha
+        e2x = proj[s:s + l].double() * scale[s:s + l, None].double() * torch.exp(2 * q[i].double())
+        sc = ((1 - 2 / (e2x + 1)) @ alpha.double()).float()
         want[i] = torch.softmax(sc, 0) @ c3d[s:s + l]
     clip_d = torch.zeros(T, 512, dtype=torch.float16, device=DEV)
     clip_d[:, :500] = c3d.to(DEV).half()
@@ -94,8 +99,8 @@ def test_attention_step_f16_matches_oracle(rows_mult):
     rl = torch.tensor(lens, dtype=torch.int32, device=DEV)
     out = torch.full((n, 500), float("nan"), device=DEV)
     out16 = torch.full((n, 512), float("nan"), dtype=torch.float16, device=DEV)
-    q_d, proj_d, alpha_d = q.to(DEV), proj.to(DEV).contiguous(), alpha.to(DEV)  # (kept alive until the kernel ran)
-    _lib.check(lib.echr_attention_step_f16(q_d.data_ptr(), proj_d.data_ptr(), clip_d.data_ptr(),
+    q_d, proj_d, alpha_d, scale_d = torch.exp(2 * q).to(DEV), proj.to(DEV).contiguous(), alpha.to(DEV), scale.to(DEV)
+    _lib.check(lib.echr_attention_step_f16(q_d.data_ptr(), proj_d.data_ptr(), scale_d.data_ptr(), clip_d.data_ptr(),
                                            alpha_d.data_ptr(), rs.data_ptr(), rl.data_ptr(), n, out.data_ptr(),
                                            out16.data_ptr(), 512, torch.cuda.current_stream().cuda_stream), "attention_f16")
     torch.cuda.synchronize()
