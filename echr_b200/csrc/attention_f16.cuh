@@ -27,10 +27,10 @@
 namespace echr {
 
 constexpr int ATR_WARPS = 8;
-constexpr int ATR_SLOTS = 2;                              // clips in flight per warp
+constexpr int ATR_SLOTS = 4;                              // clips in flight per warp
 constexpr int ATR_SLOT_BYTES = 2048;                      // table row | clip row
 constexpr int ATR_RING_BYTES = ATR_WARPS * ATR_SLOTS * ATR_SLOT_BYTES;   // 32 KB (re-used as the merge buffer)
-constexpr int ATR_SMEM = ATR_RING_BYTES + 256;            // + mbarriers and merge scalars
+constexpr int ATR_SMEM = ATR_RING_BYTES + 512;            // + mbarriers and merge scalars
 
 struct AttF16Params {
   const float* q_exp;            // [rows, 512] fp32: e^{2 (h2att(h1) + b)}

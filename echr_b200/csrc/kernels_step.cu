@@ -569,8 +569,8 @@ attention_f16_kernel(const __grid_constant__ AttF16Params P, unsigned long long*
   const uint32_t ring = smem_u32(atr_smem) + warp * (ATR_SLOTS * ATR_SLOT_BYTES);   // this warp's slots
   uint8_t* tail = atr_smem + ATR_RING_BYTES;
   const uint32_t bars = smem_u32(tail) + warp * (ATR_SLOTS * 8);                     // this warp's mbarriers
-  float* s_m = reinterpret_cast<float*>(tail + 128);   // [8] per-warp running max
-  float* s_l = reinterpret_cast<float*>(tail + 160);   // [8] per-warp running sum
+  float* s_m = reinterpret_cast<float*>(tail + 384);   // [8] per-warp running max
+  float* s_l = reinterpret_cast<float*>(tail + 416);   // [8] per-warp running sum
   if (lane == 0) {
     for (int i = 0; i < ATR_SLOTS; ++i) mbar_init(bars + 8u * i, 1);
     fence_mbar_init();

@@ -25,6 +25,11 @@ for name, a, b in (("h2d", d, h), ("d2h", h, d)):
     torch.cuda.synchronize(); print(name, "%.1f GB/s" % (10 * 0.268435456 / (time.perf_counter() - t0)))
 PY
   ;;
+quick)
+  timeout 600 python bench.py --steps 10 --no-cpu-baseline --no-second-beam > $O/bench_cfg5.json 2> $O/bench_cfg5.err
+  timeout 600 python bench.py --workload cfg2 --batch-videos 64 --no-cpu-baseline --no-second-beam > $O/bench_cfg2.json 2> $O/bench_cfg2.err
+  timeout 600 python bench.py --workload cfg3 --steps 5 --no-cpu-baseline --no-second-beam > $O/bench_cfg3.json 2> $O/bench_cfg3.err
+  timeout 600 python bench.py --workload cfg4 --steps 5 --no-cpu-baseline --no-second-beam > $O/bench_cfg4.json 2> $O/bench_cfg4.err ;;
 sweep)
   for bv in 128 256 1024; do timeout 600 python bench.py --batch-videos $bv --steps 10 --no-cpu-baseline --no-second-beam > $O/sweep_bv$bv.json 2> $O/sweep_bv$bv.err; done
   for fl in 2 3; do timeout 600 python bench.py --in-flight $fl --steps 10 --no-cpu-baseline --no-second-beam > $O/sweep_fl$fl.json 2> $O/sweep_fl$fl.err; done ;;
