@@ -13,24 +13,26 @@
 // (2^-12 relative) moves tanh by at most 1.3e-4; entries more than 8 below the row maximum flush towards 0, where
 // tanh = -1 to within e^{2(P+q)} itself.  No clamp is needed on the product: inf gives rcp -> 0, tanh = 1.
 //
-// Schedule.  One CTA (8 warps, three CTAs per SM) per decode row; warp w owns clips w, w+8, ... of the window and
-// folds them into an online softmax (running max / sum / weighted feature sum, rescaled when the max moves); the
-// eight partial states are merged through shared memory at the end.  Every warp keeps a PRIVATE two-slot ring in
-// shared memory that its lane 0 fills with cp.async.bulk (one slot = the 1 KB table row + the 1 KB clip row of one
-// clip, two copies on one mbarrier) two clips ahead: 24 warps x 4 KB = 96 KB of HBM/L2 reads in flight per SM
-// with no register held for them and no block-wide barrier inside a row.  Every byte of a window is read exactly
-// once: no score buffer (so no bound on the window length), no second pass over the clip rows.
+// Schedule.  One CTA of W warps per decode row; warp w owns clips w, w+W, ... of the window and folds them into an
+// online softmax (running max / sum / weighted feature sum, rescaled when the max moves); the W partial states are
+// merged through shared memory at the end.  Every warp keeps a PRIVATE four-slot ring in shared memory that its
+// lane 0 fills with cp.async.bulk (one slot = the 1 KB table row + the 1 KB clip row of one clip, two copies on one
+// mbarrier) up to four clips ahead: 24 warps x 8 KB of HBM/L2 reads in flight per SM with no register held for
+// them and no block-wide barrier inside a row.  Every byte of a window is read exactly once: no score buffer (so no
+// bound on the window length), no second pass over the clip rows.
+// W is chosen per launch: a row costs ~3 us of dependent latency (window descriptor -> first copies -> merge)
+// whatever its length, so launches of many short windows run 2 or 4 warps per row and 12 or 6 rows per SM
+// (cfg5: mean window 25 clips), long windows or few rows 8 warps per row (cfg3/cfg4, the latency regime).
 // Algorithmic bytes per event-step: 2052 L + 2048 (e^{2q} in) + 1000 (att out).
 #pragma once
 #include "ptx.cuh"
 
 namespace echr {
 
-constexpr int ATR_WARPS = 8;
 constexpr int ATR_SLOTS = 4;                              // clips in flight per warp
 constexpr int ATR_SLOT_BYTES = 2048;                      // table row | clip row
-constexpr int ATR_RING_BYTES = ATR_WARPS * ATR_SLOTS * ATR_SLOT_BYTES;   // 32 KB (re-used as the merge buffer)
-constexpr int ATR_SMEM = ATR_RING_BYTES + 512;            // + mbarriers and merge scalars
+constexpr int ATR_WARP_BYTES = ATR_SLOTS * ATR_SLOT_BYTES;   // per-warp ring (the rings double as the merge buffer)
+constexpr int atr_smem(int warps) { return warps * ATR_WARP_BYTES + 512; }   // + mbarriers and merge scalars
 
 struct AttF16Params {
   const float* q_exp;            // [rows, 512] fp32: e^{2 (h2att(h1) + b)}

@@ -499,6 +499,7 @@ static int stage_desc(echr_batch_t* b, const echr_batch_desc_t* d, bool check_cl
   for (int v = 0; v < d->n_videos; ++v) { vid_first[v] = 0; vid_n[v] = 0; }
   int prev_v = 0;
   int max_len = 0;
+  long long sum_len = 0;
   for (int i = 0; i < d->n_events; ++i) {
     const int v = d->host_event_video[i];
     ECHR_REQUIRE(v >= prev_v && v < d->n_videos, "echr_batch_set_inputs: event %d: video index %d not non-decreasing / out of range", i, v);
@@ -514,6 +515,7 @@ static int stage_desc(echr_batch_t* b, const echr_batch_desc_t* d, bool check_cl
     hs[1 * E + i] = off[v] + s;
     hs[2 * E + i] = e - s;
     if (e - s > max_len) max_len = e - s;
+    sum_len += e - s;
     hs[3 * E + i] = off[v] + ind;
   }
   long long pairs = 0;
@@ -537,6 +539,7 @@ static int stage_desc(echr_batch_t* b, const echr_batch_desc_t* d, bool check_cl
   b->n_pairs = (int)pairs;
   b->max_n = max_n;
   b->max_len = max_len;
+  b->mean_len = d->n_events > 0 ? (int)((sum_len + d->n_events - 1) / d->n_events) : 0;
   b->encoded = false;
   ECHR_CUDA(cudaMemcpyAsync(b->ev_video, hs, sizeof(int32_t) * ((size_t)7 * E + 2 * b->cap.max_videos),
                             cudaMemcpyHostToDevice, st));
@@ -892,7 +895,7 @@ static int enqueue_step(echr_batch* b, int rows, int t, int topk, float* logits_
     PdlScope pdl(PDL_ATT);
     if (att16) {
       const AttF16Params ap = attention_params(b, rows, t);
-      ECHR_CUDA(launch_attention_f16(ap, st, trace_ptr(b), trace_next(b, 1)));
+      ECHR_CUDA(launch_attention_f16(ap, b->mean_len, st, trace_ptr(b), trace_next(b, 1)));
     } else {
       ECHR_CUDA(launch_attention(b->q_att, (const void*)b->proj_f32, (const void*)b->c3d, ECHR_VIDEO_DIM, 0, m->alpha,
                                  b->row_start, b->row_len, rows, nullptr, cur.plane(0) + ACT_ATT,

@@ -73,6 +73,7 @@ struct echr_batch {
   // current batch
   int n_videos, n_events, n_clips, n_pairs, max_n;  // max_n = largest events-per-video
   int max_len;                                      // longest event span (clips)
+  int mean_len;                                     // mean event span (clips), rounded up
   bool encoded;
   // inputs (copies)
   float *c3d, *tap, *lda;  // [clips,500]; tap_feats[ind] per event [events,512]; [videos,100]
@@ -171,7 +172,7 @@ cudaError_t launch_attention(const float* q, const void* proj, const void* clip,
                              const int32_t* row_len, int64_t rows, float* out_f32, bf16* out_hi,
                              bf16* out_lo, int64_t ld_bf, cudaStream_t st, int max_len = 0,
                              unsigned long long* trace = nullptr, int trace_slot = 0);
-cudaError_t launch_attention_f16(const AttF16Params& P, cudaStream_t st, unsigned long long* trace = nullptr, int trace_slot = 0);
+cudaError_t launch_attention_f16(const AttF16Params& P, int mean_len, cudaStream_t st, unsigned long long* trace = nullptr, int trace_slot = 0);
 cudaError_t launch_attention_table(const float* proj, int clips, bf16* table, float* scale, cudaStream_t st);
 cudaError_t launch_decode_init(const echr_batch* b, int beam, cudaStream_t st);
 cudaError_t launch_finalize_greedy(echr_batch* b, int step, int32_t* tokens, float* logp,

@@ -175,6 +175,30 @@ gemm_tc2_kernel(const __grid_constant__ GemmParams P, int groups, int total_tile
         umma_commit(tmem_full_bar(buf));
       }
     }
+  } else if (warp == 3) {
+    // ===================== L2 prefetcher (LSTM epilogue only) =====================
+    // The epilogue gathers, per output row and tile, 1 KB of the token gate table (a random 8 KB row of a 141 MB
+    // table: an HBM miss), 256 B of cell state and, when hoisted, 1 KB of per-row bias; it can only keep one
+    // 32-column chunk of them in flight (registers).  This otherwise idle warp asks L2 for all of them up front —
+    // every tile of this CTA, right after the predecessor's results are visible — so that the epilogue's loads
+    // hit L2 instead of waiting for HBM chunk by chunk.
+    if constexpr (EPI == EPI_LSTM) {
+      for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
+        const Gemm2Tile tl = gemm2_tile(P, groups, t);
+        const GemmProblem& pb = P.prob[tl.g];
+        const int col0 = tl.n_tile * BN;
+        for (int i = lane; i < GEMM_BLOCK_M; i += 32) {
+          const long long row = static_cast<long long>(tl.m_tile) * GEMM_BLOCK_M + i;
+          if (row >= pb.M) break;
+          if (pb.tok_table != nullptr) {
+            const int tk = pb.row_key != nullptr ? token_of_key(pb.row_key[row * KEY_STRIDE]) : __ldg(pb.row_tok + row);
+            bulk_prefetch_l2(pb.tok_table + static_cast<long long>(tk) * pb.ld_tok_table + col0, BN * 4);
+          }
+          if (pb.row_bias != nullptr) bulk_prefetch_l2(pb.row_bias + row * pb.ld_row_bias + col0, BN * 4);
+          bulk_prefetch_l2(pb.c_in + row * pb.hidden + (col0 >> 2), BN);
+        }
+      }
+    }
   } else if (warp >= 4) {
     // ===================== epilogue =====================
     constexpr int HALF = BN / 2;  // 128 columns per thread

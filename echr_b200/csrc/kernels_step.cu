@@ -16,7 +16,10 @@ namespace echr {
 // GEMM epilogue) and EQ = e^{2q} (h2att GEMM epilogue), and a score costs per element one FMUL, one
 // FADD, one MUFU.RCP and one FFMA:  score' = sum_k (-2 alpha_k) / (EP_lk * EQ_k + 1).  The dropped
 // constant sum_k alpha_k is the same for every clip of the row, so the softmax is unchanged.  Both
-// exponents are clamped to +-80 when the tables are written, so the product stays finite.
+// exponents are clamped to +-80 when the tables are written (ACT_EXP2X), so each factor is finite; their
+// product may still overflow to +inf, which rcp.approx maps to 0, i.e. tanh = 1: the right limit.  The clamp
+// itself is a documented bound of this library: |P| and |q| <= 40; only a pair with both beyond
+// it and opposite signs would be evaluated differently from the reference.
 __device__ __forceinline__ float rcp_fast(float x) {
   float y;
   asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
@@ -559,15 +562,16 @@ cudaError_t launch_attention(const float* q, const void* proj, const void* clip,
 
 // ---------------------------------------------------------------------------------------------
 // 16-bit, bulk-copy staged attention: design notes in attention_f16.cuh.
-__global__ void __launch_bounds__(ATR_WARPS * 32, 3)
+template <int ATR_WARPS>
+__global__ void __launch_bounds__(ATR_WARPS * 32, 24 / ATR_WARPS)
 attention_f16_kernel(const __grid_constant__ AttF16Params P, unsigned long long* trace, int trace_slot) {
   extern __shared__ __align__(128) uint8_t atr_smem[];
   trace_begin(trace, trace_slot);
   constexpr float L2E = 1.4426950408889634f;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int r = blockIdx.x;
-  const uint32_t ring = smem_u32(atr_smem) + warp * (ATR_SLOTS * ATR_SLOT_BYTES);   // this warp's slots
-  uint8_t* tail = atr_smem + ATR_RING_BYTES;
+  const uint32_t ring = smem_u32(atr_smem) + warp * ATR_WARP_BYTES;   // this warp's slots
+  uint8_t* tail = atr_smem + ATR_WARPS * ATR_WARP_BYTES;
   const uint32_t bars = smem_u32(tail) + warp * (ATR_SLOTS * 8);                     // this warp's mbarriers
   float* s_m = reinterpret_cast<float*>(tail + 384);   // [8] per-warp running max
   float* s_l = reinterpret_cast<float*>(tail + 416);   // [8] per-warp running sum
@@ -673,7 +677,7 @@ attention_f16_kernel(const __grid_constant__ AttF16Params P, unsigned long long*
 #pragma unroll
   for (int w = 0; w < ATR_WARPS; ++w) total += s_m[w] == -INFINITY ? 0.f : s_l[w] * exp2f((s_m[w] - M) * L2E);
   const float my = mx == -INFINITY ? 0.f : exp2f((mx - M) * L2E);
-  float* red = reinterpret_cast<float*>(atr_smem);  // [8][512] over the first 16 KB of the rings
+  float* red = reinterpret_cast<float*>(atr_smem);  // [W][512] over the first quarter of the rings
 #pragma unroll
   for (int m = 0; m < 2; ++m) {
     float* d = red + warp * 512 + 256 * m + 8 * lane;
@@ -682,33 +686,43 @@ attention_f16_kernel(const __grid_constant__ AttF16Params P, unsigned long long*
   }
   __syncthreads();
   const float inv = total > 0.f ? 1.0f / total : 0.f;  // (an empty window gives a zero feature)
-  const int c0 = 2 * threadIdx.x;  // 256 threads x 2 columns
-  float v0 = 0.f, v1 = 0.f;
+  for (int c0 = 2 * threadIdx.x; c0 < 512; c0 += 64 * ATR_WARPS) {  // two columns per thread and pass
+    float v0 = 0.f, v1 = 0.f;
 #pragma unroll
-  for (int w = 0; w < ATR_WARPS; ++w) {
-    const float2 t = *reinterpret_cast<const float2*>(red + w * 512 + c0);
-    v0 += t.x;
-    v1 += t.y;
-  }
-  v0 *= inv;
-  v1 *= inv;
-  if (P.out != nullptr) {
-    __align__(4) __nv_bfloat16 h[2] = {f16_bits(v0), f16_bits(v1)};
-    *reinterpret_cast<uint32_t*>(P.out + static_cast<long long>(r) * P.ld_out + c0) = *reinterpret_cast<const uint32_t*>(h);
-  }
-  if (P.out_f32 != nullptr && c0 < 500) {
-    P.out_f32[static_cast<long long>(r) * 500 + c0] = v0;
-    P.out_f32[static_cast<long long>(r) * 500 + c0 + 1] = v1;
+    for (int w = 0; w < ATR_WARPS; ++w) {
+      const float2 t = *reinterpret_cast<const float2*>(red + w * 512 + c0);
+      v0 += t.x;
+      v1 += t.y;
+    }
+    v0 *= inv;
+    v1 *= inv;
+    if (P.out != nullptr) {
+      __align__(4) __nv_bfloat16 h[2] = {f16_bits(v0), f16_bits(v1)};
+      *reinterpret_cast<uint32_t*>(P.out + static_cast<long long>(r) * P.ld_out + c0) = *reinterpret_cast<const uint32_t*>(h);
+    }
+    if (P.out_f32 != nullptr && c0 < 500) {
+      P.out_f32[static_cast<long long>(r) * 500 + c0] = v0;
+      P.out_f32[static_cast<long long>(r) * 500 + c0 + 1] = v1;
+    }
   }
   trace_end(trace, trace_slot);
 }
 
-cudaError_t launch_attention_f16(const AttF16Params& P, cudaStream_t st, unsigned long long* trace, int trace_slot) {
-  if (P.rows == 0) return cudaSuccess;
+template <int W>
+static cudaError_t launch_attention_f16_w(const AttF16Params& P, cudaStream_t st, unsigned long long* trace, int trace_slot) {
   static int attr[MAX_DEVICES] = {};
-  cudaError_t e = set_max_dynamic_smem(attention_f16_kernel, ATR_SMEM, attr);
+  cudaError_t e = set_max_dynamic_smem(attention_f16_kernel<W>, atr_smem(W), attr);
   if (e != cudaSuccess) return e;
-  e = launch_pdl(attention_f16_kernel, dim3((unsigned)P.rows), dim3(ATR_WARPS * 32), (size_t)ATR_SMEM, st, P, trace, trace_slot);
+  return launch_pdl(attention_f16_kernel<W>, dim3((unsigned)P.rows), dim3(W * 32), (size_t)atr_smem(W), st, P, trace, trace_slot);
+}
+
+// mean_len: average window length of the launch (0 = unknown).  See attention_f16.cuh for the choice of W.
+cudaError_t launch_attention_f16(const AttF16Params& P, int mean_len, cudaStream_t st, unsigned long long* trace, int trace_slot) {
+  if (P.rows == 0) return cudaSuccess;
+  cudaError_t e;
+  if (P.rows <= 2 * num_sms() || mean_len <= 0 || mean_len > 64) e = launch_attention_f16_w<8>(P, st, trace, trace_slot);
+  else if (mean_len > 16) e = launch_attention_f16_w<4>(P, st, trace, trace_slot);
+  else e = launch_attention_f16_w<2>(P, st, trace, trace_slot);
   count_launch();
   return e;
 }

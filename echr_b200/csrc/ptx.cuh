@@ -151,6 +151,11 @@ __device__ __forceinline__ void bulk_load_1d(uint32_t dst_smem, const void* src,
       : "memory");
 }
 
+// L2 prefetch of a contiguous range (bytes multiple of 16, address 16-byte aligned): a hint, no destination.
+__device__ __forceinline__ void bulk_prefetch_l2(const void* src, uint32_t bytes) {
+  asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(src), "r"(bytes) : "memory");
+}
+
 // ---------------------------------------------------------------- tcgen05 / TMEM
 template <int kCols>
 __device__ __forceinline__ void tmem_alloc(uint32_t dst_smem) {

@@ -157,10 +157,11 @@ ECHR_API int echr_attention_step(const float* q_exp, const void* proj_exp, const
  * P = ctx2att(c3d) + b, proj_scale [n_clips] fp32 = e^{2 rowmax P}; clip16 [n_clips,512] fp16, columns 500..511
  * zero.  One CTA per row; every warp streams its clips through a private shared-memory ring filled by
  * cp.async.bulk and folds them into an online softmax; any window length.
- * out_f32 [rows,500] (may be NULL); out16 [rows, ld_out] fp16 (may be NULL). */
+ * out_f32 [rows,500] (may be NULL); out16 [rows, ld_out] fp16 (may be NULL).  mean_len: the average row_len if the
+ * caller knows it (launches of many short windows then run 2 or 4 warps per row instead of 8), 0 if unknown. */
 ECHR_API int echr_attention_step_f16(const float* q_exp, const void* proj16, const float* proj_scale, const void* clip16,
                             const float* alpha, const int32_t* row_start, const int32_t* row_len, int64_t rows,
-                            float* out_f32, void* out16, int64_t ld_out, void* stream);
+                            float* out_f32, void* out16, int64_t ld_out, int mean_len, void* stream);
 
 /* ---- model: packed weights --------------------------------------------------------------- */
 /* Packs the checkpoint into kernel layouts (bf16 planes, gate-interleaved LSTM rows, fused biases).

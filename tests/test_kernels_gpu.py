@@ -65,11 +65,11 @@ def test_attention_step_matches_oracle(clip_bf16, staged):
     assert (rec[:, 500:] == 0).all()
 
 
-@pytest.mark.parametrize("rows_mult", [1, 40])
-def test_attention_step_f16_matches_oracle(rows_mult):
+@pytest.mark.parametrize("rows_mult,mean_len", [(1, 0), (40, 0), (40, 30), (40, 8)])
+def test_attention_step_f16_matches_oracle(rows_mult, mean_len):
     """The 16-bit bulk-copy staged attention (csrc/attention_f16.cuh: fp16 projection and clip tables, one warp per
     row, online softmax) against the oracle's `attend` on the same fp16-rounded tables: windows of 1 ... 300 clips,
-    a few rows (one per warp) and many rows (every warp walks several rows, the ring runs across row boundaries)."""
+    a few rows and many rows, with 8, 4 and 2 warps per row (chosen from the mean window length the caller states)."""
     lib = _lib.load()
     sd = helpers.state_dict("bf16w")
     a = "lm_model.core.attention."
@@ -102,7 +102,8 @@ def test_attention_step_f16_matches_oracle(rows_mult):
     q_d, proj_d, alpha_d, scale_d = torch.exp(2 * q).to(DEV), proj.to(DEV).contiguous(), alpha.to(DEV), scale.to(DEV)
     _lib.check(lib.echr_attention_step_f16(q_d.data_ptr(), proj_d.data_ptr(), scale_d.data_ptr(), clip_d.data_ptr(),
                                            alpha_d.data_ptr(), rs.data_ptr(), rl.data_ptr(), n, out.data_ptr(),
-                                           out16.data_ptr(), 512, torch.cuda.current_stream().cuda_stream), "attention_f16")
+                                           out16.data_ptr(), 512, mean_len, torch.cuda.current_stream().cuda_stream),
+               "attention_f16")  # mean_len picks 8 / 4 / 2 warps per row
     torch.cuda.synchronize()
     err = (out.cpu() - want).abs().max().item()
     print("attention_f16 max err", err)

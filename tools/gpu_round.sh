@@ -37,6 +37,12 @@ ncu)
   CMD="python bench.py --videos 1024 --steps 1 --warmup 1 --no-cpu-baseline --no-second-beam"
   $CMD > $O/ncu_plain.json 2> $O/ncu_plain.err &&
   timeout 1200 ncu --metrics gpu__time_duration.sum --clock-control none -c 6000 --csv --log-file $O/launches.csv $CMD > $O/ncu_launches.log 2>&1 ;;
+scale)
+  # strong-scaling line of the default workload on NG GPUs (gpurun --gpus NG), NCCL ring / NVLS evidence in the .err
+  NG=${NG:-2}
+  NCCL_DEBUG=INFO timeout 900 python -m torch.distributed.run --nnodes=1 --nproc-per-node $NG --master-addr 127.0.0.1 --master-port 2951$NG \
+      bench.py --gpus $NG --steps 10 > $O/scale_n$NG.json 2> $O/scale_n$NG.err
+  grep -E "NCCL INFO (Channel|Connected|comm 0x|NVLS|ncclCommInit)" $O/scale_n$NG.err | head -40 > $O/scale_n$NG.nccl.txt ;;
 ncufull)
   # ncu --set full of every kernel family (tools/profile_targets.py); the raw page is exported on the box, the
   # report itself only comes back when it fits the 64 MiB return channel

@@ -55,7 +55,8 @@ rng = np.random.RandomState(1)
 sst = SST(SOpt(), precision="f16")
 ssd = {k: torch.from_numpy(((rng.rand(*t.shape) * 2 - 1) / np.sqrt(512.0)).astype(np.float32)) for k, t in sst.state_dict().items()}
 sst.load_state_dict(ssd, strict=True)
-sst = sst.to(DEV).eval()
+sst = sst.to(DEV)
+sst.eval()
 feats = [torch.randn(16, 500, device=DEV) for _ in range(8)]
 outs = sst.forward_batch(feats)
 torch.cuda.synchronize()
@@ -63,6 +64,6 @@ T, K = 100, 64
 pred = torch.rand(T, K, device=DEV)
 mask = (np.arange(T)[:, None] >= np.arange(K)[None, :]).astype(np.float32)
 P.gettop1000(pred, mask, [], 100.0, lambda s, e, n, d: (s * d / n, e * d / n), topN=100)
-P.gettop1000_nms(pred, mask, [], 100.0, lambda s, e, n, d: (s * d / n, e * d / n), topN=50, nms_overlap=0.7)
+P.gettop1000_nms(pred, mask, [], 100.0, lambda s, e, n, d: (s * d / n, e * d / n), topN=50, overlap=0.7)
 torch.cuda.synchronize()
 print("done")
