@@ -53,7 +53,7 @@ def parse():
     ap.add_argument("--no-second-beam", action="store_true", help="skip the beam=3 (greedy for cfg3) companion measurement")
     ap.add_argument("--in-flight", type=int, default=4,
                     help="batches kept in flight per GPU (CaptionPipeline lanes); 1 = one blocking batch at a time")
-    ap.add_argument("--batch-videos", type=int, default=512, help="videos per batch a rank submits")
+    ap.add_argument("--batch-videos", type=int, default=1024, help="videos per batch a rank submits")
     return ap.parse_args()
 
 

@@ -720,6 +720,14 @@ static cudaError_t launch_attention_f16_w(const AttF16Params& P, cudaStream_t st
 cudaError_t launch_attention_f16(const AttF16Params& P, int mean_len, cudaStream_t st, unsigned long long* trace, int trace_slot) {
   if (P.rows == 0) return cudaSuccess;
   cudaError_t e;
+  const char* force = knob("ECHR_ATT_W");  // (debug builds only)
+  if (force != nullptr) {
+    const int w = atoi(force);
+    e = w == 2 ? launch_attention_f16_w<2>(P, st, trace, trace_slot) : w == 4 ? launch_attention_f16_w<4>(P, st, trace, trace_slot)
+                                                                              : launch_attention_f16_w<8>(P, st, trace, trace_slot);
+    count_launch();
+    return e;
+  }
   if (P.rows <= 2 * num_sms() || mean_len <= 0 || mean_len > 64) e = launch_attention_f16_w<8>(P, st, trace, trace_slot);
   else if (mean_len > 16) e = launch_attention_f16_w<4>(P, st, trace, trace_slot);
   else e = launch_attention_f16_w<2>(P, st, trace, trace_slot);

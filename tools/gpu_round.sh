@@ -30,6 +30,11 @@ quick)
   timeout 600 python bench.py --workload cfg2 --batch-videos 64 --no-cpu-baseline --no-second-beam > $O/bench_cfg2.json 2> $O/bench_cfg2.err
   timeout 600 python bench.py --workload cfg3 --steps 5 --no-cpu-baseline --no-second-beam > $O/bench_cfg3.json 2> $O/bench_cfg3.err
   timeout 600 python bench.py --workload cfg4 --steps 5 --no-cpu-baseline --no-second-beam > $O/bench_cfg4.json 2> $O/bench_cfg4.err ;;
+attw)
+  # debug-knob build only: warps per row of the 16-bit attention forced from the environment
+  for w in 2 4 8; do for c in cfg5 cfg3 cfg4 cfg2; do
+    ECHR_ATT_W=$w timeout 600 python bench.py --workload $c --steps 5 --no-cpu-baseline --no-second-beam $( [ $c = cfg2 ] && echo --batch-videos 64 ) > $O/attw${w}_$c.json 2> $O/attw${w}_$c.err
+  done; done ;;
 sweep)
   for bv in 128 256 1024; do timeout 600 python bench.py --batch-videos $bv --steps 10 --no-cpu-baseline --no-second-beam > $O/sweep_bv$bv.json 2> $O/sweep_bv$bv.err; done
   for fl in 2 3; do timeout 600 python bench.py --in-flight $fl --steps 10 --no-cpu-baseline --no-second-beam > $O/sweep_fl$fl.json 2> $O/sweep_fl$fl.err; done ;;
