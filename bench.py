@@ -2,7 +2,7 @@
 """Benchmark of the ECHR caption-generation hot path (BASELINE.json metric: events captioned / s).
 
     python bench.py [--gpus N] [--steps K] [--warmup W] [--workload cfg5] [--beam B] [--precision f16]
-                    [--in-flight 4] [--batch-videos 512]
+                    [--in-flight 4] [--batch-videos 1024]
     python bench.py --impl reference ...      # the reference's own CPU path on the host cores (oracle/_ref)
 
 Default workload = BASELINE.json configs[4] ("cfg5"): 4096 synthetic videos (~16k events) in total, block-sharded
@@ -208,11 +208,12 @@ def main():
     try:
         return _main(args)
     finally:
+        # fd 1 stays pointed at stderr for the rest of the process (NCCL still prints while it tears down at exit);
+        # the line goes straight to the real stdout
         sys.stdout.flush()
-        os.dup2(real_stdout, 1)
-        os.close(real_stdout)
         if _RESULT:
-            print(_RESULT[0], flush=True)
+            os.write(real_stdout, (_RESULT[0] + "\n").encode())
+        os.close(real_stdout)
 
 
 _RESULT = []
