@@ -580,17 +580,8 @@ attention_f16_kernel(const __grid_constant__ AttF16Params P, unsigned long long*
     fence_mbar_init();
   }
   __syncwarp();
-  // lane's hidden units / clip columns: [8 lane + 256 m, +8), m = 0, 1 (16-byte chunks lane and lane + 32 of a row)
-  float av[16];
-#pragma unroll
-  for (int m = 0; m < 2; ++m) {
-    const float4 a0 = __ldg(reinterpret_cast<const float4*>(P.alpha + 256 * m + 8 * lane));
-    const float4 a1 = __ldg(reinterpret_cast<const float4*>(P.alpha + 256 * m + 8 * lane + 4));
-    av[8 * m + 0] = -2.f * a0.x; av[8 * m + 1] = -2.f * a0.y; av[8 * m + 2] = -2.f * a0.z; av[8 * m + 3] = -2.f * a0.w;
-    av[8 * m + 4] = -2.f * a1.x; av[8 * m + 5] = -2.f * a1.y; av[8 * m + 6] = -2.f * a1.z; av[8 * m + 7] = -2.f * a1.w;
-  }
   pdl_trigger();
-  pdl_wait();  // e^{2q} comes from the h2att GEMM launched just before; nothing but weights is read earlier
+  pdl_wait();  // e^{2q} comes from the h2att GEMM launched just before
   const int s0 = __ldg(P.row_start + r);
   const int L = __ldg(P.row_len + r);
   const int n_mine = L > warp ? (L - warp + ATR_WARPS - 1) / ATR_WARPS : 0;  // clips warp, warp + 8, ...
@@ -604,6 +595,17 @@ attention_f16_kernel(const __grid_constant__ AttF16Params P, unsigned long long*
   };
   if (lane == 0)
     for (int i = 0; i < ATR_SLOTS && i < n_mine; ++i) issue(i);
+  // (everything below is loaded while the first copies are in flight: the row's dependent chain is
+  //  window descriptor -> copies -> compute -> merge, nothing else)
+  // lane's hidden units / clip columns: [8 lane + 256 m, +8), m = 0, 1 (16-byte chunks lane and lane + 32 of a row)
+  float av[16];
+#pragma unroll
+  for (int m = 0; m < 2; ++m) {
+    const float4 a0 = __ldg(reinterpret_cast<const float4*>(P.alpha + 256 * m + 8 * lane));
+    const float4 a1 = __ldg(reinterpret_cast<const float4*>(P.alpha + 256 * m + 8 * lane + 4));
+    av[8 * m + 0] = -2.f * a0.x; av[8 * m + 1] = -2.f * a0.y; av[8 * m + 2] = -2.f * a0.z; av[8 * m + 3] = -2.f * a0.w;
+    av[8 * m + 4] = -2.f * a1.x; av[8 * m + 5] = -2.f * a1.y; av[8 * m + 6] = -2.f * a1.z; av[8 * m + 7] = -2.f * a1.w;
+  }
   float qe[16];
 #pragma unroll
   for (int m = 0; m < 2; ++m) {
@@ -651,21 +653,25 @@ attention_f16_kernel(const __grid_constant__ AttF16Params P, unsigned long long*
       }
     }
     s = warp_sum(s);
-    const float m_new = fmaxf(mx, s);
-    const float corr = exp2f((mx - m_new) * L2E);  // exp2(-inf) = 0 on the warp's first clip
-    const float p = exp2f((s - m_new) * L2E);
-    sum = fmaf(sum, corr, p);
+    if (s > mx) {  // (warp-uniform) the running maximum moves: rescale what has been accumulated — O(log n) times per row
+      const float corr = exp2f((mx - s) * L2E);  // exp2(-inf) = 0 on the warp's first clip
+      sum *= corr;
+#pragma unroll
+      for (int i2 = 0; i2 < 16; ++i2) acc[i2] *= corr;
+      mx = s;
+    }
+    const float p = exp2f((s - mx) * L2E);
+    sum += p;
 #pragma unroll
     for (int m = 0; m < 2; ++m) {
       const uint32_t w4[4] = {cu[m].x, cu[m].y, cu[m].z, cu[m].w};
 #pragma unroll
       for (int j = 0; j < 4; ++j) {
         const float2 c2 = f16x2_value(w4[j]);
-        acc[8 * m + 2 * j] = fmaf(acc[8 * m + 2 * j], corr, p * c2.x);
-        acc[8 * m + 2 * j + 1] = fmaf(acc[8 * m + 2 * j + 1], corr, p * c2.y);
+        acc[8 * m + 2 * j] = fmaf(p, c2.x, acc[8 * m + 2 * j]);
+        acc[8 * m + 2 * j + 1] = fmaf(p, c2.y, acc[8 * m + 2 * j + 1]);
       }
     }
-    mx = m_new;
   }
   // ---- merge the eight warps' (max, sum, weighted sum): att = sum_w e^{m_w - M} acc_w / sum_w e^{m_w - M} sum_w
   if (lane == 0) { s_m[warp] = mx; s_l[warp] = sum; }

@@ -39,7 +39,7 @@ sweep)
   for bv in 128 256 1024; do timeout 600 python bench.py --batch-videos $bv --steps 10 --no-cpu-baseline --no-second-beam > $O/sweep_bv$bv.json 2> $O/sweep_bv$bv.err; done
   for fl in 2 3; do timeout 600 python bench.py --in-flight $fl --steps 10 --no-cpu-baseline --no-second-beam > $O/sweep_fl$fl.json 2> $O/sweep_fl$fl.err; done ;;
 ncu)
-  CMD="python bench.py --videos 1024 --steps 1 --warmup 1 --no-cpu-baseline --no-second-beam"
+  CMD="python bench.py --steps 1 --warmup 1 --no-cpu-baseline --no-second-beam"
   $CMD > $O/ncu_plain.json 2> $O/ncu_plain.err &&
   timeout 1200 ncu --metrics gpu__time_duration.sum --clock-control none -c 6000 --csv --log-file $O/launches.csv $CMD > $O/ncu_launches.log 2>&1 ;;
 scale)
@@ -57,6 +57,13 @@ ncufull)
       -c 500 -o $O/targets -f $CMD > $O/targets_ncu.log 2>&1
   ncu -i $O/targets.ncu-rep --page raw --csv > $O/targets_raw.csv 2> $O/targets_export.log
   if [ $(stat -c %s $O/targets.ncu-rep 2>/dev/null || echo 0) -gt 40000000 ]; then rm -f $O/targets.ncu-rep; fi ;;
+ncustep)
+  # ncu --set full of the decode-step kernels at the default bench's batch shape (cfg5, 1024 videos, ~4070 rows)
+  CMD="python tools/profile_targets.py --step-only"
+  $CMD > $O/step_plain.log 2>&1 &&
+  timeout 1200 ncu --set full --clock-control none -k regex:"gemm_tc|attention_f16|finalize_greedy" -c 60 -o $O/step -f $CMD > $O/step_ncu.log 2>&1
+  ncu -i $O/step.ncu-rep --page raw --csv > $O/step_raw.csv 2> $O/step_export.log
+  if [ $(stat -c %s $O/step.ncu-rep 2>/dev/null || echo 0) -gt 40000000 ]; then rm -f $O/step.ncu-rep; fi ;;
 sanitize)
   # compute-sanitizer over smoke(): encode, greedy decode, SST encoder, selection, caption of selected proposals
   timeout 1500 compute-sanitizer --tool memcheck --error-exitcode 7 python -c "import __graft_entry__ as g; g.smoke()" > $O/sanitizer_memcheck.log 2>&1; echo "exit=$?" >> $O/sanitizer_memcheck.log

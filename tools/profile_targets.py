@@ -41,6 +41,9 @@ def run(vids, beam, what):
     print(what, "rows", lay.n_events * beam, "tokens", tuple(tok.shape))
 
 
+if "--step-only" in sys.argv:  # only the default bench's batch shape (1024 videos): the step kernels' traffic for bench.py
+    run(synth.make_workload("cfg5", n_videos=1024, bf16_features=True)[0], 1, "cfg5 batch of 1024 videos")
+    sys.exit(0)
 run(synth.make_workload("cfg5", n_videos=512, bf16_features=True)[0], 1, "cfg5 batch")
 run(synth.make_workload("cfg2", bf16_features=True)[0], 1, "cfg2")
 run(synth.make_workload("cfg4", n_videos=4, bf16_features=True)[0], 1, "cfg4 x4")
