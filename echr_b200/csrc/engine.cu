@@ -813,11 +813,6 @@ static const int KB_L2[8] = {42, 43, 44, 45, 46, 47, 48, 49};                   
 // with the constant-context blocks kept in the step GEMM (weights' column order [x | h | ctx])
 static const int KB_L0C[16] = {26, 27, 28, 29, 30, 31, 32, 33, 8, 9, 10, 11, 12, 13, 14, 15};   // h0, event
 static const int KB_L2C[10] = {42, 43, 44, 45, 46, 47, 48, 49, 24, 25};                         // h2, video
-// throughput regime: the embedded token is an operand too (activation columns 0..511, written by embed_rows_kernel),
-// so a stream's GEMM walks the weights' full column order [x | h | ctx] and its epilogue gathers nothing per row
-static const int KB_L0X[24] = {0, 1, 2, 3, 4, 5, 6, 7, 26, 27, 28, 29, 30, 31, 32, 33, 8, 9, 10, 11, 12, 13, 14, 15};
-static const int KB_L1X[24] = {0, 1, 2, 3, 4, 5, 6, 7, 34, 35, 36, 37, 38, 39, 40, 41, 16, 17, 18, 19, 20, 21, 22, 23};
-static const int KB_L2X[18] = {0, 1, 2, 3, 4, 5, 6, 7, 42, 43, 44, 45, 46, 47, 48, 49, 24, 25};
 
 enum { MODE_GREEDY = 0, MODE_BEAM = 1, MODE_TF = 2 };
 
@@ -920,26 +915,16 @@ static int enqueue_step(echr_batch* b, int rows, int t, int topk, float* logits_
       else if (mt * nt * 4 <= num_sms()) ks[1] = 2;
     }
     const bool hoist = hoist_context(rows);
-    // Where the embedded input token enters.  Latency regime: as a row of the token gate tables gathered in the
-    // epilogue (a third less K for a main loop bound by its operand stream).  Throughput regime: the persistent
-    // kernel is bound by exactly those gathers (24 KB of fp32 table rows per decode row and step: hoisting MORE terms
-    // into per-row tables made it slower, 53 -> 69 us at 4072 rows), while its tensor pipe is a third busy — there
-    // the embedding row (1 KB) is copied into the activation matrix and multiplied like every other operand.
-    const bool embed_op = !hoist;
-    const int* kbs[3] = {embed_op ? KB_L0X : hoist ? KB_L0 : KB_L0C, embed_op ? KB_L1X : KB_L1, embed_op ? KB_L2X : hoist ? KB_L2 : KB_L2C};
-    const int K[3] = {(embed_op ? 24 : hoist ? 8 : 16) * 64, (embed_op ? 24 : 16) * 64, (embed_op ? 18 : hoist ? 8 : 10) * 64};
-    if (embed_op)
-      ECHR_CUDA(launch_embed_rows(b, rows, p, use_keys ? b->argmax_key[(t + 1) & 1] : nullptr, st));
+    const int* kbs[3] = {hoist ? KB_L0 : KB_L0C, KB_L1, hoist ? KB_L2 : KB_L2C};
+    const int K[3] = {(hoist ? 8 : 16) * 64, 16 * 64, (hoist ? 8 : 10) * 64};
     for (int l = 0; l < 3; ++l) {
       wv[l] = m->w_lstm[l];
-      if (!embed_op) wv[l].p += HID;  // skip the x block of [x | h | ctx]; plane stride and ld are unchanged
+      wv[l].p += HID;  // skip the x block of [x | h | ctx]; plane stride and ld are unchanged
       s[l].A = &cur; s[l].a_kb = kbs[l]; s[l].M = rows; s[l].W = &wv[l]; s[l].N = GATES; s[l].K = K[l];
       s[l].bias = m->b_lstm[l];
       if (l != 1 && hoist) { s[l].row_bias = b->row_bias[l / 2]; s[l].ld_row_bias = GATES; }
-      if (!embed_op) {
-        s[l].row_tok = b->row_tok; s[l].tok_table = m->tok_gates[l]; s[l].ld_tok_table = GATES;
-        if (use_keys) s[l].row_key = b->argmax_key[(t + 1) & 1];  // written by the logits of step t - 1 (BOS at t = 0)
-      }
+      s[l].row_tok = b->row_tok; s[l].tok_table = m->tok_gates[l]; s[l].ld_tok_table = GATES;
+      if (use_keys) s[l].row_key = b->argmax_key[(t + 1) & 1];  // written by the logits of step t - 1 (BOS at t = 0)
       s[l].ksplit = ks[l];
       s[l].c_in = b->cstate[p] + (long long)l * rows * HID;
       s[l].c_out = b->cstate[n] + (long long)l * rows * HID;

@@ -184,9 +184,6 @@ cudaError_t launch_finalize_tf(const echr_batch* b, int step, const int32_t* seq
 cudaError_t launch_finalize_nll(const echr_batch* b, int step, const int32_t* seq, int seq_cols,
                                 const float* logits, float* target_logp, cudaStream_t st);
 cudaError_t launch_load_state(const echr_batch* b, int rows, const int32_t* it, const float* h_in, cudaStream_t st);
-// embedding rows of the next input tokens (from the packed arg-max keys, or row_tok when keys is null) -> columns
-// 0..511 of activation buffer `buf`
-cudaError_t launch_embed_rows(const echr_batch* b, int rows, int buf, const unsigned long long* keys, cudaStream_t st);
 cudaError_t launch_export_state(const echr_batch* b, int rows, float* h_out, cudaStream_t st);
 void count_launch(int n = 1);
 

@@ -1018,34 +1018,6 @@ export_state_kernel(int rows, const bf16* __restrict__ act, long long act_plane,
   }
 }
 
-// Embedding lookup (OldModel_NEW.py:134) as an operand of the gate GEMMs: one warp per decode row copies the 16-bit
-// plane row(s) of embed[token] into the X block of the activation matrix.
-__global__ void __launch_bounds__(256)
-embed_rows_kernel(int rows, const unsigned long long* __restrict__ keys, const int32_t* __restrict__ row_tok,
-                  const bf16* __restrict__ embed, long long embed_plane, int planes, bf16* __restrict__ act, long long act_plane) {
-  pdl_trigger();
-  pdl_wait();
-  const int r = blockIdx.x * 8 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
-  if (r >= rows) return;
-  const int tk = keys != nullptr ? token_of_key(keys[static_cast<long long>(r) * KEY_STRIDE]) : __ldg(row_tok + r);
-  for (int p = 0; p < planes; ++p) {
-    const uint4* src = reinterpret_cast<const uint4*>(embed + p * embed_plane + static_cast<long long>(tk) * HID);
-    uint4* dst = reinterpret_cast<uint4*>(act + p * act_plane + static_cast<long long>(r) * ACT_LD + ACT_X);
-    dst[lane] = __ldg(src + lane);
-    dst[lane + 32] = __ldg(src + lane + 32);
-  }
-}
-
-cudaError_t launch_embed_rows(const echr_batch* b, int rows, int buf, const unsigned long long* keys, cudaStream_t st) {
-  if (rows == 0) return cudaSuccess;
-  const echr_model* m = b->model;
-  const PlaneMat& act = b->act[buf];
-  cudaError_t e = launch_pdl(embed_rows_kernel, dim3((unsigned)((rows + 7) / 8)), dim3(256), 0, st, rows, keys, (const int32_t*)b->row_tok,
-                             (const bf16*)m->embed.p, (long long)m->embed.plane_stride(), (int)act.planes, act.p, (long long)act.plane_stride());
-  count_launch();
-  return e;
-}
-
 cudaError_t launch_load_state(const echr_batch* b, int rows, const int32_t* it, const float* h_in, cudaStream_t st) {
   const echr_model* m = b->model;
   load_state_kernel<<<rows, 128, 0, st>>>(rows, m->V1, it, h_in, b->row_tok, b->act[0].p,
