@@ -240,11 +240,7 @@ class Batch(object):
         return BatchLayout(self.clip_counts, self.ind_lists, self.soi_lists)
 
     def h2d_bytes(self):
-        """Bytes that cross PCIe for one submit of this batch from pinned host buffers: the library reads exactly the c3d
-        rows that lie inside a proposal and tap_feats[ind] (zero-copy kernels over the mapped host tensors), copies lda,
-        the index arrays and the list of covered clips."""
-        cov = self.unique_window_clips()
-        return int(cov * 500 + self.n_events * 512 + self.h[2].numel()) * 4 + int(7 * self.n_events + 2 * self.n_videos + cov) * 4
+        return int(self.h[0].numel() + self.n_events * 512 + self.h[2].numel()) * 4 + int(9 * self.n_events + 2 * self.n_videos) * 4
 
     def unique_window_clips(self):
         """Clips of the batch that lie inside at least one proposal (the attention never reads the others)."""
@@ -505,10 +501,8 @@ def _main(args):
                     "h2d_bytes_per_step": sum(b.h2d_bytes() for b in mine),
                     "d2h_bytes_per_step": int(n_events * S * 8 + (n_events * 4 if beam > 1 else 0)),
                     "ms_per_step": ms_host / args.steps,
-                    "host_input_bytes_per_step": sum(int(b.h[0].numel() + b.h[1].numel() + b.h[2].numel()) * 4 for b in mine),
-                    "note": "per batch: BatchLayout from the python proposal lists; host -> device of the c3d rows inside a proposal, "
-                            "tap_feats[ind], lda and the index arrays (h2d_bytes_per_step: what crosses PCIe; host_input_bytes_per_step: "
-                            "the size of the pinned input tensors the call is given); encode, decode, D2H of tokens + log-probs; bytes are rank 0's"},
+                    "note": "per batch: BatchLayout from the python proposal lists, H2D of c3d / gathered proposal states / lda / "
+                            "index arrays, encode, decode, D2H of tokens + log-probs; bytes are rank 0's"},
             "gpu_launches": int(launches),
             "gathered_equals_single_gpu": gathered_ok if world > 1 else "n/a (one rank: nothing is gathered)",
             "roofline": roofline}

@@ -368,7 +368,6 @@ static void batch_layout(echr_batch* b, Arena& a) {
   b->ev_n = ints + 6 * c.max_events;
   b->vid_first = ints + 7 * c.max_events;
   b->vid_n = b->vid_first + c.max_videos;
-  b->cov_idx = a.take<int32_t>(c.max_clips);
   b->clip_pl = a.planes(ap, c.max_clips, CLIP_PAD);
   b->proj_f32 = a.take<float>((size_t)c.max_clips * HID);
   b->proj_h = ap == 1 ? a.take<bf16>((size_t)c.max_clips * HID) : nullptr;
@@ -429,18 +428,10 @@ extern "C" int echr_batch_create(const echr_model_t* model, const echr_capacity_
                      2 * sizeof(int32_t) * ((size_t)7 * cap->max_events + 2 * cap->max_videos));
   if (e == cudaSuccess)
     e = cudaMallocHost(reinterpret_cast<void**>(&b->host_tap_base), 2 * sizeof(float) * (size_t)cap->max_events * HID);
-  if (e == cudaSuccess)
-    e = cudaMallocHost(reinterpret_cast<void**>(&b->host_cov_base), 2 * sizeof(int32_t) * (size_t)cap->max_clips);
-  if (e == cudaSuccess) {
-    b->host_marks = static_cast<uint8_t*>(malloc((size_t)cap->max_clips));
-    if (b->host_marks == nullptr) e = cudaErrorMemoryAllocation;
-  }
   for (int i = 0; i < 2 && e == cudaSuccess; ++i) e = cudaEventCreateWithFlags(&b->stage_ev[i], cudaEventDisableTiming);
   if (e != cudaSuccess) {
     if (b->host_stage_base) cudaFreeHost(b->host_stage_base);
     if (b->host_tap_base) cudaFreeHost(b->host_tap_base);
-    if (b->host_cov_base) cudaFreeHost(b->host_cov_base);
-    free(b->host_marks);
     cudaFree(b->arena);
     delete b;
     return set_error(ECHR_ERR_CUDA, "echr_batch_create: pinned staging allocation failed: %s", cudaGetErrorString(e));
@@ -454,8 +445,6 @@ extern "C" int echr_batch_create(const echr_model_t* model, const echr_capacity_
   if (e != cudaSuccess) {
     cudaFreeHost(b->host_stage_base);
     cudaFreeHost(b->host_tap_base);
-    cudaFreeHost(b->host_cov_base);
-    free(b->host_marks);
     cudaFree(b->arena);
     delete b;
     return set_error(ECHR_ERR_CUDA, "echr_batch_create: cudaMemset failed: %s", cudaGetErrorString(e));
@@ -476,8 +465,6 @@ extern "C" int echr_batch_destroy(echr_batch_t* b) {
   }
   cudaFreeHost(b->host_stage_base);
   cudaFreeHost(b->host_tap_base);
-  cudaFreeHost(b->host_cov_base);
-  free(b->host_marks);
   for (int i = 0; i < 2; ++i)
     if (b->stage_ev[i]) cudaEventDestroy(b->stage_ev[i]);
   cudaFree(b->nll_logits);
@@ -506,9 +493,6 @@ static int stage_desc(echr_batch_t* b, const echr_batch_desc_t* d, bool check_cl
   const int64_t E = b->cap.max_events;
   b->host_stage = b->host_stage_base + (size_t)b->stage_idx * ((size_t)7 * E + 2 * b->cap.max_videos);
   b->host_tap_stage = b->host_tap_base + (size_t)b->stage_idx * (size_t)E * HID;
-  b->host_cov = b->host_cov_base + (size_t)b->stage_idx * (size_t)b->cap.max_clips;
-  const bool mark = check_clips && n_clips <= b->cap.max_clips;
-  if (mark) memset(b->host_marks, 0, (size_t)n_clips);
   int32_t* hs = b->host_stage;
   int32_t* vid_first = hs + 7 * E;
   int32_t* vid_n = vid_first + b->cap.max_videos;
@@ -532,7 +516,6 @@ static int stage_desc(echr_batch_t* b, const echr_batch_desc_t* d, bool check_cl
     hs[2 * E + i] = e - s;
     if (e - s > max_len) max_len = e - s;
     sum_len += e - s;
-    if (mark) memset(b->host_marks + off[v] + s, 1, (size_t)(e - s));
     hs[3 * E + i] = off[v] + ind;
   }
   long long pairs = 0;
@@ -557,10 +540,6 @@ static int stage_desc(echr_batch_t* b, const echr_batch_desc_t* d, bool check_cl
   b->max_n = max_n;
   b->max_len = max_len;
   b->mean_len = d->n_events > 0 ? (int)((sum_len + d->n_events - 1) / d->n_events) : 0;
-  b->n_cov = 0;
-  if (mark)
-    for (int c = 0; c < n_clips; ++c)
-      if (b->host_marks[c]) b->host_cov[b->n_cov++] = c;
   b->encoded = false;
   ECHR_CUDA(cudaMemcpyAsync(b->ev_video, hs, sizeof(int32_t) * ((size_t)7 * E + 2 * b->cap.max_videos),
                             cudaMemcpyHostToDevice, st));
@@ -577,42 +556,19 @@ extern "C" int echr_batch_set_inputs(echr_batch_t* b, const echr_batch_desc_t* d
   const int64_t E = b->cap.max_events;
   const int32_t* hs = b->host_stage;
   const cudaMemcpyKind kind = on_host ? cudaMemcpyHostToDevice : cudaMemcpyDeviceToDevice;
-  // Host inputs in PINNED memory are mapped into the device address space (UVA): the kernels below read exactly
-  // the rows the path needs over PCIe — the clips inside at least one proposal, tap_feats[ind] — instead of copying
-  // whole tensors.  Pageable host memory takes the cudaMemcpy path.
-  const float* c3d_dev = nullptr;
-  const float* tap_dev = nullptr;
+  ECHR_CUDA(cudaMemcpyAsync(b->c3d, c3d, sizeof(float) * (size_t)n_clips * ECHR_VIDEO_DIM, kind, st));
+  // only tap_feats[ind] is ever read (CaptionGenerator.py:121): gather one row per event
   if (on_host) {
-    cudaPointerAttributes pa, pt;
-    if (cudaPointerGetAttributes(&pa, c3d) == cudaSuccess && pa.type == cudaMemoryTypeHost && pa.devicePointer != nullptr &&
-        cudaPointerGetAttributes(&pt, tap) == cudaSuccess && pt.type == cudaMemoryTypeHost && pt.devicePointer != nullptr) {
-      c3d_dev = static_cast<const float*>(pa.devicePointer);
-      tap_dev = static_cast<const float*>(pt.devicePointer);
-    }
-    cudaGetLastError();  // (an unregistered pointer may leave a sticky-free error code behind)
-  }
-  if (c3d_dev != nullptr) {
-    if (b->n_cov > 0) {
-      ECHR_CUDA(cudaMemcpyAsync(b->cov_idx, b->host_cov, sizeof(int32_t) * (size_t)b->n_cov, cudaMemcpyHostToDevice, st));
+    for (int i = 0; i < d->n_events; ++i)
+      memcpy(b->host_tap_stage + (size_t)i * HID, tap + (size_t)hs[3 * E + i] * HID, sizeof(float) * HID);
+    if (d->n_events > 0)
+    {
+      ECHR_CUDA(cudaMemcpyAsync(b->tap, b->host_tap_stage, sizeof(float) * (size_t)d->n_events * HID,
+                                cudaMemcpyHostToDevice, st));
       ECHR_CUDA(cudaEventRecord(b->stage_ev[b->stage_idx], st));
-      ECHR_CUDA(launch_gather_clips(b, c3d_dev, st));
     }
-    if (d->n_events > 0) ECHR_CUDA(launch_gather_tap(b, tap_dev, st));
   } else {
-    ECHR_CUDA(cudaMemcpyAsync(b->c3d, c3d, sizeof(float) * (size_t)n_clips * ECHR_VIDEO_DIM, kind, st));
-    // only tap_feats[ind] is ever read (CaptionGenerator.py:121): gather one row per event
-    if (on_host) {
-      for (int i = 0; i < d->n_events; ++i)
-        memcpy(b->host_tap_stage + (size_t)i * HID, tap + (size_t)hs[3 * E + i] * HID, sizeof(float) * HID);
-      if (d->n_events > 0)
-      {
-        ECHR_CUDA(cudaMemcpyAsync(b->tap, b->host_tap_stage, sizeof(float) * (size_t)d->n_events * HID,
-                                  cudaMemcpyHostToDevice, st));
-        ECHR_CUDA(cudaEventRecord(b->stage_ev[b->stage_idx], st));
-      }
-    } else {
-      ECHR_CUDA(launch_gather_tap(b, tap, st));
-    }
+    ECHR_CUDA(launch_gather_tap(b, tap, st));
   }
   ECHR_CUDA(cudaMemcpyAsync(b->lda, lda, sizeof(float) * (size_t)d->n_videos * ECHR_LDA_DIM, kind, st));
   return ECHR_OK;

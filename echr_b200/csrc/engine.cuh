@@ -84,13 +84,6 @@ struct echr_batch {
   int32_t* host_stage_base;
   cudaEvent_t stage_ev[2];
   int stage_idx;
-  // clips that lie inside at least one proposal (nothing else of c3d is ever read): host marks + pinned index
-  // list (double-buffered like the other staging areas) + its device copy; n_cov = entries of the current batch
-  uint8_t* host_marks;
-  int32_t* host_cov_base;
-  int32_t* host_cov;
-  int32_t* cov_idx;
-  int n_cov;
   // per-event int arrays on device: video, first clip (global), length, ind (global), pair row
   // offset, first event of the video, events in the video
   int32_t *ev_video, *ev_start, *ev_len, *ev_ind, *ev_pair_off, *ev_first, *ev_n;
@@ -170,7 +163,6 @@ cudaError_t launch_split(const float* src, int64_t rows, int64_t cols, int64_t l
                          bf16* lo, int64_t ld_dst, int64_t cols_dst, bool f16, cudaStream_t st);
 cudaError_t launch_event_feats(const echr_batch* b, cudaStream_t st);
 cudaError_t launch_gather_tap(const echr_batch* b, const float* tap_src, cudaStream_t st);
-cudaError_t launch_gather_clips(const echr_batch* b, const float* c3d_src, cudaStream_t st);
 cudaError_t launch_relation_attn(const echr_batch* b, cudaStream_t st);
 // ---- pair_mlp.cu: position embedding -> fc1 + tanh -> fc2 fused over tiles of 128 event pairs
 int launch_pair_mlp(const echr_batch* b, cudaStream_t st);

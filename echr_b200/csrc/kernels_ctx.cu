@@ -116,34 +116,6 @@ gather_tap_kernel(const float* __restrict__ tap_src, const int32_t* __restrict__
   reinterpret_cast<float4*>(dst + (long long)e * HID)[threadIdx.x] = __ldg(src + threadIdx.x);
 }
 
-// c3d rows of the clips that lie inside at least one proposal, from the caller's [clips,500] tensor into the
-// workspace copy at the same row index.  The source may be PINNED HOST memory (mapped into the device address space
-// under UVA): the rows are then read over PCIe by this kernel instead of a cudaMemcpy of the whole tensor — the
-// attention, the span mean and the ctx2att projection never look at a clip outside every proposal (36 % of the
-// clips of the GT-style workloads), so those bytes do not have to cross the bus.  One warp per clip row.
-__global__ void __launch_bounds__(256)
-gather_clips_kernel(const float* __restrict__ src, const int32_t* __restrict__ idx, int n, float* __restrict__ dst) {
-  const int i = blockIdx.x * 8 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
-  if (i >= n) return;
-  const long long row = static_cast<long long>(idx[i]) * ECHR_VIDEO_DIM;  // 2000-byte rows: 16-byte aligned
-  const float4* s4 = reinterpret_cast<const float4*>(src + row);
-  float4* d4 = reinterpret_cast<float4*>(dst + row);
-  float4 v[4];
-#pragma unroll
-  for (int k = 0; k < 4; ++k)
-    if (lane + 32 * k < ECHR_VIDEO_DIM / 4) v[k] = s4[lane + 32 * k];
-#pragma unroll
-  for (int k = 0; k < 4; ++k)
-    if (lane + 32 * k < ECHR_VIDEO_DIM / 4) d4[lane + 32 * k] = v[k];
-}
-
-cudaError_t launch_gather_clips(const echr_batch* b, const float* c3d_src, cudaStream_t st) {
-  if (b->n_cov == 0) return cudaSuccess;
-  gather_clips_kernel<<<(b->n_cov + 7) / 8, 256, 0, st>>>(c3d_src, b->cov_idx, b->n_cov, b->c3d);
-  count_launch();
-  return cudaGetLastError();
-}
-
 cudaError_t launch_gather_tap(const echr_batch* b, const float* tap_src, cudaStream_t st) {
   if (b->n_events == 0) return cudaSuccess;
   gather_tap_kernel<<<b->n_events, 128, 0, st>>>(tap_src, b->ev_ind, b->tap);
