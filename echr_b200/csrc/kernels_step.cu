@@ -585,16 +585,20 @@ attention_f16_kernel(const __grid_constant__ AttF16Params P, unsigned long long*
   const int s0 = __ldg(P.row_start + r);
   const int L = __ldg(P.row_len + r);
   const int n_mine = L > warp ? (L - warp + ATR_WARPS - 1) / ATR_WARPS : 0;  // clips warp, warp + 8, ...
-  auto issue = [&](int i) {  // lane 0: bring this warp's i-th clip into slot i % ATR_SLOTS
-    const uint32_t dst = ring + (i % ATR_SLOTS) * ATR_SLOT_BYTES;
-    const uint32_t bar = bars + 8u * (i % ATR_SLOTS);
+  // this warp's clips: table / clip rows (s0 + warp + i W), i = 0 .. n_mine - 1
+  const __nv_bfloat16* pbase = P.proj + static_cast<long long>(s0 + warp) * 512;
+  const __nv_bfloat16* cbase = P.clip + static_cast<long long>(s0 + warp) * 512;
+  const float* sbase = P.proj_scale + s0 + warp;
+  auto issue = [&](int i, int slot) {  // lane 0: bring this warp's i-th clip into `slot`
+    const uint32_t dst = ring + slot * ATR_SLOT_BYTES;
+    const uint32_t bar = bars + 8u * slot;
     mbar_arrive_expect_tx(bar, ATR_SLOT_BYTES);
-    const long long row = static_cast<long long>(s0 + warp + i * ATR_WARPS) * 512;
-    bulk_load_1d(dst, P.proj + row, 1024, bar);
-    bulk_load_1d(dst + 1024, P.clip + row, 1024, bar);
+    const long long off = static_cast<long long>(i) * (ATR_WARPS * 512);
+    bulk_load_1d(dst, pbase + off, 1024, bar);
+    bulk_load_1d(dst + 1024, cbase + off, 1024, bar);
   };
   if (lane == 0)
-    for (int i = 0; i < ATR_SLOTS && i < n_mine; ++i) issue(i);
+    for (int i = 0; i < ATR_SLOTS && i < n_mine; ++i) issue(i, i);
   // (everything below is loaded while the first copies are in flight: the row's dependent chain is
   //  window descriptor -> copies -> compute -> merge, nothing else)
   // lane's hidden units / clip columns: [8 lane + 256 m, +8), m = 0, 1 (16-byte chunks lane and lane + 32 of a row)
@@ -615,62 +619,70 @@ attention_f16_kernel(const __grid_constant__ AttF16Params P, unsigned long long*
     qe[8 * m + 0] = q0.x; qe[8 * m + 1] = q0.y; qe[8 * m + 2] = q0.z; qe[8 * m + 3] = q0.w;
     qe[8 * m + 4] = q1.x; qe[8 * m + 5] = q1.y; qe[8 * m + 6] = q1.z; qe[8 * m + 7] = q1.w;
   }
-  float sc_next = n_mine > 0 ? __ldg(P.proj_scale + s0 + warp) : 0.f;
+  // 1 / S of the warp's next clip (S = e^{2 rowmax P}): e^{2x} + 1 = S (E q + 1/S), so the per-clip scale enters the
+  // FFMA that forms the denominator and multiplies the clip's score once, instead of every element
+  auto rcp_fast = [](float x) { float y; asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x)); return y; };
+  float is_next = n_mine > 0 ? rcp_fast(__ldg(sbase)) : 0.f;
   float mx = -INFINITY, sum = 0.f;
   float acc[16];
 #pragma unroll
   for (int i = 0; i < 16; ++i) acc[i] = 0.f;
-  for (int i = 0; i < n_mine; ++i) {
-    const float sc = sc_next;
-    if (i + 1 < n_mine) sc_next = __ldg(P.proj_scale + s0 + warp + (i + 1) * ATR_WARPS);
-    mbar_wait(bars + 8u * (i % ATR_SLOTS), (i / ATR_SLOTS) & 1u);
-    const uint32_t sp = ring + (i % ATR_SLOTS) * ATR_SLOT_BYTES;
-    uint4 pu[2], cu[2];
+  // slots are walked round robin, so the loop is unrolled by the ring depth: slot and barrier addresses are constants
+  for (int base = 0; base < n_mine; base += ATR_SLOTS) {
+    const uint32_t parity = (base / ATR_SLOTS) & 1u;
 #pragma unroll
-    for (int m = 0; m < 2; ++m) {
-      asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(pu[m].x), "=r"(pu[m].y), "=r"(pu[m].z), "=r"(pu[m].w)
-                   : "r"(sp + 16u * (lane + 32 * m)));
-      asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(cu[m].x), "=r"(cu[m].y), "=r"(cu[m].z), "=r"(cu[m].w)
-                   : "r"(sp + 1024u + 16u * (lane + 32 * m)));
-    }
-    __syncwarp();  // every lane holds its part of the slot in registers: refill it
-    if (lane == 0 && i + ATR_SLOTS < n_mine) {
-      fence_proxy_async_smem();  // the lanes' generic reads before the async-proxy write
-      issue(i + ATR_SLOTS);
-    }
-    float s = 0.f;
+    for (int slot = 0; slot < ATR_SLOTS; ++slot) {
+      const int i = base + slot;
+      if (i >= n_mine) break;
+      const float inv_s = is_next;
+      if (i + 1 < n_mine) is_next = rcp_fast(__ldg(sbase + (i + 1) * ATR_WARPS));
+      mbar_wait(bars + 8u * slot, parity);
+      const uint32_t sp = ring + slot * ATR_SLOT_BYTES;
+      uint4 pu[2], cu[2];
 #pragma unroll
-    for (int m = 0; m < 2; ++m) {
-      const uint32_t w4[4] = {pu[m].x, pu[m].y, pu[m].z, pu[m].w};
-#pragma unroll
-      for (int j = 0; j < 4; ++j) {
-        const float2 e2 = f16x2_value(w4[j]);
-        float r0, r1;
-        asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r0) : "f"(fmaf(e2.x * sc, qe[8 * m + 2 * j], 1.0f)));
-        asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r1) : "f"(fmaf(e2.y * sc, qe[8 * m + 2 * j + 1], 1.0f)));
-        s = fmaf(av[8 * m + 2 * j], r0, s);
-        s = fmaf(av[8 * m + 2 * j + 1], r1, s);
+      for (int m = 0; m < 2; ++m) {
+        asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(pu[m].x), "=r"(pu[m].y), "=r"(pu[m].z), "=r"(pu[m].w)
+                     : "r"(sp + 16u * (lane + 32 * m)));
+        asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(cu[m].x), "=r"(cu[m].y), "=r"(cu[m].z), "=r"(cu[m].w)
+                     : "r"(sp + 1024u + 16u * (lane + 32 * m)));
       }
-    }
-    s = warp_sum(s);
-    if (s > mx) {  // (warp-uniform) the running maximum moves: rescale what has been accumulated — O(log n) times per row
-      const float corr = exp2f((mx - s) * L2E);  // exp2(-inf) = 0 on the warp's first clip
-      sum *= corr;
+      float s = 0.f;
 #pragma unroll
-      for (int i2 = 0; i2 < 16; ++i2) acc[i2] *= corr;
-      mx = s;
-    }
-    const float p = exp2f((s - mx) * L2E);
-    sum += p;
+      for (int m = 0; m < 2; ++m) {
+        const uint32_t w4[4] = {pu[m].x, pu[m].y, pu[m].z, pu[m].w};
 #pragma unroll
-    for (int m = 0; m < 2; ++m) {
-      const uint32_t w4[4] = {cu[m].x, cu[m].y, cu[m].z, cu[m].w};
-#pragma unroll
-      for (int j = 0; j < 4; ++j) {
-        const float2 c2 = f16x2_value(w4[j]);
-        acc[8 * m + 2 * j] = fmaf(p, c2.x, acc[8 * m + 2 * j]);
-        acc[8 * m + 2 * j + 1] = fmaf(p, c2.y, acc[8 * m + 2 * j + 1]);
+        for (int j = 0; j < 4; ++j) {
+          const float2 e2 = f16x2_value(w4[j]);
+          s = fmaf(av[8 * m + 2 * j], rcp_fast(fmaf(e2.x, qe[8 * m + 2 * j], inv_s)), s);
+          s = fmaf(av[8 * m + 2 * j + 1], rcp_fast(fmaf(e2.y, qe[8 * m + 2 * j + 1], inv_s)), s);
+        }
       }
+      s = warp_sum(s) * inv_s;
+      if (s > mx) {  // (warp-uniform) the running maximum moves: rescale what has been accumulated — O(log n) times per row
+        float corr;
+        asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(corr) : "f"((mx - s) * L2E));  // ex2(-inf) = 0 on the warp's first clip
+        sum *= corr;
+#pragma unroll
+        for (int i2 = 0; i2 < 16; ++i2) acc[i2] *= corr;
+        mx = s;
+      }
+      float p;
+      asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(p) : "f"((s - mx) * L2E));
+      sum += p;
+#pragma unroll
+      for (int m = 0; m < 2; ++m) {
+        const uint32_t w4[4] = {cu[m].x, cu[m].y, cu[m].z, cu[m].w};
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          const float2 c2 = f16x2_value(w4[j]);
+          acc[8 * m + 2 * j] = fmaf(p, c2.x, acc[8 * m + 2 * j]);
+          acc[8 * m + 2 * j + 1] = fmaf(p, c2.y, acc[8 * m + 2 * j + 1]);
+        }
+      }
+      // refill the slot: every lane's reads of it have been consumed by the arithmetic above (and __syncwarp orders
+      // the lanes), so the copy can only land after them
+      __syncwarp();
+      if (lane == 0 && i + ATR_SLOTS < n_mine) issue(i + ATR_SLOTS, slot);
     }
   }
   // ---- merge the eight warps' (max, sum, weighted sum): att = sum_w e^{m_w - M} acc_w / sum_w e^{m_w - M} sum_w
