@@ -61,16 +61,16 @@ int echr_attention_step(const float* q, const void* proj, const void* clip, int6
   return ECHR_OK;
 }
 
-int echr_attention_step_f16(const float* q_exp, const void* proj16, const float* proj_scale, const void* clip16, const float* alpha,
+int echr_attention_step_f16(const float* q_exp, const void* tab16, const float* proj_scale, const float* alpha,
                             const int32_t* row_start, const int32_t* row_len, int64_t rows, float* out_f32,
                             void* out16, int64_t ld_out, int mean_len, void* stream) {
-  ECHR_REQUIRE(q_exp && proj16 && proj_scale && clip16 && alpha && row_start && row_len, "echr_attention_step_f16: null pointer");
+  ECHR_REQUIRE(q_exp && tab16 && proj_scale && alpha && row_start && row_len, "echr_attention_step_f16: null pointer");
   ECHR_REQUIRE(rows >= 0 && rows < (1ll << 31), "echr_attention_step_f16: bad row count");
-  ECHR_REQUIRE(((uintptr_t)proj16 & 15) == 0 && ((uintptr_t)clip16 & 15) == 0, "echr_attention_step_f16: tables must be 16-byte aligned");
+  ECHR_REQUIRE(((uintptr_t)tab16 & 15) == 0, "echr_attention_step_f16: the table must be 16-byte aligned");
   ECHR_REQUIRE(out16 == nullptr || (ld_out >= 512 && ld_out % 8 == 0 && ((uintptr_t)out16 & 15) == 0),
                "echr_attention_step_f16: out16 rows must be 16-byte aligned and >= 512 wide");
   AttF16Params P;
-  P.q_exp = q_exp; P.proj = (const bf16*)proj16; P.proj_scale = proj_scale; P.clip = (const bf16*)clip16; P.alpha = alpha;
+  P.q_exp = q_exp; P.tab = (const bf16*)tab16; P.proj_scale = proj_scale; P.alpha = alpha;
   P.row_start = row_start; P.row_len = row_len; P.rows = (int)rows;
   P.out = (bf16*)out16; P.ld_out = ld_out; P.out_f32 = out_f32;
   ECHR_CUDA(launch_attention_f16(P, mean_len, (cudaStream_t)stream));

@@ -8,16 +8,19 @@
 // Tables (written once per batch by the encoder).  tanh(x) = 1 - 2 / (e^{2x} + 1) and e^{2(P+q)} = e^{2P} e^{2q}, so
 // with the projection stored in the exponential domain a score element costs ONE special-function operation (the
 // reciprocal) instead of two.  e^{2P} does not fit fp16 as it is, so every clip row is stored relative to its own
-// maximum: E_lk = e^{2 (P_lk - m_l)} in (0, 1] as fp16 [clips,512] plus S_l = e^{2 m_l} as fp32 [clips];
+// maximum: E_lk = e^{2 (P_lk - m_l)} in (0, 1] as fp16 plus S_l = e^{2 m_l} as fp32 [clips];
 // e^{2(P+q)} = (E_lk S_l) e^{2 q_k}, the last factor coming from the h2att GEMM epilogue.  The fp16 rounding of E
 // (2^-12 relative) moves tanh by at most 1.3e-4; entries more than 8 below the row maximum flush towards 0, where
 // tanh = -1 to within e^{2(P+q)} itself.  No clamp is needed on the product: inf gives rcp -> 0, tanh = 1.
 //
+// Layout.  The table row and the fp16 clip features of a clip sit side by side, tab[clip] = [E (512) | clip (512)]
+// (2 KB: the clip half is at the same time the A operand of the ctx2att GEMM, row stride 1024), so ONE bulk copy
+// brings everything the step needs of a clip: the copy engine's cost is per request, not per byte, at this size.
+//
 // Schedule.  One CTA of W warps per decode row; warp w owns clips w, w+W, ... of the window and folds them into an
 // online softmax (running max / sum / weighted feature sum, rescaled when the max moves); the W partial states are
 // merged through shared memory at the end.  Every warp keeps a PRIVATE four-slot ring in shared memory that its
-// lane 0 fills with cp.async.bulk (one slot = the 1 KB table row + the 1 KB clip row of one clip, two copies on one
-// mbarrier) up to four clips ahead: 24 warps x 8 KB of HBM/L2 reads in flight per SM with no register held for
+// lane 0 fills with cp.async.bulk (one slot = the 2 KB of one clip, one copy, one mbarrier) up to four clips ahead: 24 warps x 8 KB of HBM/L2 reads in flight per SM with no register held for
 // them and no block-wide barrier inside a row.  Every byte of a window is read exactly once: no score buffer (so no
 // bound on the window length), no second pass over the clip rows.
 // W is chosen per launch: a row costs ~3 us of dependent latency (window descriptor -> first copies -> merge)
@@ -36,9 +39,8 @@ constexpr int atr_smem(int warps) { return warps * ATR_WARP_BYTES + 512; }   // 
 
 struct AttF16Params {
   const float* q_exp;            // [rows, 512] fp32: e^{2 (h2att(h1) + b)}
-  const __nv_bfloat16* proj;     // [clips, 512] fp16 bits: E = e^{2 (P - rowmax P)}
+  const __nv_bfloat16* tab;      // [clips, 1024] fp16 bits: E = e^{2 (P - rowmax P)} (512) | clip features (500, zero padded)
   const float* proj_scale;       // [clips] fp32: S = e^{2 rowmax P}
-  const __nv_bfloat16* clip;     // [clips, 512] fp16 bits, columns 500..511 zero
   const float* alpha;            // [512]
   const int32_t* row_start;      // [rows] first clip of the row's window
   const int32_t* row_len;        // [rows] clips in the window

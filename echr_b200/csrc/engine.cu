@@ -368,9 +368,15 @@ static void batch_layout(echr_batch* b, Arena& a) {
   b->ev_n = ints + 6 * c.max_events;
   b->vid_first = ints + 7 * c.max_events;
   b->vid_n = b->vid_first + c.max_videos;
-  b->clip_pl = a.planes(ap, c.max_clips, CLIP_PAD);
+  if (ap == 1) {  // clip plane = right half of the attention table rows
+    b->proj_h = a.take<bf16>((size_t)c.max_clips * 2 * HID);
+    b->clip_pl.p = b->proj_h ? b->proj_h + HID : nullptr;
+    b->clip_pl.rows = c.max_clips; b->clip_pl.ld = 2 * HID; b->clip_pl.planes = 1; b->clip_pl.stride = 0;
+  } else {
+    b->proj_h = nullptr;
+    b->clip_pl = a.planes(ap, c.max_clips, CLIP_PAD);
+  }
   b->proj_f32 = a.take<float>((size_t)c.max_clips * HID);
-  b->proj_h = ap == 1 ? a.take<bf16>((size_t)c.max_clips * HID) : nullptr;
   b->proj_scale = ap == 1 ? a.take<float>((size_t)c.max_clips) : nullptr;
 
   b->feat_pl = a.planes(ap, c.max_events, FEAT_PAD);
@@ -658,7 +664,7 @@ static int encode_clips(echr_batch_t* b, cudaStream_t st) {
   const echr_model* m = b->model;
   const int at = m->cfg.a_terms, wt = m->cfg.w_terms;
   ECHR_CUDA(launch_split(b->c3d, b->n_clips, ECHR_VIDEO_DIM, ECHR_VIDEO_DIM, b->clip_pl.plane(0),
-                         at > 1 ? b->clip_pl.plane(1) : nullptr, CLIP_PAD, CLIP_PAD, at == 1, st));
+                         at > 1 ? b->clip_pl.plane(1) : nullptr, b->clip_pl.ld, CLIP_PAD, at == 1, st));
   GemmSpec s;
   s.A = &b->clip_pl; s.M = b->n_clips; s.W = &m->w_ctx2att; s.N = HID; s.K = CLIP_PAD;
   s.bias = m->b_ctx2att;
@@ -666,7 +672,7 @@ static int encode_clips(echr_batch_t* b, cudaStream_t st) {
   s.out_f32 = b->proj_f32; s.ld_f32 = HID;
   if (at != 1) s.act = ACT_EXP2X;
   ECHR_TRY(run_gemm(&s, 1, at, wt, 128, EPI_STORE, 1, st, "ctx2att"));
-  if (at == 1) ECHR_CUDA(launch_attention_table(b->proj_f32, b->n_clips, b->proj_h, b->proj_scale, st));
+  if (at == 1) ECHR_CUDA(launch_attention_table(b->proj_f32, b->n_clips, b->proj_h, 2 * HID, b->proj_scale, st));
   return ECHR_OK;
 }
 
@@ -855,9 +861,8 @@ enum { PART_H2ATT = 1, PART_ATT = 2, PART_GATES = 4, PART_LOGIT = 8, PART_ALL = 
 static AttF16Params attention_params(const echr_batch* b, int rows, int t) {
   AttF16Params ap;
   ap.q_exp = b->q_att;
-  ap.proj = b->proj_h;
+  ap.tab = b->proj_h;
   ap.proj_scale = b->proj_scale;
-  ap.clip = b->clip_pl.plane(0);
   ap.alpha = b->model->alpha;
   ap.row_start = b->row_start;
   ap.row_len = b->row_len;

@@ -90,9 +90,10 @@ struct echr_batch {
   int32_t *vid_first, *vid_n;  // per video: first event, number of events
   int32_t* host_stage;  // pinned staging for the arrays above
   // encode workspace
-  echr::PlaneMat clip_pl;   // [clips, 512]   c3d planes (A of ctx2att; plane 0 doubles as bf16 clip)
+  echr::PlaneMat clip_pl;   // [clips, 512]   c3d planes (A of ctx2att).  Single-plane precision: a view into the
+                            // attention table [clips, 1024] = [e^{2 (P - rowmax)} | clip], row stride 1024
   float* proj_f32;          // [clips, 512]   two-plane precisions: e^{2P}, P = ctx2att(c3d)+b; single-plane: P (scratch)
-  echr::bf16* proj_h;       // [clips, 512]   single-plane precision: e^{2 (P - rowmax P)} as fp16 (attention_f16.cuh)
+  echr::bf16* proj_h;       // [clips, 1024]  single-plane precision: the attention table (attention_f16.cuh)
   float* proj_scale;        // [clips]        single-plane precision: e^{2 rowmax P}
   echr::PlaneMat feat_pl;   // [events, 1024] (mean c3d | tap[ind])
   echr::PlaneMat x_pl;      // [events, 512]  event_emb output
@@ -173,7 +174,7 @@ cudaError_t launch_attention(const float* q, const void* proj, const void* clip,
                              bf16* out_lo, int64_t ld_bf, cudaStream_t st, int max_len = 0,
                              unsigned long long* trace = nullptr, int trace_slot = 0);
 cudaError_t launch_attention_f16(const AttF16Params& P, int mean_len, cudaStream_t st, unsigned long long* trace = nullptr, int trace_slot = 0);
-cudaError_t launch_attention_table(const float* proj, int clips, bf16* table, float* scale, cudaStream_t st);
+cudaError_t launch_attention_table(const float* proj, int clips, bf16* table, long long ld, float* scale, cudaStream_t st);
 cudaError_t launch_decode_init(const echr_batch* b, int beam, cudaStream_t st);
 cudaError_t launch_finalize_greedy(echr_batch* b, int step, int32_t* tokens, float* logp,
                                    cudaStream_t st, bool keys = false);

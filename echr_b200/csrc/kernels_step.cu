@@ -586,16 +586,13 @@ attention_f16_kernel(const __grid_constant__ AttF16Params P, unsigned long long*
   const int L = __ldg(P.row_len + r);
   const int n_mine = L > warp ? (L - warp + ATR_WARPS - 1) / ATR_WARPS : 0;  // clips warp, warp + 8, ...
   // this warp's clips: table / clip rows (s0 + warp + i W), i = 0 .. n_mine - 1
-  const __nv_bfloat16* pbase = P.proj + static_cast<long long>(s0 + warp) * 512;
-  const __nv_bfloat16* cbase = P.clip + static_cast<long long>(s0 + warp) * 512;
+  const __nv_bfloat16* tbase = P.tab + static_cast<long long>(s0 + warp) * 1024;
   const float* sbase = P.proj_scale + s0 + warp;
   auto issue = [&](int i, int slot) {  // lane 0: bring this warp's i-th clip into `slot`
     const uint32_t dst = ring + slot * ATR_SLOT_BYTES;
     const uint32_t bar = bars + 8u * slot;
     mbar_arrive_expect_tx(bar, ATR_SLOT_BYTES);
-    const long long off = static_cast<long long>(i) * (ATR_WARPS * 512);
-    bulk_load_1d(dst, pbase + off, 1024, bar);
-    bulk_load_1d(dst + 1024, cbase + off, 1024, bar);
+    bulk_load_1d(dst, tbase + static_cast<long long>(i) * (ATR_WARPS * 1024), ATR_SLOT_BYTES, bar);
   };
   if (lane == 0)
     for (int i = 0; i < ATR_SLOTS && i < n_mine; ++i) issue(i, i);
@@ -754,9 +751,9 @@ cudaError_t launch_attention_f16(const AttF16Params& P, int mean_len, cudaStream
 }
 
 // Attention table of the single-plane precision (attention_f16.cuh): one warp per clip row,
-// P fp32 [clips,512] -> E = e^{2 (P - rowmax)} as fp16 and S = e^{2 rowmax} as fp32.
+// P fp32 [clips,512] -> E = e^{2 (P - rowmax)} as fp16 (row stride ld) and S = e^{2 rowmax} as fp32.
 __global__ void __launch_bounds__(256)
-attention_table_kernel(const float* __restrict__ proj, int clips, bf16* __restrict__ table, float* __restrict__ scale) {
+attention_table_kernel(const float* __restrict__ proj, int clips, bf16* __restrict__ table, long long ld, float* __restrict__ scale) {
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int l = blockIdx.x * 8 + warp;
   if (l >= clips) return;
@@ -776,14 +773,14 @@ attention_table_kernel(const float* __restrict__ proj, int clips, bf16* __restri
     __align__(8) bf16 h[4];
 #pragma unroll
     for (int i = 0; i < 4; ++i) h[i] = f16_bits(__expf(2.0f * (v[4 * m + i] - mx)));
-    *reinterpret_cast<uint2*>(table + static_cast<long long>(l) * HID + 128 * m + 4 * lane) = *reinterpret_cast<const uint2*>(h);
+    *reinterpret_cast<uint2*>(table + static_cast<long long>(l) * ld + 128 * m + 4 * lane) = *reinterpret_cast<const uint2*>(h);
   }
   if (lane == 0) scale[l] = __expf(2.0f * fminf(mx, 43.0f));  // (finite for any finite projection)
 }
 
-cudaError_t launch_attention_table(const float* proj, int clips, bf16* table, float* scale, cudaStream_t st) {
+cudaError_t launch_attention_table(const float* proj, int clips, bf16* table, long long ld, float* scale, cudaStream_t st) {
   if (clips == 0) return cudaSuccess;
-  attention_table_kernel<<<(clips + 7) / 8, 256, 0, st>>>(proj, clips, table, scale);
+  attention_table_kernel<<<(clips + 7) / 8, 256, 0, st>>>(proj, clips, table, ld, scale);
   count_launch();
   return cudaGetLastError();
 }

@@ -153,15 +153,16 @@ ECHR_API int echr_attention_step(const float* q_exp, const void* proj_exp, const
                         void* out_lo, int64_t ld_bf, int max_len, void* stream);
 
 /* The same step over 16-bit tables (what the single-plane precision runs; csrc/attention_f16.cuh):
- * q_exp [rows,512] fp32 = e^{2 (h2att(h1) + b)}; proj16 [n_clips,512] fp16 = e^{2 (P - rowmax P)} with
- * P = ctx2att(c3d) + b, proj_scale [n_clips] fp32 = e^{2 rowmax P}; clip16 [n_clips,512] fp16, columns 500..511
- * zero.  One CTA per row; every warp streams its clips through a private shared-memory ring filled by
- * cp.async.bulk and folds them into an online softmax; any window length.
- * out_f32 [rows,500] (may be NULL); out16 [rows, ld_out] fp16 (may be NULL).  mean_len: the average row_len if the
- * caller knows it (launches of many short windows then run 2 or 4 warps per row instead of 8), 0 if unknown. */
-ECHR_API int echr_attention_step_f16(const float* q_exp, const void* proj16, const float* proj_scale, const void* clip16,
-                            const float* alpha, const int32_t* row_start, const int32_t* row_len, int64_t rows,
-                            float* out_f32, void* out16, int64_t ld_out, int mean_len, void* stream);
+ * q_exp [rows,512] fp32 = e^{2 (h2att(h1) + b)}; tab16 [n_clips,1024] fp16, per clip
+ * [ e^{2 (P - rowmax P)} (512) | clip features (500, zero padded to 512) ] with P = ctx2att(c3d) + b;
+ * proj_scale [n_clips] fp32 = e^{2 rowmax P}.  One CTA per row; every warp streams its clips through a private
+ * shared-memory ring filled by cp.async.bulk (one 2 KB copy per clip) and folds them into an online softmax; any
+ * window length.  out_f32 [rows,500] (may be NULL); out16 [rows, ld_out] fp16 (may be NULL).  mean_len: the average
+ * row_len if the caller knows it (launches of many short windows then run 2 or 4 warps per row instead of 8), 0 if
+ * unknown. */
+ECHR_API int echr_attention_step_f16(const float* q_exp, const void* tab16, const float* proj_scale, const float* alpha,
+                            const int32_t* row_start, const int32_t* row_len, int64_t rows, float* out_f32,
+                            void* out16, int64_t ld_out, int mean_len, void* stream);
 
 /* ---- model: packed weights --------------------------------------------------------------- */
 /* Packs the checkpoint into kernel layouts (bf16 planes, gate-interleaved LSTM rows, fused biases).

@@ -93,14 +93,15 @@ def test_attention_step_f16_matches_oracle(rows_mult, mean_len):
         e2x = proj[s:s + l].double() * scale[s:s + l, None].double() * torch.exp(2 * q[i].double())
         sc = ((1 - 2 / (e2x + 1)) @ alpha.double()).float()
         want[i] = torch.softmax(sc, 0) @ c3d[s:s + l]
-    clip_d = torch.zeros(T, 512, dtype=torch.float16, device=DEV)
-    clip_d[:, :500] = c3d.to(DEV).half()
+    tab_d = torch.zeros(T, 1024, dtype=torch.float16, device=DEV)  # per clip [E (512) | clip (500, zero padded)]
+    tab_d[:, :512] = proj.to(DEV)
+    tab_d[:, 512:1012] = c3d.to(DEV).half()
     rs = torch.tensor(starts, dtype=torch.int32, device=DEV)
     rl = torch.tensor(lens, dtype=torch.int32, device=DEV)
     out = torch.full((n, 500), float("nan"), device=DEV)
     out16 = torch.full((n, 512), float("nan"), dtype=torch.float16, device=DEV)
-    q_d, proj_d, alpha_d, scale_d = torch.exp(2 * q).to(DEV), proj.to(DEV).contiguous(), alpha.to(DEV), scale.to(DEV)
-    _lib.check(lib.echr_attention_step_f16(q_d.data_ptr(), proj_d.data_ptr(), scale_d.data_ptr(), clip_d.data_ptr(),
+    q_d, alpha_d, scale_d = torch.exp(2 * q).to(DEV), alpha.to(DEV), scale.to(DEV)
+    _lib.check(lib.echr_attention_step_f16(q_d.data_ptr(), tab_d.data_ptr(), scale_d.data_ptr(),
                                            alpha_d.data_ptr(), rs.data_ptr(), rl.data_ptr(), n, out.data_ptr(),
                                            out16.data_ptr(), 512, mean_len, torch.cuda.current_stream().cuda_stream),
                "attention_f16")  # mean_len picks 8 / 4 / 2 warps per row
