@@ -24,8 +24,10 @@
 // them and no block-wide barrier inside a row.  Every byte of a window is read exactly once: no score buffer (so no
 // bound on the window length), no second pass over the clip rows.
 // W is chosen per launch: a row costs ~3 us of dependent latency (window descriptor -> first copies -> merge)
-// whatever its length, so launches of many short windows run 2 or 4 warps per row and 12 or 6 rows per SM
-// (cfg5: mean window 25 clips), long windows or few rows 8 warps per row (cfg3/cfg4, the latency regime).
+// whatever its length, so a launch with more rows than 2 x SMs runs 4 warps per row and 6 rows per SM (2 and 12 when
+// the mean window is <= 16 clips); launches of few rows (the latency regime) or of unknown windows run 8 warps per row.
+// Measured (us per launch, W = 2 / 4 / 8): 4072 rows, mean window 25: 40.7 / 41.0 / 52.8; 9600 rows, mean 50:
+// - / 88 / 114; 3200 rows, mean 128: - / 95 / 96; 251 rows: 15.9 / 10.0 / 7.7.
 // Algorithmic bytes per event-step: 2052 L + 2048 (e^{2q} in) + 1000 (att out).
 #pragma once
 #include "ptx.cuh"

@@ -743,7 +743,7 @@ cudaError_t launch_attention_f16(const AttF16Params& P, int mean_len, cudaStream
     count_launch();
     return e;
   }
-  if (P.rows <= 2 * num_sms() || mean_len <= 0 || mean_len > 64) e = launch_attention_f16_w<8>(P, st, trace, trace_slot);
+  if (P.rows <= 2 * num_sms() || mean_len <= 0) e = launch_attention_f16_w<8>(P, st, trace, trace_slot);
   else if (mean_len > 16) e = launch_attention_f16_w<4>(P, st, trace, trace_slot);
   else e = launch_attention_f16_w<2>(P, st, trace, trace_slot);
   count_launch();
