@@ -1,5 +1,5 @@
 """Race hunt: replays the same batch many times and compares tokens / log-probs bitwise with the first replay.
-usage: python tools/stress_determinism.py [iters] ; environment switches (ECHR_PDL_MASK, ECHR_KSPLIT, ...) apply."""
+usage: python tools/stress_determinism.py [iters] ; the environment switches (ECHR_PDL_MASK, ECHR_KSPLIT, ...) apply in a DEBUG_KNOBS=1 build only."""
 import os, sys
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch

@@ -1,4 +1,5 @@
-"""Prints the kernel timeline of one decode-graph replay (ECHR_TRACE=1 python tools/trace_decode.py [workload])."""
+"""Prints the kernel timeline of one decode-graph replay (python tools/trace_decode.py [workload]).  Needs the debug build of the
+library (make -C echr_b200/csrc clean && make -C echr_b200/csrc DEBUG_KNOBS=1): the shipped library ignores ECHR_TRACE."""
 import os, sys
 os.environ["ECHR_TRACE"] = "1"
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
