@@ -25,6 +25,10 @@ for name, a, b in (("h2d", d, h), ("d2h", h, d)):
     torch.cuda.synchronize(); print(name, "%.1f GB/s" % (10 * 0.268435456 / (time.perf_counter() - t0)))
 PY
   ;;
+stress)
+  # race hunt in place of compute-sanitizer (closed on this pool): bitwise-identical replays of five batch shapes, greedy and beam
+  timeout 900 python tools/stress_determinism.py 100 f16 > $O/stress_f16.txt 2>&1; echo "exit=$?" >> $O/stress_f16.txt
+  timeout 900 python tools/stress_determinism.py 60 fp32 > $O/stress_fp32.txt 2>&1; echo "exit=$?" >> $O/stress_fp32.txt ;;
 quick)
   timeout 600 python bench.py --steps 10 --no-cpu-baseline --no-second-beam > $O/bench_cfg5.json 2> $O/bench_cfg5.err
   timeout 600 python bench.py --workload cfg2 --batch-videos 64 --no-cpu-baseline --no-second-beam > $O/bench_cfg2.json 2> $O/bench_cfg2.err

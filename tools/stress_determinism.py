@@ -1,5 +1,5 @@
 """Race hunt: replays the same batch many times and compares tokens / log-probs bitwise with the first replay.
-usage: python tools/stress_determinism.py [iters] ; the environment switches (ECHR_PDL_MASK, ECHR_KSPLIT, ...) apply in a DEBUG_KNOBS=1 build only."""
+usage: python tools/stress_determinism.py [iters] [precision = f16] ; the environment switches (ECHR_PDL_MASK, ECHR_KSPLIT, ...) apply in a DEBUG_KNOBS=1 build only."""
 import os, sys
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch
@@ -9,10 +9,11 @@ from echr_b200.config import echr_opt
 from echr_b200.engine import BatchLayout
 
 iters = int(sys.argv[1]) if len(sys.argv) > 1 else 200
+precision = sys.argv[2] if len(sys.argv) > 2 else "f16"
 torch.set_grad_enabled(False)
 opt = echr_opt()
 sd = synth.round_state_dict_bf16(synth.init_state_dict(opt, 0))
-m = CaptionGenerator(opt, precision="bf16w"); m.load_state_dict(sd); m = m.cuda()
+m = CaptionGenerator(opt, precision=precision); m.load_state_dict(sd); m = m.cuda()
 eng = m.engine
 cases = {
     "5ev": [synth.make_video(7, n_events=5, style="gt")],
@@ -21,6 +22,7 @@ cases = {
     "300ev": synth.make_workload("cfg2", n_videos=76)[0],
     "1200ev": synth.make_workload("cfg2", n_videos=300)[0],
 }
+print("precision", precision)
 bad_total = 0
 for name, vids in cases.items():
     lay = BatchLayout([v.c3d_feats.shape[0] for v in vids], [v.ind_select_list for v in vids], [v.soi_select_list for v in vids])
