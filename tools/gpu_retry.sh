@@ -1,0 +1,7 @@
+# usage: bash tools/gpu_retry.sh <log> <gpurun args...>   — retries while the pod answers busy (exit 3)
+LOG=$1; shift
+for i in $(seq 1 40); do
+  /usr/local/graft/bin/gpurun "$@" > $LOG 2>&1; rc=$?
+  if [ $rc -ne 3 ]; then echo "gpurun rc=$rc" >> $LOG; exit $rc; fi
+  sleep 150
+done
