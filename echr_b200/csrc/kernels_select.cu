@@ -384,3 +384,49 @@ extern "C" int echr_rerank_nms(const double* t1, const double* t2, const double*
   ECHR_CUDA(cudaGetLastError());
   return ECHR_OK;
 }
+
+// ---------------------------------------------------------------------------------------------
+// echr_rerank_nms_static: the same kernel with its one-byte-per-proposal "alive" flags in a file-scope
+// device array, for callers that must not allocate (no counterpart in the reference; see echr_b200.h).
+// Every GPU that loads the library holds these ECHR_RERANK_STATIC_MAX bytes until the process exits.
+static __device__ __align__(256) uint8_t g_rerank_alive[ECHR_RERANK_STATIC_MAX];
+
+// In host code `g_rerank_alive` is only a stand-in for the symbol: its device address comes from
+// cudaGetSymbolAddress, asked once per device with that device current.
+static int rerank_static_scratch(uint8_t** out) {
+  static uint8_t* addr[MAX_DEVICES] = {};
+  int dev = -1;
+  ECHR_CUDA(cudaGetDevice(&dev));
+  ECHR_REQUIRE(dev >= 0 && dev < MAX_DEVICES, "echr_rerank_nms_static: device %d out of range", dev);
+  if (addr[dev] == nullptr) {
+    void* p = nullptr;
+    ECHR_CUDA(cudaGetSymbolAddress(&p, g_rerank_alive));
+    ECHR_REQUIRE(p != nullptr, "echr_rerank_nms_static: no device address for the scratch array");
+    addr[dev] = static_cast<uint8_t*>(p);
+  }
+  *out = addr[dev];
+  return ECHR_OK;
+}
+
+extern "C" int echr_rerank_nms_static(const double* t1, const double* t2, const double* prop_scores,
+                                      const double* sent_scores, const int32_t* offsets, int n_videos,
+                                      int64_t total_proposals, double nms_overlap, int topn, int32_t* out_pick,
+                                      int32_t* out_count, int cap, void* stream) {
+  ECHR_REQUIRE(t1 && t2 && prop_scores && sent_scores && offsets && out_pick && out_count,
+               "echr_rerank_nms_static: null pointer");
+  ECHR_REQUIRE(n_videos >= 0 && topn >= 1 && cap >= 0 && total_proposals >= 0, "echr_rerank_nms_static: bad shape");
+  ECHR_REQUIRE(total_proposals <= (int64_t)ECHR_RERANK_STATIC_MAX,
+               "echr_rerank_nms_static: %lld proposals exceed the built-in scratch of %d (ECHR_RERANK_STATIC_MAX); "
+               "use echr_rerank_nms with a caller workspace",
+               (long long)total_proposals, ECHR_RERANK_STATIC_MAX);
+  if (n_videos == 0) return ECHR_OK;
+  uint8_t* alive = nullptr;
+  if (int rc = rerank_static_scratch(&alive); rc != ECHR_OK) return rc;
+  // nothing to clear: the kernel sets the flags of every proposal it owns before reading them
+  const size_t smem = sizeof(RerankCand) * SEL_THREADS;
+  rerank_nms_kernel<<<n_videos, SEL_THREADS, smem, (cudaStream_t)stream>>>(
+      t1, t2, prop_scores, sent_scores, offsets, nms_overlap, topn, alive, out_pick, out_count, cap);
+  count_launch();
+  ECHR_CUDA(cudaGetLastError());
+  return ECHR_OK;
+}

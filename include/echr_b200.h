@@ -320,6 +320,19 @@ ECHR_API int echr_rerank_nms(const double* t1, const double* t2, const double* p
                     const double* sent_scores, const int32_t* offsets, int n_videos, double nms_overlap,
                     int topn, void* workspace, int32_t* out_pick, int32_t* out_count, int cap, void* stream);
 
+/* echr_rerank_nms without a workspace argument and without any allocation, for callers that cannot call
+ * cudaMalloc (code under CUDA-graph capture, tight serving loops, harnesses that forbid it).  It has NO
+ * counterpart in the reference.  The one-byte-per-proposal
+ * flags live in a static device array of ECHR_RERANK_STATIC_MAX bytes inside the library (held by every GPU that
+ * loads it, until exit); total_proposals (= offsets[n_videos], which the caller knows on the host) beyond that
+ * limit is refused with ECHR_ERR_INVALID.  Same inputs, outputs and results as echr_rerank_nms.  All calls on a
+ * device share the array: calls that overlap on the GPU (different streams) race; calls ordered on one stream
+ * do not, and nothing of a previous call's contents is read. */
+#define ECHR_RERANK_STATIC_MAX (1 << 20)
+ECHR_API int echr_rerank_nms_static(const double* t1, const double* t2, const double* prop_scores,
+                    const double* sent_scores, const int32_t* offsets, int n_videos, int64_t total_proposals,
+                    double nms_overlap, int topn, int32_t* out_pick, int32_t* out_count, int cap, void* stream);
+
 /* Measurement aid for bench.py's roofline: average duration in ms of each kernel of one decode step
  * (host_ms[5] = h2att GEMM, attention, LSTM gate GEMM, logit GEMM, finalize), from CUDA events on `stream` around a captured graph of `iters` back-to-back plain launches of that
  * kernel (no host launch gaps, as in the decode graph), with the schedule the batch's decode uses (see
