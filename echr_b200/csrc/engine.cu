@@ -78,6 +78,7 @@ static const char* fill_problem(GemmProblem& pb, const GemmSpec& s, int a_terms,
   pb.N = s.N;
   pb.num_kb = s.K / GEMM_BLOCK_K;
   pb.act = s.act;
+  pb.epi_store = s.epi_store ? 1 : 0;
   pb.ksplit = s.ksplit;
   for (int i = 0; i < pb.num_kb; ++i)
     pb.a_kb[i] = (uint16_t)((s.a_kb ? s.a_kb[i] : s.a_col0 / GEMM_BLOCK_K + i) | (i < s.hi_only_first ? GEMM_KB_HI_ONLY : 0));
@@ -142,6 +143,11 @@ static bool hoist_context(int rows) {
   if (forced >= 0) return forced != 0;
   return rows < gemm2_min_rows();
 }
+// throughput regime: the next step's attention query GEMM rides in the logit launch (ECHR_FUSE_Q=0: own launch)
+static bool fuse_next_query() {
+  static const int v = knob("ECHR_FUSE_Q") ? atoi(knob("ECHR_FUSE_Q")) : 1;
+  return v != 0;
+}
 static int m_tiles_of(int rows) { return (rows + GEMM_BLOCK_M - 1) / GEMM_BLOCK_M; }
 // logit GEMM as 128 x 256 tiles shared by CTA pairs (23 x 2 CTAs per 128 rows at the ECHR vocabulary)
 static bool logit_split(const echr_model* m, int rows) {
@@ -175,6 +181,9 @@ int run_gemm(const GemmSpec* specs, int groups, int a_terms, int w_terms, int bl
     if (gx > grid_x) grid_x = gx;
   }
   const bool two = !any_split && use_gemm2(max_m, min_n, block_n);
+  for (int g = 0; g < groups; ++g)
+    if (specs[g].epi_store && !(two && epi == EPI_LOGITS))
+      return set_error(ECHR_ERR_INVALID, "%s: a store problem rides only in a persistent logit launch", what);
   for (int g = 0; g < groups; ++g) {
     const char* err = fill_problem(P.prob[g], specs[g], a_terms, w_terms, two ? GEMM2_BLOCK_N : block_n);
     if (err) return set_error(ECHR_ERR_CUDA, "%s: %s", what, err);
@@ -854,7 +863,9 @@ static int enqueue_init(echr_batch* b, int beam, cudaStream_t st) {
 // One decode step t: attention query + attention (stream 1 uses the PREVIOUS h1), the three gate
 // GEMMs with the fused LSTM cell update, the vocabulary projection with fused partial
 // log-softmax / top-k.  The caller appends the mode's finalize kernel.
-enum { PART_H2ATT = 1, PART_ATT = 2, PART_GATES = 4, PART_LOGIT = 8, PART_ALL = 15 };
+// PART_NEXT_Q (with PART_LOGIT, persistent kernel only): the attention query GEMM of step t + 1 — it needs this
+// step's h1 and nothing of the token — is a second problem of the logit launch of step t.
+enum { PART_H2ATT = 1, PART_ATT = 2, PART_GATES = 4, PART_LOGIT = 8, PART_ALL = 15, PART_NEXT_Q = 16 };
 
 // Attention of decode step t over the 16-bit tables (single-plane precision): reads the query the h2att GEMM of
 // step t wrote, writes the ATT block of activation buffer t & 1.
@@ -941,14 +952,23 @@ static int enqueue_step(echr_batch* b, int rows, int t, int topk, float* logits_
     ECHR_TRY(run_gemm(s, 3, at, wt, 128, EPI_LSTM, 1, st, "lstm_gates", b, 2));
   }
   if (parts & PART_LOGIT) {
-    GemmSpec s;
+    GemmSpec sv[2];
+    GemmSpec& s = sv[0];
     s.A = &nxt; s.a_col0 = ACT_H; s.M = rows; s.W = &m->w_logit; s.N = m->V1; s.K = 3 * HID;
     s.bias = m->b_logit; s.partial = b->partial; s.logits_out = logits_out; s.ld_logits = ld_logits;
     const bool sp = logit_split(m, rows);
     if (sp) s.ksplit = 2;
     if (use_keys) s.argmax_key = b->argmax_key[t & 1];
+    int groups = 1;
+    if (parts & PART_NEXT_Q) {
+      // the short tiles go last: they fill the tail of the persistent kernel's last round of vocabulary tiles
+      GemmSpec& q = sv[1];
+      q.A = &nxt; q.a_col0 = ACT_H + HID; q.M = rows; q.W = &m->w_h2att; q.N = HID; q.K = HID;
+      q.bias = m->b_h2att; q.act = ACT_EXP2X; q.out_f32 = b->q_att; q.ld_f32 = HID; q.epi_store = true;
+      groups = 2;
+    }
     PdlScope pdl(PDL_LOGIT);
-    ECHR_TRY(run_gemm(&s, 1, at, wt, sp ? 256 : 128, EPI_LOGITS, topk, st, "logit", b, 3));
+    ECHR_TRY(run_gemm(sv, groups, at, wt, sp ? 256 : 128, EPI_LOGITS, topk, st, "logit", b, 3));
   }
   return ECHR_OK;
 }
@@ -979,6 +999,30 @@ static int enqueue_decode(echr_batch* b, int beam, int mode, cudaStream_t st, cu
     // forks off and joins by events.  The branches touch disjoint columns of the activation matrix.
     // (throughput regime: persistent GEMMs; measured better with the attention chain on the forked stream)
     const bool crit_main = rows < gemm2_min_rows();
+    if (!crit_main && fuse_next_query()) {
+      // Throughput regime: every kernel fills the GPU, so nothing is gained by running two of them side by side;
+      // what counts is the number of launches and their tails.  The attention query GEMM of step t + 1 (a
+      // [rows,512] x [512,512] product: 12.7 us as its own launch at 4072 rows, mostly ramp and tail) becomes
+      // the last tiles of the logit launch of step t, and finalize(t) — off the token chain thanks to the
+      // arg-max keys — runs on the forked stream beside attention(t + 1) and gates(t + 1):
+      //   st:   gates(t) -> [logits(t) | query(t+1)] -> attention(t+1) -> gates(t+1) -> ...
+      //   side:                                      -> finalize(t) ----------------------^ (before logits(t+1):
+      //         it reads the partial records and clears the keys that launch accumulates into)
+      ECHR_TRY(enqueue_step(b, rows, 0, topk, nullptr, 0, st, PART_H2ATT | PART_ATT));
+      for (int t = 0; t < S; ++t) {
+        const bool last = t + 1 == S;
+        ECHR_TRY(enqueue_step(b, rows, t, topk, nullptr, 0, st, PART_GATES, true));
+        if (t > 0) ECHR_CUDA(cudaStreamWaitEvent(st, b->cap_events[1], 0));  // finalize(t - 1) done
+        ECHR_TRY(enqueue_step(b, rows, t, topk, nullptr, 0, st, PART_LOGIT | (last ? 0 : PART_NEXT_Q), true));
+        ECHR_CUDA(cudaEventRecord(b->cap_events[0], st));
+        ECHR_CUDA(cudaStreamWaitEvent(side, b->cap_events[0], 0));
+        ECHR_CUDA(launch_finalize_greedy(b, t, b->tokens_dev, b->logp_dev, side, true));
+        ECHR_CUDA(cudaEventRecord(b->cap_events[1], side));
+        if (!last) ECHR_TRY(enqueue_step(b, rows, t + 1, topk, nullptr, 0, st, PART_ATT));
+      }
+      ECHR_CUDA(cudaStreamWaitEvent(st, b->cap_events[1], 0));
+      return ECHR_OK;
+    }
     // The gate GEMM of step t+1 reads its token from the arg-max keys the logit epilogue of step t maintains
     // with atomics (ECHR_ARGMAX_KEYS=0: from finalize's row_tok), so the join waits for the logits only;
     // finalize (log-sum-exp, outputs, `unfinished`) runs beside the next gate GEMM.
@@ -1214,18 +1258,29 @@ extern "C" int echr_time_step_kernels(echr_batch_t* b, int beam, int iters, floa
   const int parts[4] = {PART_H2ATT, PART_ATT, PART_GATES, PART_LOGIT};
   int rc = enqueue_init(b, beam, st);  // fresh state (a finished beam decode leaves every slot dead)
   if (rc == ECHR_OK) rc = enqueue_step(b, rows, 0, beam > 1 ? 4 : 1, nullptr, 0, st);
+  // ... and the bookkeeping of step 0, so that the kernels below see what step 1 of a decode sees: every row its
+  // own input token (with the start token in all rows the gate GEMM's table gather would be one hot 8 KB row)
+  if (rc == ECHR_OK) {
+    const cudaError_t fe = beam > 1 ? launch_finalize_beam(b, beam, 0, b->tokens_dev, b->logp_dev, b->score_dev, st)
+                                    : launch_finalize_greedy(b, 0, b->tokens_dev, b->logp_dev, st);
+    if (fe != cudaSuccess) rc = set_error(ECHR_ERR_CUDA, "echr_time_step_kernels: finalize of step 0 failed");
+  }
   // each kernel: `iters` launches captured into one graph (no host launch gaps between them, like inside the
   // decode graph), replayed once to warm up and once between the two events
   if (rc == ECHR_OK) rc = ensure_capture_streams(b);
   if (rc == ECHR_OK && cudaStreamSynchronize(st) != cudaSuccess) rc = set_error(ECHR_ERR_CUDA, "echr_time_step_kernels: sync failed");
   const bool saved_regime = pdl_regime();
   pdl_regime() = false;  // plain launches: a launch must not overlap the tail of its identical predecessor
-  for (int k = 0; k < 5 && rc == ECHR_OK; ++k) {
+  host_ms[5] = 0.f;
+  const bool fused_q = beam == 1 && rows >= gemm2_min_rows() && fuse_next_query();
+  for (int k = 0; k < 6 && rc == ECHR_OK; ++k) {
+    if (k == 5 && !fused_q) break;
     cudaGraph_t graph = nullptr;
     cudaGraphExec_t exec = nullptr;
     if (cudaStreamBeginCapture(b->cap_stream, cudaStreamCaptureModeRelaxed) != cudaSuccess) { rc = set_error(ECHR_ERR_CUDA, "echr_time_step_kernels: capture failed"); break; }
     for (int i = 0; i < iters && rc == ECHR_OK; ++i) {
       if (k < 4) rc = enqueue_step(b, rows, 1, beam > 1 ? 4 : 1, nullptr, 0, b->cap_stream, parts[k]);
+      else if (k == 5) rc = enqueue_step(b, rows, 1, 1, nullptr, 0, b->cap_stream, PART_LOGIT | PART_NEXT_Q);
       else if (beam > 1) { if (launch_finalize_beam(b, beam, 1, b->tokens_dev, b->logp_dev, b->score_dev, b->cap_stream) != cudaSuccess) rc = set_error(ECHR_ERR_CUDA, "finalize_beam launch failed"); }
       else { if (launch_finalize_greedy(b, 1, b->tokens_dev, b->logp_dev, b->cap_stream) != cudaSuccess) rc = set_error(ECHR_ERR_CUDA, "finalize_greedy launch failed"); }
     }

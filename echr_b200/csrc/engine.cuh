@@ -218,6 +218,7 @@ struct GemmSpec {
   int N = 0, K = 0;
   const float* bias = nullptr;
   int act = 0;  // ACT_NONE
+  bool epi_store = false;  // inside a persistent EPI_LOGITS launch: store epilogue for this problem (gemm_tc2.cuh)
   float* out_f32 = nullptr;
   long long ld_f32 = 0;
   bf16* out_hi = nullptr;

@@ -127,7 +127,7 @@ cudaError_t gemm_launch_split(const GemmParams& P, int groups, int max_m, int gr
 // ---------------------------------------------------------------- persistent 128 x 256 kernel
 template <int A, int W, int EPI, int TOPK>
 static cudaError_t launch_two(const GemmParams& P, int groups, int total_tiles, int num_sms, cudaStream_t stream) {
-  using Cfg = Gemm2Cfg<A, W>;
+  using Cfg = Gemm2Cfg<A, W, gemm2_lstm_staged(A, W, EPI)>;
   const int grid = total_tiles < num_sms ? total_tiles : num_sms;
   auto kern = gemm_tc2_kernel<A, W, EPI, TOPK>;
   static int attr[MAX_DEVICES] = {};  // per instantiation and device

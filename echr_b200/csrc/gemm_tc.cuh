@@ -47,6 +47,7 @@ struct GemmProblem {
   int N;            // valid columns of D (rows of W)
   int num_kb;       // K / 64
   int act;          // EPI_STORE activation
+  int epi_store;    // persistent kernel, EPI_LOGITS launch: this problem takes the EPI_STORE epilogue instead
   int ksplit;       // SPLIT == 2 kernels: 2 = the two CTAs of a cluster each take half of the k-blocks of one
                     // tile and exchange partial accumulators through DSMEM; 1 = every CTA owns its tile
   uint16_t a_kb[GEMM_MAX_KB];  // A column-block index for each k-block; bit 15: the block's low-order

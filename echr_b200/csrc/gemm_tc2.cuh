@@ -18,21 +18,37 @@ namespace echr {
 
 constexpr int GEMM2_BLOCK_N = 256;
 
-template <int A_TERMS, int W_TERMS>
+// LSTM epilogue with its gathered operands staged through shared memory (single-plane precision only: the
+// two-plane precisions have no shared memory to spare next to two operand stages).  Per epilogue warp and
+// 32-column chunk: 32 rows x 128 B of the token gate table + 32 rows x 32 B of cell state.
+constexpr bool gemm2_lstm_staged(int a_terms, int w_terms, int epi) { return epi == EPI_LSTM && a_terms == 1 && w_terms == 1; }
+constexpr int GEMM2_STG_TOK = 32 * 128;
+constexpr int GEMM2_STG_C = 32 * 32;
+constexpr int GEMM2_STG_WARP = GEMM2_STG_TOK + GEMM2_STG_C;        // 5 KB
+constexpr int GEMM2_STG_BYTES = GEMM_EPI_WARPS * GEMM2_STG_WARP;   // 40 KB
+
+template <int A_TERMS, int W_TERMS, bool STAGED = false>
 struct Gemm2Cfg {
   static constexpr int A_PLANE_BYTES = GEMM_BLOCK_M * GEMM_BLOCK_K * 2;   // 16 KB
   static constexpr int W_PLANE_BYTES = GEMM2_BLOCK_N * GEMM_BLOCK_K * 2;  // 32 KB
   static constexpr int STAGE_BYTES = A_TERMS * A_PLANE_BYTES + W_TERMS * W_PLANE_BYTES;
-  static constexpr int STAGES = (200 * 1024) / STAGE_BYTES;  // (1,1): 4, (2,1): 3, (2,2): 2
-  // stages | barriers (256 B) | bias tiles 2 x 256 floats
-  static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 /*align slack*/ + 256 + 2048;
+  static constexpr int STG_BYTES = STAGED ? GEMM2_STG_BYTES : 0;
+  static constexpr int STAGES = (200 * 1024 - STG_BYTES) / STAGE_BYTES;  // (1,1): 4 (3 staged), (2,1): 3, (2,2): 2
+  // stages | barriers (256 B) | bias tiles 2 x 256 floats | epilogue operand staging
+  static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 /*align slack*/ + 256 + 2048 + STG_BYTES;
 };
 
 struct Gemm2Tile {
   int g, m_tile, n_tile;
 };
 
-// linear tile id -> (problem, m tile, n tile); m fastest
+// linear tile id -> (problem, m tile, n tile).  N_FASTEST = false: m fastest, CTAs running together share a weight
+// tile (vocabulary projection: 29 MB of weights, 12 MB of activations).  N_FASTEST = true: the ~148 tiles in flight
+// cover all n tiles of a band of rows, so an activation tile is fetched from HBM once and its other readers hit
+// L2 whatever else streams through it (gate GEMMs: the three weight matrices are 11 MB and stay hot, while the
+// epilogue's gathers of token rows and cell state — 150 MB per launch — would push a row band out of L2 before
+// the next of its 8 n tiles came round).
+template <bool N_FASTEST>
 __device__ __forceinline__ Gemm2Tile gemm2_tile(const GemmParams& P, int groups, int t) {
   Gemm2Tile r;
   r.g = 0;
@@ -43,8 +59,14 @@ __device__ __forceinline__ Gemm2Tile gemm2_tile(const GemmParams& P, int groups,
     t -= mt * nt;
   }
   const int mt = (P.prob[r.g].M + GEMM_BLOCK_M - 1) / GEMM_BLOCK_M;
-  r.n_tile = t / mt;
-  r.m_tile = t - r.n_tile * mt;
+  if constexpr (N_FASTEST) {
+    const int nt = (P.prob[r.g].N + GEMM2_BLOCK_N - 1) / GEMM2_BLOCK_N;
+    r.m_tile = t / nt;
+    r.n_tile = t - r.m_tile * nt;
+  } else {
+    r.n_tile = t / mt;
+    r.m_tile = t - r.n_tile * mt;
+  }
   return r;
 }
 
@@ -55,7 +77,8 @@ __device__ __forceinline__ void named_bar_sync(int id, int threads) {
 template <int A_TERMS, int W_TERMS, int EPI, int TOPK>
 __global__ void __launch_bounds__(GEMM_THREADS, 1)
 gemm_tc2_kernel(const __grid_constant__ GemmParams P, int groups, int total_tiles) {
-  using Cfg = Gemm2Cfg<A_TERMS, W_TERMS>;
+  constexpr bool STAGED = gemm2_lstm_staged(A_TERMS, W_TERMS, EPI);
+  using Cfg = Gemm2Cfg<A_TERMS, W_TERMS, STAGED>;
   constexpr int BN = GEMM2_BLOCK_N;
   trace_begin(P.trace, P.trace_slot);
 
@@ -71,6 +94,9 @@ gemm_tc2_kernel(const __grid_constant__ GemmParams P, int groups, int total_tile
   uint8_t* bar_generic = smem_raw + (bar_base - smem_u32(smem_raw));
   volatile uint32_t* tmem_ptr_generic = reinterpret_cast<volatile uint32_t*>(bar_generic + 160);
   float* sbias = reinterpret_cast<float*>(bar_generic + 256);  // [2][BN]
+  // +176: index of the tile whose epilogue has started (epilogue thread 0 -> prefetch warp; a monotonic counter, so
+  // a prefetch warp that falls behind cannot miss a phase the way a waiter on the tmem_full parities could)
+  volatile int* epi_tile = reinterpret_cast<volatile int*>(bar_generic + 176);
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -90,6 +116,7 @@ gemm_tc2_kernel(const __grid_constant__ GemmParams P, int groups, int total_tile
       mbar_init(tmem_full_bar(b), 1);
       mbar_init(tmem_empty_bar(b), GEMM_EPI_WARPS);
     }
+    *epi_tile = -1;
     fence_mbar_init();
   }
   if (warp == 2) tmem_alloc<512>(tmem_ptr_smem);
@@ -109,7 +136,7 @@ gemm_tc2_kernel(const __grid_constant__ GemmParams P, int groups, int total_tile
       int stage = 0;
       uint32_t phase = 0;
       for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
-        const Gemm2Tile tl = gemm2_tile(P, groups, t);
+        const Gemm2Tile tl = gemm2_tile<EPI == EPI_LSTM>(P, groups, t);
         const GemmProblem& pb = P.prob[tl.g];
         for (int kb = 0; kb < pb.num_kb; ++kb) {
           mbar_wait(empty_bar(stage), phase ^ 1u);
@@ -140,7 +167,7 @@ gemm_tc2_kernel(const __grid_constant__ GemmParams P, int groups, int total_tile
       uint32_t phase = 0;
       int it = 0;
       for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, ++it) {
-        const Gemm2Tile tl = gemm2_tile(P, groups, t);
+        const Gemm2Tile tl = gemm2_tile<EPI == EPI_LSTM>(P, groups, t);
         const GemmProblem& pb = P.prob[tl.g];
         const int buf = it & 1;
         mbar_wait(tmem_empty_bar(buf), ((it >> 1) & 1) ^ 1u);  // epilogue drained this accumulator
@@ -178,24 +205,49 @@ gemm_tc2_kernel(const __grid_constant__ GemmParams P, int groups, int total_tile
   } else if (warp == 3) {
     // ===================== L2 prefetcher (LSTM epilogue only) =====================
     // The epilogue gathers, per output row and tile, 1 KB of the token gate table (a random 8 KB row of a 141 MB
-    // table: an HBM miss), 256 B of cell state and, when hoisted, 1 KB of per-row bias; it can only keep one
-    // 32-column chunk of them in flight (registers).  This otherwise idle warp asks L2 for all of them up front —
-    // every tile of this CTA, right after the predecessor's results are visible — so that the epilogue's loads
-    // hit L2 instead of waiting for HBM chunk by chunk.
-    if constexpr (EPI == EPI_LSTM) {
-      for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
-        const Gemm2Tile tl = gemm2_tile(P, groups, t);
+    // table), 256 B of cell state and, when hoisted, 1 KB of per-row bias.  Inside a decode step none of it is
+    // in L2 (the attention kernel streams > 100 MB of tables between two gate launches).  This otherwise idle
+    // warp asks L2 for the operands of tile i + 1 when the epilogue of tile i starts — one tile (~10 us) ahead:
+    // far enough for HBM, near enough that the lines are still there (asking for all tiles of the CTA up front
+    // is 140 MB over the GPU, more than L2 holds: measured slower than no prefetch at all).  Not in the staged
+    // form: its asynchronous copies already run a chunk ahead (decode of 4072 rows: 5.27 ms with, 5.28 without).
+    if constexpr (EPI == EPI_LSTM && !STAGED) {
+      auto prefetch_tile = [&](int t) {
+        const Gemm2Tile tl = gemm2_tile<EPI == EPI_LSTM>(P, groups, t);
         const GemmProblem& pb = P.prob[tl.g];
         const int col0 = tl.n_tile * BN;
-        for (int i = lane; i < GEMM_BLOCK_M; i += 32) {
-          const long long row = static_cast<long long>(tl.m_tile) * GEMM_BLOCK_M + i;
-          if (row >= pb.M) break;
-          if (pb.tok_table != nullptr) {
-            const int tk = pb.row_key != nullptr ? token_of_key(pb.row_key[row * KEY_STRIDE]) : __ldg(pb.row_tok + row);
-            bulk_prefetch_l2(pb.tok_table + static_cast<long long>(tk) * pb.ld_tok_table + col0, BN * 4);
+        const long long row0 = static_cast<long long>(tl.m_tile) * GEMM_BLOCK_M;
+        int tk[GEMM_BLOCK_M / 32];  // lane l holds the tokens of rows l, l + 32, l + 64, l + 96 (four loads in flight)
+#pragma unroll
+        for (int u = 0; u < GEMM_BLOCK_M / 32; ++u) {
+          const long long row = min(row0 + lane + 32 * u, static_cast<long long>(pb.M) - 1);
+          tk[u] = pb.tok_table == nullptr ? 0
+                  : pb.row_key != nullptr ? token_of_key(pb.row_key[row * KEY_STRIDE]) : __ldg(pb.row_tok + row);
+        }
+        // one 128-byte line per lane and instruction: 8 lines per row of the token table / the per-row bias
+        // (BN floats), 2 per row of the cell state (BN / 4 floats)
+#pragma unroll
+        for (int j = 0; j < GEMM_BLOCK_M / 4; ++j) {
+          const int r = 4 * j + (lane >> 3);
+          const int tkr = __shfl_sync(0xffffffffu, tk[j >> 3], r & 31);
+          if (row0 + r < pb.M) {
+            if (pb.tok_table != nullptr)
+              prefetch_l2_line(pb.tok_table + static_cast<long long>(tkr) * pb.ld_tok_table + col0 + (lane & 7) * 32);
+            if (pb.row_bias != nullptr) prefetch_l2_line(pb.row_bias + (row0 + r) * pb.ld_row_bias + col0 + (lane & 7) * 32);
           }
-          if (pb.row_bias != nullptr) bulk_prefetch_l2(pb.row_bias + row * pb.ld_row_bias + col0, BN * 4);
-          bulk_prefetch_l2(pb.c_in + row * pb.hidden + (col0 >> 2), BN);
+        }
+#pragma unroll
+        for (int j = 0; j < GEMM_BLOCK_M / 16; ++j) {
+          const int r = 16 * j + (lane >> 1);
+          if (row0 + r < pb.M) prefetch_l2_line(pb.c_in + (row0 + r) * pb.hidden + (col0 >> 2) + (lane & 1) * 32);
+        }
+      };
+      int t = blockIdx.x;
+      if (t < total_tiles) {
+        prefetch_tile(t);
+        for (int it = 0; t + static_cast<int>(gridDim.x) < total_tiles; t += gridDim.x, ++it) {
+          while (*epi_tile < it) __nanosleep(200);  // the epilogue of tile `it` has started
+          prefetch_tile(t + gridDim.x);
         }
       }
     }
@@ -209,7 +261,7 @@ gemm_tc2_kernel(const __grid_constant__ GemmParams P, int groups, int total_tile
     const int et = threadIdx.x - 128;  // 0..255
     int it = 0;
     for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, ++it) {
-      const Gemm2Tile tl = gemm2_tile(P, groups, t);
+      const Gemm2Tile tl = gemm2_tile<EPI == EPI_LSTM>(P, groups, t);
       const GemmProblem& pb = P.prob[tl.g];
       const int buf = it & 1;
       const int col0 = tl.n_tile * BN;
@@ -231,8 +283,70 @@ gemm_tc2_kernel(const __grid_constant__ GemmParams P, int groups, int total_tile
                                                                 : __ldg(pb.row_tok + rowc)) * pb.ld_tok_table + col0 + hc0;
         c_row = pb.c_in + rowc * pb.hidden + ((col0 + hc0) >> 2);
       }
+      // Staged form (single-plane precision): the warp copies chunk c of its 32 rows into its own staging buffer
+      // with 16-byte cp.async — 8 lanes per 128 B of a token row, 2 per 32 B of cell state: one memory wavefront
+      // per 128-byte line, where the row-per-thread 32-byte loads below take one per 32 bytes and run into the
+      // load/store unit (measured inside a decode step at 4072 rows: 76 -> 63 us per launch).  Each thread then
+      // reads its own row back (16-byte pieces XOR-swizzled by the row so that a quarter-warp covers all banks).
+      // The copy of chunk c + 1 is issued as soon as chunk c has been read out and lands during its cell update.
+      const uint32_t stg_tok = bar_base + 256u + 2048u + static_cast<uint32_t>(warp - 4) * GEMM2_STG_WARP;
+      const uint32_t stg_c = stg_tok + GEMM2_STG_TOK;
+      int tk_self = 0;
+      if constexpr (STAGED) {
+        if (pb.tok_table != nullptr)
+          tk_self = pb.row_key != nullptr ? token_of_key(pb.row_key[rowc * KEY_STRIDE]) : __ldg(pb.row_tok + rowc);
+      }
+      auto stage_chunk = [&](int c) {
+        if constexpr (STAGED) {
+          const int piece = lane & 7;
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            const int r = 4 * j + (lane >> 3);
+            const int tkr = __shfl_sync(0xffffffffu, tk_self, r);
+            if (pb.tok_table != nullptr)
+              cp_async16(stg_tok + r * 128 + ((piece ^ (r & 7)) << 4),
+                         pb.tok_table + static_cast<long long>(tkr) * pb.ld_tok_table + col0 + hc0 + 32 * c + 4 * piece);
+          }
+          const long long wrow0 = static_cast<long long>(tl.m_tile) * GEMM_BLOCK_M + q * 32;
+#pragma unroll
+          for (int j = 0; j < 2; ++j) {
+            const int r = 16 * j + (lane >> 1);
+            const long long rg = min(wrow0 + r, static_cast<long long>(pb.M) - 1);
+            cp_async16(stg_c + r * 32 + (((lane & 1) ^ ((r >> 2) & 1)) << 4),
+                       pb.c_in + rg * pb.hidden + ((col0 + hc0) >> 2) + 8 * c + 4 * (lane & 1));
+          }
+          cp_async_commit();
+        }
+      };
+      auto take_chunk = [&](int c, float (&bb)[32], float (&cp)[8]) {
+        if constexpr (STAGED) {
+          cp_async_wait_all();
+          __syncwarp();
+#pragma unroll
+          for (int k = 0; k < 8; ++k) {
+            float4 x = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (pb.tok_table != nullptr) x = lds_f32x4(stg_tok + lane * 128 + ((k ^ (lane & 7)) << 4));
+            bb[4 * k] = x.x; bb[4 * k + 1] = x.y; bb[4 * k + 2] = x.z; bb[4 * k + 3] = x.w;
+          }
+#pragma unroll
+          for (int k = 0; k < 2; ++k) {
+            const float4 x = lds_f32x4(stg_c + lane * 32 + ((k ^ ((lane >> 2) & 1)) << 4));
+            cp[4 * k] = x.x; cp[4 * k + 1] = x.y; cp[4 * k + 2] = x.z; cp[4 * k + 3] = x.w;
+          }
+          if (rb_row != nullptr) {  // hoisted context next to the persistent kernel: forced from a debug knob only
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+              float r8[8];
+              ldg_nc_f32x8(rb_row + 32 * c + 8 * i, r8);
+#pragma unroll
+              for (int k = 0; k < 8; ++k) bb[8 * i + k] += r8[k];
+            }
+          }
+          __syncwarp();  // every lane has read its row: the buffer may be refilled
+        }
+      };
       auto lstm_load = [&](int c, float (&bb)[32], float (&cp)[8]) {
-        if constexpr (EPI == EPI_LSTM) {
+        if constexpr (EPI == EPI_LSTM && !STAGED) {
           ldg_nc_f32x8(c_row + 8 * c, cp);
 #pragma unroll
           for (int i = 0; i < 4; ++i) {
@@ -249,7 +363,8 @@ gemm_tc2_kernel(const __grid_constant__ GemmParams P, int groups, int total_tile
           }
         }
       };
-      if constexpr (EPI == EPI_LSTM) lstm_load(0, bbA, cpA);
+      if constexpr (STAGED) stage_chunk(0);
+      else if constexpr (EPI == EPI_LSTM) lstm_load(0, bbA, cpA);
       // bias tile -> smem.  The buffer was last read two tiles ago; every epilogue thread has passed
       // the named barrier of the previous tile since then.
       sb[et] = (pb.bias != nullptr && col0 + et < pb.N) ? __ldg(pb.bias + col0 + et) : 0.f;
@@ -257,8 +372,13 @@ gemm_tc2_kernel(const __grid_constant__ GemmParams P, int groups, int total_tile
       const uint32_t t_row = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + buf * BN + hc0;
       mbar_wait(tmem_full_bar(buf), (it >> 1) & 1);
       tc_fence_after_sync();
+      if (EPI == EPI_LSTM && !STAGED && et == 0) *epi_tile = it;
 
-      if constexpr (EPI == EPI_STORE) {
+      // A problem of a logit launch may ask for the plain store epilogue (GemmProblem::epi_store): the attention
+      // query GEMM of the next decode step rides in the logit launch of this one (engine.cu: enqueue_decode).
+      bool as_store = EPI == EPI_STORE;
+      if constexpr (EPI == EPI_LOGITS) as_store = pb.epi_store != 0;
+      if (EPI != EPI_LSTM && as_store) {
         const int act = pb.act;
 #pragma unroll 1
         for (int c = 0; c < NCH; ++c) {
@@ -310,7 +430,12 @@ gemm_tc2_kernel(const __grid_constant__ GemmParams P, int groups, int total_tile
         // before the wait on the accumulator (lstm_prefetch above).
         static_assert(NCH == 4, "the chunk pipeline below is unrolled by hand");
         auto lstm_chunk = [&](int c, float (&bb)[32], float (&cp)[8], float (&nbb)[32], float (&ncp)[8]) {
-          if (c + 1 < NCH) lstm_load(c + 1, nbb, ncp);
+          if constexpr (STAGED) {
+            take_chunk(c, bb, cp);
+            if (c + 1 < NCH) stage_chunk(c + 1);
+          } else {
+            if (c + 1 < NCH) lstm_load(c + 1, nbb, ncp);
+          }
           const int tc = hc0 + c * 32;
           const int j0 = (col0 + tc) >> 2;  // first hidden unit of this chunk (8 units)
           float v[32];
@@ -343,11 +468,18 @@ gemm_tc2_kernel(const __grid_constant__ GemmParams P, int groups, int total_tile
                   *reinterpret_cast<const uint4*>(hl);
           }
         };
-        lstm_chunk(0, bbA, cpA, bbB, cpB);
-        lstm_chunk(1, bbB, cpB, bbA, cpA);
-        lstm_chunk(2, bbA, cpA, bbB, cpB);
-        lstm_chunk(3, bbB, cpB, bbA, cpA);
-      } else {  // EPI_LOGITS: one record per (row, 64-column group); this thread owns two groups
+        if constexpr (STAGED) {  // one register set: the next chunk waits in shared memory
+          lstm_chunk(0, bbA, cpA, bbA, cpA);
+          lstm_chunk(1, bbA, cpA, bbA, cpA);
+          lstm_chunk(2, bbA, cpA, bbA, cpA);
+          lstm_chunk(3, bbA, cpA, bbA, cpA);
+        } else {
+          lstm_chunk(0, bbA, cpA, bbB, cpB);
+          lstm_chunk(1, bbB, cpB, bbA, cpA);
+          lstm_chunk(2, bbA, cpA, bbB, cpB);
+          lstm_chunk(3, bbB, cpB, bbA, cpA);
+        }
+      } else if constexpr (EPI == EPI_LOGITS) {  // one record per (row, 64-column group); this thread owns two groups
         const int n_groups = ((pb.N + BN - 1) / BN) * (BN / LOGIT_GROUP);
 #pragma unroll 1
         for (int gq = 0; gq < HALF / LOGIT_GROUP; ++gq) {

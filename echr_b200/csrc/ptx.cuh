@@ -151,9 +151,21 @@ __device__ __forceinline__ void bulk_load_1d(uint32_t dst_smem, const void* src,
       : "memory");
 }
 
-// L2 prefetch of a contiguous range (bytes multiple of 16, address 16-byte aligned): a hint, no destination.
-__device__ __forceinline__ void bulk_prefetch_l2(const void* src, uint32_t bytes) {
-  asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(src), "r"(bytes) : "memory");
+// L2 prefetch of the 128-byte line holding `src`, through the load/store unit: a warp asks for 32 lines per
+// instruction (cp.async.bulk.prefetch.L2 costs the copy engine one request per call).
+__device__ __forceinline__ void prefetch_l2_line(const void* src) {
+  asm volatile("prefetch.global.L2 [%0];" ::"l"(src) : "memory");
+}
+// Ampere-style asynchronous 16-byte copy global -> shared (L2 only), no register staging
+__device__ __forceinline__ void cp_async16(uint32_t dst_smem, const void* src) {
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst_smem), "l"(src) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
+__device__ __forceinline__ float4 lds_f32x4(uint32_t addr) {
+  float4 v;
+  asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(addr));
+  return v;
 }
 
 // ---------------------------------------------------------------- tcgen05 / TMEM

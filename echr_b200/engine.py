@@ -332,11 +332,12 @@ class Engine(object):
 
     def time_step_kernels(self, beam=1, iters=20):
         """Average ms per launch of the kernels of one decode step (CUDA events inside the library)."""
-        ms = (ctypes.c_float * 5)()
+        ms = (ctypes.c_float * 6)()
         with torch.cuda.device(self.device):
             check(self.lib.echr_time_step_kernels(self._batch, int(beam), int(iters), ms, _stream()),
                   "echr_time_step_kernels")
-        return dict(zip(("h2att", "attention", "lstm_gates", "logit", "finalize"), [float(x) for x in ms]))
+        return dict(zip(("h2att", "attention", "lstm_gates", "logit", "finalize", "logit_and_next_query"),
+                        [float(x) for x in ms]))
 
     def attention_bytes_per_element(self):
         """Storage width of the attention tables (projection + clip features): fp16 in the single-plane

@@ -334,7 +334,9 @@ ECHR_API int echr_rerank_nms_static(const double* t1, const double* t2, const do
                     double nms_overlap, int topn, int32_t* out_pick, int32_t* out_count, int cap, void* stream);
 
 /* Measurement aid for bench.py's roofline: average duration in ms of each kernel of one decode step
- * (host_ms[5] = h2att GEMM, attention, LSTM gate GEMM, logit GEMM, finalize), from CUDA events on `stream` around a captured graph of `iters` back-to-back plain launches of that
+ * (host_ms[6] = h2att GEMM, attention, LSTM gate GEMM, logit GEMM, finalize, and the logit launch that also carries
+ * the next step's attention query GEMM — what a greedy decode of >= 1024 rows runs instead of slots 3 + 0; 0 when
+ * the batch's decode does not fuse them), from CUDA events on `stream` around a captured graph of `iters` back-to-back plain launches of that
  * kernel (no host launch gaps, as in the decode graph), with the schedule the batch's decode uses (see
  * echr_batch_set_concurrency).  Needs a decoded batch; synchronises. */
 ECHR_API int echr_time_step_kernels(echr_batch_t* batch, int beam, int iters, float* host_ms, void* stream);

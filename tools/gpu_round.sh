@@ -1,5 +1,5 @@
 # One GPU-box pass of the round: parity tests, the driver's bench line, the other configurations, a PCIe probe and
-# the ncu launch list of a (shortened) bench command.   usage: bash tools/gpu_round.sh <tag> [tests|bench|ncu ...]
+# the ncu launch list of a (shortened) bench command.   usage: bash tools/gpu_round.sh <tag> [tests|regimes|bench|q5|quick|trace|ncu ...]
 TAG=${1:-run}; shift
 WHAT=${@:-tests bench ncu}
 O=gpurun_out/$TAG
@@ -9,6 +9,13 @@ tests)
   # (the regime tests in their own process: a crashed kernel there must not poison the rest of the suite)
   timeout 1200 python -m pytest tests/test_0_regimes_gpu.py tests/test_kernels_gpu.py -m gpu -q --tb=short -p no:cacheprovider -rA > $O/pytest_regimes.log 2>&1; echo "pytest exit=$?" >> $O/pytest_regimes.log
   timeout 1500 python -m pytest tests -m gpu -q --tb=short -p no:cacheprovider -rA --deselect tests/test_0_regimes_gpu.py --deselect tests/test_kernels_gpu.py > $O/pytest.log 2>&1; echo "pytest exit=$?" >> $O/pytest.log ;;
+regimes)
+  timeout 1200 python -m pytest tests/test_0_regimes_gpu.py tests/test_kernels_gpu.py -m gpu -q --tb=short -p no:cacheprovider -rA > $O/pytest_regimes.log 2>&1; echo "pytest exit=$?" >> $O/pytest_regimes.log ;;
+q5)
+  timeout 600 python bench.py --steps 10 --no-cpu-baseline > $O/bench_cfg5.json 2> $O/bench_cfg5.err ;;
+trace)
+  # debug-knob build only: kernel timeline of one decode of the default bench's batch shape
+  timeout 300 python tools/trace_decode.py cfg5 f16 1024 > $O/trace_cfg5.txt 2>&1 ;;
 bench)
   timeout 900 python bench.py > $O/bench_cfg5.json 2> $O/bench_cfg5.err
   timeout 600 python bench.py --impl reference --steps 3 --warmup 1 > $O/bench_ref.json 2> $O/bench_ref.err

@@ -27,8 +27,21 @@ ev = [torch.cuda.Event(enable_timing=True) for _ in range(4)]
 ev[0].record(); eng.set_inputs(lay, c3d, tap, lda); ev[1].record(); eng.encode(); ev[2].record(); eng.decode_greedy(); ev[3].record()
 torch.cuda.synchronize()
 print("set_inputs %.3f ms, encode %.3f ms, decode %.3f ms" % (ev[0].elapsed_time(ev[1]), ev[1].elapsed_time(ev[2]), ev[2].elapsed_time(ev[3])))
+# the same three phases with the GPU otherwise idle, five times each (what a lane of the bench adds up to per batch)
+for name, fn in (("set_inputs", lambda: eng.set_inputs(lay, c3d, tap, lda)), ("encode", eng.encode), ("decode_greedy", eng.decode_greedy)):
+    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    torch.cuda.synchronize(); a.record()
+    for _ in range(5):
+        fn()
+    b.record(); torch.cuda.synchronize()
+    print("%-14s %.3f ms per call (5 back to back)" % (name, a.elapsed_time(b) / 5))
+print("time_step_kernels (each kernel alone, back to back, us):", {k: round(v * 1e3, 1) for k, v in eng.time_step_kernels(beam=1, iters=20).items()})
+eng.decode_greedy(); torch.cuda.synchronize()
 tr = eng.trace()
 print("kernels:", len(tr))
+if not tr:
+    print("(no kernel trace: this is not the debug build)")
+    sys.exit(0)
 for i, (k, s, e) in enumerate(tr):
     if i < 14 or i >= len(tr) - 6:
         print("%4d %-11s start %9.2f  end %9.2f  dur %7.2f us" % (i, k, s, e, e - s))
