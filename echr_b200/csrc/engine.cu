@@ -89,6 +89,7 @@ static const char* fill_problem(GemmProblem& pb, const GemmSpec& s, int a_terms,
   pb.out_lo = s.out_lo;
   pb.ld_bf = s.ld_bf;
   pb.c_in = s.c_in;
+  pb.c_src = s.c_src;
   pb.c_out = s.c_out;
   pb.row_bias = s.row_bias;
   pb.ld_row_bias = s.ld_row_bias;
@@ -404,6 +405,7 @@ static void batch_layout(echr_batch* b, Arena& a) {
   b->row_len = a.take<int32_t>(c.max_rows);
   b->unfinished = a.take<int32_t>(c.max_rows);
   b->row_tok = a.take<int32_t>(c.max_rows);
+  b->row_parent = a.take<int32_t>(c.max_rows);
   for (int i = 0; i < 2; ++i) b->argmax_key[i] = a.take<unsigned long long>((size_t)c.max_rows * KEY_STRIDE);
   b->tokens_dev = a.take<int32_t>((size_t)c.max_events * S);
   b->logp_dev = a.take<float>((size_t)c.max_events * S);
@@ -886,8 +888,9 @@ static AttF16Params attention_params(const echr_batch* b, int rows, int t) {
 
 // use_keys (greedy decode): the logit epilogue keeps a packed running arg-max per row (argmax_key[t & 1]) and the
 // gate GEMM of step t + 1 takes its input token from it, so the token chain does not pass through finalize.
+// c_src (beam search): the gate epilogue takes row r's previous cell state from row c_src[r] (the parent slot).
 static int enqueue_step(echr_batch* b, int rows, int t, int topk, float* logits_out, long long ld_logits,
-                        cudaStream_t st, int parts = PART_ALL, bool use_keys = false) {
+                        cudaStream_t st, int parts = PART_ALL, bool use_keys = false, const int32_t* c_src = nullptr) {
   const echr_model* m = b->model;
   const int at = m->cfg.a_terms, wt = m->cfg.w_terms;
   const int p = t & 1, n = p ^ 1;
@@ -943,6 +946,7 @@ static int enqueue_step(echr_batch* b, int rows, int t, int topk, float* logits_
       if (use_keys) s[l].row_key = b->argmax_key[(t + 1) & 1];  // written by the logits of step t - 1 (BOS at t = 0)
       s[l].ksplit = ks[l];
       s[l].c_in = b->cstate[p] + (long long)l * rows * HID;
+      s[l].c_src = c_src;
       s[l].c_out = b->cstate[n] + (long long)l * rows * HID;
       s[l].out_hi = nxt.plane(0) + ACT_H + l * HID;
       s[l].out_lo = at > 1 ? nxt.plane(1) + ACT_H + l * HID : nullptr;
@@ -1058,7 +1062,9 @@ static int enqueue_decode(echr_batch* b, int beam, int mode, cudaStream_t st, cu
     return ECHR_OK;
   }
   for (int t = 0; t < S; ++t) {
-    ECHR_TRY(enqueue_step(b, rows, t, topk, nullptr, 0, st));
+    // beam: finalize_beam(t - 1) reordered h (a TMA operand has to be in place) but left the cell state where it
+    // was and wrote each row's parent row instead
+    ECHR_TRY(enqueue_step(b, rows, t, topk, nullptr, 0, st, PART_ALL, false, mode == MODE_BEAM && t > 0 ? b->row_parent : nullptr));
     if (mode == MODE_BEAM)
       ECHR_CUDA(launch_finalize_beam(b, beam, t, b->tokens_dev, b->logp_dev, b->score_dev, st));
     else

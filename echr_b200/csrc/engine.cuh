@@ -109,6 +109,7 @@ struct echr_batch {
   int32_t *row_start, *row_len;  // attention window per decode row
   int32_t* unfinished;      // [rows]
   int32_t* row_tok;         // [rows] input token of the next step (BOS = 0 at step 0)
+  int32_t* row_parent;      // [rows] beam search: row whose cell state this row continues at the next step
   unsigned long long* argmax_key[2];  // [rows * KEY_STRIDE] packed running arg-max of the logits (greedy), by step parity
   int32_t* tokens_dev;      // [events, S] scratch outputs for echr_caption_host
   float* logp_dev;
@@ -226,6 +227,7 @@ struct GemmSpec {
   long long ld_bf = 0;
   // LSTM
   const float* c_in = nullptr;
+  const int32_t* c_src = nullptr;  // see GemmProblem::c_src
   float* c_out = nullptr;
   const float* row_bias = nullptr;
   long long ld_row_bias = 0;

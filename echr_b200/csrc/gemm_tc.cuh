@@ -61,6 +61,8 @@ struct GemmProblem {
   long long ld_bf;
   // EPI_LSTM
   const float* c_in;   // [M, H]
+  const int32_t* c_src;  // optional [M]: row of c_in that output row r continues (beam search: the parent slot's
+                         // row, so that the cell state is never physically reordered); null = r itself
   float* c_out;        // [M, H]
   const float* row_bias;  // optional [M, N] per-row gate bias (hoisted constant-context terms); replaces bias
   long long ld_row_bias;
@@ -368,7 +370,7 @@ gemm_tc_kernel(const __grid_constant__ GemmParams P) {
       }
       if (row_ok) {
         const float4* cp = reinterpret_cast<const float4*>(
-            pb.c_in + static_cast<long long>(row) * pb.hidden + ((col0 + hc0) >> 2));
+            pb.c_in + static_cast<long long>(pb.c_src != nullptr ? __ldg(pb.c_src + row) : row) * pb.hidden + ((col0 + hc0) >> 2));
 #pragma unroll
         for (int i = 0; i < HALF / 16; ++i) {
           if (16 * i < cpt) {

@@ -239,7 +239,9 @@ gemm_tc2_kernel(const __grid_constant__ GemmParams P, int groups, int total_tile
 #pragma unroll
         for (int j = 0; j < GEMM_BLOCK_M / 16; ++j) {
           const int r = 16 * j + (lane >> 1);
-          if (row0 + r < pb.M) prefetch_l2_line(pb.c_in + (row0 + r) * pb.hidden + (col0 >> 2) + (lane & 1) * 32);
+          if (row0 + r < pb.M)
+            prefetch_l2_line(pb.c_in + (pb.c_src != nullptr ? static_cast<long long>(__ldg(pb.c_src + row0 + r)) : row0 + r) * pb.hidden +
+                             (col0 >> 2) + (lane & 1) * 32);
         }
       };
       int t = blockIdx.x;
@@ -281,7 +283,7 @@ gemm_tc2_kernel(const __grid_constant__ GemmParams P, int groups, int total_tile
           tk_row = pb.tok_table +
                    static_cast<long long>(pb.row_key != nullptr ? token_of_key(pb.row_key[rowc * KEY_STRIDE])
                                                                 : __ldg(pb.row_tok + rowc)) * pb.ld_tok_table + col0 + hc0;
-        c_row = pb.c_in + rowc * pb.hidden + ((col0 + hc0) >> 2);
+        c_row = pb.c_in + (pb.c_src != nullptr ? static_cast<long long>(__ldg(pb.c_src + rowc)) : rowc) * pb.hidden + ((col0 + hc0) >> 2);
       }
       // Staged form (single-plane precision): the warp copies chunk c of its 32 rows into its own staging buffer
       // with 16-byte cp.async — 8 lanes per 128 B of a token row, 2 per 32 B of cell state: one memory wavefront
@@ -292,9 +294,11 @@ gemm_tc2_kernel(const __grid_constant__ GemmParams P, int groups, int total_tile
       const uint32_t stg_tok = bar_base + 256u + 2048u + static_cast<uint32_t>(warp - 4) * GEMM2_STG_WARP;
       const uint32_t stg_c = stg_tok + GEMM2_STG_TOK;
       int tk_self = 0;
+      int csrc_self = static_cast<int>(rowc);  // row of c_in this thread's row continues (GemmProblem::c_src)
       if constexpr (STAGED) {
         if (pb.tok_table != nullptr)
           tk_self = pb.row_key != nullptr ? token_of_key(pb.row_key[rowc * KEY_STRIDE]) : __ldg(pb.row_tok + rowc);
+        if (pb.c_src != nullptr) csrc_self = __ldg(pb.c_src + rowc);
       }
       auto stage_chunk = [&](int c) {
         if constexpr (STAGED) {
@@ -307,11 +311,10 @@ gemm_tc2_kernel(const __grid_constant__ GemmParams P, int groups, int total_tile
               cp_async16(stg_tok + r * 128 + ((piece ^ (r & 7)) << 4),
                          pb.tok_table + static_cast<long long>(tkr) * pb.ld_tok_table + col0 + hc0 + 32 * c + 4 * piece);
           }
-          const long long wrow0 = static_cast<long long>(tl.m_tile) * GEMM_BLOCK_M + q * 32;
 #pragma unroll
           for (int j = 0; j < 2; ++j) {
             const int r = 16 * j + (lane >> 1);
-            const long long rg = min(wrow0 + r, static_cast<long long>(pb.M) - 1);
+            const long long rg = __shfl_sync(0xffffffffu, csrc_self, r);  // (clamped to a valid row with its owner)
             cp_async16(stg_c + r * 32 + (((lane & 1) ^ ((r >> 2) & 1)) << 4),
                        pb.c_in + rg * pb.hidden + ((col0 + hc0) >> 2) + 8 * c + 4 * (lane & 1));
           }

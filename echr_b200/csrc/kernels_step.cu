@@ -1049,7 +1049,7 @@ constexpr int BEAM_SEG = 3 * HID;  // 1536 elements: h of the three streams / c 
 __global__ void __launch_bounds__(BEAM_MAX * 32)
 finalize_beam_kernel(int beam, int n_tiles, int step, int seq_len, const float* __restrict__ partial,
                      int32_t* __restrict__ row_tok, bf16* __restrict__ act_next,
-                     long long act_plane, int planes, float* __restrict__ c_next, long long c_layer_stride,
+                     long long act_plane, int planes, int32_t* __restrict__ row_parent,
                      float* __restrict__ beam_score, int32_t* __restrict__ beam_live,
                      const int32_t* __restrict__ hist_tok_in, int32_t* __restrict__ hist_tok_out,
                      const float* __restrict__ hist_lp_in, float* __restrict__ hist_lp_out,
@@ -1176,12 +1176,17 @@ finalize_beam_kernel(int beam, int n_tiles, int step, int seq_len, const float* 
   if (step + 1 >= seq_len) return;
 
   // ---- 4. next inputs and state reorder
-  if (warp < beam && lane == 0) row_tok[row0 + warp] = sel_tok[warp];
+  if (warp < beam && lane == 0) {
+    row_tok[row0 + warp] = sel_tok[warp];
+    // the cell state (fp32, two thirds of the state bytes) is not moved: the next gate epilogue reads row r's previous
+    // c from row row_parent[r] of the buffer this step wrote (GemmProblem::c_src)
+    row_parent[row0 + warp] = row0 + sel_parent[warp];
+  }
   bool identity = true;
   for (int n = 0; n < beam; ++n) identity = identity && (sel_parent[n] == n);
   if (identity) return;  // uniform across the CTA
-  // Reorder h (bf16 planes of the next activation buffer) and c by parent slot.  A thread owns a column
-  // across all slots of the event (reads the <= 4 values, writes them permuted): no staging, no barriers.
+  // Reorder h (the planes of the next activation buffer: a TMA operand has to be in place) by parent slot.  A thread
+  // owns a column across all slots of the event (reads the <= 4 values, writes them permuted): no staging, no barriers.
   int par[BEAM_MAX];
 #pragma unroll
   for (int n = 0; n < BEAM_MAX; ++n) par[n] = n < beam ? sel_parent[n] : n;
@@ -1204,24 +1209,6 @@ finalize_beam_kernel(int beam, int n_tiles, int step, int seq_len, const float* 
       }
     }
   }
-  for (int c = threadIdx.x; c < BEAM_SEG / 4; c += blockDim.x) {  // float4 words of [layer][unit]
-    const int layer = (4 * c) / HID, u = 4 * c - layer * HID;
-    float* base = c_next + layer * c_layer_stride + (long long)row0 * HID + u;
-    float4 v[BEAM_MAX];
-#pragma unroll
-    for (int n = 0; n < BEAM_MAX; ++n)
-      if (n < beam) v[n] = *reinterpret_cast<const float4*>(base + (long long)n * HID);
-#pragma unroll
-    for (int n = 0; n < BEAM_MAX; ++n) {
-      if (n < beam && par[n] != n) {
-        float4 w = v[0];
-#pragma unroll
-        for (int q = 1; q < BEAM_MAX; ++q)
-          if (par[n] == q) w = v[q];
-        *reinterpret_cast<float4*>(base + (long long)n * HID) = w;
-      }
-    }
-  }
 }
 
 cudaError_t launch_finalize_beam(const echr_batch* b, int beam, int step, int32_t* tokens,
@@ -1237,7 +1224,7 @@ cudaError_t launch_finalize_beam(const echr_batch* b, int beam, int step, int32_
   const int in = step & 1, out = in ^ 1;
   finalize_beam_kernel<<<b->n_events, BEAM_MAX * 32, 0, st>>>(
       beam, n_tiles, step, S, b->partial, b->row_tok, nxt.p,
-      nxt.plane_stride(), (int)nxt.planes, b->cstate[(step + 1) & 1], rows * HID, b->beam_score,
+      nxt.plane_stride(), (int)nxt.planes, b->row_parent, b->beam_score,
       b->beam_live, b->beam_hist_tok + in * hist, b->beam_hist_tok + out * hist,
       b->beam_hist_lp + in * hist, b->beam_hist_lp + out * hist, b->best_score, tokens, logp, score,
       b->beam_trace + (long long)step * b->cap.max_rows, b->beam_trace + ((long long)S + step) * b->cap.max_rows);
