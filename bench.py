@@ -490,6 +490,12 @@ def _main(args):
                              "traffic": tr.get("attention"), "l2_bytes": tr.get("attention_l2"),
                              "bytes_per_element": el, "ms_per_launch": kt["attention"],
                              "kernel": "attention_f16_kernel" if el == 2 else "attention_v2_kernel"}
+    # its second bound: one reciprocal per (row, clip, hidden unit) on the special-function pipe, 16 per clock and SM
+    sfu_ops = sum(e - s for _, s, e in bt.windows) * beam * 512
+    sm_count = torch.cuda.get_device_properties(dev).multi_processor_count
+    sfu_rate = 16.0 * sm_count * (clocks.get("sm_mhz") or clocks.get("sm_max_mhz") or 1965) * 1e6
+    roofline["attention"]["sfu"] = {"ops": sfu_ops, "floor_us": sfu_ops / sfu_rate * 1e6,
+                                    "frac_of_launch": sfu_ops / sfu_rate / att_s}
 
     line = {"metric": METRIC, "value": total_events * args.steps / (ms_dev * 1e-3), "unit": UNIT, "n_gpus": world,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_dev / args.steps,
