@@ -29,9 +29,10 @@
 // Measured (us per launch, W = 2 / 4 / 8): 4072 rows, mean window 25: 40.7 / 41.0 / 52.8; 9600 rows, mean 50:
 // - / 88 / 114; 3200 rows, mean 128: - / 95 / 96; 251 rows: 15.9 / 10.0 / 7.7.
 // Algorithmic bytes per event-step: 2052 L + 2048 (e^{2q} in) + 1000 (att out).
-// Second bound: one reciprocal per (row, clip, hidden unit) on the special-function pipe (16 per clock and SM):
-// 512 L per row-step, i.e. 58 us of the 88 us at 9600 rows x 50 clips, 49 of 95 at 3200 x 128, 12 of 41 at 4072 x 25.
-// Long windows sit on that bound, not on HBM (sharing a window's copies between the beam slots of an event: -3 %).
+// Other bounds: one reciprocal per (row, clip, hidden unit) on the special-function pipe (16 per clock and SM), 512 L
+// per row-step: 30 us of the 84 us of a cfg3 launch, 31 of 91 (cfg4), 11 of 40 (cfg5); and the instruction stream,
+// ~216 warp instructions per clip visit of which ~115 arithmetic: 55-60 % of the launch's issue slots.  Sharing a
+// window's copies between the beam slots of an event changed the time by 3 %: long windows are not copy-bound.
 #pragma once
 #include "ptx.cuh"
 

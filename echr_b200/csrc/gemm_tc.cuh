@@ -252,7 +252,7 @@ gemm_tc_kernel(const __grid_constant__ GemmParams P) {
       int stage = 0;
       uint32_t phase = 0;
       for (int kb = kb_begin; kb < kb_end; ++kb) {
-        mbar_wait(empty_bar(stage), phase ^ 1u);
+        mbar_wait_hot(empty_bar(stage), phase ^ 1u);
         const uint32_t sa = smem_base + stage * Cfg::STAGE_BYTES;
         const uint32_t sw = sa + A_TERMS * Cfg::A_PLANE_BYTES;
         const uint16_t kbe = pb.a_kb[kb];
@@ -279,7 +279,7 @@ gemm_tc_kernel(const __grid_constant__ GemmParams P) {
       uint32_t phase = 0;
       uint32_t accum = 0;
       for (int kb = kb_begin; kb < kb_end; ++kb) {
-        mbar_wait(full_bar(stage), phase);
+        mbar_wait_hot(full_bar(stage), phase);
         tc_fence_after_sync();
         if (kb == kb_begin && P.trace_detail != nullptr)
           atomicAdd(P.trace_detail + 4 * P.trace_slot, global_timer_ns() - *t_start_smem);

@@ -139,7 +139,7 @@ gemm_tc2_kernel(const __grid_constant__ GemmParams P, int groups, int total_tile
         const Gemm2Tile tl = gemm2_tile<EPI == EPI_LSTM>(P, groups, t);
         const GemmProblem& pb = P.prob[tl.g];
         for (int kb = 0; kb < pb.num_kb; ++kb) {
-          mbar_wait(empty_bar(stage), phase ^ 1u);
+          mbar_wait_hot(empty_bar(stage), phase ^ 1u);
           const uint32_t sa = smem_base + stage * Cfg::STAGE_BYTES;
           const uint32_t sw = sa + A_TERMS * Cfg::A_PLANE_BYTES;
           const uint16_t kbe = pb.a_kb[kb];
@@ -175,7 +175,7 @@ gemm_tc2_kernel(const __grid_constant__ GemmParams P, int groups, int total_tile
         const uint32_t acc = tmem_base + buf * BN;
         uint32_t accum = 0;
         for (int kb = 0; kb < pb.num_kb; ++kb) {
-          mbar_wait(full_bar(stage), phase);
+          mbar_wait_hot(full_bar(stage), phase);
           tc_fence_after_sync();
           const uint32_t sa = smem_base + stage * Cfg::STAGE_BYTES;
           const uint32_t sw = sa + A_TERMS * Cfg::A_PLANE_BYTES;

@@ -633,7 +633,7 @@ attention_f16_kernel(const __grid_constant__ AttF16Params P, unsigned long long*
       if (i >= n_mine) break;
       const float inv_s = is_next;
       if (i + 1 < n_mine) is_next = rcp_fast(__ldg(sbase + (i + 1) * ATR_WARPS));
-      mbar_wait(bars + 8u * slot, parity);
+      mbar_wait_hot(bars + 8u * slot, parity);
       const uint32_t sp = ring + slot * ATR_SLOT_BYTES;
       uint4 pu[2], cu[2];
 #pragma unroll

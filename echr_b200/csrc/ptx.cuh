@@ -52,6 +52,14 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
   }
 }
 
+// The same bound without the message: for waits inside hot loops (the printf call of mbar_wait makes the compiler
+// spill live registers around a path that is never taken and reload them on every iteration).
+__device__ __forceinline__ void mbar_wait_hot(uint32_t bar, uint32_t parity) {
+  if (mbar_try_wait(bar, parity)) return;
+  for (unsigned spins = 0; !mbar_try_wait(bar, parity); ++spins)
+    if (spins > (1u << 26)) __trap();  // a try_wait blocks for up to ~1 us by itself: minutes, i.e. a protocol bug
+}
+
 // ---------------------------------------------------------------- thread-block clusters / DSMEM
 __device__ __forceinline__ uint32_t cluster_ctarank() {
   uint32_t r;
