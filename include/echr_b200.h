@@ -22,7 +22,7 @@
 extern "C" {
 #endif
 
-#define ECHR_B200_ABI_VERSION 4
+#define ECHR_B200_ABI_VERSION 5
 
 #if defined(__GNUC__)
 #define ECHR_API __attribute__((visibility("default")))

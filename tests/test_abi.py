@@ -22,7 +22,7 @@ def test_library_exports_every_declared_symbol():
     out = subprocess.run(["nm", "-D", "--defined-only", _lib.LIB_PATH], capture_output=True, text=True).stdout
     exported = {l.split()[-1] for l in out.splitlines() if " T " in l and l.split()[-1].startswith("echr_")}
     assert exported == set(decl), exported ^ set(decl)
-    assert _lib.load().echr_abi_version() == 4
+    assert _lib.load().echr_abi_version() == 5
 
 
 def test_weights_struct_matches_header():
