@@ -272,7 +272,7 @@ gemm_tc2_kernel(const __grid_constant__ GemmParams P, int groups, int total_tile
       float* sb = sbias + buf * BN;
       // LSTM epilogue operands that do not depend on the accumulator (see the chunk pipeline below)
       float bbA[EPI == EPI_LSTM ? 32 : 1], bbB[EPI == EPI_LSTM ? 32 : 1], cpA[EPI == EPI_LSTM ? 8 : 1], cpB[EPI == EPI_LSTM ? 8 : 1];
-      const bool lstm_rb = EPI == EPI_LSTM && (pb.row_bias != nullptr || pb.tok_table != nullptr);
+      const bool lstm_rb = EPI == EPI_LSTM && (STAGED || pb.row_bias != nullptr || pb.tok_table != nullptr);
       const long long rowc = row_ok ? row : (pb.M - 1);  // clamped: the loads below are unconditional
       const float* rb_row = nullptr;
       const float* tk_row = nullptr;
@@ -327,8 +327,13 @@ gemm_tc2_kernel(const __grid_constant__ GemmParams P, int groups, int total_tile
           __syncwarp();
 #pragma unroll
           for (int k = 0; k < 8; ++k) {
-            float4 x = make_float4(0.f, 0.f, 0.f, 0.f);
-            if (pb.tok_table != nullptr) x = lds_f32x4(stg_tok + lane * 128 + ((k ^ (lane & 7)) << 4));
+            float4 x;
+            if (pb.tok_table != nullptr) {
+              x = lds_f32x4(stg_tok + lane * 128 + ((k ^ (lane & 7)) << 4));
+            } else {  // no token table (not a decode step): the plain bias
+              x = pb.bias != nullptr ? __ldg(reinterpret_cast<const float4*>(pb.bias + col0 + hc0 + 32 * c + 4 * k))
+                                     : make_float4(0.f, 0.f, 0.f, 0.f);
+            }
             bb[4 * k] = x.x; bb[4 * k + 1] = x.y; bb[4 * k + 2] = x.z; bb[4 * k + 3] = x.w;
           }
 #pragma unroll
@@ -370,8 +375,12 @@ gemm_tc2_kernel(const __grid_constant__ GemmParams P, int groups, int total_tile
       else if constexpr (EPI == EPI_LSTM) lstm_load(0, bbA, cpA);
       // bias tile -> smem.  The buffer was last read two tiles ago; every epilogue thread has passed
       // the named barrier of the previous tile since then.
-      sb[et] = (pb.bias != nullptr && col0 + et < pb.N) ? __ldg(pb.bias + col0 + et) : 0.f;
-      named_bar_sync(1, GEMM_EPI_WARPS * 32);
+      // (not in the staged form: its bias rides in the token table — or is read directly when there is none — so the
+      //  eight epilogue warps never wait for each other)
+      if constexpr (!STAGED) {
+        sb[et] = (pb.bias != nullptr && col0 + et < pb.N) ? __ldg(pb.bias + col0 + et) : 0.f;
+        named_bar_sync(1, GEMM_EPI_WARPS * 32);
+      }
       const uint32_t t_row = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + buf * BN + hc0;
       mbar_wait(tmem_full_bar(buf), (it >> 1) & 1);
       tc_fence_after_sync();
