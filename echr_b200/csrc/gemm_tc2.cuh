@@ -22,6 +22,7 @@ constexpr int GEMM2_BLOCK_N = 256;
 // two-plane precisions have no shared memory to spare next to two operand stages).  Per epilogue warp and
 // 32-column chunk: 32 rows x 128 B of the token gate table + 32 rows x 32 B of cell state.
 constexpr bool gemm2_lstm_staged(int a_terms, int w_terms, int epi) { return epi == EPI_LSTM && a_terms == 1 && w_terms == 1; }
+constexpr int GEMM2_BIAS_BYTES = GEMM_EPI_WARPS * (GEMM2_BLOCK_N / 2) * 4;  // a private copy of its 128 bias values per epilogue warp
 constexpr int GEMM2_STG_TOK = 32 * 128;
 constexpr int GEMM2_STG_C = 32 * 32;
 constexpr int GEMM2_STG_WARP = GEMM2_STG_TOK + GEMM2_STG_C;        // 5 KB
@@ -34,8 +35,9 @@ struct Gemm2Cfg {
   static constexpr int STAGE_BYTES = A_TERMS * A_PLANE_BYTES + W_TERMS * W_PLANE_BYTES;
   static constexpr int STG_BYTES = STAGED ? GEMM2_STG_BYTES : 0;
   static constexpr int STAGES = (200 * 1024 - STG_BYTES) / STAGE_BYTES;  // (1,1): 4 (3 staged), (2,1): 3, (2,2): 2
-  // stages | barriers (256 B) | bias tiles 2 x 256 floats | epilogue operand staging
-  static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 /*align slack*/ + 256 + 2048 + STG_BYTES;
+  // stages | barriers (256 B) | bias: 128 floats per epilogue warp | epilogue operand staging
+  static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 /*align slack*/ + 256 + GEMM2_BIAS_BYTES + STG_BYTES;
+  static_assert(SMEM_BYTES <= 227 * 1024, "shared memory");
 };
 
 struct Gemm2Tile {
@@ -93,7 +95,7 @@ gemm_tc2_kernel(const __grid_constant__ GemmParams P, int groups, int total_tile
   const uint32_t tmem_ptr_smem = bar_base + 160u;
   uint8_t* bar_generic = smem_raw + (bar_base - smem_u32(smem_raw));
   volatile uint32_t* tmem_ptr_generic = reinterpret_cast<volatile uint32_t*>(bar_generic + 160);
-  float* sbias = reinterpret_cast<float*>(bar_generic + 256);  // [2][BN]
+  float* sbias = reinterpret_cast<float*>(bar_generic + 256);  // [epilogue warp][BN / 2]
   // +176: index of the tile whose epilogue has started (epilogue thread 0 -> prefetch warp; a monotonic counter, so
   // a prefetch warp that falls behind cannot miss a phase the way a waiter on the tmem_full parities could)
   volatile int* epi_tile = reinterpret_cast<volatile int*>(bar_generic + 176);
@@ -269,7 +271,9 @@ gemm_tc2_kernel(const __grid_constant__ GemmParams P, int groups, int total_tile
       const int col0 = tl.n_tile * BN;
       const int row = tl.m_tile * GEMM_BLOCK_M + q * 32 + lane;
       const bool row_ok = row < pb.M;
-      float* sb = sbias + buf * BN;
+      // this warp's own copy of the bias of its 128 columns, indexed by the column within the tile like a whole-tile
+      // buffer would be: no barrier between the epilogue warps, each runs at its own pace
+      float* sb = sbias + (warp - 4) * (BN / 2) - hc0;
       // LSTM epilogue operands that do not depend on the accumulator (see the chunk pipeline below)
       float bbA[EPI == EPI_LSTM ? 32 : 1], bbB[EPI == EPI_LSTM ? 32 : 1], cpA[EPI == EPI_LSTM ? 8 : 1], cpB[EPI == EPI_LSTM ? 8 : 1];
       const bool lstm_rb = EPI == EPI_LSTM && (STAGED || pb.row_bias != nullptr || pb.tok_table != nullptr);
@@ -291,7 +295,7 @@ gemm_tc2_kernel(const __grid_constant__ GemmParams P, int groups, int total_tile
       // load/store unit (measured inside a decode step at 4072 rows: 76 -> 63 us per launch).  Each thread then
       // reads its own row back (16-byte pieces XOR-swizzled by the row so that a quarter-warp covers all banks).
       // The copy of chunk c + 1 is issued as soon as chunk c has been read out and lands during its cell update.
-      const uint32_t stg_tok = bar_base + 256u + 2048u + static_cast<uint32_t>(warp - 4) * GEMM2_STG_WARP;
+      const uint32_t stg_tok = bar_base + 256u + GEMM2_BIAS_BYTES + static_cast<uint32_t>(warp - 4) * GEMM2_STG_WARP;
       const uint32_t stg_c = stg_tok + GEMM2_STG_TOK;
       int tk_self = 0;
       int csrc_self = static_cast<int>(rowc);  // row of c_in this thread's row continues (GemmProblem::c_src)
@@ -373,13 +377,17 @@ gemm_tc2_kernel(const __grid_constant__ GemmParams P, int groups, int total_tile
       };
       if constexpr (STAGED) stage_chunk(0);
       else if constexpr (EPI == EPI_LSTM) lstm_load(0, bbA, cpA);
-      // bias tile -> smem.  The buffer was last read two tiles ago; every epilogue thread has passed
-      // the named barrier of the previous tile since then.
+      // bias of this warp's 128 columns -> its own shared-memory copy
       // (not in the staged form: its bias rides in the token table — or is read directly when there is none — so the
       //  eight epilogue warps never wait for each other)
       if constexpr (!STAGED) {
-        sb[et] = (pb.bias != nullptr && col0 + et < pb.N) ? __ldg(pb.bias + col0 + et) : 0.f;
-        named_bar_sync(1, GEMM_EPI_WARPS * 32);
+        __syncwarp();  // every lane is done with the previous tile's values
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          const int tc = hc0 + 32 * j + lane;
+          sb[tc] = (pb.bias != nullptr && col0 + tc < pb.N) ? __ldg(pb.bias + col0 + tc) : 0.f;
+        }
+        __syncwarp();
       }
       const uint32_t t_row = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + buf * BN + hc0;
       mbar_wait(tmem_full_bar(buf), (it >> 1) & 1);
