@@ -1003,7 +1003,7 @@ static int enqueue_decode(echr_batch* b, int beam, int mode, cudaStream_t st, cu
     // forks off and joins by events.  The branches touch disjoint columns of the activation matrix.
     // (throughput regime: persistent GEMMs; measured better with the attention chain on the forked stream)
     const bool crit_main = rows < gemm2_min_rows();
-    if (!crit_main && fuse_next_query()) {
+    if (!crit_main && fuse_next_query() && use_gemm2(rows, b->model->V1, 128)) {  // (a vocabulary below one tile: not persistent)
       // Throughput regime: every kernel fills the GPU, so nothing is gained by running two of them side by side;
       // what counts is the number of launches and their tails.  The attention query GEMM of step t + 1 (a
       // [rows,512] x [512,512] product: 12.7 us as its own launch at 4072 rows, mostly ramp and tail) becomes
@@ -1278,7 +1278,7 @@ extern "C" int echr_time_step_kernels(echr_batch_t* b, int beam, int iters, floa
   const bool saved_regime = pdl_regime();
   pdl_regime() = false;  // plain launches: a launch must not overlap the tail of its identical predecessor
   host_ms[5] = 0.f;
-  const bool fused_q = beam == 1 && rows >= gemm2_min_rows() && fuse_next_query();
+  const bool fused_q = beam == 1 && rows >= gemm2_min_rows() && fuse_next_query() && use_gemm2(rows, b->model->V1, 128);
   for (int k = 0; k < 6 && rc == ECHR_OK; ++k) {
     if (k == 5 && !fused_q) break;
     cudaGraph_t graph = nullptr;

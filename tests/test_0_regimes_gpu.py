@@ -225,6 +225,39 @@ def test_cfg4_whole_batch_matches_single_videos():
     assert agree > 0.9, agree
 
 
+def test_throughput_regime_with_a_vocabulary_below_one_tile():
+    """>= 1024 rows with a vocabulary narrower than the persistent kernel's 256-column tile: the logit GEMM stays on the
+    one-tile-per-CTA kernel, so the next step's query GEMM cannot ride in it and the decode must fall back to the
+    schedule with the query GEMM as its own launch.  Checked against the same videos decoded in chunks below 1024 rows
+    (the latency-regime kernels, pinned to the oracle by test_engine_gpu.py)."""
+    opt = echr_opt(CG_seq_length=6, CG_vocab_size=200)
+    sd = synth.round_state_dict_bf16(synth.init_state_dict(opt, seed=11))
+    m = CaptionGenerator(opt, precision="f16")
+    m.load_state_dict(sd, strict=True)
+    m = m.to(DEV)
+    vids, _ = synth.make_workload("cfg5", n_videos=280, bf16_features=True)
+    lay, c3d, tap, lda = helpers.batch_of(vids, DEV)
+    assert lay.n_events >= 1024
+    for _ in range(2):  # eager on first sight, the captured graph on the second
+        tok, lp, _ = m.engine.caption_device(lay, c3d, tap, lda, beam=1)
+    tok, lp = tok.cpu(), lp.cpu()
+    assert tuple(tok.shape) == (lay.n_events, 6) and int(tok.max()) <= 200
+    row, same, worst = 0, 0, 0.0
+    for a in range(0, 280, 70):
+        part = vids[a:a + 70]
+        t2, l2, _ = m.engine.caption_device(*helpers.batch_of(part, DEV), beam=1)
+        t2, l2 = t2.cpu(), l2.cpu()
+        n = t2.shape[0]
+        eq = (t2 == tok[row:row + n]).all(1)
+        same += int(eq.sum())
+        if eq.any():
+            worst = max(worst, float((l2[eq] - lp[row:row + n][eq]).abs().max()))
+        row += n
+    assert row == lay.n_events
+    assert same >= 0.97 * row, (same, row)      # the rest: near ties resolved differently by the two GEMM kernels
+    assert worst < LOGP_HELD["f16"], worst
+
+
 # ------------------------------------------------------------------------------------------------ topN = 1000
 def test_one_video_with_1000_proposals():
     """The reference's default selection hands up to topN = 1000 proposals of one video to the caption call
