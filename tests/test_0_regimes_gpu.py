@@ -183,6 +183,16 @@ def test_cfg3_whole_batch_beam3_9600_rows():
           "to the spec's own search" % (clean, n, regret, same))
 
 
+def test_beam3_fp32_in_the_throughput_regime():
+    """Beam 3 over 4 cfg3 videos (1200 decode rows) in the two-plane precision: the persistent gate GEMM with the
+    register-pipelined epilogue reading the cell state through the parent rows finalize_beam wrote; every decision
+    of the first video replayed with the oracle's arithmetic."""
+    vids, _ = synth.make_workload("cfg3", n_videos=4)
+    clean, regret, same, n = _beam_case("fp32", vids, vids[:1])
+    print("beam 3 fp32, 1200 rows: %d of %d events with zero-regret decisions, max regret %.2e, %d identical to the spec's own search"
+          % (clean, n, regret, same))
+
+
 # ------------------------------------------------------------------------------------------------ cfg4
 @pytest.mark.parametrize("precision", ["fp32", "f16"])
 def test_cfg4_video_long_spans(precision):
