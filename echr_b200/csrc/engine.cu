@@ -907,7 +907,9 @@ static int enqueue_step(echr_batch* b, int rows, int t, int topk, float* logits_
     // (lanes sharing the GPU: one wide tile per 128 rows costs a third of the SM time of four narrow ones)
     // (throughput regime: 128 x 64 tiles, one per CTA: a [rows,512] x [512,512] product has only rows/64 tiles of
     // the persistent kernel's 128 x 256 shape, 32 CTAs at 2048 rows)
-    const int bn = rows < gemm2_min_rows() ? (b->concurrency > 1 ? 128 : 32) : 64;
+    // (beam search over thousands of events — from half a 128 x 256 tile per SM on — the persistent kernel; measured
+    // us per launch, 128 x 64 tiles / persistent: 1166 rows 6.9 / 11.9, 2045: 6.8 / 11.6, 4072: 12.6 / 11.9, 9600: 29.3 / 19.4)
+    const int bn = rows < gemm2_min_rows() ? (b->concurrency > 1 ? 128 : 32) : rows >= 32 * num_sms() ? 128 : 64;
     ECHR_TRY(run_gemm(&s, 1, at, wt, bn, EPI_STORE, 1, st, "h2att", b, 0));
   }
   if (parts & PART_ATT) {
