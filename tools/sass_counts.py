@@ -10,7 +10,7 @@ tag = sys.argv[1] if len(sys.argv) > 1 else "r02"
 so = "echr_b200/libechr_b200.so"
 out = subprocess.run(["cuobjdump", "-sass", so], capture_output=True, text=True, check=True).stdout
 names = subprocess.run(["cu++filt"], input="\n".join(re.findall(r"Function : (\S+)", out)), capture_output=True, text=True).stdout.split("\n")
-mn = ("UTCHMMA", "LDTM", "UTMALDG", "UBLKCP", "UTCBAR", "SYNCS", "MUFU", "LDG", "STG", "ATOM", "RED")
+mn = ("UTCHMMA", "LDTM", "UTMALDG", "UBLKCP", "UTCBAR", "SYNCS", "MUFU", "LDGSTS", "LDG", "STG", "ATOM", "RED")
 rows = []
 cur = None
 counts = None
@@ -44,8 +44,8 @@ def short(n):
 with open("profiles/%s_sass_counts.md" % tag, "w") as f:
     f.write("# SASS instruction counts per kernel of `%s` (`cuobjdump -sass`, sm_100a)\n\n" % so)
     f.write("UTCHMMA = tcgen05.mma, LDTM = tcgen05.ld, UTMALDG = cp.async.bulk.tensor (TMA), UBLKCP = cp.async.bulk, UTCBAR = tcgen05.commit, "
-            "SYNCS = mbarrier ops.  Template arguments: gemm_tc_kernel<A_TERMS, W_TERMS, BLOCK_N, EPI (0 store, 1 LSTM, 2 logits), TOPK, "
-            "SPLIT>, gemm_tc2_kernel<A_TERMS, W_TERMS, EPI, TOPK, ATT (attention warps)>, pair_mlp_kernel<A_TERMS, W_TERMS>.\n\n")
+            "SYNCS = mbarrier ops, LDGSTS = cp.async (the staged LSTM epilogue).  Template arguments: gemm_tc_kernel<A_TERMS, W_TERMS, BLOCK_N, "
+            "EPI (0 store, 1 LSTM, 2 logits), TOPK, SPLIT>, gemm_tc2_kernel<A_TERMS, W_TERMS, EPI, TOPK>, pair_mlp_kernel<A_TERMS, W_TERMS>.\n\n")
     f.write("| kernel | instr | " + " | ".join(mn) + " |\n|---|---|" + "---|" * len(mn) + "\n")
     for n, c in sorted(rows, key=lambda r: short(r[0])):
         f.write("| `%s` | %d | %s |\n" % (short(n), c["total"], " | ".join(str(c[k]) for k in mn)))
