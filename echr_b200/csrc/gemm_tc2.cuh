@@ -9,8 +9,10 @@
 //     flattened; m fastest so that CTAs running together share the same weight tile).
 //   * two TMEM accumulators (2 x 256 columns = all of TMEM): the epilogue of tile i overlaps the main
 //     loop of tile i+1 (tmem_full / tmem_empty mbarriers), the TMA ring never drains between tiles.
-// Warp roles: 0 TMA producer, 1 MMA issuer, 2 TMEM allocator, 4..11 epilogue (two warps per TMEM lane
-// quarter; a thread owns one output row x 128 columns).
+// Warp roles: 0 TMA producer, 1 MMA issuer, 2 TMEM allocator, 3 L2 prefetcher of the LSTM epilogue's gathers (two-plane
+// precisions only), 4..11 epilogue (two warps per TMEM lane quarter; a thread owns one output row x 128 columns).
+// The epilogue warps never synchronise with each other: each keeps its own copy of its 128 bias values, and the
+// staged LSTM epilogue (single-plane precision) its own shared-memory buffers for the gathered operands.
 #pragma once
 #include "gemm_tc.cuh"
 
