@@ -74,10 +74,6 @@ __device__ __forceinline__ Gemm2Tile gemm2_tile(const GemmParams& P, int groups,
   return r;
 }
 
-__device__ __forceinline__ void named_bar_sync(int id, int threads) {
-  asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(threads) : "memory");
-}
-
 template <int A_TERMS, int W_TERMS, int EPI, int TOPK>
 __global__ void __launch_bounds__(GEMM_THREADS, 1)
 gemm_tc2_kernel(const __grid_constant__ GemmParams P, int groups, int total_tiles) {
